@@ -1,0 +1,144 @@
+/* b200x — C ABI of the B200-native all-to-all hot path (sort / random_shuffle /
+ * sort-based groupby-aggregate) behind the ray.data block interface.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no torch / Arrow types.
+ * The reference has no native interface for this path (it is Python over
+ * pyarrow/numpy); each entry point below cites the reference call site whose
+ * arithmetic it replaces, relative to /root/reference/python/ray/data/.
+ *
+ * Conventions shared by every entry point
+ *   - Every pointer is a DEVICE pointer unless its name ends in _host.
+ *   - The caller owns every buffer. Entry points that need scratch take
+ *     `void* temp, size_t* temp_bytes`: call once with temp == NULL to get the
+ *     required size in *temp_bytes, then again with a 256-byte aligned buffer.
+ *   - `stream` is a cudaStream_t (NULL = legacy default stream). Calls are
+ *     asynchronous: they enqueue work and return without synchronising.
+ *   - The CUDA device must be current on the calling thread (cudaSetDevice).
+ *   - Return value: 0 = OK; > 0 = argument error (B200X_ERR_*);
+ *     < 0 = -(cudaError_t). b200x_last_error_string() gives the message of the
+ *     last failure on the calling thread. Nothing throws across the ABI.
+ */
+#ifndef B200X_H
+#define B200X_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200X_VERSION 100
+
+/* key column element types (enum KeyType in csrc/common.cuh) */
+#define B200X_KEY_I64 0
+#define B200X_KEY_U64 1
+#define B200X_KEY_F64 2
+#define B200X_KEY_I32 3
+#define B200X_KEY_U32 4
+#define B200X_KEY_F32 5
+#define B200X_KEY_I16 6
+#define B200X_KEY_U16 7
+#define B200X_KEY_I8 8
+#define B200X_KEY_U8 9
+
+/* value column element types for the aggregation kernels */
+#define B200X_VAL_I64 0
+#define B200X_VAL_F64 1
+
+int b200x_version(void);
+const char* b200x_last_error_string(void);
+int b200x_device_count(void);
+
+/* Stable argsort of one key column (onesweep LSD radix sort, 8-bit digits,
+ * decoupled look-back; constant digits are detected on the device and skipped).
+ *   perm_out[i] = row that lands at sorted position i
+ *   codes_out   = (optional, may be NULL) the sorted order-preserving 64-bit key codes;
+ *                 ascending for both sort directions (see b200x_encode_keys)
+ *   perm_in     = (optional) rows are visited in the order perm_in[0..n): the key of
+ *                 position i is keys[perm_in[i]]. Chaining calls from the last key
+ *                 column to the first gives a stable multi-column sort.
+ *   n < 2^30. begin_bit must be 0; end_bit (0 = all) bounds the significant code bits.
+ * Replaces pyarrow.compute.sort_indices in transform_pyarrow.sort / concat_and_sort:
+ *   _internal/arrow_ops/transform_pyarrow.py:17-21, :269-276
+ *   (via ArrowBlockAccessor.sort_and_partition / merge_sorted_blocks, _internal/arrow_block.py:449-464, :554-567) */
+int b200x_radix_argsort(const void* keys, int key_type, int descending, const uint32_t* perm_in, uint32_t* perm_out,
+                        uint64_t* codes_out, size_t n, int begin_bit, int end_bit, void* temp, size_t* temp_bytes,
+                        void* stream);
+
+/* dst[i, :] = src[idx[i], :] for rows of row_bytes bytes (a fixed-width column or a
+ * packed payload). Replaces Table.take: _internal/arrow_ops/transform_pyarrow.py:24-50,
+ * _internal/arrow_block.py:346-355. */
+int b200x_gather_rows(const void* src, size_t row_bytes, const uint32_t* idx, size_t n, void* dst, void* stream);
+
+/* Same gather for ncols 8-byte columns sharing one index vector; srcs_host/dsts_host are HOST
+ * arrays of device pointers. */
+int b200x_gather_columns8(const void* const* srcs_host, void* const* dsts_host, int ncols, const uint32_t* idx, size_t n,
+                          void* stream);
+
+/* out[i] = start + i */
+int b200x_iota_u32(uint32_t* out, size_t n, uint32_t start, void* stream);
+
+/* codes_out[i] = order-preserving 64-bit code of keys[i]: integers in numeric order,
+ * floats with -0.0 == +0.0 and NaN last; descending complements every non-NaN code.
+ * This is the comparison pyarrow's sort applies (call sites as for b200x_radix_argsort). */
+int b200x_encode_keys(const void* keys, int key_type, int descending, size_t n, uint64_t* codes_out, void* stream);
+
+/* out_index[b] = lower bound (upper == 0) or upper bound (upper != 0) of bound_codes[b] in the
+ * ascending array codes[0..n). Replaces find_partition_index / find_partitions:
+ * _internal/util.py:719-758, :761-779 (numpy.searchsorted per boundary). */
+int b200x_search_sorted_codes(const uint64_t* codes, size_t n, const uint64_t* bound_codes, int num_bounds, int upper,
+                              uint64_t* out_index, void* stream);
+
+/* Seeded pseudo-random bijection pi on [0, n) (6-round Feistel network over the smallest
+ * even-width binary domain >= n, cycle-walked into range). Deterministic in (seed, n).
+ *   inverse != 0 evaluates pi^-1.
+ * b200x_permute_rows:   dst[j, :] = src[pi(j), :]      (permutation + take fused, no index array)
+ * b200x_perm_indices:   out[t] = pi(start + t), t in [0, count)
+ * b200x_perm_indices_host: same values computed on the host (out_host is a HOST pointer)
+ * Replaces numpy.random.RandomState(seed).permutation(n) + take in
+ * ArrowBlockAccessor.random_shuffle (_internal/arrow_block.py:249-255), reached from
+ * ShuffleTaskSpec.map / reduce (_internal/planner/exchange/shuffle_task_spec.py:81-84, :119-123).
+ * The MT19937 stream itself is not reproduced: the contract is an exact multiset
+ * permutation that is deterministic per seed. */
+int b200x_permute_rows(const void* src, size_t row_bytes, size_t n, uint64_t seed, int inverse, void* dst, void* stream);
+int b200x_perm_indices(size_t n, uint64_t seed, int inverse, size_t start, size_t count, uint32_t* out, void* stream);
+int b200x_perm_indices_host(size_t n, uint64_t seed, int inverse, size_t start, size_t count, uint32_t* out_host);
+
+/* Group boundaries of an ascending code array: group_starts[g] = first position of group g,
+ * *num_groups_out (device) = number of distinct codes. group_starts needs room for n entries.
+ * Replaces the per-row key comparison loop of ArrowBlockAccessor.combine
+ * (_internal/arrow_block.py:490-515) and GroupedData.map_groups' boundary finder
+ * (grouped_data.py:181-200). */
+int b200x_group_boundaries(const uint64_t* codes, size_t n, uint32_t* group_starts, uint32_t* num_groups_out, void* temp,
+                           size_t* temp_bytes, void* stream);
+
+/* Segmented reduction of one value column over the groups found above (group_starts and the
+ * device scalar num_groups as written by b200x_group_boundaries). Row i of the sorted order
+ * holds values[perm[i]] (perm may be NULL = already in sorted order). For every group g
+ * writes, where the output pointer is not NULL:
+ *   sum_out[g] (int64 wrap-around or float64), min_out[g], max_out[g]  (same type as values)
+ * If center (float64 per group) is given, the reduced quantity is (v - center[g])^2 as float64
+ * (sum of squared differences for Std) and all outputs are float64.
+ * Deterministic for a given n (fixed reduction tree).
+ * Replaces pyarrow.compute.sum/min_max on each group's slice and the accumulator merges:
+ * _internal/arrow_block.py:370-447 (sum/min/max/mean/sum_of_squared_diffs_from_mean),
+ * aggregate/_aggregate.py:105-319, _internal/arrow_block.py:569-680 (aggregate_combined_blocks). */
+int b200x_segmented_reduce(const uint32_t* group_starts, const uint32_t* num_groups, const uint32_t* perm,
+                           const void* values, int value_type, size_t n, const double* center, void* sum_out,
+                           void* min_out, void* max_out, void* temp, size_t* temp_bytes, void* stream);
+
+/* counts_out[g] = rows in group g (int64), g < *num_groups; max_groups bounds the launch.
+ * Replaces Count's accumulate_block (num_rows of the group slice): aggregate/_aggregate.py:90-102. */
+int b200x_group_counts(const uint32_t* group_starts, const uint32_t* num_groups, size_t max_groups, size_t n,
+                       int64_t* counts_out, void* stream);
+
+/* mode 0: out[g] = sum[g] / counts[g]                         (Mean.finalize, aggregate/_aggregate.py:238)
+ * mode 1: out[g] = counts[g] < 2 ? 0 : sqrt(sum[g] / (counts[g] - ddof))   (Std.finalize, :296-302) */
+int b200x_finalize_groups(const void* sum, int value_type, const int64_t* counts, size_t num_groups, int mode, int ddof,
+                          double* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200X_H */

@@ -1,0 +1,114 @@
+"""ctypes binding of libb200x.so (the C ABI in include/b200x.h).
+
+The library is the product: there is no CPU or torch fallback. Importing this
+module never fails (so host-only logic and CPU tests can run), but the first
+call that needs a kernel raises if the shared library is missing or a CUDA
+device is not available.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+import threading
+from ctypes import c_char_p, c_double, c_int, c_size_t, c_uint32, c_uint64, c_void_p, POINTER
+from typing import Optional
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200x.so")
+CSRC_DIR = os.path.join(_HERE, "csrc")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "b200x.h")
+
+KEY_I64, KEY_U64, KEY_F64, KEY_I32, KEY_U32, KEY_F32, KEY_I16, KEY_U16, KEY_I8, KEY_U8 = range(10)
+VAL_I64, VAL_F64 = 0, 1
+
+_size_p = POINTER(c_size_t)
+
+# name -> (restype, argtypes); mirrors include/b200x.h one to one
+SIGNATURES = {
+    "b200x_version": (c_int, []),
+    "b200x_last_error_string": (c_char_p, []),
+    "b200x_device_count": (c_int, []),
+    "b200x_radix_argsort": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_int, c_int,
+                                    c_void_p, _size_p, c_void_p]),
+    "b200x_gather_rows": (c_int, [c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_void_p]),
+    "b200x_gather_columns8": (c_int, [POINTER(c_void_p), POINTER(c_void_p), c_int, c_void_p, c_size_t, c_void_p]),
+    "b200x_iota_u32": (c_int, [c_void_p, c_size_t, c_uint32, c_void_p]),
+    "b200x_encode_keys": (c_int, [c_void_p, c_int, c_int, c_size_t, c_void_p, c_void_p]),
+    "b200x_search_sorted_codes": (c_int, [c_void_p, c_size_t, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "b200x_permute_rows": (c_int, [c_void_p, c_size_t, c_size_t, c_uint64, c_int, c_void_p, c_void_p]),
+    "b200x_perm_indices": (c_int, [c_size_t, c_uint64, c_int, c_size_t, c_size_t, c_void_p, c_void_p]),
+    "b200x_perm_indices_host": (c_int, [c_size_t, c_uint64, c_int, c_size_t, c_size_t, c_void_p]),
+    "b200x_group_boundaries": (c_int, [c_void_p, c_size_t, c_void_p, c_void_p, c_void_p, _size_p, c_void_p]),
+    "b200x_segmented_reduce": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_size_t, c_void_p, c_void_p,
+                                       c_void_p, c_void_p, c_void_p, _size_p, c_void_p]),
+    "b200x_group_counts": (c_int, [c_void_p, c_void_p, c_size_t, c_size_t, c_void_p, c_void_p]),
+    "b200x_finalize_groups": (c_int, [c_void_p, c_int, c_void_p, c_size_t, c_int, c_int, c_void_p, c_void_p]),
+}
+
+
+class B200XError(RuntimeError):
+    """A b200x entry point returned a non-zero status."""
+
+    def __init__(self, fn: str, code: int, message: str):
+        super().__init__(f"{fn} failed with status {code}: {message}")
+        self.fn, self.code, self.message = fn, code, message
+
+
+_lock = threading.Lock()
+_lib: Optional[ctypes.CDLL] = None
+launch_count = 0  # number of b200x entry-point calls that enqueue kernels (bench.py reports it)
+
+
+def build(verbose: bool = False) -> str:
+    """Compile libb200x.so in-tree with nvcc for sm_100a (works without a GPU)."""
+    res = subprocess.run(["make", "-C", CSRC_DIR, "-j8"], capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("building libb200x.so failed:\n" + res.stdout + res.stderr)
+    if verbose:
+        print(res.stdout)
+    return LIB_PATH
+
+
+def load() -> ctypes.CDLL:
+    """Load the library, failing loudly when it is absent (no fallback path exists)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing. Build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                f"(or `make -C {CSRC_DIR}`); this package has no CPU fallback."
+            )
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)  # AttributeError = header / library mismatch: fail loudly
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def call(name: str, *args) -> None:
+    """Call an entry point and raise B200XError on a non-zero status."""
+    global launch_count
+    lib = load()
+    rc = getattr(lib, name)(*args)
+    launch_count += 1
+    if rc != 0:
+        msg = lib.b200x_last_error_string()
+        raise B200XError(name, rc, msg.decode("utf-8", "replace") if msg else "")
+
+
+def query_temp(name: str, *args_before_temp, stream=None) -> int:
+    """Two-phase temp-size query: args up to (not including) temp/temp_bytes/stream."""
+    need = c_size_t(0)
+    lib = load()
+    rc = getattr(lib, name)(*args_before_temp, None, ctypes.byref(need), stream)
+    if rc != 0:
+        msg = lib.b200x_last_error_string()
+        raise B200XError(name, rc, msg.decode("utf-8", "replace") if msg else "")
+    return int(need.value)

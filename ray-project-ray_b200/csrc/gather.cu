@@ -1,0 +1,162 @@
+// Row / column gather: out[i] = in[idx[i]].
+//
+// Replaces pyarrow.Table.take(indices) as used by the reference after every
+// sort_indices / permutation:
+//   transform_pyarrow.take_table     python/ray/data/_internal/arrow_ops/transform_pyarrow.py:24-50
+//   ArrowBlockAccessor.take          python/ray/data/_internal/arrow_block.py:346-355
+//   ArrowBlockAccessor.random_shuffle  (permutation + take)            arrow_block.py:249-255
+//
+// Layout: a fixed-width column is a dense [n, row_bytes] byte matrix (row_bytes
+// = 8 for an int64/float64 column, 64/90/100 for a packed payload). Each row is
+// moved by row_bytes / V consecutive lanes using V-byte accesses, V the widest
+// of 16/8/4/2/1 that divides row_bytes and the base alignment, so that stores
+// are fully coalesced and loads are coalesced per source row.
+#include "common.cuh"
+#include "../../include/b200x.h"
+
+namespace b200x {
+
+template <typename V>
+__global__ void __launch_bounds__(256)
+gather_rows_kernel(const V* __restrict__ src, const uint32_t* __restrict__ idx, V* __restrict__ dst, uint64_t n,
+                   uint32_t vec_per_row) {
+  // one thread per V-sized chunk; grid-stride in units of chunks
+  const uint64_t total = n * vec_per_row;
+  for (uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t r = t / vec_per_row;
+    const uint32_t c = (uint32_t)(t - r * vec_per_row);
+    const uint64_t s = idx[r];
+    dst[t] = src[s * vec_per_row + c];
+  }
+}
+
+// Specialisation for rows of exactly one vector (8- or 16-byte columns): four
+// independent gathers in flight per thread.
+template <typename V>
+__global__ void __launch_bounds__(256)
+gather_elems_kernel(const V* __restrict__ src, const uint32_t* __restrict__ idx, V* __restrict__ dst, uint64_t n) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + 3 * stride < n; i += 4 * stride) {
+    const uint32_t s0 = idx[i], s1 = idx[i + stride], s2 = idx[i + 2 * stride], s3 = idx[i + 3 * stride];
+    const V v0 = src[s0], v1 = src[s1], v2 = src[s2], v3 = src[s3];
+    dst[i] = v0;
+    dst[i + stride] = v1;
+    dst[i + 2 * stride] = v2;
+    dst[i + 3 * stride] = v3;
+  }
+  for (; i < n; i += stride) dst[i] = src[idx[i]];
+}
+
+constexpr int MAX_GATHER_COLS = 16;
+struct ColPtrs {
+  const uint64_t* src[MAX_GATHER_COLS];
+  uint64_t* dst[MAX_GATHER_COLS];
+};
+
+// Several 8-byte columns that share one index vector: the index is read once
+// and ncols independent loads are in flight per thread.
+__global__ void __launch_bounds__(256)
+gather_cols8_kernel(const ColPtrs p, int ncols, const uint32_t* __restrict__ idx, uint64_t n) {
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t s = idx[i];
+    uint64_t v[MAX_GATHER_COLS];
+#pragma unroll
+    for (int c = 0; c < MAX_GATHER_COLS; ++c)
+      if (c < ncols) v[c] = p.src[c][s];
+#pragma unroll
+    for (int c = 0; c < MAX_GATHER_COLS; ++c)
+      if (c < ncols) p.dst[c][i] = v[c];
+  }
+}
+
+__global__ void __launch_bounds__(256) iota_kernel(uint32_t* out, uint64_t n, uint32_t start) {
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    out[i] = start + (uint32_t)i;
+}
+
+static inline uint32_t grid_for(uint64_t work_items, int threads, int per_sm) {
+  uint64_t blocks = (work_items + threads - 1) / threads;
+  const uint64_t cap = (uint64_t)sm_count() * per_sm;
+  if (blocks > cap) blocks = cap;
+  if (blocks == 0) blocks = 1;
+  return (uint32_t)blocks;
+}
+
+}  // namespace b200x
+
+using namespace b200x;
+
+extern "C" int b200x_gather_rows(const void* src, size_t row_bytes, const uint32_t* idx, size_t n, void* dst,
+                                 void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (n == 0 || row_bytes == 0) return B200X_OK;
+  if (src == nullptr || idx == nullptr || dst == nullptr) {
+    set_error("b200x_gather_rows: NULL pointer");
+    return B200X_ERR_ARG;
+  }
+  if (row_bytes > (1u << 20)) {
+    set_error("b200x_gather_rows: row_bytes=%zu too large", row_bytes);
+    return B200X_ERR_TOO_LARGE;
+  }
+  const uintptr_t al = (uintptr_t)src | (uintptr_t)dst | (uintptr_t)row_bytes;
+  int v = 16;
+  while (v > 1 && (al & (uintptr_t)(v - 1)) != 0) v >>= 1;
+  const uint32_t vpr = (uint32_t)(row_bytes / v);
+  const uint64_t total = (uint64_t)n * vpr;
+  if (vpr == 1 && v >= 8) {
+    const uint32_t g = grid_for(n / 4 + 1, 256, 16);
+    if (v == 16)
+      gather_elems_kernel<uint4><<<g, 256, 0, stream>>>((const uint4*)src, idx, (uint4*)dst, n);
+    else
+      gather_elems_kernel<uint64_t><<<g, 256, 0, stream>>>((const uint64_t*)src, idx, (uint64_t*)dst, n);
+    B200X_LAUNCH_CHECK("gather_elems_kernel");
+    return B200X_OK;
+  }
+  const uint32_t g = grid_for(total, 256, 16);
+  switch (v) {
+    case 16: gather_rows_kernel<uint4><<<g, 256, 0, stream>>>((const uint4*)src, idx, (uint4*)dst, n, vpr); break;
+    case 8: gather_rows_kernel<uint64_t><<<g, 256, 0, stream>>>((const uint64_t*)src, idx, (uint64_t*)dst, n, vpr); break;
+    case 4: gather_rows_kernel<uint32_t><<<g, 256, 0, stream>>>((const uint32_t*)src, idx, (uint32_t*)dst, n, vpr); break;
+    case 2: gather_rows_kernel<uint16_t><<<g, 256, 0, stream>>>((const uint16_t*)src, idx, (uint16_t*)dst, n, vpr); break;
+    default: gather_rows_kernel<uint8_t><<<g, 256, 0, stream>>>((const uint8_t*)src, idx, (uint8_t*)dst, n, vpr); break;
+  }
+  B200X_LAUNCH_CHECK("gather_rows_kernel");
+  return B200X_OK;
+}
+
+extern "C" int b200x_gather_columns8(const void* const* srcs, void* const* dsts, int ncols, const uint32_t* idx,
+                                     size_t n, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (n == 0 || ncols == 0) return B200X_OK;
+  if (srcs == nullptr || dsts == nullptr || idx == nullptr || ncols < 0) {
+    set_error("b200x_gather_columns8: bad arguments");
+    return B200X_ERR_ARG;
+  }
+  for (int c0 = 0; c0 < ncols; c0 += MAX_GATHER_COLS) {
+    const int m = (ncols - c0 < MAX_GATHER_COLS) ? ncols - c0 : MAX_GATHER_COLS;
+    ColPtrs p;
+    for (int c = 0; c < MAX_GATHER_COLS; ++c) {
+      p.src[c] = (c < m) ? (const uint64_t*)srcs[c0 + c] : nullptr;
+      p.dst[c] = (c < m) ? (uint64_t*)dsts[c0 + c] : nullptr;
+      if (c < m && (p.src[c] == nullptr || p.dst[c] == nullptr || (((uintptr_t)p.src[c] | (uintptr_t)p.dst[c]) & 7))) {
+        set_error("b200x_gather_columns8: column %d is NULL or not 8-byte aligned", c0 + c);
+        return B200X_ERR_ALIGN;
+      }
+    }
+    gather_cols8_kernel<<<grid_for(n, 256, 16), 256, 0, stream>>>(p, m, idx, n);
+    B200X_LAUNCH_CHECK("gather_cols8_kernel");
+  }
+  return B200X_OK;
+}
+
+extern "C" int b200x_iota_u32(uint32_t* out, size_t n, uint32_t start, void* stream_) {
+  if (n == 0) return B200X_OK;
+  if (out == nullptr) {
+    set_error("b200x_iota_u32: NULL pointer");
+    return B200X_ERR_ARG;
+  }
+  iota_kernel<<<grid_for(n, 256, 16), 256, 0, (cudaStream_t)stream_>>>(out, n, start);
+  B200X_LAUNCH_CHECK("iota_kernel");
+  return B200X_OK;
+}

@@ -1,0 +1,70 @@
+// Key encoding and range-partition boundary search on a sorted block.
+//
+// Replaces find_partition_index / find_partitions
+// (python/ray/data/_internal/util.py:719-758, :761-779), which run
+// numpy.searchsorted per boundary on the sorted key column, and the key
+// normalisation that pyarrow's sort does internally.
+//
+// Because the sorted block is held as order-preserving 64-bit codes that are
+// ascending for BOTH sort directions (descending complements the code), the two
+// reference cases collapse to plain lower/upper bounds on the codes:
+//   ascending : index = #rows <  b  = lower_bound(codes, code(b))   (rows == b go right)
+//   descending: index = #rows >= b  = upper_bound(codes, code(b))   (rows == b go left)
+#include "common.cuh"
+#include "../../include/b200x.h"
+
+namespace b200x {
+
+__global__ void __launch_bounds__(256)
+encode_kernel(const void* __restrict__ raw, int kt, int desc, uint64_t n, uint64_t* __restrict__ codes) {
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    codes[i] = load_encode(raw, i, kt, desc != 0);
+}
+
+__global__ void __launch_bounds__(128)
+search_kernel(const uint64_t* __restrict__ codes, uint64_t n, const uint64_t* __restrict__ bounds, int nb, int upper,
+              uint64_t* __restrict__ out) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nb) return;
+  const uint64_t x = bounds[b];
+  uint64_t lo = 0, hi = n;
+  while (lo < hi) {
+    const uint64_t mid = lo + ((hi - lo) >> 1);
+    const uint64_t v = codes[mid];
+    const bool go_right = upper ? (v <= x) : (v < x);
+    if (go_right) lo = mid + 1; else hi = mid;
+  }
+  out[b] = lo;
+}
+
+}  // namespace b200x
+
+using namespace b200x;
+
+extern "C" int b200x_encode_keys(const void* keys, int key_type, int descending, size_t n, uint64_t* codes_out,
+                                 void* stream_) {
+  if (n == 0) return B200X_OK;
+  if (keys == nullptr || codes_out == nullptr || key_type < 0 || key_type >= KEY_TYPE_COUNT) {
+    set_error("b200x_encode_keys: bad arguments");
+    return B200X_ERR_ARG;
+  }
+  uint64_t blocks = (n + 255) / 256;
+  const uint64_t cap = (uint64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  encode_kernel<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream_>>>(keys, key_type, descending, n, codes_out);
+  B200X_LAUNCH_CHECK("encode_kernel");
+  return B200X_OK;
+}
+
+extern "C" int b200x_search_sorted_codes(const uint64_t* codes, size_t n, const uint64_t* bound_codes, int num_bounds,
+                                         int upper, uint64_t* out_index, void* stream_) {
+  if (num_bounds == 0) return B200X_OK;
+  if (bound_codes == nullptr || out_index == nullptr || num_bounds < 0 || (n > 0 && codes == nullptr)) {
+    set_error("b200x_search_sorted_codes: bad arguments");
+    return B200X_ERR_ARG;
+  }
+  search_kernel<<<(num_bounds + 127) / 128, 128, 0, (cudaStream_t)stream_>>>(codes, n, bound_codes, num_bounds, upper,
+                                                                          out_index);
+  B200X_LAUNCH_CHECK("search_kernel");
+  return B200X_OK;
+}

@@ -1,0 +1,502 @@
+// Stable LSD radix argsort ("onesweep": one histogram sweep up front, then one
+// read + one write of the (code, row-index) pairs per 8-bit digit, chained
+// between thread blocks with decoupled look-back).
+//
+// Replaces, for a device-resident block, the reference's
+//   pyarrow.compute.sort_indices(table, sort_keys=...)
+// call in transform_pyarrow.sort / concat_and_sort
+// (python/ray/data/_internal/arrow_ops/transform_pyarrow.py:17-21, :269-276),
+// reached from ArrowBlockAccessor.sort_and_partition / merge_sorted_blocks
+// (python/ray/data/_internal/arrow_block.py:449-464, :554-567).
+//
+// Properties the parity contract needs:
+//   * stable (equal keys keep input order) in ascending AND descending order
+//     (descending = ascending sort of complemented codes, see common.cuh);
+//   * -0.0 ties with +0.0, NaN sorts last in both directions;
+//   * multi-column keys = chained calls, last key column first, feeding
+//     perm_out of one call as perm_in of the next.
+//
+// Everything is decided on the device (which digits are constant and can be
+// skipped, which buffer a pass reads / writes), so the entry point never
+// synchronises with the host.
+#include "common.cuh"
+#include "../../include/b200x.h"
+
+namespace b200x {
+
+constexpr int RADIX_BITS = 8;
+constexpr int RADIX = 1 << RADIX_BITS;
+constexpr int MAX_PASSES = 8;
+
+// look-back word: [flag:2][count:30]
+constexpr uint32_t LB_FLAG_AGG = 1u << 30;   // tile-local count only
+constexpr uint32_t LB_FLAG_INCL = 2u << 30;  // inclusive prefix over tiles 0..t
+constexpr uint32_t LB_VALUE_MASK = (1u << 30) - 1;
+
+struct SortPlan {
+  uint32_t active[MAX_PASSES];   // 1 if the digit varies over the input
+  uint32_t src_sel[MAX_PASSES];  // ping-pong buffer the pass reads from (ignored for the first active pass)
+  int32_t first;                 // first active pass (-1: none)
+  int32_t last;                  // last active pass (-1: none)
+  uint32_t tile_counter[MAX_PASSES];
+  uint32_t pad[6];
+};
+
+// ---------------------------------------------------------------------------
+// Kernel 1: all-digit histogram of the encoded keys (one read of the key column)
+// ---------------------------------------------------------------------------
+constexpr int HIST_THREADS = 512;
+constexpr int HIST_IPT = 8;
+
+__global__ void __launch_bounds__(HIST_THREADS)
+hist_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ perm_in, int kt, int desc, uint32_t n,
+            int npass, uint32_t* __restrict__ ghist /*[MAX_PASSES][RADIX]*/) {
+  __shared__ uint32_t sh[MAX_PASSES * RADIX];
+  for (int i = threadIdx.x; i < MAX_PASSES * RADIX; i += HIST_THREADS) sh[i] = 0;
+  __syncthreads();
+
+  const uint32_t chunk = HIST_THREADS * HIST_IPT;
+  const unsigned lane = threadIdx.x & 31;
+  for (uint64_t base = (uint64_t)blockIdx.x * chunk; base < n; base += (uint64_t)gridDim.x * chunk) {
+    uint64_t code[HIST_IPT];
+    bool valid[HIST_IPT];
+#pragma unroll
+    for (int j = 0; j < HIST_IPT; ++j) {
+      uint64_t i = base + (uint64_t)j * HIST_THREADS + threadIdx.x;
+      valid[j] = i < n;
+      code[j] = 0;
+      if (valid[j]) {
+        size_t src = perm_in ? (size_t)perm_in[i] : (size_t)i;
+        code[j] = load_encode(raw, src, kt, desc != 0);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < HIST_IPT; ++j) {
+      const unsigned act = __ballot_sync(0xffffffffu, valid[j]);
+      if (!valid[j]) continue;
+      for (int p = 0; p < npass; ++p) {
+        const uint32_t d = (uint32_t)(code[j] >> (p * RADIX_BITS)) & (RADIX - 1);
+        int same;
+        __match_all_sync(act, d, &same);
+        if (same) {
+          // whole warp hits one bin (constant digit): one add instead of a 32-way conflict
+          if (lane == (unsigned)(__ffs(act) - 1)) atomicAdd(&sh[p * RADIX + d], (uint32_t)__popc(act));
+        } else {
+          atomicAdd(&sh[p * RADIX + d], 1u);
+        }
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < npass * RADIX; i += HIST_THREADS) {
+    uint32_t v = sh[i];
+    if (v) atomicAdd(&ghist[i], v);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Kernel 2: per-digit exclusive scan + plan (1 block of RADIX threads)
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(RADIX)
+plan_kernel(uint32_t* __restrict__ ghist, SortPlan* __restrict__ plan, uint32_t n, int npass) {
+  __shared__ uint32_t warp_tot[RADIX / 32];
+  __shared__ uint32_t s_active[MAX_PASSES];
+  const int d = threadIdx.x;
+  const unsigned lane = d & 31, w = d >> 5;
+  if (d < MAX_PASSES) s_active[d] = 0;
+  __syncthreads();
+  for (int p = 0; p < npass; ++p) {
+    const uint32_t c = ghist[p * RADIX + d];
+    // a digit is constant iff one bin holds all n keys
+    if (c != 0 && c != n) s_active[p] = 1;  // benign race: all writers store 1
+    uint32_t x = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= (unsigned)o) x += y;
+    }
+    if (lane == 31) warp_tot[w] = x;
+    __syncthreads();
+    uint32_t off = 0;
+    for (unsigned k = 0; k < w; ++k) off += warp_tot[k];
+    ghist[p * RADIX + d] = off + x - c;  // exclusive
+    __syncthreads();
+  }
+  if (d == 0) {
+    int first = -1, last = -1;
+    uint32_t sel = 0;
+    for (int p = 0; p < MAX_PASSES; ++p) {
+      const uint32_t a = (p < npass) ? s_active[p] : 0;
+      plan->active[p] = a;
+      plan->tile_counter[p] = 0;
+      plan->src_sel[p] = 0;
+      if (a) {
+        if (first < 0) {
+          first = p;  // reads the raw column, writes buffer 0
+          sel = 0;
+        } else {
+          plan->src_sel[p] = sel;
+          sel ^= 1;
+        }
+        last = p;
+      }
+    }
+    plan->first = first;
+    plan->last = last;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Kernel 3: one digit pass
+// ---------------------------------------------------------------------------
+struct PassArgs {
+  const void* raw;          // raw key column (first active pass only)
+  const uint32_t* perm_in;  // optional row indirection for the first pass
+  uint64_t* kbuf[2];        // ping-pong code buffers
+  uint32_t* vbuf[2];        // ping-pong row-index buffers
+  uint64_t* codes_out;      // optional: sorted codes (last pass)
+  uint32_t* perm_out;       // sorted row indices (last pass)
+  const uint32_t* gbase;    // [RADIX] exclusive digit offsets of this pass
+  uint32_t* lookback;       // [tiles][RADIX]
+  SortPlan* plan;
+  uint32_t n;
+  int pass;
+  int kt;
+  int desc;
+};
+
+template <int THREADS, int IPT>
+struct PassSmem {
+  static constexpr int TILE = THREADS * IPT;
+  static constexpr int WARPS = THREADS / 32;
+  static constexpr size_t bytes = (size_t)TILE * 8 + (size_t)TILE * 4 + (size_t)WARPS * RADIX * 4 + RADIX * 4 * 2 + 64;
+};
+
+template <int THREADS, int IPT>
+__global__ void __launch_bounds__(THREADS)
+onesweep_pass_kernel(const PassArgs a) {
+  constexpr int TILE = THREADS * IPT;
+  constexpr int WARPS = THREADS / 32;
+  static_assert(THREADS >= RADIX, "need one thread per digit");
+
+  SortPlan* plan = a.plan;
+  if (!plan->active[a.pass]) return;
+
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  uint64_t* skeys = (uint64_t*)smem_raw;                       // [TILE]
+  uint32_t* svals = (uint32_t*)(skeys + TILE);                 // [TILE]
+  uint32_t* whist = svals + TILE;                              // [WARPS][RADIX]
+  uint32_t* obase = whist + WARPS * RADIX;                     // [RADIX] global base - tile-local start
+  uint32_t* swarp = obase + RADIX;                             // [RADIX/32] scan scratch (+ tile id)
+  __shared__ uint32_t s_tile;
+
+  const int tid = threadIdx.x;
+  const unsigned lane = tid & 31;
+  const int warp = tid >> 5;
+  const int shift = a.pass * RADIX_BITS;
+  const bool is_first = plan->first == a.pass;
+  const bool is_last = plan->last == a.pass;
+
+  // Tiles are handed out in launch order so that a tile only ever waits on
+  // tiles that are already resident (no look-back deadlock).
+  if (tid == 0) s_tile = atomicAdd(&plan->tile_counter[a.pass], 1u);
+  for (int i = tid; i < WARPS * RADIX; i += THREADS) whist[i] = 0;
+  __syncthreads();
+  const uint32_t tile = s_tile;
+  const uint64_t tile_base = (uint64_t)tile * TILE;
+  const uint32_t n = a.n;
+  const uint32_t n_valid = (uint32_t)min((uint64_t)TILE, (uint64_t)n - tile_base);
+
+  const uint64_t* kin;
+  const uint32_t* vin;
+  uint64_t* kout;
+  uint32_t* vout;
+  {
+    const uint32_t sel = plan->src_sel[a.pass];
+    kin = sel ? a.kbuf[1] : a.kbuf[0];
+    vin = sel ? a.vbuf[1] : a.vbuf[0];
+    const uint32_t dsel = is_first ? 0u : (sel ^ 1u);
+    kout = is_last ? a.codes_out : (dsel ? a.kbuf[1] : a.kbuf[0]);
+    vout = is_last ? a.perm_out : (dsel ? a.vbuf[1] : a.vbuf[0]);
+  }
+
+  // ---- load: warp-striped, item j of lane l = tile_base + warp*32*IPT + j*32 + l
+  uint64_t key[IPT];
+  uint32_t val[IPT];
+  const uint32_t wbase = (uint32_t)warp * 32 * IPT + lane;
+#pragma unroll
+  for (int j = 0; j < IPT; ++j) {
+    const uint32_t t = wbase + j * 32;
+    key[j] = ~0ull;
+    val[j] = 0;
+    if (t < n_valid) {
+      const uint64_t i = tile_base + t;
+      if (is_first) {
+        const uint32_t src = a.perm_in ? a.perm_in[i] : (uint32_t)i;
+        key[j] = load_encode(a.raw, src, a.kt, a.desc != 0);
+        val[j] = src;
+      } else {
+        key[j] = ld_stream_u64(kin + i);
+        val[j] = ld_stream_u32(vin + i);
+      }
+    }
+  }
+
+  // ---- rank within the warp (stable: order = (item j, lane))
+  uint32_t* wh = whist + warp * RADIX;
+  uint16_t rank[IPT];
+  const unsigned lt = lanemask_lt();
+#pragma unroll
+  for (int j = 0; j < IPT; ++j) {
+    const uint32_t d = (uint32_t)(key[j] >> shift) & (RADIX - 1);
+    const unsigned peers = __match_any_sync(0xffffffffu, d);
+    const int leader = __ffs(peers) - 1;
+    uint32_t old = 0;
+    if ((int)lane == leader) {
+      old = wh[d];
+      wh[d] = old + __popc(peers);
+    }
+    old = __shfl_sync(0xffffffffu, old, leader);
+    rank[j] = (uint16_t)(old + __popc(peers & lt));
+    __syncwarp();
+  }
+  __syncthreads();
+
+  // ---- per-digit: scan over warps, tile histogram, look-back
+  uint32_t my_count = 0, my_start = 0;
+  if (tid < RADIX) {
+    uint32_t sum = 0;
+#pragma unroll
+    for (int w = 0; w < WARPS; ++w) {
+      const uint32_t c = whist[w * RADIX + tid];
+      whist[w * RADIX + tid] = sum;
+      sum += c;
+    }
+    // padding items of a partial tile all carry digit 255 and sit at the end
+    if (tid == RADIX - 1) sum -= (uint32_t)(TILE - n_valid);
+    my_count = sum;
+    // publish the tile-local count as early as possible
+    volatile uint32_t* lb = a.lookback + (size_t)tile * RADIX + tid;
+    *lb = (tile == 0 ? LB_FLAG_INCL : LB_FLAG_AGG) | my_count;
+
+    // exclusive scan of counts over the 256 digits -> start of each digit inside the tile
+    uint32_t x = my_count;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= (unsigned)o) x += y;
+    }
+    if (lane == 31) swarp[warp] = x;
+    my_start = x - my_count;
+  }
+  __syncthreads();
+  if (tid < RADIX) {
+    uint32_t off = 0;
+    for (int k = 0; k < warp; ++k) off += swarp[k];
+    my_start += off;
+#pragma unroll
+    for (int w = 0; w < WARPS; ++w) whist[w * RADIX + tid] += my_start;
+  }
+  __syncthreads();
+
+  // ---- scatter into shared memory in tile-sorted order
+#pragma unroll
+  for (int j = 0; j < IPT; ++j) {
+    const uint32_t d = (uint32_t)(key[j] >> shift) & (RADIX - 1);
+    const uint32_t pos = wh[d] + rank[j];
+    skeys[pos] = key[j];
+    svals[pos] = val[j];
+  }
+
+  // ---- decoupled look-back (digit threads), overlapped with the scatter above
+  if (tid < RADIX) {
+    uint32_t excl = 0;
+    if (tile > 0) {
+      int64_t t = (int64_t)tile - 1;
+      while (true) {
+        volatile uint32_t* p = a.lookback + (size_t)t * RADIX + tid;
+        uint32_t v = *p;
+        while ((v & ~LB_VALUE_MASK) == 0) {
+          __nanosleep(40);
+          v = *p;
+        }
+        excl += v & LB_VALUE_MASK;
+        if (v & LB_FLAG_INCL) break;
+        --t;
+      }
+      volatile uint32_t* lb = a.lookback + (size_t)tile * RADIX + tid;
+      *lb = LB_FLAG_INCL | (excl + my_count);
+    }
+    obase[tid] = a.gbase[tid] + excl - my_start;
+  }
+  __syncthreads();
+
+  // ---- coalesced write-out: consecutive threads -> consecutive addresses per digit run
+  if (kout != nullptr) {
+    for (uint32_t i = tid; i < n_valid; i += THREADS) {
+      const uint64_t k = skeys[i];
+      const uint32_t d = (uint32_t)(k >> shift) & (RADIX - 1);
+      const uint32_t dst = obase[d] + i;
+      kout[dst] = k;
+      vout[dst] = svals[i];
+    }
+  } else {
+    for (uint32_t i = tid; i < n_valid; i += THREADS) {
+      const uint64_t k = skeys[i];
+      const uint32_t d = (uint32_t)(k >> shift) & (RADIX - 1);
+      vout[obase[d] + i] = svals[i];
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Kernel 4: nothing to sort (every digit constant): identity permutation
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+no_pass_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ perm_in, int kt, int desc, uint32_t n,
+               const SortPlan* __restrict__ plan, uint64_t* __restrict__ codes_out, uint32_t* __restrict__ perm_out) {
+  if (plan->first >= 0) return;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t src = perm_in ? perm_in[i] : (uint32_t)i;
+    perm_out[i] = src;
+    if (codes_out) codes_out[i] = load_encode(raw, src, kt, desc != 0);
+  }
+}
+
+// Tile shape. 512 x 12 keeps (code, index, rank) in < 64 registers so two
+// blocks share an SM, and stages 6144 pairs (72 KB) in shared memory.
+constexpr int PASS_THREADS = 512;
+constexpr int PASS_IPT = 12;
+constexpr int PASS_TILE = PASS_THREADS * PASS_IPT;
+
+struct TempLayout {
+  size_t off_plan, off_hist, off_lookback, off_k0, off_k1, off_v0, off_v1, total;
+  uint32_t tiles;
+};
+
+static TempLayout temp_layout(size_t n, int npass) {
+  TempLayout L;
+  L.tiles = (uint32_t)((n + PASS_TILE - 1) / PASS_TILE);
+  size_t o = 0;
+  L.off_plan = o;      o = align_up(o + sizeof(SortPlan), 256);
+  L.off_hist = o;      o = align_up(o + sizeof(uint32_t) * MAX_PASSES * RADIX, 256);
+  L.off_lookback = o;  o = align_up(o + sizeof(uint32_t) * (size_t)npass * L.tiles * RADIX, 256);
+  L.off_k0 = o;        o = align_up(o + n * 8, 256);
+  L.off_k1 = o;        o = align_up(o + n * 8, 256);
+  L.off_v0 = o;        o = align_up(o + n * 4, 256);
+  L.off_v1 = o;        o = align_up(o + n * 4, 256);
+  L.total = o;
+  return L;
+}
+
+}  // namespace b200x
+
+using namespace b200x;
+
+extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descending, const uint32_t* perm_in,
+                                   uint32_t* perm_out, uint64_t* codes_out, size_t n, int begin_bit, int end_bit,
+                                   void* temp, size_t* temp_bytes, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (temp_bytes == nullptr) {
+    set_error("b200x_radix_argsort: temp_bytes is NULL");
+    return B200X_ERR_ARG;
+  }
+  if (key_type < 0 || key_type >= KEY_TYPE_COUNT) {
+    set_error("b200x_radix_argsort: bad key_type %d", key_type);
+    return B200X_ERR_ARG;
+  }
+  if (n >= ((size_t)1 << 30)) {
+    set_error("b200x_radix_argsort: n=%zu exceeds the 2^30-1 rows one call can sort", n);
+    return B200X_ERR_TOO_LARGE;
+  }
+  const int kbits = key_type_bits(key_type);
+  if (begin_bit != 0) {
+    set_error("b200x_radix_argsort: begin_bit must be 0");
+    return B200X_ERR_ARG;
+  }
+  if (end_bit <= 0 || end_bit > 64) end_bit = 64;
+  // NaN of a 32-bit float maps to the all-ones 64-bit code, so floats always scan all digits
+  int bits = (key_type == KEY_F32 || key_type == KEY_F64) ? 64 : min(kbits, end_bit);
+  const int npass = (bits + RADIX_BITS - 1) / RADIX_BITS;
+
+  const TempLayout L = temp_layout(n, npass);
+  if (temp == nullptr) {
+    *temp_bytes = L.total;
+    return B200X_OK;
+  }
+  if (*temp_bytes < L.total) {
+    set_error("b200x_radix_argsort: temp buffer %zu < required %zu bytes", *temp_bytes, L.total);
+    return B200X_ERR_TEMP;
+  }
+  if (((uintptr_t)temp & 255) != 0) {
+    set_error("b200x_radix_argsort: temp must be 256-byte aligned");
+    return B200X_ERR_ALIGN;
+  }
+  if (n == 0) return B200X_OK;
+  if (keys == nullptr || perm_out == nullptr) {
+    set_error("b200x_radix_argsort: keys/perm_out is NULL");
+    return B200X_ERR_ARG;
+  }
+
+  unsigned char* base = (unsigned char*)temp;
+  SortPlan* plan = (SortPlan*)(base + L.off_plan);
+  uint32_t* ghist = (uint32_t*)(base + L.off_hist);
+  uint32_t* lookback = (uint32_t*)(base + L.off_lookback);
+
+  // plan + histograms + look-back words start at zero (one contiguous clear)
+  B200X_CUDA(cudaMemsetAsync(base, 0, L.off_k0, stream));
+
+  const int sms = sm_count();
+  {
+    const uint32_t chunk = HIST_THREADS * HIST_IPT;
+    uint32_t blocks = (uint32_t)((n + chunk - 1) / chunk);
+    const uint32_t cap = (uint32_t)sms * 4;
+    if (blocks > cap) blocks = cap;
+    hist_kernel<<<blocks, HIST_THREADS, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, npass, ghist);
+    B200X_LAUNCH_CHECK("hist_kernel");
+  }
+  plan_kernel<<<1, RADIX, 0, stream>>>(ghist, plan, (uint32_t)n, npass);
+  B200X_LAUNCH_CHECK("plan_kernel");
+
+  static thread_local int smem_set_dev = -1;
+  constexpr size_t smem = PassSmem<PASS_THREADS, PASS_IPT>::bytes;
+  {
+    int dev = 0;
+    B200X_CUDA(cudaGetDevice(&dev));
+    if (dev != smem_set_dev) {
+      B200X_CUDA(cudaFuncSetAttribute(onesweep_pass_kernel<PASS_THREADS, PASS_IPT>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      smem_set_dev = dev;
+    }
+  }
+
+  PassArgs a;
+  a.raw = keys;
+  a.perm_in = perm_in;
+  a.kbuf[0] = (uint64_t*)(base + L.off_k0);
+  a.kbuf[1] = (uint64_t*)(base + L.off_k1);
+  a.vbuf[0] = (uint32_t*)(base + L.off_v0);
+  a.vbuf[1] = (uint32_t*)(base + L.off_v1);
+  a.codes_out = codes_out;
+  a.perm_out = perm_out;
+  a.plan = plan;
+  a.n = (uint32_t)n;
+  a.kt = key_type;
+  a.desc = descending;
+  for (int p = 0; p < npass; ++p) {
+    a.pass = p;
+    a.gbase = ghist + p * RADIX;
+    a.lookback = lookback + (size_t)p * L.tiles * RADIX;
+    onesweep_pass_kernel<PASS_THREADS, PASS_IPT><<<L.tiles, PASS_THREADS, smem, stream>>>(a);
+    B200X_LAUNCH_CHECK("onesweep_pass_kernel");
+  }
+  {
+    uint32_t blocks = (uint32_t)((n + 255) / 256);
+    const uint32_t cap = (uint32_t)sms * 8;
+    if (blocks > cap) blocks = cap;
+    no_pass_kernel<<<blocks, 256, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, plan, codes_out,
+                                               perm_out);
+    B200X_LAUNCH_CHECK("no_pass_kernel");
+  }
+  return B200X_OK;
+}

@@ -1,0 +1,201 @@
+// Seeded random permutation without an index array: a Feistel bijection on [0, n)
+// evaluated per output row, fused with the row gather.
+//
+// Replaces ArrowBlockAccessor.random_shuffle
+// (python/ray/data/_internal/arrow_block.py:249-255:
+//  numpy.random.RandomState(seed).permutation(n) followed by take), as called by
+// ShuffleTaskSpec.map / reduce
+// (python/ray/data/_internal/planner/exchange/shuffle_task_spec.py:81-84, :119-123).
+//
+// The reference materialises an int64 index vector with a sequential
+// Fisher-Yates walk over the MT19937 stream; neither is reproducible in parallel
+// nor part of the parity contract (pull- and push-based shuffles already give
+// different permutations for one seed). What is kept: an exact permutation,
+// fully determined by (seed, n).
+//
+// pi(x): split x into two k-bit halves (2k = smallest even width with 2^2k >= n),
+// run ROUNDS Feistel rounds with a murmur3-finalizer round function keyed from
+// splitmix64(seed), and repeat ("cycle walk") while the result is >= n. The
+// domain is < 4n, so the expected walk is < 4 steps (usually < 2).
+#include "common.cuh"
+#include "../../include/b200x.h"
+
+namespace b200x {
+
+constexpr int FEISTEL_ROUNDS = 6;
+
+struct PermSpec {
+  uint64_t n;
+  uint32_t half_bits;
+  uint32_t half_mask;
+  uint32_t key[FEISTEL_ROUNDS];
+};
+
+__host__ __device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+
+__host__ __device__ __forceinline__ uint32_t fmix32(uint32_t h) {
+  h ^= h >> 16;
+  h *= 0x85EBCA6Bu;
+  h ^= h >> 13;
+  h *= 0xC2B2AE35u;
+  h ^= h >> 16;
+  return h;
+}
+
+static PermSpec make_spec(uint64_t n, uint64_t seed) {
+  PermSpec s;
+  s.n = n;
+  int bits = 0;
+  while (bits < 64 && (n > 1) && (((uint64_t)1 << bits) < n)) ++bits;  // bits = ceil(log2(n))
+  uint32_t k = (uint32_t)((bits + 1) / 2);
+  if (k == 0) k = 1;
+  s.half_bits = k;
+  s.half_mask = (k >= 32) ? 0xFFFFFFFFu : ((1u << k) - 1u);
+  uint64_t st = seed;
+  for (int r = 0; r < FEISTEL_ROUNDS; ++r) {
+    st = splitmix64(st + (uint64_t)r);
+    s.key[r] = (uint32_t)(st >> 32);
+  }
+  return s;
+}
+
+__host__ __device__ __forceinline__ uint64_t feistel_fwd_once(const PermSpec& s, uint64_t x) {
+  uint32_t L = (uint32_t)(x >> s.half_bits) & s.half_mask;
+  uint32_t R = (uint32_t)x & s.half_mask;
+#pragma unroll
+  for (int r = 0; r < FEISTEL_ROUNDS; ++r) {
+    const uint32_t F = fmix32(R * 0x9E3779B1u + s.key[r]) & s.half_mask;
+    const uint32_t nl = R;
+    R = L ^ F;
+    L = nl;
+  }
+  return ((uint64_t)L << s.half_bits) | R;
+}
+
+__host__ __device__ __forceinline__ uint64_t feistel_inv_once(const PermSpec& s, uint64_t x) {
+  uint32_t L = (uint32_t)(x >> s.half_bits) & s.half_mask;
+  uint32_t R = (uint32_t)x & s.half_mask;
+#pragma unroll
+  for (int r = FEISTEL_ROUNDS - 1; r >= 0; --r) {
+    const uint32_t pr = L;
+    const uint32_t F = fmix32(pr * 0x9E3779B1u + s.key[r]) & s.half_mask;
+    L = R ^ F;
+    R = pr;
+  }
+  return ((uint64_t)L << s.half_bits) | R;
+}
+
+__host__ __device__ __forceinline__ uint64_t perm_eval(const PermSpec& s, uint64_t x, bool inverse) {
+  if (s.n <= 1) return x;
+  do {
+    x = inverse ? feistel_inv_once(s, x) : feistel_fwd_once(s, x);
+  } while (x >= s.n);
+  return x;
+}
+
+__global__ void __launch_bounds__(256)
+perm_indices_kernel(const PermSpec s, int inverse, uint64_t start, uint64_t count, uint32_t* __restrict__ out) {
+  for (uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; t < count; t += (uint64_t)gridDim.x * blockDim.x)
+    out[t] = (uint32_t)perm_eval(s, start + t, inverse != 0);
+}
+
+// dst[j] = src[pi(j)], rows of vec_per_row V-sized chunks. LANES_PER_ROW consecutive
+// lanes (a power of two <= 32) share one row so that pi is evaluated once per row.
+template <typename V>
+__global__ void __launch_bounds__(256)
+permute_rows_kernel(const V* __restrict__ src, V* __restrict__ dst, const PermSpec s, int inverse,
+                    uint32_t vec_per_row, uint32_t lanes_per_row) {
+  const uint64_t n = s.n;
+  const uint32_t lane_in_row = threadIdx.x % lanes_per_row;
+  const uint64_t rows_per_iter = ((uint64_t)gridDim.x * blockDim.x) / lanes_per_row;
+  uint64_t r = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / lanes_per_row;
+  for (; r < n; r += rows_per_iter) {
+    const uint64_t sr = perm_eval(s, r, inverse != 0);
+    const V* sp = src + sr * vec_per_row;
+    V* dp = dst + r * vec_per_row;
+    for (uint32_t c = lane_in_row; c < vec_per_row; c += lanes_per_row) dp[c] = sp[c];
+  }
+}
+
+}  // namespace b200x
+
+using namespace b200x;
+
+static int check_perm_n(const char* fn, size_t n) {
+  if (n > 0xFFFFFFFFull) {
+    set_error("%s: n=%zu exceeds 2^32-1 rows", fn, n);
+    return B200X_ERR_TOO_LARGE;
+  }
+  return B200X_OK;
+}
+
+extern "C" int b200x_perm_indices(size_t n, uint64_t seed, int inverse, size_t start, size_t count, uint32_t* out,
+                                  void* stream_) {
+  if (int rc = check_perm_n("b200x_perm_indices", n)) return rc;
+  if (count == 0) return B200X_OK;
+  if (out == nullptr || start + count > n) {
+    set_error("b200x_perm_indices: bad range [%zu, %zu) of %zu or NULL out", start, start + count, n);
+    return B200X_ERR_ARG;
+  }
+  const PermSpec s = make_spec(n, seed);
+  uint64_t blocks = (count + 255) / 256;
+  const uint64_t cap = (uint64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  perm_indices_kernel<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream_>>>(s, inverse, start, count, out);
+  B200X_LAUNCH_CHECK("perm_indices_kernel");
+  return B200X_OK;
+}
+
+extern "C" int b200x_perm_indices_host(size_t n, uint64_t seed, int inverse, size_t start, size_t count,
+                                       uint32_t* out_host) {
+  if (int rc = check_perm_n("b200x_perm_indices_host", n)) return rc;
+  if (count == 0) return B200X_OK;
+  if (out_host == nullptr || start + count > n) {
+    set_error("b200x_perm_indices_host: bad range or NULL out");
+    return B200X_ERR_ARG;
+  }
+  const PermSpec s = make_spec(n, seed);
+  for (size_t t = 0; t < count; ++t) out_host[t] = (uint32_t)perm_eval(s, start + t, inverse != 0);
+  return B200X_OK;
+}
+
+extern "C" int b200x_permute_rows(const void* src, size_t row_bytes, size_t n, uint64_t seed, int inverse, void* dst,
+                                  void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (int rc = check_perm_n("b200x_permute_rows", n)) return rc;
+  if (n == 0 || row_bytes == 0) return B200X_OK;
+  if (src == nullptr || dst == nullptr) {
+    set_error("b200x_permute_rows: NULL pointer");
+    return B200X_ERR_ARG;
+  }
+  if (row_bytes > (1u << 20)) {
+    set_error("b200x_permute_rows: row_bytes=%zu too large", row_bytes);
+    return B200X_ERR_TOO_LARGE;
+  }
+  const PermSpec s = make_spec(n, seed);
+  const uintptr_t al = (uintptr_t)src | (uintptr_t)dst | (uintptr_t)row_bytes;
+  int v = 16;
+  while (v > 1 && (al & (uintptr_t)(v - 1)) != 0) v >>= 1;
+  const uint32_t vpr = (uint32_t)(row_bytes / v);
+  uint32_t lpr = 1;
+  while (lpr < vpr && lpr < 32) lpr <<= 1;
+  const uint64_t threads_needed = (uint64_t)n * lpr;
+  uint64_t blocks = (threads_needed + 255) / 256;
+  const uint64_t cap = (uint64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  const uint32_t g = (uint32_t)blocks;
+  switch (v) {
+    case 16: permute_rows_kernel<uint4><<<g, 256, 0, stream>>>((const uint4*)src, (uint4*)dst, s, inverse, vpr, lpr); break;
+    case 8: permute_rows_kernel<uint64_t><<<g, 256, 0, stream>>>((const uint64_t*)src, (uint64_t*)dst, s, inverse, vpr, lpr); break;
+    case 4: permute_rows_kernel<uint32_t><<<g, 256, 0, stream>>>((const uint32_t*)src, (uint32_t*)dst, s, inverse, vpr, lpr); break;
+    case 2: permute_rows_kernel<uint16_t><<<g, 256, 0, stream>>>((const uint16_t*)src, (uint16_t*)dst, s, inverse, vpr, lpr); break;
+    default: permute_rows_kernel<uint8_t><<<g, 256, 0, stream>>>((const uint8_t*)src, (uint8_t*)dst, s, inverse, vpr, lpr); break;
+  }
+  B200X_LAUNCH_CHECK("permute_rows_kernel");
+  return B200X_OK;
+}

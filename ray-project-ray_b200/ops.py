@@ -1,0 +1,255 @@
+"""Thin tensor-level wrappers over the C ABI.
+
+torch is used here only to own device buffers (`torch.empty`), to hand over
+`data_ptr()` / the current CUDA stream, and to switch the current device. All
+arithmetic happens in libb200x.so; there is no torch or CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import (KEY_F32, KEY_F64, KEY_I8, KEY_I16, KEY_I32, KEY_I64, KEY_U8, KEY_U16, KEY_U32, KEY_U64, VAL_F64,
+                   VAL_I64)
+
+_KEY_TYPES = {
+    torch.int64: KEY_I64, torch.float64: KEY_F64, torch.int32: KEY_I32, torch.float32: KEY_F32,
+    torch.int16: KEY_I16, torch.int8: KEY_I8, torch.uint8: KEY_U8,
+}
+for _name, _kt in (("uint64", KEY_U64), ("uint32", KEY_U32), ("uint16", KEY_U16)):
+    if hasattr(torch, _name):
+        _KEY_TYPES[getattr(torch, _name)] = _kt
+
+MAX_SORT_ROWS = (1 << 30) - 1
+
+
+def key_type_of(t: torch.Tensor) -> int:
+    try:
+        return _KEY_TYPES[t.dtype]
+    except KeyError:
+        raise TypeError(f"unsupported key dtype {t.dtype}; supported: {sorted(map(str, _KEY_TYPES))}") from None
+
+
+def _require_cuda(*tensors: Optional[torch.Tensor]) -> torch.device:
+    dev = None
+    for t in tensors:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise RuntimeError("b200x ops need CUDA tensors: the device path has no CPU fallback")
+        if not t.is_contiguous():
+            raise ValueError("b200x ops need contiguous tensors")
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise ValueError(f"tensors on different devices: {dev} vs {t.device}")
+    if dev is None:
+        raise ValueError("no tensor given")
+    return dev
+
+
+def _stream(dev: torch.device) -> int:
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _temp(nbytes: int, dev: torch.device) -> torch.Tensor:
+    return torch.empty(max(nbytes, 256), dtype=torch.uint8, device=dev)
+
+
+def argsort(keys: torch.Tensor, descending: bool = False, perm_in: Optional[torch.Tensor] = None,
+            want_codes: bool = False, end_bit: int = 0) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    """Stable argsort of a 1-D key column. Returns (perm uint32-as-int32 tensor, sorted codes or None).
+
+    The permutation is stored in an int32 tensor whose bits are the uint32 row indices.
+    """
+    dev = _require_cuda(keys, perm_in)
+    if keys.dim() != 1:
+        raise ValueError("keys must be 1-D")
+    n = keys.numel() if perm_in is None else perm_in.numel()
+    if n > MAX_SORT_ROWS:
+        raise ValueError(f"one sort call handles at most {MAX_SORT_ROWS} rows, got {n}")
+    kt = key_type_of(keys)
+    perm_out = torch.empty(n, dtype=torch.int32, device=dev)
+    codes = torch.empty(n, dtype=torch.int64, device=dev) if want_codes else None
+    with torch.cuda.device(dev):
+        st = _stream(dev)
+        need = _lib.query_temp("b200x_radix_argsort", _ptr(keys), kt, int(descending), _ptr(perm_in), _ptr(perm_out),
+                               _ptr(codes), n, 0, end_bit, stream=st)
+        temp = _temp(need, dev)
+        nb = ctypes.c_size_t(temp.numel())
+        _lib.call("b200x_radix_argsort", _ptr(keys), kt, int(descending), _ptr(perm_in), _ptr(perm_out), _ptr(codes),
+                  n, 0, end_bit, temp.data_ptr(), ctypes.byref(nb), st)
+        temp.record_stream(torch.cuda.current_stream(dev))
+    return perm_out, codes
+
+
+def gather(col: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+    """out[i] = col[idx[i]] along dim 0 for a contiguous fixed-width column ([n] or [n, ...])."""
+    dev = _require_cuda(col, idx)
+    n = idx.numel()
+    out = torch.empty((n,) + tuple(col.shape[1:]), dtype=col.dtype, device=dev)
+    if n == 0:
+        return out
+    row_bytes = col.element_size()
+    for s in col.shape[1:]:
+        row_bytes *= s
+    with torch.cuda.device(dev):
+        _lib.call("b200x_gather_rows", col.data_ptr(), row_bytes, idx.data_ptr(), n, out.data_ptr(), _stream(dev))
+    return out
+
+
+def gather_columns(cols: Sequence[torch.Tensor], idx: torch.Tensor) -> List[torch.Tensor]:
+    """Gather several columns with one index vector; 8-byte 1-D columns share one launch."""
+    outs: List[Optional[torch.Tensor]] = [None] * len(cols)
+    n = idx.numel()
+    eight = [i for i, c in enumerate(cols) if c.dim() == 1 and c.element_size() == 8]
+    if len(eight) >= 2 and n > 0:
+        dev = _require_cuda(idx, *[cols[i] for i in eight])
+        for i in eight:
+            outs[i] = torch.empty(n, dtype=cols[i].dtype, device=dev)
+        srcs = (ctypes.c_void_p * len(eight))(*[cols[i].data_ptr() for i in eight])
+        dsts = (ctypes.c_void_p * len(eight))(*[outs[i].data_ptr() for i in eight])
+        with torch.cuda.device(dev):
+            _lib.call("b200x_gather_columns8", srcs, dsts, len(eight), idx.data_ptr(), n, _stream(dev))
+    for i, c in enumerate(cols):
+        if outs[i] is None:
+            outs[i] = gather(c, idx)
+    return outs  # type: ignore[return-value]
+
+
+def iota(n: int, dev: torch.device, start: int = 0) -> torch.Tensor:
+    out = torch.empty(n, dtype=torch.int32, device=dev)
+    if n:
+        with torch.cuda.device(dev):
+            _lib.call("b200x_iota_u32", out.data_ptr(), n, start, _stream(dev))
+    return out
+
+
+def encode_keys(keys: torch.Tensor, descending: bool = False) -> torch.Tensor:
+    dev = _require_cuda(keys)
+    out = torch.empty(keys.numel(), dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        _lib.call("b200x_encode_keys", keys.data_ptr(), key_type_of(keys), int(descending), keys.numel(),
+                  out.data_ptr(), _stream(dev))
+    return out
+
+
+def search_sorted_codes(codes: torch.Tensor, bound_codes: torch.Tensor, upper: bool) -> torch.Tensor:
+    dev = _require_cuda(codes, bound_codes)
+    out = torch.empty(bound_codes.numel(), dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        _lib.call("b200x_search_sorted_codes", codes.data_ptr(), codes.numel(), bound_codes.data_ptr(),
+                  bound_codes.numel(), int(upper), out.data_ptr(), _stream(dev))
+    return out
+
+
+def permute_rows(col: torch.Tensor, seed: int, inverse: bool = False) -> torch.Tensor:
+    """out[j] = col[pi_seed(j)] — seeded permutation fused with the row gather."""
+    dev = _require_cuda(col)
+    out = torch.empty_like(col)
+    n = col.shape[0]
+    if n == 0:
+        return out
+    row_bytes = col.element_size()
+    for s in col.shape[1:]:
+        row_bytes *= s
+    with torch.cuda.device(dev):
+        _lib.call("b200x_permute_rows", col.data_ptr(), row_bytes, n, seed & 0xFFFFFFFFFFFFFFFF, int(inverse),
+                  out.data_ptr(), _stream(dev))
+    return out
+
+
+def perm_indices(n: int, seed: int, dev: torch.device, inverse: bool = False, start: int = 0,
+                 count: Optional[int] = None) -> torch.Tensor:
+    count = n - start if count is None else count
+    out = torch.empty(count, dtype=torch.int32, device=dev)
+    if count:
+        with torch.cuda.device(dev):
+            _lib.call("b200x_perm_indices", n, seed & 0xFFFFFFFFFFFFFFFF, int(inverse), start, count, out.data_ptr(),
+                      _stream(dev))
+    return out
+
+
+def perm_indices_host(n: int, seed: int, inverse: bool = False, start: int = 0, count: Optional[int] = None):
+    """The same permutation evaluated by the library on the host (small n: slice-order shuffles)."""
+    import numpy as np
+
+    count = n - start if count is None else count
+    out = np.empty(count, dtype=np.uint32)
+    if count:
+        _lib.call("b200x_perm_indices_host", n, seed & 0xFFFFFFFFFFFFFFFF, int(inverse), start, count,
+                  out.ctypes.data_as(ctypes.c_void_p))
+        _lib.launch_count -= 1  # host-only entry point
+    return out
+
+
+def group_boundaries(codes: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """(group_starts int32[n] (first num_groups valid), num_groups int32[1]) of an ascending code array."""
+    dev = _require_cuda(codes)
+    n = codes.numel()
+    starts = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+    ng = torch.zeros(1, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        st = _stream(dev)
+        need = _lib.query_temp("b200x_group_boundaries", codes.data_ptr(), n, starts.data_ptr(), ng.data_ptr(),
+                               stream=st)
+        temp = _temp(need, dev)
+        nb = ctypes.c_size_t(temp.numel())
+        _lib.call("b200x_group_boundaries", codes.data_ptr(), n, starts.data_ptr(), ng.data_ptr(), temp.data_ptr(),
+                  ctypes.byref(nb), st)
+    return starts, ng
+
+
+def value_type_of(t: torch.Tensor) -> int:
+    if t.dtype == torch.int64:
+        return VAL_I64
+    if t.dtype == torch.float64:
+        return VAL_F64
+    raise TypeError(f"aggregation needs an int64 or float64 column, got {t.dtype}")
+
+
+def segmented_reduce(starts: torch.Tensor, ng: torch.Tensor, num_groups: int, perm: Optional[torch.Tensor],
+                     values: torch.Tensor, n: int, want_sum=True, want_min=False, want_max=False,
+                     center: Optional[torch.Tensor] = None):
+    """Per-group (sum, min, max) of values[perm] over sorted runs; entries not requested are None."""
+    dev = _require_cuda(starts, ng, perm, values, center)
+    vt = value_type_of(values)
+    out_dtype = torch.float64 if center is not None else values.dtype
+    mk = lambda want: torch.empty(num_groups, dtype=out_dtype, device=dev) if want else None  # noqa: E731
+    s, mn, mx = mk(want_sum), mk(want_min), mk(want_max)
+    with torch.cuda.device(dev):
+        st = _stream(dev)
+        need = _lib.query_temp("b200x_segmented_reduce", starts.data_ptr(), ng.data_ptr(), _ptr(perm),
+                               values.data_ptr(), vt, n, _ptr(center), _ptr(s), _ptr(mn), _ptr(mx), stream=st)
+        temp = _temp(need, dev)
+        nb = ctypes.c_size_t(temp.numel())
+        _lib.call("b200x_segmented_reduce", starts.data_ptr(), ng.data_ptr(), _ptr(perm), values.data_ptr(), vt, n,
+                  _ptr(center), _ptr(s), _ptr(mn), _ptr(mx), temp.data_ptr(), ctypes.byref(nb), st)
+    return s, mn, mx
+
+
+def group_counts(starts: torch.Tensor, ng: torch.Tensor, num_groups: int, n: int) -> torch.Tensor:
+    dev = _require_cuda(starts, ng)
+    out = torch.empty(num_groups, dtype=torch.int64, device=dev)
+    if num_groups:
+        with torch.cuda.device(dev):
+            _lib.call("b200x_group_counts", starts.data_ptr(), ng.data_ptr(), num_groups, n, out.data_ptr(),
+                      _stream(dev))
+    return out
+
+
+def finalize_groups(sums: torch.Tensor, counts: torch.Tensor, mode: int, ddof: int = 1) -> torch.Tensor:
+    dev = _require_cuda(sums, counts)
+    out = torch.empty(sums.numel(), dtype=torch.float64, device=dev)
+    if sums.numel():
+        with torch.cuda.device(dev):
+            _lib.call("b200x_finalize_groups", sums.data_ptr(), value_type_of(sums), counts.data_ptr(), sums.numel(),
+                      mode, ddof, out.data_ptr(), _stream(dev))
+    return out

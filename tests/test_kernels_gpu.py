@@ -1,0 +1,196 @@
+"""GPU parity tests of the individual C-ABI kernels against numpy restatements."""
+import numpy as np
+import pytest
+import torch
+
+from ray_project_ray_b200 import ops
+from oracle import exchange_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+def _u32(t):
+    return t.cpu().numpy().view(np.uint32)
+
+
+def _keys(kind, n, rng):
+    if kind == "i64_full":
+        return rng.integers(np.iinfo(np.int64).min, np.iinfo(np.int64).max, n, dtype=np.int64)
+    if kind == "i64_small":
+        return rng.integers(-500, 500, n, dtype=np.int64)
+    if kind == "i64_perm":
+        return rng.permutation(n).astype(np.int64)
+    if kind == "i64_const":
+        return np.full(n, 7, dtype=np.int64)
+    if kind == "f64":
+        x = rng.standard_normal(n)
+        if n >= 16:
+            x[rng.integers(0, n, n // 8)] = np.nan
+            x[rng.integers(0, n, n // 8)] = 0.0
+            x[rng.integers(0, n, n // 8)] = -0.0
+            x[rng.integers(0, n, 3)] = np.inf
+            x[rng.integers(0, n, 3)] = -np.inf
+            x[rng.integers(0, n, 3)] = np.float64(np.nan) * -1
+        return x
+    if kind == "f64_ties":
+        return rng.integers(-20, 20, n).astype(np.float64) / 4
+    if kind == "i32":
+        return rng.integers(-2**31, 2**31 - 1, n, dtype=np.int64).astype(np.int32)
+    if kind == "f32":
+        x = rng.standard_normal(n).astype(np.float32)
+        if n >= 16:
+            x[rng.integers(0, n, n // 8)] = np.nan
+            x[rng.integers(0, n, n // 8)] = -0.0
+        return x
+    if kind == "u8":
+        return rng.integers(0, 256, n, dtype=np.int64).astype(np.uint8)
+    if kind == "i16":
+        return rng.integers(-2**15, 2**15, n, dtype=np.int64).astype(np.int16)
+    raise KeyError(kind)
+
+
+@pytest.mark.parametrize("kind", ["i64_full", "i64_small", "i64_perm", "i64_const", "f64", "f64_ties", "i32", "f32", "u8", "i16"])
+@pytest.mark.parametrize("n", [0, 1, 2, 31, 33, 1000, 6143, 6144, 6145, 100_003, 1_500_000])
+@pytest.mark.parametrize("descending", [False, True])
+def test_argsort_matches_oracle(cuda_device, kind, n, descending):
+    rng = np.random.default_rng(1234 + n)
+    k = _keys(kind, n, rng)
+    want = orc.stable_argsort(k, descending)
+    t = torch.from_numpy(k).to(cuda_device)
+    perm, codes = ops.argsort(t, descending, want_codes=True)
+    torch.cuda.synchronize()
+    got = _u32(perm)
+    assert got.dtype == np.uint32 and got.shape == (n,)
+    np.testing.assert_array_equal(got, want.astype(np.uint32))
+    want_codes = orc.encode_keys(k, descending)[want]
+    np.testing.assert_array_equal(codes.cpu().numpy().view(np.uint64), want_codes)
+
+
+def test_argsort_uint64_and_uint16(cuda_device):
+    rng = np.random.default_rng(5)
+    n = 200_000
+    hi = rng.integers(0, 2**63, n, dtype=np.int64).astype(np.uint64) * 2 + rng.integers(0, 2, n).astype(np.uint64)
+    hi[: n // 4] = hi[n // 4 : n // 2]  # ties on the major key
+    lo = rng.integers(0, 2**16, n, dtype=np.int64).astype(np.uint16)
+    want = orc.stable_argsort_multi([hi, lo], False)
+    thi = torch.from_numpy(hi.view(np.int64)).to(cuda_device).view(torch.uint64)
+    tlo = torch.from_numpy(lo.view(np.int16)).to(cuda_device).view(torch.uint16)
+    p1, _ = ops.argsort(tlo, False)
+    p2, _ = ops.argsort(thi, False, perm_in=p1)
+    np.testing.assert_array_equal(_u32(p2), want.astype(np.uint32))
+    # descending multi-column: both columns descending, ties keep input order
+    want = orc.stable_argsort_multi([hi, lo], True)
+    p1, _ = ops.argsort(tlo, True)
+    p2, _ = ops.argsort(thi, True, perm_in=p1)
+    np.testing.assert_array_equal(_u32(p2), want.astype(np.uint32))
+
+
+@pytest.mark.parametrize("shape,dtype", [((1000,), np.int64), ((1000,), np.float64), ((5000, 8), np.int64),
+                                         ((3000, 64), np.uint8), ((3000, 90), np.uint8), ((3000, 100), np.uint8),
+                                         ((777, 3), np.int16), ((1000,), np.int32), ((1000,), np.uint8), ((0, 8), np.int64)])
+def test_gather_rows(cuda_device, shape, dtype):
+    rng = np.random.default_rng(7)
+    src = rng.integers(0, 120, shape).astype(dtype)
+    n = shape[0]
+    idx = rng.integers(0, max(n, 1), 2 * n).astype(np.int32) if n else np.zeros(0, np.int32)
+    out = ops.gather(torch.from_numpy(src).to(cuda_device), torch.from_numpy(idx).to(cuda_device))
+    np.testing.assert_array_equal(out.cpu().numpy(), src[idx])
+
+
+def test_gather_columns(cuda_device):
+    rng = np.random.default_rng(8)
+    n = 50_000
+    cols = [rng.integers(0, 2**62, n, dtype=np.int64) for _ in range(9)] + [rng.standard_normal(n)]
+    pay = rng.integers(0, 255, (n, 24)).astype(np.uint8)
+    idx = rng.permutation(n).astype(np.int32)
+    outs = ops.gather_columns([torch.from_numpy(c).to(cuda_device) for c in cols] + [torch.from_numpy(pay).to(cuda_device)],
+                              torch.from_numpy(idx).to(cuda_device))
+    for o, c in zip(outs, cols + [pay]):
+        np.testing.assert_array_equal(o.cpu().numpy(), c[idx])
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 17, 1000, 65_536, 65_537, 1_000_003])
+@pytest.mark.parametrize("seed", [0, 1, 2**40 + 3])
+def test_permutation_is_bijection_and_matches_oracle(cuda_device, n, seed):
+    fwd = _u32(ops.perm_indices(n, seed, cuda_device))
+    assert np.array_equal(np.sort(fwd), np.arange(n, dtype=np.uint32))
+    np.testing.assert_array_equal(fwd, orc.feistel_permutation(n, seed))
+    np.testing.assert_array_equal(fwd, ops.perm_indices_host(n, seed))
+    inv = _u32(ops.perm_indices(n, seed, cuda_device, inverse=True))
+    np.testing.assert_array_equal(inv[fwd], np.arange(n, dtype=np.uint32))
+    if n > 1000:
+        other = _u32(ops.perm_indices(n, seed + 1, cuda_device))
+        assert (other != fwd).mean() > 0.9
+        assert (fwd != np.arange(n)).mean() > 0.9
+
+
+@pytest.mark.parametrize("shape,dtype", [((10_000,), np.int64), ((10_000, 64), np.uint8), ((4_097, 72), np.uint8),
+                                         ((5_000, 100), np.uint8), ((3, 8), np.int64)])
+def test_permute_rows(cuda_device, shape, dtype):
+    rng = np.random.default_rng(9)
+    src = rng.integers(0, 120, shape).astype(dtype)
+    out = ops.permute_rows(torch.from_numpy(src).to(cuda_device), seed=11)
+    p = orc.feistel_permutation(shape[0], 11)
+    np.testing.assert_array_equal(out.cpu().numpy(), src[p])
+    back = ops.permute_rows(out, seed=11, inverse=True)
+    # out[j] = src[pi(j)]; back[j] = out[pi^-1(j)] = src[pi(pi^-1(j))] = src[j]
+    np.testing.assert_array_equal(back.cpu().numpy(), src)
+
+
+@pytest.mark.parametrize("n,ngroups", [(1, 1), (10, 3), (2048, 1), (2049, 2049), (100_000, 7), (100_000, 50_000), (300_000, 1000)])
+@pytest.mark.parametrize("vkind", ["i64", "f64"])
+def test_groupby_kernels(cuda_device, n, ngroups, vkind):
+    rng = np.random.default_rng(n + ngroups)
+    keys = np.sort(rng.integers(0, ngroups, n, dtype=np.int64))
+    vals = rng.integers(-2**40, 2**40, n, dtype=np.int64) if vkind == "i64" else rng.standard_normal(n) * 1e3
+    perm = rng.permutation(n).astype(np.int32)
+    vals_unsorted = np.empty_like(vals)
+    vals_unsorted[perm] = vals  # values[perm[i]] == vals[i]
+    codes = torch.from_numpy(orc.encode_keys(keys, False).view(np.int64)).to(cuda_device)
+    starts, ng = ops.group_boundaries(codes)
+    G = int(ng.item())
+    uk, ustart, ucount = np.unique(keys, return_index=True, return_counts=True)
+    assert G == len(uk)
+    np.testing.assert_array_equal(starts[:G].cpu().numpy(), ustart.astype(np.int32))
+    s, mn, mx = ops.segmented_reduce(starts, ng, G, torch.from_numpy(perm).to(cuda_device),
+                                     torch.from_numpy(vals_unsorted).to(cuda_device), n, True, True, True)
+    cnt = ops.group_counts(starts, ng, G, n)
+    np.testing.assert_array_equal(cnt.cpu().numpy(), ucount)
+    ws = np.add.reduceat(vals, ustart)
+    wmn = np.minimum.reduceat(vals, ustart)
+    wmx = np.maximum.reduceat(vals, ustart)
+    if vkind == "i64":
+        np.testing.assert_array_equal(s.cpu().numpy(), ws)
+    else:
+        np.testing.assert_allclose(s.cpu().numpy(), ws, rtol=1e-9, atol=1e-6)
+    np.testing.assert_array_equal(mn.cpu().numpy(), wmn)
+    np.testing.assert_array_equal(mx.cpu().numpy(), wmx)
+    mean = ops.finalize_groups(s, cnt, 0)
+    np.testing.assert_allclose(mean.cpu().numpy(), ws / ucount, rtol=1e-9, atol=1e-9)
+    # sum of squared differences from the group mean (Std)
+    m2, _, _ = ops.segmented_reduce(starts, ng, G, torch.from_numpy(perm).to(cuda_device),
+                                    torch.from_numpy(vals_unsorted).to(cuda_device), n, True, False, False, center=mean)
+    want_m2 = np.add.reduceat((vals.astype(np.float64) - np.repeat(ws / ucount, ucount)) ** 2, ustart)
+    np.testing.assert_allclose(m2.cpu().numpy(), want_m2, rtol=1e-6, atol=1e-3)
+    std = ops.finalize_groups(m2, cnt, 1, 1)
+    want_std = np.where(ucount < 2, 0.0, np.sqrt(want_m2 / np.maximum(ucount - 1, 1)))
+    np.testing.assert_allclose(std.cpu().numpy(), want_std, rtol=1e-6, atol=1e-6)
+    # second run is bit-identical (fixed reduction order)
+    s2, _, _ = ops.segmented_reduce(starts, ng, G, torch.from_numpy(perm).to(cuda_device),
+                                    torch.from_numpy(vals_unsorted).to(cuda_device), n, True, False, False)
+    assert torch.equal(s, s2)
+
+
+def test_search_sorted_codes(cuda_device):
+    rng = np.random.default_rng(3)
+    keys = np.sort(rng.integers(0, 1000, 20_000, dtype=np.int64))
+    codes = orc.encode_keys(keys, False)
+    bounds = np.array([-5, 0, 1, 500, 999, 1000, 5000], dtype=np.int64)
+    bc = orc.encode_keys(bounds, False)
+    tc = torch.from_numpy(codes.view(np.int64)).to(cuda_device)
+    tb = torch.from_numpy(bc.view(np.int64)).to(cuda_device)
+    lo = ops.search_sorted_codes(tc, tb, upper=False).cpu().numpy()
+    hi = ops.search_sorted_codes(tc, tb, upper=True).cpu().numpy()
+    np.testing.assert_array_equal(lo, np.searchsorted(keys, bounds, side="left"))
+    np.testing.assert_array_equal(hi, np.searchsorted(keys, bounds, side="right"))
+    np.testing.assert_array_equal(ops.encode_keys(torch.from_numpy(keys).to(cuda_device)).cpu().numpy().view(np.uint64), codes)
