@@ -55,6 +55,8 @@ int b200x_device_count(void);
  *   perm_out[i] = row that lands at sorted position i
  *   codes_out   = (optional, may be NULL) the sorted order-preserving 64-bit key codes;
  *                 ascending for both sort directions (see b200x_encode_keys)
+ *   keys_out    = (optional, integer key types only) the sorted key column itself, decoded from
+ *                 the codes by the last pass (saves a random gather of the key column)
  *   perm_in     = (optional) rows are visited in the order perm_in[0..n): the key of
  *                 position i is keys[perm_in[i]]. Chaining calls from the last key
  *                 column to the first gives a stable multi-column sort.
@@ -63,8 +65,8 @@ int b200x_device_count(void);
  *   _internal/arrow_ops/transform_pyarrow.py:17-21, :269-276
  *   (via ArrowBlockAccessor.sort_and_partition / merge_sorted_blocks, _internal/arrow_block.py:449-464, :554-567) */
 int b200x_radix_argsort(const void* keys, int key_type, int descending, const uint32_t* perm_in, uint32_t* perm_out,
-                        uint64_t* codes_out, size_t n, int begin_bit, int end_bit, void* temp, size_t* temp_bytes,
-                        void* stream);
+                        uint64_t* codes_out, void* keys_out, size_t n, int begin_bit, int end_bit, void* temp,
+                        size_t* temp_bytes, void* stream);
 
 /* dst[i, :] = src[idx[i], :] for rows of row_bytes bytes (a fixed-width column or a
  * packed payload). Replaces Table.take: _internal/arrow_ops/transform_pyarrow.py:24-50,
@@ -119,14 +121,18 @@ int b200x_group_boundaries(const uint64_t* codes, size_t n, uint32_t* group_star
  * writes, where the output pointer is not NULL:
  *   sum_out[g] (int64 wrap-around or float64), min_out[g], max_out[g]  (same type as values)
  * If center (float64 per group) is given, the reduced quantity is (v - center[g])^2 as float64
- * (sum of squared differences for Std) and all outputs are float64.
+ * (sum of squared differences for Std) and all outputs are float64; weights (int64 per input
+ * row, optional, only with center) multiplies each squared difference and addend (float64 per
+ * input row, optional, only with center) is added to it: together they merge Std partials,
+ * M2 = sum_p M2_p + count_p * (mean_p - mean)^2 (aggregate/_aggregate.py:264-283).
  * Deterministic for a given n (fixed reduction tree).
  * Replaces pyarrow.compute.sum/min_max on each group's slice and the accumulator merges:
  * _internal/arrow_block.py:370-447 (sum/min/max/mean/sum_of_squared_diffs_from_mean),
  * aggregate/_aggregate.py:105-319, _internal/arrow_block.py:569-680 (aggregate_combined_blocks). */
 int b200x_segmented_reduce(const uint32_t* group_starts, const uint32_t* num_groups, const uint32_t* perm,
-                           const void* values, int value_type, size_t n, const double* center, void* sum_out,
-                           void* min_out, void* max_out, void* temp, size_t* temp_bytes, void* stream);
+                           const void* values, int value_type, size_t n, const double* center, const int64_t* weights,
+                           const double* addend, void* sum_out, void* min_out, void* max_out, void* temp,
+                           size_t* temp_bytes, void* stream);
 
 /* counts_out[g] = rows in group g (int64), g < *num_groups; max_groups bounds the launch.
  * Replaces Count's accumulate_block (num_rows of the group slice): aggregate/_aggregate.py:90-102. */

@@ -15,7 +15,7 @@ from ctypes import c_char_p, c_double, c_int, c_size_t, c_uint32, c_uint64, c_vo
 from typing import Optional
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200x.so")
+LIB_PATH = os.environ.get("B200X_LIB", os.path.join(_HERE, "libb200x.so"))  # env override: kernel-tuning builds
 CSRC_DIR = os.path.join(_HERE, "csrc")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "b200x.h")
 
@@ -29,8 +29,8 @@ SIGNATURES = {
     "b200x_version": (c_int, []),
     "b200x_last_error_string": (c_char_p, []),
     "b200x_device_count": (c_int, []),
-    "b200x_radix_argsort": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_int, c_int,
-                                    c_void_p, _size_p, c_void_p]),
+    "b200x_radix_argsort": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_int,
+                                    c_int, c_void_p, _size_p, c_void_p]),
     "b200x_gather_rows": (c_int, [c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_void_p]),
     "b200x_gather_columns8": (c_int, [POINTER(c_void_p), POINTER(c_void_p), c_int, c_void_p, c_size_t, c_void_p]),
     "b200x_iota_u32": (c_int, [c_void_p, c_size_t, c_uint32, c_void_p]),
@@ -41,7 +41,7 @@ SIGNATURES = {
     "b200x_perm_indices_host": (c_int, [c_size_t, c_uint64, c_int, c_size_t, c_size_t, c_void_p]),
     "b200x_group_boundaries": (c_int, [c_void_p, c_size_t, c_void_p, c_void_p, c_void_p, _size_p, c_void_p]),
     "b200x_segmented_reduce": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_size_t, c_void_p, c_void_p,
-                                       c_void_p, c_void_p, c_void_p, _size_p, c_void_p]),
+                                       c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, _size_p, c_void_p]),
     "b200x_group_counts": (c_int, [c_void_p, c_void_p, c_size_t, c_size_t, c_void_p, c_void_p]),
     "b200x_finalize_groups": (c_int, [c_void_p, c_int, c_void_p, c_size_t, c_int, c_int, c_void_p, c_void_p]),
 }

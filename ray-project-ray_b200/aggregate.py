@@ -1,0 +1,305 @@
+"""Aggregations: the AggregateFn library and its device implementation.
+
+API mirror of python/ray/data/aggregate/_aggregate.py:20-319 (AggregateFn, Count, Sum, Min, Max,
+Mean, Std; same constructor arguments, same output column names `sum(x)`, `mean(x)`, `count()`,
+same `_2` suffix for duplicate names, arrow_block.py:537-552).
+
+The reference evaluates an aggregation with Python callables (init / accumulate_block / merge /
+finalize) per group. On the device a built-in aggregation is instead a (kind, column) pair that
+selects outputs of the segmented-reduce kernel, and a partially combined block (the output of
+`combine`, the input of `aggregate_combined_blocks`) stores each accumulator in flat columns:
+
+  count          name                      int64
+  sum/min/max    name                      column dtype
+  mean           name (= sum), name::count
+  std            name (= M2),  name::sum, name::count      (M2 about the partial's own mean)
+
+User-defined AggregateFn callables cannot run on the device and raise NotImplementedError.
+Nulls do not exist in the device block format, so `ignore_nulls` has no effect (has_data is
+always true in the reference's null wrappers, _internal/null_aggregate.py:28-250).
+"""
+from __future__ import annotations
+
+from typing import Callable, Dict, List, Optional, Sequence, Tuple, Union
+
+import numpy as np
+import torch
+
+from . import ops
+from .block import DeviceBlock, KeyType, AggType, _contig
+
+SEP = "::"
+
+
+class AggregateFn:
+    def __init__(self, init: Callable = None, merge: Callable = None, accumulate_row: Callable = None,
+                 accumulate_block: Callable = None, finalize: Callable = lambda a: a, name: Optional[str] = None):
+        if (accumulate_row is None and accumulate_block is None) or (
+            accumulate_row is not None and accumulate_block is not None
+        ):
+            raise ValueError("Exactly one of accumulate_row or accumulate_block must be provided.")
+        self.init, self.merge, self.finalize, self.name = init, merge, finalize, name
+        self.accumulate_row, self.accumulate_block = accumulate_row, accumulate_block
+        self._device_kind: Optional[str] = None
+
+    def _validate(self, schema) -> None:
+        pass
+
+
+class _AggregateOnKeyBase(AggregateFn):
+    def _setup(self, kind: str, on: Optional[str], alias_name: Optional[str], ignore_nulls: bool = True):
+        self._key_fn = on
+        self._device_kind = kind
+        self._ignore_nulls = ignore_nulls
+        self.name = alias_name if alias_name else f"{kind}({str(on)})"
+        self._rs_name = self.name
+        self.init = self.merge = self.accumulate_block = self.accumulate_row = None
+        self.finalize = lambda a: a
+
+    def _validate(self, schema) -> None:
+        from .sort_task_spec import SortKey
+
+        SortKey(self._key_fn).validate_schema(schema)
+
+
+class Count(AggregateFn):
+    """Rows per group (counts every row: _aggregate.py:90-102)."""
+
+    def __init__(self):
+        self.name = "count()"
+        self._device_kind = "count"
+        self._key_fn = None
+        self.init = self.merge = self.accumulate_block = self.accumulate_row = None
+        self.finalize = lambda a: a
+
+
+class Sum(_AggregateOnKeyBase):
+    def __init__(self, on: Optional[str] = None, ignore_nulls: bool = True, alias_name: Optional[str] = None):
+        self._setup("sum", on, alias_name, ignore_nulls)
+
+
+class Min(_AggregateOnKeyBase):
+    def __init__(self, on: Optional[str] = None, ignore_nulls: bool = True, alias_name: Optional[str] = None):
+        self._setup("min", on, alias_name, ignore_nulls)
+
+
+class Max(_AggregateOnKeyBase):
+    def __init__(self, on: Optional[str] = None, ignore_nulls: bool = True, alias_name: Optional[str] = None):
+        self._setup("max", on, alias_name, ignore_nulls)
+
+
+class Mean(_AggregateOnKeyBase):
+    def __init__(self, on: Optional[str] = None, ignore_nulls: bool = True, alias_name: Optional[str] = None):
+        self._setup("mean", on, alias_name, ignore_nulls)
+
+
+class Std(_AggregateOnKeyBase):
+    def __init__(self, on: Optional[str] = None, ddof: int = 1, ignore_nulls: bool = True,
+                 alias_name: Optional[str] = None):
+        self._setup("std", on, alias_name, ignore_nulls)
+        self._ddof = ddof
+
+
+def _device_kind(agg: AggregateFn) -> str:
+    kind = getattr(agg, "_device_kind", None)
+    if kind is None:
+        raise NotImplementedError(
+            "user-defined AggregateFn callables cannot run on device blocks; use Count/Sum/Min/Max/Mean/Std")
+    return kind
+
+
+def resolved_names(aggs: Sequence[AggregateFn]) -> List[str]:
+    """Output column names with the reference's conflict rule (arrow_block.py:537-552)."""
+    count: Dict[str, int] = {}
+    out = []
+    for agg in aggs:
+        name = agg.name
+        c = count.get(name, 0)
+        out.append(name if c == 0 else f"{name}_{c + 1}")
+        count[name] = c + 1
+    return out
+
+
+def _value_column(block: DeviceBlock, on: str) -> torch.Tensor:
+    if on not in block.columns:
+        raise ValueError(f"The column '{on}' does not exist in the schema '{block.schema()}'.")
+    v = _contig(block.columns[on])
+    if v.dim() != 1:
+        raise TypeError(f"cannot aggregate the multi-byte payload column {on!r}")
+    if v.dtype in (torch.int32, torch.int16, torch.int8, torch.uint8):
+        raise TypeError(f"aggregations take int64 or float64 columns; cast {on!r} ({v.dtype}) first")
+    if v.dtype == torch.float32:
+        raise TypeError(f"aggregations take int64 or float64 columns; cast {on!r} (float32) first")
+    return v
+
+
+def _groups_of_sorted(block: DeviceBlock, key: Optional[str]):
+    """(group_starts, num_groups tensor, G) of a block already sorted by `key` (None: one group)."""
+    n = block.num_rows
+    dev = block.device
+    if key is None:
+        starts = torch.zeros(1, dtype=torch.int32, device=dev)
+        ng = torch.ones(1, dtype=torch.int32, device=dev)
+        return starts, ng, 1
+    codes = ops.encode_keys(_contig(block.columns[key]), False)
+    starts, ng = ops.group_boundaries(codes)
+    return starts, ng, int(ng.item())
+
+
+def _reduce_partials(kind: str, agg: AggregateFn, name: str, src: DeviceBlock, starts, ng, G: int, perm, n: int,
+                     raw: bool) -> Dict[str, torch.Tensor]:
+    """Accumulator columns of one aggregation for G groups.
+    raw=True: `src` holds data rows (combine). raw=False: `src` holds partial rows (merge)."""
+    out: Dict[str, torch.Tensor] = {}
+    if kind == "count":
+        if raw:
+            out[name] = ops.group_counts(starts, ng, G, n)
+        else:
+            out[name] = ops.segmented_reduce(starts, ng, G, perm, _contig(src.columns[name]), n)[0]
+        return out
+    col = _value_column(src, agg._key_fn) if raw else _contig(src.columns[name])
+    if kind == "sum":
+        out[name] = ops.segmented_reduce(starts, ng, G, perm, col, n)[0]
+    elif kind == "min":
+        out[name] = ops.segmented_reduce(starts, ng, G, perm, col, n, want_sum=False, want_min=True)[1]
+    elif kind == "max":
+        out[name] = ops.segmented_reduce(starts, ng, G, perm, col, n, want_sum=False, want_max=True)[2]
+    elif kind == "mean":
+        out[name] = ops.segmented_reduce(starts, ng, G, perm, col, n)[0]
+        if raw:
+            out[name + SEP + "count"] = ops.group_counts(starts, ng, G, n)
+        else:
+            out[name + SEP + "count"] = ops.segmented_reduce(starts, ng, G, perm,
+                                                             _contig(src.columns[name + SEP + "count"]), n)[0]
+    elif kind == "std":
+        if raw:
+            s = ops.segmented_reduce(starts, ng, G, perm, col, n)[0]
+            cnt = ops.group_counts(starts, ng, G, n)
+            mean = ops.finalize_groups(s, cnt, 0)
+            m2 = ops.segmented_reduce(starts, ng, G, perm, col, n, center=mean)[0]
+        else:
+            # Chan et al. merge of (M2, sum, count) partials (Std.merge, _aggregate.py:264-283):
+            # M2 = sum_p M2_p + sum_p count_p * (mean_p - mean)^2
+            ps, pc = _contig(src.columns[name + SEP + "sum"]), _contig(src.columns[name + SEP + "count"])
+            s = ops.segmented_reduce(starts, ng, G, perm, ps, n)[0]
+            cnt = ops.segmented_reduce(starts, ng, G, perm, pc, n)[0]
+            mean = ops.finalize_groups(s, cnt, 0)
+            part_mean = ops.finalize_groups(ps, pc, 0)
+            m2 = ops.segmented_reduce(starts, ng, G, perm, part_mean, n, center=mean, weights=pc, addend=col)[0]
+        out[name], out[name + SEP + "sum"], out[name + SEP + "count"] = m2, s, cnt
+    else:
+        raise ValueError(kind)
+    return out
+
+
+def _finalize(kind: str, agg: AggregateFn, name: str, acc: Dict[str, torch.Tensor]) -> torch.Tensor:
+    if kind in ("count", "sum", "min", "max"):
+        return acc[name]
+    if kind == "mean":
+        return ops.finalize_groups(acc[name], acc[name + SEP + "count"], 0)
+    if kind == "std":
+        return ops.finalize_groups(acc[name], acc[name + SEP + "count"], 1, getattr(agg, "_ddof", 1))
+    raise ValueError(kind)
+
+
+def _check_key(key) -> Optional[str]:
+    if isinstance(key, list):
+        if len(key) == 1:
+            return key[0]
+        if len(key) == 0:
+            return None
+        raise NotImplementedError("grouping by more than one key column is not implemented on device blocks")
+    return key
+
+
+def aggregate_sorted(block: DeviceBlock, key: Optional[str], aggs: Sequence[AggregateFn], perm, codes,
+                     finalize: bool, n: int) -> DeviceBlock:
+    """One-shot groupby over rows visited in sorted order `perm` whose ascending key codes are
+    `codes` (both from ops.argsort); the fused scheduler path."""
+    key = _check_key(key)
+    dev = block.device
+    names = resolved_names(aggs)
+    if key is None:
+        starts = torch.zeros(1, dtype=torch.int32, device=dev)
+        ng = torch.ones(1, dtype=torch.int32, device=dev)
+        G = 1
+    else:
+        starts, ng = ops.group_boundaries(codes)
+        G = int(ng.item())
+    cols: Dict[str, torch.Tensor] = {}
+    if key is not None:
+        first_rows = ops.gather(perm, starts[:G].contiguous()) if perm is not None else starts[:G].contiguous()
+        cols[key] = ops.gather(_contig(block.columns[key]), first_rows)
+    for agg, name in zip(aggs, names):
+        kind = _device_kind(agg)
+        acc = _reduce_partials(kind, agg, name, block, starts, ng, G, perm, n, raw=True)
+        if finalize:
+            cols[name] = _finalize(kind, agg, name, acc)
+        else:
+            cols.update(acc)
+    return DeviceBlock(cols, num_rows=G, device=dev)
+
+
+def combine_block(block: DeviceBlock, key, aggs: Sequence[AggregateFn], presorted: bool = True) -> DeviceBlock:
+    """ArrowBlockAccessor.combine (arrow_block.py:466-548): one partial-accumulator row per group of
+    a block sorted by key."""
+    key = _check_key(key)
+    n = block.num_rows
+    names = resolved_names(aggs)
+    if n == 0:
+        return DeviceBlock.empty(block.device)
+    if key is None:
+        codes = None
+    else:
+        codes = ops.encode_keys(_contig(block.columns[key]), False)
+    return aggregate_sorted(block, key, aggs, None, codes, finalize=False, n=n)
+
+
+def merge_combined_blocks(blocks: Sequence[DeviceBlock], key, aggs: Sequence[AggregateFn], finalize: bool) -> DeviceBlock:
+    """ArrowBlockAccessor.aggregate_combined_blocks (arrow_block.py:569-680): merge partial rows with
+    equal keys (mapper order within a key, as heapq.merge gives), optionally finalize."""
+    key = _check_key(key)
+    blocks = [b for b in blocks if b.num_rows > 0]
+    if not blocks:
+        return DeviceBlock.empty()
+    allp = DeviceBlock.concat(blocks)
+    n = allp.num_rows
+    dev = allp.device
+    names = resolved_names(aggs)
+    if key is None:
+        perm = None
+        starts = torch.zeros(1, dtype=torch.int32, device=dev)
+        ng = torch.ones(1, dtype=torch.int32, device=dev)
+        G = 1
+    else:
+        perm, codes, _ = ops.argsort(_contig(allp.columns[key]), False, want_codes=True)
+        starts, ng = ops.group_boundaries(codes)
+        G = int(ng.item())
+    cols: Dict[str, torch.Tensor] = {}
+    if key is not None:
+        first_rows = ops.gather(perm, starts[:G].contiguous())
+        cols[key] = ops.gather(_contig(allp.columns[key]), first_rows)
+    for agg, name in zip(aggs, names):
+        kind = _device_kind(agg)
+        acc = _reduce_partials(kind, agg, name, allp, starts, ng, G, perm, n, raw=False)
+        if finalize:
+            cols[name] = _finalize(kind, agg, name, acc)
+        else:
+            cols.update(acc)
+    return DeviceBlock(cols, num_rows=G, device=dev)
+
+
+def _global_reduce(col: torch.Tensor, want: str, center: Optional[float] = None):
+    """Whole-column sum / min / max / sum of squared differences, returned as a Python scalar
+    (BlockAccessor.sum/min/max/sum_of_squared_diffs_from_mean, arrow_block.py:404-447)."""
+    col = _contig(col)
+    n = col.numel()
+    dev = col.device
+    starts = torch.zeros(1, dtype=torch.int32, device=dev)
+    ng = torch.ones(1, dtype=torch.int32, device=dev)
+    if want == "m2":
+        c = torch.full((1,), float(center), dtype=torch.float64, device=dev)
+        return ops.segmented_reduce(starts, ng, 1, None, col, n, center=c)[0].item()
+    s, mn, mx = ops.segmented_reduce(starts, ng, 1, None, col, n, want_sum=want == "sum", want_min=want == "min",
+                                     want_max=want == "max")
+    return {"sum": s, "min": mn, "max": mx}[want].item()

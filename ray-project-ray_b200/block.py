@@ -1,0 +1,576 @@
+"""Device blocks: the columnar HBM block format and its BlockAccessor.
+
+Mirrors the data-plane types of the reference (python/ray/data/block.py:54, :123-215,
+:219-435) for a block whose columns live in HBM:
+
+  Block            -> DeviceBlock: ordered {column name: torch CUDA tensor}, every column
+                      `[n]` (any fixed-width dtype) or `[n, w]` (a packed fixed-width payload,
+                      row-major so that a row moves as one contiguous w-byte record).
+  BlockAccessor    -> DeviceBlockAccessor: the hot-path methods of ArrowBlockAccessor
+                      (python/ray/data/_internal/arrow_block.py:159-680) implemented by calling
+                      the C ABI; nothing is computed with torch ops or on the CPU.
+  BlockMetadata / BlockExecStats -> same fields.
+
+Null values and variable-width columns are outside the device format (fixed-width
+int/float keys and payloads); ingesting an Arrow column with nulls raises.
+"""
+from __future__ import annotations
+
+import os
+import time
+from dataclasses import dataclass
+from typing import Any, Dict, Iterator, List, Optional, Sequence, Tuple, Union
+
+import numpy as np
+import torch
+
+from . import ops
+
+try:  # resource is POSIX-only, as in the reference (block.py:21-24)
+    import resource
+except ImportError:  # pragma: no cover
+    resource = None
+
+KeyType = Any
+AggType = Any
+
+
+def default_device() -> torch.device:
+    """The CUDA device new blocks are placed on: LOCAL_RANK's GPU under torchrun, else cuda:0."""
+    if not torch.cuda.is_available():
+        raise RuntimeError("the device block format needs a CUDA device; there is no CPU fallback")
+    return torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")) % torch.cuda.device_count())
+
+
+class BlockExecStats:
+    """Execution stats of one map / merge / reduce step (reference: block.py:123-154)."""
+
+    def __init__(self):
+        self.start_time_s: Optional[float] = None
+        self.end_time_s: Optional[float] = None
+        self.wall_time_s: Optional[float] = None
+        self.udf_time_s: Optional[float] = 0
+        self.cpu_time_s: Optional[float] = None
+        self.node_id = f"gpu{os.environ.get('LOCAL_RANK', '0')}"
+        self.max_rss_bytes: int = 0
+        self.task_idx: Optional[int] = None
+
+    @staticmethod
+    def builder() -> "_BlockExecStatsBuilder":
+        return _BlockExecStatsBuilder()
+
+    def __repr__(self):
+        return repr({"wall_time_s": self.wall_time_s, "cpu_time_s": self.cpu_time_s,
+                     "udf_time_s": self.udf_time_s, "node_id": self.node_id})
+
+
+class _BlockExecStatsBuilder:
+    def __init__(self):
+        self.start_time = time.perf_counter()
+        self.start_cpu = time.process_time()
+
+    def build(self) -> BlockExecStats:
+        stats = BlockExecStats()
+        stats.start_time_s = self.start_time
+        stats.end_time_s = time.perf_counter()
+        stats.wall_time_s = stats.end_time_s - self.start_time
+        stats.cpu_time_s = time.process_time() - self.start_cpu
+        if resource is not None:
+            stats.max_rss_bytes = int(resource.getrusage(resource.RUSAGE_SELF).ru_maxrss * 1e3)
+        return stats
+
+
+@dataclass
+class BlockMetadata:
+    """Reference: block.py:194-215."""
+
+    num_rows: Optional[int]
+    size_bytes: Optional[int]
+    schema: Optional[Any]
+    input_files: Optional[List[str]]
+    exec_stats: Optional[BlockExecStats]
+
+    def __post_init__(self):
+        if self.input_files is None:
+            self.input_files = []
+        if self.size_bytes is not None:
+            assert isinstance(self.size_bytes, int)
+
+
+class Schema:
+    """Column names and dtypes of a device block (stands in for pyarrow.Schema)."""
+
+    def __init__(self, names: Sequence[str], types: Sequence[Tuple[torch.dtype, Tuple[int, ...]]]):
+        self.names = list(names)
+        self.types = list(types)
+
+    def __eq__(self, other):
+        return isinstance(other, Schema) and self.names == other.names and self.types == other.types
+
+    def __repr__(self):
+        cols = ", ".join(f"{n}: {str(t[0]).replace('torch.', '')}{list(t[1]) if t[1] else ''}"
+                         for n, t in zip(self.names, self.types))
+        return f"Schema({cols})"
+
+
+_NP_TO_TORCH = {
+    np.dtype(np.int64): torch.int64, np.dtype(np.float64): torch.float64, np.dtype(np.int32): torch.int32,
+    np.dtype(np.float32): torch.float32, np.dtype(np.int16): torch.int16, np.dtype(np.int8): torch.int8,
+    np.dtype(np.uint8): torch.uint8, np.dtype(np.bool_): torch.uint8,
+}
+_NP_UNSIGNED_VIEW = {np.dtype(np.uint64): (np.int64, "uint64"), np.dtype(np.uint32): (np.int32, "uint32"),
+                     np.dtype(np.uint16): (np.int16, "uint16")}
+
+
+def _to_device(col: np.ndarray, device: torch.device) -> torch.Tensor:
+    col = np.ascontiguousarray(col)
+    if col.dtype in _NP_UNSIGNED_VIEW:
+        signed, name = _NP_UNSIGNED_VIEW[col.dtype]
+        return torch.from_numpy(col.view(signed)).to(device, non_blocking=True).view(getattr(torch, name))
+    if col.dtype == np.bool_:
+        col = col.view(np.uint8)
+    if col.dtype not in _NP_TO_TORCH:
+        raise TypeError(f"column dtype {col.dtype} is not a fixed-width type the device block format holds")
+    return torch.from_numpy(col).to(device, non_blocking=True)
+
+
+def _to_host(t: torch.Tensor) -> np.ndarray:
+    if t.dtype in (getattr(torch, "uint64", None), getattr(torch, "uint32", None), getattr(torch, "uint16", None)):
+        signed = {8: torch.int64, 4: torch.int32, 2: torch.int16}[t.element_size()]
+        unsigned = {8: np.uint64, 4: np.uint32, 2: np.uint16}[t.element_size()]
+        return t.view(signed).cpu().numpy().view(unsigned)
+    return t.cpu().numpy()
+
+
+class DeviceBlock:
+    """A columnar block resident in HBM. Immutable by convention; slices are views."""
+
+    __slots__ = ("columns", "_n", "device")
+
+    def __init__(self, columns: Dict[str, torch.Tensor], num_rows: Optional[int] = None,
+                 device: Optional[torch.device] = None):
+        self.columns: Dict[str, torch.Tensor] = dict(columns)
+        n = num_rows
+        dev = device
+        for name, t in self.columns.items():
+            if not isinstance(t, torch.Tensor):
+                raise TypeError(f"column {name!r} is not a tensor")
+            if n is None:
+                n = t.shape[0]
+            elif t.shape[0] != n:
+                raise ValueError(f"column {name!r} has {t.shape[0]} rows, expected {n}")
+            if dev is None:
+                dev = t.device
+        self._n = int(n or 0)
+        self.device = dev
+
+    # -- construction -------------------------------------------------------------------
+    @staticmethod
+    def from_numpy(cols: Dict[str, np.ndarray], device: Optional[torch.device] = None) -> "DeviceBlock":
+        device = device or default_device()
+        return DeviceBlock({k: _to_device(np.asarray(v), device) for k, v in cols.items()}, device=device)
+
+    @staticmethod
+    def from_arrow(table, device: Optional[torch.device] = None) -> "DeviceBlock":
+        import pyarrow as pa
+
+        device = device or default_device()
+        cols: Dict[str, torch.Tensor] = {}
+        for name in table.column_names:
+            col = table[name]
+            if col.null_count:
+                raise ValueError(f"column {name!r} has nulls; the device block format holds non-null fixed-width data")
+            if isinstance(col, pa.ChunkedArray):
+                col = col.combine_chunks()
+            if pa.types.is_fixed_size_binary(col.type):
+                w = col.type.byte_width
+                buf = np.frombuffer(col.buffers()[1], dtype=np.uint8, count=len(col) * w, offset=col.offset * w)
+                arr = buf.reshape(len(col), w)
+            elif pa.types.is_null(col.type):
+                raise ValueError(f"column {name!r} has null type")
+            else:
+                arr = col.to_numpy(zero_copy_only=False)
+            cols[name] = _to_device(arr, device)
+        return DeviceBlock(cols, num_rows=table.num_rows, device=device)
+
+    @staticmethod
+    def from_pandas(df, device: Optional[torch.device] = None) -> "DeviceBlock":
+        return DeviceBlock.from_numpy({str(c): df[c].to_numpy() for c in df.columns}, device)
+
+    @staticmethod
+    def empty(device: Optional[torch.device] = None) -> "DeviceBlock":
+        return DeviceBlock({}, num_rows=0, device=device)
+
+    # -- introspection ------------------------------------------------------------------
+    @property
+    def num_rows(self) -> int:
+        return self._n
+
+    @property
+    def column_names(self) -> List[str]:
+        return list(self.columns)
+
+    def __len__(self) -> int:
+        return self._n
+
+    def __getitem__(self, name: str) -> torch.Tensor:
+        return self.columns[name]
+
+    def __repr__(self):
+        return f"DeviceBlock(rows={self._n}, {self.schema()})"
+
+    def schema(self) -> Optional[Schema]:
+        if not self.columns:
+            return None
+        return Schema(list(self.columns), [(t.dtype, tuple(t.shape[1:])) for t in self.columns.values()])
+
+    def size_bytes(self) -> int:
+        return int(sum(t.numel() * t.element_size() for t in self.columns.values()))
+
+    # -- zero-copy structure ops --------------------------------------------------------
+    def slice(self, start: int, end: int) -> "DeviceBlock":
+        start = max(0, min(start, self._n))
+        end = max(start, min(end, self._n))
+        return DeviceBlock({k: v[start:end] for k, v in self.columns.items()}, num_rows=end - start,
+                           device=self.device)
+
+    def select(self, names: Sequence[str]) -> "DeviceBlock":
+        return DeviceBlock({k: self.columns[k] for k in names}, num_rows=self._n, device=self.device)
+
+    @staticmethod
+    def concat(blocks: Sequence["DeviceBlock"]) -> "DeviceBlock":
+        """Concatenate same-schema blocks in order (empty / schema-less blocks are dropped).
+
+        Adjacent views of one buffer (the normal case for blocks cut from one dataset buffer)
+        are re-joined without a copy."""
+        blocks = [b for b in blocks if b.num_rows > 0]
+        if not blocks:
+            return DeviceBlock.empty()
+        if len(blocks) == 1:
+            return blocks[0]
+        names = blocks[0].column_names
+        out: Dict[str, torch.Tensor] = {}
+        for name in names:
+            parts = [b.columns[name] for b in blocks]
+            out[name] = _join_views(parts)
+        return DeviceBlock(out, device=blocks[0].device)
+
+    # -- egress (D2H happens only here) -------------------------------------------------
+    def to_numpy(self, columns: Optional[Sequence[str]] = None) -> Dict[str, np.ndarray]:
+        names = list(columns) if columns is not None else list(self.columns)
+        return {k: _to_host(self.columns[k].contiguous()) for k in names}
+
+    def to_arrow(self):
+        import pyarrow as pa
+
+        arrays, names = [], []
+        for k, v in self.to_numpy().items():
+            if v.ndim == 2:
+                arrays.append(pa.FixedSizeBinaryArray.from_buffers(pa.binary(v.shape[1] * v.dtype.itemsize), len(v),
+                                                                   [None, pa.py_buffer(np.ascontiguousarray(v))]))
+            else:
+                arrays.append(pa.array(v))
+            names.append(k)
+        return pa.table(arrays, names=names) if names else pa.table({})
+
+    def to_pandas(self):
+        import pandas as pd
+
+        return pd.DataFrame({k: (list(v) if v.ndim == 2 else v) for k, v in self.to_numpy().items()})
+
+
+def _join_views(parts: List[torch.Tensor]) -> torch.Tensor:
+    first = parts[0]
+    row = first.stride(0) * first.element_size() if first.dim() >= 1 and first.shape[0] > 0 else 0
+    contiguous = all(p.is_contiguous() and p.dtype == first.dtype and p.shape[1:] == first.shape[1:] for p in parts)
+    if contiguous and row:
+        ptr = first.data_ptr()
+        same = True
+        for p in parts:
+            if p.data_ptr() != ptr or p.untyped_storage().data_ptr() != first.untyped_storage().data_ptr():
+                same = False
+                break
+            ptr += p.shape[0] * row
+        if same:
+            total = sum(p.shape[0] for p in parts)
+            return first.as_strided((total,) + tuple(first.shape[1:]), first.stride(), first.storage_offset())
+    return torch.cat([p for p in parts], dim=0)
+
+
+Block = DeviceBlock
+
+
+def _as_device_block(block: Any) -> DeviceBlock:
+    if isinstance(block, DeviceBlock):
+        return block
+    try:
+        import pyarrow as pa
+
+        if isinstance(block, pa.Table):
+            return DeviceBlock.from_arrow(block)
+    except ImportError:  # pragma: no cover
+        pass
+    try:
+        import pandas as pd
+
+        if isinstance(block, pd.DataFrame):
+            return DeviceBlock.from_pandas(block)
+    except ImportError:  # pragma: no cover
+        pass
+    if isinstance(block, dict):
+        return DeviceBlock.from_numpy(block)
+    raise TypeError(f"Not a block type: {block!r} ({type(block)})")
+
+
+class BlockAccessor:
+    """`BlockAccessor.for_block` (reference: block.py:380-407). Arrow tables, DataFrames and
+    dicts of numpy arrays are moved to the device first; everything runs on DeviceBlockAccessor."""
+
+    @staticmethod
+    def for_block(block: Any) -> "DeviceBlockAccessor":
+        return DeviceBlockAccessor(_as_device_block(block))
+
+
+class DeviceBlockAccessor(BlockAccessor):
+    def __init__(self, block: DeviceBlock):
+        self._block = block
+
+    # -- plain accessors (block.py:227-378) ---------------------------------------------
+    def num_rows(self) -> int:
+        return self._block.num_rows
+
+    def size_bytes(self) -> int:
+        return self._block.size_bytes()
+
+    def schema(self):
+        return self._block.schema()
+
+    def column_names(self) -> List[str]:
+        return self._block.column_names
+
+    def to_block(self) -> DeviceBlock:
+        return self._block
+
+    def to_arrow(self):
+        return self._block.to_arrow()
+
+    def to_pandas(self):
+        return self._block.to_pandas()
+
+    def to_numpy(self, columns: Optional[Union[str, List[str]]] = None):
+        if isinstance(columns, str):
+            return self._block.to_numpy([columns])[columns]
+        return self._block.to_numpy(columns)
+
+    def iter_rows(self, public_row_format: bool = True) -> Iterator[Dict[str, Any]]:
+        host = self._block.to_numpy()
+        for i in range(self._block.num_rows):
+            yield {k: (v[i].item() if v.ndim == 1 else v[i]) for k, v in host.items()}
+
+    def slice(self, start: int, end: int, copy: bool = False) -> DeviceBlock:
+        out = self._block.slice(start, end)
+        if copy:
+            out = DeviceBlock({k: v.clone() for k, v in out.columns.items()}, num_rows=out.num_rows, device=out.device)
+        return out
+
+    def select(self, columns: List[str]) -> DeviceBlock:
+        if not all(isinstance(c, str) for c in columns):
+            raise ValueError(f"Columns must be a list of column name strings, but got: {columns}.")
+        return self._block.select(columns)
+
+    def get_metadata(self, input_files: Optional[List[str]] = None,
+                     exec_stats: Optional[BlockExecStats] = None) -> BlockMetadata:
+        return BlockMetadata(num_rows=self.num_rows(), size_bytes=self.size_bytes(), schema=self.schema(),
+                             input_files=input_files, exec_stats=exec_stats)
+
+    # -- gathers ------------------------------------------------------------------------
+    def take(self, indices: torch.Tensor) -> DeviceBlock:
+        """Rows at `indices` (int32 tensor holding uint32 row numbers). arrow_block.py:346-355."""
+        b = self._block
+        names = b.column_names
+        outs = ops.gather_columns([_contig(b.columns[k]) for k in names], indices)
+        return DeviceBlock(dict(zip(names, outs)), num_rows=indices.numel(), device=b.device)
+
+    def random_shuffle(self, random_seed: Optional[int]) -> DeviceBlock:
+        """Seeded permutation of the rows. arrow_block.py:249-255 (permutation + take, fused here)."""
+        b = self._block
+        seed = 0 if random_seed is None else int(random_seed)
+        if random_seed is None:
+            seed = int.from_bytes(os.urandom(8), "little")
+        return DeviceBlock({k: ops.permute_rows(_contig(v), seed) for k, v in b.columns.items()},
+                           num_rows=b.num_rows, device=b.device)
+
+    def sample(self, n_samples: int, sort_key: "SortKey") -> DeviceBlock:
+        """`n_samples` rows of the key columns. table_block.py:252-262, arrow_block.py:365-368.
+
+        The reference draws with the unseeded `random.sample`; here rows are taken at evenly spaced
+        positions, which is deterministic (splitters are load-balance hints, not part of parity)."""
+        b = self._block
+        cols = sort_key.get_columns()
+        if b.num_rows == 0 or not b.columns:
+            return DeviceBlock.empty(b.device)
+        n_samples = min(n_samples, b.num_rows)
+        pos = ((np.arange(n_samples, dtype=np.float64) + 0.5) * (b.num_rows / max(n_samples, 1))).astype(np.int64)
+        idx = torch.from_numpy(pos.astype(np.int32)).to(b.device)
+        return DeviceBlockAccessor(b.select(cols)).take(idx)
+
+    # -- sort (arrow_block.py:449-464, :554-567) ------------------------------------------
+    def _argsort(self, sort_key: "SortKey", want_codes: bool):
+        """Stable multi-column argsort: chain from the last key column to the first."""
+        b = self._block
+        cols = sort_key.get_columns()
+        desc = sort_key.get_descending()
+        perm = codes = skeys = None
+        for i, name in enumerate(reversed(cols)):
+            lastcall = i == len(cols) - 1
+            perm, codes, skeys = ops.argsort(_contig(b.columns[name]), desc, perm_in=perm,
+                                             want_codes=want_codes and lastcall, want_keys=lastcall)
+        return perm, codes, skeys
+
+    def sort(self, sort_key: "SortKey", want_codes: bool = False):
+        """Whole block in sorted order (transform_pyarrow.sort: sort_indices + take)."""
+        b = self._block
+        perm, codes, skeys = self._argsort(sort_key, want_codes)
+        first_key = sort_key.get_columns()[0]
+        names = [k for k in b.column_names if not (skeys is not None and k == first_key)]
+        outs = ops.gather_columns([_contig(b.columns[k]) for k in names], perm)
+        cols = dict(zip(names, outs))
+        if skeys is not None:
+            cols[first_key] = skeys
+        out = DeviceBlock({k: cols[k] for k in b.column_names}, num_rows=b.num_rows, device=b.device)
+        return out, codes
+
+    def sort_and_partition(self, boundaries: List[Any], sort_key: "SortKey") -> List[DeviceBlock]:
+        b = self._block
+        if b.num_rows == 0:
+            return [DeviceBlock.empty(b.device) for _ in range(len(boundaries) + 1)]
+        table, codes = self.sort(sort_key, want_codes=len(boundaries) > 0)
+        if len(boundaries) == 0:
+            return [table]
+        return find_partitions(table, codes, boundaries, sort_key)
+
+    @staticmethod
+    def merge_sorted_blocks(blocks: List[DeviceBlock], sort_key: "SortKey") -> Tuple[DeviceBlock, BlockMetadata]:
+        stats = BlockExecStats.builder()
+        blocks = [_as_device_block(b) for b in blocks]
+        blocks = [b for b in blocks if b.num_rows > 0]
+        if not blocks:
+            ret = DeviceBlock.empty()
+        else:
+            ret, _ = DeviceBlockAccessor(DeviceBlock.concat(blocks)).sort(sort_key)
+        return ret, DeviceBlockAccessor(ret).get_metadata(None, exec_stats=stats.build())
+
+    # -- per-column reductions over the whole block (arrow_block.py:370-447) --------------
+    def count(self, on: str) -> Optional[int]:
+        if not isinstance(on, str):
+            raise ValueError(f"on must be a string when aggregating on device blocks, but got:{type(on)}.")
+        return None if self.num_rows() == 0 else self.num_rows()
+
+    def _whole_block_reduce(self, on: str, want: str):
+        from .aggregate import _global_reduce
+
+        if not isinstance(on, str):
+            raise ValueError(f"on must be a string when aggregating on device blocks, but got:{type(on)}.")
+        if self.num_rows() == 0:
+            return None
+        return _global_reduce(self._block.columns[on], want)
+
+    def sum(self, on: str, ignore_nulls: bool = True):
+        return self._whole_block_reduce(on, "sum")
+
+    def min(self, on: str, ignore_nulls: bool = True):
+        return self._whole_block_reduce(on, "min")
+
+    def max(self, on: str, ignore_nulls: bool = True):
+        return self._whole_block_reduce(on, "max")
+
+    def mean(self, on: str, ignore_nulls: bool = True):
+        s = self._whole_block_reduce(on, "sum")
+        return None if s is None else s / self.num_rows()
+
+    def sum_of_squared_diffs_from_mean(self, on: str, ignore_nulls: bool = True, mean: Optional[float] = None):
+        from .aggregate import _global_reduce
+
+        if self.num_rows() == 0:
+            return None
+        if mean is None:
+            mean = self.mean(on, ignore_nulls)
+        return _global_reduce(self._block.columns[on], "m2", center=float(mean))
+
+    # -- groupby (arrow_block.py:466-680) -------------------------------------------------
+    def combine(self, key: Union[str, List[str], None], aggs: Sequence["AggregateFn"]) -> DeviceBlock:
+        from .aggregate import combine_block
+
+        if key is not None and not isinstance(key, (str, list)):
+            raise ValueError(f"key must be a string, list of strings or None when aggregating on device blocks, "
+                             f"but got: {type(key)}.")
+        return combine_block(self._block, key, aggs, presorted=True)
+
+    @staticmethod
+    def aggregate_combined_blocks(blocks: List[DeviceBlock], key: Union[str, List[str], None],
+                                  aggs: Sequence["AggregateFn"], finalize: bool) -> Tuple[DeviceBlock, BlockMetadata]:
+        from .aggregate import merge_combined_blocks
+
+        stats = BlockExecStats.builder()
+        ret = merge_combined_blocks([_as_device_block(b) for b in blocks], key, aggs, finalize)
+        return ret, DeviceBlockAccessor(ret).get_metadata(None, exec_stats=stats.build())
+
+    @staticmethod
+    def builder():
+        from .builder import DeviceBlockBuilder
+
+        return DeviceBlockBuilder()
+
+
+def _contig(t: torch.Tensor) -> torch.Tensor:
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def boundary_codes(boundaries: Sequence[Any], key_col: torch.Tensor, descending: bool) -> torch.Tensor:
+    """Encode scalar boundary values with the key column's own code (util.py:719-758 compares
+    boundary values with column values; an int column against a float boundary compares as
+    `x < b`  <=>  `x < ceil(b)`)."""
+    dt = key_col.dtype
+    vals = []
+    for b in boundaries:
+        if isinstance(b, (tuple, list)):
+            b = b[0]
+        if hasattr(b, "item"):
+            b = b.item()
+        vals.append(b)
+    if dt.is_floating_point:
+        host = np.asarray(vals, dtype=np.float64 if dt == torch.float64 else np.float32)
+    else:
+        info = np.iinfo(_to_host(torch.empty(0, dtype=dt)).dtype)
+        ints = [int(min(max(int(np.ceil(v)), info.min), info.max)) if isinstance(v, float) else
+                int(min(max(int(v), info.min), info.max)) for v in vals]
+        host = np.asarray(ints, dtype=_to_host(torch.empty(0, dtype=dt)).dtype)
+    dev_vals = _to_device(host, key_col.device)
+    return ops.encode_keys(dev_vals, descending)
+
+
+def find_partition_indices(codes: torch.Tensor, boundaries: Sequence[Any], key_col: torch.Tensor,
+                           descending: bool) -> List[int]:
+    """find_partition_index for every boundary (util.py:719-758) on the sorted code array.
+    Ascending: #rows < b (lower bound). Descending: #rows >= b (upper bound of the complemented code)."""
+    if len(boundaries) == 0:
+        return []
+    bc = boundary_codes(boundaries, key_col, descending)
+    idx = ops.search_sorted_codes(codes, bc, upper=descending)
+    return [int(x) for x in idx.cpu().tolist()]
+
+
+def find_partitions(table: DeviceBlock, codes: torch.Tensor, boundaries: Sequence[Any],
+                    sort_key: "SortKey") -> List[DeviceBlock]:
+    """Cut a sorted block at the boundaries (util.py:761-779). Single key column boundaries;
+    multi-column boundaries partition on the first key column's value only (a coarser, still
+    order-respecting cut: every row of partition i sorts before every row of partition i+1)."""
+    first = sort_key.get_columns()[0]
+    bounds = find_partition_indices(codes, boundaries, table.columns[first], sort_key.get_descending())
+    parts, last = [], 0
+    for idx in bounds:
+        idx = max(idx, last)
+        parts.append(table.slice(last, idx))
+        last = idx
+    parts.append(table.slice(last, table.num_rows))
+    return parts

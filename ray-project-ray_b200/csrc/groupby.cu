@@ -196,7 +196,8 @@ template <typename VIn, typename T, bool CENTER>
 __global__ void __launch_bounds__(G_THREADS)
 seg_reduce_kernel(const uint32_t* __restrict__ group_starts, const uint32_t* __restrict__ num_groups_p,
                   const uint32_t* __restrict__ perm, const VIn* __restrict__ values, uint64_t n,
-                  const double* __restrict__ center, OutPtrs<T> out, TileSummary<T>* __restrict__ summ) {
+                  const double* __restrict__ center, const int64_t* __restrict__ weights,
+                  const double* __restrict__ addend, OutPtrs<T> out, TileSummary<T>* __restrict__ summ) {
   __shared__ uint8_t s_flag[G_TILE];
   __shared__ uint32_t s_lohi[2];
   __shared__ uint32_t s_wcnt[G_THREADS / 32];
@@ -215,12 +216,20 @@ seg_reduce_kernel(const uint32_t* __restrict__ group_starts, const uint32_t* __r
 
   // values of this thread's 8 consecutive rows (issued before the flag barrier)
   VIn v[G_IPT];
+  double wgt[G_IPT], add[G_IPT];
   const uint64_t r0 = tbase + (uint64_t)threadIdx.x * G_IPT;
 #pragma unroll
   for (int j = 0; j < G_IPT; ++j) {
     const uint64_t i = r0 + j;
     v[j] = (VIn)0;
-    if (i < tend) v[j] = values[perm ? (uint64_t)perm[i] : i];
+    wgt[j] = 1.0;
+    add[j] = 0.0;
+    if (i < tend) {
+      const uint64_t src = perm ? (uint64_t)perm[i] : i;
+      v[j] = values[src];
+      if (CENTER && weights) wgt[j] = (double)weights[src];
+      if (CENTER && addend) add[j] = addend[src];
+    }
   }
   __syncthreads();
 
@@ -259,7 +268,7 @@ seg_reduce_kernel(const uint32_t* __restrict__ group_starts, const uint32_t* __r
       T val;
       if (CENTER) {
         const double d = (double)v[j] - center[run0 + seen];
-        val = (T)(d * d);
+        val = (T)(d * d * wgt[j] + add[j]);
       } else {
         val = (T)v[j];
       }
@@ -386,13 +395,14 @@ static inline uint32_t tiles_of(size_t n) { return (uint32_t)((n + G_TILE - 1) /
 
 template <typename VIn, typename T, bool CENTER>
 static int launch_seg_reduce(const uint32_t* group_starts, const uint32_t* num_groups, const uint32_t* perm,
-                             const void* values, size_t n, const double* center, void* sum_out, void* min_out,
-                             void* max_out, void* temp, cudaStream_t stream) {
+                             const void* values, size_t n, const double* center, const int64_t* weights,
+                             const double* addend, void* sum_out, void* min_out, void* max_out, void* temp,
+                             cudaStream_t stream) {
   const uint32_t Tn = tiles_of(n);
   OutPtrs<T> out{(T*)sum_out, (T*)min_out, (T*)max_out};
   TileSummary<T>* summ = (TileSummary<T>*)temp;
   seg_reduce_kernel<VIn, T, CENTER><<<Tn, G_THREADS, 0, stream>>>(group_starts, num_groups, perm, (const VIn*)values, n,
-                                                                  center, out, summ);
+                                                                  center, weights, addend, out, summ);
   B200X_LAUNCH_CHECK("seg_reduce_kernel");
   stitch_kernel<T><<<1, SCAN_THREADS, 0, stream>>>(summ, Tn, num_groups, out);
   B200X_LAUNCH_CHECK("stitch_kernel");
@@ -448,8 +458,8 @@ extern "C" int b200x_group_boundaries(const uint64_t* codes, size_t n, uint32_t*
 
 extern "C" int b200x_segmented_reduce(const uint32_t* group_starts, const uint32_t* num_groups, const uint32_t* perm,
                                       const void* values, int value_type, size_t n, const double* center,
-                                      void* sum_out, void* min_out, void* max_out, void* temp, size_t* temp_bytes,
-                                      void* stream_) {
+                                      const int64_t* weights, const double* addend, void* sum_out, void* min_out,
+                                      void* max_out, void* temp, size_t* temp_bytes, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   if (temp_bytes == nullptr) {
     set_error("b200x_segmented_reduce: temp_bytes is NULL");
@@ -479,12 +489,12 @@ extern "C" int b200x_segmented_reduce(const uint32_t* group_starts, const uint32
   }
   if (center != nullptr) {
     if (value_type == B200X_VAL_I64)
-      return launch_seg_reduce<int64_t, double, true>(group_starts, num_groups, perm, values, n, center, sum_out, min_out, max_out, temp, stream);
-    return launch_seg_reduce<double, double, true>(group_starts, num_groups, perm, values, n, center, sum_out, min_out, max_out, temp, stream);
+      return launch_seg_reduce<int64_t, double, true>(group_starts, num_groups, perm, values, n, center, weights, addend, sum_out, min_out, max_out, temp, stream);
+    return launch_seg_reduce<double, double, true>(group_starts, num_groups, perm, values, n, center, weights, addend, sum_out, min_out, max_out, temp, stream);
   }
   if (value_type == B200X_VAL_I64)
-    return launch_seg_reduce<int64_t, int64_t, false>(group_starts, num_groups, perm, values, n, nullptr, sum_out, min_out, max_out, temp, stream);
-  return launch_seg_reduce<double, double, false>(group_starts, num_groups, perm, values, n, nullptr, sum_out, min_out, max_out, temp, stream);
+    return launch_seg_reduce<int64_t, int64_t, false>(group_starts, num_groups, perm, values, n, nullptr, nullptr, nullptr, sum_out, min_out, max_out, temp, stream);
+  return launch_seg_reduce<double, double, false>(group_starts, num_groups, perm, values, n, nullptr, nullptr, nullptr, sum_out, min_out, max_out, temp, stream);
 }
 
 extern "C" int b200x_group_counts(const uint32_t* group_starts, const uint32_t* num_groups, size_t max_groups, size_t n,

@@ -155,6 +155,7 @@ struct PassArgs {
   uint64_t* kbuf[2];        // ping-pong code buffers
   uint32_t* vbuf[2];        // ping-pong row-index buffers
   uint64_t* codes_out;      // optional: sorted codes (last pass)
+  void* keys_out;           // optional: sorted keys decoded to the column type (last pass, integer types)
   uint32_t* perm_out;       // sorted row indices (last pass)
   const uint32_t* gbase;    // [RADIX] exclusive digit offsets of this pass
   uint32_t* lookback;       // [tiles][RADIX]
@@ -165,19 +166,57 @@ struct PassArgs {
   int desc;
 };
 
+// Lanes of the warp that hold the same 8-bit digit. MATCH.ANY runs on the slow ADU pipe
+// (it capped the pass at ~65% ADU utilisation in profiles/), so the peer mask is built
+// from one VOTE.BALLOT per digit bit: test bit -> ballot -> complement if my bit is 0 -> and.
+__device__ __forceinline__ unsigned match_digit(uint32_t d) {
+  unsigned peers;
+  asm volatile(
+      "{\n"
+      " .reg .pred p;\n"
+      " .reg .b32 m, t;\n"
+      " and.b32 t, %1, 1;   setp.ne.u32 p, t, 0; vote.sync.ballot.b32 m, p, 0xffffffff; @!p not.b32 m, m; mov.b32 %0, m;\n"
+      " and.b32 t, %1, 2;   setp.ne.u32 p, t, 0; vote.sync.ballot.b32 m, p, 0xffffffff; @!p not.b32 m, m; and.b32 %0, %0, m;\n"
+      " and.b32 t, %1, 4;   setp.ne.u32 p, t, 0; vote.sync.ballot.b32 m, p, 0xffffffff; @!p not.b32 m, m; and.b32 %0, %0, m;\n"
+      " and.b32 t, %1, 8;   setp.ne.u32 p, t, 0; vote.sync.ballot.b32 m, p, 0xffffffff; @!p not.b32 m, m; and.b32 %0, %0, m;\n"
+      " and.b32 t, %1, 16;  setp.ne.u32 p, t, 0; vote.sync.ballot.b32 m, p, 0xffffffff; @!p not.b32 m, m; and.b32 %0, %0, m;\n"
+      " and.b32 t, %1, 32;  setp.ne.u32 p, t, 0; vote.sync.ballot.b32 m, p, 0xffffffff; @!p not.b32 m, m; and.b32 %0, %0, m;\n"
+      " and.b32 t, %1, 64;  setp.ne.u32 p, t, 0; vote.sync.ballot.b32 m, p, 0xffffffff; @!p not.b32 m, m; and.b32 %0, %0, m;\n"
+      " and.b32 t, %1, 128; setp.ne.u32 p, t, 0; vote.sync.ballot.b32 m, p, 0xffffffff; @!p not.b32 m, m; and.b32 %0, %0, m;\n"
+      "}\n"
+      : "=r"(peers)
+      : "r"(d));
+  return peers;
+}
+
+// code -> value of the (integer) key column it came from
+__device__ __forceinline__ void store_decoded(void* out, size_t i, uint64_t code, int kt, bool desc) {
+  switch (kt) {
+    case KEY_I64: ((uint64_t*)out)[i] = (desc ? ~code : code) ^ 0x8000000000000000ull; break;
+    case KEY_U64: ((uint64_t*)out)[i] = desc ? ~code : code; break;
+    case KEY_I32: ((uint32_t*)out)[i] = (uint32_t)(desc ? ~code : code) ^ 0x80000000u; break;
+    case KEY_U32: ((uint32_t*)out)[i] = (uint32_t)(desc ? ~code : code); break;
+    case KEY_I16: ((uint16_t*)out)[i] = (uint16_t)((uint16_t)(desc ? ~code : code) ^ 0x8000u); break;
+    case KEY_U16: ((uint16_t*)out)[i] = (uint16_t)(desc ? ~code : code); break;
+    case KEY_I8: ((uint8_t*)out)[i] = (uint8_t)((uint8_t)(desc ? ~code : code) ^ 0x80u); break;
+    default: ((uint8_t*)out)[i] = (uint8_t)(desc ? ~code : code); break;
+  }
+}
+
 template <int THREADS, int IPT>
 struct PassSmem {
   static constexpr int TILE = THREADS * IPT;
   static constexpr int WARPS = THREADS / 32;
-  static constexpr size_t bytes = (size_t)TILE * 8 + (size_t)TILE * 4 + (size_t)WARPS * RADIX * 4 + RADIX * 4 * 2 + 64;
+  static constexpr size_t bytes = (size_t)TILE * 8 + (size_t)TILE * 4 + (size_t)WARPS * RADIX * 2 + RADIX * 4 + 64;
 };
 
-template <int THREADS, int IPT>
-__global__ void __launch_bounds__(THREADS)
+template <int THREADS, int IPT, int MIN_BLOCKS>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
 onesweep_pass_kernel(const PassArgs a) {
   constexpr int TILE = THREADS * IPT;
   constexpr int WARPS = THREADS / 32;
   static_assert(THREADS >= RADIX, "need one thread per digit");
+  static_assert(TILE < 65536, "tile-local offsets are kept in 16 bits");
 
   SortPlan* plan = a.plan;
   if (!plan->active[a.pass]) return;
@@ -185,10 +224,10 @@ onesweep_pass_kernel(const PassArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   uint64_t* skeys = (uint64_t*)smem_raw;                       // [TILE]
   uint32_t* svals = (uint32_t*)(skeys + TILE);                 // [TILE]
-  uint32_t* whist = svals + TILE;                              // [WARPS][RADIX]
-  uint32_t* obase = whist + WARPS * RADIX;                     // [RADIX] global base - tile-local start
-  uint32_t* swarp = obase + RADIX;                             // [RADIX/32] scan scratch (+ tile id)
+  uint32_t* obase = svals + TILE;                              // [RADIX] global base - tile-local start
+  uint16_t* whist = (uint16_t*)(obase + RADIX);                // [WARPS][RADIX]
   __shared__ uint32_t s_tile;
+  __shared__ uint32_t swarp[RADIX / 32];
 
   const int tid = threadIdx.x;
   const unsigned lane = tid & 31;
@@ -200,64 +239,62 @@ onesweep_pass_kernel(const PassArgs a) {
   // Tiles are handed out in launch order so that a tile only ever waits on
   // tiles that are already resident (no look-back deadlock).
   if (tid == 0) s_tile = atomicAdd(&plan->tile_counter[a.pass], 1u);
-  for (int i = tid; i < WARPS * RADIX; i += THREADS) whist[i] = 0;
+  for (int i = tid; i < WARPS * RADIX / 2; i += THREADS) ((uint32_t*)whist)[i] = 0;
   __syncthreads();
   const uint32_t tile = s_tile;
   const uint64_t tile_base = (uint64_t)tile * TILE;
   const uint32_t n = a.n;
   const uint32_t n_valid = (uint32_t)min((uint64_t)TILE, (uint64_t)n - tile_base);
 
-  const uint64_t* kin;
-  const uint32_t* vin;
-  uint64_t* kout;
-  uint32_t* vout;
-  {
-    const uint32_t sel = plan->src_sel[a.pass];
-    kin = sel ? a.kbuf[1] : a.kbuf[0];
-    vin = sel ? a.vbuf[1] : a.vbuf[0];
-    const uint32_t dsel = is_first ? 0u : (sel ^ 1u);
-    kout = is_last ? a.codes_out : (dsel ? a.kbuf[1] : a.kbuf[0]);
-    vout = is_last ? a.perm_out : (dsel ? a.vbuf[1] : a.vbuf[0]);
-  }
-
   // ---- load: warp-striped, item j of lane l = tile_base + warp*32*IPT + j*32 + l
   uint64_t key[IPT];
   uint32_t val[IPT];
   const uint32_t wbase = (uint32_t)warp * 32 * IPT + lane;
+  if (is_first) {
 #pragma unroll
-  for (int j = 0; j < IPT; ++j) {
-    const uint32_t t = wbase + j * 32;
-    key[j] = ~0ull;
-    val[j] = 0;
-    if (t < n_valid) {
-      const uint64_t i = tile_base + t;
-      if (is_first) {
+    for (int j = 0; j < IPT; ++j) {
+      const uint32_t t = wbase + j * 32;
+      key[j] = ~0ull;
+      val[j] = 0;
+      if (t < n_valid) {
+        const uint64_t i = tile_base + t;
         const uint32_t src = a.perm_in ? a.perm_in[i] : (uint32_t)i;
         key[j] = load_encode(a.raw, src, a.kt, a.desc != 0);
         val[j] = src;
-      } else {
-        key[j] = ld_stream_u64(kin + i);
-        val[j] = ld_stream_u32(vin + i);
+      }
+    }
+  } else {
+    const uint32_t sel = plan->src_sel[a.pass];
+    const uint64_t* kin = (sel ? a.kbuf[1] : a.kbuf[0]) + tile_base;
+    const uint32_t* vin = (sel ? a.vbuf[1] : a.vbuf[0]) + tile_base;
+#pragma unroll
+    for (int j = 0; j < IPT; ++j) {
+      const uint32_t t = wbase + j * 32;
+      key[j] = ~0ull;
+      val[j] = 0;
+      if (t < n_valid) {
+        key[j] = ld_stream_u64(kin + t);
+        val[j] = ld_stream_u32(vin + t);
       }
     }
   }
 
   // ---- rank within the warp (stable: order = (item j, lane))
-  uint32_t* wh = whist + warp * RADIX;
-  uint16_t rank[IPT];
+  uint16_t* wh = whist + warp * RADIX;
+  uint32_t rank[IPT];
   const unsigned lt = lanemask_lt();
 #pragma unroll
   for (int j = 0; j < IPT; ++j) {
     const uint32_t d = (uint32_t)(key[j] >> shift) & (RADIX - 1);
-    const unsigned peers = __match_any_sync(0xffffffffu, d);
+    const unsigned peers = match_digit(d);
     const int leader = __ffs(peers) - 1;
     uint32_t old = 0;
     if ((int)lane == leader) {
       old = wh[d];
-      wh[d] = old + __popc(peers);
+      wh[d] = (uint16_t)(old + __popc(peers));
     }
     old = __shfl_sync(0xffffffffu, old, leader);
-    rank[j] = (uint16_t)(old + __popc(peers & lt));
+    rank[j] = old + __popc(peers & lt);
     __syncwarp();
   }
   __syncthreads();
@@ -269,7 +306,7 @@ onesweep_pass_kernel(const PassArgs a) {
 #pragma unroll
     for (int w = 0; w < WARPS; ++w) {
       const uint32_t c = whist[w * RADIX + tid];
-      whist[w * RADIX + tid] = sum;
+      whist[w * RADIX + tid] = (uint16_t)sum;
       sum += c;
     }
     // padding items of a partial tile all carry digit 255 and sit at the end
@@ -295,7 +332,7 @@ onesweep_pass_kernel(const PassArgs a) {
     for (int k = 0; k < warp; ++k) off += swarp[k];
     my_start += off;
 #pragma unroll
-    for (int w = 0; w < WARPS; ++w) whist[w * RADIX + tid] += my_start;
+    for (int w = 0; w < WARPS; ++w) whist[w * RADIX + tid] += (uint16_t)my_start;
   }
   __syncthreads();
 
@@ -303,7 +340,7 @@ onesweep_pass_kernel(const PassArgs a) {
 #pragma unroll
   for (int j = 0; j < IPT; ++j) {
     const uint32_t d = (uint32_t)(key[j] >> shift) & (RADIX - 1);
-    const uint32_t pos = wh[d] + rank[j];
+    const uint32_t pos = (uint32_t)wh[d] + rank[j];
     skeys[pos] = key[j];
     svals[pos] = val[j];
   }
@@ -317,7 +354,7 @@ onesweep_pass_kernel(const PassArgs a) {
         volatile uint32_t* p = a.lookback + (size_t)t * RADIX + tid;
         uint32_t v = *p;
         while ((v & ~LB_VALUE_MASK) == 0) {
-          __nanosleep(40);
+          __nanosleep(20);
           v = *p;
         }
         excl += v & LB_VALUE_MASK;
@@ -332,19 +369,33 @@ onesweep_pass_kernel(const PassArgs a) {
   __syncthreads();
 
   // ---- coalesced write-out: consecutive threads -> consecutive addresses per digit run
-  if (kout != nullptr) {
-    for (uint32_t i = tid; i < n_valid; i += THREADS) {
-      const uint64_t k = skeys[i];
-      const uint32_t d = (uint32_t)(k >> shift) & (RADIX - 1);
-      const uint32_t dst = obase[d] + i;
-      kout[dst] = k;
-      vout[dst] = svals[i];
+  if (!is_last) {
+    const uint32_t dsel = is_first ? 0u : (plan->src_sel[a.pass] ^ 1u);
+    uint64_t* kout = dsel ? a.kbuf[1] : a.kbuf[0];
+    uint32_t* vout = dsel ? a.vbuf[1] : a.vbuf[0];
+#pragma unroll
+    for (int j = 0; j < IPT; ++j) {
+      const uint32_t i = tid + j * THREADS;
+      if (i < n_valid) {
+        const uint64_t k = skeys[i];
+        const uint32_t d = (uint32_t)(k >> shift) & (RADIX - 1);
+        const uint32_t dst = obase[d] + i;
+        kout[dst] = k;
+        vout[dst] = svals[i];
+      }
     }
   } else {
-    for (uint32_t i = tid; i < n_valid; i += THREADS) {
-      const uint64_t k = skeys[i];
-      const uint32_t d = (uint32_t)(k >> shift) & (RADIX - 1);
-      vout[obase[d] + i] = svals[i];
+#pragma unroll
+    for (int j = 0; j < IPT; ++j) {
+      const uint32_t i = tid + j * THREADS;
+      if (i < n_valid) {
+        const uint64_t k = skeys[i];
+        const uint32_t d = (uint32_t)(k >> shift) & (RADIX - 1);
+        const uint32_t dst = obase[d] + i;
+        a.perm_out[dst] = svals[i];
+        if (a.codes_out) a.codes_out[dst] = k;
+        if (a.keys_out) store_decoded(a.keys_out, dst, k, a.kt, a.desc != 0);
+      }
     }
   }
 }
@@ -354,19 +405,29 @@ onesweep_pass_kernel(const PassArgs a) {
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 no_pass_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ perm_in, int kt, int desc, uint32_t n,
-               const SortPlan* __restrict__ plan, uint64_t* __restrict__ codes_out, uint32_t* __restrict__ perm_out) {
+               const SortPlan* __restrict__ plan, uint64_t* __restrict__ codes_out, void* __restrict__ keys_out,
+               uint32_t* __restrict__ perm_out) {
   if (plan->first >= 0) return;
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
     const uint32_t src = perm_in ? perm_in[i] : (uint32_t)i;
     perm_out[i] = src;
-    if (codes_out) codes_out[i] = load_encode(raw, src, kt, desc != 0);
+    const uint64_t c = load_encode(raw, src, kt, desc != 0);
+    if (codes_out) codes_out[i] = c;
+    if (keys_out) store_decoded(keys_out, i, c, kt, desc != 0);
   }
 }
 
-// Tile shape. 512 x 12 keeps (code, index, rank) in < 64 registers so two
-// blocks share an SM, and stages 6144 pairs (72 KB) in shared memory.
-constexpr int PASS_THREADS = 512;
-constexpr int PASS_IPT = 12;
+// Tile shape (measured on B200, 100M int64 keys, 8 passes): 384x12x3 7.17 ms, 512x12x2 7.38,
+// 256x16x3 7.41, 384x16x2 7.42, 256x24x2 7.69, 1024x8x1 8.63, 512x16x1 8.82, 256x32x1 9.95.
+// 384 x 12 stages 4608 pairs (54 KB) in shared memory; three blocks share an SM.
+#ifndef B200X_PASS_THREADS
+#define B200X_PASS_THREADS 384
+#define B200X_PASS_IPT 12
+#define B200X_PASS_MINB 3
+#endif
+constexpr int PASS_THREADS = B200X_PASS_THREADS;
+constexpr int PASS_IPT = B200X_PASS_IPT;
+constexpr int PASS_MINB = B200X_PASS_MINB;
 constexpr int PASS_TILE = PASS_THREADS * PASS_IPT;
 
 struct TempLayout {
@@ -394,8 +455,8 @@ static TempLayout temp_layout(size_t n, int npass) {
 using namespace b200x;
 
 extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descending, const uint32_t* perm_in,
-                                   uint32_t* perm_out, uint64_t* codes_out, size_t n, int begin_bit, int end_bit,
-                                   void* temp, size_t* temp_bytes, void* stream_) {
+                                   uint32_t* perm_out, uint64_t* codes_out, void* keys_out, size_t n, int begin_bit,
+                                   int end_bit, void* temp, size_t* temp_bytes, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   if (temp_bytes == nullptr) {
     set_error("b200x_radix_argsort: temp_bytes is NULL");
@@ -403,6 +464,11 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
   }
   if (key_type < 0 || key_type >= KEY_TYPE_COUNT) {
     set_error("b200x_radix_argsort: bad key_type %d", key_type);
+    return B200X_ERR_ARG;
+  }
+  if (keys_out != nullptr && (key_type == KEY_F64 || key_type == KEY_F32)) {
+    // -0.0 and NaN payloads do not survive the code; float keys are gathered like any other column
+    set_error("b200x_radix_argsort: keys_out is only available for integer key types");
     return B200X_ERR_ARG;
   }
   if (n >= ((size_t)1 << 30)) {
@@ -464,7 +530,7 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
     int dev = 0;
     B200X_CUDA(cudaGetDevice(&dev));
     if (dev != smem_set_dev) {
-      B200X_CUDA(cudaFuncSetAttribute(onesweep_pass_kernel<PASS_THREADS, PASS_IPT>,
+      B200X_CUDA(cudaFuncSetAttribute(onesweep_pass_kernel<PASS_THREADS, PASS_IPT, PASS_MINB>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       smem_set_dev = dev;
     }
@@ -478,6 +544,7 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
   a.vbuf[0] = (uint32_t*)(base + L.off_v0);
   a.vbuf[1] = (uint32_t*)(base + L.off_v1);
   a.codes_out = codes_out;
+  a.keys_out = keys_out;
   a.perm_out = perm_out;
   a.plan = plan;
   a.n = (uint32_t)n;
@@ -487,7 +554,7 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
     a.pass = p;
     a.gbase = ghist + p * RADIX;
     a.lookback = lookback + (size_t)p * L.tiles * RADIX;
-    onesweep_pass_kernel<PASS_THREADS, PASS_IPT><<<L.tiles, PASS_THREADS, smem, stream>>>(a);
+    onesweep_pass_kernel<PASS_THREADS, PASS_IPT, PASS_MINB><<<L.tiles, PASS_THREADS, smem, stream>>>(a);
     B200X_LAUNCH_CHECK("onesweep_pass_kernel");
   }
   {
@@ -495,7 +562,7 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
     const uint32_t cap = (uint32_t)sms * 8;
     if (blocks > cap) blocks = cap;
     no_pass_kernel<<<blocks, 256, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, plan, codes_out,
-                                               perm_out);
+                                               keys_out, perm_out);
     B200X_LAUNCH_CHECK("no_pass_kernel");
   }
   return B200X_OK;

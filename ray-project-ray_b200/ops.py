@@ -64,10 +64,13 @@ def _temp(nbytes: int, dev: torch.device) -> torch.Tensor:
 
 
 def argsort(keys: torch.Tensor, descending: bool = False, perm_in: Optional[torch.Tensor] = None,
-            want_codes: bool = False, end_bit: int = 0) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
-    """Stable argsort of a 1-D key column. Returns (perm uint32-as-int32 tensor, sorted codes or None).
+            want_codes: bool = False, want_keys: bool = False, end_bit: int = 0):
+    """Stable argsort of a 1-D key column.
 
-    The permutation is stored in an int32 tensor whose bits are the uint32 row indices.
+    Returns (perm, codes, sorted_keys): perm is an int32 tensor whose bits are the uint32 row
+    indices; codes (int64 bits of the uint64 codes) only if want_codes; sorted_keys (the key
+    column in sorted order, written by the last radix pass) only if want_keys and the key
+    type is an integer type (float keys must be gathered: -0.0 / NaN bits are not in the code).
     """
     dev = _require_cuda(keys, perm_in)
     if keys.dim() != 1:
@@ -78,16 +81,16 @@ def argsort(keys: torch.Tensor, descending: bool = False, perm_in: Optional[torc
     kt = key_type_of(keys)
     perm_out = torch.empty(n, dtype=torch.int32, device=dev)
     codes = torch.empty(n, dtype=torch.int64, device=dev) if want_codes else None
+    skeys = torch.empty(n, dtype=keys.dtype, device=dev) if (want_keys and not keys.dtype.is_floating_point) else None
     with torch.cuda.device(dev):
         st = _stream(dev)
         need = _lib.query_temp("b200x_radix_argsort", _ptr(keys), kt, int(descending), _ptr(perm_in), _ptr(perm_out),
-                               _ptr(codes), n, 0, end_bit, stream=st)
+                               _ptr(codes), _ptr(skeys), n, 0, end_bit, stream=st)
         temp = _temp(need, dev)
         nb = ctypes.c_size_t(temp.numel())
         _lib.call("b200x_radix_argsort", _ptr(keys), kt, int(descending), _ptr(perm_in), _ptr(perm_out), _ptr(codes),
-                  n, 0, end_bit, temp.data_ptr(), ctypes.byref(nb), st)
-        temp.record_stream(torch.cuda.current_stream(dev))
-    return perm_out, codes
+                  _ptr(skeys), n, 0, end_bit, temp.data_ptr(), ctypes.byref(nb), st)
+    return perm_out, codes, skeys
 
 
 def gather(col: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
@@ -217,9 +220,10 @@ def value_type_of(t: torch.Tensor) -> int:
 
 def segmented_reduce(starts: torch.Tensor, ng: torch.Tensor, num_groups: int, perm: Optional[torch.Tensor],
                      values: torch.Tensor, n: int, want_sum=True, want_min=False, want_max=False,
-                     center: Optional[torch.Tensor] = None):
+                     center: Optional[torch.Tensor] = None, weights: Optional[torch.Tensor] = None,
+                     addend: Optional[torch.Tensor] = None):
     """Per-group (sum, min, max) of values[perm] over sorted runs; entries not requested are None."""
-    dev = _require_cuda(starts, ng, perm, values, center)
+    dev = _require_cuda(starts, ng, perm, values, center, weights, addend)
     vt = value_type_of(values)
     out_dtype = torch.float64 if center is not None else values.dtype
     mk = lambda want: torch.empty(num_groups, dtype=out_dtype, device=dev) if want else None  # noqa: E731
@@ -227,11 +231,13 @@ def segmented_reduce(starts: torch.Tensor, ng: torch.Tensor, num_groups: int, pe
     with torch.cuda.device(dev):
         st = _stream(dev)
         need = _lib.query_temp("b200x_segmented_reduce", starts.data_ptr(), ng.data_ptr(), _ptr(perm),
-                               values.data_ptr(), vt, n, _ptr(center), _ptr(s), _ptr(mn), _ptr(mx), stream=st)
+                               values.data_ptr(), vt, n, _ptr(center), _ptr(weights), _ptr(addend), _ptr(s), _ptr(mn),
+                               _ptr(mx), stream=st)
         temp = _temp(need, dev)
         nb = ctypes.c_size_t(temp.numel())
         _lib.call("b200x_segmented_reduce", starts.data_ptr(), ng.data_ptr(), _ptr(perm), values.data_ptr(), vt, n,
-                  _ptr(center), _ptr(s), _ptr(mn), _ptr(mx), temp.data_ptr(), ctypes.byref(nb), st)
+                  _ptr(center), _ptr(weights), _ptr(addend), _ptr(s), _ptr(mn), _ptr(mx), temp.data_ptr(),
+                  ctypes.byref(nb), st)
     return s, mn, mx
 
 

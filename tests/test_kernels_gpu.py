@@ -57,13 +57,17 @@ def test_argsort_matches_oracle(cuda_device, kind, n, descending):
     k = _keys(kind, n, rng)
     want = orc.stable_argsort(k, descending)
     t = torch.from_numpy(k).to(cuda_device)
-    perm, codes = ops.argsort(t, descending, want_codes=True)
+    perm, codes, skeys = ops.argsort(t, descending, want_codes=True, want_keys=True)
     torch.cuda.synchronize()
     got = _u32(perm)
     assert got.dtype == np.uint32 and got.shape == (n,)
     np.testing.assert_array_equal(got, want.astype(np.uint32))
     want_codes = orc.encode_keys(k, descending)[want]
     np.testing.assert_array_equal(codes.cpu().numpy().view(np.uint64), want_codes)
+    if k.dtype.kind in "iu":
+        np.testing.assert_array_equal(skeys.cpu().numpy(), k[want])
+    else:
+        assert skeys is None
 
 
 def test_argsort_uint64_and_uint16(cuda_device):
@@ -75,13 +79,13 @@ def test_argsort_uint64_and_uint16(cuda_device):
     want = orc.stable_argsort_multi([hi, lo], False)
     thi = torch.from_numpy(hi.view(np.int64)).to(cuda_device).view(torch.uint64)
     tlo = torch.from_numpy(lo.view(np.int16)).to(cuda_device).view(torch.uint16)
-    p1, _ = ops.argsort(tlo, False)
-    p2, _ = ops.argsort(thi, False, perm_in=p1)
+    p1, _, _ = ops.argsort(tlo, False)
+    p2, _, _ = ops.argsort(thi, False, perm_in=p1)
     np.testing.assert_array_equal(_u32(p2), want.astype(np.uint32))
     # descending multi-column: both columns descending, ties keep input order
     want = orc.stable_argsort_multi([hi, lo], True)
-    p1, _ = ops.argsort(tlo, True)
-    p2, _ = ops.argsort(thi, True, perm_in=p1)
+    p1, _, _ = ops.argsort(tlo, True)
+    p2, _, _ = ops.argsort(thi, True, perm_in=p1)
     np.testing.assert_array_equal(_u32(p2), want.astype(np.uint32))
 
 

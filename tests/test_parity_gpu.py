@@ -1,0 +1,345 @@
+"""GPU parity tests of the whole path (Dataset API -> planner -> scheduler -> C ABI kernels)
+against the reference outputs in tests/golden/ and the CPU oracle. Sort order, block contents,
+integer aggregates and counts are bit-exact; float sums / means / stds within 1e-6 relative
+(the tolerance BASELINE.json's north_star states)."""
+import numpy as np
+import pyarrow as pa
+import pyarrow.compute as pac
+import pytest
+import torch
+
+import ray_project_ray_b200.data as rd
+from oracle import exchange_oracle as orc
+from ray_project_ray_b200.aggregate import Count, Max, Mean, Min, Std, Sum
+from ray_project_ray_b200.aggregate_task_spec import SortAggregateTaskSpec
+from ray_project_ray_b200.block import BlockAccessor, DeviceBlock
+from ray_project_ray_b200.context import DataContext
+from ray_project_ray_b200.interfaces import RefBundle, TaskContext
+from ray_project_ray_b200.schedulers import (GpuExchangeScheduler, PullBasedShuffleTaskScheduler,
+                                             PushBasedShuffleTaskScheduler)
+from ray_project_ray_b200.shuffle_task_spec import ShuffleTaskSpec
+from ray_project_ray_b200.sort_task_spec import SortKey, SortTaskSpec
+from tests import _golden as G
+
+pytestmark = pytest.mark.gpu
+FLOAT_RTOL = 1e-6
+
+SCHEDULERS = {"fused": GpuExchangeScheduler, "pull": PullBasedShuffleTaskScheduler, "push": PushBasedShuffleTaskScheduler}
+
+
+@pytest.fixture(autouse=True)
+def _restore_context():
+    ctx = DataContext.get_current()
+    saved = (ctx.use_push_based_shuffle, ctx.use_fused_device_exchange)
+    yield
+    ctx.use_push_based_shuffle, ctx.use_fused_device_exchange = saved
+
+
+def _set_scheduler(name):
+    ctx = DataContext.get_current()
+    ctx.use_fused_device_exchange = name == "fused"
+    ctx.use_push_based_shuffle = name == "push"
+
+
+def _bundles(blocks):
+    dev = [DeviceBlock.from_numpy(b) if b else DeviceBlock.empty() for b in blocks]
+    return [RefBundle([(b, BlockAccessor.for_block(b).get_metadata(None, None))], owns_blocks=True) for b in dev]
+
+
+def _run(sched, spec, blocks, R):
+    out, stats = SCHEDULERS[sched](spec).execute(_bundles(blocks), R, TaskContext(task_idx=0, target_max_block_size=1 << 30))
+    return [b.blocks[0][0] for b in out], stats
+
+
+# ------------------------------------------------------------------------------- sort
+@pytest.mark.parametrize("sched", ["fused", "pull", "push"])
+@pytest.mark.parametrize("case", [c["tag"] for c in G.meta()["sort_cases"] if not c["push"]])
+def test_sort_blocks_equal_reference(case, sched, cuda_device):
+    """Same input blocks + the boundaries the reference sampled -> identical output blocks."""
+    info = next(c for c in G.meta()["sort_cases"] if c["tag"] == case)
+    a = G.arrays()
+    blocks = G.sort_case_blocks(info["case"])
+    desc = info["descending"]
+    bounds = [(b.item(),) for b in a[case + "_bounds"]]
+    if desc:
+        bounds.reverse()  # generate_sort_fn hands descending boundaries to the spec (planner/sort.py:52-54)
+    outs, stats = _run(sched, SortTaskSpec(bounds, SortKey("k", descending=desc)), blocks, len(bounds) + 1)
+    want = G.split_by_sizes(a[case + "_rows"], a[case + "_sizes"])
+    assert [b.num_rows for b in outs] == [len(w) for w in want]
+    key = a[f"sort_{info['case']}_key"]
+    for got, w in zip(outs, want):
+        if len(w):
+            host = got.to_numpy()
+            np.testing.assert_array_equal(host["row"], w)
+            np.testing.assert_array_equal(host["k"].view(np.int64), key[w].view(np.int64))  # bit-exact incl. -0.0
+    assert sorted(stats.keys()) == (["map", "merge", "reduce"] if sched == "push" else ["map", "reduce"])
+
+
+@pytest.mark.parametrize("sched", ["fused", "pull", "push"])
+@pytest.mark.parametrize("desc", [False, True])
+def test_dataset_sort_nan_keys_global_order(desc, sched, cuda_device):
+    _set_scheduler(sched)
+    a = G.arrays()
+    key = a["sort_f64_nan_key"]
+    ds = rd.from_numpy_columns({"k": key, "row": np.arange(len(key), dtype=np.int64)}, override_num_blocks=8)
+    out = ds.sort("k", descending=desc)
+    assert out.num_blocks() == 8
+    host = out.to_numpy()
+    np.testing.assert_array_equal(host["row"], a[f"sort_f64_nan_{'desc' if desc else 'asc'}_rows"])
+    np.testing.assert_array_equal(host["k"].view(np.int64), key[host["row"]].view(np.int64))
+
+
+@pytest.mark.parametrize("sched", ["fused", "pull"])
+@pytest.mark.parametrize("desc", [False, True])
+def test_dataset_sort_two_columns(desc, sched, cuda_device):
+    _set_scheduler(sched)
+    a = G.arrays()
+    n = len(a["sort2_k1"])
+    ds = rd.from_numpy_columns({"a": a["sort2_k1"], "b": a["sort2_k2"], "row": np.arange(n, dtype=np.int64)},
+                               override_num_blocks=8)
+    out = ds.sort(["a", "b"], descending=desc)
+    np.testing.assert_array_equal(out.to_numpy()["row"], a[f"sort2_{'desc' if desc else 'asc'}_rows"])
+
+
+@pytest.mark.parametrize("sched", ["fused", "pull", "push"])
+def test_sort_with_specified_boundaries(sched, cuda_device):
+    """python/ray/data/tests/test_sort.py:23-51."""
+    _set_scheduler(sched)
+    for case in G.meta()["specified_boundaries"]:
+        ds = rd.range(1000, override_num_blocks=20).sort("id", case["descending"], case["boundaries"])
+        blocks = [list(b["id"]) if b else [] for b in ds.iter_batches(batch_size=None)]
+        assert blocks == case["blocks"]
+
+
+@pytest.mark.parametrize("sched", ["fused", "pull", "push"])
+def test_sort_simple_and_empty(sched, cuda_device):
+    """python/ray/data/tests/test_sort.py:54-76."""
+    _set_scheduler(sched)
+    rng = np.random.default_rng(0)
+    xs = rng.permutation(100).tolist()
+    ds = rd.from_items(xs, override_num_blocks=4)
+    assert [r["item"] for r in ds.sort("item").take(100)] == list(range(100))
+    assert len([n for n in ds.sort("item")._block_num_rows() if n > 0]) == 4
+    assert [r["item"] for r in ds.sort("item", descending=True).take(100)] == list(reversed(range(100)))
+    empty = rd.from_items([])
+    assert empty.sort("item").count() == 0 and empty.sort("item").take() == []
+    assert rd.range(10).filter(lambda r: r["id"] > 10).sort("id").count() == 0
+
+
+@pytest.mark.parametrize("sched", ["fused", "pull", "push"])
+def test_sort_partition_same_key_to_same_block(sched, cuda_device):
+    """python/ray/data/tests/test_sort.py:79-94."""
+    _set_scheduler(sched)
+    ds = rd.from_items([1] * 100).repartition(100).sort("item")
+    sizes = ds._block_num_rows()
+    assert len(sizes) == 100 and sum(1 for s in sizes if s > 0) == 1 and sum(sizes) == 100
+
+
+def test_sort_empty_blocks_block_level(cuda_device):
+    """python/ray/data/tests/test_sort.py:142-191."""
+    acc = BlockAccessor.for_block(pa.Table.from_pydict({}))
+    assert acc.sample(10, SortKey("A")).num_rows == 0
+    parts = acc.sort_and_partition([1, 5, 10], SortKey("A"))
+    assert len(parts) == 4 and all(p.num_rows == 0 for p in parts)
+    assert BlockAccessor.for_block(pa.Table.from_pydict({})).merge_sorted_blocks([pa.Table.from_pydict({})], SortKey("A"))[0].num_rows == 0
+    ds = rd.from_items([{"A": x % 3, "B": x} for x in range(3)], override_num_blocks=3).filter(lambda r: r["A"] == 0)
+    assert list(ds.sort("A").iter_rows()) == [{"A": 0, "B": 0}]
+    assert len(SortTaskSpec.sample_boundaries(rd.range(10).filter(lambda r: r["id"] > 10).get_internal_block_refs(),
+                                              SortKey("id"), 3)) == 2
+
+
+@pytest.mark.parametrize("sched", ["fused", "pull"])
+def test_config1_shape_sort_desc_matches_pyarrow(sched, cuda_device):
+    """BASELINE configs[0] at reduced size: range(n) ids permuted, 8 int64 payload columns,
+    sort('id', descending=True); the whole table must equal take(sort_indices)."""
+    _set_scheduler(sched)
+    n = 200_000
+    rng = np.random.default_rng(1)
+    ids = rng.integers(0, n // 4, n, dtype=np.int64)  # ties: tie order is part of the contract
+    cols = {"id": ids}
+    for j in range(8):
+        cols[f"p{j}"] = rng.integers(0, 2**62, n, dtype=np.int64)
+    out = rd.from_numpy_columns(cols, override_num_blocks=8).sort("id", descending=True)
+    assert out.num_blocks() == 8
+    got = out.to_numpy()
+    table = pa.table(cols)
+    want = table.take(pac.sort_indices(table, [("id", "descending")]))
+    for c in cols:
+        np.testing.assert_array_equal(got[c], want[c].to_numpy())
+
+
+def test_sort_packed_payload_and_narrow_keys(cuda_device):
+    """gensort-shaped rows: (hi uint64, lo uint16) key + 90-byte packed payload (configs[3])."""
+    n = 50_000
+    rng = np.random.default_rng(2)
+    hi = rng.integers(0, 2**63, n, dtype=np.int64).astype(np.uint64) * 2 + 1
+    hi[: n // 3] = hi[n // 3: 2 * (n // 3)]
+    lo = rng.integers(0, 2**16, n).astype(np.uint16)
+    pay = rng.integers(0, 256, (n, 90)).astype(np.uint8)
+    out = rd.from_numpy_columns({"hi": hi, "lo": lo, "payload": pay}, override_num_blocks=4).sort(["hi", "lo"]).to_numpy()
+    order = orc.stable_argsort_multi([hi, lo], False)
+    np.testing.assert_array_equal(out["hi"], hi[order])
+    np.testing.assert_array_equal(out["lo"], lo[order])
+    np.testing.assert_array_equal(out["payload"], pay[order])
+
+
+# ---------------------------------------------------------------------------- groupby
+AGGS = lambda: [Sum("v"), Mean("f"), Count(), Min("v"), Max("f"), Std("f"), Mean("v"), Sum("f")]  # noqa: E731
+
+
+@pytest.mark.parametrize("sched", ["fused", "pull", "push"])
+def test_groupby_equals_reference(sched, cuda_device):
+    a, m = G.arrays(), G.meta()
+    B, n = m["sort_shape"]["blocks"], m["sort_shape"]["rows_per_block"]
+    _set_scheduler(sched)
+    ds = rd.from_numpy_columns({"k": a["agg_k"], "v": a["agg_v"], "f": a["agg_f"],
+                                "unused": np.arange(B * n, dtype=np.int64)}, override_num_blocks=B)
+    out = ds.groupby("k").aggregate(*AGGS())
+    assert out.num_blocks() == B
+    got = out.to_numpy()
+    tag = "agg_pull"
+    assert list(got.keys()) == m[tag + "_columns"]
+    for c in ("k", "sum(v)", "count()", "min(v)"):
+        np.testing.assert_array_equal(got[c], a[f"{tag}_{c}"])
+    np.testing.assert_array_equal(got["max(f)"], a[f"{tag}_max(f)"])
+    for c in ("mean(f)", "std(f)", "mean(v)", "sum(f)"):
+        np.testing.assert_allclose(got[c], a[f"{tag}_{c}"], rtol=FLOAT_RTOL)
+
+
+@pytest.mark.parametrize("sched", ["fused", "pull", "push"])
+def test_small_groupby_goldens(sched, cuda_device):
+    """python/ray/data/tests/test_all_to_all.py:187-317, :508-580: A = x % 3, B = x."""
+    _set_scheduler(sched)
+    m = G.meta()
+    xs = m["small_groupby_input"]
+    ds = rd.from_items([{"A": x % 3, "B": x} for x in xs], override_num_blocks=4)
+    out = ds.groupby("A").aggregate(Sum("B"), Mean("B"), Count(), Min("B"), Max("B"), Std("B")).to_numpy()
+    assert list(out["A"]) == [0, 1, 2]
+    assert list(out["sum(B)"]) == [1683, 1617, 1650]
+    assert list(out["mean(B)"]) == [49.5, 49.0, 50.0]
+    assert list(out["count()"]) == [34, 33, 33]
+    assert list(out["min(B)"]) == m["small_groupby"]["min(B)"] and list(out["max(B)"]) == m["small_groupby"]["max(B)"]
+    np.testing.assert_allclose(out["std(B)"], m["small_groupby"]["std(B)"], rtol=FLOAT_RTOL)
+    assert [r["count()"] for r in ds.groupby("A").count().take_all()] == [34, 33, 33]
+    assert [r["sum(B)"] for r in ds.groupby("A").sum("B").take_all()] == [1683, 1617, 1650]
+    # global aggregation (key=None) and the Dataset shortcuts
+    g = m["small_global_agg"]
+    assert ds.sum("B") == g["sum(B)"][0] == 4950 and ds.min("B") == 0 and ds.max("B") == 99
+    assert ds.mean("B") == g["mean(B)"][0] and abs(ds.std("B") - g["std(B)"][0]) < 1e-9
+    assert ds.aggregate(Sum("B"), Count()) == {"sum(B)": 4950, "count()": 100}
+    # duplicate names
+    cols = ds.groupby("A").aggregate(Sum("B"), Sum("B"), Count(), Count()).columns()
+    assert cols == m["dup_names_columns"]
+    assert sorted(ds.unique("A")) == [0, 1, 2]
+
+
+def test_groupby_skewed_and_single_group(cuda_device):
+    """Zipf-like skew: one key holds most rows (spans many reduction tiles)."""
+    rng = np.random.default_rng(3)
+    n = 400_000
+    k = np.where(rng.random(n) < 0.7, 7, rng.integers(0, 5000, n)).astype(np.int64)
+    v = rng.integers(-2**31, 2**31, n, dtype=np.int64)
+    f = rng.random(n)
+    out = rd.from_numpy_columns({"k": k, "v": v, "f": f}, override_num_blocks=8).groupby("k").aggregate(
+        Sum("v"), Mean("f"), Count(), Std("f")).to_numpy()
+    want = pa.table({"k": k, "v": v, "f": f}).group_by("k").aggregate(
+        [("v", "sum"), ("f", "mean"), ("v", "count"), ("f", "stddev", pac.VarianceOptions(ddof=1))]).sort_by("k")
+    np.testing.assert_array_equal(out["k"], want["k"].to_numpy())
+    np.testing.assert_array_equal(out["sum(v)"], want["v_sum"].to_numpy())
+    np.testing.assert_array_equal(out["count()"], want["v_count"].to_numpy())
+    np.testing.assert_allclose(out["mean(f)"], want["f_mean"].to_numpy(), rtol=FLOAT_RTOL)
+    std_want = np.nan_to_num(want["f_stddev"].to_numpy(zero_copy_only=False).astype(np.float64), nan=0.0)
+    np.testing.assert_allclose(out["std(f)"], std_want, rtol=FLOAT_RTOL, atol=1e-12)
+
+
+def test_aggregate_task_spec_map_reduce_partials(cuda_device):
+    """SortAggregateTaskSpec.map / reduce with partial_reduce, as the push-based merge stage uses them."""
+    rng = np.random.default_rng(4)
+    blocks = [{"k": rng.integers(0, 50, 3000, dtype=np.int64), "f": rng.random(3000)} for _ in range(3)]
+    aggs = [Sum("f"), Mean("f"), Count(), Std("f"), Min("f")]
+    bounds = [(10,), (30,)]
+    maps = [SortAggregateTaskSpec.map(i, DeviceBlock.from_numpy(b), 3, bounds, "k", aggs)[:-1] for i, b in enumerate(blocks)]
+    finals = []
+    for j in range(3):
+        partial, _ = SortAggregateTaskSpec.reduce("k", aggs, *[m[j] for m in maps[:2]], partial_reduce=True)
+        final, meta = SortAggregateTaskSpec.reduce("k", aggs, partial, maps[2][j])
+        finals.append(final)
+        assert meta.num_rows == final.num_rows
+    got = DeviceBlock.concat(finals).to_numpy()
+    want = orc.concat(orc.aggregate_dataset(blocks, "k", [("sum", "f"), ("mean", "f"), ("count", None), ("std", "f"), ("min", "f")], bounds))
+    np.testing.assert_array_equal(got["k"], want["k"])
+    np.testing.assert_array_equal(got["count()"], want["count()"])
+    np.testing.assert_array_equal(got["min(f)"], want["min(f)"])
+    for c in ("sum(f)", "mean(f)", "std(f)"):
+        np.testing.assert_allclose(got[c], np.asarray(want[c], dtype=np.float64), rtol=FLOAT_RTOL)
+
+
+# --------------------------------------------------------------------- random_shuffle
+@pytest.mark.parametrize("sched", ["fused", "pull", "push"])
+def test_random_shuffle_properties(sched, cuda_device):
+    """python/ray/data/tests/test_all_to_all.py:1050-1142."""
+    _set_scheduler(sched)
+    B, n = 8, 2500
+    ds = rd.range(B * n, override_num_blocks=B)
+    r0, r0b, r1 = (ds.random_shuffle(seed=s) for s in (0, 0, 1))
+    a, b, c = (np.concatenate([blk["id"] for blk in r.iter_batches(batch_size=None)]) for r in (r0, r0b, r1))
+    np.testing.assert_array_equal(a, b)                       # same seed, same output
+    assert (a != c).mean() > 0.9                              # different seed
+    np.testing.assert_array_equal(np.sort(a), np.arange(B * n))  # exact multiset permutation
+    assert (a != np.arange(B * n)).mean() > 0.9               # input order not preserved
+    assert r0.num_blocks() == B and sum(r0._block_num_rows()) == B * n
+    for blk in r0.iter_batches(batch_size=None):              # every output draws from every input
+        assert len(set(blk["id"] // n)) == B
+        runs = np.diff(blk["id"]) == 1
+        assert runs.sum() < 0.01 * len(runs) + 10             # no long contiguous runs
+    assert ds.random_shuffle().count() == B * n               # unseeded works
+    assert rd.from_items([]).random_shuffle(seed=0).count() == 0
+    with pytest.raises(DeprecationWarning):
+        ds.random_shuffle(seed=0, num_blocks=3)
+
+
+def test_random_shuffle_pull_equals_oracle_restatement(cuda_device):
+    """Task-structured shuffle (per-block permutation, slices, shuffled slice order, per-reducer
+    permutation) is restated in the oracle with the same Feistel stream: exact equality."""
+    B, n = 4, 1003
+    row = np.arange(B * n, dtype=np.int64)
+    pay = np.random.default_rng(0).integers(0, 256, (B * n, 24)).astype(np.uint8)
+    blocks = [{"row": row[i * n:(i + 1) * n], "pay": pay[i * n:(i + 1) * n]} for i in range(B)]
+    outs, _ = _run("pull", ShuffleTaskSpec(1 << 30, random_shuffle=True, random_seed=5), blocks, B)
+    want = orc.shuffle_dataset(blocks, 5)
+    for got, w in zip(outs, want):
+        host = got.to_numpy()
+        np.testing.assert_array_equal(host["row"], w["row"])
+        np.testing.assert_array_equal(host["pay"], w["pay"])
+
+
+def test_random_shuffle_fused_is_one_global_bijection(cuda_device):
+    n = 100_000
+    pay = np.random.default_rng(1).integers(0, 256, (n, 64)).astype(np.uint8)
+    ds = rd.from_numpy_columns({"id": np.arange(n, dtype=np.int64), "payload": pay}, override_num_blocks=8)
+    out = ds.random_shuffle(seed=0).to_numpy()
+    p = orc.feistel_permutation(n, 0)
+    np.testing.assert_array_equal(out["id"], p.astype(np.int64))
+    np.testing.assert_array_equal(out["payload"], pay[p])
+
+
+def test_repartition(cuda_device):
+    """Split repartition keeps row order; shuffle repartition gives output j the j-th ceil(n/R)-row
+    slice of every input block (ShuffleTaskSpec without random_shuffle, shuffle_task_spec.py:86-93)."""
+    ds = rd.range(1000, override_num_blocks=7).repartition(3)
+    assert ds.num_blocks() == 3 and ds.count() == 1000
+    np.testing.assert_array_equal(ds.to_numpy()["id"], np.arange(1000))
+    src = rd.range(1000, override_num_blocks=7)
+    out = src.repartition(3, shuffle=True)
+    assert out.num_blocks() == 3 and out.count() == 1000
+    ins = [b["id"] for b in src.iter_batches(batch_size=None)]
+    for j, blk in enumerate(out.iter_batches(batch_size=None)):
+        want = np.concatenate([x[j * -(-len(x) // 3):(j + 1) * -(-len(x) // 3)] for x in ins])
+        np.testing.assert_array_equal(blk["id"], want)
+
+
+def test_product_fails_loudly_without_cuda_tensors():
+    from ray_project_ray_b200 import ops
+
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.argsort(torch.zeros(4, dtype=torch.int64))
