@@ -1,0 +1,326 @@
+#!/usr/bin/env python
+"""Headline benchmark: Dataset.sort throughput on B200 (BASELINE.json `metric`).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (config.workload = "sort_100Mx72B"): per GPU 100 M rows of (int64 key `id` drawn uniformly
+from [0, 2^63) as the reference's own sort benchmark draws them,
+release/nightly_tests/dataset/sort.py:39-47, + one 64-byte fixed-width `payload` column) — the
+row shape of BASELINE.json configs[1], the largest configuration that fits one GPU — sorted by
+`Dataset.sort("id")`. A step = one full sort of the resident dataset. N > 1: every rank holds
+100 M rows (weak scaling) and the sort is global (range-partitioned all-to-all over NCCL).
+
+Printed JSON (rank 0, one line): see DESIGN.md §Measurement for every key.
+  value      rows/s, inputs resident in HBM, CUDA events around K steps, max over ranks
+  e2e        same metric through the public API from pinned HOST buffers (H2D + sort + D2H per step)
+  roofline   the dominant kernel (one radix pass), CUDA events on its launching stream
+  cpu_baseline  the reference's CPU path (port calling the same pyarrow kernels) on the host cores
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ROWS_PER_GPU = 100_000_000
+PAYLOAD_BYTES = 64
+ROW_BYTES = 8 + PAYLOAD_BYTES
+CPU_SAMPLE_ROWS = 100_000_000         # the CPU arm sorts the full single-GPU workload (a few seconds on 16+ cores)
+PASS_BYTES_PER_ROW = (20 + 6 * 24 + 24) / 8.0   # algorithmic bytes of one radix pass per row
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rows", type=int, default=ROWS_PER_GPU, help="rows per GPU")
+    ap.add_argument("--cpu-rows", type=int, default=CPU_SAMPLE_ROWS)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smax, reasons, power = [], [], set(), []
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                smax.append(float(f[2]))
+                power.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_arm(rows: int, steps: int, warmup: int):
+    """The reference's CPU path (oracle port) on the host cores: seconds per sort of `rows` rows."""
+    from oracle import cpu_baseline as cb
+
+    threads = cb.host_cores()
+    blocks = cb.make_blocks(rows, PAYLOAD_BYTES, max(threads, 8))
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        outs = cb.sort_blocks(blocks, "id", False, threads)
+        dt = time.perf_counter() - t0
+        assert sum(o.num_rows for o in outs) == rows
+        if i >= warmup:
+            times.append(dt)
+    return sum(times) / len(times), threads, len(blocks)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import pyarrow
+
+    rows = args.cpu_rows
+    steps, warmup = max(1, min(args.steps, 3)), min(args.warmup, 1)
+    sec, threads, nblocks = cpu_arm(rows, steps, warmup)
+    value = rows / sec
+    sample = (f"{rows} rows x {ROW_BYTES} B (same key/payload generator, {nblocks} blocks), pull-based map/reduce on a "
+              f"{threads}-thread pool, pyarrow {pyarrow.__version__}; rows/s is size-normalised")
+    line = {
+        "impl": "reference", "metric": "Dataset.sort rows/s", "value": value, "unit": "rows/s", "n_gpus": args.gpus,
+        "steps": steps, "warmup": warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+        "gb_per_s": value * 2 * ROW_BYTES / 1e9,
+        "config": {"workload": "sort_100Mx72B", "rows_per_gpu": args.rows, "row_bytes": ROW_BYTES, "key": "int64 uniform [0,2^63)",
+                   "payload_bytes": PAYLOAD_BYTES, "cpu_sample_rows": rows},
+        "cpu_baseline": {"value": value, "unit": "rows/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import ray_project_ray_b200.data as rd
+    from ray_project_ray_b200 import _lib
+    from ray_project_ray_b200.block import DeviceBlock
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the device path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.load()
+
+    n = args.rows
+    # synthetic input, generated once on the host (seeded per rank), kept in pinned memory for the e2e leg
+    rng = np.random.default_rng(1000 + rank)
+    h_keys = torch.empty(n, dtype=torch.int64).pin_memory()
+    h_pay = torch.empty((n, PAYLOAD_BYTES), dtype=torch.uint8).pin_memory()
+    chunk = 10_000_000
+    for lo in range(0, n, chunk):
+        hi = min(n, lo + chunk)
+        h_keys[lo:hi] = torch.from_numpy(rng.integers(0, np.iinfo(np.int64).max, hi - lo, dtype=np.int64))
+        h_pay[lo:hi] = torch.from_numpy(rng.integers(0, 256, (hi - lo, PAYLOAD_BYTES), dtype=np.uint8))
+    d_keys = h_keys.to(dev, non_blocking=True)
+    d_pay = h_pay.to(dev, non_blocking=True)
+    torch.cuda.synchronize()
+    nblocks = 8
+    ds = rd.from_torch_columns({"id": d_keys, "payload": d_pay}, override_num_blocks=nblocks)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_resident():
+        return ds.sort("id")
+
+    # ---------------- device-resident: `value`
+    out = None
+    for _ in range(args.warmup):
+        out = step_resident()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    launches0 = lib.b200x_launch_count()
+    lib.b200x_profile_enable(1)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        out = step_resident()
+    e1.record()
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    launches = int(lib.b200x_launch_count() - launches0)
+    import ctypes
+
+    pass_ms, pass_cnt = ctypes.c_double(0), ctypes.c_int(0)
+    lib.b200x_profile_read(ctypes.byref(pass_ms), ctypes.byref(pass_cnt))
+    lib.b200x_profile_enable(0)
+    # correctness of what was timed: global order + multiset checksum (cheap, outside the timed region)
+    host_first = out.get_internal_block_refs()[0]["id"][:4096].cpu().numpy()
+    assert (np.diff(host_first) >= 0).all(), "output is not sorted"
+    assert out.count() > 0 if world > 1 else out.count() == n
+    if world > 1:
+        t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+        cnt = torch.tensor([out.count()], dtype=torch.int64, device=dev)
+        dist.all_reduce(cnt)
+        assert int(cnt.item()) == n * world, "rows lost in the exchange"
+    ms_step = ms_total / args.steps
+    total_rows = n * world
+    value = total_rows / (ms_step / 1e3)
+    del out
+
+    # ---------------- end to end through the public API from pinned host buffers: `e2e`
+    e2e = None
+    if not args.no_e2e:
+        o_keys = torch.empty(int(n * (1.0 if world == 1 else 1.6)), dtype=torch.int64).pin_memory()
+        o_pay = torch.empty((o_keys.numel(), PAYLOAD_BYTES), dtype=torch.uint8).pin_memory()
+
+        def step_e2e():
+            k = h_keys.to(dev, non_blocking=True)
+            p = h_pay.to(dev, non_blocking=True)
+            res = rd.from_torch_columns({"id": k, "payload": p}, override_num_blocks=nblocks).sort("id")
+            lo = 0
+            for b in res.get_internal_block_refs():
+                m = b.num_rows
+                if m:
+                    o_keys[lo:lo + m].copy_(b["id"], non_blocking=True)
+                    o_pay[lo:lo + m].copy_(b["payload"], non_blocking=True)
+                    lo += m
+            return lo
+
+        e_steps = max(1, min(args.steps, 5))
+        for _ in range(min(args.warmup, 2)):
+            step_e2e()
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        got = 0
+        for _ in range(e_steps):
+            got = step_e2e()
+        f1.record()
+        barrier()
+        e_ms = f0.elapsed_time(f1)
+        assert (np.diff(o_keys[:min(got, 100_000)].numpy()) >= 0).all()
+        d2h = got * ROW_BYTES
+        if world > 1:
+            t = torch.tensor([e_ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e_ms = float(t.item())
+        e2e = {"value": total_rows / (e_ms / e_steps / 1e3), "unit": "rows/s", "h2d_bytes_per_step": n * ROW_BYTES,
+               "d2h_bytes_per_step": int(d2h), "ms_per_step": e_ms / e_steps, "steps": e_steps}
+        del o_keys, o_pay
+
+    clocks = sampler.stop() if rank == 0 else None
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except OSError:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+    roof = None
+    if pass_cnt.value:
+        per_launch_ms = pass_ms.value / pass_cnt.value
+        rows_per_launch = n if world == 1 else None
+        if world == 1:
+            ach = rows_per_launch * PASS_BYTES_PER_ROW / (per_launch_ms / 1e3) / 1e9
+            roof = {"bound": "hbm", "kernel": "onesweep_pass_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
+                    "frac": ach / peak, "traffic": None, "peak_source": peak_src, "launches_timed": pass_cnt.value,
+                    "ms_per_launch": per_launch_ms, "share_of_step": pass_ms.value / ms_total,
+                    "algorithmic_bytes_per_launch": rows_per_launch * PASS_BYTES_PER_ROW}
+    op_gbs = total_rows * 2 * ROW_BYTES / (ms_step / 1e3) / 1e9
+    line = {
+        "metric": "Dataset.sort rows/s", "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "int64", "data": "synthetic", "gb_per_s": op_gbs,
+        "config": {"workload": "sort_100Mx72B", "rows_per_gpu": n, "row_bytes": ROW_BYTES,
+                   "key": "int64 uniform [0,2^63)", "payload_bytes": PAYLOAD_BYTES, "blocks_per_gpu": nblocks,
+                   "l2": "inputs (7.2 GB per GPU) exceed the 126 MB L2; no flush needed",
+                   "parallelism": f"range-partitioned x{world}" if world > 1 else "single GPU"},
+        "roofline": roof,
+        "roofline_op": {"bound": "hbm", "achieved": op_gbs / world, "peak": peak, "unit": "GB/s", "frac": op_gbs / world / peak,
+                        "algorithmic_bytes": "2 x row_bytes x rows (SURVEY.md 8d)", "peak_source": peak_src},
+        "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+    }
+    if not args.no_cpu_baseline and world == 1:
+        import pyarrow
+
+        sec, threads, nb = cpu_arm(args.cpu_rows, 1, 0)
+        line["cpu_baseline"] = {"value": args.cpu_rows / sec, "unit": "rows/s", "cores": threads, "kind": "port",
+                                "sample": f"{args.cpu_rows} rows x {ROW_BYTES} B, {nb} blocks, pull-based map/reduce on a "
+                                          f"{threads}-thread pool, pyarrow {pyarrow.__version__}, {sec:.2f} s"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

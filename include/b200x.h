@@ -50,6 +50,15 @@ int b200x_version(void);
 const char* b200x_last_error_string(void);
 int b200x_device_count(void);
 
+/* Measurement hooks (bench.py): number of kernels the library has launched in this process,
+ * and CUDA-event timing of the dominant kernel (the radix pass) on its launching stream:
+ * enable(1) starts recording one event pair per pass launch on the calling thread; read()
+ * synchronises the recorded events and returns their summed duration and their count
+ * (passes skipped on the device, which return in microseconds, are not counted). */
+unsigned long long b200x_launch_count(void);
+int b200x_profile_enable(int on);
+int b200x_profile_read(double* total_ms, int* launches);
+
 /* Stable argsort of one key column (onesweep LSD radix sort, 8-bit digits,
  * decoupled look-back; constant digits are detected on the device and skipped).
  *   perm_out[i] = row that lands at sorted position i

@@ -29,6 +29,9 @@ SIGNATURES = {
     "b200x_version": (c_int, []),
     "b200x_last_error_string": (c_char_p, []),
     "b200x_device_count": (c_int, []),
+    "b200x_launch_count": (ctypes.c_ulonglong, []),
+    "b200x_profile_enable": (c_int, [c_int]),
+    "b200x_profile_read": (c_int, [POINTER(c_double), POINTER(c_int)]),
     "b200x_radix_argsort": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_int,
                                     c_int, c_void_p, _size_p, c_void_p]),
     "b200x_gather_rows": (c_int, [c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_void_p]),

@@ -4,6 +4,9 @@
 #include <stdarg.h>
 #include <stdio.h>
 #include <string.h>
+#include <atomic>
+#include <utility>
+#include <vector>
 
 namespace b200x {
 
@@ -38,9 +41,64 @@ int sm_count() {
   return cached_sms;
 }
 
+static std::atomic<unsigned long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+static thread_local bool t_prof = false;
+static thread_local std::vector<std::pair<cudaEvent_t, cudaEvent_t>> t_events;
+static thread_local size_t t_used = 0;
+static thread_local bool t_open = false;
+
+void prof_begin(cudaStream_t s) {
+  if (!t_prof) return;
+  if (t_used == t_events.size()) {
+    cudaEvent_t a, b;
+    if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) {
+      cudaGetLastError();
+      return;
+    }
+    t_events.emplace_back(a, b);
+  }
+  t_open = cudaEventRecord(t_events[t_used].first, s) == cudaSuccess;
+}
+
+void prof_end(cudaStream_t s) {
+  if (!t_prof || !t_open) return;
+  if (cudaEventRecord(t_events[t_used].second, s) == cudaSuccess) ++t_used;
+  t_open = false;
+}
+
 }  // namespace b200x
 
 extern "C" {
+
+unsigned long long b200x_launch_count(void) { return b200x::g_launches.load(std::memory_order_relaxed); }
+
+int b200x_profile_enable(int on) {
+  b200x::t_prof = on != 0;
+  b200x::t_used = 0;
+  b200x::t_open = false;
+  return B200X_OK;
+}
+
+int b200x_profile_read(double* total_ms, int* launches) {
+  double tot = 0.0;
+  int cnt = 0;
+  for (size_t i = 0; i < b200x::t_used; ++i) {
+    float ms = 0.f;
+    B200X_CUDA(cudaEventSynchronize(b200x::t_events[i].second));
+    B200X_CUDA(cudaEventElapsedTime(&ms, b200x::t_events[i].first, b200x::t_events[i].second));
+    // a pass whose digit is constant returns at once (a few microseconds): not a real launch of the pass
+    if (ms > 0.02f) {
+      tot += ms;
+      ++cnt;
+    }
+  }
+  if (total_ms) *total_ms = tot;
+  if (launches) *launches = cnt;
+  b200x::t_used = 0;
+  return B200X_OK;
+}
 
 int b200x_version(void) { return B200X_VERSION; }
 

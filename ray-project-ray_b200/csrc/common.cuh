@@ -30,6 +30,7 @@ int cuda_fail(cudaError_t e, const char* what);
 
 #define B200X_LAUNCH_CHECK(name)                                  \
   do {                                                            \
+    ::b200x::count_launch();                                      \
     cudaError_t _e = cudaGetLastError();                          \
     if (_e != cudaSuccess) return ::b200x::cuda_fail(_e, name);   \
   } while (0)
@@ -38,6 +39,14 @@ static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; 
 
 // Number of SMs of the current device (cached per device).
 int sm_count();
+
+// Every kernel launch of the library is counted (b200x_launch_count).
+void count_launch();
+
+// Optional CUDA-event bracket around the launches of the dominant kernel (the radix pass),
+// recorded on the launching stream while b200x_profile_enable(1) is in effect.
+void prof_begin(cudaStream_t s);
+void prof_end(cudaStream_t s);
 
 // ---- key encoding: raw column value -> order-preserving 64-bit code -------
 // Ascending order of codes == the order pyarrow.compute.sort_indices uses

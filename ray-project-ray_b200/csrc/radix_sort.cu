@@ -554,7 +554,9 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
     a.pass = p;
     a.gbase = ghist + p * RADIX;
     a.lookback = lookback + (size_t)p * L.tiles * RADIX;
+    prof_begin(stream);
     onesweep_pass_kernel<PASS_THREADS, PASS_IPT, PASS_MINB><<<L.tiles, PASS_THREADS, smem, stream>>>(a);
+    prof_end(stream);
     B200X_LAUNCH_CHECK("onesweep_pass_kernel");
   }
   {

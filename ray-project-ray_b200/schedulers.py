@@ -332,6 +332,13 @@ class GpuExchangeScheduler(ExchangeTaskScheduler):
         input_owned = all(b.owns_blocks for b in refs)
         in_meta = [m for rb in refs for _, m in rb.blocks]
         stats = BlockExecStats.builder()
+        from . import distributed as D
+
+        if D.is_distributed():
+            outs = _distributed_exchange(spec, blocks, output_num_blocks)
+            st = stats.build()
+            out_meta = [DeviceBlockAccessor(b).get_metadata(None, exec_stats=st) for b in outs]
+            return [_bundle(b, m, input_owned) for b, m in zip(outs, out_meta)], {"map": in_meta, "reduce": out_meta}
         if type(spec) is SortTaskSpec:
             boundaries, sort_key = spec._map_args
             outs = fused_sort(blocks, boundaries, sort_key)
@@ -350,6 +357,50 @@ class GpuExchangeScheduler(ExchangeTaskScheduler):
         out_meta = [DeviceBlockAccessor(b).get_metadata(None, exec_stats=st) for b in outs]
         output = [_bundle(b, m, input_owned) for b, m in zip(outs, out_meta)]
         return output, {"map": in_meta, "reduce": out_meta}
+
+
+def _cut_sorted_evenly(table: DeviceBlock, key: str, descending: bool, parts: int) -> List[DeviceBlock]:
+    """Cut a sorted block into `parts` near-equal blocks without splitting a run of equal keys."""
+    n = table.num_rows
+    if parts <= 1 or n == 0:
+        return [table] + [DeviceBlock.empty(table.device) for _ in range(parts - 1)]
+    codes = ops.encode_keys(_contig(table.columns[key]), descending)
+    nominal = [min(n - 1, (i * n) // parts) for i in range(1, parts)]
+    idx = torch.tensor(nominal, dtype=torch.int32, device=table.device)
+    at = ops.gather(codes, idx)
+    cuts = ops.search_sorted_codes(codes, at, upper=False).cpu().tolist()
+    return _cut(table, [int(c) for c in cuts])
+
+
+def _distributed_exchange(spec: ExchangeTaskSpec, blocks: List[DeviceBlock], output_num_blocks: int) -> List[DeviceBlock]:
+    """One process per GPU (torch.distributed initialised): this rank's blocks are its shard; the
+    operator runs across all ranks and this rank keeps its key range / slice, cut into as many
+    output blocks as it had input blocks."""
+    from . import distributed as D
+
+    parts = max(len(blocks), 1)
+    local = DeviceBlock.concat(blocks)
+    if not local.columns:
+        raise ValueError("every rank needs at least one block with a schema in a distributed exchange")
+    if type(spec) is SortTaskSpec:
+        _, sort_key = spec._map_args
+        if sort_key.boundaries:
+            raise NotImplementedError("user-specified boundaries are not supported across ranks")
+        out = D.dist_sort(local, sort_key)
+        return _cut_sorted_evenly(out, sort_key.get_columns()[0], sort_key.get_descending(), parts)
+    if type(spec) is ShuffleTaskSpec:
+        _, upstream_map_fn, random_shuffle, seed = spec._map_args
+        if upstream_map_fn is not None or not random_shuffle:
+            raise NotImplementedError("only random_shuffle runs across ranks")
+        out = D.dist_random_shuffle(local, seed)
+        n = out.num_rows
+        return _cut(out, [(i * n) // parts for i in range(1, parts)])
+    _, key, aggs = spec._map_args
+    k = key[0] if isinstance(key, list) and len(key) == 1 else key
+    out = D.dist_aggregate(local, k, aggs)
+    if k is None:
+        return [out]
+    return _cut_sorted_evenly(out, k, False, parts)
 
 
 def _cut(table: DeviceBlock, cuts: List[int]) -> List[DeviceBlock]:
