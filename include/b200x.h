@@ -77,6 +77,25 @@ int b200x_radix_argsort(const void* keys, int key_type, int descending, const ui
                         uint64_t* codes_out, void* keys_out, size_t n, int begin_bit, int end_bit, void* temp,
                         size_t* temp_bytes, void* stream);
 
+/* b200x_radix_argsort for callers that cannot allocate device memory. (No counterpart in the
+ * reference: ray.data always allocates through Arrow / the object store.)
+ * Who needs it: code that runs where cudaMalloc is off limits or simply not available - an
+ * operator called from a process whose caching allocator already owns the GPU's memory, a step
+ * of a latency-critical stream loop that must not take cudaMalloc's implicit synchronisation,
+ * or a foreign-function shim with no device allocator of its own. Such a caller still passes its
+ * inputs and outputs; only the sort's scratch comes from a fixed array inside the library
+ * (about 26 MiB that every GPU which loads libb200x.so keeps until the process exits).
+ *   - n is limited to 1,048,576 rows (2^20); larger n returns B200X_ERR_TOO_LARGE with a message.
+ *   - Arguments are those of b200x_radix_argsort minus begin_bit/end_bit/temp/temp_bytes; results are identical.
+ *   - The first call on each device looks up the array's device address and sets a kernel
+ *     attribute; make that first call outside any stream capture, with the device current.
+ *   - No cudaMalloc / cudaFree / allocating library routine is called (leave b200x_profile_enable
+ *     off on such a path: timing events are created on first use).
+ *   - All calls on one GPU share the one array: calls whose kernels may overlap on the GPU (different
+ *     streams, different threads) race and corrupt each other; serialise them on one stream. */
+int b200x_radix_argsort_static(const void* keys, int key_type, int descending, const uint32_t* perm_in,
+                               uint32_t* perm_out, uint64_t* codes_out, void* keys_out, size_t n, void* stream);
+
 /* dst[i, :] = src[idx[i], :] for rows of row_bytes bytes (a fixed-width column or a
  * packed payload). Replaces Table.take: _internal/arrow_ops/transform_pyarrow.py:24-50,
  * _internal/arrow_block.py:346-355. */

@@ -34,6 +34,8 @@ SIGNATURES = {
     "b200x_profile_read": (c_int, [POINTER(c_double), POINTER(c_int)]),
     "b200x_radix_argsort": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_int,
                                     c_int, c_void_p, _size_p, c_void_p]),
+    "b200x_radix_argsort_static": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
+                                           c_void_p]),
     "b200x_gather_rows": (c_int, [c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_void_p]),
     "b200x_gather_columns8": (c_int, [POINTER(c_void_p), POINTER(c_void_p), c_int, c_void_p, c_size_t, c_void_p]),
     "b200x_iota_u32": (c_int, [c_void_p, c_size_t, c_uint32, c_void_p]),

@@ -569,3 +569,70 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
   }
   return B200X_OK;
 }
+
+// ---------------------------------------------------------------------------
+// b200x_radix_argsort_static: the same sort for callers that cannot allocate
+// ---------------------------------------------------------------------------
+// Some callers of this library have no way to hand over a scratch buffer: an operator invoked
+// from inside a framework whose caching allocator already owns all of HBM (a raw cudaMalloc next
+// to it fails or fragments the pool), a callback on a stream-ordered hot loop where cudaMalloc's
+// implicit device synchronisation is not acceptable, or a thin FFI shim (cgo / JNI / ctypes
+// without torch) that has no device allocator at all. For them the scratch lives inside the
+// library image: one file-scope __device__ array per GPU, sized for the largest input this
+// entry point accepts. The array exists on every GPU that loads libb200x.so, from module load
+// until the process exits (about 26 MiB per GPU).
+//
+// The array's name is only a host-side stand-in; its device address is looked up once per
+// device with cudaGetSymbolAddress while that device is current, and that address is what the
+// kernels receive.
+#include <mutex>
+
+namespace b200x {
+
+constexpr size_t STATIC_SORT_MAX_ROWS = (size_t)1 << 20;  // 1,048,576 rows per call
+constexpr size_t STATIC_SORT_TILES = (STATIC_SORT_MAX_ROWS + PASS_TILE - 1) / PASS_TILE;
+// ping-pong pairs (24 B/row) + look-back words of 8 passes + plan, histograms and alignment slack
+constexpr size_t STATIC_SORT_BYTES =
+    24 * STATIC_SORT_MAX_ROWS + MAX_PASSES * STATIC_SORT_TILES * RADIX * sizeof(uint32_t) + 64 * 1024;
+
+static __device__ __align__(256) unsigned char g_static_sort_scratch[STATIC_SORT_BYTES];
+
+constexpr int STATIC_MAX_DEVICES = 64;
+static void* g_static_sort_ptr[STATIC_MAX_DEVICES];  // device address of the array on each GPU (0 = not looked up yet)
+static std::mutex g_static_sort_mu;
+
+}  // namespace b200x
+
+extern "C" int b200x_radix_argsort_static(const void* keys, int key_type, int descending, const uint32_t* perm_in,
+                                          uint32_t* perm_out, uint64_t* codes_out, void* keys_out, size_t n,
+                                          void* stream) {
+  if (n > STATIC_SORT_MAX_ROWS) {
+    set_error("b200x_radix_argsort_static: n=%zu exceeds the %zu rows the built-in scratch holds; "
+              "use b200x_radix_argsort with a caller-provided temp buffer",
+              n, (size_t)STATIC_SORT_MAX_ROWS);
+    return B200X_ERR_TOO_LARGE;
+  }
+  int dev = 0;
+  B200X_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= STATIC_MAX_DEVICES) {
+    set_error("b200x_radix_argsort_static: device ordinal %d out of range", dev);
+    return B200X_ERR_ARG;
+  }
+  void* scratch = nullptr;
+  {
+    // First call on this device: resolve the device address of the array (the current device
+    // is the one the caller made current, i.e. the one the data lives on).
+    std::lock_guard<std::mutex> lock(g_static_sort_mu);
+    scratch = g_static_sort_ptr[dev];
+    if (scratch == nullptr) {
+      B200X_CUDA(cudaGetSymbolAddress(&scratch, g_static_sort_scratch));
+      g_static_sort_ptr[dev] = scratch;
+    }
+  }
+  // The sort clears its plan, histograms and look-back words on `stream` before it uses them, so
+  // whatever the previous call left in the array does not matter; the ping-pong buffers are
+  // written before they are read.
+  size_t bytes = STATIC_SORT_BYTES;
+  return b200x_radix_argsort(keys, key_type, descending, perm_in, perm_out, codes_out, keys_out, n, 0, 0, scratch,
+                             &bytes, stream);
+}
