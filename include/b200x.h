@@ -120,8 +120,8 @@ int b200x_encode_keys(const void* keys, int key_type, int descending, size_t n, 
 int b200x_search_sorted_codes(const uint64_t* codes, size_t n, const uint64_t* bound_codes, int num_bounds, int upper,
                               uint64_t* out_index, void* stream);
 
-/* Seeded pseudo-random bijection pi on [0, n) (6-round Feistel network over the smallest
- * even-width binary domain >= n, cycle-walked into range). Deterministic in (seed, n).
+/* Seeded pseudo-random bijection pi on [0, n) (6 alternating Feistel rounds over the 2^ceil(log2 n)
+ * domain, cycle-walked into range). Deterministic in (seed, n).
  *   inverse != 0 evaluates pi^-1.
  * b200x_permute_rows:   dst[j, :] = src[pi(j), :]      (permutation + take fused, no index array)
  * b200x_perm_indices:   out[t] = pi(start + t), t in [0, count)

@@ -232,40 +232,40 @@ def _feistel_spec(n: int, seed: int):
     bits = 0
     while n > 1 and (1 << bits) < n:
         bits += 1
-    k = max(1, (bits + 1) // 2)
-    mask = (1 << k) - 1
+    bits = max(bits, 2)
+    lo = (bits + 1) // 2
+    hi = bits - lo
     keys, st = [], seed & _M64
     for r in range(FEISTEL_ROUNDS):
         st = _splitmix64((st + r) & _M64)
         keys.append(st >> 32)
-    return k, mask, keys
+    return lo, (1 << lo) - 1, (1 << hi) - 1, keys
 
 
 def feistel_permutation(n: int, seed: int, inverse: bool = False) -> np.ndarray:
-    """pi(0..n) of csrc/shuffle.cu as a uint32 array."""
+    """pi(0..n) of csrc/shuffle.cu as a uint32 array: alternating Feistel rounds on the
+    (hi | lo) split of a ceil(log2 n)-bit value, cycle-walked while the result is >= n."""
     if n <= 1:
         return np.arange(n, dtype=np.uint32)
-    k, mask, keys = _feistel_spec(n, seed)
-    x = np.arange(n, dtype=np.uint64)
+    lo_bits, lo_mask, hi_mask, keys = _feistel_spec(n, seed)
+    x = np.arange(n, dtype=np.uint32)
     pending = np.ones(n, dtype=bool)
+    mul = np.uint32(0x9E3779B1)
     with np.errstate(over="ignore"):
         while pending.any():
             cur = x[pending]
-            L = ((cur >> np.uint64(k)) & np.uint64(mask)).astype(np.uint32)
-            R = (cur & np.uint64(mask)).astype(np.uint32)
-            if not inverse:
-                for r in range(FEISTEL_ROUNDS):
-                    F = _fmix32((R * np.uint32(0x9E3779B1) + np.uint32(keys[r])).astype(np.uint32)) & np.uint32(mask)
-                    L, R = R, L ^ F
-            else:
-                for r in range(FEISTEL_ROUNDS - 1, -1, -1):
-                    pr = L
-                    F = _fmix32((pr * np.uint32(0x9E3779B1) + np.uint32(keys[r])).astype(np.uint32)) & np.uint32(mask)
-                    L, R = R ^ F, pr
-            nxt = (L.astype(np.uint64) << np.uint64(k)) | R.astype(np.uint64)
+            L = (cur >> np.uint32(lo_bits)) & np.uint32(hi_mask)
+            R = cur & np.uint32(lo_mask)
+            order = range(FEISTEL_ROUNDS - 1, -1, -1) if inverse else range(FEISTEL_ROUNDS)
+            for r in order:
+                if r % 2 == 0:
+                    L = L ^ (_fmix32((R * mul + np.uint32(keys[r])).astype(np.uint32)) & np.uint32(hi_mask))
+                else:
+                    R = R ^ (_fmix32((L * mul + np.uint32(keys[r])).astype(np.uint32)) & np.uint32(lo_mask))
+            nxt = ((L << np.uint32(lo_bits)) | R).astype(np.uint32)
             x[pending] = nxt
             pending[pending] = nxt >= n
-    return x.astype(np.uint32)
+    return x
 
 
 def random_shuffle_block(table: Table, seed: Optional[int]) -> Table:

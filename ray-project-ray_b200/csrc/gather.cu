@@ -20,13 +20,32 @@ template <typename V>
 __global__ void __launch_bounds__(256)
 gather_rows_kernel(const V* __restrict__ src, const uint32_t* __restrict__ idx, V* __restrict__ dst, uint64_t n,
                    uint32_t vec_per_row) {
-  // one thread per V-sized chunk; grid-stride in units of chunks
+  // one thread per V-sized chunk; grid-stride in units of chunks, four independent
+  // (index -> load -> store) chains in flight per thread
+  constexpr int U = 4;
   const uint64_t total = n * vec_per_row;
-  for (uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (uint64_t)gridDim.x * blockDim.x) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; t + (U - 1) * stride < total; t += U * stride) {
+    uint64_t s[U];
+    uint32_t c[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const uint64_t tt = t + u * stride;
+      const uint64_t r = tt / vec_per_row;
+      c[u] = (uint32_t)(tt - r * vec_per_row);
+      s[u] = idx[r];
+    }
+    V v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) v[u] = src[s[u] * vec_per_row + c[u]];
+#pragma unroll
+    for (int u = 0; u < U; ++u) dst[t + u * stride] = v[u];
+  }
+  for (; t < total; t += stride) {
     const uint64_t r = t / vec_per_row;
     const uint32_t c = (uint32_t)(t - r * vec_per_row);
-    const uint64_t s = idx[r];
-    dst[t] = src[s * vec_per_row + c];
+    dst[t] = src[(uint64_t)idx[r] * vec_per_row + c];
   }
 }
 

@@ -13,10 +13,12 @@
 // different permutations for one seed). What is kept: an exact permutation,
 // fully determined by (seed, n).
 //
-// pi(x): split x into two k-bit halves (2k = smallest even width with 2^2k >= n),
-// run ROUNDS Feistel rounds with a murmur3-finalizer round function keyed from
-// splitmix64(seed), and repeat ("cycle walk") while the result is >= n. The
-// domain is < 4n, so the expected walk is < 4 steps (usually < 2).
+// pi(x): x is split into a low part R (ceil(bits/2) bits) and a high part L (floor(bits/2) bits),
+// bits = ceil(log2 n), and run through ROUNDS alternating Feistel rounds (even rounds:
+// L ^= F(R), odd rounds: R ^= F(L)) with a murmur3-finalizer round function keyed from
+// splitmix64(seed); the result is "cycle walked" (re-encrypted) while it is >= n. The domain
+// 2^bits is < 2n, so the expected walk is < 2 steps. Every round is its own inverse, so
+// pi^-1 runs the rounds backwards.
 #include "common.cuh"
 #include "../../include/b200x.h"
 
@@ -26,8 +28,9 @@ constexpr int FEISTEL_ROUNDS = 6;
 
 struct PermSpec {
   uint64_t n;
-  uint32_t half_bits;
-  uint32_t half_mask;
+  uint32_t lo_bits;   // width of R
+  uint32_t lo_mask;
+  uint32_t hi_mask;   // mask of L
   uint32_t key[FEISTEL_ROUNDS];
 };
 
@@ -51,11 +54,12 @@ static PermSpec make_spec(uint64_t n, uint64_t seed) {
   PermSpec s;
   s.n = n;
   int bits = 0;
-  while (bits < 64 && (n > 1) && (((uint64_t)1 << bits) < n)) ++bits;  // bits = ceil(log2(n))
-  uint32_t k = (uint32_t)((bits + 1) / 2);
-  if (k == 0) k = 1;
-  s.half_bits = k;
-  s.half_mask = (k >= 32) ? 0xFFFFFFFFu : ((1u << k) - 1u);
+  while (bits < 32 && (n > 1) && (((uint64_t)1 << bits) < n)) ++bits;  // bits = ceil(log2(n))
+  if (bits < 2) bits = 2;
+  const uint32_t lo = (uint32_t)((bits + 1) / 2), hi = (uint32_t)bits - lo;
+  s.lo_bits = lo;
+  s.lo_mask = (1u << lo) - 1u;
+  s.hi_mask = (1u << hi) - 1u;
   uint64_t st = seed;
   for (int r = 0; r < FEISTEL_ROUNDS; ++r) {
     st = splitmix64(st + (uint64_t)r);
@@ -64,38 +68,25 @@ static PermSpec make_spec(uint64_t n, uint64_t seed) {
   return s;
 }
 
-__host__ __device__ __forceinline__ uint64_t feistel_fwd_once(const PermSpec& s, uint64_t x) {
-  uint32_t L = (uint32_t)(x >> s.half_bits) & s.half_mask;
-  uint32_t R = (uint32_t)x & s.half_mask;
+__host__ __device__ __forceinline__ uint32_t feistel_once(const PermSpec& s, uint32_t x, bool inverse) {
+  uint32_t L = (x >> s.lo_bits) & s.hi_mask;
+  uint32_t R = x & s.lo_mask;
 #pragma unroll
-  for (int r = 0; r < FEISTEL_ROUNDS; ++r) {
-    const uint32_t F = fmix32(R * 0x9E3779B1u + s.key[r]) & s.half_mask;
-    const uint32_t nl = R;
-    R = L ^ F;
-    L = nl;
+  for (int i = 0; i < FEISTEL_ROUNDS; ++i) {
+    const int r = inverse ? (FEISTEL_ROUNDS - 1 - i) : i;
+    if ((r & 1) == 0) L ^= fmix32(R * 0x9E3779B1u + s.key[r]) & s.hi_mask;
+    else R ^= fmix32(L * 0x9E3779B1u + s.key[r]) & s.lo_mask;
   }
-  return ((uint64_t)L << s.half_bits) | R;
-}
-
-__host__ __device__ __forceinline__ uint64_t feistel_inv_once(const PermSpec& s, uint64_t x) {
-  uint32_t L = (uint32_t)(x >> s.half_bits) & s.half_mask;
-  uint32_t R = (uint32_t)x & s.half_mask;
-#pragma unroll
-  for (int r = FEISTEL_ROUNDS - 1; r >= 0; --r) {
-    const uint32_t pr = L;
-    const uint32_t F = fmix32(pr * 0x9E3779B1u + s.key[r]) & s.half_mask;
-    L = R ^ F;
-    R = pr;
-  }
-  return ((uint64_t)L << s.half_bits) | R;
+  return (L << s.lo_bits) | R;
 }
 
 __host__ __device__ __forceinline__ uint64_t perm_eval(const PermSpec& s, uint64_t x, bool inverse) {
   if (s.n <= 1) return x;
+  uint32_t y = (uint32_t)x;
   do {
-    x = inverse ? feistel_inv_once(s, x) : feistel_fwd_once(s, x);
-  } while (x >= s.n);
-  return x;
+    y = feistel_once(s, y, inverse);
+  } while (y >= s.n);
+  return y;
 }
 
 __global__ void __launch_bounds__(256)
@@ -104,21 +95,33 @@ perm_indices_kernel(const PermSpec s, int inverse, uint64_t start, uint64_t coun
     out[t] = (uint32_t)perm_eval(s, start + t, inverse != 0);
 }
 
-// dst[j] = src[pi(j)], rows of vec_per_row V-sized chunks. LANES_PER_ROW consecutive
-// lanes (a power of two <= 32) share one row so that pi is evaluated once per row.
+// dst[j] = src[pi(j)], rows of vec_per_row V-sized chunks. A warp takes 32 consecutive output
+// rows: each lane evaluates pi for one of them (so the bijection costs one evaluation per row,
+// not one per 16-byte chunk), then groups of lanes_per_row lanes copy the rows, the source row
+// number being broadcast with a shuffle.
 template <typename V>
 __global__ void __launch_bounds__(256)
 permute_rows_kernel(const V* __restrict__ src, V* __restrict__ dst, const PermSpec s, int inverse,
                     uint32_t vec_per_row, uint32_t lanes_per_row) {
   const uint64_t n = s.n;
-  const uint32_t lane_in_row = threadIdx.x % lanes_per_row;
-  const uint64_t rows_per_iter = ((uint64_t)gridDim.x * blockDim.x) / lanes_per_row;
-  uint64_t r = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / lanes_per_row;
-  for (; r < n; r += rows_per_iter) {
-    const uint64_t sr = perm_eval(s, r, inverse != 0);
-    const V* sp = src + sr * vec_per_row;
-    V* dp = dst + r * vec_per_row;
-    for (uint32_t c = lane_in_row; c < vec_per_row; c += lanes_per_row) dp[c] = sp[c];
+  const unsigned lane = threadIdx.x & 31;
+  const uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  const uint32_t groups = 32 / lanes_per_row;      // rows copied concurrently by one warp
+  const uint32_t g = lane / lanes_per_row, c0 = lane % lanes_per_row;
+  for (uint64_t r0 = warp * 32; r0 < n; r0 += nwarps * 32) {
+    const uint64_t mine = r0 + lane;
+    const uint32_t sr = mine < n ? (uint32_t)perm_eval(s, mine, inverse != 0) : 0u;
+    for (uint32_t i = 0; i < 32; i += groups) {
+      const uint32_t ri = i + g;                   // row of this lane group within the warp's 32
+      const uint32_t srow = __shfl_sync(0xffffffffu, sr, ri);
+      const uint64_t r = r0 + ri;
+      if (r < n) {
+        const V* sp = src + (uint64_t)srow * vec_per_row;
+        V* dp = dst + r * vec_per_row;
+        for (uint32_t c = c0; c < vec_per_row; c += lanes_per_row) dp[c] = sp[c];
+      }
+    }
   }
 }
 

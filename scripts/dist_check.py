@@ -1,0 +1,99 @@
+"""Multi-GPU parity check (run under torchrun, one rank per GPU):
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29501 scripts/dist_check.py
+Each rank holds a shard; results of Dataset.sort / groupby().aggregate / random_shuffle across ranks are
+gathered on rank 0 and compared with the CPU oracle run on the concatenated input."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+import torch.distributed as dist
+
+import ray_project_ray_b200.data as rd
+from oracle import exchange_oracle as orc
+from ray_project_ray_b200.aggregate import Count, Mean, Std, Sum
+
+
+def gather_np(arr, world, rank):
+    objs = [None] * world
+    dist.all_gather_object(objs, arr)
+    return objs
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    n = 200_000 + 1000 * rank
+    rng = np.random.default_rng(100 + rank)
+    for kind in ("i64_ties", "f64"):
+        if kind == "i64_ties":
+            key = rng.integers(0, 5000, n, dtype=np.int64)
+        else:
+            key = np.round(rng.standard_normal(n), 3)
+            key[::50] = np.nan
+            key[::70] = -0.0
+        rowid = np.arange(n, dtype=np.int64) + rank * 10_000_000
+        pay = rng.integers(0, 256, (n, 40), dtype=np.uint8)
+        ds = rd.from_numpy_columns({"k": key, "row": rowid, "pay": pay}, override_num_blocks=4)
+        for desc in (False, True):
+            out = ds.sort("k", descending=desc)
+            assert out.num_blocks() == 4
+            got = out.to_numpy()
+            parts = gather_np((got["row"], got["pay"].sum(axis=1)), world, rank)
+            ins = gather_np((key, rowid, pay.sum(axis=1)), world, rank)
+            if rank == 0:
+                allk = np.concatenate([p[0] for p in ins])
+                allr = np.concatenate([p[1] for p in ins])
+                allp = np.concatenate([p[2] for p in ins])
+                order = orc.stable_argsort(allk, desc)
+                np.testing.assert_array_equal(np.concatenate([p[0] for p in parts]), allr[order])
+                np.testing.assert_array_equal(np.concatenate([p[1] for p in parts]), allp[order])
+                sizes = [len(p[0]) for p in parts]
+                print(f"sort {kind} desc={desc}: OK, rows per rank {sizes}", flush=True)
+    # groupby
+    gk = rng.integers(0, 3000, n, dtype=np.int64)
+    gv = rng.integers(-2**31, 2**31, n, dtype=np.int64)
+    gf = rng.random(n)
+    ds = rd.from_numpy_columns({"k": gk, "v": gv, "f": gf}, override_num_blocks=4)
+    got = ds.groupby("k").aggregate(Sum("v"), Mean("f"), Count(), Std("f")).to_numpy()
+    parts = gather_np(got, world, rank)
+    ins = gather_np((gk, gv, gf), world, rank)
+    if rank == 0:
+        allk, allv, allf = (np.concatenate([p[i] for p in ins]) for i in range(3))
+        want = orc.concat(orc.aggregate_dataset([{"k": allk, "v": allv, "f": allf}], "k",
+                                                [("sum", "v"), ("mean", "f"), ("count", None), ("std", "f")], []))
+        cat = {c: np.concatenate([p[c] for p in parts]) for c in parts[0]}
+        np.testing.assert_array_equal(cat["k"], want["k"])
+        np.testing.assert_array_equal(cat["sum(v)"], want["sum(v)"])
+        np.testing.assert_array_equal(cat["count()"], want["count()"])
+        np.testing.assert_allclose(cat["mean(f)"], want["mean(f)"], rtol=1e-6)
+        np.testing.assert_allclose(cat["std(f)"], want["std(f)"], rtol=1e-6)
+        print("groupby: OK, groups per rank", [len(p["k"]) for p in parts], flush=True)
+    g = ds.aggregate(Sum("v"), Count())
+    if rank == 0:
+        assert g == {"sum(v)": int(np.concatenate([p[1] for p in ins]).sum()), "count()": sum(len(p[0]) for p in ins)}, g
+        print("global aggregate: OK", flush=True)
+    # random shuffle
+    rowid = np.arange(n, dtype=np.int64) + rank * 10_000_000
+    ds = rd.from_numpy_columns({"row": rowid}, override_num_blocks=4)
+    a = ds.random_shuffle(seed=0).to_numpy()["row"]
+    b = ds.random_shuffle(seed=0).to_numpy()["row"]
+    c = ds.random_shuffle(seed=1).to_numpy()["row"]
+    pa, pb, pc = (gather_np(x, world, rank) for x in (a, b, c))
+    ins = gather_np(rowid, world, rank)
+    if rank == 0:
+        A, B, C = (np.concatenate(x) for x in (pa, pb, pc))
+        assert np.array_equal(A, B) and (A != C).mean() > 0.9
+        assert np.array_equal(np.sort(A), np.sort(np.concatenate(ins)))
+        for x in pa:
+            assert len(set(x // 10_000_000)) == world  # every rank's output draws from every rank
+        print("random_shuffle: OK (deterministic per seed, exact multiset), rows per rank", [len(x) for x in pa], flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
