@@ -120,6 +120,11 @@ int b200x_encode_keys(const void* keys, int key_type, int descending, size_t n, 
 int b200x_search_sorted_codes(const uint64_t* codes, size_t n, const uint64_t* bound_codes, int num_bounds, int upper,
                               uint64_t* out_index, void* stream);
 
+/* The same search on a key column that is already SORTED in the given direction (codes are computed
+ * on the fly), so cutting a sorted block at boundaries needs no code array. */
+int b200x_search_sorted_keys(const void* keys_sorted, int key_type, int descending, size_t n,
+                             const uint64_t* bound_codes, int num_bounds, int upper, uint64_t* out_index, void* stream);
+
 /* Seeded pseudo-random bijection pi on [0, n) (6 alternating Feistel rounds over the 2^ceil(log2 n)
  * domain, cycle-walked into range). Deterministic in (seed, n).
  *   inverse != 0 evaluates pi^-1.

@@ -41,6 +41,7 @@ SIGNATURES = {
     "b200x_iota_u32": (c_int, [c_void_p, c_size_t, c_uint32, c_void_p]),
     "b200x_encode_keys": (c_int, [c_void_p, c_int, c_int, c_size_t, c_void_p, c_void_p]),
     "b200x_search_sorted_codes": (c_int, [c_void_p, c_size_t, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "b200x_search_sorted_keys": (c_int, [c_void_p, c_int, c_int, c_size_t, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "b200x_permute_rows": (c_int, [c_void_p, c_size_t, c_size_t, c_uint64, c_int, c_void_p, c_void_p]),
     "b200x_perm_indices": (c_int, [c_size_t, c_uint64, c_int, c_size_t, c_size_t, c_void_p, c_void_p]),
     "b200x_perm_indices_host": (c_int, [c_size_t, c_uint64, c_int, c_size_t, c_size_t, c_void_p]),

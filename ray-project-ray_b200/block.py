@@ -444,10 +444,10 @@ class DeviceBlockAccessor(BlockAccessor):
         b = self._block
         if b.num_rows == 0:
             return [DeviceBlock.empty(b.device) for _ in range(len(boundaries) + 1)]
-        table, codes = self.sort(sort_key, want_codes=len(boundaries) > 0)
+        table, _ = self.sort(sort_key)
         if len(boundaries) == 0:
             return [table]
-        return find_partitions(table, codes, boundaries, sort_key)
+        return find_partitions(table, boundaries, sort_key)
 
     @staticmethod
     def merge_sorted_blocks(blocks: List[DeviceBlock], sort_key: "SortKey") -> Tuple[DeviceBlock, BlockMetadata]:
@@ -549,24 +549,22 @@ def boundary_codes(boundaries: Sequence[Any], key_col: torch.Tensor, descending:
     return ops.encode_keys(dev_vals, descending)
 
 
-def find_partition_indices(codes: torch.Tensor, boundaries: Sequence[Any], key_col: torch.Tensor,
-                           descending: bool) -> List[int]:
-    """find_partition_index for every boundary (util.py:719-758) on the sorted code array.
+def find_partition_indices(sorted_keys: torch.Tensor, boundaries: Sequence[Any], descending: bool) -> List[int]:
+    """find_partition_index for every boundary (util.py:719-758) on the SORTED first key column.
     Ascending: #rows < b (lower bound). Descending: #rows >= b (upper bound of the complemented code)."""
     if len(boundaries) == 0:
         return []
-    bc = boundary_codes(boundaries, key_col, descending)
-    idx = ops.search_sorted_codes(codes, bc, upper=descending)
+    bc = boundary_codes(boundaries, sorted_keys, descending)
+    idx = ops.search_sorted_keys(_contig(sorted_keys), descending, bc, upper=descending)
     return [int(x) for x in idx.cpu().tolist()]
 
 
-def find_partitions(table: DeviceBlock, codes: torch.Tensor, boundaries: Sequence[Any],
-                    sort_key: "SortKey") -> List[DeviceBlock]:
+def find_partitions(table: DeviceBlock, boundaries: Sequence[Any], sort_key: "SortKey") -> List[DeviceBlock]:
     """Cut a sorted block at the boundaries (util.py:761-779). Single key column boundaries;
     multi-column boundaries partition on the first key column's value only (a coarser, still
     order-respecting cut: every row of partition i sorts before every row of partition i+1)."""
     first = sort_key.get_columns()[0]
-    bounds = find_partition_indices(codes, boundaries, table.columns[first], sort_key.get_descending())
+    bounds = find_partition_indices(table.columns[first], boundaries, sort_key.get_descending())
     parts, last = [], 0
     for idx in bounds:
         idx = max(idx, last)

@@ -37,9 +37,42 @@ search_kernel(const uint64_t* __restrict__ codes, uint64_t n, const uint64_t* __
   out[b] = lo;
 }
 
+// Same search on a SORTED RAW key column: the code of keys[mid] is computed on the fly, so a
+// sorted block needs no materialised code array to be cut at boundaries.
+__global__ void __launch_bounds__(128)
+search_keys_kernel(const void* __restrict__ keys, int kt, int desc, uint64_t n, const uint64_t* __restrict__ bounds,
+                   int nb, int upper, uint64_t* __restrict__ out) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nb) return;
+  const uint64_t x = bounds[b];
+  uint64_t lo = 0, hi = n;
+  while (lo < hi) {
+    const uint64_t mid = lo + ((hi - lo) >> 1);
+    const uint64_t v = load_encode(keys, mid, kt, desc != 0);
+    const bool go_right = upper ? (v <= x) : (v < x);
+    if (go_right) lo = mid + 1; else hi = mid;
+  }
+  out[b] = lo;
+}
+
 }  // namespace b200x
 
 using namespace b200x;
+
+extern "C" int b200x_search_sorted_keys(const void* keys_sorted, int key_type, int descending, size_t n,
+                                        const uint64_t* bound_codes, int num_bounds, int upper, uint64_t* out_index,
+                                        void* stream_) {
+  if (num_bounds == 0) return B200X_OK;
+  if (bound_codes == nullptr || out_index == nullptr || num_bounds < 0 || (n > 0 && keys_sorted == nullptr) ||
+      key_type < 0 || key_type >= KEY_TYPE_COUNT) {
+    set_error("b200x_search_sorted_keys: bad arguments");
+    return B200X_ERR_ARG;
+  }
+  search_keys_kernel<<<(num_bounds + 127) / 128, 128, 0, (cudaStream_t)stream_>>>(keys_sorted, key_type, descending, n,
+                                                                               bound_codes, num_bounds, upper, out_index);
+  B200X_LAUNCH_CHECK("search_keys_kernel");
+  return B200X_OK;
+}
 
 extern "C" int b200x_encode_keys(const void* keys, int key_type, int descending, size_t n, uint64_t* codes_out,
                                  void* stream_) {

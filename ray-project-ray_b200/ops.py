@@ -153,6 +153,17 @@ def search_sorted_codes(codes: torch.Tensor, bound_codes: torch.Tensor, upper: b
     return out
 
 
+def search_sorted_keys(keys_sorted: torch.Tensor, descending: bool, bound_codes: torch.Tensor, upper: bool) -> torch.Tensor:
+    """Lower/upper bound of boundary codes in a raw key column sorted in the given direction."""
+    dev = _require_cuda(keys_sorted, bound_codes)
+    out = torch.empty(bound_codes.numel(), dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        _lib.call("b200x_search_sorted_keys", keys_sorted.data_ptr(), key_type_of(keys_sorted), int(descending),
+                  keys_sorted.numel(), bound_codes.data_ptr(), bound_codes.numel(), int(upper), out.data_ptr(),
+                  _stream(dev))
+    return out
+
+
 def permute_rows(col: torch.Tensor, seed: int, inverse: bool = False) -> torch.Tensor:
     """out[j] = col[pi_seed(j)] — seeded permutation fused with the row gather."""
     dev = _require_cuda(col)

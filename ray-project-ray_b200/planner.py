@@ -15,7 +15,8 @@ from .aggregate import AggregateFn
 from .aggregate_task_spec import SortAggregateTaskSpec
 from .context import DataContext
 from .interfaces import (AllToAllTransformFn, ExchangeTaskSpec, RefBundle, StatsDict, TaskContext, _NullProgressBar)
-from .schedulers import GpuExchangeScheduler, PullBasedShuffleTaskScheduler, PushBasedShuffleTaskScheduler
+from .schedulers import (AutoBoundaries, GpuExchangeScheduler, PullBasedShuffleTaskScheduler,
+                         PushBasedShuffleTaskScheduler)
 from .shuffle_task_spec import ShuffleTaskSpec
 from .sort_task_spec import SortKey, SortTaskSpec
 
@@ -105,7 +106,9 @@ def generate_sort_fn(sort_key: SortKey,
             return (blocks, {})
         sort_key.validate_schema(_unified_schema(metadata))
         num_outputs = len(blocks)  # same number of output partitions as mappers
-        if not sort_key.boundaries:
+        if not sort_key.boundaries and DataContext.get_current().use_fused_device_exchange:
+            boundaries = AutoBoundaries(num_outputs)  # the fused scheduler cuts the sorted result itself
+        elif not sort_key.boundaries:
             boundaries = SortTaskSpec.sample_boundaries(
                 blocks, sort_key, num_outputs,
                 samples_per_block=max(DataContext.get_current().sort_samples_per_block,
@@ -114,7 +117,7 @@ def generate_sort_fn(sort_key: SortKey,
             boundaries = [(b,) for b in sort_key.boundaries]
             num_outputs = len(boundaries) + 1
         _, ascending = sort_key.to_pandas_sort_args()
-        if not ascending:
+        if not ascending and not isinstance(boundaries, AutoBoundaries):
             boundaries.reverse()
         sort_spec = SortTaskSpec(boundaries=boundaries, sort_key=sort_key)
         return _pick_scheduler(sort_spec).execute(
@@ -169,6 +172,9 @@ def generate_aggregate_fn(key: Optional[str], aggs: List[AggregateFn],
             agg_fn._validate(unified_schema)
         if key is None:
             num_outputs, boundaries = 1, []
+        elif DataContext.get_current().use_fused_device_exchange:
+            num_outputs = len(blocks)
+            boundaries = AutoBoundaries(num_outputs)
         else:
             num_outputs = len(blocks)
             boundaries = SortTaskSpec.sample_boundaries(

@@ -325,6 +325,14 @@ class GpuExchangeScheduler(ExchangeTaskScheduler):
         spec = self._exchange_spec
         if _debug_limit_execution_to_num_blocks is not None or type(spec) not in (
                 SortTaskSpec, ShuffleTaskSpec, SortAggregateTaskSpec):
+            if type(spec) in (SortTaskSpec, SortAggregateTaskSpec) and isinstance(spec._map_args[0], AutoBoundaries):
+                # the task-structured path needs real splitters: sample them now
+                key = spec._map_args[1]
+                sort_key = key if isinstance(key, SortKey) else SortKey(key)
+                bounds = SortTaskSpec.sample_boundaries(_input_blocks(refs), sort_key, output_num_blocks)
+                if sort_key.get_descending():
+                    bounds.reverse()
+                spec._map_args[0] = bounds
             return PullBasedShuffleTaskScheduler(spec).execute(
                 refs, output_num_blocks, task_ctx, map_ray_remote_args, reduce_ray_remote_args,
                 _debug_limit_execution_to_num_blocks=_debug_limit_execution_to_num_blocks)
@@ -359,16 +367,27 @@ class GpuExchangeScheduler(ExchangeTaskScheduler):
         return output, {"map": in_meta, "reduce": out_meta}
 
 
+class AutoBoundaries(list):
+    """Marker passed as `boundaries` when the scheduler may choose the partition cuts itself:
+    `len()` is R-1 like a real boundary list. The fused scheduler then cuts the globally sorted
+    result into R near-equal blocks at tie-respecting positions, which needs no sampling pass
+    (block boundaries are load-balance hints in the reference, not part of its result contract)."""
+
+    def __init__(self, num_outputs: int):
+        super().__init__([None] * max(num_outputs - 1, 0))
+
+
 def _cut_sorted_evenly(table: DeviceBlock, key: str, descending: bool, parts: int) -> List[DeviceBlock]:
-    """Cut a sorted block into `parts` near-equal blocks without splitting a run of equal keys."""
+    """Cut a sorted block into `parts` near-equal blocks without splitting a run of equal keys
+    (equal keys must land in one block: util.py:756-758, tests/test_sort.py:79-94)."""
     n = table.num_rows
     if parts <= 1 or n == 0:
         return [table] + [DeviceBlock.empty(table.device) for _ in range(parts - 1)]
-    codes = ops.encode_keys(_contig(table.columns[key]), descending)
+    col = _contig(table.columns[key])
     nominal = [min(n - 1, (i * n) // parts) for i in range(1, parts)]
     idx = torch.tensor(nominal, dtype=torch.int32, device=table.device)
-    at = ops.gather(codes, idx)
-    cuts = ops.search_sorted_codes(codes, at, upper=False).cpu().tolist()
+    at = ops.encode_keys(ops.gather(col, idx), descending)       # R-1 boundary codes
+    cuts = ops.search_sorted_keys(col, descending, at, upper=False).cpu().tolist()
     return _cut(table, [int(c) for c in cuts])
 
 
@@ -422,13 +441,15 @@ def fused_sort(blocks: List[DeviceBlock], boundaries: List[Any], sort_key: SortK
     if table.num_rows == 0:
         return [DeviceBlock.empty(table.device) for _ in range(R)]
     acc = DeviceBlockAccessor(table)
-    out, codes = acc.sort(sort_key, want_codes=R > 1)
+    out, _ = acc.sort(sort_key)
     if R == 1:
         return [out]
+    first = sort_key.get_columns()[0]
+    if isinstance(boundaries, AutoBoundaries):
+        return _cut_sorted_evenly(out, first, sort_key.get_descending(), R)
     if any(b is None or (isinstance(b, tuple) and b[0] is None) for b in boundaries):
         return [out] + [DeviceBlock.empty(table.device) for _ in range(R - 1)]
-    first = sort_key.get_columns()[0]
-    cuts = find_partition_indices(codes, boundaries, out.columns[first], sort_key.get_descending())
+    cuts = find_partition_indices(out.columns[first], boundaries, sort_key.get_descending())
     return _cut(out, cuts)
 
 
@@ -495,6 +516,7 @@ def fused_aggregate(blocks: List[DeviceBlock], boundaries: List[Any], key, aggs)
     out = aggregate_sorted(table, k, aggs, perm, codes, finalize=True, n=n)
     if R == 1 or any(b is None or (isinstance(b, tuple) and b[0] is None) for b in boundaries):
         return [out] + [DeviceBlock.empty(table.device) for _ in range(R - 1)]
-    gcodes = ops.encode_keys(_contig(out.columns[k]), False)
-    cuts = find_partition_indices(gcodes, boundaries, out.columns[k], False)
+    if isinstance(boundaries, AutoBoundaries):
+        return _cut_sorted_evenly(out, k, False, R)
+    cuts = find_partition_indices(out.columns[k], boundaries, False)
     return _cut(out, cuts)
