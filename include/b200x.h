@@ -59,8 +59,11 @@ unsigned long long b200x_launch_count(void);
 int b200x_profile_enable(int on);
 int b200x_profile_read(double* total_ms, int* launches);
 
-/* Stable argsort of one key column (onesweep LSD radix sort, 8-bit digits,
- * decoupled look-back; constant digits are detected on the device and skipped).
+/* Stable argsort of one key column. Radix sort on order-preserving 64-bit codes with 8-bit digits
+ * and decoupled look-back ("onesweep" passes). The device inspects the keys and picks
+ *   - LSD: one pass per varying byte (constant bytes are skipped), or
+ *   - HYBRID: two passes on the top 16 varying bits, then each of the <= 65536 runs is finished
+ *     in shared memory (3 trips through HBM instead of up to 8) when keys are spread out.
  *   perm_out[i] = row that lands at sorted position i
  *   codes_out   = (optional, may be NULL) the sorted order-preserving 64-bit key codes;
  *                 ascending for both sort directions (see b200x_encode_keys)
@@ -76,6 +79,11 @@ int b200x_profile_read(double* total_ms, int* launches);
 int b200x_radix_argsort(const void* keys, int key_type, int descending, const uint32_t* perm_in, uint32_t* perm_out,
                         uint64_t* codes_out, void* keys_out, size_t n, int begin_bit, int end_bit, void* temp,
                         size_t* temp_bytes, void* stream);
+
+/* Tuning knobs (process-wide). key 0: fewest rows for which b200x_radix_argsort considers its
+ * HYBRID mode (two global passes on the top 16 varying bits, then every run is finished in shared
+ * memory); default 2^22. Results never depend on the mode. */
+int b200x_set_tuning(int key, long long value);
 
 /* b200x_radix_argsort for callers that cannot allocate device memory. (No counterpart in the
  * reference: ray.data always allocates through Arrow / the object store.)

@@ -34,6 +34,7 @@ SIGNATURES = {
     "b200x_profile_read": (c_int, [POINTER(c_double), POINTER(c_int)]),
     "b200x_radix_argsort": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_int,
                                     c_int, c_void_p, _size_p, c_void_p]),
+    "b200x_set_tuning": (c_int, [c_int, ctypes.c_longlong]),
     "b200x_radix_argsort_static": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
                                            c_void_p]),
     "b200x_gather_rows": (c_int, [c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_void_p]),

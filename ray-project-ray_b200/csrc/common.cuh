@@ -101,6 +101,32 @@ __device__ __forceinline__ uint64_t encode_f32_bits(uint32_t b, bool desc) {
   return desc ? (uint64_t)(uint32_t)(~c) : (uint64_t)c;
 }
 
+// Raw bits of element i (zero-extended) and their code, separately: kernels load a batch of raw
+// bits first (one plain load per element, so the loads overlap) and encode afterwards.
+__device__ __forceinline__ uint64_t load_raw_bits(const void* __restrict__ col, size_t i, int width) {
+  switch (width) {
+    case 8: return ((const uint64_t*)col)[i];
+    case 4: return ((const uint32_t*)col)[i];
+    case 2: return ((const uint16_t*)col)[i];
+    default: return ((const uint8_t*)col)[i];
+  }
+}
+
+__device__ __forceinline__ uint64_t encode_bits(uint64_t b, int kt, bool desc) {
+  switch (kt) {
+    case KEY_I64: { const uint64_t c = b ^ 0x8000000000000000ull; return desc ? ~c : c; }
+    case KEY_U64: return desc ? ~b : b;
+    case KEY_F64: return encode_f64_bits(b, desc);
+    case KEY_I32: { const uint32_t c = (uint32_t)b ^ 0x80000000u; return desc ? (uint32_t)~c : c; }
+    case KEY_U32: { const uint32_t c = (uint32_t)b; return desc ? (uint32_t)~c : c; }
+    case KEY_F32: return encode_f32_bits((uint32_t)b, desc);
+    case KEY_I16: { const uint16_t c = (uint16_t)b ^ 0x8000u; return desc ? (uint16_t)~c : c; }
+    case KEY_U16: { const uint16_t c = (uint16_t)b; return desc ? (uint16_t)~c : c; }
+    case KEY_I8: { const uint8_t c = (uint8_t)b ^ 0x80u; return desc ? (uint8_t)~c : c; }
+    default: { const uint8_t c = (uint8_t)b; return desc ? (uint8_t)~c : c; }
+  }
+}
+
 // Load element i of a raw key column and encode it.
 __device__ __forceinline__ uint64_t load_encode(const void* __restrict__ col, size_t i, int kt, bool desc) {
   switch (kt) {

@@ -39,7 +39,28 @@ struct SortPlan {
   int32_t first;                 // first active pass (-1: none)
   int32_t last;                  // last active pass (-1: none)
   uint32_t tile_counter[MAX_PASSES];
+  uint32_t shift[MAX_PASSES];    // bit position of the 8-bit digit of each pass
   uint32_t pad[6];
+};
+
+// Which algorithm sorts this input; decided on the device from the keys themselves.
+//   LSD    : one pass per varying byte, least significant first (any input).
+//   HYBRID : two passes on the top 16 varying bits (LSD order, so the result is grouped into at
+//            most 65536 runs by those bits), then every run - a few thousand pairs - is finished
+//            in shared memory over the remaining low bits. 3 trips through HBM instead of up to 8.
+//            Chosen when there are enough rows, more than 16 varying bits and no run exceeds what
+//            one block can hold (spread-out keys: random ints, hashes, floats, timestamps, ids).
+constexpr uint32_t MODE_LSD = 0, MODE_HYBRID = 1;
+constexpr uint32_t JOINT_BINS = 1u << 16;
+
+struct SortCtl {
+  unsigned long long or_mask;    // OR of all codes
+  unsigned long long nand_mask;  // OR of all ~codes  (a bit varies iff set in both)
+  uint32_t candidate;            // hybrid is worth checking (enough rows, > 16 varying bits)
+  uint32_t mode;
+  uint32_t shiftA, shiftB;       // digit positions of the two global passes (low one first)
+  uint32_t max_run;
+  uint32_t pad[7];
 };
 
 // ---------------------------------------------------------------------------
@@ -50,7 +71,8 @@ constexpr int HIST_IPT = 8;
 
 __global__ void __launch_bounds__(HIST_THREADS)
 hist_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ perm_in, int kt, int desc, uint32_t n,
-            int npass, uint32_t* __restrict__ ghist /*[MAX_PASSES][RADIX]*/) {
+            int npass, uint32_t* __restrict__ ghist /*[MAX_PASSES][RADIX]*/, const SortCtl* __restrict__ ctl) {
+  if (ctl->mode == MODE_HYBRID) return;
   __shared__ uint32_t sh[MAX_PASSES * RADIX];
   for (int i = threadIdx.x; i < MAX_PASSES * RADIX; i += HIST_THREADS) sh[i] = 0;
   __syncthreads();
@@ -130,6 +152,7 @@ plan_kernel(uint32_t* __restrict__ ghist, SortPlan* __restrict__ plan, uint32_t 
       plan->active[p] = a;
       plan->tile_counter[p] = 0;
       plan->src_sel[p] = 0;
+      plan->shift[p] = (uint32_t)(p * RADIX_BITS);
       if (a) {
         if (first < 0) {
           first = p;  // reads the raw column, writes buffer 0
@@ -232,7 +255,7 @@ onesweep_pass_kernel(const PassArgs a) {
   const int tid = threadIdx.x;
   const unsigned lane = tid & 31;
   const int warp = tid >> 5;
-  const int shift = a.pass * RADIX_BITS;
+  const int shift = (int)plan->shift[a.pass];
   const bool is_first = plan->first == a.pass;
   const bool is_last = plan->last == a.pass;
 
@@ -251,17 +274,23 @@ onesweep_pass_kernel(const PassArgs a) {
   uint32_t val[IPT];
   const uint32_t wbase = (uint32_t)warp * 32 * IPT + lane;
   if (is_first) {
+    const int width = key_type_bytes(a.kt);
 #pragma unroll
     for (int j = 0; j < IPT; ++j) {
       const uint32_t t = wbase + j * 32;
-      key[j] = ~0ull;
-      val[j] = 0;
-      if (t < n_valid) {
-        const uint64_t i = tile_base + t;
-        const uint32_t src = a.perm_in ? a.perm_in[i] : (uint32_t)i;
-        key[j] = load_encode(a.raw, src, a.kt, a.desc != 0);
-        val[j] = src;
-      }
+      val[j] = (uint32_t)(tile_base + t);
+      if (a.perm_in) val[j] = (t < n_valid) ? a.perm_in[tile_base + t] : 0u;
+    }
+#pragma unroll
+    for (int j = 0; j < IPT; ++j) {
+      const uint32_t t = wbase + j * 32;
+      key[j] = (t < n_valid) ? load_raw_bits(a.raw, (size_t)val[j], width) : 0ull;
+    }
+#pragma unroll
+    for (int j = 0; j < IPT; ++j) {
+      const uint32_t t = wbase + j * 32;
+      key[j] = (t < n_valid) ? encode_bits(key[j], a.kt, a.desc != 0) : ~0ull;
+      if (t >= n_valid) val[j] = 0;
     }
   } else {
     const uint32_t sel = plan->src_sel[a.pass];
@@ -405,15 +434,423 @@ onesweep_pass_kernel(const PassArgs a) {
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 no_pass_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ perm_in, int kt, int desc, uint32_t n,
-               const SortPlan* __restrict__ plan, uint64_t* __restrict__ codes_out, void* __restrict__ keys_out,
-               uint32_t* __restrict__ perm_out) {
-  if (plan->first >= 0) return;
+               const SortPlan* __restrict__ plan, const SortCtl* __restrict__ ctl, uint64_t* __restrict__ codes_out,
+               void* __restrict__ keys_out, uint32_t* __restrict__ perm_out) {
+  if (plan->first >= 0 || ctl->mode == MODE_HYBRID) return;
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
     const uint32_t src = perm_in ? perm_in[i] : (uint32_t)i;
     perm_out[i] = src;
     const uint64_t c = load_encode(raw, src, kt, desc != 0);
     if (codes_out) codes_out[i] = c;
     if (keys_out) store_decoded(keys_out, i, c, kt, desc != 0);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// HYBRID mode kernels
+// ---------------------------------------------------------------------------
+// Tunable from the host (b200x_set_tuning): fewest rows for which HYBRID is considered.
+static unsigned long long g_hybrid_min_rows = 1ull << 22;
+
+// H1: which bits vary at all. One read of the key column.
+__global__ void __launch_bounds__(512)
+analyze_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ perm_in, int kt, int desc, uint32_t n,
+               SortCtl* __restrict__ ctl) {
+  unsigned long long o = 0, na = 0;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  const int width = key_type_bytes(kt);
+  constexpr int U = 8;  // independent loads in flight per thread
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + (U - 1) * stride < n; i += U * stride) {
+    uint64_t c[U];
+    if (perm_in) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) c[u] = perm_in[i + u * stride];
+#pragma unroll
+      for (int u = 0; u < U; ++u) c[u] = load_raw_bits(raw, (size_t)c[u], width);
+    } else {
+#pragma unroll
+      for (int u = 0; u < U; ++u) c[u] = load_raw_bits(raw, (size_t)(i + u * stride), width);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const uint64_t e = encode_bits(c[u], kt, desc != 0);
+      o |= e;
+      na |= ~e;
+    }
+  }
+  for (; i < n; i += stride) {
+    const uint64_t c = load_encode(raw, perm_in ? (size_t)perm_in[i] : (size_t)i, kt, desc != 0);
+    o |= c;
+    na |= ~c;
+  }
+  unsigned olo = __reduce_or_sync(0xffffffffu, (unsigned)o), ohi = __reduce_or_sync(0xffffffffu, (unsigned)(o >> 32));
+  unsigned nlo = __reduce_or_sync(0xffffffffu, (unsigned)na), nhi = __reduce_or_sync(0xffffffffu, (unsigned)(na >> 32));
+  if ((threadIdx.x & 31) == 0) {
+    atomicOr(&ctl->or_mask, ((unsigned long long)ohi << 32) | olo);
+    atomicOr(&ctl->nand_mask, ((unsigned long long)nhi << 32) | nlo);
+  }
+}
+
+// H2: choose the two global digits = the top 16 varying bits.
+__global__ void hybrid_plan0_kernel(SortCtl* __restrict__ ctl, uint32_t n, unsigned long long min_rows) {
+  const unsigned long long vary = ctl->or_mask & ctl->nand_mask;
+  ctl->mode = MODE_LSD;
+  ctl->candidate = 0;
+  if (vary == 0) return;
+  const int top = 64 - __clzll((long long)vary);  // number of low bits up to and including the highest varying bit
+  if (top > 16 && (unsigned long long)n >= min_rows) {
+    ctl->candidate = 1;
+    ctl->shiftB = (uint32_t)(top - 8);
+    ctl->shiftA = (uint32_t)(top - 16);
+  }
+}
+
+// H3: how many keys fall into each of the 65536 (digit B, digit A) runs. One read of the key
+// column; counts go straight to the 256 KB table with fire-and-forget global atomics (RED), which
+// stays in L2. (A shared-memory table needs 128 KB per block, i.e. 16 warps per SM, and shared
+// atomics at that occupancy ran 5x slower: 1.57 ms per 100 M keys.)
+__global__ void __launch_bounds__(512)
+joint_hist_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ perm_in, int kt, int desc, uint32_t n,
+                  const SortCtl* __restrict__ ctl, uint32_t* __restrict__ joint) {
+  if (!ctl->candidate) return;
+  const uint32_t shiftA = ctl->shiftA;
+  const int width = key_type_bytes(kt);
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  constexpr int U = 8;
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + (U - 1) * stride < n; i += U * stride) {
+    uint64_t c[U];
+    if (perm_in) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) c[u] = perm_in[i + u * stride];
+#pragma unroll
+      for (int u = 0; u < U; ++u) c[u] = load_raw_bits(raw, (size_t)c[u], width);
+    } else {
+#pragma unroll
+      for (int u = 0; u < U; ++u) c[u] = load_raw_bits(raw, (size_t)(i + u * stride), width);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      atomicAdd(&joint[(uint32_t)(encode_bits(c[u], kt, desc != 0) >> shiftA) & (JOINT_BINS - 1)], 1u);
+  }
+  for (; i < n; i += stride) {
+    const uint64_t e = load_encode(raw, perm_in ? (size_t)perm_in[i] : (size_t)i, kt, desc != 0);
+    atomicAdd(&joint[(uint32_t)(e >> shiftA) & (JOINT_BINS - 1)], 1u);
+  }
+}
+
+// H4 (one block of 1024): run starts = exclusive scan of the joint table in (B, A) order; the
+// two digit histograms are its row / column sums; decide the mode.
+constexpr uint32_t FIN_IPT = 8;
+constexpr uint32_t FIN_SMALL_THREADS = 256, FIN_BIG_THREADS = 512;   // runs <= 2048 / <= 4096 pairs
+constexpr uint32_t FIN_MAX = FIN_BIG_THREADS * FIN_IPT;
+
+__global__ void __launch_bounds__(1024)
+hybrid_plan1_kernel(SortCtl* __restrict__ ctl, const uint32_t* __restrict__ joint, uint32_t* __restrict__ run_start,
+                    uint32_t* __restrict__ hbase /*[2][RADIX]*/, SortPlan* __restrict__ hplan, uint32_t n) {
+  __shared__ uint32_t s_warp[32];
+  __shared__ uint32_t s_histA[RADIX], s_histB[RADIX];
+  __shared__ uint32_t s_max;
+  const int tid = threadIdx.x;
+  const unsigned lane = tid & 31, w = tid >> 5;
+  if (tid == 0) {
+    for (int p = 0; p < MAX_PASSES; ++p) {
+      hplan->active[p] = 0;
+      hplan->src_sel[p] = 0;
+      hplan->tile_counter[p] = 0;
+      hplan->shift[p] = 0;
+    }
+    hplan->first = -1;
+    hplan->last = -1;
+  }
+  if (!ctl->candidate) return;
+  if (tid < RADIX) s_histA[tid] = s_histB[tid] = 0;
+  if (tid == 0) s_max = 0;
+  __syncthreads();
+  constexpr int PER = JOINT_BINS / 1024;  // 64 consecutive bins per thread, all of one digit B
+  uint32_t local[PER];
+  uint32_t sum = 0, mx = 0;
+#pragma unroll 8
+  for (int k = 0; k < PER; ++k) {
+    const uint32_t bin = tid * PER + k;
+    const uint32_t c = joint[bin];
+    local[k] = c;
+    sum += c;
+    mx = max(mx, c);
+    if (c) atomicAdd(&s_histA[bin & 255u], c);
+  }
+  if (sum) atomicAdd(&s_histB[(tid * PER) >> 8], sum);
+  atomicMax(&s_max, mx);
+  uint32_t x = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= (unsigned)o) x += y;
+  }
+  if (lane == 31) s_warp[w] = x;
+  __syncthreads();
+  uint32_t off = 0;
+  for (unsigned k = 0; k < w; ++k) off += s_warp[k];
+  uint32_t run = off + x - sum;
+#pragma unroll 8
+  for (int k = 0; k < PER; ++k) {
+    run_start[tid * PER + k] = run;
+    run += local[k];
+  }
+  if (tid == 1023) run_start[JOINT_BINS] = run;
+  __syncthreads();
+  // exclusive scans of the two 256-bin digit histograms (one warp-scan each over 8 values per lane)
+  if (w < 2) {
+    uint32_t* h = w == 0 ? s_histA : s_histB;
+    uint32_t v[8], t = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      v[k] = h[lane * 8 + k];
+      t += v[k];
+    }
+    uint32_t xs = t;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t y = __shfl_up_sync(0xffffffffu, xs, o);
+      if (lane >= (unsigned)o) xs += y;
+    }
+    uint32_t r = xs - t;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      hbase[w * RADIX + lane * 8 + k] = r;
+      r += v[k];
+    }
+  }
+  if (tid == 0) {
+    ctl->max_run = s_max;
+    if (s_max <= FIN_MAX) {
+      ctl->mode = MODE_HYBRID;
+      hplan->active[0] = hplan->active[1] = 1;
+      hplan->shift[0] = ctl->shiftA;
+      hplan->shift[1] = ctl->shiftB;
+      hplan->first = 0;   // pass A reads the raw column and writes buffer 0
+      hplan->last = -1;   // neither pass writes the outputs: the finisher does
+      hplan->src_sel[1] = 0;  // pass B reads buffer 0, writes buffer 1
+    }
+  }
+}
+
+// H5: finish one run (all pairs that agree on the top 16 varying bits) in shared memory.
+struct FinArgs {
+  const uint64_t* kin;   // pairs after the two global passes
+  const uint32_t* vin;
+  uint32_t* perm_out;
+  uint64_t* codes_out;
+  void* keys_out;
+  const uint32_t* run_start;  // [65537]
+  const SortCtl* ctl;
+  int kt;
+  int desc;
+};
+
+constexpr uint32_t TIE_MAX = 48;  // longest group of equal windows the in-place tie repair handles
+
+template <uint32_t THREADS>
+struct FinSmem {
+  uint64_t keys[THREADS * FIN_IPT];
+  uint32_t vals[THREADS * FIN_IPT];
+  uint16_t whist[(THREADS / 32) * RADIX];
+  uint32_t swarp[RADIX / 32];
+  uint32_t slow;
+};
+
+// One stable counting-sort round on up to 8 bits at `shift` over the block's m pairs.
+// Pairs live in registers in warp-striped order (item j of lane l of warp w = w*32*nit + j*32 + l,
+// so register order is memory order) and come back in the same arrangement, now sorted.
+// Slots beyond m hold the all-ones code and stay at the end.
+template <uint32_t THREADS>
+__device__ __forceinline__ void fin_round(uint64_t (&key)[FIN_IPT], uint32_t (&val)[FIN_IPT], uint32_t nit, int shift,
+                                          uint32_t mask, FinSmem<THREADS>& sm, bool reload) {
+  constexpr uint32_t WARPS = THREADS / 32;
+  static_assert(THREADS >= RADIX, "one thread per digit");
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (uint32_t i = tid; i < WARPS * RADIX / 2; i += THREADS) ((uint32_t*)sm.whist)[i] = 0;
+  __syncthreads();
+  uint16_t* wh = sm.whist + warp * RADIX;
+  uint32_t rank[FIN_IPT];
+  const unsigned lt = lanemask_lt();
+#pragma unroll
+  for (uint32_t j = 0; j < FIN_IPT; ++j) {
+    if (j < nit) {
+      const uint32_t d = (uint32_t)(key[j] >> shift) & mask;
+      const unsigned peers = match_digit(d);
+      const int leader = __ffs(peers) - 1;
+      uint32_t old = 0;
+      if ((int)lane == leader) {
+        old = wh[d];
+        wh[d] = (uint16_t)(old + __popc(peers));
+      }
+      old = __shfl_sync(0xffffffffu, old, leader);
+      rank[j] = old + __popc(peers & lt);
+      __syncwarp();
+    }
+  }
+  __syncthreads();
+  uint32_t my_count = 0, my_start = 0;
+  if (tid < RADIX) {
+    uint32_t sum = 0;
+#pragma unroll
+    for (uint32_t w = 0; w < WARPS; ++w) {
+      const uint32_t c = sm.whist[w * RADIX + tid];
+      sm.whist[w * RADIX + tid] = (uint16_t)sum;
+      sum += c;
+    }
+    my_count = sum;
+    uint32_t x = my_count;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= (unsigned)o) x += y;
+    }
+    if (lane == 31) sm.swarp[warp] = x;
+    my_start = x - my_count;
+  }
+  __syncthreads();
+  if (tid < RADIX) {
+    uint32_t off = 0;
+    for (uint32_t k = 0; k < warp; ++k) off += sm.swarp[k];
+    my_start += off;
+#pragma unroll
+    for (uint32_t w = 0; w < WARPS; ++w) sm.whist[w * RADIX + tid] += (uint16_t)my_start;
+  }
+  __syncthreads();
+#pragma unroll
+  for (uint32_t j = 0; j < FIN_IPT; ++j) {
+    if (j < nit) {
+      const uint32_t d = (uint32_t)(key[j] >> shift) & mask;
+      const uint32_t pos = (uint32_t)wh[d] + rank[j];
+      sm.keys[pos] = key[j];
+      sm.vals[pos] = val[j];
+    }
+  }
+  __syncthreads();
+  if (reload) {
+    const uint32_t wbase = warp * 32 * nit + lane;
+#pragma unroll
+    for (uint32_t j = 0; j < FIN_IPT; ++j) {
+      if (j < nit) {
+        key[j] = sm.keys[wbase + j * 32];
+        val[j] = sm.vals[wbase + j * 32];
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ void fin_load(uint64_t (&key)[FIN_IPT], uint32_t (&val)[FIN_IPT], uint32_t nit, uint32_t m,
+                                         const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin) {
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t wbase = warp * 32 * nit + lane;
+#pragma unroll
+  for (uint32_t j = 0; j < FIN_IPT; ++j) {
+    key[j] = ~0ull;
+    val[j] = 0;
+    const uint32_t t = wbase + j * 32;
+    if (j < nit && t < m) {
+      key[j] = ld_stream_u64(kin + t);
+      val[j] = ld_stream_u32(vin + t);
+    }
+  }
+}
+
+// LSD over bits [lo, hi) in rounds of up to 8 bits; the result is left in shared memory.
+template <uint32_t THREADS>
+__device__ __forceinline__ void fin_lsd(uint64_t (&key)[FIN_IPT], uint32_t (&val)[FIN_IPT], uint32_t nit, int lo,
+                                        int hi, FinSmem<THREADS>& sm) {
+  for (int b = lo; b < hi; b += RADIX_BITS) {
+    const int nb = min(RADIX_BITS, hi - b);
+    fin_round<THREADS>(key, val, nit, b, (1u << nb) - 1u, sm, /*reload=*/b + RADIX_BITS < hi);
+  }
+}
+
+// THREADS = 256 serves inputs whose longest run is <= 2048 pairs, THREADS = 512 the rest (<= 4096);
+// both are launched and the one that does not apply returns at once.
+template <uint32_t THREADS>
+__global__ void __launch_bounds__(THREADS, 1024 / THREADS)
+finish_runs_kernel(const FinArgs a) {
+  const SortCtl* ctl = a.ctl;
+  if (ctl->mode != MODE_HYBRID) return;
+  const bool small_cfg = ctl->max_run <= FIN_SMALL_THREADS * FIN_IPT;
+  if (small_cfg != (THREADS == FIN_SMALL_THREADS)) return;
+  const uint32_t start = a.run_start[blockIdx.x];
+  const uint32_t m = a.run_start[blockIdx.x + 1] - start;
+  if (m == 0) return;
+  extern __shared__ __align__(16) unsigned char fin_raw[];
+  FinSmem<THREADS>& sm = *reinterpret_cast<FinSmem<THREADS>*>(fin_raw);
+  const uint32_t tid = threadIdx.x;
+  const int R = (int)ctl->shiftA;  // low bits still unsorted inside the run
+  const uint32_t nit = (m + THREADS - 1) / THREADS;
+  const uint64_t* kin = a.kin + start;
+  const uint32_t* vin = a.vin + start;
+  uint64_t key[FIN_IPT];
+  uint32_t val[FIN_IPT];
+  fin_load(key, val, nit, m, kin, vin);
+  if (tid == 0) sm.slow = 0;
+
+  // Sort by a window of the top 16 remaining bits only (two 8-bit rounds). Pairs that still tie on
+  // the window are rare for spread-out keys and form tiny groups; each element then finds its
+  // place inside its group by comparing the bits below the window with its neighbours in shared
+  // memory. (A single 8-bit round leaves groups of ~m/256 pairs and the neighbour scan then costs
+  // more than the second round: 1.73 vs 1.30 ms per 100 M pairs.) Groups longer than TIE_MAX
+  // (duplicate-heavy keys) send the run down the plain path: LSD over every remaining bit.
+  const int W = 2 * RADIX_BITS;
+  bool tie_repair = R > W;
+  if (tie_repair) fin_lsd<THREADS>(key, val, nit, R - W, R, sm);
+  else fin_lsd<THREADS>(key, val, nit, 0, R, sm);
+  // (fin_lsd ends with a barrier: shared memory holds the pairs sorted by the window)
+  uint32_t fpos[FIN_IPT];
+  if (tie_repair) {
+    const int wshift = R - W;
+    const uint64_t lowmask = (1ull << wshift) - 1ull;
+#pragma unroll
+    for (uint32_t j = 0; j < FIN_IPT; ++j) {
+      const uint32_t i = tid + j * THREADS;
+      fpos[j] = i;
+      if (i < m) {
+        const uint64_t k = sm.keys[i];
+        const uint64_t win = k >> wshift, low = k & lowmask;
+        uint32_t gs = i, before = 0, steps = 0;
+        while (gs > 0 && steps <= TIE_MAX) {
+          const uint64_t o = sm.keys[gs - 1];
+          if ((o >> wshift) != win) break;
+          --gs;
+          ++steps;
+          before += ((o & lowmask) <= low) ? 1u : 0u;  // earlier element, not larger: stays ahead
+        }
+        uint32_t ge = i + 1, after_smaller = 0;
+        while (ge < m && steps <= TIE_MAX) {
+          const uint64_t o = sm.keys[ge];
+          if ((o >> wshift) != win) break;
+          after_smaller += ((o & lowmask) < low) ? 1u : 0u;  // later element, strictly smaller: moves ahead
+          ++ge;
+          ++steps;
+        }
+        if (steps > TIE_MAX) sm.slow = 1;
+        fpos[j] = gs + before + after_smaller;
+      }
+    }
+    __syncthreads();
+    if (sm.slow) {
+      fin_load(key, val, nit, m, kin, vin);
+      fin_lsd<THREADS>(key, val, nit, 0, R, sm);
+      tie_repair = false;
+    }
+  }
+#pragma unroll
+  for (uint32_t j = 0; j < FIN_IPT; ++j) {
+    const uint32_t i = tid + j * THREADS;
+    if (i < m) {
+      const uint32_t dst = start + (tie_repair ? fpos[j] : i);
+      const uint64_t k = sm.keys[i];
+      a.perm_out[dst] = sm.vals[i];
+      if (a.codes_out) a.codes_out[dst] = k;
+      if (a.keys_out) store_decoded(a.keys_out, dst, k, a.kt, a.desc != 0);
+    }
   }
 }
 
@@ -431,7 +868,8 @@ constexpr int PASS_MINB = B200X_PASS_MINB;
 constexpr int PASS_TILE = PASS_THREADS * PASS_IPT;
 
 struct TempLayout {
-  size_t off_plan, off_hist, off_lookback, off_k0, off_k1, off_v0, off_v1, total;
+  size_t off_plan, off_hplan, off_ctl, off_hist, off_hbase, off_joint, off_runs, off_lookback, off_hlookback;
+  size_t off_k0, off_k1, off_v0, off_v1, total;
   uint32_t tiles;
 };
 
@@ -439,13 +877,19 @@ static TempLayout temp_layout(size_t n, int npass) {
   TempLayout L;
   L.tiles = (uint32_t)((n + PASS_TILE - 1) / PASS_TILE);
   size_t o = 0;
-  L.off_plan = o;      o = align_up(o + sizeof(SortPlan), 256);
-  L.off_hist = o;      o = align_up(o + sizeof(uint32_t) * MAX_PASSES * RADIX, 256);
-  L.off_lookback = o;  o = align_up(o + sizeof(uint32_t) * (size_t)npass * L.tiles * RADIX, 256);
-  L.off_k0 = o;        o = align_up(o + n * 8, 256);
-  L.off_k1 = o;        o = align_up(o + n * 8, 256);
-  L.off_v0 = o;        o = align_up(o + n * 4, 256);
-  L.off_v1 = o;        o = align_up(o + n * 4, 256);
+  L.off_plan = o;       o = align_up(o + sizeof(SortPlan), 256);
+  L.off_hplan = o;      o = align_up(o + sizeof(SortPlan), 256);
+  L.off_ctl = o;        o = align_up(o + sizeof(SortCtl), 256);
+  L.off_hist = o;       o = align_up(o + sizeof(uint32_t) * MAX_PASSES * RADIX, 256);
+  L.off_hbase = o;      o = align_up(o + sizeof(uint32_t) * 2 * RADIX, 256);
+  L.off_joint = o;      o = align_up(o + sizeof(uint32_t) * JOINT_BINS, 256);
+  L.off_runs = o;       o = align_up(o + sizeof(uint32_t) * (JOINT_BINS + 1), 256);
+  L.off_lookback = o;   o = align_up(o + sizeof(uint32_t) * (size_t)npass * L.tiles * RADIX, 256);
+  L.off_hlookback = o;  o = align_up(o + sizeof(uint32_t) * (size_t)2 * L.tiles * RADIX, 256);
+  L.off_k0 = o;         o = align_up(o + n * 8, 256);
+  L.off_k1 = o;         o = align_up(o + n * 8, 256);
+  L.off_v0 = o;         o = align_up(o + n * 4, 256);
+  L.off_v1 = o;         o = align_up(o + n * 4, 256);
   L.total = o;
   return L;
 }
@@ -453,6 +897,15 @@ static TempLayout temp_layout(size_t n, int npass) {
 }  // namespace b200x
 
 using namespace b200x;
+
+extern "C" int b200x_set_tuning(int key, long long value) {
+  if (key == 0 && value >= 0) {
+    g_hybrid_min_rows = (unsigned long long)value;
+    return B200X_OK;
+  }
+  set_error("b200x_set_tuning: unknown key %d or bad value", key);
+  return B200X_ERR_ARG;
+}
 
 extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descending, const uint32_t* perm_in,
                                    uint32_t* perm_out, uint64_t* codes_out, void* keys_out, size_t n, int begin_bit,
@@ -506,32 +959,32 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
 
   unsigned char* base = (unsigned char*)temp;
   SortPlan* plan = (SortPlan*)(base + L.off_plan);
+  SortPlan* hplan = (SortPlan*)(base + L.off_hplan);
+  SortCtl* ctl = (SortCtl*)(base + L.off_ctl);
   uint32_t* ghist = (uint32_t*)(base + L.off_hist);
+  uint32_t* hbase = (uint32_t*)(base + L.off_hbase);
+  uint32_t* joint = (uint32_t*)(base + L.off_joint);
+  uint32_t* run_start = (uint32_t*)(base + L.off_runs);
   uint32_t* lookback = (uint32_t*)(base + L.off_lookback);
+  uint32_t* hlookback = (uint32_t*)(base + L.off_hlookback);
 
-  // plan + histograms + look-back words start at zero (one contiguous clear)
+  // plans, control block, histograms and look-back words start at zero (one contiguous clear)
   B200X_CUDA(cudaMemsetAsync(base, 0, L.off_k0, stream));
 
   const int sms = sm_count();
-  {
-    const uint32_t chunk = HIST_THREADS * HIST_IPT;
-    uint32_t blocks = (uint32_t)((n + chunk - 1) / chunk);
-    const uint32_t cap = (uint32_t)sms * 4;
-    if (blocks > cap) blocks = cap;
-    hist_kernel<<<blocks, HIST_THREADS, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, npass, ghist);
-    B200X_LAUNCH_CHECK("hist_kernel");
-  }
-  plan_kernel<<<1, RADIX, 0, stream>>>(ghist, plan, (uint32_t)n, npass);
-  B200X_LAUNCH_CHECK("plan_kernel");
-
+  constexpr size_t pass_smem = PassSmem<PASS_THREADS, PASS_IPT>::bytes;
+  constexpr size_t fin_small_smem = sizeof(FinSmem<FIN_SMALL_THREADS>), fin_big_smem = sizeof(FinSmem<FIN_BIG_THREADS>);
   static thread_local int smem_set_dev = -1;
-  constexpr size_t smem = PassSmem<PASS_THREADS, PASS_IPT>::bytes;
   {
     int dev = 0;
     B200X_CUDA(cudaGetDevice(&dev));
     if (dev != smem_set_dev) {
       B200X_CUDA(cudaFuncSetAttribute(onesweep_pass_kernel<PASS_THREADS, PASS_IPT, PASS_MINB>,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pass_smem));
+      B200X_CUDA(cudaFuncSetAttribute(finish_runs_kernel<FIN_SMALL_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)fin_small_smem));
+      B200X_CUDA(cudaFuncSetAttribute(finish_runs_kernel<FIN_BIG_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)fin_big_smem));
       smem_set_dev = dev;
     }
   }
@@ -546,16 +999,68 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
   a.codes_out = codes_out;
   a.keys_out = keys_out;
   a.perm_out = perm_out;
-  a.plan = plan;
   a.n = (uint32_t)n;
   a.kt = key_type;
   a.desc = descending;
+
+  // ---- analysis + HYBRID path (kernels return at once when the device picks LSD)
+  const bool try_hybrid = bits > 2 * RADIX_BITS && (unsigned long long)n >= g_hybrid_min_rows;
+  if (try_hybrid) {
+    uint32_t blocks = (uint32_t)((n + 512 * 8 - 1) / (512 * 8));
+    if (blocks > (uint32_t)sms * 4) blocks = (uint32_t)sms * 4;
+    analyze_kernel<<<blocks, 512, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, ctl);
+    B200X_LAUNCH_CHECK("analyze_kernel");
+    hybrid_plan0_kernel<<<1, 1, 0, stream>>>(ctl, (uint32_t)n, g_hybrid_min_rows);
+    B200X_LAUNCH_CHECK("hybrid_plan0_kernel");
+    joint_hist_kernel<<<blocks, 512, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, ctl, joint);
+    B200X_LAUNCH_CHECK("joint_hist_kernel");
+    hybrid_plan1_kernel<<<1, 1024, 0, stream>>>(ctl, joint, run_start, hbase, hplan, (uint32_t)n);
+    B200X_LAUNCH_CHECK("hybrid_plan1_kernel");
+    a.plan = hplan;
+    for (int p = 0; p < 2; ++p) {
+      a.pass = p;
+      a.gbase = hbase + p * RADIX;
+      a.lookback = hlookback + (size_t)p * L.tiles * RADIX;
+      prof_begin(stream);
+      onesweep_pass_kernel<PASS_THREADS, PASS_IPT, PASS_MINB><<<L.tiles, PASS_THREADS, pass_smem, stream>>>(a);
+      prof_end(stream);
+      B200X_LAUNCH_CHECK("onesweep_pass_kernel");
+    }
+    FinArgs f;
+    f.kin = a.kbuf[1];
+    f.vin = a.vbuf[1];
+    f.perm_out = perm_out;
+    f.codes_out = codes_out;
+    f.keys_out = keys_out;
+    f.run_start = run_start;
+    f.ctl = ctl;
+    f.kt = key_type;
+    f.desc = descending;
+    finish_runs_kernel<FIN_SMALL_THREADS><<<JOINT_BINS, FIN_SMALL_THREADS, fin_small_smem, stream>>>(f);
+    B200X_LAUNCH_CHECK("finish_runs_kernel");
+    finish_runs_kernel<FIN_BIG_THREADS><<<JOINT_BINS, FIN_BIG_THREADS, fin_big_smem, stream>>>(f);
+    B200X_LAUNCH_CHECK("finish_runs_kernel");
+  }
+
+  // ---- LSD path (kernels return at once when the device picked HYBRID)
+  {
+    const uint32_t chunk = HIST_THREADS * HIST_IPT;
+    uint32_t blocks = (uint32_t)((n + chunk - 1) / chunk);
+    const uint32_t cap = (uint32_t)sms * 4;
+    if (blocks > cap) blocks = cap;
+    hist_kernel<<<blocks, HIST_THREADS, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, npass, ghist,
+                                                     ctl);
+    B200X_LAUNCH_CHECK("hist_kernel");
+  }
+  plan_kernel<<<1, RADIX, 0, stream>>>(ghist, plan, (uint32_t)n, npass);
+  B200X_LAUNCH_CHECK("plan_kernel");
+  a.plan = plan;
   for (int p = 0; p < npass; ++p) {
     a.pass = p;
     a.gbase = ghist + p * RADIX;
     a.lookback = lookback + (size_t)p * L.tiles * RADIX;
     prof_begin(stream);
-    onesweep_pass_kernel<PASS_THREADS, PASS_IPT, PASS_MINB><<<L.tiles, PASS_THREADS, smem, stream>>>(a);
+    onesweep_pass_kernel<PASS_THREADS, PASS_IPT, PASS_MINB><<<L.tiles, PASS_THREADS, pass_smem, stream>>>(a);
     prof_end(stream);
     B200X_LAUNCH_CHECK("onesweep_pass_kernel");
   }
@@ -563,7 +1068,7 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
     uint32_t blocks = (uint32_t)((n + 255) / 256);
     const uint32_t cap = (uint32_t)sms * 8;
     if (blocks > cap) blocks = cap;
-    no_pass_kernel<<<blocks, 256, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, plan, codes_out,
+    no_pass_kernel<<<blocks, 256, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, plan, ctl, codes_out,
                                                keys_out, perm_out);
     B200X_LAUNCH_CHECK("no_pass_kernel");
   }
@@ -591,9 +1096,9 @@ namespace b200x {
 
 constexpr size_t STATIC_SORT_MAX_ROWS = (size_t)1 << 20;  // 1,048,576 rows per call
 constexpr size_t STATIC_SORT_TILES = (STATIC_SORT_MAX_ROWS + PASS_TILE - 1) / PASS_TILE;
-// ping-pong pairs (24 B/row) + look-back words of 8 passes + plan, histograms and alignment slack
+// ping-pong pairs (24 B/row) + look-back words of 8 + 2 passes + plans, histograms, run table and alignment slack
 constexpr size_t STATIC_SORT_BYTES =
-    24 * STATIC_SORT_MAX_ROWS + MAX_PASSES * STATIC_SORT_TILES * RADIX * sizeof(uint32_t) + 64 * 1024;
+    24 * STATIC_SORT_MAX_ROWS + (MAX_PASSES + 2) * STATIC_SORT_TILES * RADIX * sizeof(uint32_t) + 1024 * 1024;
 
 static __device__ __align__(256) unsigned char g_static_sort_scratch[STATIC_SORT_BYTES];
 

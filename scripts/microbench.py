@@ -37,7 +37,7 @@ def main():
         best, avg = timeit(fn)
         print(f"{name:40s} best {best:8.3f} ms avg {avg:8.3f} ms  {bytes_ / best / 1e6:8.1f} GB/s (algorithmic)", flush=True)
 
-    kfull = torch.randint(-2**62, 2**62, (n,), dtype=torch.int64, device=dev, generator=g)
+    kfull = torch.randint(0, 2**63 - 1, (n,), dtype=torch.int64, device=dev, generator=g)
     kperm = torch.randperm(n, device=dev, generator=g)
     k20 = torch.randint(0, 1_000_000, (n,), dtype=torch.int64, device=dev, generator=g)
     run("argsort i64 full-range (8 passes)", lambda: ops.argsort(kfull), n * (8 + 8 * 24))

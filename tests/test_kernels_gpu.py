@@ -70,6 +70,54 @@ def test_argsort_matches_oracle(cuda_device, kind, n, descending):
         assert skeys is None
 
 
+@pytest.fixture
+def force_hybrid():
+    """Let the sort consider its HYBRID mode at any size (default: >= 2^22 rows)."""
+    from ray_project_ray_b200 import _lib
+
+    _lib.call("b200x_set_tuning", 0, 1)
+    yield
+    _lib.call("b200x_set_tuning", 0, 1 << 22)
+
+
+@pytest.mark.parametrize("kind", ["i64_full", "i64_small", "i64_perm", "f64", "f64_ties", "i32", "f32", "i64_dups", "i64_heavy",
+                                  "i64_lowbits", "i64_window_ties"])
+@pytest.mark.parametrize("n", [2, 33, 1000, 70_000, 1_500_000])
+@pytest.mark.parametrize("descending", [False, True])
+def test_argsort_hybrid_mode_matches_oracle(cuda_device, force_hybrid, kind, n, descending):
+    """Same contract with HYBRID forced on: spread keys finish in shared memory, duplicate-heavy or
+    skewed inputs must fall back (runs too long / many equal windows) without changing the result."""
+    rng = np.random.default_rng(99 + n)
+    if kind == "i64_dups":        # few distinct wide keys: long runs of equal keys inside a 16-bit bucket
+        k = rng.integers(np.iinfo(np.int64).min, np.iinfo(np.int64).max, 50, dtype=np.int64)[rng.integers(0, 50, n)]
+    elif kind == "i64_heavy":     # one heavy hitter + wide tail
+        k = rng.integers(np.iinfo(np.int64).min, np.iinfo(np.int64).max, n, dtype=np.int64)
+        k[rng.random(n) < 0.6] = 123456789
+    elif kind == "i64_lowbits":   # top 40 bits from a small set, low 24 bits random: ties on the 24-bit window
+        k = (rng.integers(0, 300, n, dtype=np.int64) << 40) | rng.integers(0, 1 << 24, n, dtype=np.int64)
+    elif kind == "i64_window_ties":  # equal down to bit 8, differing only in the lowest byte
+        k = (rng.integers(0, 1 << 30, max(n // 6, 1), dtype=np.int64)[rng.integers(0, max(n // 6, 1), n)] << 8) | rng.integers(0, 256, n, dtype=np.int64)
+    else:
+        k = _keys(kind, n, rng)
+    want = orc.stable_argsort(k, descending)
+    t = torch.from_numpy(k).to(cuda_device)
+    perm, codes, skeys = ops.argsort(t, descending, want_codes=True, want_keys=True)
+    np.testing.assert_array_equal(_u32(perm), want.astype(np.uint32))
+    np.testing.assert_array_equal(codes.cpu().numpy().view(np.uint64), orc.encode_keys(k, descending)[want])
+    if k.dtype.kind in "iu":
+        np.testing.assert_array_equal(skeys.cpu().numpy(), k[want])
+
+
+def test_argsort_hybrid_default_threshold_large(cuda_device):
+    """Above the default threshold (2^22 rows) spread keys take HYBRID; check against numpy."""
+    rng = np.random.default_rng(7)
+    n = 6_000_000
+    for k in (rng.integers(np.iinfo(np.int64).min, np.iinfo(np.int64).max, n, dtype=np.int64), rng.standard_normal(n),
+              rng.permutation(n).astype(np.int64)):
+        perm, _, _ = ops.argsort(torch.from_numpy(k).to(cuda_device), False)
+        np.testing.assert_array_equal(_u32(perm), np.argsort(k, kind="stable").astype(np.uint32))
+
+
 def test_argsort_uint64_and_uint16(cuda_device):
     rng = np.random.default_rng(5)
     n = 200_000
