@@ -35,7 +35,15 @@ ROWS_PER_GPU = 100_000_000
 PAYLOAD_BYTES = 64
 ROW_BYTES = 8 + PAYLOAD_BYTES
 CPU_SAMPLE_ROWS = 100_000_000         # the CPU arm sorts the full single-GPU workload (a few seconds on 16+ cores)
-PASS_BYTES_PER_ROW = (20 + 6 * 24 + 24) / 8.0   # algorithmic bytes of one radix pass per row
+# Algorithmic bytes per row of one launch of each timed kernel class, and the DRAM traffic
+# per row ncu measured for it (profiles/, dram__bytes_read.sum + dram__bytes_write.sum; None = not captured).
+KERNELS = {
+    0: ("onesweep_pass_kernel", 22.0, 25.6),         # HYBRID: pass A reads 8 writes 12, pass B reads 12 writes 12
+    1: ("gather_rows_kernel<uint4>", 4 + 2 * PAYLOAD_BYTES, None),   # index + read row + write row
+    2: ("finish_runs_kernel", 12 + 4 + 8, None),      # read pair, write row index + decoded key
+    3: ("joint_hist_kernel", 8.0, None),              # read key column
+    6: ("hist_kernel", 8.0, None),
+}
 
 
 def parse():
@@ -208,8 +216,12 @@ def run_ours(args):
     launches = int(lib.b200x_launch_count() - launches0)
     import ctypes
 
-    pass_ms, pass_cnt = ctypes.c_double(0), ctypes.c_int(0)
-    lib.b200x_profile_read(ctypes.byref(pass_ms), ctypes.byref(pass_cnt))
+    kernel_times = {}
+    for kid, (kname, _, _) in KERNELS.items():
+        k_ms, k_cnt = ctypes.c_double(0), ctypes.c_int(0)
+        lib.b200x_profile_read(kid, ctypes.byref(k_ms), ctypes.byref(k_cnt))
+        if k_cnt.value:
+            kernel_times[kid] = (k_ms.value, k_cnt.value)
     lib.b200x_profile_enable(0)
     # correctness of what was timed: global order + multiset checksum (cheap, outside the timed region)
     host_first = out.get_internal_block_refs()[0]["id"][:4096].cpu().numpy()
@@ -233,31 +245,48 @@ def run_ours(args):
         o_keys = torch.empty(int(n * (1.0 if world == 1 else 1.6)), dtype=torch.int64).pin_memory()
         o_pay = torch.empty((o_keys.numel(), PAYLOAD_BYTES), dtype=torch.uint8).pin_memory()
 
+        copy_stream = torch.cuda.Stream(device=dev)
+        keep = []  # results whose D2H is still in flight
+
         def step_e2e():
+            # H2D of this step's inputs + sort on the main stream; D2H of the result on a second stream, so
+            # that the D2H of step i overlaps the H2D of step i+1 (PCIe is full duplex). Every step still
+            # copies all of its inputs in and all of its result out.
             k = h_keys.to(dev, non_blocking=True)
             p = h_pay.to(dev, non_blocking=True)
             res = rd.from_torch_columns({"id": k, "payload": p}, override_num_blocks=nblocks).sort("id")
+            done = torch.cuda.Event()
+            done.record()
+            copy_stream.wait_event(done)
             lo = 0
-            for b in res.get_internal_block_refs():
-                m = b.num_rows
-                if m:
-                    o_keys[lo:lo + m].copy_(b["id"], non_blocking=True)
-                    o_pay[lo:lo + m].copy_(b["payload"], non_blocking=True)
-                    lo += m
+            with torch.cuda.stream(copy_stream):
+                for b in res.get_internal_block_refs():
+                    m = b.num_rows
+                    if m:
+                        o_keys[lo:lo + m].copy_(b["id"], non_blocking=True)
+                        o_pay[lo:lo + m].copy_(b["payload"], non_blocking=True)
+                        lo += m
+            keep.append(res)
+            if len(keep) > 2:
+                keep.pop(0)
             return lo
 
         e_steps = max(1, min(args.steps, 5))
         for _ in range(min(args.warmup, 2)):
             step_e2e()
+        copy_stream.synchronize()
         barrier()
         f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         f0.record()
         got = 0
         for _ in range(e_steps):
             got = step_e2e()
-        f1.record()
+        with torch.cuda.stream(copy_stream):
+            f1.record()
+        copy_stream.synchronize()
         barrier()
         e_ms = f0.elapsed_time(f1)
+        keep.clear()
         assert (np.diff(o_keys[:min(got, 100_000)].numpy()) >= 0).all()
         d2h = got * ROW_BYTES
         if world > 1:
@@ -282,16 +311,23 @@ def run_ours(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
-    roof = None
-    if pass_cnt.value:
-        per_launch_ms = pass_ms.value / pass_cnt.value
-        rows_per_launch = n if world == 1 else None
-        if world == 1:
-            ach = rows_per_launch * PASS_BYTES_PER_ROW / (per_launch_ms / 1e3) / 1e9
-            roof = {"bound": "hbm", "kernel": "onesweep_pass_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
-                    "frac": ach / peak, "traffic": None, "peak_source": peak_src, "launches_timed": pass_cnt.value,
-                    "ms_per_launch": per_launch_ms, "share_of_step": pass_ms.value / ms_total,
-                    "algorithmic_bytes_per_launch": rows_per_launch * PASS_BYTES_PER_ROW}
+    roof, breakdown = None, {}
+    for kid, (k_ms, k_cnt) in kernel_times.items():
+        kname, alg_b, traffic_b = KERNELS[kid]
+        per_launch_ms = k_ms / k_cnt
+        ach = n * alg_b / (per_launch_ms / 1e3) / 1e9
+        breakdown[kname] = {"launches": k_cnt, "ms_per_launch": per_launch_ms, "share_of_step": k_ms / ms_total,
+                            "achieved_gbs": ach, "frac": ach / peak}
+    if kernel_times and world == 1:
+        kid = max(kernel_times, key=lambda k: kernel_times[k][0])   # dominant = largest share of the timed region
+        kname, alg_b, traffic_b = KERNELS[kid]
+        k_ms, k_cnt = kernel_times[kid]
+        per_launch_ms = k_ms / k_cnt
+        ach = n * alg_b / (per_launch_ms / 1e3) / 1e9
+        roof = {"bound": "hbm", "kernel": kname, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                "traffic": (n * traffic_b if traffic_b else None), "peak_source": peak_src, "launches_timed": k_cnt,
+                "ms_per_launch": per_launch_ms, "share_of_step": k_ms / ms_total,
+                "algorithmic_bytes_per_launch": n * alg_b}
     op_gbs = total_rows * 2 * ROW_BYTES / (ms_step / 1e3) / 1e9
     line = {
         "metric": "Dataset.sort rows/s", "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps,
@@ -304,7 +340,7 @@ def run_ours(args):
         "roofline": roof,
         "roofline_op": {"bound": "hbm", "achieved": op_gbs / world, "peak": peak, "unit": "GB/s", "frac": op_gbs / world / peak,
                         "algorithmic_bytes": "2 x row_bytes x rows (SURVEY.md 8d)", "peak_source": peak_src},
-        "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+        "kernels": breakdown, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
     }
     if not args.no_cpu_baseline and world == 1:
         import pyarrow

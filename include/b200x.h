@@ -51,13 +51,14 @@ const char* b200x_last_error_string(void);
 int b200x_device_count(void);
 
 /* Measurement hooks (bench.py): number of kernels the library has launched in this process,
- * and CUDA-event timing of the dominant kernel (the radix pass) on its launching stream:
- * enable(1) starts recording one event pair per pass launch on the calling thread; read()
- * synchronises the recorded events and returns their summed duration and their count
- * (passes skipped on the device, which return in microseconds, are not counted). */
+ * and CUDA-event timing of the main kernels on their launching stream: enable(1) clears the
+ * record and starts recording one event pair per launch on the calling thread; read(kernel, ...)
+ * synchronises and returns the summed duration and the launch count of one kernel class
+ * (0 radix pass, 1 row gather, 2 run finisher, 3 joint histogram, 6 LSD histogram). Launches that
+ * return at once because the device chose the other sort path are not counted. */
 unsigned long long b200x_launch_count(void);
 int b200x_profile_enable(int on);
-int b200x_profile_read(double* total_ms, int* launches);
+int b200x_profile_read(int kernel, double* total_ms, int* launches);
 
 /* Stable argsort of one key column. Radix sort on order-preserving 64-bit codes with 8-bit digits
  * and decoupled look-back ("onesweep" passes). The device inspects the keys and picks
@@ -132,6 +133,12 @@ int b200x_search_sorted_codes(const uint64_t* codes, size_t n, const uint64_t* b
  * on the fly), so cutting a sorted block at boundaries needs no code array. */
 int b200x_search_sorted_keys(const void* keys_sorted, int key_type, int descending, size_t n,
                              const uint64_t* bound_codes, int num_bounds, int upper, uint64_t* out_index, void* stream);
+
+/* out_index[i] (i < parts-1) = the cut that splits a SORTED key column into `parts` near-equal blocks
+ * without separating equal keys: the first row whose key equals the key at row floor((i+1)*n/parts).
+ * (The reference's rule that equal keys land in one partition: _internal/util.py:756-758.) */
+int b200x_even_cuts(const void* keys_sorted, int key_type, int descending, size_t n, int parts, uint64_t* out_index,
+                    void* stream);
 
 /* Seeded pseudo-random bijection pi on [0, n) (6 alternating Feistel rounds over the 2^ceil(log2 n)
  * domain, cycle-walked into range). Deterministic in (seed, n).

@@ -31,7 +31,7 @@ SIGNATURES = {
     "b200x_device_count": (c_int, []),
     "b200x_launch_count": (ctypes.c_ulonglong, []),
     "b200x_profile_enable": (c_int, [c_int]),
-    "b200x_profile_read": (c_int, [POINTER(c_double), POINTER(c_int)]),
+    "b200x_profile_read": (c_int, [c_int, POINTER(c_double), POINTER(c_int)]),
     "b200x_radix_argsort": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_int,
                                     c_int, c_void_p, _size_p, c_void_p]),
     "b200x_set_tuning": (c_int, [c_int, ctypes.c_longlong]),
@@ -43,6 +43,7 @@ SIGNATURES = {
     "b200x_encode_keys": (c_int, [c_void_p, c_int, c_int, c_size_t, c_void_p, c_void_p]),
     "b200x_search_sorted_codes": (c_int, [c_void_p, c_size_t, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "b200x_search_sorted_keys": (c_int, [c_void_p, c_int, c_int, c_size_t, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "b200x_even_cuts": (c_int, [c_void_p, c_int, c_int, c_size_t, c_int, c_void_p, c_void_p]),
     "b200x_permute_rows": (c_int, [c_void_p, c_size_t, c_size_t, c_uint64, c_int, c_void_p, c_void_p]),
     "b200x_perm_indices": (c_int, [c_size_t, c_uint64, c_int, c_size_t, c_size_t, c_void_p, c_void_p]),
     "b200x_perm_indices_host": (c_int, [c_size_t, c_uint64, c_int, c_size_t, c_size_t, c_void_p]),

@@ -46,10 +46,11 @@ void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 static thread_local bool t_prof = false;
 static thread_local std::vector<std::pair<cudaEvent_t, cudaEvent_t>> t_events;
+static thread_local std::vector<int> t_kernel;
 static thread_local size_t t_used = 0;
 static thread_local bool t_open = false;
 
-void prof_begin(cudaStream_t s) {
+void prof_begin(cudaStream_t s, int kernel) {
   if (!t_prof) return;
   if (t_used == t_events.size()) {
     cudaEvent_t a, b;
@@ -58,7 +59,9 @@ void prof_begin(cudaStream_t s) {
       return;
     }
     t_events.emplace_back(a, b);
+    t_kernel.push_back(0);
   }
+  t_kernel[t_used] = kernel;
   t_open = cudaEventRecord(t_events[t_used].first, s) == cudaSuccess;
 }
 
@@ -81,22 +84,22 @@ int b200x_profile_enable(int on) {
   return B200X_OK;
 }
 
-int b200x_profile_read(double* total_ms, int* launches) {
+int b200x_profile_read(int kernel, double* total_ms, int* launches) {
   double tot = 0.0;
   int cnt = 0;
   for (size_t i = 0; i < b200x::t_used; ++i) {
+    if (b200x::t_kernel[i] != kernel) continue;
     float ms = 0.f;
     B200X_CUDA(cudaEventSynchronize(b200x::t_events[i].second));
     B200X_CUDA(cudaEventElapsedTime(&ms, b200x::t_events[i].first, b200x::t_events[i].second));
-    // a pass whose digit is constant returns at once (a few microseconds): not a real launch of the pass
-    if (ms > 0.02f) {
+    // a kernel that returns at once because the device chose the other path (a few microseconds) is not counted
+    if (ms > 0.1f) {
       tot += ms;
       ++cnt;
     }
   }
   if (total_ms) *total_ms = tot;
   if (launches) *launches = cnt;
-  b200x::t_used = 0;
   return B200X_OK;
 }
 

@@ -43,9 +43,11 @@ int sm_count();
 // Every kernel launch of the library is counted (b200x_launch_count).
 void count_launch();
 
-// Optional CUDA-event bracket around the launches of the dominant kernel (the radix pass),
-// recorded on the launching stream while b200x_profile_enable(1) is in effect.
-void prof_begin(cudaStream_t s);
+// Optional CUDA-event bracket around kernel launches, recorded on the launching stream while
+// b200x_profile_enable(1) is in effect (bench.py's live per-kernel timing).
+enum ProfKernel : int { PROF_PASS = 0, PROF_GATHER = 1, PROF_FINISH = 2, PROF_JOINT = 3, PROF_PERMUTE = 4, PROF_SEGRED = 5,
+                        PROF_HIST = 6, PROF_COUNT = 7 };
+void prof_begin(cudaStream_t s, int kernel);
 void prof_end(cudaStream_t s);
 
 // ---- key encoding: raw column value -> order-preserving 64-bit code -------

@@ -133,6 +133,7 @@ extern "C" int b200x_gather_rows(const void* src, size_t row_bytes, const uint32
     return B200X_OK;
   }
   const uint32_t g = grid_for(total, 256, 16);
+  prof_begin(stream, PROF_GATHER);
   switch (v) {
     case 16: gather_rows_kernel<uint4><<<g, 256, 0, stream>>>((const uint4*)src, idx, (uint4*)dst, n, vpr); break;
     case 8: gather_rows_kernel<uint64_t><<<g, 256, 0, stream>>>((const uint64_t*)src, idx, (uint64_t*)dst, n, vpr); break;
@@ -140,6 +141,7 @@ extern "C" int b200x_gather_rows(const void* src, size_t row_bytes, const uint32
     case 2: gather_rows_kernel<uint16_t><<<g, 256, 0, stream>>>((const uint16_t*)src, idx, (uint16_t*)dst, n, vpr); break;
     default: gather_rows_kernel<uint8_t><<<g, 256, 0, stream>>>((const uint8_t*)src, idx, (uint8_t*)dst, n, vpr); break;
   }
+  prof_end(stream);
   B200X_LAUNCH_CHECK("gather_rows_kernel");
   return B200X_OK;
 }

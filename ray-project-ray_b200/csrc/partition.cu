@@ -55,9 +55,39 @@ search_keys_kernel(const void* __restrict__ keys, int kt, int desc, uint64_t n, 
   out[b] = lo;
 }
 
+// Cut positions that split a sorted key column into `parts` near-equal blocks without splitting a
+// run of equal keys: cut i = first row whose key equals the key at row floor(i*n/parts).
+__global__ void __launch_bounds__(128)
+even_cuts_kernel(const void* __restrict__ keys, int kt, int desc, uint64_t n, int parts, uint64_t* __restrict__ out) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= parts - 1) return;
+  uint64_t pos = (uint64_t)(b + 1) * n / (uint64_t)parts;
+  if (pos >= n) pos = n - 1;
+  const uint64_t x = load_encode(keys, pos, kt, desc != 0);
+  uint64_t lo = 0, hi = pos;  // the answer is <= pos
+  while (lo < hi) {
+    const uint64_t mid = lo + ((hi - lo) >> 1);
+    if (load_encode(keys, mid, kt, desc != 0) < x) lo = mid + 1; else hi = mid;
+  }
+  out[b] = lo;
+}
+
 }  // namespace b200x
 
 using namespace b200x;
+
+extern "C" int b200x_even_cuts(const void* keys_sorted, int key_type, int descending, size_t n, int parts,
+                               uint64_t* out_index, void* stream_) {
+  if (parts <= 1) return B200X_OK;
+  if (n == 0 || keys_sorted == nullptr || out_index == nullptr || key_type < 0 || key_type >= KEY_TYPE_COUNT) {
+    set_error("b200x_even_cuts: bad arguments");
+    return B200X_ERR_ARG;
+  }
+  even_cuts_kernel<<<(parts - 1 + 127) / 128, 128, 0, (cudaStream_t)stream_>>>(keys_sorted, key_type, descending, n, parts,
+                                                                              out_index);
+  B200X_LAUNCH_CHECK("even_cuts_kernel");
+  return B200X_OK;
+}
 
 extern "C" int b200x_search_sorted_keys(const void* keys_sorted, int key_type, int descending, size_t n,
                                         const uint64_t* bound_codes, int num_bounds, int upper, uint64_t* out_index,

@@ -1012,7 +1012,9 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
     B200X_LAUNCH_CHECK("analyze_kernel");
     hybrid_plan0_kernel<<<1, 1, 0, stream>>>(ctl, (uint32_t)n, g_hybrid_min_rows);
     B200X_LAUNCH_CHECK("hybrid_plan0_kernel");
+    prof_begin(stream, PROF_JOINT);
     joint_hist_kernel<<<blocks, 512, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, ctl, joint);
+    prof_end(stream);
     B200X_LAUNCH_CHECK("joint_hist_kernel");
     hybrid_plan1_kernel<<<1, 1024, 0, stream>>>(ctl, joint, run_start, hbase, hplan, (uint32_t)n);
     B200X_LAUNCH_CHECK("hybrid_plan1_kernel");
@@ -1021,7 +1023,7 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
       a.pass = p;
       a.gbase = hbase + p * RADIX;
       a.lookback = hlookback + (size_t)p * L.tiles * RADIX;
-      prof_begin(stream);
+      prof_begin(stream, PROF_PASS);
       onesweep_pass_kernel<PASS_THREADS, PASS_IPT, PASS_MINB><<<L.tiles, PASS_THREADS, pass_smem, stream>>>(a);
       prof_end(stream);
       B200X_LAUNCH_CHECK("onesweep_pass_kernel");
@@ -1036,9 +1038,13 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
     f.ctl = ctl;
     f.kt = key_type;
     f.desc = descending;
+    prof_begin(stream, PROF_FINISH);
     finish_runs_kernel<FIN_SMALL_THREADS><<<JOINT_BINS, FIN_SMALL_THREADS, fin_small_smem, stream>>>(f);
+    prof_end(stream);
     B200X_LAUNCH_CHECK("finish_runs_kernel");
+    prof_begin(stream, PROF_FINISH);
     finish_runs_kernel<FIN_BIG_THREADS><<<JOINT_BINS, FIN_BIG_THREADS, fin_big_smem, stream>>>(f);
+    prof_end(stream);
     B200X_LAUNCH_CHECK("finish_runs_kernel");
   }
 
@@ -1048,8 +1054,10 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
     uint32_t blocks = (uint32_t)((n + chunk - 1) / chunk);
     const uint32_t cap = (uint32_t)sms * 4;
     if (blocks > cap) blocks = cap;
+    prof_begin(stream, PROF_HIST);
     hist_kernel<<<blocks, HIST_THREADS, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, npass, ghist,
                                                      ctl);
+    prof_end(stream);
     B200X_LAUNCH_CHECK("hist_kernel");
   }
   plan_kernel<<<1, RADIX, 0, stream>>>(ghist, plan, (uint32_t)n, npass);
@@ -1059,7 +1067,7 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
     a.pass = p;
     a.gbase = ghist + p * RADIX;
     a.lookback = lookback + (size_t)p * L.tiles * RADIX;
-    prof_begin(stream);
+    prof_begin(stream, PROF_PASS);
     onesweep_pass_kernel<PASS_THREADS, PASS_IPT, PASS_MINB><<<L.tiles, PASS_THREADS, pass_smem, stream>>>(a);
     prof_end(stream);
     B200X_LAUNCH_CHECK("onesweep_pass_kernel");

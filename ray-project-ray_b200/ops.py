@@ -164,6 +164,17 @@ def search_sorted_keys(keys_sorted: torch.Tensor, descending: bool, bound_codes:
     return out
 
 
+def even_cuts(keys_sorted: torch.Tensor, descending: bool, parts: int) -> torch.Tensor:
+    """parts-1 tie-respecting cut positions of a sorted key column (int64 tensor on the device)."""
+    dev = _require_cuda(keys_sorted)
+    out = torch.empty(max(parts - 1, 0), dtype=torch.int64, device=dev)
+    if parts > 1 and keys_sorted.numel() > 0:
+        with torch.cuda.device(dev):
+            _lib.call("b200x_even_cuts", keys_sorted.data_ptr(), key_type_of(keys_sorted), int(descending),
+                      keys_sorted.numel(), parts, out.data_ptr(), _stream(dev))
+    return out
+
+
 def permute_rows(col: torch.Tensor, seed: int, inverse: bool = False) -> torch.Tensor:
     """out[j] = col[pi_seed(j)] — seeded permutation fused with the row gather."""
     dev = _require_cuda(col)

@@ -383,11 +383,7 @@ def _cut_sorted_evenly(table: DeviceBlock, key: str, descending: bool, parts: in
     n = table.num_rows
     if parts <= 1 or n == 0:
         return [table] + [DeviceBlock.empty(table.device) for _ in range(parts - 1)]
-    col = _contig(table.columns[key])
-    nominal = [min(n - 1, (i * n) // parts) for i in range(1, parts)]
-    idx = torch.tensor(nominal, dtype=torch.int32, device=table.device)
-    at = ops.encode_keys(ops.gather(col, idx), descending)       # R-1 boundary codes
-    cuts = ops.search_sorted_keys(col, descending, at, upper=False).cpu().tolist()
+    cuts = ops.even_cuts(_contig(table.columns[key]), descending, parts).cpu().tolist()
     return _cut(table, [int(c) for c in cuts])
 
 
