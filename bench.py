@@ -14,7 +14,7 @@ row shape of BASELINE.json configs[1], the largest configuration that fits one G
 Printed JSON (rank 0, one line): see DESIGN.md §Measurement for every key.
   value      rows/s, inputs resident in HBM, CUDA events around K steps, max over ranks
   e2e        same metric through the public API from pinned HOST buffers (H2D + sort + D2H per step)
-  roofline   the dominant kernel (one radix pass), CUDA events on its launching stream
+  roofline   the kernel with the largest share of the step, CUDA events on its launching stream (all kernels: `kernels`)
   cpu_baseline  the reference's CPU path (port calling the same pyarrow kernels) on the host cores
 """
 from __future__ import annotations

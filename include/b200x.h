@@ -140,6 +140,33 @@ int b200x_search_sorted_keys(const void* keys_sorted, int key_type, int descendi
 int b200x_even_cuts(const void* keys_sorted, int key_type, int descending, size_t n, int parts, uint64_t* out_index,
                     void* stream);
 
+/* Fused partition-gather + exchange over NVLink peer memory (one GPU per process, all on one box).
+ * Rows are visited in send order i = 0..n-1 (row perm[i] of src, or row i if perm is NULL); rows
+ * [send_off_host[d], send_off_host[d+1]) go to rank d and are stored directly into that rank's receive buffer
+ * peer_base_host[d] (a peer-mapped device address, e.g. from torch symmetric memory), starting at row
+ * peer_row_off_host[d] of it. The *_host arrays are HOST arrays of length world (+1 for send_off). No send
+ * buffer exists; the caller orders ranks with a barrier before and after. world <= 16.
+ * Replaces the object-store hop between map and reduce tasks
+ * (_internal/planner/exchange/pull_based_shuffle_task_scheduler.py:86-124,
+ *  push_based_shuffle_task_scheduler.py:514-568). */
+int b200x_scatter_rows_to_peers(const void* src, size_t row_bytes, const uint32_t* perm, size_t n,
+                                const unsigned long long* send_off_host, void* const* peer_base_host,
+                                const unsigned long long* peer_row_off_host, int world, void* stream);
+
+/* Partition-first variant of the same exchange (no local sort before the transfer).
+ * b200x_partition_targets: target_out[r] = owner << 28 | slot for every row r, where owner = number of
+ * splitter codes <= code(keys[r]) (so equal keys share an owner, _internal/util.py:756-758) and slot = the row's
+ * position among the rows this rank sends to that owner, in row order (a stable split: ties keep their
+ * order through the exchange). counts_out[16] (device) = rows per owner. n < 2^28, <= 15 splitters.
+ * b200x_scatter_rows_by_target: row r of src (read in order) is stored at row peer_row_off_host[owner] + slot
+ * of peer_base_host[owner]. */
+int b200x_partition_targets(const void* keys, int key_type, int descending, size_t n, const uint64_t* splitter_codes,
+                            int num_splitters, uint32_t* target_out, unsigned long long* counts_out, void* temp,
+                            size_t* temp_bytes, void* stream);
+int b200x_scatter_rows_by_target(const void* src, size_t row_bytes, const uint32_t* target, size_t n,
+                                 void* const* peer_base_host, const unsigned long long* peer_row_off_host, int world,
+                                 void* stream);
+
 /* Seeded pseudo-random bijection pi on [0, n) (6 alternating Feistel rounds over the 2^ceil(log2 n)
  * domain, cycle-walked into range). Deterministic in (seed, n).
  *   inverse != 0 evaluates pi^-1.

@@ -44,6 +44,12 @@ SIGNATURES = {
     "b200x_search_sorted_codes": (c_int, [c_void_p, c_size_t, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "b200x_search_sorted_keys": (c_int, [c_void_p, c_int, c_int, c_size_t, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "b200x_even_cuts": (c_int, [c_void_p, c_int, c_int, c_size_t, c_int, c_void_p, c_void_p]),
+    "b200x_scatter_rows_to_peers": (c_int, [c_void_p, c_size_t, c_void_p, c_size_t, POINTER(ctypes.c_ulonglong),
+                                            POINTER(c_void_p), POINTER(ctypes.c_ulonglong), c_int, c_void_p]),
+    "b200x_partition_targets": (c_int, [c_void_p, c_int, c_int, c_size_t, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
+                                        _size_p, c_void_p]),
+    "b200x_scatter_rows_by_target": (c_int, [c_void_p, c_size_t, c_void_p, c_size_t, POINTER(c_void_p),
+                                             POINTER(ctypes.c_ulonglong), c_int, c_void_p]),
     "b200x_permute_rows": (c_int, [c_void_p, c_size_t, c_size_t, c_uint64, c_int, c_void_p, c_void_p]),
     "b200x_perm_indices": (c_int, [c_size_t, c_uint64, c_int, c_size_t, c_size_t, c_void_p, c_void_p]),
     "b200x_perm_indices_host": (c_int, [c_size_t, c_uint64, c_int, c_size_t, c_size_t, c_void_p]),

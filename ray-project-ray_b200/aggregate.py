@@ -147,10 +147,36 @@ def _groups_of_sorted(block: DeviceBlock, key: Optional[str]):
 
 
 def _reduce_partials(kind: str, agg: AggregateFn, name: str, src: DeviceBlock, starts, ng, G: int, perm, n: int,
-                     raw: bool) -> Dict[str, torch.Tensor]:
+                     raw: bool, cache: Optional[dict] = None) -> Dict[str, torch.Tensor]:
     """Accumulator columns of one aggregation for G groups.
-    raw=True: `src` holds data rows (combine). raw=False: `src` holds partial rows (merge)."""
+    raw=True: `src` holds data rows (combine). raw=False: `src` holds partial rows (merge).
+    `cache` (raw only) shares one pass over a value column between aggregations of that column:
+    the first request computes sum, min and max of the column in a single launch."""
     out: Dict[str, torch.Tensor] = {}
+    if raw and cache is not None:
+        def counts():
+            if "count" not in cache:
+                cache["count"] = ops.group_counts(starts, ng, G, n)
+            return cache["count"]
+
+        def smm(on):
+            if ("smm", on) not in cache:
+                cache[("smm", on)] = ops.segmented_reduce(starts, ng, G, perm, _value_column(src, on), n, True, True, True)
+            return cache[("smm", on)]
+
+        if kind == "count":
+            return {name: counts()}
+        if kind in ("sum", "min", "max"):
+            return {name: smm(agg._key_fn)[("sum", "min", "max").index(kind)]}
+        if kind == "mean":
+            return {name: smm(agg._key_fn)[0], name + SEP + "count": counts()}
+        if kind == "std":
+            s_, cnt = smm(agg._key_fn)[0], counts()
+            if ("mean", agg._key_fn) not in cache:
+                cache[("mean", agg._key_fn)] = ops.finalize_groups(s_, cnt, 0)
+            m2 = ops.segmented_reduce(starts, ng, G, perm, _value_column(src, agg._key_fn), n,
+                                      center=cache[("mean", agg._key_fn)])[0]
+            return {name: m2, name + SEP + "sum": s_, name + SEP + "count": cnt}
     if kind == "count":
         if raw:
             out[name] = ops.group_counts(starts, ng, G, n)
@@ -230,9 +256,10 @@ def aggregate_sorted(block: DeviceBlock, key: Optional[str], aggs: Sequence[Aggr
     if key is not None:
         first_rows = ops.gather(perm, starts[:G].contiguous()) if perm is not None else starts[:G].contiguous()
         cols[key] = ops.gather(_contig(block.columns[key]), first_rows)
+    cache: dict = {}
     for agg, name in zip(aggs, names):
         kind = _device_kind(agg)
-        acc = _reduce_partials(kind, agg, name, block, starts, ng, G, perm, n, raw=True)
+        acc = _reduce_partials(kind, agg, name, block, starts, ng, G, perm, n, raw=True, cache=cache)
         if finalize:
             cols[name] = _finalize(kind, agg, name, acc)
         else:

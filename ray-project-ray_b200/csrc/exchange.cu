@@ -1,0 +1,379 @@
+// Fused partition-gather + exchange over NVLink peer memory.
+//
+// The reference moves every map output to its reducer through the object store (plasma shared
+// memory inside a node, chunked gRPC between nodes:
+// python/ray/data/_internal/planner/exchange/pull_based_shuffle_task_scheduler.py:86-124,
+// push_based_shuffle_task_scheduler.py:514-568). On one NVSwitch box the same hop is ONE kernel:
+// each rank walks its rows in destination order (perm = the local sort order, so the rows for
+// rank d are one contiguous run), reads the row from its own HBM and stores it straight into rank
+// d's receive buffer through the peer mapping, at the offset reserved for this sender. There is
+// no send buffer and no separate copy: the gather that would have filled the send buffer is the
+// transfer. Consecutive threads write consecutive remote addresses (rows for one peer are
+// contiguous on both sides), so NVLink sees full-width stores.
+//
+// Ordering across ranks (all writers done before anybody reads) is the caller's job: a barrier on
+// the symmetric-memory signal pads before and after this kernel (distributed.py).
+#include "common.cuh"
+#include "../../include/b200x.h"
+
+namespace b200x {
+
+constexpr int MAX_PEERS = 16;
+
+struct PeerPlan {
+  unsigned char* base[MAX_PEERS];          // receive buffer of rank d (peer-mapped address)
+  unsigned long long row_off[MAX_PEERS];   // first row in rank d's buffer reserved for this sender
+  unsigned long long send_off[MAX_PEERS + 1];  // rows [send_off[d], send_off[d+1]) of the send order go to rank d
+  int world;
+};
+
+template <typename V>
+__global__ void __launch_bounds__(256)
+scatter_rows_to_peers_kernel(const V* __restrict__ src, const uint32_t* __restrict__ perm, const PeerPlan p, uint64_t n,
+                             uint32_t vec_per_row) {
+  constexpr int U = 8;  // stores in flight per thread: NVLink latency is ~2 us, keep the links busy from few blocks
+  const uint64_t total = n * vec_per_row;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t t0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; t0 < total; t0 += U * stride) {
+    V v[U];
+    V* dst[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const uint64_t t = t0 + u * stride;
+      dst[u] = nullptr;
+      if (t < total) {
+        const uint64_t i = t / vec_per_row;
+        const uint32_t c = (uint32_t)(t - i * vec_per_row);
+        int d = 0;
+#pragma unroll
+        for (int k = 1; k < MAX_PEERS; ++k)
+          if (k < p.world && i >= p.send_off[k]) d = k;
+        const uint64_t srow = perm ? (uint64_t)perm[i] : i;
+        v[u] = src[srow * vec_per_row + c];
+        dst[u] = reinterpret_cast<V*>(p.base[d]) + (p.row_off[d] + (i - p.send_off[d])) * vec_per_row + c;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (dst[u]) *dst[u] = v[u];
+  }
+}
+
+}  // namespace b200x
+
+using namespace b200x;
+
+extern "C" int b200x_scatter_rows_to_peers(const void* src, size_t row_bytes, const uint32_t* perm, size_t n,
+                                           const unsigned long long* send_off_host, void* const* peer_base_host,
+                                           const unsigned long long* peer_row_off_host, int world, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (world <= 0 || world > MAX_PEERS) {
+    set_error("b200x_scatter_rows_to_peers: world=%d out of range [1, %d]", world, MAX_PEERS);
+    return B200X_ERR_ARG;
+  }
+  if (n == 0 || row_bytes == 0) return B200X_OK;
+  if (src == nullptr || send_off_host == nullptr || peer_base_host == nullptr || peer_row_off_host == nullptr) {
+    set_error("b200x_scatter_rows_to_peers: NULL pointer");
+    return B200X_ERR_ARG;
+  }
+  PeerPlan p;
+  p.world = world;
+  uintptr_t al = (uintptr_t)src | (uintptr_t)row_bytes;
+  for (int d = 0; d < MAX_PEERS; ++d) {
+    p.base[d] = d < world ? (unsigned char*)peer_base_host[d] : nullptr;
+    p.row_off[d] = d < world ? peer_row_off_host[d] : 0;
+    if (d < world) al |= (uintptr_t)p.base[d];
+  }
+  for (int d = 0; d <= MAX_PEERS; ++d) p.send_off[d] = d <= world ? send_off_host[d] : send_off_host[world];
+  if (p.send_off[0] != 0 || p.send_off[world] != n) {
+    set_error("b200x_scatter_rows_to_peers: send offsets must start at 0 and end at n");
+    return B200X_ERR_ARG;
+  }
+  int v = 16;
+  while (v > 1 && (al & (uintptr_t)(v - 1)) != 0) v >>= 1;
+  const uint32_t vpr = (uint32_t)(row_bytes / v);
+  const uint64_t total = (uint64_t)n * vpr;
+  // A quarter of the resident-block slots: the transfer is link-bound, and the sort of the already
+  // received key column runs next to it on another stream.
+  uint64_t blocks = (total / 8 + 255) / 256;
+  const uint64_t cap = (uint64_t)sm_count() * 4;
+  if (blocks > cap) blocks = cap;
+  if (blocks == 0) blocks = 1;
+  const uint32_t g = (uint32_t)blocks;
+  prof_begin(stream, PROF_GATHER);
+  switch (v) {
+    case 16: scatter_rows_to_peers_kernel<uint4><<<g, 256, 0, stream>>>((const uint4*)src, perm, p, n, vpr); break;
+    case 8: scatter_rows_to_peers_kernel<uint64_t><<<g, 256, 0, stream>>>((const uint64_t*)src, perm, p, n, vpr); break;
+    case 4: scatter_rows_to_peers_kernel<uint32_t><<<g, 256, 0, stream>>>((const uint32_t*)src, perm, p, n, vpr); break;
+    case 2: scatter_rows_to_peers_kernel<uint16_t><<<g, 256, 0, stream>>>((const uint16_t*)src, perm, p, n, vpr); break;
+    default: scatter_rows_to_peers_kernel<uint8_t><<<g, 256, 0, stream>>>((const uint8_t*)src, perm, p, n, vpr); break;
+  }
+  prof_end(stream);
+  B200X_LAUNCH_CHECK("scatter_rows_to_peers_kernel");
+  return B200X_OK;
+}
+
+// ---------------------------------------------------------------------------
+// Partition-first exchange: where does every row go, without sorting first
+// ---------------------------------------------------------------------------
+// b200x_partition_targets: for every row, the rank that owns its key range (found by comparing the
+// key's code with the W-1 splitter codes) and the row's slot among the rows this rank sends there,
+// in row order (a stable W-way split, so ties keep their order through the exchange).
+// b200x_scatter_rows_by_target: stores row r (read sequentially, full-width) at that slot of the
+// owner's receive buffer. Together they replace "sort locally, gather into send order, copy":
+// the payload is read once, in order, and lands remotely in one kernel.
+namespace b200x {
+
+constexpr int PT_THREADS = 256;
+constexpr int PT_IPT = 8;
+constexpr int PT_TILE = PT_THREADS * PT_IPT;
+constexpr int PT_WARPS = PT_THREADS / 32;
+constexpr uint32_t SLOT_BITS = 28;  // target = owner << 28 | slot
+
+__device__ __forceinline__ uint32_t owner_of(uint64_t code, const uint64_t* __restrict__ s_split, int nsplit) {
+  uint32_t d = 0;
+  for (int k = 0; k < nsplit; ++k) d += (s_split[k] <= code) ? 1u : 0u;  // rows equal to a splitter go right
+  return d;
+}
+
+// lanes of the warp with the same 4-bit value
+__device__ __forceinline__ unsigned match4(uint32_t d) {
+  unsigned peers = 0xffffffffu;
+#pragma unroll
+  for (int b = 0; b < 4; ++b) {
+    const bool bit = (d >> b) & 1u;
+    const unsigned m = __ballot_sync(0xffffffffu, bit);
+    peers &= bit ? m : ~m;
+  }
+  return peers;
+}
+
+// pass 1: rows per owner in each tile
+__global__ void __launch_bounds__(PT_THREADS)
+pt_count_kernel(const void* __restrict__ keys, int kt, int desc, uint64_t n, const uint64_t* __restrict__ split, int nsplit,
+                uint32_t* __restrict__ tile_counts /*[tiles][MAX_PEERS]*/) {
+  __shared__ uint64_t s_split[MAX_PEERS];
+  __shared__ uint32_t s_cnt[MAX_PEERS];
+  if (threadIdx.x < MAX_PEERS) {
+    s_split[threadIdx.x] = threadIdx.x < (unsigned)nsplit ? split[threadIdx.x] : ~0ull;
+    s_cnt[threadIdx.x] = 0;
+  }
+  __syncthreads();
+  const uint64_t base = (uint64_t)blockIdx.x * PT_TILE;
+  const unsigned lane = threadIdx.x & 31;
+#pragma unroll
+  for (int j = 0; j < PT_IPT; ++j) {
+    const uint64_t r = base + (uint64_t)j * PT_THREADS + threadIdx.x;
+    const uint32_t d = r < n ? owner_of(load_encode(keys, r, kt, desc != 0), s_split, nsplit) : (uint32_t)(MAX_PEERS - 1);
+    const unsigned act = __ballot_sync(0xffffffffu, r < n);
+    const unsigned peers = match4(d) & act;
+    if (r < n && (int)lane == __ffs(peers) - 1) atomicAdd(&s_cnt[d], (uint32_t)__popc(peers));
+  }
+  __syncthreads();
+  if (threadIdx.x < MAX_PEERS) tile_counts[(size_t)blockIdx.x * MAX_PEERS + threadIdx.x] = s_cnt[threadIdx.x];
+}
+
+// pass 2 (one block per owner): exclusive scan of that owner's tile counts over tiles; total -> counts_out
+__global__ void __launch_bounds__(1024)
+pt_scan_kernel(uint32_t* __restrict__ tile_counts, uint32_t tiles, unsigned long long* __restrict__ counts_out) {
+  __shared__ uint32_t s_warp[32];
+  const int d = blockIdx.x;
+  const unsigned lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const uint32_t per = (tiles + 1023) / 1024;
+  const uint32_t lo = min(tiles, threadIdx.x * per), hi = min(tiles, lo + per);
+  uint32_t sum = 0;
+#pragma unroll 4
+  for (uint32_t t = lo; t < hi; ++t) sum += tile_counts[(size_t)t * MAX_PEERS + d];
+  uint32_t x = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= (unsigned)o) x += y;
+  }
+  if (lane == 31) s_warp[w] = x;
+  __syncthreads();
+  uint32_t off = 0;
+  for (unsigned k = 0; k < w; ++k) off += s_warp[k];
+  uint32_t run = off + x - sum;
+  for (uint32_t t = lo; t < hi; ++t) {
+    const uint32_t c = tile_counts[(size_t)t * MAX_PEERS + d];
+    tile_counts[(size_t)t * MAX_PEERS + d] = run;
+    run += c;
+  }
+  if (threadIdx.x == 1023) counts_out[d] = off + x;
+}
+
+// pass 3: every row's target = owner << 28 | slot. Warp-striped rows (item j of lane l of warp w =
+// tile row w*256 + j*32 + l), so that ranks follow row order.
+__global__ void __launch_bounds__(PT_THREADS)
+pt_target_kernel(const void* __restrict__ keys, int kt, int desc, uint64_t n, const uint64_t* __restrict__ split, int nsplit,
+                 const uint32_t* __restrict__ tile_base /*[tiles][MAX_PEERS]*/, uint32_t* __restrict__ target) {
+  __shared__ uint64_t s_split[MAX_PEERS];
+  __shared__ uint32_t s_wcnt[PT_WARPS][MAX_PEERS];
+  if (threadIdx.x < MAX_PEERS) s_split[threadIdx.x] = threadIdx.x < (unsigned)nsplit ? split[threadIdx.x] : ~0ull;
+  if (threadIdx.x < PT_WARPS * MAX_PEERS) (&s_wcnt[0][0])[threadIdx.x] = 0;
+  __syncthreads();
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned lt = lanemask_lt();
+  const uint64_t base = (uint64_t)blockIdx.x * PT_TILE + (uint64_t)warp * 32 * PT_IPT + lane;
+  uint32_t dest[PT_IPT], rank[PT_IPT];
+#pragma unroll
+  for (int j = 0; j < PT_IPT; ++j) {
+    const uint64_t r = base + (uint64_t)j * 32;
+    const bool valid = r < n;
+    dest[j] = valid ? owner_of(load_encode(keys, r, kt, desc != 0), s_split, nsplit) : (uint32_t)(MAX_PEERS - 1);
+    const unsigned act = __ballot_sync(0xffffffffu, valid);
+    const unsigned peers = match4(dest[j]) & act;
+    uint32_t old = 0;
+    const int leader = __ffs(peers) - 1;
+    if (valid && (int)lane == leader) {
+      old = s_wcnt[warp][dest[j]];
+      s_wcnt[warp][dest[j]] = old + __popc(peers);
+    }
+    old = __shfl_sync(0xffffffffu, old, leader < 0 ? 0 : leader);
+    rank[j] = old + __popc(peers & lt);
+    __syncwarp();
+  }
+  __syncthreads();
+  // exclusive scan over warps per owner, plus the tile's base slot
+  if (threadIdx.x < MAX_PEERS) {
+    uint32_t run = tile_base[(size_t)blockIdx.x * MAX_PEERS + threadIdx.x];
+    for (int w = 0; w < PT_WARPS; ++w) {
+      const uint32_t c = s_wcnt[w][threadIdx.x];
+      s_wcnt[w][threadIdx.x] = run;
+      run += c;
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < PT_IPT; ++j) {
+    const uint64_t r = base + (uint64_t)j * 32;
+    if (r < n) target[r] = (dest[j] << SLOT_BITS) | (s_wcnt[warp][dest[j]] + rank[j]);
+  }
+}
+
+template <typename V>
+__global__ void __launch_bounds__(256)
+scatter_rows_by_target_kernel(const V* __restrict__ src, const uint32_t* __restrict__ target, const PeerPlan p, uint64_t n,
+                              uint32_t vec_per_row) {
+  constexpr int U = 4;
+  const uint64_t total = n * vec_per_row;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t t0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; t0 < total; t0 += U * stride) {
+    V v[U];
+    V* dst[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const uint64_t t = t0 + u * stride;
+      dst[u] = nullptr;
+      if (t < total) {
+        const uint64_t r = t / vec_per_row;
+        const uint32_t c = (uint32_t)(t - r * vec_per_row);
+        const uint32_t tg = target[r];
+        const uint32_t d = tg >> SLOT_BITS;
+        const uint64_t slot = tg & ((1u << SLOT_BITS) - 1u);
+        v[u] = src[t];
+        dst[u] = reinterpret_cast<V*>(p.base[d]) + (p.row_off[d] + slot) * vec_per_row + c;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (dst[u]) *dst[u] = v[u];
+  }
+}
+
+}  // namespace b200x
+
+extern "C" int b200x_partition_targets(const void* keys, int key_type, int descending, size_t n,
+                                       const uint64_t* splitter_codes, int num_splitters, uint32_t* target_out,
+                                       unsigned long long* counts_out, void* temp, size_t* temp_bytes, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (temp_bytes == nullptr) {
+    set_error("b200x_partition_targets: temp_bytes is NULL");
+    return B200X_ERR_ARG;
+  }
+  if (num_splitters < 0 || num_splitters >= MAX_PEERS || key_type < 0 || key_type >= KEY_TYPE_COUNT) {
+    set_error("b200x_partition_targets: bad key_type or more than %d splitters", MAX_PEERS - 1);
+    return B200X_ERR_ARG;
+  }
+  if (n >= ((size_t)1 << SLOT_BITS)) {
+    set_error("b200x_partition_targets: n=%zu exceeds 2^28-1 rows per call", n);
+    return B200X_ERR_TOO_LARGE;
+  }
+  const uint32_t tiles = (uint32_t)((n + PT_TILE - 1) / PT_TILE);
+  const size_t need = align_up((size_t)(tiles + 1) * MAX_PEERS * sizeof(uint32_t), 256);
+  if (temp == nullptr) {
+    *temp_bytes = need;
+    return B200X_OK;
+  }
+  if (*temp_bytes < need) {
+    set_error("b200x_partition_targets: temp buffer %zu < required %zu bytes", *temp_bytes, need);
+    return B200X_ERR_TEMP;
+  }
+  if (counts_out == nullptr) {
+    set_error("b200x_partition_targets: counts_out is NULL");
+    return B200X_ERR_ARG;
+  }
+  if (n == 0) {
+    B200X_CUDA(cudaMemsetAsync(counts_out, 0, sizeof(unsigned long long) * MAX_PEERS, stream));
+    return B200X_OK;
+  }
+  if (keys == nullptr || target_out == nullptr || (num_splitters > 0 && splitter_codes == nullptr)) {
+    set_error("b200x_partition_targets: NULL pointer");
+    return B200X_ERR_ARG;
+  }
+  uint32_t* tile_counts = (uint32_t*)temp;
+  pt_count_kernel<<<tiles, PT_THREADS, 0, stream>>>(keys, key_type, descending, n, splitter_codes, num_splitters,
+                                                    tile_counts);
+  B200X_LAUNCH_CHECK("pt_count_kernel");
+  pt_scan_kernel<<<MAX_PEERS, 1024, 0, stream>>>(tile_counts, tiles, counts_out);
+  B200X_LAUNCH_CHECK("pt_scan_kernel");
+  pt_target_kernel<<<tiles, PT_THREADS, 0, stream>>>(keys, key_type, descending, n, splitter_codes, num_splitters,
+                                                     tile_counts, target_out);
+  B200X_LAUNCH_CHECK("pt_target_kernel");
+  return B200X_OK;
+}
+
+extern "C" int b200x_scatter_rows_by_target(const void* src, size_t row_bytes, const uint32_t* target, size_t n,
+                                            void* const* peer_base_host, const unsigned long long* peer_row_off_host,
+                                            int world, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (world <= 0 || world > MAX_PEERS) {
+    set_error("b200x_scatter_rows_by_target: world=%d out of range [1, %d]", world, MAX_PEERS);
+    return B200X_ERR_ARG;
+  }
+  if (n == 0 || row_bytes == 0) return B200X_OK;
+  if (src == nullptr || target == nullptr || peer_base_host == nullptr || peer_row_off_host == nullptr) {
+    set_error("b200x_scatter_rows_by_target: NULL pointer");
+    return B200X_ERR_ARG;
+  }
+  PeerPlan p;
+  p.world = world;
+  uintptr_t al = (uintptr_t)src | (uintptr_t)row_bytes;
+  for (int d = 0; d < MAX_PEERS; ++d) {
+    p.base[d] = d < world ? (unsigned char*)peer_base_host[d] : nullptr;
+    p.row_off[d] = d < world ? peer_row_off_host[d] : 0;
+    if (d < world) al |= (uintptr_t)p.base[d];
+  }
+  for (int d = 0; d <= MAX_PEERS; ++d) p.send_off[d] = 0;
+  int v = 16;
+  while (v > 1 && (al & (uintptr_t)(v - 1)) != 0) v >>= 1;
+  const uint32_t vpr = (uint32_t)(row_bytes / v);
+  const uint64_t total = (uint64_t)n * vpr;
+  uint64_t blocks = (total / 4 + 255) / 256;
+  const uint64_t cap = (uint64_t)sm_count() * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks == 0) blocks = 1;
+  const uint32_t g = (uint32_t)blocks;
+  prof_begin(stream, PROF_GATHER);
+  switch (v) {
+    case 16: scatter_rows_by_target_kernel<uint4><<<g, 256, 0, stream>>>((const uint4*)src, target, p, n, vpr); break;
+    case 8: scatter_rows_by_target_kernel<uint64_t><<<g, 256, 0, stream>>>((const uint64_t*)src, target, p, n, vpr); break;
+    case 4: scatter_rows_by_target_kernel<uint32_t><<<g, 256, 0, stream>>>((const uint32_t*)src, target, p, n, vpr); break;
+    case 2: scatter_rows_by_target_kernel<uint16_t><<<g, 256, 0, stream>>>((const uint16_t*)src, target, p, n, vpr); break;
+    default: scatter_rows_by_target_kernel<uint8_t><<<g, 256, 0, stream>>>((const uint8_t*)src, target, p, n, vpr); break;
+  }
+  prof_end(stream);
+  B200X_LAUNCH_CHECK("scatter_rows_by_target_kernel");
+  return B200X_OK;
+}

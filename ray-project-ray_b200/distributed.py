@@ -34,6 +34,15 @@ from .block import DeviceBlock, DeviceBlockAccessor, _contig
 from .sort_task_spec import SortKey
 
 
+def _transport() -> str:
+    """"auto" (peer-memory stores when every rank can map every other, else NCCL), "p2p" or "nccl"."""
+    from .context import DataContext
+
+    import os
+
+    return str(DataContext.get_current().get_config("exchange_transport", os.environ.get("B200X_EXCHANGE_TRANSPORT", "auto")))
+
+
 def is_distributed() -> bool:
     return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
 
@@ -90,6 +99,118 @@ def exchange_block(block: DeviceBlock, send_counts: Sequence[int], group=None) -
     return DeviceBlock(cols, num_rows=int(sum(recv_counts)), device=block.device)
 
 
+# ------------------------------------------------------- peer-memory (NVLink P2P) transport
+_symm_cache: Dict[Tuple[int, int], Tuple[torch.Tensor, object]] = {}
+_p2p_ok: Dict[str, Optional[bool]] = {"state": None}
+_ROW_ROUND = 1 << 20
+
+
+def _symm_buffer(slot: int, nbytes: int, dev: torch.device, group):
+    """A receive buffer that every rank can store into: torch symmetric memory (cuMem + peer mapping),
+    allocated once per (slot, size) and reused by later exchanges."""
+    import torch.distributed._symmetric_memory as symm
+
+    key = (slot, nbytes)
+    if key not in _symm_cache:
+        t = symm.empty(nbytes, dtype=torch.uint8, device=dev)
+        h = symm.rendezvous(t, group if group is not None else dist.group.WORLD)
+        _symm_cache[key] = (t, h)
+    return _symm_cache[key]
+
+
+def p2p_available(dev: torch.device, group=None) -> bool:
+    """True when every rank can map every other rank's memory (one NVSwitch box). Decided once,
+    collectively: if any rank fails to set up symmetric memory, all ranks use the NCCL transport."""
+    if _p2p_ok["state"] is None:
+        ok = 1
+        try:
+            _symm_buffer(-1, 4096, dev, group)
+        except Exception as e:  # noqa: BLE001  (driver / container without peer mapping support)
+            import logging
+
+            logging.getLogger("ray.data").warning("peer-memory exchange unavailable (%s); using NCCL all-to-all", e)
+            ok = 0
+        flag = torch.tensor([ok], dtype=torch.int32, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        _p2p_ok["state"] = bool(flag.item())
+    return bool(_p2p_ok["state"])
+
+
+class P2PExchange:
+    """Fused gather + exchange over peer memory. `columns` maps name -> (source column, row order or
+    None). Row i of the send order (row order[i] of the source) goes to the rank that owns it, written
+    by ONE kernel per column directly into that rank's receive buffer over NVLink (csrc/exchange.cu);
+    no send buffer, no NCCL copy. Columns can be sent in groups (`send`) separated by `fence`, so
+    that work on the first group (sorting the received keys) overlaps the transfer of the rest.
+    `view` returns tensors that ALIAS the receive buffers: consume them before the next exchange."""
+
+    def __init__(self, columns: Dict[str, Tuple[torch.Tensor, Optional[torch.Tensor]]], n: int,
+                 send_counts: Sequence[int], dev: torch.device, group=None, target: Optional[torch.Tensor] = None):
+        import ctypes
+
+        self.columns, self.n, self.dev, self.group = columns, n, dev, group
+        self.target = target  # per-row owner<<28|slot (partition-first mode): rows are read in order
+        self.world, rank = dist.get_world_size(group), dist.get_rank(group)
+        C = all_gather_counts(send_counts, group, dev)
+        self.n_recv = int(C[:, rank].sum())
+        cap_rows = int(C.sum(axis=0).max())
+        cap_rows = max(_ROW_ROUND, (cap_rows + _ROW_ROUND - 1) // _ROW_ROUND * _ROW_ROUND)
+        send_off = np.concatenate(([0], np.cumsum(np.asarray(send_counts, dtype=np.int64))))
+        row_off = C[:rank, :].sum(axis=0)  # rows that lower ranks put before mine, per destination
+        self._so = (ctypes.c_ulonglong * (self.world + 1))(*[int(x) for x in send_off])
+        self._ro = (ctypes.c_ulonglong * self.world)(*[int(x) for x in row_off])
+        self._bufs = {}
+        for slot, (name, (col, _)) in enumerate(columns.items()):
+            row_bytes = col.element_size()
+            for d in col.shape[1:]:
+                row_bytes *= int(d)
+            self._bufs[name] = (_symm_buffer(slot, cap_rows * row_bytes, dev, group), row_bytes)
+        self._handle = next(iter(self._bufs.values()))[0][1]
+
+    def fence(self) -> None:
+        """Device-side barrier over all ranks on the current stream (symmetric-memory signal pads): before
+        the first send = everyone is done reading the previous contents; after a send = all stores landed."""
+        self._handle.barrier(channel=0)
+
+    def send(self, names: Sequence[str]) -> None:
+        import ctypes
+
+        from . import _lib
+
+        with torch.cuda.device(self.dev):
+            st = torch.cuda.current_stream(self.dev).cuda_stream
+            for name in names:
+                col, order = self.columns[name]
+                (buf, h), row_bytes = self._bufs[name]
+                bases = (ctypes.c_void_p * self.world)(*[int(p) for p in h.buffer_ptrs])
+                if self.target is not None:
+                    _lib.call("b200x_scatter_rows_by_target", _contig(col).data_ptr(), row_bytes, self.target.data_ptr(),
+                              self.n, bases, self._ro, self.world, st)
+                    continue
+                _lib.call("b200x_scatter_rows_to_peers", _contig(col).data_ptr(), row_bytes,
+                          None if order is None else order.data_ptr(), self.n, self._so, bases, self._ro, self.world, st)
+
+    def view(self, names: Sequence[str]) -> Dict[str, torch.Tensor]:
+        out = {}
+        for name in names:
+            col, _ = self.columns[name]
+            (buf, _), row_bytes = self._bufs[name]
+            flat = buf[: self.n_recv * row_bytes]
+            shape = (self.n_recv,) + tuple(col.shape[1:])
+            out[name] = flat.view(col.dtype).reshape(shape) if col.dtype != torch.uint8 else flat.reshape(shape)
+        return out
+
+
+_side_streams: Dict[int, torch.cuda.Stream] = {}
+
+
+def _side_stream(dev: torch.device) -> torch.cuda.Stream:
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    if idx not in _side_streams:
+        _side_streams[idx] = torch.cuda.Stream(device=dev)
+    return _side_streams[idx]
+
+
 # ------------------------------------------------------------------------ device steps
 def _sample_codes(codes_sorted: torch.Tensor, num_samples: int) -> torch.Tensor:
     n = codes_sorted.numel()
@@ -108,12 +229,22 @@ def dist_sort(local: DeviceBlock, sort_key: SortKey, group=None, samples_per_ran
     n = local.num_rows
     first = sort_key.get_columns()[0]
     desc = sort_key.get_descending()
-    if n > 0:
+    use_p2p = dev.type == "cuda" and _transport() != "nccl" and p2p_available(dev, group)
+    if use_p2p and _transport() != "p2p_sort_first":
+        return _p2p_partition_sort(local, sort_key, n, dev, group, samples_per_rank)
+    perm = skeys = None
+    if n > 0 and use_p2p:
+        perm, codes, skeys = acc._argsort(sort_key, want_codes=True)   # no local gather: rows leave in sort order
+        sorted_local = None
+        samples = _sample_codes(codes, samples_per_rank)
+    elif n > 0:
         sorted_local, codes = acc.sort(sort_key, want_codes=True)
         samples = _sample_codes(codes, samples_per_rank)
     else:
         sorted_local, codes = local, torch.empty(0, dtype=torch.int64, device=dev)
         samples = codes
+        if use_p2p:
+            perm = torch.empty(0, dtype=torch.int32, device=dev)
     # splitters: every rank gathers every rank's samples and computes the same quantiles
     padded = torch.full((samples_per_rank + 1,), -1, dtype=torch.int64, device=dev)
     padded[0] = samples.numel()
@@ -129,11 +260,123 @@ def dist_sort(local: DeviceBlock, sort_key: SortKey, group=None, samples_per_ran
     else:
         cuts = [0] * (world - 1) if n == 0 else [n] * (world - 1)
     send_counts = split_counts_from_cuts(cuts, n)
+    if use_p2p:
+        return _p2p_sort_exchange(local, sort_key, perm, skeys, n, send_counts, dev, group)
     received = exchange_block(sorted_local, send_counts, group)
     if received.num_rows == 0:
         return received
     out, _ = DeviceBlockAccessor(received).sort(sort_key)
     return out
+
+
+def _gather_samples(sample_codes: torch.Tensor, samples_per_rank: int, world: int, dev, group) -> np.ndarray:
+    """all_gather every rank's (possibly fewer than samples_per_rank) sample codes -> one uint64 host array."""
+    padded = torch.full((samples_per_rank + 1,), -1, dtype=torch.int64, device=dev)
+    padded[0] = sample_codes.numel()
+    padded[1:1 + sample_codes.numel()] = sample_codes
+    gathered = [torch.empty_like(padded) for _ in range(world)]
+    dist.all_gather(gathered, padded, group=group)
+    host = torch.stack(gathered).cpu().numpy()
+    return np.concatenate([row[1:1 + int(row[0])].view(np.uint64) for row in host])
+
+
+def _p2p_partition_sort(local: DeviceBlock, sort_key: SortKey, n: int, dev, group, samples_per_rank: int) -> DeviceBlock:
+    """Partition-first distributed sort over peer memory:
+      sample raw keys -> identical splitters on every rank -> per-row (owner, slot) targets (stable split,
+      no sort) -> key columns stored into the owners' receive buffers -> while the payload columns follow
+      over NVLink, the received keys are sorted on a second stream -> one gather of the received payload.
+    The payload is read once sequentially on the sender and gathered once on the receiver."""
+    world = dist.get_world_size(group)
+    key_cols = sort_key.get_columns()
+    first, desc = key_cols[0], sort_key.get_descending()
+    keycol = _contig(local.columns[first])
+    if n > 0:
+        m = min(samples_per_rank, n)
+        pos = ((np.arange(m, dtype=np.float64) + 0.5) * (n / m)).astype(np.int64).astype(np.int32)
+        sample_codes = ops.encode_keys(ops.gather(keycol, torch.from_numpy(pos).to(dev)), desc)
+    else:
+        sample_codes = torch.empty(0, dtype=torch.int64, device=dev)
+    splitters = choose_splitters(_gather_samples(sample_codes, samples_per_rank, world, dev, group), world)
+    if splitters.size != world - 1:   # no rank has any row
+        splitters = np.full(world - 1, np.iinfo(np.uint64).max, dtype=np.uint64)
+    sp = torch.from_numpy(splitters.view(np.int64)).to(dev)
+    target, counts = ops.partition_targets(keycol, desc, sp)
+    send_counts = [int(c) for c in counts.cpu().tolist()[:world]]
+    cols = {name: (_contig(local.columns[name]), None)
+            for name in key_cols + [c for c in local.column_names if c not in key_cols]}
+    rest = [c for c in cols if c not in key_cols]
+    ex = P2PExchange(cols, n, send_counts, dev, group, target=target)
+    main = torch.cuda.current_stream(dev)
+    ex.fence()
+    ex.send(key_cols)
+    ex.fence()
+    if ex.n_recv == 0:
+        ex.send(rest)
+        ex.fence()
+        return DeviceBlock({k: v.clone() for k, v in ex.view(list(cols)).items()}, num_rows=0, device=dev)
+    keys_block = DeviceBlock(ex.view(key_cols), num_rows=ex.n_recv, device=dev)
+    side = _side_stream(dev)
+    landed, sorted_ev = torch.cuda.Event(), torch.cuda.Event()
+    landed.record(main)
+    with torch.cuda.stream(side):
+        side.wait_event(landed)
+        perm2, _, skeys2 = DeviceBlockAccessor(keys_block)._argsort(sort_key, False)
+        sorted_ev.record(side)
+    ex.send(rest)
+    ex.fence()
+    main.wait_event(sorted_ev)
+    perm2.record_stream(main)
+    if skeys2 is not None:
+        skeys2.record_stream(main)
+    recv = ex.view(list(cols))
+    names = [c for c in local.column_names if not (skeys2 is not None and c == first)]
+    outs = ops.gather_columns([recv[c] for c in names], perm2)
+    out_cols = dict(zip(names, outs))
+    if skeys2 is not None:
+        out_cols[first] = skeys2
+    return DeviceBlock({c: out_cols[c] for c in local.column_names}, num_rows=ex.n_recv, device=dev)
+
+
+def _p2p_sort_exchange(local: DeviceBlock, sort_key: SortKey, perm, skeys, n: int, send_counts, dev, group) -> DeviceBlock:
+    """Exchange in two groups: key columns first; while the payload columns are in flight over
+    NVLink, the received keys are already being sorted on a second stream."""
+    key_cols = sort_key.get_columns()
+    first = key_cols[0]
+    cols = {}
+    for name in key_cols + [c for c in local.column_names if c not in key_cols]:
+        col = _contig(local.columns[name])
+        cols[name] = (skeys, None) if (skeys is not None and name == first) else (col, perm)
+    rest = [c for c in cols if c not in key_cols]
+    ex = P2PExchange(cols, n, send_counts, dev, group)
+    main = torch.cuda.current_stream(dev)
+    ex.fence()
+    ex.send(key_cols)
+    ex.fence()
+    if ex.n_recv == 0:
+        ex.send(rest)
+        ex.fence()
+        return DeviceBlock({k: v.clone() for k, v in ex.view(list(cols)).items()}, num_rows=0, device=dev)
+    keys_block = DeviceBlock(ex.view(key_cols), num_rows=ex.n_recv, device=dev)
+    side = _side_stream(dev)
+    landed, sorted_ev = torch.cuda.Event(), torch.cuda.Event()
+    landed.record(main)
+    with torch.cuda.stream(side):
+        side.wait_event(landed)
+        perm2, _, skeys2 = DeviceBlockAccessor(keys_block)._argsort(sort_key, False)
+        sorted_ev.record(side)
+    ex.send(rest)
+    ex.fence()
+    main.wait_event(sorted_ev)
+    perm2.record_stream(main)
+    if skeys2 is not None:
+        skeys2.record_stream(main)
+    recv = ex.view(list(cols))
+    names = [c for c in local.column_names if not (skeys2 is not None and c == first)]
+    outs = ops.gather_columns([recv[c] for c in names], perm2)
+    out_cols = dict(zip(names, outs))
+    if skeys2 is not None:
+        out_cols[first] = skeys2
+    return DeviceBlock({c: out_cols[c] for c in local.column_names}, num_rows=ex.n_recv, device=dev)
 
 
 def dist_random_shuffle(local: DeviceBlock, seed: Optional[int], group=None) -> DeviceBlock:

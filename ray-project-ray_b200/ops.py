@@ -175,6 +175,38 @@ def even_cuts(keys_sorted: torch.Tensor, descending: bool, parts: int) -> torch.
     return out
 
 
+def partition_targets(keys: torch.Tensor, descending: bool, splitter_codes: torch.Tensor):
+    """(target int32[n] = owner << 28 | slot, counts int64[16]) of a stable split of the rows by key range."""
+    dev = _require_cuda(keys, splitter_codes if splitter_codes.numel() else None)
+    n = keys.numel()
+    target = torch.empty(n, dtype=torch.int32, device=dev)
+    counts = torch.zeros(16, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        st = _stream(dev)
+        args = (keys.data_ptr(), key_type_of(keys), int(descending), n,
+                splitter_codes.data_ptr() if splitter_codes.numel() else None, splitter_codes.numel(),
+                target.data_ptr(), counts.data_ptr())
+        need = _lib.query_temp("b200x_partition_targets", *args, stream=st)
+        temp = _temp(need, dev)
+        nb = ctypes.c_size_t(temp.numel())
+        _lib.call("b200x_partition_targets", *args, temp.data_ptr(), ctypes.byref(nb), st)
+    return target, counts
+
+
+def scatter_rows_by_target(col: torch.Tensor, target: torch.Tensor, bases: Sequence[int], row_offsets: Sequence[int]) -> None:
+    """Row r of `col` -> row row_offsets[owner] + slot of the buffer at device address bases[owner]."""
+    dev = _require_cuda(col, target)
+    n = col.shape[0]
+    row_bytes = col.element_size()
+    for s in col.shape[1:]:
+        row_bytes *= s
+    w = len(bases)
+    b = (ctypes.c_void_p * w)(*[int(x) for x in bases])
+    ro = (ctypes.c_ulonglong * w)(*[int(x) for x in row_offsets])
+    with torch.cuda.device(dev):
+        _lib.call("b200x_scatter_rows_by_target", col.data_ptr(), row_bytes, target.data_ptr(), n, b, ro, w, _stream(dev))
+
+
 def permute_rows(col: torch.Tensor, seed: int, inverse: bool = False) -> torch.Tensor:
     """out[j] = col[pi_seed(j)] — seeded permutation fused with the row gather."""
     dev = _require_cuda(col)

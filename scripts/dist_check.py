@@ -26,9 +26,13 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", rank))
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from ray_project_ray_b200.context import DataContext
+    from ray_project_ray_b200 import distributed as D
+
     n = 200_000 + 1000 * rank
     rng = np.random.default_rng(100 + rank)
-    for kind in ("i64_ties", "f64"):
+    for transport, kind in (("nccl", "i64_ties"), ("nccl", "f64"), ("auto", "i64_ties"), ("auto", "f64"), ("p2p_sort_first", "i64_ties"), ("p2p_sort_first", "f64"), ("auto", "i64_ties")):
+        DataContext.get_current().set_config("exchange_transport", transport)
         if kind == "i64_ties":
             key = rng.integers(0, 5000, n, dtype=np.int64)
         else:
@@ -52,7 +56,7 @@ def main():
                 np.testing.assert_array_equal(np.concatenate([p[0] for p in parts]), allr[order])
                 np.testing.assert_array_equal(np.concatenate([p[1] for p in parts]), allp[order])
                 sizes = [len(p[0]) for p in parts]
-                print(f"sort {kind} desc={desc}: OK, rows per rank {sizes}", flush=True)
+                print(f"sort {kind} desc={desc} transport={transport} (p2p={D._p2p_ok['state']}): OK, rows per rank {sizes}", flush=True)
     # groupby
     gk = rng.integers(0, 3000, n, dtype=np.int64)
     gv = rng.integers(-2**31, 2**31, n, dtype=np.int64)

@@ -246,3 +246,32 @@ def test_search_sorted_codes(cuda_device):
     np.testing.assert_array_equal(lo, np.searchsorted(keys, bounds, side="left"))
     np.testing.assert_array_equal(hi, np.searchsorted(keys, bounds, side="right"))
     np.testing.assert_array_equal(ops.encode_keys(torch.from_numpy(keys).to(cuda_device)).cpu().numpy().view(np.uint64), codes)
+
+
+@pytest.mark.parametrize("n,world", [(1, 2), (1000, 2), (2048, 4), (2049, 8), (300_000, 8), (1_000_003, 16)])
+@pytest.mark.parametrize("descending", [False, True])
+def test_partition_targets_and_scatter(cuda_device, n, world, descending):
+    """Stable W-way split by key range + scatter into per-owner buffers (the 'peers' are local buffers here)."""
+    rng = np.random.default_rng(n + world)
+    keys = rng.integers(-1000, 1000, n, dtype=np.int64)
+    codes = orc.encode_keys(keys, descending)
+    split = np.sort(orc.encode_keys(rng.integers(-900, 900, world - 1, dtype=np.int64), descending))
+    owner = np.searchsorted(split, codes, side="right")          # number of splitters <= code
+    t_keys = torch.from_numpy(keys).to(cuda_device)
+    t_split = torch.from_numpy(split.view(np.int64)).to(cuda_device)
+    target, counts = ops.partition_targets(t_keys, descending, t_split)
+    tg = target.cpu().numpy().view(np.uint32)
+    np.testing.assert_array_equal(tg >> 28, owner)
+    want_counts = np.bincount(owner, minlength=16)
+    np.testing.assert_array_equal(counts.cpu().numpy(), want_counts)
+    for d in range(world):  # slots follow row order inside every owner
+        np.testing.assert_array_equal(tg[owner == d] & ((1 << 28) - 1), np.arange(want_counts[d]))
+    pay = rng.integers(0, 256, (n, 24), dtype=np.uint8)
+    t_pay = torch.from_numpy(pay).to(cuda_device)
+    bufs = [torch.zeros((int(want_counts[d]) + 3, 24), dtype=torch.uint8, device=cuda_device) for d in range(world)]
+    ops.scatter_rows_by_target(t_pay, target, [b.data_ptr() for b in bufs], [3] * world)
+    kbufs = [torch.zeros(int(want_counts[d]) + 3, dtype=torch.int64, device=cuda_device) for d in range(world)]
+    ops.scatter_rows_by_target(t_keys, target, [b.data_ptr() for b in kbufs], [3] * world)
+    for d in range(world):
+        np.testing.assert_array_equal(bufs[d].cpu().numpy()[3:], pay[owner == d])
+        np.testing.assert_array_equal(kbufs[d].cpu().numpy()[3:], keys[owner == d])
