@@ -38,10 +38,10 @@ CPU_SAMPLE_ROWS = 100_000_000         # the CPU arm sorts the full single-GPU wo
 # Algorithmic bytes per row of one launch of each timed kernel class, and the DRAM traffic
 # per row ncu measured for it (profiles/, dram__bytes_read.sum + dram__bytes_write.sum; None = not captured).
 KERNELS = {
-    0: ("onesweep_pass_kernel", 22.0, 25.6),         # HYBRID: pass A reads 8 writes 12, pass B reads 12 writes 12
-    1: ("gather_rows_kernel<uint4>", 4 + 2 * PAYLOAD_BYTES, None),   # index + read row + write row
-    2: ("finish_runs_kernel", 12 + 4 + 8, None),      # read pair, write row index + decoded key
-    3: ("joint_hist_kernel", 8.0, None),              # read key column
+    0: ("onesweep_pass_kernel", 22.0, 26.0),         # HYBRID: pass A reads 8 writes 12, pass B reads 12 writes 12
+    1: ("gather_rows_kernel<uint4>", 4 + 2 * PAYLOAD_BYTES, 197.6),  # index + read row + write row (64 B rows cost 128 B of DRAM reads)
+    2: ("finish_runs_kernel", 12 + 4 + 8, 23.5),      # read pair, write row index + decoded key
+    3: ("joint_hist_kernel", 8.0, 8.0),               # read key column
     6: ("hist_kernel", 8.0, None),
 }
 
