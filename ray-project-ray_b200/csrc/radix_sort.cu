@@ -54,8 +54,11 @@ constexpr uint32_t MODE_LSD = 0, MODE_HYBRID = 1;
 constexpr uint32_t JOINT_BINS = 1u << 16;
 
 struct SortCtl {
-  unsigned long long or_mask;    // OR of all codes
-  unsigned long long nand_mask;  // OR of all ~codes  (a bit varies iff set in both)
+  unsigned long long max_code;   // largest code
+  unsigned long long max_inv;    // largest ~code (smallest code = ~max_inv); both start at 0
+  unsigned long long base;       // smallest code: HYBRID sorts code - base, so a narrow key range anywhere
+                                 // in the 64-bit space (one rank's slice of a distributed sort, timestamps)
+                                 // still spreads over all 65536 runs
   uint32_t candidate;            // hybrid is worth checking (enough rows, > 16 varying bits)
   uint32_t mode;
   uint32_t shiftA, shiftB;       // digit positions of the two global passes (low one first)
@@ -183,6 +186,7 @@ struct PassArgs {
   const uint32_t* gbase;    // [RADIX] exclusive digit offsets of this pass
   uint32_t* lookback;       // [tiles][RADIX]
   SortPlan* plan;
+  const SortCtl* ctl;       // HYBRID passes sort code - ctl->base (NULL: plain codes)
   uint32_t n;
   int pass;
   int kt;
@@ -275,6 +279,7 @@ onesweep_pass_kernel(const PassArgs a) {
   const uint32_t wbase = (uint32_t)warp * 32 * IPT + lane;
   if (is_first) {
     const int width = key_type_bytes(a.kt);
+    const unsigned long long base = a.ctl ? a.ctl->base : 0ull;
 #pragma unroll
     for (int j = 0; j < IPT; ++j) {
       const uint32_t t = wbase + j * 32;
@@ -289,7 +294,7 @@ onesweep_pass_kernel(const PassArgs a) {
 #pragma unroll
     for (int j = 0; j < IPT; ++j) {
       const uint32_t t = wbase + j * 32;
-      key[j] = (t < n_valid) ? encode_bits(key[j], a.kt, a.desc != 0) : ~0ull;
+      key[j] = (t < n_valid) ? encode_bits(key[j], a.kt, a.desc != 0) - base : ~0ull;
       if (t >= n_valid) val[j] = 0;
     }
   } else {
@@ -452,11 +457,11 @@ no_pass_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ perm_i
 // Tunable from the host (b200x_set_tuning): fewest rows for which HYBRID is considered.
 static unsigned long long g_hybrid_min_rows = 1ull << 22;
 
-// H1: which bits vary at all. One read of the key column.
+// H1: smallest and largest code. One read of the key column.
 __global__ void __launch_bounds__(512)
 analyze_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ perm_in, int kt, int desc, uint32_t n,
                SortCtl* __restrict__ ctl) {
-  unsigned long long o = 0, na = 0;
+  unsigned long long o = 0, na = 0;  // running max of code / of ~code
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   const int width = key_type_bytes(kt);
   constexpr int U = 8;  // independent loads in flight per thread
@@ -475,30 +480,35 @@ analyze_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ perm_i
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const uint64_t e = encode_bits(c[u], kt, desc != 0);
-      o |= e;
-      na |= ~e;
+      o = max(o, (unsigned long long)e);
+      na = max(na, (unsigned long long)~e);
     }
   }
   for (; i < n; i += stride) {
     const uint64_t c = load_encode(raw, perm_in ? (size_t)perm_in[i] : (size_t)i, kt, desc != 0);
-    o |= c;
-    na |= ~c;
+    o = max(o, (unsigned long long)c);
+    na = max(na, (unsigned long long)~c);
   }
-  unsigned olo = __reduce_or_sync(0xffffffffu, (unsigned)o), ohi = __reduce_or_sync(0xffffffffu, (unsigned)(o >> 32));
-  unsigned nlo = __reduce_or_sync(0xffffffffu, (unsigned)na), nhi = __reduce_or_sync(0xffffffffu, (unsigned)(na >> 32));
+#pragma unroll
+  for (int d = 16; d >= 1; d >>= 1) {
+    o = max(o, __shfl_xor_sync(0xffffffffu, o, d));
+    na = max(na, __shfl_xor_sync(0xffffffffu, na, d));
+  }
   if ((threadIdx.x & 31) == 0) {
-    atomicOr(&ctl->or_mask, ((unsigned long long)ohi << 32) | olo);
-    atomicOr(&ctl->nand_mask, ((unsigned long long)nhi << 32) | nlo);
+    atomicMax(&ctl->max_code, o);
+    atomicMax(&ctl->max_inv, na);
   }
 }
 
-// H2: choose the two global digits = the top 16 varying bits.
+// H2: choose the two global digits = the top 16 bits of (code - smallest code).
 __global__ void hybrid_plan0_kernel(SortCtl* __restrict__ ctl, uint32_t n, unsigned long long min_rows) {
-  const unsigned long long vary = ctl->or_mask & ctl->nand_mask;
+  const unsigned long long lo = ~ctl->max_inv;
+  const unsigned long long vary = ctl->max_code - lo;  // width of the occupied code range
   ctl->mode = MODE_LSD;
   ctl->candidate = 0;
+  ctl->base = lo;
   if (vary == 0) return;
-  const int top = 64 - __clzll((long long)vary);  // number of low bits up to and including the highest varying bit
+  const int top = 64 - __clzll((long long)vary);  // bits needed for code - base
   if (top > 16 && (unsigned long long)n >= min_rows) {
     ctl->candidate = 1;
     ctl->shiftB = (uint32_t)(top - 8);
@@ -515,6 +525,7 @@ joint_hist_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ per
                   const SortCtl* __restrict__ ctl, uint32_t* __restrict__ joint) {
   if (!ctl->candidate) return;
   const uint32_t shiftA = ctl->shiftA;
+  const unsigned long long base = ctl->base;
   const int width = key_type_bytes(kt);
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   constexpr int U = 8;
@@ -532,11 +543,11 @@ joint_hist_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ per
     }
 #pragma unroll
     for (int u = 0; u < U; ++u)
-      atomicAdd(&joint[(uint32_t)(encode_bits(c[u], kt, desc != 0) >> shiftA) & (JOINT_BINS - 1)], 1u);
+      atomicAdd(&joint[(uint32_t)((encode_bits(c[u], kt, desc != 0) - base) >> shiftA) & (JOINT_BINS - 1)], 1u);
   }
   for (; i < n; i += stride) {
     const uint64_t e = load_encode(raw, perm_in ? (size_t)perm_in[i] : (size_t)i, kt, desc != 0);
-    atomicAdd(&joint[(uint32_t)(e >> shiftA) & (JOINT_BINS - 1)], 1u);
+    atomicAdd(&joint[(uint32_t)((e - base) >> shiftA) & (JOINT_BINS - 1)], 1u);
   }
 }
 
@@ -784,6 +795,7 @@ finish_runs_kernel(const FinArgs a) {
   FinSmem<THREADS>& sm = *reinterpret_cast<FinSmem<THREADS>*>(fin_raw);
   const uint32_t tid = threadIdx.x;
   const int R = (int)ctl->shiftA;  // low bits still unsorted inside the run
+  const unsigned long long base = ctl->base;
   const uint32_t nit = (m + THREADS - 1) / THREADS;
   const uint64_t* kin = a.kin + start;
   const uint32_t* vin = a.vin + start;
@@ -846,7 +858,7 @@ finish_runs_kernel(const FinArgs a) {
     const uint32_t i = tid + j * THREADS;
     if (i < m) {
       const uint32_t dst = start + (tie_repair ? fpos[j] : i);
-      const uint64_t k = sm.keys[i];
+      const uint64_t k = sm.keys[i] + base;
       a.perm_out[dst] = sm.vals[i];
       if (a.codes_out) a.codes_out[dst] = k;
       if (a.keys_out) store_decoded(a.keys_out, dst, k, a.kt, a.desc != 0);
@@ -1019,6 +1031,7 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
     hybrid_plan1_kernel<<<1, 1024, 0, stream>>>(ctl, joint, run_start, hbase, hplan, (uint32_t)n);
     B200X_LAUNCH_CHECK("hybrid_plan1_kernel");
     a.plan = hplan;
+    a.ctl = ctl;
     for (int p = 0; p < 2; ++p) {
       a.pass = p;
       a.gbase = hbase + p * RADIX;
@@ -1063,6 +1076,7 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
   plan_kernel<<<1, RADIX, 0, stream>>>(ghist, plan, (uint32_t)n, npass);
   B200X_LAUNCH_CHECK("plan_kernel");
   a.plan = plan;
+  a.ctl = nullptr;
   for (int p = 0; p < npass; ++p) {
     a.pass = p;
     a.gbase = ghist + p * RADIX;

@@ -81,7 +81,7 @@ def force_hybrid():
 
 
 @pytest.mark.parametrize("kind", ["i64_full", "i64_small", "i64_perm", "f64", "f64_ties", "i32", "f32", "i64_dups", "i64_heavy",
-                                  "i64_lowbits", "i64_window_ties"])
+                                  "i64_lowbits", "i64_window_ties", "i64_cluster", "i64_straddle"])
 @pytest.mark.parametrize("n", [2, 33, 1000, 70_000, 1_500_000])
 @pytest.mark.parametrize("descending", [False, True])
 def test_argsort_hybrid_mode_matches_oracle(cuda_device, force_hybrid, kind, n, descending):
@@ -95,6 +95,10 @@ def test_argsort_hybrid_mode_matches_oracle(cuda_device, force_hybrid, kind, n, 
         k[rng.random(n) < 0.6] = 123456789
     elif kind == "i64_lowbits":   # top 40 bits from a small set, low 24 bits random: ties on the 24-bit window
         k = (rng.integers(0, 300, n, dtype=np.int64) << 40) | rng.integers(0, 1 << 24, n, dtype=np.int64)
+    elif kind == "i64_cluster":   # narrow range far from zero (one rank's slice of a distributed sort)
+        k = np.int64(5_000_000_000_000_000_123) + rng.integers(0, 1 << 45, n, dtype=np.int64)
+    elif kind == "i64_straddle":  # range that crosses a high-bit boundary of the code space
+        k = rng.integers(-(1 << 40), 1 << 40, n, dtype=np.int64)
     elif kind == "i64_window_ties":  # equal down to bit 8, differing only in the lowest byte
         k = (rng.integers(0, 1 << 30, max(n // 6, 1), dtype=np.int64)[rng.integers(0, max(n // 6, 1), n)] << 8) | rng.integers(0, 256, n, dtype=np.int64)
     else:
