@@ -282,6 +282,78 @@ scatter_rows_by_target_kernel(const V* __restrict__ src, const uint32_t* __restr
   }
 }
 
+// Staged variant for rows up to 128 bytes: a block takes a tile of consecutive rows, reorders them in
+// shared memory by (owner, slot) - the slots of one owner inside a tile are consecutive - and then writes
+// each owner's rows as ONE contiguous run, consecutive threads storing consecutive 16-byte pieces. Remote
+// stores therefore leave the SM as full 128-byte requests instead of one 8..64-byte packet per row
+// (8 GPUs, 100 M rows: key column 3.45 ms unstaged).
+constexpr int ST_THREADS = 256;
+constexpr int ST_MAX_TILE = 1024;
+constexpr int ST_DATA_BYTES = 32 * 1024;
+
+template <typename V>
+__global__ void __launch_bounds__(ST_THREADS)
+scatter_rows_staged_kernel(const V* __restrict__ src, const uint32_t* __restrict__ target, const PeerPlan p, uint64_t n,
+                           uint32_t vec_per_row, uint32_t tile_rows) {
+  extern __shared__ __align__(16) unsigned char st_raw[];
+  V* sdata = reinterpret_cast<V*>(st_raw);                                            // [tile_rows * vec_per_row]
+  unsigned long long* sdst = reinterpret_cast<unsigned long long*>(st_raw + ST_DATA_BYTES);  // [tile_rows] destination of staged row i
+  uint16_t* slp = reinterpret_cast<uint16_t*>(sdst + ST_MAX_TILE);                     // [tile_rows] staged position of tile row
+  __shared__ uint32_t s_cnt[MAX_PEERS], s_min[MAX_PEERS], s_off[MAX_PEERS];
+  const uint64_t r0 = (uint64_t)blockIdx.x * tile_rows;
+  const uint32_t rows = (uint32_t)min((uint64_t)tile_rows, n - r0);
+  if (threadIdx.x < MAX_PEERS) {
+    s_cnt[threadIdx.x] = 0;
+    s_min[threadIdx.x] = 0xFFFFFFFFu;
+  }
+  __syncthreads();
+  constexpr int RPT = ST_MAX_TILE / ST_THREADS;
+  uint32_t tg[RPT];
+#pragma unroll
+  for (int k = 0; k < RPT; ++k) {
+    const uint32_t lr = threadIdx.x + k * ST_THREADS;
+    tg[k] = 0;
+    if (lr < rows) {
+      tg[k] = target[r0 + lr];
+      const uint32_t d = tg[k] >> SLOT_BITS, slot = tg[k] & ((1u << SLOT_BITS) - 1u);
+      atomicAdd(&s_cnt[d], 1u);
+      atomicMin(&s_min[d], slot);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t run = 0;
+    for (int d = 0; d < MAX_PEERS; ++d) {
+      s_off[d] = run;
+      run += s_cnt[d];
+    }
+  }
+  __syncthreads();
+  const size_t row_bytes = (size_t)vec_per_row * sizeof(V);
+#pragma unroll
+  for (int k = 0; k < RPT; ++k) {
+    const uint32_t lr = threadIdx.x + k * ST_THREADS;
+    if (lr < rows) {
+      const uint32_t d = tg[k] >> SLOT_BITS, slot = tg[k] & ((1u << SLOT_BITS) - 1u);
+      const uint32_t lp = s_off[d] + (slot - s_min[d]);
+      slp[lr] = (uint16_t)lp;
+      sdst[lp] = (unsigned long long)(p.base[d] + (p.row_off[d] + slot) * row_bytes);
+    }
+  }
+  __syncthreads();
+  const uint32_t chunks = rows * vec_per_row;
+  const V* tsrc = src + r0 * vec_per_row;
+  for (uint32_t t = threadIdx.x; t < chunks; t += ST_THREADS) {  // sequential, coalesced read of the tile
+    const uint32_t lr = t / vec_per_row, c = t - lr * vec_per_row;
+    sdata[(uint32_t)slp[lr] * vec_per_row + c] = tsrc[t];
+  }
+  __syncthreads();
+  for (uint32_t t = threadIdx.x; t < chunks; t += ST_THREADS) {  // owner runs leave as contiguous stores
+    const uint32_t i = t / vec_per_row, c = t - i * vec_per_row;
+    reinterpret_cast<V*>(sdst[i])[c] = sdata[t];
+  }
+}
+
 }  // namespace b200x
 
 extern "C" int b200x_partition_targets(const void* keys, int key_type, int descending, size_t n,
@@ -360,6 +432,23 @@ extern "C" int b200x_scatter_rows_by_target(const void* src, size_t row_bytes, c
   while (v > 1 && (al & (uintptr_t)(v - 1)) != 0) v >>= 1;
   const uint32_t vpr = (uint32_t)(row_bytes / v);
   const uint64_t total = (uint64_t)n * vpr;
+  if (row_bytes <= 128) {
+    uint32_t tile_rows = (uint32_t)(ST_DATA_BYTES / row_bytes) / ST_THREADS * ST_THREADS;
+    if (tile_rows > (uint32_t)ST_MAX_TILE) tile_rows = ST_MAX_TILE;
+    const size_t smem = ST_DATA_BYTES + ST_MAX_TILE * sizeof(unsigned long long) + ST_MAX_TILE * sizeof(uint16_t);
+    const uint32_t g = (uint32_t)((n + tile_rows - 1) / tile_rows);
+    prof_begin(stream, PROF_GATHER);
+    switch (v) {
+      case 16: scatter_rows_staged_kernel<uint4><<<g, ST_THREADS, smem, stream>>>((const uint4*)src, target, p, n, vpr, tile_rows); break;
+      case 8: scatter_rows_staged_kernel<uint64_t><<<g, ST_THREADS, smem, stream>>>((const uint64_t*)src, target, p, n, vpr, tile_rows); break;
+      case 4: scatter_rows_staged_kernel<uint32_t><<<g, ST_THREADS, smem, stream>>>((const uint32_t*)src, target, p, n, vpr, tile_rows); break;
+      case 2: scatter_rows_staged_kernel<uint16_t><<<g, ST_THREADS, smem, stream>>>((const uint16_t*)src, target, p, n, vpr, tile_rows); break;
+      default: scatter_rows_staged_kernel<uint8_t><<<g, ST_THREADS, smem, stream>>>((const uint8_t*)src, target, p, n, vpr, tile_rows); break;
+    }
+    prof_end(stream);
+    B200X_LAUNCH_CHECK("scatter_rows_staged_kernel");
+    return B200X_OK;
+  }
   uint64_t blocks = (total / 4 + 255) / 256;
   const uint64_t cap = (uint64_t)sm_count() * 8;
   if (blocks > cap) blocks = cap;
