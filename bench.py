@@ -56,6 +56,7 @@ def parse():
     ap.add_argument("--cpu-rows", type=int, default=CPU_SAMPLE_ROWS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the random_shuffle / groupby side measurements")
     return ap.parse_args()
 
 
@@ -297,6 +298,48 @@ def run_ours(args):
                "d2h_bytes_per_step": int(d2h), "ms_per_step": e_ms / e_steps, "steps": e_steps}
         del o_keys, o_pay
 
+    # ---------------- the other two operators of the path (N = 1 only; reported under "extras", not the metric)
+    extras = None
+    if world == 1 and not args.no_extras:
+        from ray_project_ray_b200.aggregate import Count, Mean, Sum
+
+        def timed(fn, steps=3, warm=2):
+            for _ in range(warm):
+                fn()
+            torch.cuda.synchronize()
+            g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            g0.record()
+            for _ in range(steps):
+                r = fn()
+            g1.record()
+            torch.cuda.synchronize()
+            return g0.elapsed_time(g1) / steps, r
+
+        peak_x = 6548.8
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+                peak_x = float(json.load(f).get("hbm_gbs", peak_x))
+        except OSError:
+            pass
+        extras = {}
+        ms, r = timed(lambda: ds.random_shuffle(seed=0))
+        assert r.count() == n
+        gbs = n * 2 * ROW_BYTES / (ms / 1e3) / 1e9
+        extras["random_shuffle"] = {"workload": f"configs[1]: {n} rows x (8 B id + {PAYLOAD_BYTES} B payload), seed=0, one global bijection",
+                                    "ms_per_step": ms, "rows_per_s": n / (ms / 1e3), "gb_per_s": gbs, "frac_of_hbm_peak": gbs / peak_x}
+        del r
+        gn, groups = 2 * n, 1_000_000
+        gen = torch.Generator(device=dev).manual_seed(4)
+        gk = torch.randint(0, groups, (gn,), dtype=torch.int64, device=dev, generator=gen)
+        gv = torch.randint(-2**31, 2**31, (gn,), dtype=torch.int64, device=dev, generator=gen)
+        gds = rd.from_torch_columns({"k": gk, "v": gv}, override_num_blocks=nblocks)
+        ms, r = timed(lambda: gds.groupby("k").aggregate(Sum("v"), Mean("v"), Count()))
+        assert r.count() == groups and int(r.sum("count()")) == gn
+        gbs = (gn * 16 + groups * 32) / (ms / 1e3) / 1e9
+        extras["groupby_aggregate"] = {"workload": f"configs[2]: {gn} rows, {groups} distinct int64 keys (uniform), Sum+Mean+Count of one int64 column",
+                                       "ms_per_step": ms, "rows_per_s": gn / (ms / 1e3), "gb_per_s": gbs, "frac_of_hbm_peak": gbs / peak_x}
+        del r, gds, gk, gv
+
     clocks = sampler.stop() if rank == 0 else None
     if rank != 0:
         if world > 1:
@@ -340,7 +383,7 @@ def run_ours(args):
         "roofline": roof,
         "roofline_op": {"bound": "hbm", "achieved": op_gbs / world, "peak": peak, "unit": "GB/s", "frac": op_gbs / world / peak,
                         "algorithmic_bytes": "2 x row_bytes x rows (SURVEY.md 8d)", "peak_source": peak_src},
-        "kernels": breakdown, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+        "kernels": breakdown, "e2e": e2e, "extras": extras, "gpu_launches": launches, "clocks": clocks,
     }
     if not args.no_cpu_baseline and world == 1:
         import pyarrow
