@@ -510,9 +510,11 @@ def fused_aggregate(blocks: List[DeviceBlock], boundaries: List[Any], key, aggs)
         return [aggregate_sorted(table, None, aggs, None, None, finalize=True, n=n)]
     perm, codes, _ = ops.argsort(_contig(table.columns[k]), False, want_codes=True)
     out = aggregate_sorted(table, k, aggs, perm, codes, finalize=True, n=n)
-    if R == 1 or any(b is None or (isinstance(b, tuple) and b[0] is None) for b in boundaries):
-        return [out] + [DeviceBlock.empty(table.device) for _ in range(R - 1)]
+    if R == 1:
+        return [out]
     if isinstance(boundaries, AutoBoundaries):
         return _cut_sorted_evenly(out, k, False, R)
+    if any(b is None or (isinstance(b, tuple) and b[0] is None) for b in boundaries):
+        return [out] + [DeviceBlock.empty(table.device) for _ in range(R - 1)]
     cuts = find_partition_indices(out.columns[k], boundaries, False)
     return _cut(out, cuts)

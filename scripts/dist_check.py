@@ -57,6 +57,22 @@ def main():
                 np.testing.assert_array_equal(np.concatenate([p[1] for p in parts]), allp[order])
                 sizes = [len(p[0]) for p in parts]
                 print(f"sort {kind} desc={desc} transport={transport} (p2p={D._p2p_ok['state']}): OK, rows per rank {sizes}", flush=True)
+    # gensort-shaped records (configs[3]): 10-byte key as (hi uint64, lo uint16) + 90-byte payload
+    m = 60_000
+    hi = rng.integers(0, 2**63, m, dtype=np.int64).astype(np.uint64) * 2 + rng.integers(0, 2, m).astype(np.uint64)
+    hi[: m // 3] = hi[m // 3: 2 * (m // 3)]
+    lo = rng.integers(0, 2**16, m).astype(np.uint16)
+    pay = rng.integers(0, 256, (m, 90), dtype=np.uint8)
+    out = rd.from_numpy_columns({"hi": hi, "lo": lo, "payload": pay}, override_num_blocks=2).sort(["hi", "lo"]).to_numpy()
+    parts = gather_np((out["hi"], out["lo"], out["payload"].sum(axis=1)), world, rank)
+    ins = gather_np((hi, lo, pay.sum(axis=1)), world, rank)
+    if rank == 0:
+        ahi, alo, ap = (np.concatenate([p[i] for p in ins]) for i in range(3))
+        order = orc.stable_argsort_multi([ahi, alo], False)
+        np.testing.assert_array_equal(np.concatenate([p[0] for p in parts]), ahi[order])
+        np.testing.assert_array_equal(np.concatenate([p[1] for p in parts]), alo[order])
+        np.testing.assert_array_equal(np.concatenate([p[2] for p in parts]), ap[order])
+        print("gensort-shaped 2-column key sort: OK", flush=True)
     # groupby
     gk = rng.integers(0, 3000, n, dtype=np.int64)
     gv = rng.integers(-2**31, 2**31, n, dtype=np.int64)
