@@ -190,6 +190,11 @@ int b200x_perm_indices_host(size_t n, uint64_t seed, int inverse, size_t start, 
 int b200x_group_boundaries(const uint64_t* codes, size_t n, uint32_t* group_starts, uint32_t* num_groups_out, void* temp,
                            size_t* temp_bytes, void* stream);
 
+/* The same for a multi-column key: codes_host is a HOST array of num_cols (<= 4) device code arrays of the
+ * rows in sorted order; a group starts where any column changes (groupby(["a", "b"]), dataset.py:1788-1836). */
+int b200x_group_boundaries_multi(const uint64_t* const* codes_host, int num_cols, size_t n, uint32_t* group_starts,
+                                 uint32_t* num_groups_out, void* temp, size_t* temp_bytes, void* stream);
+
 /* Segmented reduction of one value column over the groups found above (group_starts and the
  * device scalar num_groups as written by b200x_group_boundaries). Row i of the sorted order
  * holds values[perm[i]] (perm may be NULL = already in sorted order). For every group g
@@ -218,6 +223,9 @@ int b200x_group_counts(const uint32_t* group_starts, const uint32_t* num_groups,
  * mode 1: out[g] = counts[g] < 2 ? 0 : sqrt(sum[g] / (counts[g] - ddof))   (Std.finalize, :296-302) */
 int b200x_finalize_groups(const void* sum, int value_type, const int64_t* counts, size_t num_groups, int mode, int ddof,
                           double* out, void* stream);
+
+/* out[g] = max(|min_in[g]|, |max_in[g]|), same type as the inputs (AbsMax, aggregate/_aggregate.py:323-357). */
+int b200x_absmax_groups(const void* min_in, const void* max_in, int value_type, size_t num_groups, void* out, void* stream);
 
 #ifdef __cplusplus
 }

@@ -54,6 +54,9 @@ SIGNATURES = {
     "b200x_perm_indices": (c_int, [c_size_t, c_uint64, c_int, c_size_t, c_size_t, c_void_p, c_void_p]),
     "b200x_perm_indices_host": (c_int, [c_size_t, c_uint64, c_int, c_size_t, c_size_t, c_void_p]),
     "b200x_group_boundaries": (c_int, [c_void_p, c_size_t, c_void_p, c_void_p, c_void_p, _size_p, c_void_p]),
+    "b200x_group_boundaries_multi": (c_int, [POINTER(c_void_p), c_int, c_size_t, c_void_p, c_void_p, c_void_p, _size_p,
+                                             c_void_p]),
+    "b200x_absmax_groups": (c_int, [c_void_p, c_void_p, c_int, c_size_t, c_void_p, c_void_p]),
     "b200x_segmented_reduce": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_size_t, c_void_p, c_void_p,
                                        c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, _size_p, c_void_p]),
     "b200x_group_counts": (c_int, [c_void_p, c_void_p, c_size_t, c_size_t, c_void_p, c_void_p]),

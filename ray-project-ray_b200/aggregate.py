@@ -100,6 +100,14 @@ class Std(_AggregateOnKeyBase):
         self._ddof = ddof
 
 
+class AbsMax(_AggregateOnKeyBase):
+    """Largest absolute value per group (_aggregate.py:323-357)."""
+
+    def __init__(self, on: Optional[str] = None, ignore_nulls: bool = True, alias_name: Optional[str] = None):
+        self._setup("abs_max", on, alias_name, ignore_nulls)
+        self._device_kind = "absmax"
+
+
 def _device_kind(agg: AggregateFn) -> str:
     kind = getattr(agg, "_device_kind", None)
     if kind is None:
@@ -168,6 +176,9 @@ def _reduce_partials(kind: str, agg: AggregateFn, name: str, src: DeviceBlock, s
             return {name: counts()}
         if kind in ("sum", "min", "max"):
             return {name: smm(agg._key_fn)[("sum", "min", "max").index(kind)]}
+        if kind == "absmax":
+            t = smm(agg._key_fn)
+            return {name: ops.absmax_groups(t[1], t[2])}
         if kind == "mean":
             return {name: smm(agg._key_fn)[0], name + SEP + "count": counts()}
         if kind == "std":
@@ -188,8 +199,12 @@ def _reduce_partials(kind: str, agg: AggregateFn, name: str, src: DeviceBlock, s
         out[name] = ops.segmented_reduce(starts, ng, G, perm, col, n)[0]
     elif kind == "min":
         out[name] = ops.segmented_reduce(starts, ng, G, perm, col, n, want_sum=False, want_min=True)[1]
-    elif kind == "max":
-        out[name] = ops.segmented_reduce(starts, ng, G, perm, col, n, want_sum=False, want_max=True)[2]
+    elif kind in ("max", "absmax"):
+        if raw and kind == "absmax":
+            t = ops.segmented_reduce(starts, ng, G, perm, col, n, False, True, True)
+            out[name] = ops.absmax_groups(t[1], t[2])
+        else:  # partial abs-max values are >= 0: merging them is a max
+            out[name] = ops.segmented_reduce(starts, ng, G, perm, col, n, want_sum=False, want_max=True)[2]
     elif kind == "mean":
         out[name] = ops.segmented_reduce(starts, ng, G, perm, col, n)[0]
         if raw:
@@ -219,7 +234,7 @@ def _reduce_partials(kind: str, agg: AggregateFn, name: str, src: DeviceBlock, s
 
 
 def _finalize(kind: str, agg: AggregateFn, name: str, acc: Dict[str, torch.Tensor]) -> torch.Tensor:
-    if kind in ("count", "sum", "min", "max"):
+    if kind in ("count", "sum", "min", "max", "absmax"):
         return acc[name]
     if kind == "mean":
         return ops.finalize_groups(acc[name], acc[name + SEP + "count"], 0)
@@ -228,34 +243,66 @@ def _finalize(kind: str, agg: AggregateFn, name: str, acc: Dict[str, torch.Tenso
     raise ValueError(kind)
 
 
-def _check_key(key) -> Optional[str]:
+def _check_key(key):
+    """None (global aggregation), one column name, or a list of >= 2 column names (at most 4)."""
     if isinstance(key, list):
         if len(key) == 1:
             return key[0]
         if len(key) == 0:
             return None
-        raise NotImplementedError("grouping by more than one key column is not implemented on device blocks")
+        if len(key) > 4:
+            raise NotImplementedError("grouping by more than four key columns is not implemented on device blocks")
+        return list(key)
     return key
 
 
-def aggregate_sorted(block: DeviceBlock, key: Optional[str], aggs: Sequence[AggregateFn], perm, codes,
-                     finalize: bool, n: int) -> DeviceBlock:
-    """One-shot groupby over rows visited in sorted order `perm` whose ascending key codes are
-    `codes` (both from ops.argsort); the fused scheduler path."""
+def _key_list(key) -> List[str]:
+    return [] if key is None else ([key] if isinstance(key, str) else list(key))
+
+
+def _sorted_key_codes(block: DeviceBlock, keys: List[str], perm) -> List[torch.Tensor]:
+    """Ascending codes of every key column, in the sorted row order."""
+    out = []
+    for k in keys:
+        col = _contig(block.columns[k])
+        if perm is not None:
+            col = ops.gather(col, perm)
+        out.append(ops.encode_keys(col, False))
+    return out
+
+
+def _argsort_keys(block: DeviceBlock, keys: List[str], want_codes: bool):
+    """Stable multi-column argsort (last key column first). Returns (perm, codes of the first column or None)."""
+    perm = codes = None
+    for i, k in enumerate(reversed(keys)):
+        last = i == len(keys) - 1
+        perm, codes, _ = ops.argsort(_contig(block.columns[k]), False, perm_in=perm, want_codes=want_codes and last)
+    return perm, codes
+
+
+def aggregate_sorted(block: DeviceBlock, key, aggs: Sequence[AggregateFn], perm, codes, finalize: bool, n: int) -> DeviceBlock:
+    """One-shot groupby over rows visited in sorted order `perm`. `codes`: the ascending codes of the
+    (single) key column in that order, or None to derive them from the block."""
     key = _check_key(key)
+    keys = _key_list(key)
     dev = block.device
     names = resolved_names(aggs)
-    if key is None:
+    if not keys:
         starts = torch.zeros(1, dtype=torch.int32, device=dev)
         ng = torch.ones(1, dtype=torch.int32, device=dev)
         G = 1
     else:
-        starts, ng = ops.group_boundaries(codes)
+        if len(keys) == 1 and codes is not None:
+            codes_list = [codes]
+        else:
+            codes_list = _sorted_key_codes(block, keys, perm)
+        starts, ng = ops.group_boundaries_multi(codes_list)
         G = int(ng.item())
     cols: Dict[str, torch.Tensor] = {}
-    if key is not None:
+    if keys:
         first_rows = ops.gather(perm, starts[:G].contiguous()) if perm is not None else starts[:G].contiguous()
-        cols[key] = ops.gather(_contig(block.columns[key]), first_rows)
+        for k in keys:
+            cols[k] = ops.gather(_contig(block.columns[k]), first_rows)
     cache: dict = {}
     for agg, name in zip(aggs, names):
         kind = _device_kind(agg)
@@ -270,22 +317,17 @@ def aggregate_sorted(block: DeviceBlock, key: Optional[str], aggs: Sequence[Aggr
 def combine_block(block: DeviceBlock, key, aggs: Sequence[AggregateFn], presorted: bool = True) -> DeviceBlock:
     """ArrowBlockAccessor.combine (arrow_block.py:466-548): one partial-accumulator row per group of
     a block sorted by key."""
-    key = _check_key(key)
     n = block.num_rows
-    names = resolved_names(aggs)
     if n == 0:
         return DeviceBlock.empty(block.device)
-    if key is None:
-        codes = None
-    else:
-        codes = ops.encode_keys(_contig(block.columns[key]), False)
-    return aggregate_sorted(block, key, aggs, None, codes, finalize=False, n=n)
+    return aggregate_sorted(block, key, aggs, None, None, finalize=False, n=n)
 
 
 def merge_combined_blocks(blocks: Sequence[DeviceBlock], key, aggs: Sequence[AggregateFn], finalize: bool) -> DeviceBlock:
     """ArrowBlockAccessor.aggregate_combined_blocks (arrow_block.py:569-680): merge partial rows with
     equal keys (mapper order within a key, as heapq.merge gives), optionally finalize."""
     key = _check_key(key)
+    keys = _key_list(key)
     blocks = [b for b in blocks if b.num_rows > 0]
     if not blocks:
         return DeviceBlock.empty()
@@ -293,19 +335,21 @@ def merge_combined_blocks(blocks: Sequence[DeviceBlock], key, aggs: Sequence[Agg
     n = allp.num_rows
     dev = allp.device
     names = resolved_names(aggs)
-    if key is None:
+    if not keys:
         perm = None
         starts = torch.zeros(1, dtype=torch.int32, device=dev)
         ng = torch.ones(1, dtype=torch.int32, device=dev)
         G = 1
     else:
-        perm, codes, _ = ops.argsort(_contig(allp.columns[key]), False, want_codes=True)
-        starts, ng = ops.group_boundaries(codes)
+        perm, codes = _argsort_keys(allp, keys, want_codes=len(keys) == 1)
+        codes_list = [codes] if len(keys) == 1 else _sorted_key_codes(allp, keys, perm)
+        starts, ng = ops.group_boundaries_multi(codes_list)
         G = int(ng.item())
     cols: Dict[str, torch.Tensor] = {}
-    if key is not None:
+    if keys:
         first_rows = ops.gather(perm, starts[:G].contiguous())
-        cols[key] = ops.gather(_contig(allp.columns[key]), first_rows)
+        for k in keys:
+            cols[k] = ops.gather(_contig(allp.columns[k]), first_rows)
     for agg, name in zip(aggs, names):
         kind = _device_kind(agg)
         acc = _reduce_partials(kind, agg, name, allp, starts, ng, G, perm, n, raw=False)

@@ -27,12 +27,24 @@ constexpr int SCAN_THREADS = 1024;
 
 // ------------------------------- boundaries --------------------------------
 
-__device__ __forceinline__ bool is_head(const uint64_t* __restrict__ codes, uint64_t i) {
-  return i == 0 || codes[i] != codes[i - 1];
+constexpr int MAX_GROUP_COLS = 4;
+struct CodeCols {
+  const uint64_t* c[MAX_GROUP_COLS];
+  int n;
+};
+
+// a group starts where ANY key column changes
+__device__ __forceinline__ bool is_head(const CodeCols& k, uint64_t i) {
+  if (i == 0) return true;
+  bool h = false;
+#pragma unroll
+  for (int j = 0; j < MAX_GROUP_COLS; ++j)
+    if (j < k.n) h |= k.c[j][i] != k.c[j][i - 1];
+  return h;
 }
 
 __global__ void __launch_bounds__(G_THREADS)
-heads_count_kernel(const uint64_t* __restrict__ codes, uint64_t n, uint32_t* __restrict__ tile_heads) {
+heads_count_kernel(const CodeCols codes, uint64_t n, uint32_t* __restrict__ tile_heads) {
   __shared__ uint32_t s_warp[G_THREADS / 32];
   const uint64_t base = (uint64_t)blockIdx.x * G_TILE;
   uint32_t c = 0;
@@ -80,7 +92,7 @@ scan_tiles_kernel(uint32_t* __restrict__ tile_heads, uint32_t T, uint32_t* __res
 }
 
 __global__ void __launch_bounds__(G_THREADS)
-group_starts_kernel(const uint64_t* __restrict__ codes, uint64_t n, const uint32_t* __restrict__ tile_base,
+group_starts_kernel(const CodeCols codes, uint64_t n, const uint32_t* __restrict__ tile_base,
                     uint32_t* __restrict__ group_starts) {
   __shared__ uint32_t s_warp[G_THREADS / 32];
   const uint64_t base = (uint64_t)blockIdx.x * G_TILE;
@@ -391,6 +403,19 @@ finalize_kernel(const void* __restrict__ sum, int vt, const int64_t* __restrict_
   }
 }
 
+__global__ void __launch_bounds__(256)
+absmax_kernel(const void* __restrict__ mn, const void* __restrict__ mx, int vt, uint64_t G, void* __restrict__ out) {
+  for (uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; g < G; g += (uint64_t)gridDim.x * blockDim.x) {
+    if (vt == B200X_VAL_I64) {
+      const int64_t a = ((const int64_t*)mn)[g], b = ((const int64_t*)mx)[g];
+      const int64_t aa = a < 0 ? -a : a, bb = b < 0 ? -b : b;
+      ((int64_t*)out)[g] = aa > bb ? aa : bb;
+    } else {
+      ((double*)out)[g] = fmax(fabs(((const double*)mn)[g]), fabs(((const double*)mx)[g]));
+    }
+  }
+}
+
 static inline uint32_t tiles_of(size_t n) { return (uint32_t)((n + G_TILE - 1) / G_TILE); }
 
 template <typename VIn, typename T, bool CENTER>
@@ -413,8 +438,27 @@ static int launch_seg_reduce(const uint32_t* group_starts, const uint32_t* num_g
 
 using namespace b200x;
 
+extern "C" int b200x_group_boundaries_multi(const uint64_t* const* codes_host, int num_cols, size_t n,
+                                            uint32_t* group_starts, uint32_t* num_groups_out, void* temp,
+                                            size_t* temp_bytes, void* stream_);
+
 extern "C" int b200x_group_boundaries(const uint64_t* codes, size_t n, uint32_t* group_starts, uint32_t* num_groups_out,
                                       void* temp, size_t* temp_bytes, void* stream_) {
+  const uint64_t* one[1] = {codes};
+  return b200x_group_boundaries_multi(one, 1, n, group_starts, num_groups_out, temp, temp_bytes, stream_);
+}
+
+extern "C" int b200x_group_boundaries_multi(const uint64_t* const* codes_host, int num_cols, size_t n,
+                                            uint32_t* group_starts, uint32_t* num_groups_out, void* temp,
+                                            size_t* temp_bytes, void* stream_) {
+  if (codes_host == nullptr || num_cols < 1 || num_cols > MAX_GROUP_COLS) {
+    set_error("b200x_group_boundaries_multi: 1..%d key columns", MAX_GROUP_COLS);
+    return B200X_ERR_ARG;
+  }
+  CodeCols cc;
+  cc.n = num_cols;
+  for (int j = 0; j < MAX_GROUP_COLS; ++j) cc.c[j] = j < num_cols ? codes_host[j] : nullptr;
+  const uint64_t* codes = cc.c[0];
   cudaStream_t stream = (cudaStream_t)stream_;
   if (temp_bytes == nullptr) {
     set_error("b200x_group_boundaries: temp_bytes is NULL");
@@ -442,16 +486,18 @@ extern "C" int b200x_group_boundaries(const uint64_t* codes, size_t n, uint32_t*
     B200X_CUDA(cudaMemsetAsync(num_groups_out, 0, sizeof(uint32_t), stream));
     return B200X_OK;
   }
+  for (int j = 1; j < num_cols; ++j)
+    if (cc.c[j] == nullptr) codes = nullptr;
   if (codes == nullptr || group_starts == nullptr) {
     set_error("b200x_group_boundaries: NULL pointer");
     return B200X_ERR_ARG;
   }
   uint32_t* tile_heads = (uint32_t*)temp;
-  heads_count_kernel<<<Tn, G_THREADS, 0, stream>>>(codes, n, tile_heads);
+  heads_count_kernel<<<Tn, G_THREADS, 0, stream>>>(cc, n, tile_heads);
   B200X_LAUNCH_CHECK("heads_count_kernel");
   scan_tiles_kernel<<<1, SCAN_THREADS, 0, stream>>>(tile_heads, Tn, num_groups_out);
   B200X_LAUNCH_CHECK("scan_tiles_kernel");
-  group_starts_kernel<<<Tn, G_THREADS, 0, stream>>>(codes, n, tile_heads, group_starts);
+  group_starts_kernel<<<Tn, G_THREADS, 0, stream>>>(cc, n, tile_heads, group_starts);
   B200X_LAUNCH_CHECK("group_starts_kernel");
   return B200X_OK;
 }
@@ -525,5 +571,21 @@ extern "C" int b200x_finalize_groups(const void* sum, int value_type, const int6
   if (blocks > cap) blocks = cap;
   finalize_kernel<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream_>>>(sum, value_type, counts, num_groups, mode, ddof, out);
   B200X_LAUNCH_CHECK("finalize_kernel");
+  return B200X_OK;
+}
+
+extern "C" int b200x_absmax_groups(const void* min_in, const void* max_in, int value_type, size_t num_groups, void* out,
+                                   void* stream_) {
+  if (num_groups == 0) return B200X_OK;
+  if (min_in == nullptr || max_in == nullptr || out == nullptr ||
+      (value_type != B200X_VAL_I64 && value_type != B200X_VAL_F64)) {
+    set_error("b200x_absmax_groups: bad arguments");
+    return B200X_ERR_ARG;
+  }
+  uint64_t blocks = (num_groups + 255) / 256;
+  const uint64_t cap = (uint64_t)sm_count() * 8;
+  if (blocks > cap) blocks = cap;
+  absmax_kernel<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream_>>>(min_in, max_in, value_type, num_groups, out);
+  B200X_LAUNCH_CHECK("absmax_kernel");
   return B200X_OK;
 }

@@ -398,6 +398,8 @@ def dist_aggregate(local: DeviceBlock, key: Optional[str], aggs, group=None, sam
 
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     dev = local.device
+    if isinstance(key, list):
+        raise NotImplementedError("multi-column groupby keys are not supported across ranks yet")
     local = SortAggregateTaskSpec._prune_unused_columns(local, key, aggs)
     n = local.num_rows
     if key is None:

@@ -264,6 +264,36 @@ def group_boundaries(codes: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
     return starts, ng
 
 
+def group_boundaries_multi(codes_list: Sequence[torch.Tensor]) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Group boundaries for a multi-column key: a group starts where any of the (sorted-order) code columns changes."""
+    if len(codes_list) == 1:
+        return group_boundaries(codes_list[0])
+    dev = _require_cuda(*codes_list)
+    n = codes_list[0].numel()
+    starts = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+    ng = torch.zeros(1, dtype=torch.int32, device=dev)
+    ptrs = (ctypes.c_void_p * len(codes_list))(*[c.data_ptr() for c in codes_list])
+    with torch.cuda.device(dev):
+        st = _stream(dev)
+        need = _lib.query_temp("b200x_group_boundaries_multi", ptrs, len(codes_list), n, starts.data_ptr(), ng.data_ptr(),
+                               stream=st)
+        temp = _temp(need, dev)
+        nb = ctypes.c_size_t(temp.numel())
+        _lib.call("b200x_group_boundaries_multi", ptrs, len(codes_list), n, starts.data_ptr(), ng.data_ptr(),
+                  temp.data_ptr(), ctypes.byref(nb), st)
+    return starts, ng
+
+
+def absmax_groups(mn: torch.Tensor, mx: torch.Tensor) -> torch.Tensor:
+    dev = _require_cuda(mn, mx)
+    out = torch.empty_like(mn)
+    if mn.numel():
+        with torch.cuda.device(dev):
+            _lib.call("b200x_absmax_groups", mn.data_ptr(), mx.data_ptr(), value_type_of(mn), mn.numel(), out.data_ptr(),
+                      _stream(dev))
+    return out
+
+
 def value_type_of(t: torch.Tensor) -> int:
     if t.dtype == torch.int64:
         return VAL_I64

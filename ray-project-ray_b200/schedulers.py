@@ -506,10 +506,17 @@ def fused_aggregate(blocks: List[DeviceBlock], boundaries: List[Any], key, aggs)
     if n == 0:
         return [DeviceBlock.empty(table.device) for _ in range(R)]
     k = key[0] if isinstance(key, list) and len(key) == 1 else key
-    if k is None:
+    if k is None or (isinstance(k, list) and len(k) == 0):
         return [aggregate_sorted(table, None, aggs, None, None, finalize=True, n=n)]
-    perm, codes, _ = ops.argsort(_contig(table.columns[k]), False, want_codes=True)
-    out = aggregate_sorted(table, k, aggs, perm, codes, finalize=True, n=n)
+    if isinstance(k, list):
+        from .aggregate import _argsort_keys
+
+        perm, _ = _argsort_keys(table, k, want_codes=False)
+        out = aggregate_sorted(table, k, aggs, perm, None, finalize=True, n=n)
+        k = k[0]  # output blocks are cut on the first key column (rows equal in it stay together)
+    else:
+        perm, codes, _ = ops.argsort(_contig(table.columns[k]), False, want_codes=True)
+        out = aggregate_sorted(table, k, aggs, perm, codes, finalize=True, n=n)
     if R == 1:
         return [out]
     if isinstance(boundaries, AutoBoundaries):

@@ -343,3 +343,33 @@ def test_product_fails_loudly_without_cuda_tensors():
 
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         ops.argsort(torch.zeros(4, dtype=torch.int64))
+
+
+@pytest.mark.parametrize("sched", ["fused", "pull", "push"])
+def test_groupby_two_key_columns_and_absmax(sched, cuda_device):
+    """groupby(["a", "b"]) (dataset.py:1788-1836) and AbsMax (_aggregate.py:323-357) against pyarrow's group_by."""
+    from ray_project_ray_b200.aggregate import AbsMax
+
+    _set_scheduler(sched)
+    rng = np.random.default_rng(12)
+    n = 60_000
+    a = rng.integers(0, 40, n, dtype=np.int64)
+    b = rng.integers(-3, 3, n).astype(np.float64) / 2          # float second key with -0.0 / 0.0 ties
+    b[rng.integers(0, n, 500)] = -0.0
+    v = rng.integers(-10**9, 10**9, n, dtype=np.int64)
+    f = rng.standard_normal(n)
+    ds = rd.from_numpy_columns({"a": a, "b": b, "v": v, "f": f, "junk": np.arange(n)}, override_num_blocks=6)
+    out = ds.groupby(["a", "b"]).aggregate(Sum("v"), Count(), Mean("f"), AbsMax("v"), AbsMax("f"), Max("f")).to_numpy()
+    assert list(out.keys()) == ["a", "b", "sum(v)", "count()", "mean(f)", "abs_max(v)", "abs_max(f)", "max(f)"]
+    t = pa.table({"a": a, "b": b + 0.0, "v": v, "f": f, "av": np.abs(v), "af": np.abs(f)})
+    want = t.group_by(["a", "b"]).aggregate([("v", "sum"), ("v", "count"), ("f", "mean"), ("av", "max"), ("af", "max"),
+                                             ("f", "max")]).sort_by([("a", "ascending"), ("b", "ascending")])
+    np.testing.assert_array_equal(out["a"], want["a"].to_numpy())
+    np.testing.assert_array_equal(out["b"] + 0.0, want["b"].to_numpy())
+    np.testing.assert_array_equal(out["sum(v)"], want["v_sum"].to_numpy())
+    np.testing.assert_array_equal(out["count()"], want["v_count"].to_numpy())
+    np.testing.assert_array_equal(out["abs_max(v)"], want["av_max"].to_numpy())
+    np.testing.assert_array_equal(out["abs_max(f)"], want["af_max"].to_numpy())
+    np.testing.assert_array_equal(out["max(f)"], want["f_max"].to_numpy())
+    np.testing.assert_allclose(out["mean(f)"], want["f_mean"].to_numpy(), rtol=FLOAT_RTOL)
+    assert ds.aggregate(AbsMax("v")) == {"abs_max(v)": int(np.abs(v).max())}
