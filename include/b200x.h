@@ -83,7 +83,9 @@ int b200x_radix_argsort(const void* keys, int key_type, int descending, const ui
 
 /* Tuning knobs (process-wide). key 0: fewest rows for which b200x_radix_argsort considers its
  * HYBRID mode (two global passes on the top 16 varying bits, then every run is finished in shared
- * memory); default 2^22. Results never depend on the mode. */
+ * memory); default 2^22. key 1: most blocks per SM the staged peer scatter launches (0 = one block per tile);
+ * a small value leaves room for work running next to the transfer on another stream. Results never depend
+ * on either. */
 int b200x_set_tuning(int key, long long value);
 
 /* b200x_radix_argsort for callers that cannot allocate device memory. (No counterpart in the

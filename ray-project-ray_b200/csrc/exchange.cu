@@ -287,6 +287,9 @@ scatter_rows_by_target_kernel(const V* __restrict__ src, const uint32_t* __restr
 // each owner's rows as ONE contiguous run, consecutive threads storing consecutive 16-byte pieces. Remote
 // stores therefore leave the SM as full 128-byte requests instead of one 8..64-byte packet per row
 // (8 GPUs, 100 M rows: key column 3.45 ms unstaged).
+// b200x_set_tuning(1, k): staged scatter launches at most k blocks per SM (0 = one block per tile)
+int g_scatter_blocks_per_sm = 0;
+
 constexpr int ST_THREADS = 256;
 constexpr int ST_MAX_TILE = 1024;
 constexpr int ST_DATA_BYTES = 32 * 1024;
@@ -300,7 +303,11 @@ scatter_rows_staged_kernel(const V* __restrict__ src, const uint32_t* __restrict
   unsigned long long* sdst = reinterpret_cast<unsigned long long*>(st_raw + ST_DATA_BYTES);  // [tile_rows] destination of staged row i
   uint16_t* slp = reinterpret_cast<uint16_t*>(sdst + ST_MAX_TILE);                     // [tile_rows] staged position of tile row
   __shared__ uint32_t s_cnt[MAX_PEERS], s_min[MAX_PEERS], s_off[MAX_PEERS];
-  const uint64_t r0 = (uint64_t)blockIdx.x * tile_rows;
+  const uint64_t num_tiles = (n + tile_rows - 1) / tile_rows;
+  // grid-stride over tiles: the host can launch one block per tile, or only a few blocks per SM so that
+  // the transfer leaves most of every SM to work running next to it on another stream
+  for (uint64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+  const uint64_t r0 = tile * tile_rows;
   const uint32_t rows = (uint32_t)min((uint64_t)tile_rows, n - r0);
   if (threadIdx.x < MAX_PEERS) {
     s_cnt[threadIdx.x] = 0;
@@ -351,6 +358,8 @@ scatter_rows_staged_kernel(const V* __restrict__ src, const uint32_t* __restrict
   for (uint32_t t = threadIdx.x; t < chunks; t += ST_THREADS) {  // owner runs leave as contiguous stores
     const uint32_t i = t / vec_per_row, c = t - i * vec_per_row;
     reinterpret_cast<V*>(sdst[i])[c] = sdata[t];
+  }
+  __syncthreads();
   }
 }
 
@@ -436,7 +445,10 @@ extern "C" int b200x_scatter_rows_by_target(const void* src, size_t row_bytes, c
     uint32_t tile_rows = (uint32_t)(ST_DATA_BYTES / row_bytes) / ST_THREADS * ST_THREADS;
     if (tile_rows > (uint32_t)ST_MAX_TILE) tile_rows = ST_MAX_TILE;
     const size_t smem = ST_DATA_BYTES + ST_MAX_TILE * sizeof(unsigned long long) + ST_MAX_TILE * sizeof(uint16_t);
-    const uint32_t g = (uint32_t)((n + tile_rows - 1) / tile_rows);
+    uint64_t gtiles = (n + tile_rows - 1) / tile_rows;
+    if (g_scatter_blocks_per_sm > 0 && gtiles > (uint64_t)sm_count() * g_scatter_blocks_per_sm)
+      gtiles = (uint64_t)sm_count() * g_scatter_blocks_per_sm;
+    const uint32_t g = (uint32_t)gtiles;
     prof_begin(stream, PROF_GATHER);
     switch (v) {
       case 16: scatter_rows_staged_kernel<uint4><<<g, ST_THREADS, smem, stream>>>((const uint4*)src, target, p, n, vpr, tile_rows); break;

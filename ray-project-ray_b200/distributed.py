@@ -322,7 +322,16 @@ def _p2p_partition_sort(local: DeviceBlock, sort_key: SortKey, n: int, dev, grou
         side.wait_event(landed)
         perm2, _, skeys2 = DeviceBlockAccessor(keys_block)._argsort(sort_key, False)
         sorted_ev.record(side)
-    ex.send(rest)
+    # The payload transfer is link-bound: two blocks per SM keep NVLink busy and leave the rest of every SM to
+    # the sort running next to it (measured at 2 GPUs: sort || send 6.3 ms, against 10.5 ms with one block per
+    # tile and 9.4 ms back to back).
+    from . import _lib
+
+    _lib.call("b200x_set_tuning", 1, 2)
+    try:
+        ex.send(rest)
+    finally:
+        _lib.call("b200x_set_tuning", 1, 0)
     ex.fence()
     main.wait_event(sorted_ev)
     perm2.record_stream(main)

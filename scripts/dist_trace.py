@@ -43,4 +43,21 @@ for it in range(3):
     ex.send(["payload"]); t = T("send payload", t)
     ex.fence(); t = T("fence", t)
     out = ops.gather(ex.view(["payload"])["payload"], perm2); t = T("final payload gather", t)
+# overlap experiment: received-key sort on a side stream while the payload scatter runs on the main stream
+side = D._side_stream(dev)
+from ray_project_ray_b200 import _lib
+for bps in (0, 0, 1, 2, 4):
+    _lib.call("b200x_set_tuning", 1, bps)
+    torch.cuda.synchronize(); dist.barrier(); t = time.perf_counter()
+    ex.fence(); ex.send(["payload"]); ex.fence()
+    t = T(f"payload send alone, blocks/SM={bps}", t)
+    torch.cuda.synchronize(); dist.barrier(); t = time.perf_counter()
+    ex.fence()
+    ev = torch.cuda.Event(); ev.record()
+    with torch.cuda.stream(side):
+        side.wait_event(ev)
+        perm2, _, sk2 = DeviceBlockAccessor(kb)._argsort(sk, False)
+    ex.send(["payload"]); ex.fence()
+    side.synchronize()
+    t = T(f"CONCURRENT sort || payload send, blocks/SM={bps}", t)
 dist.destroy_process_group()
