@@ -161,10 +161,17 @@ pt_count_kernel(const void* __restrict__ keys, int kt, int desc, uint64_t n, con
   __syncthreads();
   const uint64_t base = (uint64_t)blockIdx.x * PT_TILE;
   const unsigned lane = threadIdx.x & 31;
+  const int width = key_type_bytes(kt);
+  uint64_t raw[PT_IPT];
+#pragma unroll
+  for (int j = 0; j < PT_IPT; ++j) {  // all loads first, so that they overlap
+    const uint64_t r = base + (uint64_t)j * PT_THREADS + threadIdx.x;
+    raw[j] = r < n ? load_raw_bits(keys, r, width) : 0ull;
+  }
 #pragma unroll
   for (int j = 0; j < PT_IPT; ++j) {
     const uint64_t r = base + (uint64_t)j * PT_THREADS + threadIdx.x;
-    const uint32_t d = r < n ? owner_of(load_encode(keys, r, kt, desc != 0), s_split, nsplit) : (uint32_t)(MAX_PEERS - 1);
+    const uint32_t d = r < n ? owner_of(encode_bits(raw[j], kt, desc != 0), s_split, nsplit) : (uint32_t)(MAX_PEERS - 1);
     const unsigned act = __ballot_sync(0xffffffffu, r < n);
     const unsigned peers = match4(d) & act;
     if (r < n && (int)lane == __ffs(peers) - 1) atomicAdd(&s_cnt[d], (uint32_t)__popc(peers));
@@ -217,11 +224,18 @@ pt_target_kernel(const void* __restrict__ keys, int kt, int desc, uint64_t n, co
   const unsigned lt = lanemask_lt();
   const uint64_t base = (uint64_t)blockIdx.x * PT_TILE + (uint64_t)warp * 32 * PT_IPT + lane;
   uint32_t dest[PT_IPT], rank[PT_IPT];
+  const int width = key_type_bytes(kt);
+  uint64_t raw[PT_IPT];
+#pragma unroll
+  for (int j = 0; j < PT_IPT; ++j) {
+    const uint64_t r = base + (uint64_t)j * 32;
+    raw[j] = r < n ? load_raw_bits(keys, r, width) : 0ull;
+  }
 #pragma unroll
   for (int j = 0; j < PT_IPT; ++j) {
     const uint64_t r = base + (uint64_t)j * 32;
     const bool valid = r < n;
-    dest[j] = valid ? owner_of(load_encode(keys, r, kt, desc != 0), s_split, nsplit) : (uint32_t)(MAX_PEERS - 1);
+    dest[j] = valid ? owner_of(encode_bits(raw[j], kt, desc != 0), s_split, nsplit) : (uint32_t)(MAX_PEERS - 1);
     const unsigned act = __ballot_sync(0xffffffffu, valid);
     const unsigned peers = match4(dest[j]) & act;
     uint32_t old = 0;
