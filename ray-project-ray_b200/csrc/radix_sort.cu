@@ -187,6 +187,7 @@ struct PassArgs {
   uint32_t* lookback;       // [tiles][RADIX]
   SortPlan* plan;
   const SortCtl* ctl;       // HYBRID passes sort code - ctl->base (NULL: plain codes)
+  uint32_t* mark_runs;      // HYBRID pass B: [65536] first position of every (B, A) run, found while writing
   uint32_t n;
   int pass;
   int kt;
@@ -416,6 +417,15 @@ onesweep_pass_kernel(const PassArgs a) {
         const uint32_t dst = obase[d] + i;
         kout[dst] = k;
         vout[dst] = svals[i];
+        if (a.mark_runs != nullptr && a.pass == 1) {
+          // The input of pass B is sorted by digit A, so inside a tile the pairs of one digit B are in
+          // (B, A) order: a pair whose predecessor in the tile lies in another (B, A) bin is the first of
+          // its bin in this tile. The run may have been begun by an earlier tile: keep the minimum.
+          const uint32_t mshift = plan->shift[0];
+          const uint32_t bin = (uint32_t)(k >> mshift) & (JOINT_BINS - 1);
+          const uint32_t pbin = i ? (uint32_t)(skeys[i - 1] >> mshift) & (JOINT_BINS - 1) : ~0u;
+          if (pbin != bin) atomicMin(&a.mark_runs[bin], dst);
+        }
       }
     }
   } else {
@@ -516,14 +526,18 @@ __global__ void hybrid_plan0_kernel(SortCtl* __restrict__ ctl, uint32_t n, unsig
   }
 }
 
-// H3: how many keys fall into each of the 65536 (digit B, digit A) runs. One read of the key
-// column; counts go straight to the 256 KB table with fire-and-forget global atomics (RED), which
-// stays in L2. (A shared-memory table needs 128 KB per block, i.e. 16 warps per SM, and shared
-// atomics at that occupancy ran 5x slower: 1.57 ms per 100 M keys.)
+// H3: histograms of the two global digits (A = bits [shiftA, shiftA+8), B = the 8 bits above) of
+// code - base. One read of the key column, two shared-memory atomics per key at full occupancy.
+// (A 65536-bin joint histogram - which would also give the run boundaries up front - cost 0.7 ms
+// per 100 M keys with global atomics and 1.6 ms with a 128 KB shared-memory table; the boundaries
+// are instead marked by pass B as it writes, see mark_runs.)
 __global__ void __launch_bounds__(512)
-joint_hist_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ perm_in, int kt, int desc, uint32_t n,
-                  const SortCtl* __restrict__ ctl, uint32_t* __restrict__ joint) {
+digit2_hist_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ perm_in, int kt, int desc, uint32_t n,
+                   const SortCtl* __restrict__ ctl, uint32_t* __restrict__ hist2 /*[2][RADIX]*/) {
   if (!ctl->candidate) return;
+  __shared__ uint32_t sh[2 * RADIX];
+  for (int i = threadIdx.x; i < 2 * RADIX; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
   const uint32_t shiftA = ctl->shiftA;
   const unsigned long long base = ctl->base;
   const int width = key_type_bytes(kt);
@@ -542,30 +556,39 @@ joint_hist_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ per
       for (int u = 0; u < U; ++u) c[u] = load_raw_bits(raw, (size_t)(i + u * stride), width);
     }
 #pragma unroll
-    for (int u = 0; u < U; ++u)
-      atomicAdd(&joint[(uint32_t)((encode_bits(c[u], kt, desc != 0) - base) >> shiftA) & (JOINT_BINS - 1)], 1u);
+    for (int u = 0; u < U; ++u) {
+      const uint32_t bin = (uint32_t)((encode_bits(c[u], kt, desc != 0) - base) >> shiftA) & (JOINT_BINS - 1);
+      atomicAdd(&sh[bin & 255u], 1u);
+      atomicAdd(&sh[RADIX + (bin >> 8)], 1u);
+    }
   }
   for (; i < n; i += stride) {
     const uint64_t e = load_encode(raw, perm_in ? (size_t)perm_in[i] : (size_t)i, kt, desc != 0);
-    atomicAdd(&joint[(uint32_t)((e - base) >> shiftA) & (JOINT_BINS - 1)], 1u);
+    const uint32_t bin = (uint32_t)((e - base) >> shiftA) & (JOINT_BINS - 1);
+    atomicAdd(&sh[bin & 255u], 1u);
+    atomicAdd(&sh[RADIX + (bin >> 8)], 1u);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 2 * RADIX; i += blockDim.x) {
+    const uint32_t v = sh[i];
+    if (v) atomicAdd(&hist2[i], v);
   }
 }
 
-// H4 (one block of 1024): run starts = exclusive scan of the joint table in (B, A) order; the
-// two digit histograms are its row / column sums; decide the mode.
 constexpr uint32_t FIN_IPT = 8;
 constexpr uint32_t FIN_SMALL_THREADS = 256, FIN_BIG_THREADS = 512;   // runs <= 2048 / <= 4096 pairs
 constexpr uint32_t FIN_MAX = FIN_BIG_THREADS * FIN_IPT;
 
-__global__ void __launch_bounds__(1024)
-hybrid_plan1_kernel(SortCtl* __restrict__ ctl, const uint32_t* __restrict__ joint, uint32_t* __restrict__ run_start,
-                    uint32_t* __restrict__ hbase /*[2][RADIX]*/, SortPlan* __restrict__ hplan, uint32_t n) {
-  __shared__ uint32_t s_warp[32];
-  __shared__ uint32_t s_histA[RADIX], s_histB[RADIX];
+// H4 (one block of RADIX threads): exclusive scans of the two digit histograms; arm the two passes
+// unless a digit bin is so full that some run must exceed what the finisher holds.
+__global__ void __launch_bounds__(RADIX)
+hybrid_plan1_kernel(SortCtl* __restrict__ ctl, const uint32_t* __restrict__ hist2, uint32_t* __restrict__ hbase /*[2][RADIX]*/,
+                    SortPlan* __restrict__ hplan, uint32_t n) {
+  __shared__ uint32_t warp_tot[RADIX / 32];
   __shared__ uint32_t s_max;
-  const int tid = threadIdx.x;
-  const unsigned lane = tid & 31, w = tid >> 5;
-  if (tid == 0) {
+  const int d = threadIdx.x;
+  const unsigned lane = d & 31, w = d >> 5;
+  if (d == 0) {
     for (int p = 0; p < MAX_PASSES; ++p) {
       hplan->active[p] = 0;
       hplan->src_sel[p] = 0;
@@ -574,76 +597,84 @@ hybrid_plan1_kernel(SortCtl* __restrict__ ctl, const uint32_t* __restrict__ join
     }
     hplan->first = -1;
     hplan->last = -1;
+    s_max = 0;
   }
   if (!ctl->candidate) return;
-  if (tid < RADIX) s_histA[tid] = s_histB[tid] = 0;
-  if (tid == 0) s_max = 0;
   __syncthreads();
-  constexpr int PER = JOINT_BINS / 1024;  // 64 consecutive bins per thread, all of one digit B
-  uint32_t local[PER];
-  uint32_t sum = 0, mx = 0;
-#pragma unroll 8
-  for (int k = 0; k < PER; ++k) {
-    const uint32_t bin = tid * PER + k;
-    const uint32_t c = joint[bin];
-    local[k] = c;
-    sum += c;
-    mx = max(mx, c);
-    if (c) atomicAdd(&s_histA[bin & 255u], c);
-  }
-  if (sum) atomicAdd(&s_histB[(tid * PER) >> 8], sum);
-  atomicMax(&s_max, mx);
-  uint32_t x = sum;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
-    if (lane >= (unsigned)o) x += y;
-  }
-  if (lane == 31) s_warp[w] = x;
-  __syncthreads();
-  uint32_t off = 0;
-  for (unsigned k = 0; k < w; ++k) off += s_warp[k];
-  uint32_t run = off + x - sum;
-#pragma unroll 8
-  for (int k = 0; k < PER; ++k) {
-    run_start[tid * PER + k] = run;
-    run += local[k];
-  }
-  if (tid == 1023) run_start[JOINT_BINS] = run;
-  __syncthreads();
-  // exclusive scans of the two 256-bin digit histograms (one warp-scan each over 8 values per lane)
-  if (w < 2) {
-    uint32_t* h = w == 0 ? s_histA : s_histB;
-    uint32_t v[8], t = 0;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      v[k] = h[lane * 8 + k];
-      t += v[k];
-    }
-    uint32_t xs = t;
+  for (int p = 0; p < 2; ++p) {
+    const uint32_t c = hist2[p * RADIX + d];
+    atomicMax(&s_max, c);
+    uint32_t x = c;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      uint32_t y = __shfl_up_sync(0xffffffffu, xs, o);
-      if (lane >= (unsigned)o) xs += y;
+      uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= (unsigned)o) x += y;
     }
-    uint32_t r = xs - t;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      hbase[w * RADIX + lane * 8 + k] = r;
-      r += v[k];
-    }
+    if (lane == 31) warp_tot[w] = x;
+    __syncthreads();
+    uint32_t off = 0;
+    for (unsigned k = 0; k < w; ++k) off += warp_tot[k];
+    hbase[p * RADIX + d] = off + x - c;
+    __syncthreads();
   }
+  if (d == 0 && (unsigned long long)s_max <= (unsigned long long)RADIX * FIN_MAX) {
+    hplan->active[0] = hplan->active[1] = 1;
+    hplan->shift[0] = ctl->shiftA;
+    hplan->shift[1] = ctl->shiftB;
+    hplan->first = 0;   // pass A reads the raw column and writes buffer 0
+    hplan->last = -1;   // neither pass writes the outputs: the finisher does
+    hplan->src_sel[1] = 0;  // pass B reads buffer 0, writes buffer 1
+  }
+}
+
+// H4b (one block of 1024, after pass B): pass B left in run_start[bin] the position of the first pair of
+// every non-empty (B, A) bin and 0xFFFFFFFF for empty bins. Fill the empty ones (an empty run starts
+// where the next run starts), find the longest run and decide the mode.
+__global__ void __launch_bounds__(1024)
+runs_fill_kernel(SortCtl* __restrict__ ctl, const SortPlan* __restrict__ hplan, uint32_t* __restrict__ run_start,
+                 uint32_t n) {
+  if (!hplan->active[1]) return;
+  __shared__ uint32_t s_min[32];
+  __shared__ uint32_t s_max;
+  const int tid = threadIdx.x;
+  const unsigned lane = tid & 31, w = tid >> 5;
+  if (tid == 0) s_max = 0;
+  constexpr int PER = JOINT_BINS / 1024;  // 64 consecutive bins per thread
+  uint32_t local[PER];
+  uint32_t mn = 0xFFFFFFFFu;
+#pragma unroll 8
+  for (int k = 0; k < PER; ++k) {
+    local[k] = run_start[tid * PER + k];
+    mn = min(mn, local[k]);
+  }
+  // suffix minimum over threads: x = min of mn over threads >= tid
+  uint32_t x = mn;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t y = __shfl_down_sync(0xffffffffu, x, o);
+    if (lane + o < 32) x = min(x, y);
+  }
+  if (lane == 0) s_min[w] = x;
+  __syncthreads();
+  uint32_t right = n;  // min over all threads of later warps, n if none
+  for (unsigned k = w + 1; k < 32; ++k) right = min(right, s_min[k]);
+  uint32_t after = __shfl_down_sync(0xffffffffu, x, 1);  // suffix min of the threads after me in my warp
+  if (lane == 31) after = 0xFFFFFFFFu;
+  uint32_t next = min(min(after, right), n);  // start of the first non-empty run after my 64 bins
+  uint32_t mx = 0;
+#pragma unroll 8
+  for (int k = PER - 1; k >= 0; --k) {
+    const uint32_t st = min(local[k], next);  // empty bin: inherits the next start
+    mx = max(mx, next - st);
+    run_start[tid * PER + k] = st;
+    next = st;
+  }
+  atomicMax(&s_max, mx);
+  if (tid == 0) run_start[JOINT_BINS] = n;
+  __syncthreads();
   if (tid == 0) {
     ctl->max_run = s_max;
-    if (s_max <= FIN_MAX) {
-      ctl->mode = MODE_HYBRID;
-      hplan->active[0] = hplan->active[1] = 1;
-      hplan->shift[0] = ctl->shiftA;
-      hplan->shift[1] = ctl->shiftB;
-      hplan->first = 0;   // pass A reads the raw column and writes buffer 0
-      hplan->last = -1;   // neither pass writes the outputs: the finisher does
-      hplan->src_sel[1] = 0;  // pass B reads buffer 0, writes buffer 1
-    }
+    ctl->mode = s_max <= FIN_MAX ? MODE_HYBRID : MODE_LSD;
   }
 }
 
@@ -894,7 +925,7 @@ static TempLayout temp_layout(size_t n, int npass) {
   L.off_ctl = o;        o = align_up(o + sizeof(SortCtl), 256);
   L.off_hist = o;       o = align_up(o + sizeof(uint32_t) * MAX_PASSES * RADIX, 256);
   L.off_hbase = o;      o = align_up(o + sizeof(uint32_t) * 2 * RADIX, 256);
-  L.off_joint = o;      o = align_up(o + sizeof(uint32_t) * JOINT_BINS, 256);
+  L.off_joint = o;      o = align_up(o + sizeof(uint32_t) * 2 * RADIX, 256);  // the two digit histograms
   L.off_runs = o;       o = align_up(o + sizeof(uint32_t) * (JOINT_BINS + 1), 256);
   L.off_lookback = o;   o = align_up(o + sizeof(uint32_t) * (size_t)npass * L.tiles * RADIX, 256);
   L.off_hlookback = o;  o = align_up(o + sizeof(uint32_t) * (size_t)2 * L.tiles * RADIX, 256);
@@ -981,7 +1012,7 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
   SortCtl* ctl = (SortCtl*)(base + L.off_ctl);
   uint32_t* ghist = (uint32_t*)(base + L.off_hist);
   uint32_t* hbase = (uint32_t*)(base + L.off_hbase);
-  uint32_t* joint = (uint32_t*)(base + L.off_joint);
+  uint32_t* hist2 = (uint32_t*)(base + L.off_joint);
   uint32_t* run_start = (uint32_t*)(base + L.off_runs);
   uint32_t* lookback = (uint32_t*)(base + L.off_lookback);
   uint32_t* hlookback = (uint32_t*)(base + L.off_hlookback);
@@ -1030,14 +1061,16 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
     B200X_LAUNCH_CHECK("analyze_kernel");
     hybrid_plan0_kernel<<<1, 1, 0, stream>>>(ctl, (uint32_t)n, g_hybrid_min_rows);
     B200X_LAUNCH_CHECK("hybrid_plan0_kernel");
+    B200X_CUDA(cudaMemsetAsync(run_start, 0xFF, sizeof(uint32_t) * (JOINT_BINS + 1), stream));
     prof_begin(stream, PROF_JOINT);
-    joint_hist_kernel<<<blocks, 512, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, ctl, joint);
+    digit2_hist_kernel<<<blocks, 512, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, ctl, hist2);
     prof_end(stream);
-    B200X_LAUNCH_CHECK("joint_hist_kernel");
-    hybrid_plan1_kernel<<<1, 1024, 0, stream>>>(ctl, joint, run_start, hbase, hplan, (uint32_t)n);
+    B200X_LAUNCH_CHECK("digit2_hist_kernel");
+    hybrid_plan1_kernel<<<1, RADIX, 0, stream>>>(ctl, hist2, hbase, hplan, (uint32_t)n);
     B200X_LAUNCH_CHECK("hybrid_plan1_kernel");
     a.plan = hplan;
     a.ctl = ctl;
+    a.mark_runs = run_start;
     for (int p = 0; p < 2; ++p) {
       a.pass = p;
       a.gbase = hbase + p * RADIX;
@@ -1047,6 +1080,8 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
       prof_end(stream);
       B200X_LAUNCH_CHECK("onesweep_pass_kernel");
     }
+    runs_fill_kernel<<<1, 1024, 0, stream>>>(ctl, hplan, run_start, (uint32_t)n);
+    B200X_LAUNCH_CHECK("runs_fill_kernel");
     FinArgs f;
     f.kin = a.kbuf[1];
     f.vin = a.vbuf[1];
@@ -1083,6 +1118,7 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
   B200X_LAUNCH_CHECK("plan_kernel");
   a.plan = plan;
   a.ctl = nullptr;
+  a.mark_runs = nullptr;
   for (int p = 0; p < npass; ++p) {
     a.pass = p;
     a.gbase = ghist + p * RADIX;
