@@ -229,6 +229,14 @@ int b200x_finalize_groups(const void* sum, int value_type, const int64_t* counts
 /* out[g] = max(|min_in[g]|, |max_in[g]|), same type as the inputs (AbsMax, aggregate/_aggregate.py:323-357). */
 int b200x_absmax_groups(const void* min_in, const void* max_in, int value_type, size_t num_groups, void* out, void* stream);
 
+/* out[g] = q-quantile of group g's values by linear interpolation between the two nearest ranks,
+ * rounded to 5 decimals when it falls between two rows, exactly as the reference's `percentile`
+ * (Quantile, aggregate/_aggregate.py:360-431, finalize :406-417). `perm` must visit the rows ordered
+ * by (group key, value); group_starts are positions in that order. 0 <= q <= 1. out is float64. */
+int b200x_group_quantile(const uint32_t* group_starts, const uint32_t* num_groups, size_t max_groups,
+                         const uint32_t* perm, const void* values, int value_type, size_t n, double q, double* out,
+                         void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -424,3 +424,37 @@ def aggregate_dataset(blocks: Sequence[Table], key: str, aggs, boundaries: List[
         parts = sort_and_partition(blk, boundaries, [key], False)
         mapped.append([combine(p, key, aggs) if num_rows(p) else {} for p in parts])
     return [aggregate_combined_blocks([m[j] for m in mapped], key, aggs) for j in range(R)]
+
+
+# --------------------------------------------------------------------------------------
+# Quantile (aggregate/_aggregate.py:360-431). The reference's accumulator is the list of every
+# value of the group (merge = list concatenation, :378-398), so the result does not depend on how
+# rows were split into blocks; finalize is `percentile` (:406-417).
+# --------------------------------------------------------------------------------------
+def percentile(values: Sequence, q: float):
+    """_aggregate.py:406-417, step by step (Python floats, Python round)."""
+    if len(values) == 0:
+        return None
+    vals = sorted(values)
+    k = (len(vals) - 1) * q
+    f = math.floor(k)
+    c = math.ceil(k)
+    if f == c:
+        return vals[int(k)]
+    d0 = vals[int(f)] * (c - k)
+    d1 = vals[int(c)] * (k - f)
+    return round(d0 + d1, 5)
+
+
+def quantile_dataset(blocks: Sequence[Table], key: Optional[str], on: str, q: float = 0.5) -> Table:
+    """groupby(key).aggregate(Quantile(on, q)) over the whole dataset: keys ascending, one value per
+    group (Python int/float as the reference returns them). key=None: one global group."""
+    allp = concat([b for b in blocks if b and num_rows(b) > 0])
+    v = allp[on]
+    if key is None:
+        return {f"quantile({on})": np.array([percentile(v.tolist(), q)], dtype=object)}
+    order = np.argsort(allp[key], kind="stable")
+    ks, vs = allp[key][order], v[order]
+    starts, lens = _group_runs(ks)
+    out = [percentile(vs[s:s + ln].tolist(), q) for s, ln in zip(starts, lens)]
+    return {key: ks[starts], f"quantile({on})": np.array(out, dtype=object)}

@@ -13,6 +13,9 @@ selects outputs of the segmented-reduce kernel, and a partially combined block (
   sum/min/max    name                      column dtype
   mean           name (= sum), name::count
   std            name (= M2),  name::sum, name::count      (M2 about the partial's own mean)
+  quantile       (holistic) the accumulator is the list of every value, as in the reference: when a
+                 Quantile is among the aggregations the partial block is the pruned rows themselves
+                 (sorted by key) and every aggregation is evaluated at the final merge
 
 User-defined AggregateFn callables cannot run on the device and raise NotImplementedError.
 Nulls do not exist in the device block format, so `ignore_nulls` has no effect (has_data is
@@ -108,11 +111,25 @@ class AbsMax(_AggregateOnKeyBase):
         self._device_kind = "absmax"
 
 
+class Quantile(_AggregateOnKeyBase):
+    """q-quantile per group by linear interpolation, rounded to 5 decimals between rows
+    (_aggregate.py:360-431; the result column is float64)."""
+
+    def __init__(self, on: Optional[str] = None, q: float = 0.5, ignore_nulls: bool = True,
+                 alias_name: Optional[str] = None):
+        self._setup("quantile", on, alias_name, ignore_nulls)
+        self._q = q
+
+
+def _holistic(aggs: Sequence[AggregateFn]) -> bool:
+    return any(getattr(a, "_device_kind", None) == "quantile" for a in aggs)
+
+
 def _device_kind(agg: AggregateFn) -> str:
     kind = getattr(agg, "_device_kind", None)
     if kind is None:
         raise NotImplementedError(
-            "user-defined AggregateFn callables cannot run on device blocks; use Count/Sum/Min/Max/Mean/Std")
+            "user-defined AggregateFn callables cannot run on device blocks; use Count/Sum/Min/Max/Mean/Std/AbsMax/Quantile")
     return kind
 
 
@@ -174,6 +191,11 @@ def _reduce_partials(kind: str, agg: AggregateFn, name: str, src: DeviceBlock, s
 
         if kind == "count":
             return {name: counts()}
+        if kind == "quantile":
+            on = agg._key_fn
+            if ("qperm", on) not in cache:  # rows ordered by (keys, value): same group positions as `starts`
+                cache[("qperm", on)] = _argsort_keys(src, list(cache.get("keys", [])) + [on], want_codes=False)[0]
+            return {name: ops.group_quantile(starts, ng, G, cache[("qperm", on)], _value_column(src, on), n, agg._q)}
         if kind in ("sum", "min", "max"):
             return {name: smm(agg._key_fn)[("sum", "min", "max").index(kind)]}
         if kind == "absmax":
@@ -234,7 +256,7 @@ def _reduce_partials(kind: str, agg: AggregateFn, name: str, src: DeviceBlock, s
 
 
 def _finalize(kind: str, agg: AggregateFn, name: str, acc: Dict[str, torch.Tensor]) -> torch.Tensor:
-    if kind in ("count", "sum", "min", "max", "absmax"):
+    if kind in ("count", "sum", "min", "max", "absmax", "quantile"):
         return acc[name]
     if kind == "mean":
         return ops.finalize_groups(acc[name], acc[name + SEP + "count"], 0)
@@ -287,6 +309,15 @@ def aggregate_sorted(block: DeviceBlock, key, aggs: Sequence[AggregateFn], perm,
     keys = _key_list(key)
     dev = block.device
     names = resolved_names(aggs)
+    if not finalize and _holistic(aggs):
+        for agg in aggs:
+            if getattr(agg, "_key_fn", None) is not None:
+                _value_column(block, agg._key_fn)
+        if perm is None:
+            return block
+        from .block import DeviceBlockAccessor
+
+        return DeviceBlockAccessor(block).take(perm)
     if not keys:
         starts = torch.zeros(1, dtype=torch.int32, device=dev)
         ng = torch.ones(1, dtype=torch.int32, device=dev)
@@ -303,7 +334,7 @@ def aggregate_sorted(block: DeviceBlock, key, aggs: Sequence[AggregateFn], perm,
         first_rows = ops.gather(perm, starts[:G].contiguous()) if perm is not None else starts[:G].contiguous()
         for k in keys:
             cols[k] = ops.gather(_contig(block.columns[k]), first_rows)
-    cache: dict = {}
+    cache: dict = {"keys": keys}
     for agg, name in zip(aggs, names):
         kind = _device_kind(agg)
         acc = _reduce_partials(kind, agg, name, block, starts, ng, G, perm, n, raw=True, cache=cache)
@@ -335,6 +366,11 @@ def merge_combined_blocks(blocks: Sequence[DeviceBlock], key, aggs: Sequence[Agg
     n = allp.num_rows
     dev = allp.device
     names = resolved_names(aggs)
+    if _holistic(aggs):  # the partials are rows: aggregate them as data (stable by key: mapper order within a key)
+        perm = codes = None
+        if keys:
+            perm, codes = _argsort_keys(allp, keys, want_codes=len(keys) == 1)
+        return aggregate_sorted(allp, key, aggs, perm, codes, finalize=finalize, n=n)
     if not keys:
         perm = None
         starts = torch.zeros(1, dtype=torch.int32, device=dev)

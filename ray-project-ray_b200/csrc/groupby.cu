@@ -416,6 +416,39 @@ absmax_kernel(const void* __restrict__ mn, const void* __restrict__ mx, int vt, 
   }
 }
 
+// Quantile of each group by linear interpolation between the two nearest ranks. `perm` visits the
+// rows ordered by (group key, value), so a group's values are ascending inside [start, end).
+// The arithmetic is the reference's, step by step, without fused multiply-adds:
+// k = (m - 1) * q; f = floor(k); c = ceil(k); f == c ? v[f] : round(v[f] * (c - k) + v[c] * (k - f), 5)
+__global__ void __launch_bounds__(256)
+group_quantile_kernel(const uint32_t* __restrict__ group_starts, const uint32_t* __restrict__ num_groups_p,
+                      const uint32_t* __restrict__ perm, const void* __restrict__ values, int vt, uint64_t n, double q,
+                      double* __restrict__ out) {
+  const uint32_t G = *num_groups_p;
+  for (uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; g < G; g += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t s = group_starts[g];
+    const uint64_t e = (g + 1 < G) ? group_starts[g + 1] : n;
+    const uint64_t m = e - s;
+    const double k = __dmul_rn((double)(m - 1), q);
+    const double f = floor(k), c = ceil(k);
+    auto value_at = [&](uint64_t r) -> double {
+      const uint64_t row = perm ? (uint64_t)perm[s + r] : s + r;
+      return (vt == B200X_VAL_I64) ? (double)((const int64_t*)values)[row] : ((const double*)values)[row];
+    };
+    double r;
+    if (f == c) {
+      r = value_at((uint64_t)k);
+    } else {
+      const double d0 = __dmul_rn(value_at((uint64_t)f), __dsub_rn(c, k));
+      const double d1 = __dmul_rn(value_at((uint64_t)c), __dsub_rn(k, f));
+      r = __dadd_rn(d0, d1);
+      // round(x, 5): beyond 2^52 / 1e5 the scaled value is an integer already
+      if (fabs(r) < 4.0e10) r = __ddiv_rn(rint(__dmul_rn(r, 1.0e5)), 1.0e5);
+    }
+    out[g] = r;
+  }
+}
+
 static inline uint32_t tiles_of(size_t n) { return (uint32_t)((n + G_TILE - 1) / G_TILE); }
 
 template <typename VIn, typename T, bool CENTER>
@@ -587,5 +620,31 @@ extern "C" int b200x_absmax_groups(const void* min_in, const void* max_in, int v
   if (blocks > cap) blocks = cap;
   absmax_kernel<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream_>>>(min_in, max_in, value_type, num_groups, out);
   B200X_LAUNCH_CHECK("absmax_kernel");
+  return B200X_OK;
+}
+
+extern "C" int b200x_group_quantile(const uint32_t* group_starts, const uint32_t* num_groups, size_t max_groups,
+                                    const uint32_t* perm, const void* values, int value_type, size_t n, double q,
+                                    double* out, void* stream_) {
+  if (max_groups == 0 || n == 0) return B200X_OK;
+  if (group_starts == nullptr || num_groups == nullptr || values == nullptr || out == nullptr ||
+      (value_type != B200X_VAL_I64 && value_type != B200X_VAL_F64)) {
+    set_error("b200x_group_quantile: bad arguments");
+    return B200X_ERR_ARG;
+  }
+  if (!(q >= 0.0 && q <= 1.0)) {
+    set_error("b200x_group_quantile: q=%g outside [0, 1]", q);
+    return B200X_ERR_ARG;
+  }
+  if (n > 0xFFFFFFFFull) {
+    set_error("b200x_group_quantile: n=%zu exceeds 2^32-1", n);
+    return B200X_ERR_TOO_LARGE;
+  }
+  uint64_t blocks = (max_groups + 255) / 256;
+  const uint64_t cap = (uint64_t)sm_count() * 8;
+  if (blocks > cap) blocks = cap;
+  group_quantile_kernel<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream_>>>(group_starts, num_groups, perm, values,
+                                                                             value_type, n, q, out);
+  B200X_LAUNCH_CHECK("group_quantile_kernel");
   return B200X_OK;
 }

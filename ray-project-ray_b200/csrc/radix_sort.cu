@@ -526,6 +526,25 @@ __global__ void hybrid_plan0_kernel(SortCtl* __restrict__ ctl, uint32_t n, unsig
   }
 }
 
+constexpr uint32_t SAMPLE_EVERY = 64;
+
+// H2b: every 64th key counts its (B, A) bin - a cheap early warning for runs far beyond what the
+// finisher holds, so that heavily duplicated columns go to the LSD path before any pass is spent.
+__global__ void __launch_bounds__(256)
+sample_bins_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ perm_in, int kt, int desc, uint32_t n,
+                   const SortCtl* __restrict__ ctl, uint32_t* __restrict__ sampled /*[JOINT_BINS]*/) {
+  if (!ctl->candidate) return;
+  const uint32_t shiftA = ctl->shiftA;
+  const unsigned long long base = ctl->base;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  const uint64_t ns = n / SAMPLE_EVERY;
+  for (uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; s < ns; s += stride) {
+    const uint64_t i = s * SAMPLE_EVERY;
+    const uint64_t e = load_encode(raw, perm_in ? (size_t)perm_in[i] : (size_t)i, kt, desc != 0);
+    atomicAdd(&sampled[(uint32_t)((e - base) >> shiftA) & (JOINT_BINS - 1)], 1u);
+  }
+}
+
 // H3: histograms of the two global digits (A = bits [shiftA, shiftA+8), B = the 8 bits above) of
 // code - base. One read of the key column, two shared-memory atomics per key at full occupancy.
 // (A 65536-bin joint histogram - which would also give the run boundaries up front - cost 0.7 ms
@@ -582,13 +601,14 @@ constexpr uint32_t FIN_MAX = FIN_BIG_THREADS * FIN_IPT;
 // H4 (one block of RADIX threads): exclusive scans of the two digit histograms; arm the two passes
 // unless a digit bin is so full that some run must exceed what the finisher holds.
 __global__ void __launch_bounds__(RADIX)
-hybrid_plan1_kernel(SortCtl* __restrict__ ctl, const uint32_t* __restrict__ hist2, uint32_t* __restrict__ hbase /*[2][RADIX]*/,
-                    SortPlan* __restrict__ hplan, uint32_t n) {
+hybrid_plan1_kernel(SortCtl* __restrict__ ctl, const uint32_t* __restrict__ hist2, const uint32_t* __restrict__ sampled,
+                    uint32_t* __restrict__ hbase /*[2][RADIX]*/, SortPlan* __restrict__ hplan, uint32_t n) {
   __shared__ uint32_t warp_tot[RADIX / 32];
-  __shared__ uint32_t s_max;
+  __shared__ uint32_t s_max, s_smax;
   const int d = threadIdx.x;
   const unsigned lane = d & 31, w = d >> 5;
   if (d == 0) {
+    s_smax = 0;
     for (int p = 0; p < MAX_PASSES; ++p) {
       hplan->active[p] = 0;
       hplan->src_sel[p] = 0;
@@ -601,6 +621,11 @@ hybrid_plan1_kernel(SortCtl* __restrict__ ctl, const uint32_t* __restrict__ hist
   }
   if (!ctl->candidate) return;
   __syncthreads();
+  {
+    uint32_t m = 0;
+    for (int i = d; i < (int)JOINT_BINS; i += RADIX) m = max(m, sampled[i]);
+    atomicMax(&s_smax, m);
+  }
   for (int p = 0; p < 2; ++p) {
     const uint32_t c = hist2[p * RADIX + d];
     atomicMax(&s_max, c);
@@ -617,7 +642,10 @@ hybrid_plan1_kernel(SortCtl* __restrict__ ctl, const uint32_t* __restrict__ hist
     hbase[p * RADIX + d] = off + x - c;
     __syncthreads();
   }
-  if (d == 0 && (unsigned long long)s_max <= (unsigned long long)RADIX * FIN_MAX) {
+  // a sampled count of FIN_MAX / SAMPLE_EVERY is what the longest admissible run shows on average;
+  // 1.5 x that is > 4 sigma above it, so data that fits is not turned away
+  if (d == 0 && (unsigned long long)s_max <= (unsigned long long)RADIX * FIN_MAX &&
+      s_smax * SAMPLE_EVERY <= FIN_MAX + FIN_MAX / 2) {
     hplan->active[0] = hplan->active[1] = 1;
     hplan->shift[0] = ctl->shiftA;
     hplan->shift[1] = ctl->shiftB;
@@ -925,7 +953,7 @@ static TempLayout temp_layout(size_t n, int npass) {
   L.off_ctl = o;        o = align_up(o + sizeof(SortCtl), 256);
   L.off_hist = o;       o = align_up(o + sizeof(uint32_t) * MAX_PASSES * RADIX, 256);
   L.off_hbase = o;      o = align_up(o + sizeof(uint32_t) * 2 * RADIX, 256);
-  L.off_joint = o;      o = align_up(o + sizeof(uint32_t) * 2 * RADIX, 256);  // the two digit histograms
+  L.off_joint = o;      o = align_up(o + sizeof(uint32_t) * (2 * RADIX + JOINT_BINS), 256);  // digit histograms + sampled bins
   L.off_runs = o;       o = align_up(o + sizeof(uint32_t) * (JOINT_BINS + 1), 256);
   L.off_lookback = o;   o = align_up(o + sizeof(uint32_t) * (size_t)npass * L.tiles * RADIX, 256);
   L.off_hlookback = o;  o = align_up(o + sizeof(uint32_t) * (size_t)2 * L.tiles * RADIX, 256);
@@ -1062,11 +1090,19 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
     hybrid_plan0_kernel<<<1, 1, 0, stream>>>(ctl, (uint32_t)n, g_hybrid_min_rows);
     B200X_LAUNCH_CHECK("hybrid_plan0_kernel");
     B200X_CUDA(cudaMemsetAsync(run_start, 0xFF, sizeof(uint32_t) * (JOINT_BINS + 1), stream));
+    {
+      uint32_t sblocks = (uint32_t)((n / SAMPLE_EVERY + 255) / 256);
+      if (sblocks > (uint32_t)sms * 8) sblocks = (uint32_t)sms * 8;
+      if (sblocks == 0) sblocks = 1;
+      sample_bins_kernel<<<sblocks, 256, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, ctl,
+                                                      hist2 + 2 * RADIX);
+      B200X_LAUNCH_CHECK("sample_bins_kernel");
+    }
     prof_begin(stream, PROF_JOINT);
     digit2_hist_kernel<<<blocks, 512, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, ctl, hist2);
     prof_end(stream);
     B200X_LAUNCH_CHECK("digit2_hist_kernel");
-    hybrid_plan1_kernel<<<1, RADIX, 0, stream>>>(ctl, hist2, hbase, hplan, (uint32_t)n);
+    hybrid_plan1_kernel<<<1, RADIX, 0, stream>>>(ctl, hist2, hist2 + 2 * RADIX, hbase, hplan, (uint32_t)n);
     B200X_LAUNCH_CHECK("hybrid_plan1_kernel");
     a.plan = hplan;
     a.ctl = ctl;

@@ -335,6 +335,19 @@ def group_counts(starts: torch.Tensor, ng: torch.Tensor, num_groups: int, n: int
     return out
 
 
+def group_quantile(starts: torch.Tensor, ng: torch.Tensor, num_groups: int, perm: Optional[torch.Tensor],
+                   values: torch.Tensor, n: int, q: float) -> torch.Tensor:
+    """Per-group q-quantile (float64); `perm` visits rows ordered by (group key, value)."""
+    dev = _require_cuda(starts, ng, values)
+    out = torch.empty(num_groups, dtype=torch.float64, device=dev)
+    if num_groups and n:
+        with torch.cuda.device(dev):
+            _lib.call("b200x_group_quantile", starts.data_ptr(), ng.data_ptr(), num_groups,
+                      perm.data_ptr() if perm is not None else None, values.data_ptr(), value_type_of(values), n,
+                      float(q), out.data_ptr(), _stream(dev))
+    return out
+
+
 def finalize_groups(sums: torch.Tensor, counts: torch.Tensor, mode: int, ddof: int = 1) -> torch.Tensor:
     dev = _require_cuda(sums, counts)
     out = torch.empty(sums.numel(), dtype=torch.float64, device=dev)

@@ -43,6 +43,15 @@ def main():
     run("argsort i64 full-range (8 passes)", lambda: ops.argsort(kfull), n * (8 + 8 * 24))
     run("argsort i64 permutation (4 passes)", lambda: ops.argsort(kperm), n * (8 + 4 * 24))
     run("argsort i64 1M distinct (3 passes)", lambda: ops.argsort(k20, want_codes=True), n * (8 + 3 * 24))
+    heavy = torch.randint(0, 2**63 - 1, (2000,), dtype=torch.int64, device=dev, generator=g)[torch.randint(0, 2000, (n,), device=dev, generator=g)]
+    run("argsort i64 2000 heavy keys, wide range (LSD after sampled warning)", lambda: ops.argsort(heavy), n * (8 + 8 * 24))
+    del heavy
+    mid = torch.randint(0, 2**63 - 1, (20000,), dtype=torch.int64, device=dev, generator=g)[torch.randint(0, 20000, (n,), device=dev, generator=g)]
+    run("argsort i64 20000 keys x 5000 rows, wide range", lambda: ops.argsort(mid), n * (8 + 8 * 24))
+    del mid
+    f64 = torch.randn(n, dtype=torch.float64, device=dev, generator=g)
+    run("argsort f64 normal", lambda: ops.argsort(f64), n * (8 + 8 * 24))
+    del f64
     run("argsort i64 perm desc", lambda: ops.argsort(kperm, True), n * (8 + 4 * 24))
     perm, _, _ = ops.argsort(kperm)
     pay64 = torch.empty((n, 64), dtype=torch.uint8, device=dev)

@@ -36,3 +36,11 @@ def split_by_sizes(flat, sizes):
         out.append(flat[lo:lo + int(s)])
         lo += int(s)
     return out
+
+
+def quantile():
+    """Outputs of the reference's Quantile aggregation (golden/quantile_outputs.json, inputs included)."""
+    if "q" not in _cache:
+        with open(os.path.join(_DIR, "quantile_outputs.json")) as f:
+            _cache["q"] = json.load(f)
+    return _cache["q"]

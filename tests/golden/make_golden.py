@@ -7,7 +7,8 @@ an eager in-process fake so that BOTH of the reference's schedulers run as writt
 (SURVEY.md §8c). Nothing here is shipped or imported by the product; the outputs are committed
 so that tests can run on the GPU box, where /root/reference does not exist.
 
-    python tests/golden/make_golden.py
+    python tests/golden/make_golden.py            # everything
+    python tests/golden/make_golden.py quantile   # only quantile_outputs.json
 """
 import importlib
 import inspect
@@ -390,7 +391,71 @@ def run_all():
     print("wrote", len(arrays), "arrays;", os.path.getsize(os.path.join(OUT, "reference_outputs.npz")) // 1024, "KiB")
 
 
+def run_quantile(shim=None):
+    """Quantile goldens (aggregate/_aggregate.py:360-431) -> quantile_outputs.json (inputs included)."""
+    ray, rb, tc, PB = shim or install_shim()
+    from ray.data.block import BlockAccessor
+    from ray.data.context import DataContext
+    from ray.data.aggregate import Count, Quantile, Sum
+    agg_mod = importlib.import_module("ray.data._internal.planner.aggregate")
+
+    def bundles(tables):
+        return [rb.RefBundle([(Ref(t), BlockAccessor.for_block(t).get_metadata(None, None))], owns_blocks=True)
+                for t in tables]
+
+    def ctx():
+        return tc.TaskContext(task_idx=0, target_max_block_size=1 << 30,
+                              sub_progress_bar_dict={"Sort Sample": PB(), "Shuffle Map": PB(), "Shuffle Reduce": PB()})
+
+    def run(tables, key, aggs, push):
+        DataContext.get_current().use_push_based_shuffle = push
+        random.seed(777)
+        out, _ = agg_mod.generate_aggregate_fn(key, aggs)(bundles(tables), ctx())
+        cols = {}
+        for b in out:
+            t = ray.get(b.blocks[0][0])
+            if t.num_rows:
+                for c in t.column_names:
+                    cols.setdefault(c, []).extend(t[c].to_pylist())
+        return cols
+
+    rng = np.random.default_rng(20240602)
+    N, B, G = 2000, 4, 37
+    k = rng.integers(0, G, N, dtype=np.int64)
+    vi = rng.integers(-10**6, 10**6, N, dtype=np.int64)
+    vf = np.round(rng.standard_normal(N) * 1000, 3)
+    n = N // B
+    tables = [pa.table({"k": k[i * n:(i + 1) * n], "vi": vi[i * n:(i + 1) * n], "vf": vf[i * n:(i + 1) * n]})
+              for i in range(B)]
+    qs = [0.0, 0.1, 0.25, 0.5, 0.9, 0.99, 1.0]
+    gold = {"pyarrow": pa.__version__, "numpy": np.__version__, "k": k.tolist(), "vi": vi.tolist(), "vf": vf.tolist(),
+            "blocks": B, "qs": qs, "grouped": {}, "global": {}}
+    for push in (False, True):
+        aggs = [Quantile("vi", q=q, alias_name=f"qi{j}") for j, q in enumerate(qs)]
+        aggs += [Quantile("vf", q=q, alias_name=f"qf{j}") for j, q in enumerate(qs)]
+        aggs += [Count(), Sum("vi"), Quantile("vf")]
+        gold["grouped"]["push" if push else "pull"] = run(tables, "k", aggs, push)
+    aggs = [Quantile("vi", q=q, alias_name=f"qi{j}") for j, q in enumerate(qs)]
+    aggs += [Quantile("vf", q=q, alias_name=f"qf{j}") for j, q in enumerate(qs)]
+    gold["global"] = run(tables, None, aggs, False)
+    # the reference's own test data (tests/test_all_to_all.py:720-775): A = x % 3, B = x
+    xs = list(range(100))
+    random.seed(1)
+    random.shuffle(xs)
+    small = [pa.table({"A": [x % 3 for x in xs[i::4]], "B": xs[i::4]}) for i in range(4)]
+    gold["small_input"] = xs
+    gold["small_grouped"] = run(small, "A", [Count(), Quantile("B"), Quantile("B", q=0.9, alias_name="q9")], False)
+    gold["small_global"] = run(small, None, [Quantile("B")], False)
+    with open(os.path.join(OUT, "quantile_outputs.json"), "w") as fjson:
+        json.dump(gold, fjson, default=lambda o: o.item() if hasattr(o, "item") else str(o))
+    print("wrote quantile_outputs.json", os.path.getsize(os.path.join(OUT, "quantile_outputs.json")) // 1024, "KiB")
+
+
 if __name__ == "__main__":
     if not os.path.isdir(REF):
         sys.exit("needs /root/reference (build container only)")
-    run_all()
+    if sys.argv[1:] == ["quantile"]:
+        run_quantile()
+    else:
+        run_all()
+        run_quantile()

@@ -188,3 +188,27 @@ def test_feistel_is_a_bijection_with_inverse():
             assert np.array_equal(np.sort(p), np.arange(n))
             q = orc.feistel_permutation(n, seed, inverse=True)
             assert np.array_equal(q[p], np.arange(n))
+
+
+def test_quantile_restatement_equals_reference_outputs():
+    """Quantile (aggregate/_aggregate.py:360-431): the value at an exact rank, the interpolation rounded
+    to 5 decimals between ranks, equal to what the reference's code returned. (The reference's column type
+    is int64 or double depending on which groups share an output block; values are what is pinned.)"""
+    q = G.quantile()
+    k, vi, vf = np.array(q["k"], np.int64), np.array(q["vi"], np.int64), np.array(q["vf"], np.float64)
+    B = q["blocks"]
+    n = len(k) // B
+    blocks = [{"k": k[i * n:(i + 1) * n], "vi": vi[i * n:(i + 1) * n], "vf": vf[i * n:(i + 1) * n]} for i in range(B)]
+    assert q["grouped"]["pull"] == q["grouped"]["push"]
+    ref = q["grouped"]["pull"]
+    for j, qq in enumerate(q["qs"]):
+        for col, name in (("vi", f"qi{j}"), ("vf", f"qf{j}")):
+            got = orc.quantile_dataset(blocks, "k", col, qq)
+            assert list(got["k"]) == ref["k"]
+            assert list(got[f"quantile({col})"]) == ref[name]
+            assert list(orc.quantile_dataset(blocks, None, col, qq)[f"quantile({col})"]) == q["global"][name]
+    xs = q["small_input"]
+    small = [{"A": np.array([x % 3 for x in xs[i::4]]), "B": np.array(xs[i::4])} for i in range(4)]
+    assert list(orc.quantile_dataset(small, "A", "B")["quantile(B)"]) == q["small_grouped"]["quantile(B)"] == [49.5, 49, 50]
+    assert list(orc.quantile_dataset(small, "A", "B", 0.9)["quantile(B)"]) == q["small_grouped"]["q9"]
+    assert list(orc.quantile_dataset(small, None, "B")["quantile(B)"]) == q["small_global"]["quantile(B)"]

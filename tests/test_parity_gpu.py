@@ -373,3 +373,45 @@ def test_groupby_two_key_columns_and_absmax(sched, cuda_device):
     np.testing.assert_array_equal(out["max(f)"], want["f_max"].to_numpy())
     np.testing.assert_allclose(out["mean(f)"], want["f_mean"].to_numpy(), rtol=FLOAT_RTOL)
     assert ds.aggregate(AbsMax("v")) == {"abs_max(v)": int(np.abs(v).max())}
+
+
+@pytest.mark.parametrize("sched", ["fused", "pull", "push"])
+def test_quantile_equals_reference_outputs(sched, cuda_device):
+    """Quantile (aggregate/_aggregate.py:360-431) against what the reference's own code returned
+    (tests/golden/quantile_outputs.json) and its test data (tests/test_all_to_all.py:720-775)."""
+    from ray_project_ray_b200.aggregate import Quantile
+
+    _set_scheduler(sched)
+    q = G.quantile()
+    k, vi, vf = np.array(q["k"], np.int64), np.array(q["vi"], np.int64), np.array(q["vf"], np.float64)
+    ds = rd.from_numpy_columns({"k": k, "vi": vi, "vf": vf, "junk": np.arange(len(k))}, override_num_blocks=q["blocks"])
+    aggs = [Quantile("vi", q=qq, alias_name=f"qi{j}") for j, qq in enumerate(q["qs"])]
+    aggs += [Quantile("vf", q=qq, alias_name=f"qf{j}") for j, qq in enumerate(q["qs"])]
+    out = ds.groupby("k").aggregate(*aggs, Count(), Sum("vi"), Quantile("vf")).to_numpy()
+    ref = q["grouped"]["pull"]
+    assert list(out.keys()) == list(ref.keys())
+    np.testing.assert_array_equal(out["k"], ref["k"])
+    np.testing.assert_array_equal(out["count()"], ref["count()"])
+    np.testing.assert_array_equal(out["sum(vi)"], ref["sum(vi)"])
+    for name in ref:
+        if name.startswith("q"):
+            assert out[name].dtype == np.float64
+            np.testing.assert_allclose(out[name], np.array(ref[name], np.float64), rtol=1e-12, atol=0)
+    glob = ds.aggregate(*aggs)
+    for name, v in q["global"].items():
+        assert abs(glob[name] - v[0]) <= 1e-12 * abs(v[0])
+    xs = q["small_input"]
+    small = rd.from_items([{"A": x % 3, "B": x} for x in xs], override_num_blocks=4)
+    got = small.groupby("A").aggregate(Count(), Quantile("B"), Quantile("B", q=0.9, alias_name="q9")).to_numpy()
+    assert list(got["quantile(B)"]) == [49.5, 49.0, 50.0] and list(got["q9"]) == q["small_grouped"]["q9"]
+    assert small.aggregate(Quantile("B")) == {"quantile(B)": 49.5}
+    # one row per group, and a group spanning many blocks
+    one = rd.from_numpy_columns({"k": np.arange(1000), "v": np.arange(1000) * 1.5}, override_num_blocks=3)
+    np.testing.assert_array_equal(one.groupby("k").aggregate(Quantile("v", q=0.3)).to_numpy()["quantile(v)"],
+                                  np.arange(1000) * 1.5)
+    rng = np.random.default_rng(5)
+    v = rng.standard_normal(300_001)
+    big = rd.from_numpy_columns({"k": np.zeros(v.size, np.int64), "v": v}, override_num_blocks=8)
+    got = big.groupby("k").aggregate(Quantile("v", q=0.5), Quantile("v", q=0.123, alias_name="p")).to_numpy()
+    assert got["quantile(v)"][0] == np.sort(v)[150_000]
+    assert abs(got["p"][0] - orc.percentile(v.tolist(), 0.123)) <= 1e-12
