@@ -41,7 +41,7 @@ KERNELS = {
     0: ("onesweep_pass_kernel", 22.0, 26.0),         # HYBRID: pass A reads 8 writes 12, pass B reads 12 writes 12
     1: ("gather_rows_kernel<uint4>", 4 + 2 * PAYLOAD_BYTES, 197.6),  # index + read row + write row (64 B rows cost 128 B of DRAM reads)
     2: ("finish_runs_kernel", 12 + 4 + 8, 23.5),      # read pair, write row index + decoded key
-    3: ("joint_hist_kernel", 8.0, 8.0),               # read key column
+    3: ("digit2_hist_kernel", 8.0, 8.0),              # read key column
     6: ("hist_kernel", 8.0, None),
 }
 

@@ -95,7 +95,7 @@ int b200x_set_tuning(int key, long long value);
  * of a latency-critical stream loop that must not take cudaMalloc's implicit synchronisation,
  * or a foreign-function shim with no device allocator of its own. Such a caller still passes its
  * inputs and outputs; only the sort's scratch comes from a fixed array inside the library
- * (about 26 MiB that every GPU which loads libb200x.so keeps until the process exits).
+ * (about 27 MiB that every GPU which loads libb200x.so keeps until the process exits).
  *   - n is limited to 1,048,576 rows (2^20); larger n returns B200X_ERR_TOO_LARGE with a message.
  *   - Arguments are those of b200x_radix_argsort minus begin_bit/end_bit/temp/temp_bytes; results are identical.
  *   - The first call on each device looks up the array's device address and sets a kernel

@@ -49,9 +49,17 @@ struct SortPlan {
 //            most 65536 runs by those bits), then every run - a few thousand pairs - is finished
 //            in shared memory over the remaining low bits. 3 trips through HBM instead of up to 8.
 //            Chosen when there are enough rows, more than 16 varying bits and no run exceeds what
-//            one block can hold (spread-out keys: random ints, hashes, floats, timestamps, ids).
+//            one block can hold. The 65536 runs are cut either
+//              U: uniformly, bin = (code - smallest code) >> shiftA (random ints, hashes, ids), or
+//              T: through a 65536-entry table built from a sample when U overflows: the U bins become
+//                 coarse buckets; a bucket holding more than the target number of rows is split into
+//                 2^s bins by its next s bits, consecutive sparse buckets are merged into one bin, so
+//                 that every bin holds about the same number of rows (a piecewise-linear CDF: floats
+//                 from any smooth distribution, clustered timestamps, skewed ids).
 constexpr uint32_t MODE_LSD = 0, MODE_HYBRID = 1;
 constexpr uint32_t JOINT_BINS = 1u << 16;
+constexpr int KEY_FIELD = 48;  // T: pass A rewrites the key as [bin:16][bits below the bin, left-aligned:48]
+constexpr uint32_t TAB_MERGED = 31;  // table entry = bin << 5 | s; s = 31: the bucket shares its bin with neighbours
 
 struct SortCtl {
   unsigned long long max_code;   // largest code
@@ -63,8 +71,22 @@ struct SortCtl {
   uint32_t mode;
   uint32_t shiftA, shiftB;       // digit positions of the two global passes (low one first)
   uint32_t max_run;
-  uint32_t pad[7];
+  uint32_t tmode;                // 1: bins come from the table (T), 0: uniform cut (U)
+  uint32_t shiftC;               // T: coarse bucket = (code - base) >> shiftC (= U's shiftA, <= 48)
+  uint32_t pad[5];
 };
+
+// T: key -> [bin:16][remaining bits:48], order-preserving. A split bucket keeps the R = shiftC - s bits
+// below its bin exactly (R <= 48). A merged bin spans several buckets: the field gets the key's top 48
+// bits (monotone, not exact) and the finisher re-reads those few keys from the column.
+__device__ __forceinline__ uint64_t remap_key(uint64_t k, const uint32_t* __restrict__ tab, uint32_t shiftC) {
+  const uint32_t e = __ldg(tab + (uint32_t)(k >> shiftC));
+  const uint32_t sb = e & 31u;
+  const uint64_t hi = (uint64_t)(e >> 5) << KEY_FIELD;
+  if (sb == TAB_MERGED) return hi | (k >> 16);
+  const uint64_t rem = k & ((1ull << shiftC) - 1ull);
+  return hi + (rem << (KEY_FIELD - ((int)shiftC - (int)sb)));
+}
 
 // ---------------------------------------------------------------------------
 // Kernel 1: all-digit histogram of the encoded keys (one read of the key column)
@@ -238,7 +260,11 @@ struct PassSmem {
   static constexpr size_t bytes = (size_t)TILE * 8 + (size_t)TILE * 4 + (size_t)WARPS * RADIX * 2 + RADIX * 4 + 64;
 };
 
-template <int THREADS, int IPT, int MIN_BLOCKS>
+// WALK = false: one block per tile (fastest when the pass is active: blocks in different phases overlap).
+// WALK = true: as many blocks as are resident, each claiming tiles until none is left - launching it
+// for a pass that turns out inactive costs nothing, whereas ~20000 blocks that return at once cost
+// ~50 us per launch. The LSD passes, which idle whenever the device picks HYBRID, use WALK.
+template <int THREADS, int IPT, int MIN_BLOCKS, bool WALK>
 __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
 onesweep_pass_kernel(const PassArgs a) {
   constexpr int TILE = THREADS * IPT;
@@ -264,14 +290,17 @@ onesweep_pass_kernel(const PassArgs a) {
   const bool is_first = plan->first == a.pass;
   const bool is_last = plan->last == a.pass;
 
+  const uint32_t n = a.n;
+  const uint32_t num_tiles = (uint32_t)(((uint64_t)n + TILE - 1) / TILE);
+  do {
   // Tiles are handed out in launch order so that a tile only ever waits on
   // tiles that are already resident (no look-back deadlock).
   if (tid == 0) s_tile = atomicAdd(&plan->tile_counter[a.pass], 1u);
   for (int i = tid; i < WARPS * RADIX / 2; i += THREADS) ((uint32_t*)whist)[i] = 0;
   __syncthreads();
   const uint32_t tile = s_tile;
+  if (WALK && tile >= num_tiles) break;
   const uint64_t tile_base = (uint64_t)tile * TILE;
-  const uint32_t n = a.n;
   const uint32_t n_valid = (uint32_t)min((uint64_t)TILE, (uint64_t)n - tile_base);
 
   // ---- load: warp-striped, item j of lane l = tile_base + warp*32*IPT + j*32 + l
@@ -442,6 +471,8 @@ onesweep_pass_kernel(const PassArgs a) {
       }
     }
   }
+  if (WALK) __syncthreads();  // shared memory is rewritten by the next tile
+  } while (WALK);
 }
 
 // ---------------------------------------------------------------------------
@@ -527,22 +558,203 @@ __global__ void hybrid_plan0_kernel(SortCtl* __restrict__ ctl, uint32_t n, unsig
 }
 
 constexpr uint32_t SAMPLE_EVERY = 64;
+constexpr uint32_t FIN_IPT = 8;
+// finisher block sizes: runs <= 2048 / <= 4096 / <= 8192 pairs
+constexpr uint32_t FIN_SMALL_THREADS = 256, FIN_BIG_THREADS = 512, FIN_HUGE_THREADS = 1024;
+constexpr uint32_t FIN_MAX = FIN_HUGE_THREADS * FIN_IPT;
+// a sampled count of FIN_MAX / SAMPLE_EVERY is what the longest admissible run shows on average; allowing
+// 1.25 x that (2.8 sigma) keeps data that fits from being turned away
+constexpr uint32_t SAMPLED_LIMIT = (FIN_MAX + FIN_MAX / 4) / SAMPLE_EVERY;
+// U is kept while its longest sampled run stays within what the 512-thread finisher holds
+constexpr uint32_t SAMPLED_LIMIT_U = (FIN_BIG_THREADS * FIN_IPT + FIN_BIG_THREADS * FIN_IPT / 2) / SAMPLE_EVERY;
 
-// H2b: every 64th key counts its (B, A) bin - a cheap early warning for runs far beyond what the
-// finisher holds, so that heavily duplicated columns go to the LSD path before any pass is spent.
+// H2b: every 64th key counts its bin - a cheap early warning for runs far beyond what the finisher
+// holds. First call (which = 0): U bins; the counts also serve as the coarse histogram the T table is
+// built from if U fails. Second call (which = 1, only if T was chosen): T bins.
 __global__ void __launch_bounds__(256)
 sample_bins_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ perm_in, int kt, int desc, uint32_t n,
-                   const SortCtl* __restrict__ ctl, uint32_t* __restrict__ sampled /*[JOINT_BINS]*/) {
+                   const SortCtl* __restrict__ ctl, int which, uint32_t* __restrict__ sampled /*[JOINT_BINS]*/,
+                   const uint32_t* __restrict__ tab) {
   if (!ctl->candidate) return;
-  const uint32_t shiftA = ctl->shiftA;
+  if (which == 1 && !ctl->tmode) return;
+  const uint32_t shiftA = ctl->shiftA, shiftC = ctl->shiftC;
   const unsigned long long base = ctl->base;
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   const uint64_t ns = n / SAMPLE_EVERY;
   for (uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; s < ns; s += stride) {
     const uint64_t i = s * SAMPLE_EVERY;
-    const uint64_t e = load_encode(raw, perm_in ? (size_t)perm_in[i] : (size_t)i, kt, desc != 0);
-    atomicAdd(&sampled[(uint32_t)((e - base) >> shiftA) & (JOINT_BINS - 1)], 1u);
+    uint64_t k = load_encode(raw, perm_in ? (size_t)perm_in[i] : (size_t)i, kt, desc != 0) - base;
+    if (which == 1) k = remap_key(k, tab, shiftC);
+    atomicAdd(&sampled[(uint32_t)(k >> shiftA) & (JOINT_BINS - 1)], 1u);
   }
+}
+
+// H2c (one block of 1024, 64 consecutive buckets per thread): keep U if its sample looks fine;
+// otherwise build the T table from the sampled U bins. A bucket with more than `target` rows gets
+// 2^s bins, s = ceil(log2(rows / target)); the others are merged, in order, into bins of about
+// target / 2 rows (a new bin starts after a split bucket and whenever the running row count of
+// sparse buckets crosses a multiple of target / 2). target = the smallest value, searched in steps
+// of 2^(1/4), for which all bins together number <= 65536.
+__global__ void __launch_bounds__(1024)
+hybrid_planT_kernel(SortCtl* __restrict__ ctl, const uint32_t* __restrict__ sampled, uint32_t* __restrict__ tab,
+                    uint32_t n) {
+  if (!ctl->candidate) return;
+  __shared__ uint32_t s_red[32];
+  __shared__ uint32_t s_val;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  constexpr int PER = JOINT_BINS / 1024;
+  constexpr uint32_t DENSE = 0x80000000u;
+  const uint32_t* mine = sampled + tid * PER;
+  auto block_sum = [&](uint32_t v) -> uint32_t {
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if (lane == 0) s_red[w] = v;
+    __syncthreads();
+    uint32_t t = 0;
+    for (int k = 0; k < 32; ++k) t += s_red[k];
+    return t;
+  };
+  auto block_excl_scan = [&](uint32_t v) -> uint32_t {
+    uint32_t x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= (uint32_t)o) x += y;
+    }
+    __syncthreads();
+    if (lane == 31) s_red[w] = x;
+    __syncthreads();
+    uint32_t off = x - v;
+    for (uint32_t k = 0; k < w; ++k) off += s_red[k];
+    return off;
+  };
+  {
+    uint32_t m = 0;
+#pragma unroll 8
+    for (uint32_t i = tid; i < JOINT_BINS; i += 1024) m = max(m, sampled[i]);
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (lane == 0) s_red[w] = m;
+    __syncthreads();
+    if (tid == 0) {
+      uint32_t t = 0;
+      for (int k = 0; k < 32; ++k) t = max(t, s_red[k]);
+      s_val = t;
+    }
+    __syncthreads();
+    if (s_val <= SAMPLED_LIMIT_U) return;  // U (tmode stays 0)
+  }
+  const uint32_t shiftC = ctl->shiftA;  // the U bins are the coarse buckets
+  const uint32_t smax = min(16u, shiftC);
+  // Bucket sizes in quarter-octaves above T0 = n / 65536: Q = ceil(4 log2(rows / T0)), 0 if rows <= T0.
+  // With target = T0 * 2^(t/4) a bucket is split iff Q > t, into 2^s bins, s = ceil((Q - t) / 4).
+  const float T0 = fmaxf((float)n / (float)JOINT_BINS, 64.0f);
+  auto q_of = [&](uint32_t samples) -> int {
+    const float r = (float)samples * (float)SAMPLE_EVERY;
+    if (!(r > T0)) return 0;
+    return min((int)ceilf(4.0f * log2f(r / T0)), 127);
+  };
+  auto bits_for = [&](int Q, int t) -> uint32_t { return min((uint32_t)((Q - t + 3) / 4), smax); };  // Q > t
+  __shared__ uint32_t s_cnt[128], s_rows[128];
+  __shared__ int s_t;
+  if (tid < 128) s_cnt[tid] = s_rows[tid] = 0;
+  if (tid == 0) s_t = 1 << 30;
+  __syncthreads();
+  for (int q = 0; q < PER; ++q) {
+    const uint32_t c = mine[q];
+    if (c) {
+      const int Q = q_of(c);
+      atomicAdd(&s_cnt[Q], 1u);
+      atomicAdd(&s_rows[Q], c);
+    }
+  }
+  __syncthreads();
+  constexpr int T_STEPS = 48;
+  if (tid < T_STEPS) {
+    const int t = (int)tid;
+    const float target_t = T0 * exp2f(0.25f * (float)t);
+    float bins = 2.0f, sparse = 0.0f;
+    for (int Q = 0; Q < 128; ++Q) {
+      if (Q > t) bins += (float)s_cnt[Q] * (float)((1u << bits_for(Q, t)) + 1u);  // + 1: a split bucket ends a merged run
+      else sparse += (float)s_rows[Q];
+    }
+    bins += sparse * (float)SAMPLE_EVERY / (0.5f * target_t);
+    // a merged bin holds < 1.5 x target rows, a split one about target (the density varies little inside a bucket)
+    if (bins <= (float)JOINT_BINS && target_t * 1.75f <= (float)FIN_MAX) atomicMin(&s_t, t);
+  }
+  __syncthreads();
+  const int t_sel = s_t;
+  if (t_sel >= T_STEPS) {
+    if (tid == 0) ctl->candidate = 0;
+    return;
+  }
+  const float target = T0 * exp2f(0.25f * (float)t_sel);
+  const float quantum = 0.5f * target;
+  // interim entries: DENSE | s for split buckets, the quantum index of the running sparse row count otherwise
+  uint32_t my_sparse = 0;
+  for (int q = 0; q < PER; ++q) {
+    if (!(q_of(mine[q]) > t_sel)) my_sparse += mine[q];
+  }
+  uint32_t running = block_excl_scan(my_sparse);
+  for (int q = 0; q < PER; ++q) {
+    const int Q = q_of(mine[q]);
+    if (Q > t_sel) {
+      tab[tid * PER + q] = DENSE | bits_for(Q, t_sel);
+    } else {
+      tab[tid * PER + q] = (uint32_t)((float)running * (float)SAMPLE_EVERY / quantum);
+      running += mine[q];
+    }
+  }
+  __syncthreads();
+  const uint32_t prev0 = tid == 0 ? DENSE : tab[tid * PER - 1];
+  uint32_t cnt = 0, prev = prev0;
+  for (int q = 0; q < PER; ++q) {
+    const uint32_t e = tab[tid * PER + q];
+    if (e & DENSE) cnt += 1u << (e & 31u);
+    else cnt += ((prev & DENSE) || prev != e) ? 1u : 0u;
+    prev = e;
+  }
+  uint32_t run = block_excl_scan(cnt);  // (its barriers also order the reads above before the writes below)
+  const uint32_t total = block_sum(cnt);
+  if (total > JOINT_BINS) {
+    if (tid == 0) ctl->candidate = 0;
+    return;
+  }
+  prev = prev0;
+  for (int q = 0; q < PER; ++q) {
+    const uint32_t e = tab[tid * PER + q];
+    if (e & DENSE) {
+      tab[tid * PER + q] = (run << 5) | (e & 31u);
+      run += 1u << (e & 31u);
+    } else {
+      if ((prev & DENSE) || prev != e) ++run;
+      tab[tid * PER + q] = ((run - 1u) << 5) | TAB_MERGED;
+    }
+    prev = e;
+  }
+  if (tid == 0) {
+    ctl->tmode = 1;
+    ctl->shiftC = shiftC;
+    ctl->shiftA = (uint32_t)KEY_FIELD;
+    ctl->shiftB = (uint32_t)KEY_FIELD + RADIX_BITS;
+  }
+}
+
+// H2d (one block of 1024): T only - the sampled T bins must look admissible before a full pass is spent on them.
+__global__ void __launch_bounds__(1024)
+hybrid_checkT_kernel(SortCtl* __restrict__ ctl, const uint32_t* __restrict__ sampledT) {
+  if (!ctl->candidate || !ctl->tmode) return;
+  __shared__ uint32_t s_m;
+  if (threadIdx.x == 0) s_m = 0;
+  __syncthreads();
+  uint32_t m = 0;
+  for (uint32_t i = threadIdx.x; i < JOINT_BINS; i += 1024) m = max(m, sampledT[i]);
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0) atomicMax(&s_m, m);
+  __syncthreads();
+  if (threadIdx.x == 0 && s_m > SAMPLED_LIMIT) ctl->candidate = 0;
 }
 
 // H3: histograms of the two global digits (A = bits [shiftA, shiftA+8), B = the 8 bits above) of
@@ -550,14 +762,19 @@ sample_bins_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ pe
 // (A 65536-bin joint histogram - which would also give the run boundaries up front - cost 0.7 ms
 // per 100 M keys with global atomics and 1.6 ms with a 128 KB shared-memory table; the boundaries
 // are instead marked by pass B as it writes, see mark_runs.)
-__global__ void __launch_bounds__(512)
+// TMODE: the keys go through the bucket table first, and the rewritten keys and their row numbers
+// are stored (kout, vout) for pass A to read instead of the column. Both variants are launched; the
+// one that does not apply returns at once.
+template <bool TMODE>
+__global__ void __launch_bounds__(512, 2)
 digit2_hist_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ perm_in, int kt, int desc, uint32_t n,
-                   const SortCtl* __restrict__ ctl, uint32_t* __restrict__ hist2 /*[2][RADIX]*/) {
-  if (!ctl->candidate) return;
+                   const SortCtl* __restrict__ ctl, uint32_t* __restrict__ hist2 /*[2][RADIX]*/,
+                   const uint32_t* __restrict__ tab, uint64_t* __restrict__ kout, uint32_t* __restrict__ vout) {
+  if (!ctl->candidate || (ctl->tmode != 0) != TMODE) return;
   __shared__ uint32_t sh[2 * RADIX];
   for (int i = threadIdx.x; i < 2 * RADIX; i += blockDim.x) sh[i] = 0;
   __syncthreads();
-  const uint32_t shiftA = ctl->shiftA;
+  const uint32_t shiftA = ctl->shiftA, shiftC = ctl->shiftC;
   const unsigned long long base = ctl->base;
   const int width = key_type_bytes(kt);
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
@@ -565,25 +782,38 @@ digit2_hist_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ pe
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   for (; i + (U - 1) * stride < n; i += U * stride) {
     uint64_t c[U];
+    uint32_t src[U];
     if (perm_in) {
 #pragma unroll
-      for (int u = 0; u < U; ++u) c[u] = perm_in[i + u * stride];
-#pragma unroll
-      for (int u = 0; u < U; ++u) c[u] = load_raw_bits(raw, (size_t)c[u], width);
+      for (int u = 0; u < U; ++u) src[u] = perm_in[i + u * stride];
     } else {
 #pragma unroll
-      for (int u = 0; u < U; ++u) c[u] = load_raw_bits(raw, (size_t)(i + u * stride), width);
+      for (int u = 0; u < U; ++u) src[u] = (uint32_t)(i + u * stride);
     }
 #pragma unroll
+    for (int u = 0; u < U; ++u) c[u] = load_raw_bits(raw, (size_t)src[u], width);
+#pragma unroll
     for (int u = 0; u < U; ++u) {
-      const uint32_t bin = (uint32_t)((encode_bits(c[u], kt, desc != 0) - base) >> shiftA) & (JOINT_BINS - 1);
+      uint64_t k = encode_bits(c[u], kt, desc != 0) - base;
+      if (TMODE) {
+        k = remap_key(k, tab, shiftC);
+        kout[i + u * stride] = k;
+        vout[i + u * stride] = src[u];
+      }
+      const uint32_t bin = (uint32_t)(k >> shiftA) & (JOINT_BINS - 1);
       atomicAdd(&sh[bin & 255u], 1u);
       atomicAdd(&sh[RADIX + (bin >> 8)], 1u);
     }
   }
   for (; i < n; i += stride) {
-    const uint64_t e = load_encode(raw, perm_in ? (size_t)perm_in[i] : (size_t)i, kt, desc != 0);
-    const uint32_t bin = (uint32_t)((e - base) >> shiftA) & (JOINT_BINS - 1);
+    const uint32_t src = perm_in ? perm_in[i] : (uint32_t)i;
+    uint64_t k = load_encode(raw, (size_t)src, kt, desc != 0) - base;
+    if (TMODE) {
+      k = remap_key(k, tab, shiftC);
+      kout[i] = k;
+      vout[i] = src;
+    }
+    const uint32_t bin = (uint32_t)(k >> shiftA) & (JOINT_BINS - 1);
     atomicAdd(&sh[bin & 255u], 1u);
     atomicAdd(&sh[RADIX + (bin >> 8)], 1u);
   }
@@ -594,15 +824,12 @@ digit2_hist_kernel(const void* __restrict__ raw, const uint32_t* __restrict__ pe
   }
 }
 
-constexpr uint32_t FIN_IPT = 8;
-constexpr uint32_t FIN_SMALL_THREADS = 256, FIN_BIG_THREADS = 512;   // runs <= 2048 / <= 4096 pairs
-constexpr uint32_t FIN_MAX = FIN_BIG_THREADS * FIN_IPT;
-
 // H4 (one block of RADIX threads): exclusive scans of the two digit histograms; arm the two passes
 // unless a digit bin is so full that some run must exceed what the finisher holds.
 __global__ void __launch_bounds__(RADIX)
-hybrid_plan1_kernel(SortCtl* __restrict__ ctl, const uint32_t* __restrict__ hist2, const uint32_t* __restrict__ sampled,
-                    uint32_t* __restrict__ hbase /*[2][RADIX]*/, SortPlan* __restrict__ hplan, uint32_t n) {
+hybrid_plan1_kernel(SortCtl* __restrict__ ctl, const uint32_t* __restrict__ hist2, const uint32_t* __restrict__ sampledU,
+                    const uint32_t* __restrict__ sampledT, uint32_t* __restrict__ hbase /*[2][RADIX]*/,
+                    SortPlan* __restrict__ hplan, uint32_t n) {
   __shared__ uint32_t warp_tot[RADIX / 32];
   __shared__ uint32_t s_max, s_smax;
   const int d = threadIdx.x;
@@ -622,6 +849,7 @@ hybrid_plan1_kernel(SortCtl* __restrict__ ctl, const uint32_t* __restrict__ hist
   if (!ctl->candidate) return;
   __syncthreads();
   {
+    const uint32_t* sampled = ctl->tmode ? sampledT : sampledU;
     uint32_t m = 0;
     for (int i = d; i < (int)JOINT_BINS; i += RADIX) m = max(m, sampled[i]);
     atomicMax(&s_smax, m);
@@ -642,14 +870,12 @@ hybrid_plan1_kernel(SortCtl* __restrict__ ctl, const uint32_t* __restrict__ hist
     hbase[p * RADIX + d] = off + x - c;
     __syncthreads();
   }
-  // a sampled count of FIN_MAX / SAMPLE_EVERY is what the longest admissible run shows on average;
-  // 1.5 x that is > 4 sigma above it, so data that fits is not turned away
-  if (d == 0 && (unsigned long long)s_max <= (unsigned long long)RADIX * FIN_MAX &&
-      s_smax * SAMPLE_EVERY <= FIN_MAX + FIN_MAX / 2) {
+  if (d == 0 && (unsigned long long)s_max <= (unsigned long long)RADIX * FIN_MAX && s_smax <= SAMPLED_LIMIT) {
     hplan->active[0] = hplan->active[1] = 1;
     hplan->shift[0] = ctl->shiftA;
     hplan->shift[1] = ctl->shiftB;
-    hplan->first = 0;   // pass A reads the raw column and writes buffer 0
+    hplan->first = ctl->tmode ? -1 : 0;  // pass A reads the raw column (T: the rewritten keys in buffer 1), writes buffer 0
+    hplan->src_sel[0] = 1;
     hplan->last = -1;   // neither pass writes the outputs: the finisher does
     hplan->src_sel[1] = 0;  // pass B reads buffer 0, writes buffer 1
   }
@@ -662,42 +888,40 @@ __global__ void __launch_bounds__(1024)
 runs_fill_kernel(SortCtl* __restrict__ ctl, const SortPlan* __restrict__ hplan, uint32_t* __restrict__ run_start,
                  uint32_t n) {
   if (!hplan->active[1]) return;
-  __shared__ uint32_t s_min[32];
+  __shared__ uint32_t s_wmin[32];
   __shared__ uint32_t s_max;
-  const int tid = threadIdx.x;
-  const unsigned lane = tid & 31, w = tid >> 5;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   if (tid == 0) s_max = 0;
-  constexpr int PER = JOINT_BINS / 1024;  // 64 consecutive bins per thread
-  uint32_t local[PER];
+  // warp w owns bins [w * 2048, (w + 1) * 2048), 32 consecutive bins per step (coalesced)
+  constexpr uint32_t PER_WARP = JOINT_BINS / 32, STEPS = PER_WARP / 32;
+  uint32_t* mine = run_start + w * PER_WARP + lane;
   uint32_t mn = 0xFFFFFFFFu;
 #pragma unroll 8
-  for (int k = 0; k < PER; ++k) {
-    local[k] = run_start[tid * PER + k];
-    mn = min(mn, local[k]);
-  }
-  // suffix minimum over threads: x = min of mn over threads >= tid
-  uint32_t x = mn;
+  for (uint32_t it = 0; it < STEPS; ++it) mn = min(mn, mine[it * 32]);
 #pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    uint32_t y = __shfl_down_sync(0xffffffffu, x, o);
-    if (lane + o < 32) x = min(x, y);
-  }
-  if (lane == 0) s_min[w] = x;
+  for (int o = 16; o >= 1; o >>= 1) mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+  if (lane == 0) s_wmin[w] = mn;
   __syncthreads();
-  uint32_t right = n;  // min over all threads of later warps, n if none
-  for (unsigned k = w + 1; k < 32; ++k) right = min(right, s_min[k]);
-  uint32_t after = __shfl_down_sync(0xffffffffu, x, 1);  // suffix min of the threads after me in my warp
-  if (lane == 31) after = 0xFFFFFFFFu;
-  uint32_t next = min(min(after, right), n);  // start of the first non-empty run after my 64 bins
+  uint32_t carry = n;  // start of the first non-empty run after the bins still to be visited
+  for (uint32_t k = w + 1; k < 32; ++k) carry = min(carry, s_wmin[k]);
   uint32_t mx = 0;
-#pragma unroll 8
-  for (int k = PER - 1; k >= 0; --k) {
-    const uint32_t st = min(local[k], next);  // empty bin: inherits the next start
-    mx = max(mx, next - st);
-    run_start[tid * PER + k] = st;
-    next = st;
+  for (int it = (int)STEPS - 1; it >= 0; --it) {
+    uint32_t x = mine[it * 32];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t y = __shfl_down_sync(0xffffffffu, x, o);
+      if (lane + o < 32) x = min(x, y);
+    }
+    x = min(x, carry);  // an empty bin starts where the next run starts
+    uint32_t nxt = __shfl_down_sync(0xffffffffu, x, 1);
+    if (lane == 31) nxt = carry;
+    mx = max(mx, nxt - x);
+    mine[it * 32] = x;
+    carry = __shfl_sync(0xffffffffu, x, 0);
   }
-  atomicMax(&s_max, mx);
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if (lane == 0) atomicMax(&s_max, mx);
   if (tid == 0) run_start[JOINT_BINS] = n;
   __syncthreads();
   if (tid == 0) {
@@ -715,6 +939,8 @@ struct FinArgs {
   void* keys_out;
   const uint32_t* run_start;  // [65537]
   const SortCtl* ctl;
+  const uint32_t* tab;        // T: bucket table
+  const void* raw;            // T: the key column (re-read for buckets whose low bits did not fit the key field)
   int kt;
   int desc;
 };
@@ -838,90 +1064,180 @@ __device__ __forceinline__ void fin_lsd(uint64_t (&key)[FIN_IPT], uint32_t (&val
   }
 }
 
-// THREADS = 256 serves inputs whose longest run is <= 2048 pairs, THREADS = 512 the rest (<= 4096);
-// both are launched and the one that does not apply returns at once.
+// T: what a bin holds. j1 = the last bucket whose first bin is <= run. A split bucket: the run's keys agree
+// above R = shiftC - s bits. A merged bin (buckets j0..j1): its keys are re-read from the column and taken
+// relative to bucket j0.
+__device__ __noinline__ void fin_locate_run(const uint32_t* __restrict__ tab, int shiftC, uint32_t run,
+                                            uint32_t* s_bucket, int& R, unsigned long long& base, bool& reread) {
+  if (threadIdx.x == 0) {
+    uint32_t lo = 0, hi = JOINT_BINS - 1;
+    while (lo < hi) {
+      const uint32_t mid = (lo + hi + 1) >> 1;
+      if ((tab[mid] >> 5) <= run) lo = mid;
+      else hi = mid - 1;
+    }
+    const uint32_t j1 = lo, e = tab[j1];
+    uint32_t j0 = j1;
+    if ((e & 31u) == TAB_MERGED) {
+      lo = 0, hi = j1;
+      while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if ((tab[mid] >> 5) >= run) hi = mid;
+        else lo = mid + 1;
+      }
+      j0 = lo;
+    }
+    s_bucket[0] = j0;
+    s_bucket[1] = j1;
+    s_bucket[2] = e;
+  }
+  __syncthreads();
+  const uint32_t j0 = s_bucket[0], j1 = s_bucket[1], e = s_bucket[2];
+  if ((e & 31u) == TAB_MERGED) {
+    reread = true;
+    R = shiftC + (j1 > j0 ? 32 - __clz((int)(j1 - j0)) : 0);
+    base += (unsigned long long)j0 << shiftC;
+  } else {
+    R = shiftC - (int)(e & 31u);
+    base += ((unsigned long long)j1 << shiftC) | ((unsigned long long)(run - (e >> 5)) << R);
+  }
+}
+
+// Finish one run with a block of THREADS threads (m <= THREADS * FIN_IPT pairs starting at `start`).
+template <uint32_t THREADS>
+__device__ __forceinline__ void finish_one_run(const FinArgs& a, const SortCtl* ctl, FinSmem<THREADS>& sm,
+                                               uint32_t* s_bucket, uint32_t run, uint32_t start, uint32_t m) {
+  {
+    const uint32_t tid = threadIdx.x;
+    const bool tmode = ctl->tmode != 0;
+    const int shiftC = (int)ctl->shiftC;
+    int R = (int)ctl->shiftA;  // low bits still unsorted inside the run
+    unsigned long long base = ctl->base;
+    bool reread = false;
+    if (tmode) fin_locate_run(a.tab, shiftC, run, s_bucket, R, base, reread);
+    const uint32_t nit = (m + THREADS - 1) / THREADS;
+    const uint64_t* kin = a.kin + start;
+    const uint32_t* vin = a.vin + start;
+    uint64_t key[FIN_IPT];
+    uint32_t val[FIN_IPT];
+    // the pairs of the run; T: keys reduced to the R bits that vary inside the run
+    auto load_run = [&]() {
+      fin_load(key, val, nit, m, kin, vin);
+      if (tmode) {
+        const uint32_t wb = (tid >> 5) * 32 * nit + (tid & 31);
+#pragma unroll
+        for (uint32_t j = 0; j < FIN_IPT; ++j) {
+          if (j < nit && wb + j * 32 < m) {
+            if (reread) key[j] = load_encode(a.raw, (size_t)val[j], a.kt, a.desc != 0) - base;
+            else key[j] = (key[j] & ((1ull << KEY_FIELD) - 1ull)) >> (KEY_FIELD - R);
+          }
+        }
+      }
+    };
+    load_run();
+    if (tid == 0) sm.slow = 0;
+
+    // Sort by a window of the top 16 remaining bits only (two 8-bit rounds). Pairs that still tie on
+    // the window are rare for spread-out keys and form tiny groups; each element then finds its
+    // place inside its group by comparing the bits below the window with its neighbours in shared
+    // memory. (A single 8-bit round leaves groups of ~m/256 pairs and the neighbour scan then costs
+    // more than the second round: 1.73 vs 1.30 ms per 100 M pairs.) Groups longer than TIE_MAX
+    // (duplicate-heavy keys) send the run down the plain path: LSD over every remaining bit.
+    const int W = 2 * RADIX_BITS;
+    bool tie_repair = R > W;
+    if (tie_repair) fin_lsd<THREADS>(key, val, nit, R - W, R, sm);
+    else fin_lsd<THREADS>(key, val, nit, 0, max(R, 1), sm);  // (R = 0: equal keys, one round just stages them)
+    // (fin_lsd ends with a barrier: shared memory holds the pairs sorted by the window)
+    uint32_t fpos[FIN_IPT];
+    if (tie_repair) {
+      const int wshift = R - W;
+      const uint64_t lowmask = (1ull << wshift) - 1ull;
+#pragma unroll
+      for (uint32_t j = 0; j < FIN_IPT; ++j) {
+        const uint32_t i = tid + j * THREADS;
+        fpos[j] = i;
+        if (i < m) {
+          const uint64_t k = sm.keys[i];
+          const uint64_t win = k >> wshift, low = k & lowmask;
+          uint32_t gs = i, before = 0, steps = 0;
+          while (gs > 0 && steps <= TIE_MAX) {
+            const uint64_t o = sm.keys[gs - 1];
+            if ((o >> wshift) != win) break;
+            --gs;
+            ++steps;
+            before += ((o & lowmask) <= low) ? 1u : 0u;  // earlier element, not larger: stays ahead
+          }
+          uint32_t ge = i + 1, after_smaller = 0;
+          while (ge < m && steps <= TIE_MAX) {
+            const uint64_t o = sm.keys[ge];
+            if ((o >> wshift) != win) break;
+            after_smaller += ((o & lowmask) < low) ? 1u : 0u;  // later element, strictly smaller: moves ahead
+            ++ge;
+            ++steps;
+          }
+          if (steps > TIE_MAX) sm.slow = 1;
+          fpos[j] = gs + before + after_smaller;
+        }
+      }
+      __syncthreads();
+      if (sm.slow) {
+        load_run();
+        fin_lsd<THREADS>(key, val, nit, 0, R, sm);
+        tie_repair = false;
+      }
+    }
+#pragma unroll
+    for (uint32_t j = 0; j < FIN_IPT; ++j) {
+      const uint32_t i = tid + j * THREADS;
+      if (i < m) {
+        const uint32_t dst = start + (tie_repair ? fpos[j] : i);
+        const uint64_t k = sm.keys[i] + base;
+        a.perm_out[dst] = sm.vals[i];
+        if (a.codes_out) a.codes_out[dst] = k;
+        if (a.keys_out) store_decoded(a.keys_out, dst, k, a.kt, a.desc != 0);
+      }
+    }
+  }
+}
+
+// Block sizes by run length: 256 threads for runs <= 2048 pairs, 512 up to 4096, 1024 up to 8192.
+// The first two launch one block per run (a block whose run belongs to another size class returns
+// at once); the 1024-thread kernel, rarely needed, launches only as many blocks as are resident and
+// walks over the runs, so that launching it for nothing costs nothing. (Walking was tried for the
+// 512-thread kernel too: its idle launch costs 60 us, but walking - strided or with a run counter -
+// made a table-binned sort of 100 M doubles, where half of the rows are in such runs, 0.13-0.25 ms slower.)
+__device__ __forceinline__ uint32_t fin_class(uint32_t m) {
+  return m <= FIN_SMALL_THREADS * FIN_IPT ? FIN_SMALL_THREADS : m <= FIN_BIG_THREADS * FIN_IPT ? FIN_BIG_THREADS
+                                                                                                : FIN_HUGE_THREADS;
+}
+
 template <uint32_t THREADS>
 __global__ void __launch_bounds__(THREADS, 1024 / THREADS)
 finish_runs_kernel(const FinArgs a) {
   const SortCtl* ctl = a.ctl;
   if (ctl->mode != MODE_HYBRID) return;
-  const bool small_cfg = ctl->max_run <= FIN_SMALL_THREADS * FIN_IPT;
-  if (small_cfg != (THREADS == FIN_SMALL_THREADS)) return;
+  if (THREADS != FIN_SMALL_THREADS && ctl->max_run <= FIN_SMALL_THREADS * FIN_IPT) return;
   const uint32_t start = a.run_start[blockIdx.x];
   const uint32_t m = a.run_start[blockIdx.x + 1] - start;
-  if (m == 0) return;
+  if (m == 0 || fin_class(m) != THREADS) return;
   extern __shared__ __align__(16) unsigned char fin_raw[];
-  FinSmem<THREADS>& sm = *reinterpret_cast<FinSmem<THREADS>*>(fin_raw);
-  const uint32_t tid = threadIdx.x;
-  const int R = (int)ctl->shiftA;  // low bits still unsorted inside the run
-  const unsigned long long base = ctl->base;
-  const uint32_t nit = (m + THREADS - 1) / THREADS;
-  const uint64_t* kin = a.kin + start;
-  const uint32_t* vin = a.vin + start;
-  uint64_t key[FIN_IPT];
-  uint32_t val[FIN_IPT];
-  fin_load(key, val, nit, m, kin, vin);
-  if (tid == 0) sm.slow = 0;
+  __shared__ uint32_t s_bucket[3];
+  finish_one_run<THREADS>(a, ctl, *reinterpret_cast<FinSmem<THREADS>*>(fin_raw), s_bucket, blockIdx.x, start, m);
+}
 
-  // Sort by a window of the top 16 remaining bits only (two 8-bit rounds). Pairs that still tie on
-  // the window are rare for spread-out keys and form tiny groups; each element then finds its
-  // place inside its group by comparing the bits below the window with its neighbours in shared
-  // memory. (A single 8-bit round leaves groups of ~m/256 pairs and the neighbour scan then costs
-  // more than the second round: 1.73 vs 1.30 ms per 100 M pairs.) Groups longer than TIE_MAX
-  // (duplicate-heavy keys) send the run down the plain path: LSD over every remaining bit.
-  const int W = 2 * RADIX_BITS;
-  bool tie_repair = R > W;
-  if (tie_repair) fin_lsd<THREADS>(key, val, nit, R - W, R, sm);
-  else fin_lsd<THREADS>(key, val, nit, 0, R, sm);
-  // (fin_lsd ends with a barrier: shared memory holds the pairs sorted by the window)
-  uint32_t fpos[FIN_IPT];
-  if (tie_repair) {
-    const int wshift = R - W;
-    const uint64_t lowmask = (1ull << wshift) - 1ull;
-#pragma unroll
-    for (uint32_t j = 0; j < FIN_IPT; ++j) {
-      const uint32_t i = tid + j * THREADS;
-      fpos[j] = i;
-      if (i < m) {
-        const uint64_t k = sm.keys[i];
-        const uint64_t win = k >> wshift, low = k & lowmask;
-        uint32_t gs = i, before = 0, steps = 0;
-        while (gs > 0 && steps <= TIE_MAX) {
-          const uint64_t o = sm.keys[gs - 1];
-          if ((o >> wshift) != win) break;
-          --gs;
-          ++steps;
-          before += ((o & lowmask) <= low) ? 1u : 0u;  // earlier element, not larger: stays ahead
-        }
-        uint32_t ge = i + 1, after_smaller = 0;
-        while (ge < m && steps <= TIE_MAX) {
-          const uint64_t o = sm.keys[ge];
-          if ((o >> wshift) != win) break;
-          after_smaller += ((o & lowmask) < low) ? 1u : 0u;  // later element, strictly smaller: moves ahead
-          ++ge;
-          ++steps;
-        }
-        if (steps > TIE_MAX) sm.slow = 1;
-        fpos[j] = gs + before + after_smaller;
-      }
-    }
-    __syncthreads();
-    if (sm.slow) {
-      fin_load(key, val, nit, m, kin, vin);
-      fin_lsd<THREADS>(key, val, nit, 0, R, sm);
-      tie_repair = false;
-    }
-  }
-#pragma unroll
-  for (uint32_t j = 0; j < FIN_IPT; ++j) {
-    const uint32_t i = tid + j * THREADS;
-    if (i < m) {
-      const uint32_t dst = start + (tie_repair ? fpos[j] : i);
-      const uint64_t k = sm.keys[i] + base;
-      a.perm_out[dst] = sm.vals[i];
-      if (a.codes_out) a.codes_out[dst] = k;
-      if (a.keys_out) store_decoded(a.keys_out, dst, k, a.kt, a.desc != 0);
-    }
+template <uint32_t THREADS>
+__global__ void __launch_bounds__(THREADS, 1024 / THREADS)
+finish_runs_walk_kernel(const FinArgs a) {
+  const SortCtl* ctl = a.ctl;
+  if (ctl->mode != MODE_HYBRID || ctl->max_run <= (THREADS / 2) * FIN_IPT) return;  // no run of this size class
+  extern __shared__ __align__(16) unsigned char fin_raw[];
+  __shared__ uint32_t s_bucket[3];
+  for (uint32_t run = blockIdx.x; run < JOINT_BINS; run += gridDim.x) {
+    const uint32_t start = a.run_start[run];
+    const uint32_t m = a.run_start[run + 1] - start;
+    if (m == 0 || fin_class(m) != THREADS) continue;
+    __syncthreads();  // the previous run's shared memory is no longer read
+    finish_one_run<THREADS>(a, ctl, *reinterpret_cast<FinSmem<THREADS>*>(fin_raw), s_bucket, run, start, m);
   }
 }
 
@@ -938,6 +1254,17 @@ constexpr int PASS_IPT = B200X_PASS_IPT;
 constexpr int PASS_MINB = B200X_PASS_MINB;
 constexpr int PASS_TILE = PASS_THREADS * PASS_IPT;
 
+// blocks of the finisher that are resident on the GPU at once (it walks over the runs)
+template <uint32_t THREADS>
+static uint32_t fin_grid(size_t smem, int sms) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, finish_runs_walk_kernel<THREADS>, (int)THREADS, smem) !=
+          cudaSuccess || per_sm < 1)
+    per_sm = 1;
+  const uint32_t g = (uint32_t)per_sm * (uint32_t)sms;
+  return g > JOINT_BINS ? JOINT_BINS : g;
+}
+
 struct TempLayout {
   size_t off_plan, off_hplan, off_ctl, off_hist, off_hbase, off_joint, off_runs, off_lookback, off_hlookback;
   size_t off_k0, off_k1, off_v0, off_v1, total;
@@ -953,7 +1280,8 @@ static TempLayout temp_layout(size_t n, int npass) {
   L.off_ctl = o;        o = align_up(o + sizeof(SortCtl), 256);
   L.off_hist = o;       o = align_up(o + sizeof(uint32_t) * MAX_PASSES * RADIX, 256);
   L.off_hbase = o;      o = align_up(o + sizeof(uint32_t) * 2 * RADIX, 256);
-  L.off_joint = o;      o = align_up(o + sizeof(uint32_t) * (2 * RADIX + JOINT_BINS), 256);  // digit histograms + sampled bins
+  // digit histograms, sampled U bins, sampled T bins, T table
+  L.off_joint = o;      o = align_up(o + sizeof(uint32_t) * (2 * RADIX + 3 * JOINT_BINS), 256);
   L.off_runs = o;       o = align_up(o + sizeof(uint32_t) * (JOINT_BINS + 1), 256);
   L.off_lookback = o;   o = align_up(o + sizeof(uint32_t) * (size_t)npass * L.tiles * RADIX, 256);
   L.off_hlookback = o;  o = align_up(o + sizeof(uint32_t) * (size_t)2 * L.tiles * RADIX, 256);
@@ -1051,17 +1379,22 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
   const int sms = sm_count();
   constexpr size_t pass_smem = PassSmem<PASS_THREADS, PASS_IPT>::bytes;
   constexpr size_t fin_small_smem = sizeof(FinSmem<FIN_SMALL_THREADS>), fin_big_smem = sizeof(FinSmem<FIN_BIG_THREADS>);
+  constexpr size_t fin_huge_smem = sizeof(FinSmem<FIN_HUGE_THREADS>);
   static thread_local int smem_set_dev = -1;
   {
     int dev = 0;
     B200X_CUDA(cudaGetDevice(&dev));
     if (dev != smem_set_dev) {
-      B200X_CUDA(cudaFuncSetAttribute(onesweep_pass_kernel<PASS_THREADS, PASS_IPT, PASS_MINB>,
+      B200X_CUDA(cudaFuncSetAttribute(onesweep_pass_kernel<PASS_THREADS, PASS_IPT, PASS_MINB, false>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pass_smem));
+      B200X_CUDA(cudaFuncSetAttribute(onesweep_pass_kernel<PASS_THREADS, PASS_IPT, PASS_MINB, true>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pass_smem));
       B200X_CUDA(cudaFuncSetAttribute(finish_runs_kernel<FIN_SMALL_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)fin_small_smem));
       B200X_CUDA(cudaFuncSetAttribute(finish_runs_kernel<FIN_BIG_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)fin_big_smem));
+      B200X_CUDA(cudaFuncSetAttribute(finish_runs_walk_kernel<FIN_HUGE_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)fin_huge_smem));
       smem_set_dev = dev;
     }
   }
@@ -1090,19 +1423,33 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
     hybrid_plan0_kernel<<<1, 1, 0, stream>>>(ctl, (uint32_t)n, g_hybrid_min_rows);
     B200X_LAUNCH_CHECK("hybrid_plan0_kernel");
     B200X_CUDA(cudaMemsetAsync(run_start, 0xFF, sizeof(uint32_t) * (JOINT_BINS + 1), stream));
-    {
-      uint32_t sblocks = (uint32_t)((n / SAMPLE_EVERY + 255) / 256);
-      if (sblocks > (uint32_t)sms * 8) sblocks = (uint32_t)sms * 8;
-      if (sblocks == 0) sblocks = 1;
-      sample_bins_kernel<<<sblocks, 256, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, ctl,
-                                                      hist2 + 2 * RADIX);
-      B200X_LAUNCH_CHECK("sample_bins_kernel");
-    }
+    uint32_t* sampledU = hist2 + 2 * RADIX;
+    uint32_t* sampledT = sampledU + JOINT_BINS;
+    uint32_t* tab = sampledT + JOINT_BINS;
+    uint32_t sblocks = (uint32_t)((n / SAMPLE_EVERY + 255) / 256);
+    if (sblocks > (uint32_t)sms * 8) sblocks = (uint32_t)sms * 8;
+    if (sblocks == 0) sblocks = 1;
+    sample_bins_kernel<<<sblocks, 256, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, ctl, 0, sampledU,
+                                                    tab);
+    B200X_LAUNCH_CHECK("sample_bins_kernel");
+    hybrid_planT_kernel<<<1, 1024, 0, stream>>>(ctl, sampledU, tab, (uint32_t)n);
+    B200X_LAUNCH_CHECK("hybrid_planT_kernel");
+    sample_bins_kernel<<<sblocks, 256, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, ctl, 1, sampledT,
+                                                    tab);
+    B200X_LAUNCH_CHECK("sample_bins_kernel");
+    hybrid_checkT_kernel<<<1, 1024, 0, stream>>>(ctl, sampledT);
+    B200X_LAUNCH_CHECK("hybrid_checkT_kernel");
     prof_begin(stream, PROF_JOINT);
-    digit2_hist_kernel<<<blocks, 512, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, ctl, hist2);
+    digit2_hist_kernel<false><<<blocks, 512, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, ctl, hist2,
+                                                          tab, nullptr, nullptr);
     prof_end(stream);
     B200X_LAUNCH_CHECK("digit2_hist_kernel");
-    hybrid_plan1_kernel<<<1, RADIX, 0, stream>>>(ctl, hist2, hist2 + 2 * RADIX, hbase, hplan, (uint32_t)n);
+    prof_begin(stream, PROF_JOINT);
+    digit2_hist_kernel<true><<<blocks, 512, 0, stream>>>(keys, perm_in, key_type, descending, (uint32_t)n, ctl, hist2,
+                                                         tab, a.kbuf[1], a.vbuf[1]);
+    prof_end(stream);
+    B200X_LAUNCH_CHECK("digit2_hist_kernel");
+    hybrid_plan1_kernel<<<1, RADIX, 0, stream>>>(ctl, hist2, sampledU, sampledT, hbase, hplan, (uint32_t)n);
     B200X_LAUNCH_CHECK("hybrid_plan1_kernel");
     a.plan = hplan;
     a.ctl = ctl;
@@ -1112,7 +1459,7 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
       a.gbase = hbase + p * RADIX;
       a.lookback = hlookback + (size_t)p * L.tiles * RADIX;
       prof_begin(stream, PROF_PASS);
-      onesweep_pass_kernel<PASS_THREADS, PASS_IPT, PASS_MINB><<<L.tiles, PASS_THREADS, pass_smem, stream>>>(a);
+      onesweep_pass_kernel<PASS_THREADS, PASS_IPT, PASS_MINB, false><<<L.tiles, PASS_THREADS, pass_smem, stream>>>(a);
       prof_end(stream);
       B200X_LAUNCH_CHECK("onesweep_pass_kernel");
     }
@@ -1126,6 +1473,8 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
     f.keys_out = keys_out;
     f.run_start = run_start;
     f.ctl = ctl;
+    f.tab = tab;
+    f.raw = keys;
     f.kt = key_type;
     f.desc = descending;
     prof_begin(stream, PROF_FINISH);
@@ -1134,6 +1483,10 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
     B200X_LAUNCH_CHECK("finish_runs_kernel");
     prof_begin(stream, PROF_FINISH);
     finish_runs_kernel<FIN_BIG_THREADS><<<JOINT_BINS, FIN_BIG_THREADS, fin_big_smem, stream>>>(f);
+    prof_end(stream);
+    B200X_LAUNCH_CHECK("finish_runs_kernel");
+    prof_begin(stream, PROF_FINISH);
+    finish_runs_walk_kernel<FIN_HUGE_THREADS><<<fin_grid<FIN_HUGE_THREADS>(fin_huge_smem, sms), FIN_HUGE_THREADS, fin_huge_smem, stream>>>(f);
     prof_end(stream);
     B200X_LAUNCH_CHECK("finish_runs_kernel");
   }
@@ -1155,12 +1508,17 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
   a.plan = plan;
   a.ctl = nullptr;
   a.mark_runs = nullptr;
+  uint32_t walk_grid = (uint32_t)sms * PASS_MINB;
+  if (walk_grid > L.tiles) walk_grid = L.tiles;
   for (int p = 0; p < npass; ++p) {
     a.pass = p;
     a.gbase = ghist + p * RADIX;
     a.lookback = lookback + (size_t)p * L.tiles * RADIX;
     prof_begin(stream, PROF_PASS);
-    onesweep_pass_kernel<PASS_THREADS, PASS_IPT, PASS_MINB><<<L.tiles, PASS_THREADS, pass_smem, stream>>>(a);
+    if (try_hybrid)  // the device may well pick HYBRID: idle passes must be free
+      onesweep_pass_kernel<PASS_THREADS, PASS_IPT, PASS_MINB, true><<<walk_grid, PASS_THREADS, pass_smem, stream>>>(a);
+    else
+      onesweep_pass_kernel<PASS_THREADS, PASS_IPT, PASS_MINB, false><<<L.tiles, PASS_THREADS, pass_smem, stream>>>(a);
     prof_end(stream);
     B200X_LAUNCH_CHECK("onesweep_pass_kernel");
   }
@@ -1185,7 +1543,7 @@ extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descendin
 // without torch) that has no device allocator at all. For them the scratch lives inside the
 // library image: one file-scope __device__ array per GPU, sized for the largest input this
 // entry point accepts. The array exists on every GPU that loads libb200x.so, from module load
-// until the process exits (about 26 MiB per GPU).
+// until the process exits (about 27 MiB per GPU).
 //
 // The array's name is only a host-side stand-in; its device address is looked up once per
 // device with cudaGetSymbolAddress while that device is current, and that address is what the
@@ -1198,7 +1556,7 @@ constexpr size_t STATIC_SORT_MAX_ROWS = (size_t)1 << 20;  // 1,048,576 rows per 
 constexpr size_t STATIC_SORT_TILES = (STATIC_SORT_MAX_ROWS + PASS_TILE - 1) / PASS_TILE;
 // ping-pong pairs (24 B/row) + look-back words of 8 + 2 passes + plans, histograms, run table and alignment slack
 constexpr size_t STATIC_SORT_BYTES =
-    24 * STATIC_SORT_MAX_ROWS + (MAX_PASSES + 2) * STATIC_SORT_TILES * RADIX * sizeof(uint32_t) + 1024 * 1024;
+    24 * STATIC_SORT_MAX_ROWS + (MAX_PASSES + 2) * STATIC_SORT_TILES * RADIX * sizeof(uint32_t) + 2 * 1024 * 1024;
 
 static __device__ __align__(256) unsigned char g_static_sort_scratch[STATIC_SORT_BYTES];
 

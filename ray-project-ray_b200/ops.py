@@ -64,7 +64,7 @@ def _temp(nbytes: int, dev: torch.device) -> torch.Tensor:
 
 
 def argsort(keys: torch.Tensor, descending: bool = False, perm_in: Optional[torch.Tensor] = None,
-            want_codes: bool = False, want_keys: bool = False, end_bit: int = 0):
+            want_codes: bool = False, want_keys: bool = False, end_bit: int = 0, _debug: Optional[dict] = None):
     """Stable argsort of a 1-D key column.
 
     Returns (perm, codes, sorted_keys): perm is an int32 tensor whose bits are the uint32 row
@@ -90,6 +90,14 @@ def argsort(keys: torch.Tensor, descending: bool = False, perm_in: Optional[torc
         nb = ctypes.c_size_t(temp.numel())
         _lib.call("b200x_radix_argsort", _ptr(keys), kt, int(descending), _ptr(perm_in), _ptr(perm_out), _ptr(codes),
                   _ptr(skeys), n, 0, end_bit, temp.data_ptr(), ctypes.byref(nb), st)
+        if _debug is not None and n:
+            # tests only: which algorithm the device chose (SortCtl in csrc/radix_sort.cu, third 256-byte slot of temp)
+            import struct
+
+            raw = bytes(temp[512:512 + 56].cpu().numpy())
+            cand, mode, shift_a, shift_b, max_run, tmode, shift_c = struct.unpack_from("<7I", raw, 24)
+            _debug.update(candidate=cand, mode=("lsd", "hybrid")[mode], table=bool(tmode), max_run=max_run,
+                          shiftA=shift_a, shiftB=shift_b, shiftC=shift_c)
     return perm_out, codes, skeys
 
 

@@ -122,6 +122,54 @@ def test_argsort_hybrid_default_threshold_large(cuda_device):
         np.testing.assert_array_equal(_u32(perm), np.argsort(k, kind="stable").astype(np.uint32))
 
 
+@pytest.mark.parametrize("descending", [False, True])
+@pytest.mark.parametrize("kind", ["f64_normal", "f64_lognormal", "f64_mixture_tiny", "f32_normal", "i64_gauss_narrow",
+                                  "i64_gauss_wide", "i64_two_clusters", "f64_with_specials"])
+def test_argsort_table_binned_hybrid(cuda_device, force_hybrid, kind, descending):
+    """Keys from smooth but far-from-uniform distributions: the uniform 65536-way cut overflows, the
+    sampled bucket table takes over (HYBRID, table=True). Sparse coarse buckets whose low bits do not
+    fit the rewritten key (doubles: tiny magnitudes) are re-read from the column by the finisher."""
+    rng = np.random.default_rng(4321)
+    n = 3_000_000
+    if kind == "f64_normal":
+        k = rng.standard_normal(n)
+    elif kind == "f64_lognormal":
+        k = np.exp(rng.standard_normal(n) * 3)
+    elif kind == "f64_mixture_tiny":      # populated binades down to 1e-300: many single-bin (re-read) buckets
+        k = rng.standard_normal(n) * 10.0 ** rng.integers(-300, 3, n)
+    elif kind == "f32_normal":
+        k = rng.standard_normal(n).astype(np.float32)
+    elif kind == "i64_gauss_narrow":
+        k = (rng.standard_normal(n) * 2**30).astype(np.int64) + 10**15
+    elif kind == "i64_gauss_wide":
+        k = (rng.standard_normal(n) * 2**59).astype(np.int64)
+    elif kind == "i64_two_clusters":
+        k = np.where(rng.random(n) < 0.5, rng.integers(0, 1 << 40, n), (1 << 62) + rng.integers(0, 1 << 50, n)).astype(np.int64)
+    else:
+        k = rng.standard_normal(n)
+        k[rng.integers(0, n, 1000)] = np.nan
+        k[rng.integers(0, n, 1000)] = -0.0
+        k[rng.integers(0, n, 1000)] = 0.0
+        k[rng.integers(0, n, 10)] = np.inf
+        k[rng.integers(0, n, 10)] = -np.inf
+    want = orc.stable_argsort(k, descending)
+    dbg = {}
+    t = torch.from_numpy(k).to(cuda_device)
+    perm, codes, skeys = ops.argsort(t, descending, want_codes=True, want_keys=True, _debug=dbg)
+    np.testing.assert_array_equal(_u32(perm), want.astype(np.uint32))
+    np.testing.assert_array_equal(codes.cpu().numpy().view(np.uint64), orc.encode_keys(k, descending)[want])
+    if k.dtype.kind in "iu":
+        np.testing.assert_array_equal(skeys.cpu().numpy(), k[want])
+    assert dbg["mode"] == "hybrid", dbg
+    if kind in ("f64_normal", "f32_normal", "f64_with_specials"):
+        assert dbg["table"], dbg  # (the other kinds may still fit the uniform cut at this size)
+    # through a row indirection (second key of a multi-column sort)
+    p0 = torch.from_numpy(rng.permutation(n).astype(np.uint32).view(np.int32)).to(cuda_device)
+    perm2, _, _ = ops.argsort(t, descending, perm_in=p0)
+    src = _u32(p0)
+    np.testing.assert_array_equal(_u32(perm2), src[orc.stable_argsort(k[src], descending)])
+
+
 def test_argsort_uint64_and_uint16(cuda_device):
     rng = np.random.default_rng(5)
     n = 200_000
