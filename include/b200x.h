@@ -125,6 +125,14 @@ int b200x_iota_u32(uint32_t* out, size_t n, uint32_t start, void* stream);
  * This is the comparison pyarrow's sort applies (call sites as for b200x_radix_argsort). */
 int b200x_encode_keys(const void* keys, int key_type, int descending, size_t n, uint64_t* codes_out, void* stream);
 
+/* out[i] = bytes [offset, offset + width) of row i of a fixed-width byte-string column (row_bytes per row)
+ * as a big-endian unsigned integer, left-aligned in 64 bits and zero-padded; 1 <= width <= 8. Sorting a
+ * w-byte key = chained b200x_radix_argsort calls (key type U64) over its ceil(w / 8) chunks, last chunk
+ * first: the lexicographic order pyarrow.compute.sort_indices gives binary / fixed_size_binary keys
+ * (transform_pyarrow.py:17-21; gensort-style 10-byte keys). */
+int b200x_pack_key_bytes(const void* col, size_t row_bytes, size_t offset, int width, size_t n, uint64_t* out,
+                         void* stream);
+
 /* out_index[b] = lower bound (upper == 0) or upper bound (upper != 0) of bound_codes[b] in the
  * ascending array codes[0..n). Replaces find_partition_index / find_partitions:
  * _internal/util.py:719-758, :761-779 (numpy.searchsorted per boundary). */

@@ -81,6 +81,14 @@ def stable_argsort_multi(cols: Sequence[np.ndarray], descending: bool) -> np.nda
     return np.lexsort(list(reversed(codes)))  # lexsort: last key is primary; it is stable
 
 
+def stable_argsort_bytes(col: np.ndarray, descending: bool) -> np.ndarray:
+    """Row order of pyarrow's sort_indices on a fixed_size_binary / binary key (transform_pyarrow.py:17-21):
+    lexicographic by unsigned bytes, stable in both directions. `col` is [n, width] uint8."""
+    assert col.ndim == 2 and col.dtype == np.uint8
+    keys = [(255 - col[:, j]) if descending else col[:, j] for j in range(col.shape[1])]
+    return np.lexsort(list(reversed(keys)))  # last key is primary; stable
+
+
 def take(table: Table, idx: np.ndarray) -> Table:
     """transform_pyarrow.take_table (transform_pyarrow.py:24-50)."""
     return {k: v[idx] for k, v in table.items()}

@@ -119,6 +119,37 @@ extern "C" int b200x_encode_keys(const void* keys, int key_type, int descending,
   return B200X_OK;
 }
 
+// Fixed-width byte-string keys: bytes [offset, offset + width) of every row as one big-endian unsigned
+// integer, left-aligned in 64 bits (zero-padded on the right), so that comparing the integers compares
+// the byte strings lexicographically (the order pyarrow gives binary / fixed_size_binary columns).
+__global__ void __launch_bounds__(256)
+pack_key_bytes_kernel(const unsigned char* __restrict__ col, uint64_t row_bytes, uint32_t offset, uint32_t width,
+                      uint64_t n, uint64_t* __restrict__ out) {
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const unsigned char* p = col + i * row_bytes + offset;
+    uint64_t v = 0;
+#pragma unroll
+    for (uint32_t b = 0; b < 8; ++b) v = (v << 8) | (b < width ? (uint64_t)p[b] : 0ull);
+    out[i] = v;
+  }
+}
+
+extern "C" int b200x_pack_key_bytes(const void* col, size_t row_bytes, size_t offset, int width, size_t n,
+                                    uint64_t* out, void* stream_) {
+  if (n == 0) return B200X_OK;
+  if (col == nullptr || out == nullptr || width < 1 || width > 8 || offset + (size_t)width > row_bytes) {
+    set_error("b200x_pack_key_bytes: bad arguments (row_bytes=%zu offset=%zu width=%d)", row_bytes, offset, width);
+    return B200X_ERR_ARG;
+  }
+  uint64_t blocks = (n + 255) / 256;
+  const uint64_t cap = (uint64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  pack_key_bytes_kernel<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream_>>>((const unsigned char*)col, row_bytes,
+                                                                            (uint32_t)offset, (uint32_t)width, n, out);
+  B200X_LAUNCH_CHECK("pack_key_bytes_kernel");
+  return B200X_OK;
+}
+
 extern "C" int b200x_search_sorted_codes(const uint64_t* codes, size_t n, const uint64_t* bound_codes, int num_bounds,
                                          int upper, uint64_t* out_index, void* stream_) {
   if (num_bounds == 0) return B200X_OK;

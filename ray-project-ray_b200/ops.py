@@ -152,6 +152,25 @@ def encode_keys(keys: torch.Tensor, descending: bool = False) -> torch.Tensor:
     return out
 
 
+def pack_key_bytes(col: torch.Tensor, offset: int, width: int) -> torch.Tensor:
+    """Bytes [offset, offset + width) of every row of a [n, w] uint8 column as big-endian uint64 (left-aligned)."""
+    dev = _require_cuda(col)
+    if col.dim() != 2 or col.dtype != torch.uint8:
+        raise TypeError("byte-string keys are [n, width] uint8 columns")
+    n, w = col.shape
+    out = torch.empty(n, dtype=torch.uint64, device=dev)
+    if n:
+        with torch.cuda.device(dev):
+            _lib.call("b200x_pack_key_bytes", col.data_ptr(), w, offset, width, n, out.data_ptr(), _stream(dev))
+    return out
+
+
+def byte_key_chunks(col: torch.Tensor) -> List[torch.Tensor]:
+    """A [n, w] uint8 key column as ceil(w / 8) uint64 columns, most significant first."""
+    w = col.shape[1]
+    return [pack_key_bytes(col, off, min(8, w - off)) for off in range(0, w, 8)]
+
+
 def search_sorted_codes(codes: torch.Tensor, bound_codes: torch.Tensor, upper: bool) -> torch.Tensor:
     dev = _require_cuda(codes, bound_codes)
     out = torch.empty(bound_codes.numel(), dtype=torch.int64, device=dev)

@@ -11,8 +11,12 @@ from __future__ import annotations
 from functools import partial
 from typing import Any, Dict, List, Optional, Tuple
 
+import torch
+
+from . import ops
 from .aggregate import AggregateFn
 from .aggregate_task_spec import SortAggregateTaskSpec
+from .block import DeviceBlock, DeviceBlockAccessor, _contig
 from .context import DataContext
 from .interfaces import (AllToAllTransformFn, ExchangeTaskSpec, RefBundle, StatsDict, TaskContext, _NullProgressBar)
 from .schedulers import (AutoBoundaries, GpuExchangeScheduler, PullBasedShuffleTaskScheduler,
@@ -96,6 +100,67 @@ def _unified_schema(metadata):
     return None
 
 
+BYTE_KEY_SEP = "::be"
+
+
+def _byte_key_columns(blocks: List[DeviceBlock], sort_key: SortKey) -> List[str]:
+    """Key columns that are fixed-width byte strings ([n, w] uint8)."""
+    for b in blocks:
+        if b.columns:
+            return [k for k in sort_key.get_columns()
+                    if k in b.columns and b.columns[k].dim() == 2 and b.columns[k].dtype == torch.uint8]
+    return []
+
+
+def _expand_byte_keys(refs: List[RefBundle], sort_key: SortKey, byte_cols: List[str]):
+    """A w-byte string key sorts like the tuple of its big-endian 8-byte chunks: add those chunks as
+    uint64 columns `<name>::be<i>` and sort by them (every scheduler, the boundary sampling and the
+    multi-GPU exchange then see an ordinary multi-column integer key)."""
+    new_cols, derived = [], []
+    out_refs = []
+    for ref in refs:
+        pairs = []
+        for block, _ in ref.blocks:
+            if block.columns:
+                cols = dict(block.columns)
+                for k in byte_cols:
+                    for i, chunk in enumerate(ops.byte_key_chunks(_contig(block.columns[k]))):
+                        cols[f"{k}{BYTE_KEY_SEP}{i}"] = chunk
+                block = DeviceBlock(cols, num_rows=block.num_rows, device=block.device)
+            pairs.append((block, DeviceBlockAccessor(block).get_metadata(None, None)))
+        out_refs.append(RefBundle(pairs, owns_blocks=ref.owns_blocks))
+    width = {}
+    for ref in refs:
+        for block, _ in ref.blocks:
+            if block.columns:
+                width = {k: block.columns[k].shape[1] for k in byte_cols}
+                break
+        if width:
+            break
+    for k in sort_key.get_columns():
+        if k in byte_cols:
+            names = [f"{k}{BYTE_KEY_SEP}{i}" for i in range((width[k] + 7) // 8)]
+            new_cols += names
+            derived += names
+        else:
+            new_cols.append(k)
+    return out_refs, SortKey(new_cols, descending=[sort_key.get_descending()] * len(new_cols)), derived
+
+
+def _drop_columns(refs: List[RefBundle], names: List[str]) -> List[RefBundle]:
+    out = []
+    for ref in refs:
+        pairs = []
+        for block, meta in ref.blocks:
+            if block.columns:
+                block = DeviceBlock({k: v for k, v in block.columns.items() if k not in names},
+                                    num_rows=block.num_rows, device=block.device)
+                meta = DeviceBlockAccessor(block).get_metadata(None, exec_stats=meta.exec_stats)
+            pairs.append((block, meta))
+        out.append(RefBundle(pairs, owns_blocks=ref.owns_blocks))
+    return out
+
+
 def generate_sort_fn(sort_key: SortKey,
                      _debug_limit_shuffle_execution_to_num_blocks: Optional[int] = None) -> AllToAllTransformFn:
     """Sort blocks by the key column(s) (planner/sort.py:21-74)."""
@@ -105,6 +170,13 @@ def generate_sort_fn(sort_key: SortKey,
         if len(blocks) == 0:
             return (blocks, {})
         sort_key.validate_schema(_unified_schema(metadata))
+        byte_cols = _byte_key_columns(blocks, sort_key)
+        if byte_cols:
+            if sort_key.boundaries:
+                raise ValueError("user-specified boundaries are numeric; they cannot cut a byte-string key")
+            refs2, sort_key2, derived = _expand_byte_keys(refs, sort_key, byte_cols)
+            out, stats = fn(sort_key2, refs2, ctx)
+            return _drop_columns(out, derived), stats
         num_outputs = len(blocks)  # same number of output partitions as mappers
         if not sort_key.boundaries and DataContext.get_current().use_fused_device_exchange:
             boundaries = AutoBoundaries(num_outputs)  # the fused scheduler cuts the sorted result itself

@@ -212,3 +212,19 @@ def test_quantile_restatement_equals_reference_outputs():
     assert list(orc.quantile_dataset(small, "A", "B")["quantile(B)"]) == q["small_grouped"]["quantile(B)"] == [49.5, 49, 50]
     assert list(orc.quantile_dataset(small, "A", "B", 0.9)["quantile(B)"]) == q["small_grouped"]["q9"]
     assert list(orc.quantile_dataset(small, None, "B")["quantile(B)"]) == q["small_global"]["quantile(B)"]
+
+
+def test_byte_string_key_order_equals_pyarrow():
+    """fixed_size_binary keys: the oracle's order is what pyarrow.compute.sort_indices gives (asc, desc, ties)."""
+    import pyarrow as pa
+    import pyarrow.compute as pac
+
+    rng = np.random.default_rng(8)
+    for w in (1, 3, 8, 10, 17):
+        col = rng.integers(0, 4 if w > 3 else 256, (5000, w)).astype(np.uint8)   # few symbols: many ties and shared prefixes
+        col[rng.integers(0, 5000, 50)] = 0
+        col[rng.integers(0, 5000, 50)] = 255
+        arr = pa.FixedSizeBinaryArray.from_buffers(pa.binary(w), len(col), [None, pa.py_buffer(col.tobytes())])
+        for desc in (False, True):
+            want = pac.sort_indices(pa.table({"k": arr}), [("k", "descending" if desc else "ascending")]).to_numpy()
+            np.testing.assert_array_equal(orc.stable_argsort_bytes(col, desc), want)

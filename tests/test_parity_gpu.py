@@ -415,3 +415,44 @@ def test_quantile_equals_reference_outputs(sched, cuda_device):
     got = big.groupby("k").aggregate(Quantile("v", q=0.5), Quantile("v", q=0.123, alias_name="p")).to_numpy()
     assert got["quantile(v)"][0] == np.sort(v)[150_000]
     assert abs(got["p"][0] - orc.percentile(v.tolist(), 0.123)) <= 1e-12
+
+
+@pytest.mark.parametrize("sched", ["fused", "pull", "push"])
+@pytest.mark.parametrize("desc", [False, True])
+def test_sort_by_byte_string_key(sched, desc, cuda_device):
+    """Fixed-width byte-string keys (gensort's 10-byte key) sort in pyarrow's lexicographic
+    order, stably, through every scheduler; the packed chunk columns do not appear in the output."""
+    from ray_project_ray_b200 import ops
+
+    _set_scheduler(sched)
+    rng = np.random.default_rng(21)
+    n = 40_000
+    key = rng.integers(0, 256, (n, 10)).astype(np.uint8)
+    key[:, :8] = key[rng.integers(0, 300, n), :8]           # many ties on the first 8 bytes: the last 2 decide
+    key[rng.integers(0, n, 200)] = key[0]                    # exact duplicates: stability
+    payload = rng.integers(0, 256, (n, 90)).astype(np.uint8)
+    row = np.arange(n, dtype=np.int64)
+    ds = rd.from_numpy_columns({"key": key, "payload": payload, "row": row}, override_num_blocks=5)
+    out = ds.sort("key", descending=desc)
+    assert out.columns() == ["key", "payload", "row"] and out.num_blocks() == 5
+    got = out.to_numpy()
+    want = orc.stable_argsort_bytes(key, desc)
+    np.testing.assert_array_equal(got["row"], row[want])
+    np.testing.assert_array_equal(got["key"], key[want])
+    np.testing.assert_array_equal(got["payload"], payload[want])
+    # mixed key: an integer column first, the byte string second
+    a = rng.integers(0, 7, n, dtype=np.int64)
+    ds2 = rd.from_numpy_columns({"a": a, "key": key[:, :3].copy(), "row": row}, override_num_blocks=3)
+    got2 = ds2.sort(["a", "key"], descending=desc).to_numpy()
+    k3 = key[:, :3]
+    order = np.lexsort([(255 - k3[:, 2]) if desc else k3[:, 2], (255 - k3[:, 1]) if desc else k3[:, 1],
+                        (255 - k3[:, 0]) if desc else k3[:, 0], -a if desc else a])
+    np.testing.assert_array_equal(got2["row"], row[order])
+    # the packing kernel itself
+    t = torch.from_numpy(key).to(cuda_device)
+    hi = ops.pack_key_bytes(t, 0, 8).cpu().numpy().view(np.uint64)
+    lo = ops.pack_key_bytes(t, 8, 2).cpu().numpy().view(np.uint64)
+    np.testing.assert_array_equal(hi, key[:, :8].copy().view(">u8").astype(np.uint64).ravel())
+    np.testing.assert_array_equal(lo, (key[:, 8].astype(np.uint64) << np.uint64(56)) | (key[:, 9].astype(np.uint64) << np.uint64(48)))
+    with pytest.raises(ValueError):
+        ds.sort("key", boundaries=[1, 2])
