@@ -27,7 +27,7 @@ from .aggregate import AggregateFn, Count, Max, Mean, Min, Std, Sum
 from .block import Block, BlockAccessor, BlockExecStats, BlockMetadata, DeviceBlock, DeviceBlockAccessor, default_device
 from .context import DataContext
 from .interfaces import RefBundle, StatsDict
-from .planner import Aggregate, RandomShuffle, Repartition, Sort, plan_all_to_all_op
+from .planner import Aggregate, RandomizeBlocks, RandomShuffle, Repartition, Sort, plan_all_to_all_op
 from .sort_task_spec import SortKey
 
 _brange = builtins.range  # this module defines the ray.data-style `range()` constructor below
@@ -69,6 +69,10 @@ class Dataset:
                 "`num_blocks` parameter is deprecated in Ray 2.9. random_shuffle() does not support to change "
                 "the number of output blocks. Use repartition() instead.")
         return self._run_all_to_all(RandomShuffle(None, seed=seed, ray_remote_args=ray_remote_args))
+
+    def randomize_block_order(self, *, seed: Optional[int] = None) -> "Dataset":
+        """Shuffle the blocks (not the rows inside them); dataset.py:1050-1083."""
+        return self._run_all_to_all(RandomizeBlocks(None, seed=seed))
 
     def repartition(self, num_blocks: int, *, shuffle: bool = False) -> "Dataset":
         return self._run_all_to_all(Repartition(None, num_outputs=num_blocks, shuffle=shuffle))
@@ -204,26 +208,32 @@ class Dataset:
         for b in self._blocks:
             yield from DeviceBlockAccessor(b).iter_rows()
 
-    def iter_batches(self, *, batch_size: Optional[int] = None, batch_format: str = "numpy", **_ignored):
-        for b in self._blocks:
-            if batch_size is None:
-                chunks = [b]
-            else:
-                chunks = [b.slice(i, i + batch_size) for i in _brange(0, b.num_rows, batch_size)]
-            for c in chunks:
-                if batch_format in ("pyarrow", "arrow"):
-                    yield c.to_arrow()
-                elif batch_format == "pandas":
-                    yield c.to_pandas()
-                else:
-                    yield c.to_numpy()
+    def _iter_batch_blocks(self, batch_size, drop_last, local_shuffle_buffer_size, local_shuffle_seed):
+        from .batcher import blocks_to_batches
 
-    def iter_torch_batches(self, *, batch_size: Optional[int] = None, **_ignored):
-        """Batches as dicts of CUDA tensors: zero-copy views of the blocks (no D2H)."""
-        for b in self._blocks:
-            step = batch_size or max(b.num_rows, 1)
-            for i in _brange(0, b.num_rows, step):
-                yield dict(b.slice(i, i + step).columns)
+        return blocks_to_batches(iter(self._blocks), batch_size=batch_size, drop_last=drop_last,
+                                 shuffle_buffer_min_size=local_shuffle_buffer_size, shuffle_seed=local_shuffle_seed)
+
+    def iter_batches(self, *, batch_size: Optional[int] = 256, batch_format: str = "numpy", drop_last: bool = False,
+                     local_shuffle_buffer_size: Optional[int] = None, local_shuffle_seed: Optional[int] = None,
+                     **_ignored):
+        """Batches of `batch_size` rows cut across block boundaries (batch_size=None: one batch per
+        block), optionally drawn through a local shuffle buffer (dataset.py:3640-3708)."""
+        for c in self._iter_batch_blocks(batch_size, drop_last, local_shuffle_buffer_size, local_shuffle_seed):
+            if batch_format in ("pyarrow", "arrow"):
+                yield c.to_arrow()
+            elif batch_format == "pandas":
+                yield c.to_pandas()
+            else:
+                yield c.to_numpy()
+
+    def iter_torch_batches(self, *, batch_size: Optional[int] = 256, drop_last: bool = False,
+                           local_shuffle_buffer_size: Optional[int] = None, local_shuffle_seed: Optional[int] = None,
+                           **_ignored):
+        """Batches as dicts of CUDA tensors (no D2H): views of the blocks where a batch lies inside one
+        block, device concatenations where it spans two (dataset.py:3710-3800)."""
+        for c in self._iter_batch_blocks(batch_size, drop_last, local_shuffle_buffer_size, local_shuffle_seed):
+            yield dict(c.columns)
 
     def take(self, limit: int = 20) -> List[Dict[str, Any]]:
         return list(itertools.islice(self.iter_rows(), limit))

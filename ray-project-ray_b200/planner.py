@@ -55,6 +55,15 @@ class Repartition(AbstractAllToAll):
         self._shuffle = shuffle
 
 
+class RandomizeBlocks(AbstractAllToAll):
+    """logical/operators/all_to_all_operator.py:37-57."""
+
+    def __init__(self, input_op: Any = None, seed: Optional[int] = None):
+        super().__init__("RandomizeBlockOrder", input_op)
+        self._seed = seed
+        self._name = self.name
+
+
 class Sort(AbstractAllToAll):
     def __init__(self, input_op: Any = None, sort_key: SortKey = None):
         super().__init__("Sort", input_op,
@@ -292,6 +301,27 @@ def generate_repartition_fn(num_outputs: int, shuffle: bool,
     return fn
 
 
+def generate_randomize_blocks_fn(op: RandomizeBlocks) -> AllToAllTransformFn:
+    """Shuffle the order of the blocks, not their rows (planner/randomize_blocks.py:12-57): a host-side
+    `random.shuffle` of the (block, metadata) list, seeded with `random.seed(seed)` when a seed is given -
+    the same calls as the reference, so a seed gives the same block order. No data moves."""
+
+    def fn(refs: List[RefBundle], context: TaskContext) -> Tuple[List[RefBundle], StatsDict]:
+        import random
+
+        blocks_with_metadata = [(block, meta) for ref_bundle in refs for block, meta in ref_bundle.blocks]
+        if len(blocks_with_metadata) == 0:
+            return refs, {op._name: []}
+        if op._seed is not None:
+            random.seed(op._seed)
+        input_owned = all(b.owns_blocks for b in refs)
+        random.shuffle(blocks_with_metadata)
+        output = [RefBundle([(block, meta)], owns_blocks=input_owned) for block, meta in blocks_with_metadata]
+        return output, {op._name: [meta for _, meta in blocks_with_metadata]}
+
+    return fn
+
+
 class AllToAllOperator:
     """Blocking physical operator: buffers every input bundle, then runs `bulk_fn` once
     (base_physical_operator.py:40-132)."""
@@ -355,7 +385,9 @@ def plan_all_to_all_op(op: AbstractAllToAll, input_physical_dag: Any = None) -> 
     """Logical all-to-all op -> AllToAllOperator (plan_all_to_all_op.py:21-92)."""
     ctx = DataContext.get_current()
     target_max_block_size = None
-    if isinstance(op, RandomShuffle):
+    if isinstance(op, RandomizeBlocks):
+        fn = generate_randomize_blocks_fn(op)
+    elif isinstance(op, RandomShuffle):
         debug = ctx.get_config("debug_limit_shuffle_execution_to_num_blocks", None)
         fn = generate_random_shuffle_fn(op._seed, op._num_outputs, op._ray_remote_args, debug)
         target_max_block_size = ctx.target_shuffle_max_block_size

@@ -44,3 +44,11 @@ def quantile():
         with open(os.path.join(_DIR, "quantile_outputs.json")) as f:
             _cache["q"] = json.load(f)
     return _cache["q"]
+
+
+def batcher():
+    """Batch boundaries and shuffle-buffer contents of the reference's Batcher / ShufflingBatcher."""
+    if "b" not in _cache:
+        with open(os.path.join(_DIR, "batcher_outputs.json")) as f:
+            _cache["b"] = json.load(f)
+    return _cache["b"]

@@ -9,6 +9,7 @@ so that tests can run on the GPU box, where /root/reference does not exist.
 
     python tests/golden/make_golden.py            # everything
     python tests/golden/make_golden.py quantile   # only quantile_outputs.json
+    python tests/golden/make_golden.py batcher    # only batcher_outputs.json
 """
 import importlib
 import inspect
@@ -451,11 +452,76 @@ def run_quantile(shim=None):
     print("wrote quantile_outputs.json", os.path.getsize(os.path.join(OUT, "quantile_outputs.json")) // 1024, "KiB")
 
 
+def run_batcher(shim=None):
+    """Batcher / ShufflingBatcher goldens (_internal/batcher.py) -> batcher_outputs.json. The classes are
+    the reference's own; the driver loop is block_batching/util.py:116-139 restated (that module needs
+    ray.actor). random_shuffle is replaced by a recorder that keeps the row order, so that which rows
+    are in the buffer at every re-shuffle, the seeds used and the batch boundaries are all pinned."""
+    install = shim or install_shim()
+    bmod = importlib.import_module("ray.data._internal.batcher")
+    from ray.data._internal.arrow_block import ArrowBlockAccessor
+
+    shuffles = []
+    orig = ArrowBlockAccessor.random_shuffle
+
+    def recorder(self, random_seed):
+        shuffles.append({"seed": random_seed, "rows": self._table["row"].to_pylist()})
+        return self._table
+
+    ArrowBlockAccessor.random_shuffle = recorder
+    cases = []
+    combos = [([5, 0, 12, 1, 22], 7, None, False), ([5, 0, 12, 1, 22], 7, None, True), ([5, 0, 12, 1, 22], None, None, False),
+              ([100], 32, None, False), ([3, 3, 3, 3], 10, None, False), ([3, 3, 3, 3], 10, None, True),
+              ([50, 50, 50, 50, 50], 16, 40, False), ([50, 50, 50, 50, 50], 16, 40, True), ([10] * 30, 25, 60, False),
+              ([500], 64, 100, False), ([7, 0, 9, 200, 1, 1, 1, 64], 32, 10, False), ([20, 20], 50, 5, False)]
+    for sizes, batch_size, min_size, drop_last in combos:
+        del shuffles[:]
+        lo, blocks = 0, []
+        for sz in sizes:
+            blocks.append(pa.table({"row": np.arange(lo, lo + sz, dtype=np.int64)}))
+            lo += sz
+        if min_size is not None:
+            batcher = bmod.ShufflingBatcher(batch_size=batch_size, shuffle_buffer_min_size=min_size, shuffle_seed=11)
+        else:
+            batcher = bmod.Batcher(batch_size=batch_size)
+        out = []
+        for blk in blocks:
+            batcher.add(blk)
+            while batcher.has_batch():
+                out.append(batcher.next_batch()["row"].to_pylist())
+        batcher.done_adding()
+        while batcher.has_batch():
+            out.append(batcher.next_batch()["row"].to_pylist())
+        if not drop_last and batcher.has_any():
+            out.append(batcher.next_batch()["row"].to_pylist())
+        cases.append({"block_sizes": sizes, "batch_size": batch_size, "shuffle_buffer_min_size": min_size,
+                      "drop_last": drop_last, "batches": out, "shuffles": [dict(x) for x in shuffles]})
+    ArrowBlockAccessor.random_shuffle = orig
+    # randomize_block_order (planner/randomize_blocks.py): the reference's own function on 9 one-row blocks
+    ray, rb, tc, PB = install
+    from ray.data.block import BlockAccessor
+    rmod = importlib.import_module("ray.data._internal.planner.randomize_blocks")
+    orders = {}
+    for seed in (0, 1, 42, 2024):
+        op = types.SimpleNamespace(_seed=seed, _name="RandomizeBlockOrder")
+        tables = [pa.table({"row": [i]}) for i in range(9)]
+        refs = [rb.RefBundle([(Ref(t), BlockAccessor.for_block(t).get_metadata(None, None))], owns_blocks=True)
+                for t in tables]
+        out, _ = rmod.generate_randomize_blocks_fn(op)(refs, None)
+        orders[str(seed)] = [ray.get(b.blocks[0][0])["row"][0].as_py() for b in out]
+    with open(os.path.join(OUT, "batcher_outputs.json"), "w") as fjson:
+        json.dump({"cases": cases, "randomize_block_order": orders}, fjson)
+    print("wrote batcher_outputs.json", os.path.getsize(os.path.join(OUT, "batcher_outputs.json")) // 1024, "KiB")
+
+
 if __name__ == "__main__":
     if not os.path.isdir(REF):
         sys.exit("needs /root/reference (build container only)")
     if sys.argv[1:] == ["quantile"]:
         run_quantile()
+    elif sys.argv[1:] == ["batcher"]:
+        run_batcher()
     else:
         run_all()
         run_quantile()
+        run_batcher()

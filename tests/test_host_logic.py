@@ -140,3 +140,52 @@ def test_product_never_imports_the_oracle():
             if f.endswith(".py"):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in src, f"{f} mentions the oracle"
+
+
+def test_batchers_equal_reference_batch_boundaries_and_shuffle_buffers(monkeypatch):
+    """Batcher / ShufflingBatcher host logic (_internal/batcher.py) against the reference's own classes:
+    same batches, and - with the shuffle replaced by a recorder on both sides - the same rows in the
+    shuffle buffer at every re-shuffle with the same seeds. Runs on CPU tensors (no kernels involved)."""
+    import torch
+
+    from ray_project_ray_b200.batcher import blocks_to_batches
+    from ray_project_ray_b200.block import DeviceBlock, DeviceBlockAccessor
+    from tests import _golden as G
+
+    shuffles = []
+
+    def recorder(self, random_seed):
+        shuffles.append({"seed": random_seed, "rows": self._block.columns["row"].tolist()})
+        return self._block
+
+    monkeypatch.setattr(DeviceBlockAccessor, "random_shuffle", recorder)
+    for case in G.batcher()["cases"]:
+        del shuffles[:]
+        lo, blocks = 0, []
+        for sz in case["block_sizes"]:
+            blocks.append(DeviceBlock({"row": torch.arange(lo, lo + sz)}, device=torch.device("cpu")))
+            lo += sz
+        out = [b.columns["row"].tolist() for b in blocks_to_batches(
+            iter(blocks), batch_size=case["batch_size"], drop_last=case["drop_last"],
+            shuffle_buffer_min_size=case["shuffle_buffer_min_size"], shuffle_seed=11)]
+        assert out == case["batches"], case["block_sizes"]
+        assert shuffles == case["shuffles"], case["block_sizes"]
+
+
+def test_randomize_block_order_equals_reference_order():
+    """planner/randomize_blocks.py: random.seed(seed) + random.shuffle of the block list - the same calls,
+    so the same block order as the reference's own function returned (tests/golden/batcher_outputs.json)."""
+    import torch
+
+    from ray_project_ray_b200.block import DeviceBlock, DeviceBlockAccessor
+    from ray_project_ray_b200.interfaces import RefBundle
+    from ray_project_ray_b200.planner import RandomizeBlocks, generate_randomize_blocks_fn
+    from tests import _golden as G
+
+    for seed, want in G.batcher()["randomize_block_order"].items():
+        blocks = [DeviceBlock({"row": torch.tensor([i])}, device=torch.device("cpu")) for i in range(9)]
+        refs = [RefBundle([(b, DeviceBlockAccessor(b).get_metadata(None, None))], owns_blocks=True) for b in blocks]
+        out, stats = generate_randomize_blocks_fn(RandomizeBlocks(None, seed=int(seed)))(refs, None)
+        assert [int(r.blocks[0][0].columns["row"][0]) for r in out] == want
+        assert list(stats) == ["RandomizeBlockOrder"] and len(stats["RandomizeBlockOrder"]) == 9
+    assert generate_randomize_blocks_fn(RandomizeBlocks(None, seed=1))([], None) == ([], {"RandomizeBlockOrder": []})

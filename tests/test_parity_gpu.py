@@ -456,3 +456,33 @@ def test_sort_by_byte_string_key(sched, desc, cuda_device):
     np.testing.assert_array_equal(lo, (key[:, 8].astype(np.uint64) << np.uint64(56)) | (key[:, 9].astype(np.uint64) << np.uint64(48)))
     with pytest.raises(ValueError):
         ds.sort("key", boundaries=[1, 2])
+
+
+def test_iter_batches_across_blocks_and_local_shuffle(cuda_device):
+    """Dataset.iter_batches / iter_torch_batches (dataset.py:3640-3800): batches of batch_size rows cut
+    across block boundaries; with a local shuffle buffer every row still appears exactly once, the
+    result is deterministic per seed, and rows leave the stream order (tests/test_iterator... local_shuffle)."""
+    n = 10_000
+    ds = rd.range(n, override_num_blocks=7)
+    sizes = [len(b["id"]) for b in ds.iter_batches(batch_size=512)]
+    assert sizes == [512] * (n // 512) + [n % 512]
+    assert np.array_equal(np.concatenate([b["id"] for b in ds.iter_batches(batch_size=512)]), np.arange(n))
+    assert sum(len(b["id"]) for b in ds.iter_batches(batch_size=512, drop_last=True)) == (n // 512) * 512
+    tb = list(ds.iter_torch_batches(batch_size=3000))
+    assert all(t["id"].is_cuda for t in tb) and [t["id"].numel() for t in tb] == [3000, 3000, 3000, 1000]
+
+    def run(seed):
+        return [b["id"] for b in ds.iter_batches(batch_size=256, local_shuffle_buffer_size=1000, local_shuffle_seed=seed)]
+
+    a, b, c = run(5), run(5), run(6)
+    flat = np.concatenate(a)
+    assert [len(x) for x in a][:-1] == [256] * (len(a) - 1)
+    assert np.array_equal(np.sort(flat), np.arange(n)) and not np.array_equal(flat, np.arange(n))
+    assert all(np.array_equal(x, y) for x, y in zip(a, b))
+    assert not np.array_equal(flat, np.concatenate(c))
+    # a local buffer shuffles locally: early batches only hold rows from the first blocks
+    assert a[0].max() < 4 * (n // 7 + 1)
+    with pytest.raises(ValueError):
+        next(iter(ds.iter_batches(batch_size=None, local_shuffle_buffer_size=10)))
+    order = [int(b["id"][0]) for b in rd.range(90, override_num_blocks=9).randomize_block_order(seed=42).iter_batches(batch_size=None)]
+    assert order == [10 * i for i in G.batcher()["randomize_block_order"]["42"]]
