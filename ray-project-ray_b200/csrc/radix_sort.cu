@@ -947,12 +947,21 @@ struct FinArgs {
 
 constexpr uint32_t TIE_MAX = 48;  // longest group of equal windows the in-place tie repair handles
 
+// window of the one-round counting sort: about one bin per pair (2048 bins for runs <= 2048 pairs, ...)
+template <uint32_t THREADS>
+struct FinWindow {
+  static constexpr int BITS = THREADS == 256 ? 11 : THREADS == 512 ? 12 : 13;
+  static constexpr uint32_t BINS = 1u << BITS;
+};
+
 template <uint32_t THREADS>
 struct FinSmem {
   uint64_t keys[THREADS * FIN_IPT];
   uint32_t vals[THREADS * FIN_IPT];
+  uint32_t hist[FinWindow<THREADS>::BINS + 1];  // counting sort: bin counts, then bin starts
+  uint16_t ord[THREADS * FIN_IPT];              // counting sort: position of the pair in the run as loaded
   uint16_t whist[(THREADS / 32) * RADIX];
-  uint32_t swarp[RADIX / 32];
+  uint32_t swarp[32];
   uint32_t slow;
 };
 
@@ -1137,54 +1146,110 @@ __device__ __forceinline__ void finish_one_run(const FinArgs& a, const SortCtl* 
     load_run();
     if (tid == 0) sm.slow = 0;
 
-    // Sort by a window of the top 16 remaining bits only (two 8-bit rounds). Pairs that still tie on
-    // the window are rare for spread-out keys and form tiny groups; each element then finds its
-    // place inside its group by comparing the bits below the window with its neighbours in shared
-    // memory. (A single 8-bit round leaves groups of ~m/256 pairs and the neighbour scan then costs
-    // more than the second round: 1.73 vs 1.30 ms per 100 M pairs.) Groups longer than TIE_MAX
-    // (duplicate-heavy keys) send the run down the plain path: LSD over every remaining bit.
-    const int W = 2 * RADIX_BITS;
-    bool tie_repair = R > W;
-    if (tie_repair) fin_lsd<THREADS>(key, val, nit, R - W, R, sm);
-    else fin_lsd<THREADS>(key, val, nit, 0, max(R, 1), sm);  // (R = 0: equal keys, one round just stages them)
-    // (fin_lsd ends with a barrier: shared memory holds the pairs sorted by the window)
+    // One counting-sort round on a window of the top bits that remain, with about one bin per pair:
+    // every pair takes a ticket in its bin (a shared-memory atomic, so the order inside a bin is
+    // arbitrary), the bins are scanned, the pairs are scattered. Pairs that share a bin are rare for
+    // spread-out keys and form tiny groups; each pair then finds its place inside its group by
+    // comparing (bits below the window, position in the run as loaded) with the others - which also
+    // restores stability. (Two ballot-ranked 8-bit rounds on a 16-bit window, the earlier scheme, cost
+    // 311 instructions per pair; one 8-bit round left groups of ~m/256 pairs and was slower still.)
+    // A group longer than TIE_MAX (duplicate-heavy keys) sends the run down the plain path: stable LSD
+    // over every remaining bit.
+    // (At most 8 bits left - narrow keys, many duplicates per value: one stable ballot-ranked round
+    // sorts the run outright; ticketed bins would hold long groups of equal keys.)
+    bool tie_repair = R > RADIX_BITS;
     uint32_t fpos[FIN_IPT];
-    if (tie_repair) {
-      const int wshift = R - W;
+    if (!tie_repair) {
+      fin_lsd<THREADS>(key, val, nit, 0, max(R, 1), sm);  // (R = 0: equal keys, the round just stages them)
+    } else {
+      constexpr int WB = FinWindow<THREADS>::BITS;
+      constexpr uint32_t BINS = FinWindow<THREADS>::BINS;
+      const int wbits = min(R, WB);
+      const int wshift = R - wbits;
+      const uint32_t wmask = (1u << wbits) - 1u;
       const uint64_t lowmask = (1ull << wshift) - 1ull;
+      for (uint32_t i = tid; i <= BINS; i += THREADS) sm.hist[i] = 0;
+      __syncthreads();
+      uint32_t ticket[FIN_IPT];
+      {
+        const uint32_t wb = (tid >> 5) * 32 * nit + (tid & 31);
+#pragma unroll
+        for (uint32_t j = 0; j < FIN_IPT; ++j) {
+          if (j < nit && wb + j * 32 < m) ticket[j] = atomicAdd(&sm.hist[(uint32_t)(key[j] >> wshift) & wmask], 1u);
+        }
+      }
+      __syncthreads();
+      {
+        // exclusive scan of the bin counts: BINS / THREADS consecutive bins per thread
+        constexpr uint32_t PERT = BINS / THREADS;
+        uint32_t c[PERT], tot = 0;
+#pragma unroll
+        for (uint32_t q = 0; q < PERT; ++q) {
+          c[q] = sm.hist[tid * PERT + q];
+          tot += c[q];
+        }
+        uint32_t x = tot;
+        const uint32_t lane = tid & 31, w = tid >> 5;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+          if (lane >= (uint32_t)o) x += y;
+        }
+        if (lane == 31) sm.swarp[w] = x;
+        __syncthreads();
+        uint32_t off = x - tot;
+        for (uint32_t k = 0; k < w; ++k) off += sm.swarp[k];
+#pragma unroll
+        for (uint32_t q = 0; q < PERT; ++q) {
+          sm.hist[tid * PERT + q] = off;
+          off += c[q];
+        }
+        if (tid == THREADS - 1) sm.hist[BINS] = off;  // = m
+      }
+      __syncthreads();
+      {
+        const uint32_t wb = (tid >> 5) * 32 * nit + (tid & 31);
+#pragma unroll
+        for (uint32_t j = 0; j < FIN_IPT; ++j) {
+          if (j < nit && wb + j * 32 < m) {
+            const uint32_t pos = sm.hist[(uint32_t)(key[j] >> wshift) & wmask] + ticket[j];
+            sm.keys[pos] = key[j];
+            sm.vals[pos] = val[j];
+            sm.ord[pos] = (uint16_t)(wb + j * 32);
+          }
+        }
+      }
+      __syncthreads();
 #pragma unroll
       for (uint32_t j = 0; j < FIN_IPT; ++j) {
         const uint32_t i = tid + j * THREADS;
         fpos[j] = i;
         if (i < m) {
           const uint64_t k = sm.keys[i];
-          const uint64_t win = k >> wshift, low = k & lowmask;
-          uint32_t gs = i, before = 0, steps = 0;
-          while (gs > 0 && steps <= TIE_MAX) {
-            const uint64_t o = sm.keys[gs - 1];
-            if ((o >> wshift) != win) break;
-            --gs;
-            ++steps;
-            before += ((o & lowmask) <= low) ? 1u : 0u;  // earlier element, not larger: stays ahead
+          const uint32_t d = (uint32_t)(k >> wshift) & wmask;
+          const uint32_t gs = sm.hist[d], ge = sm.hist[d + 1];
+          if (ge - gs > 1) {
+            if (ge - gs > TIE_MAX) {
+              sm.slow = 1;
+            } else {
+              const uint64_t low = k & lowmask;
+              const uint32_t me = sm.ord[i];
+              uint32_t ahead = 0;  // pairs of my bin that sort before me: smaller low bits, or equal and loaded earlier
+              for (uint32_t e = gs; e < ge; ++e) {
+                const uint64_t ol = sm.keys[e] & lowmask;
+                ahead += (ol < low || (ol == low && sm.ord[e] < me)) ? 1u : 0u;
+              }
+              fpos[j] = gs + ahead;
+            }
           }
-          uint32_t ge = i + 1, after_smaller = 0;
-          while (ge < m && steps <= TIE_MAX) {
-            const uint64_t o = sm.keys[ge];
-            if ((o >> wshift) != win) break;
-            after_smaller += ((o & lowmask) < low) ? 1u : 0u;  // later element, strictly smaller: moves ahead
-            ++ge;
-            ++steps;
-          }
-          if (steps > TIE_MAX) sm.slow = 1;
-          fpos[j] = gs + before + after_smaller;
         }
       }
-      __syncthreads();
-      if (sm.slow) {
-        load_run();
-        fin_lsd<THREADS>(key, val, nit, 0, R, sm);
-        tie_repair = false;
-      }
+    }
+    __syncthreads();
+    if (tie_repair && sm.slow) {
+      load_run();
+      fin_lsd<THREADS>(key, val, nit, 0, R, sm);
+      tie_repair = false;
     }
 #pragma unroll
     for (uint32_t j = 0; j < FIN_IPT; ++j) {
