@@ -945,6 +945,9 @@ struct FinArgs {
   int desc;
 };
 
+#ifndef B200X_FIN_TPS
+#define B200X_FIN_TPS 1024  // resident finisher threads per SM the register budget is set for
+#endif
 constexpr uint32_t TIE_MAX = 48;  // longest group of equal windows the in-place tie repair handles
 
 // window of the one-round counting sort: about one bin per pair (2048 bins for runs <= 2048 pairs, ...)
@@ -1277,7 +1280,7 @@ __device__ __forceinline__ uint32_t fin_class(uint32_t m) {
 }
 
 template <uint32_t THREADS>
-__global__ void __launch_bounds__(THREADS, 1024 / THREADS)
+__global__ void __launch_bounds__(THREADS, B200X_FIN_TPS / THREADS)
 finish_runs_kernel(const FinArgs a) {
   const SortCtl* ctl = a.ctl;
   if (ctl->mode != MODE_HYBRID) return;

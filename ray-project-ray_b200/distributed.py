@@ -22,6 +22,8 @@ movement inside a rank is the C-ABI kernels.
 """
 from __future__ import annotations
 
+import os
+
 import math
 from typing import Dict, List, Optional, Sequence, Tuple
 
@@ -327,7 +329,7 @@ def _p2p_partition_sort(local: DeviceBlock, sort_key: SortKey, n: int, dev, grou
     # tile and 9.4 ms back to back).
     from . import _lib
 
-    _lib.call("b200x_set_tuning", 1, 2)
+    _lib.call("b200x_set_tuning", 1, int(os.environ.get("B200X_PAYLOAD_BLOCKS_PER_SM", "2")))
     try:
         ex.send(rest)
     finally:
