@@ -125,13 +125,24 @@ int b200x_iota_u32(uint32_t* out, size_t n, uint32_t start, void* stream);
  * This is the comparison pyarrow's sort applies (call sites as for b200x_radix_argsort). */
 int b200x_encode_keys(const void* keys, int key_type, int descending, size_t n, uint64_t* codes_out, void* stream);
 
+/* *count_out = number of positions i >= 1 with keys[i] == keys[i-1] in a sorted key column (compared as
+ * codes: -0.0 == +0.0). Zero = all keys distinct: a multi-column sort (transform_pyarrow.py:17-21 with several
+ * sort keys) then needs only the sort by its first column. No counterpart in the reference. */
+int b200x_count_adjacent_equal(const void* keys, int key_type, size_t n, uint64_t* count_out, void* stream);
+
 /* out[i] = bytes [offset, offset + width) of row i of a fixed-width byte-string column (row_bytes per row)
- * as a big-endian unsigned integer, left-aligned in 64 bits and zero-padded; 1 <= width <= 8. Sorting a
- * w-byte key = chained b200x_radix_argsort calls (key type U64) over its ceil(w / 8) chunks, last chunk
- * first: the lexicographic order pyarrow.compute.sort_indices gives binary / fixed_size_binary keys
- * (transform_pyarrow.py:17-21; gensort-style 10-byte keys). */
-int b200x_pack_key_bytes(const void* col, size_t row_bytes, size_t offset, int width, size_t n, uint64_t* out,
-                         void* stream);
+ * as a big-endian unsigned integer, left-aligned in an out_bytes-wide (2, 4 or 8) unsigned integer and
+ * zero-padded; 1 <= width <= out_bytes. Sorting a w-byte key = chained b200x_radix_argsort calls (key types
+ * U64 / U32 / U16) over its chunks, last chunk first: the lexicographic order pyarrow.compute.sort_indices
+ * gives binary / fixed_size_binary keys (transform_pyarrow.py:17-21; gensort-style 10-byte keys). */
+int b200x_pack_key_bytes(const void* col, size_t row_bytes, size_t offset, int width, size_t n, void* out,
+                         int out_bytes, void* stream);
+
+/* The inverse of b200x_pack_key_bytes: writes the first `width` big-endian bytes of chunk[i] to bytes
+ * [offset, offset + width) of row i (the key column is rebuilt from its sorted chunks instead of being
+ * carried through the exchange). No counterpart in the reference. */
+int b200x_unpack_key_bytes(const void* chunk, int chunk_bytes, int width, void* col, size_t row_bytes, size_t offset,
+                           size_t n, void* stream);
 
 /* out_index[b] = lower bound (upper == 0) or upper bound (upper != 0) of bound_codes[b] in the
  * ascending array codes[0..n). Replaces find_partition_index / find_partitions:

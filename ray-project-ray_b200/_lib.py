@@ -61,7 +61,9 @@ SIGNATURES = {
                                        c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, _size_p, c_void_p]),
     "b200x_group_counts": (c_int, [c_void_p, c_void_p, c_size_t, c_size_t, c_void_p, c_void_p]),
     "b200x_finalize_groups": (c_int, [c_void_p, c_int, c_void_p, c_size_t, c_int, c_int, c_void_p, c_void_p]),
-    "b200x_pack_key_bytes": (c_int, [c_void_p, c_size_t, c_size_t, c_int, c_size_t, c_void_p, c_void_p]),
+    "b200x_count_adjacent_equal": (c_int, [c_void_p, c_int, c_size_t, c_void_p, c_void_p]),
+    "b200x_pack_key_bytes": (c_int, [c_void_p, c_size_t, c_size_t, c_int, c_size_t, c_void_p, c_int, c_void_p]),
+    "b200x_unpack_key_bytes": (c_int, [c_void_p, c_int, c_int, c_void_p, c_size_t, c_size_t, c_size_t, c_void_p]),
     "b200x_group_quantile": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_void_p, c_int, c_size_t, c_double,
                                      c_void_p, c_void_p]),
 }

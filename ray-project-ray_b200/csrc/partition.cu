@@ -119,34 +119,108 @@ extern "C" int b200x_encode_keys(const void* keys, int key_type, int descending,
   return B200X_OK;
 }
 
+// Number of positions i >= 1 with keys[i] == keys[i - 1] (as codes: -0.0 == +0.0, NaN == NaN) in a sorted column:
+// zero means every key is distinct, i.e. lower-priority key columns cannot influence the order.
+__global__ void __launch_bounds__(256)
+count_adjacent_equal_kernel(const void* __restrict__ keys, int kt, uint64_t n, unsigned long long* __restrict__ out) {
+  unsigned long long c = 0;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x + 1; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    c += load_encode(keys, i, kt, false) == load_encode(keys, i - 1, kt, false) ? 1ull : 0ull;
+#pragma unroll
+  for (int d = 16; d >= 1; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, c);
+}
+
+extern "C" int b200x_count_adjacent_equal(const void* keys, int key_type, size_t n, uint64_t* count_out, void* stream_) {
+  if (count_out == nullptr || key_type < 0 || key_type >= KEY_TYPE_COUNT || (n > 0 && keys == nullptr)) {
+    set_error("b200x_count_adjacent_equal: bad arguments");
+    return B200X_ERR_ARG;
+  }
+  cudaStream_t st = (cudaStream_t)stream_;
+  B200X_CUDA(cudaMemsetAsync(count_out, 0, sizeof(uint64_t), st));
+  if (n < 2) return B200X_OK;
+  uint64_t blocks = (n + 255) / 256;
+  const uint64_t cap = (uint64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  count_adjacent_equal_kernel<<<(uint32_t)blocks, 256, 0, st>>>(keys, key_type, n, (unsigned long long*)count_out);
+  B200X_LAUNCH_CHECK("count_adjacent_equal_kernel");
+  return B200X_OK;
+}
+
 // Fixed-width byte-string keys: bytes [offset, offset + width) of every row as one big-endian unsigned
-// integer, left-aligned in 64 bits (zero-padded on the right), so that comparing the integers compares
+// integer, left-aligned in OUT (zero-padded on the right), so that comparing the integers compares
 // the byte strings lexicographically (the order pyarrow gives binary / fixed_size_binary columns).
+template <typename OUT>
 __global__ void __launch_bounds__(256)
 pack_key_bytes_kernel(const unsigned char* __restrict__ col, uint64_t row_bytes, uint32_t offset, uint32_t width,
-                      uint64_t n, uint64_t* __restrict__ out) {
+                      uint64_t n, OUT* __restrict__ out) {
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
     const unsigned char* p = col + i * row_bytes + offset;
     uint64_t v = 0;
 #pragma unroll
-    for (uint32_t b = 0; b < 8; ++b) v = (v << 8) | (b < width ? (uint64_t)p[b] : 0ull);
-    out[i] = v;
+    for (uint32_t b = 0; b < sizeof(OUT); ++b) v = (v << 8) | (b < width ? (uint64_t)p[b] : 0ull);
+    out[i] = (OUT)v;
   }
 }
 
-extern "C" int b200x_pack_key_bytes(const void* col, size_t row_bytes, size_t offset, int width, size_t n,
-                                    uint64_t* out, void* stream_) {
+// The inverse: the first `width` big-endian bytes of every chunk back into bytes [offset, offset + width) of the rows.
+template <typename IN>
+__global__ void __launch_bounds__(256)
+unpack_key_bytes_kernel(const IN* __restrict__ chunk, uint32_t width, unsigned char* __restrict__ col,
+                        uint64_t row_bytes, uint32_t offset, uint64_t n) {
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t v = (uint64_t)chunk[i];
+    unsigned char* p = col + i * row_bytes + offset;
+#pragma unroll
+    for (uint32_t b = 0; b < sizeof(IN); ++b)
+      if (b < width) p[b] = (unsigned char)(v >> (8 * (sizeof(IN) - 1 - b)));
+  }
+}
+
+static bool chunk_args_ok(size_t row_bytes, size_t offset, int width, int chunk_bytes) {
+  return width >= 1 && (chunk_bytes == 2 || chunk_bytes == 4 || chunk_bytes == 8) && width <= chunk_bytes &&
+         offset + (size_t)width <= row_bytes;
+}
+
+extern "C" int b200x_pack_key_bytes(const void* col, size_t row_bytes, size_t offset, int width, size_t n, void* out,
+                                    int out_bytes, void* stream_) {
   if (n == 0) return B200X_OK;
-  if (col == nullptr || out == nullptr || width < 1 || width > 8 || offset + (size_t)width > row_bytes) {
-    set_error("b200x_pack_key_bytes: bad arguments (row_bytes=%zu offset=%zu width=%d)", row_bytes, offset, width);
+  if (col == nullptr || out == nullptr || !chunk_args_ok(row_bytes, offset, width, out_bytes)) {
+    set_error("b200x_pack_key_bytes: bad arguments (row_bytes=%zu offset=%zu width=%d out_bytes=%d)", row_bytes, offset,
+              width, out_bytes);
     return B200X_ERR_ARG;
   }
   uint64_t blocks = (n + 255) / 256;
   const uint64_t cap = (uint64_t)sm_count() * 16;
   if (blocks > cap) blocks = cap;
-  pack_key_bytes_kernel<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream_>>>((const unsigned char*)col, row_bytes,
-                                                                            (uint32_t)offset, (uint32_t)width, n, out);
+  const unsigned char* c = (const unsigned char*)col;
+  cudaStream_t st = (cudaStream_t)stream_;
+  const uint32_t g = (uint32_t)blocks, off = (uint32_t)offset, w = (uint32_t)width;
+  if (out_bytes == 8) pack_key_bytes_kernel<uint64_t><<<g, 256, 0, st>>>(c, row_bytes, off, w, n, (uint64_t*)out);
+  else if (out_bytes == 4) pack_key_bytes_kernel<uint32_t><<<g, 256, 0, st>>>(c, row_bytes, off, w, n, (uint32_t*)out);
+  else pack_key_bytes_kernel<uint16_t><<<g, 256, 0, st>>>(c, row_bytes, off, w, n, (uint16_t*)out);
   B200X_LAUNCH_CHECK("pack_key_bytes_kernel");
+  return B200X_OK;
+}
+
+extern "C" int b200x_unpack_key_bytes(const void* chunk, int chunk_bytes, int width, void* col, size_t row_bytes,
+                                      size_t offset, size_t n, void* stream_) {
+  if (n == 0) return B200X_OK;
+  if (col == nullptr || chunk == nullptr || !chunk_args_ok(row_bytes, offset, width, chunk_bytes)) {
+    set_error("b200x_unpack_key_bytes: bad arguments (row_bytes=%zu offset=%zu width=%d chunk_bytes=%d)", row_bytes,
+              offset, width, chunk_bytes);
+    return B200X_ERR_ARG;
+  }
+  uint64_t blocks = (n + 255) / 256;
+  const uint64_t cap = (uint64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  unsigned char* c = (unsigned char*)col;
+  cudaStream_t st = (cudaStream_t)stream_;
+  const uint32_t g = (uint32_t)blocks, off = (uint32_t)offset, w = (uint32_t)width;
+  if (chunk_bytes == 8) unpack_key_bytes_kernel<uint64_t><<<g, 256, 0, st>>>((const uint64_t*)chunk, w, c, row_bytes, off, n);
+  else if (chunk_bytes == 4) unpack_key_bytes_kernel<uint32_t><<<g, 256, 0, st>>>((const uint32_t*)chunk, w, c, row_bytes, off, n);
+  else unpack_key_bytes_kernel<uint16_t><<<g, 256, 0, st>>>((const uint16_t*)chunk, w, c, row_bytes, off, n);
+  B200X_LAUNCH_CHECK("unpack_key_bytes_kernel");
   return B200X_OK;
 }
 

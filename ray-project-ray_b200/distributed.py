@@ -320,13 +320,10 @@ def _p2p_partition_sort(local: DeviceBlock, sort_key: SortKey, n: int, dev, grou
     side = _side_stream(dev)
     landed, sorted_ev = torch.cuda.Event(), torch.cuda.Event()
     landed.record(main)
-    with torch.cuda.stream(side):
-        side.wait_event(landed)
-        perm2, _, skeys2 = DeviceBlockAccessor(keys_block)._argsort(sort_key, False)
-        sorted_ev.record(side)
     # The payload transfer is link-bound: two blocks per SM keep NVLink busy and leave the rest of every SM to
     # the sort running next to it (measured at 2 GPUs: sort || send 6.3 ms, against 10.5 ms with one block per
-    # tile and 9.4 ms back to back).
+    # tile and 9.4 ms back to back). It is enqueued first: the sort below may synchronise the host with its own
+    # stream (multi-column keys probe whether the first column alone decides the order).
     from . import _lib
 
     _lib.call("b200x_set_tuning", 1, int(os.environ.get("B200X_PAYLOAD_BLOCKS_PER_SM", "2")))
@@ -335,6 +332,10 @@ def _p2p_partition_sort(local: DeviceBlock, sort_key: SortKey, n: int, dev, grou
     finally:
         _lib.call("b200x_set_tuning", 1, 0)
     ex.fence()
+    with torch.cuda.stream(side):
+        side.wait_event(landed)
+        perm2, _, skeys2 = DeviceBlockAccessor(keys_block)._argsort(sort_key, False)
+        sorted_ev.record(side)
     main.wait_event(sorted_ev)
     perm2.record_stream(main)
     if skeys2 is not None:
@@ -371,12 +372,12 @@ def _p2p_sort_exchange(local: DeviceBlock, sort_key: SortKey, perm, skeys, n: in
     side = _side_stream(dev)
     landed, sorted_ev = torch.cuda.Event(), torch.cuda.Event()
     landed.record(main)
+    ex.send(rest)  # (enqueued before the sort, which may synchronise the host with its own stream)
+    ex.fence()
     with torch.cuda.stream(side):
         side.wait_event(landed)
         perm2, _, skeys2 = DeviceBlockAccessor(keys_block)._argsort(sort_key, False)
         sorted_ev.record(side)
-    ex.send(rest)
-    ex.fence()
     main.wait_event(sorted_ev)
     perm2.record_stream(main)
     if skeys2 is not None:

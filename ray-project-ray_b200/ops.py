@@ -152,23 +152,53 @@ def encode_keys(keys: torch.Tensor, descending: bool = False) -> torch.Tensor:
     return out
 
 
+def count_adjacent_equal(sorted_keys: torch.Tensor) -> torch.Tensor:
+    """int64[1] on the device: how many rows of a sorted key column equal their predecessor."""
+    dev = _require_cuda(sorted_keys)
+    out = torch.empty(1, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        _lib.call("b200x_count_adjacent_equal", sorted_keys.data_ptr(), key_type_of(sorted_keys), sorted_keys.numel(),
+                  out.data_ptr(), _stream(dev))
+    return out
+
+
+def _chunk_dtype(width: int) -> torch.dtype:
+    return torch.uint16 if width <= 2 else (torch.uint32 if width <= 4 else torch.uint64)
+
+
 def pack_key_bytes(col: torch.Tensor, offset: int, width: int) -> torch.Tensor:
-    """Bytes [offset, offset + width) of every row of a [n, w] uint8 column as big-endian uint64 (left-aligned)."""
+    """Bytes [offset, offset + width) of every row of a [n, w] uint8 column as a big-endian unsigned integer
+    column (uint16 / uint32 / uint64 by width, left-aligned)."""
     dev = _require_cuda(col)
     if col.dim() != 2 or col.dtype != torch.uint8:
         raise TypeError("byte-string keys are [n, width] uint8 columns")
     n, w = col.shape
-    out = torch.empty(n, dtype=torch.uint64, device=dev)
+    out = torch.empty(n, dtype=_chunk_dtype(width), device=dev)
     if n:
         with torch.cuda.device(dev):
-            _lib.call("b200x_pack_key_bytes", col.data_ptr(), w, offset, width, n, out.data_ptr(), _stream(dev))
+            _lib.call("b200x_pack_key_bytes", col.data_ptr(), w, offset, width, n, out.data_ptr(), out.element_size(),
+                      _stream(dev))
     return out
 
 
 def byte_key_chunks(col: torch.Tensor) -> List[torch.Tensor]:
-    """A [n, w] uint8 key column as ceil(w / 8) uint64 columns, most significant first."""
+    """A [n, w] uint8 key column as ceil(w / 8) unsigned integer columns, most significant first."""
     w = col.shape[1]
     return [pack_key_bytes(col, off, min(8, w - off)) for off in range(0, w, 8)]
+
+
+def unpack_key_bytes(chunks: Sequence[torch.Tensor], width: int) -> torch.Tensor:
+    """Inverse of byte_key_chunks: the [n, width] uint8 column whose 8-byte chunks are `chunks`."""
+    dev = _require_cuda(*chunks)
+    n = chunks[0].numel()
+    out = torch.empty((n, width), dtype=torch.uint8, device=dev)
+    if n:
+        with torch.cuda.device(dev):
+            for i, ch in enumerate(chunks):
+                off = 8 * i
+                _lib.call("b200x_unpack_key_bytes", ch.data_ptr(), ch.element_size(), min(8, width - off), out.data_ptr(),
+                          width, off, n, _stream(dev))
+    return out
 
 
 def search_sorted_codes(codes: torch.Tensor, bound_codes: torch.Tensor, upper: bool) -> torch.Tensor:

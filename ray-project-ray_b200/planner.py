@@ -122,48 +122,53 @@ def _byte_key_columns(blocks: List[DeviceBlock], sort_key: SortKey) -> List[str]
 
 
 def _expand_byte_keys(refs: List[RefBundle], sort_key: SortKey, byte_cols: List[str]):
-    """A w-byte string key sorts like the tuple of its big-endian 8-byte chunks: add those chunks as
-    uint64 columns `<name>::be<i>` and sort by them (every scheduler, the boundary sampling and the
-    multi-GPU exchange then see an ordinary multi-column integer key)."""
-    new_cols, derived = [], []
-    out_refs = []
+    """A w-byte string key sorts like the tuple of its big-endian 8-byte chunks: replace the key column by
+    those chunks as unsigned integer columns `<name>::be<i>` and sort by them (every scheduler, the boundary
+    sampling and the multi-GPU exchange then see an ordinary multi-column integer key). The chunks hold
+    every byte of the key, so the key column itself does not travel: it is rebuilt from the sorted chunks."""
+    out_refs, width, order = [], {}, None
     for ref in refs:
         pairs = []
         for block, _ in ref.blocks:
             if block.columns:
-                cols = dict(block.columns)
-                for k in byte_cols:
-                    for i, chunk in enumerate(ops.byte_key_chunks(_contig(block.columns[k]))):
-                        cols[f"{k}{BYTE_KEY_SEP}{i}"] = chunk
+                order = order or list(block.columns)
+                cols = {}
+                for name, col in block.columns.items():
+                    if name in byte_cols:
+                        width[name] = int(col.shape[1])
+                        for i, chunk in enumerate(ops.byte_key_chunks(_contig(col))):
+                            cols[f"{name}{BYTE_KEY_SEP}{i}"] = chunk
+                    else:
+                        cols[name] = col
                 block = DeviceBlock(cols, num_rows=block.num_rows, device=block.device)
             pairs.append((block, DeviceBlockAccessor(block).get_metadata(None, None)))
         out_refs.append(RefBundle(pairs, owns_blocks=ref.owns_blocks))
-    width = {}
-    for ref in refs:
-        for block, _ in ref.blocks:
-            if block.columns:
-                width = {k: block.columns[k].shape[1] for k in byte_cols}
-                break
-        if width:
-            break
+    new_cols = []
     for k in sort_key.get_columns():
         if k in byte_cols:
-            names = [f"{k}{BYTE_KEY_SEP}{i}" for i in range((width[k] + 7) // 8)]
-            new_cols += names
-            derived += names
+            new_cols += [f"{k}{BYTE_KEY_SEP}{i}" for i in range((width[k] + 7) // 8)]
         else:
             new_cols.append(k)
-    return out_refs, SortKey(new_cols, descending=[sort_key.get_descending()] * len(new_cols)), derived
+    new_key = SortKey(new_cols, descending=[sort_key.get_descending()] * len(new_cols))
+    return out_refs, new_key, (width, order)
 
 
-def _drop_columns(refs: List[RefBundle], names: List[str]) -> List[RefBundle]:
+def _restore_byte_keys(refs: List[RefBundle], packed) -> List[RefBundle]:
+    """Undo _expand_byte_keys on the output blocks: chunks -> key column, original column order."""
+    width, order = packed
     out = []
     for ref in refs:
         pairs = []
         for block, meta in ref.blocks:
             if block.columns:
-                block = DeviceBlock({k: v for k, v in block.columns.items() if k not in names},
-                                    num_rows=block.num_rows, device=block.device)
+                cols = {}
+                for name in order:
+                    if name in width:
+                        chunks = [_contig(block.columns[f"{name}{BYTE_KEY_SEP}{i}"]) for i in range((width[name] + 7) // 8)]
+                        cols[name] = ops.unpack_key_bytes(chunks, width[name])
+                    else:
+                        cols[name] = block.columns[name]
+                block = DeviceBlock(cols, num_rows=block.num_rows, device=block.device)
                 meta = DeviceBlockAccessor(block).get_metadata(None, exec_stats=meta.exec_stats)
             pairs.append((block, meta))
         out.append(RefBundle(pairs, owns_blocks=ref.owns_blocks))
@@ -183,9 +188,9 @@ def generate_sort_fn(sort_key: SortKey,
         if byte_cols:
             if sort_key.boundaries:
                 raise ValueError("user-specified boundaries are numeric; they cannot cut a byte-string key")
-            refs2, sort_key2, derived = _expand_byte_keys(refs, sort_key, byte_cols)
+            refs2, sort_key2, packed = _expand_byte_keys(refs, sort_key, byte_cols)
             out, stats = fn(sort_key2, refs2, ctx)
-            return _drop_columns(out, derived), stats
+            return _restore_byte_keys(out, packed), stats
         num_outputs = len(blocks)  # same number of output partitions as mappers
         if not sort_key.boundaries and DataContext.get_current().use_fused_device_exchange:
             boundaries = AutoBoundaries(num_outputs)  # the fused scheduler cuts the sorted result itself

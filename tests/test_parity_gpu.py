@@ -450,10 +450,18 @@ def test_sort_by_byte_string_key(sched, desc, cuda_device):
     np.testing.assert_array_equal(got2["row"], row[order])
     # the packing kernel itself
     t = torch.from_numpy(key).to(cuda_device)
-    hi = ops.pack_key_bytes(t, 0, 8).cpu().numpy().view(np.uint64)
-    lo = ops.pack_key_bytes(t, 8, 2).cpu().numpy().view(np.uint64)
-    np.testing.assert_array_equal(hi, key[:, :8].copy().view(">u8").astype(np.uint64).ravel())
-    np.testing.assert_array_equal(lo, (key[:, 8].astype(np.uint64) << np.uint64(56)) | (key[:, 9].astype(np.uint64) << np.uint64(48)))
+    hi = ops.pack_key_bytes(t, 0, 8)
+    lo = ops.pack_key_bytes(t, 8, 2)
+    assert hi.dtype == torch.uint64 and lo.dtype == torch.uint16
+    np.testing.assert_array_equal(hi.view(torch.int64).cpu().numpy().view(np.uint64),
+                                  key[:, :8].copy().view(">u8").astype(np.uint64).ravel())
+    np.testing.assert_array_equal(lo.view(torch.int16).cpu().numpy().view(np.uint16),
+                                  (key[:, 8].astype(np.uint16) << 8) | key[:, 9].astype(np.uint16))
+    np.testing.assert_array_equal(ops.unpack_key_bytes([hi, lo], 10).cpu().numpy(), key)
+    k3 = torch.from_numpy(key[:, :3].copy()).to(cuda_device)
+    c3 = ops.byte_key_chunks(k3)
+    assert len(c3) == 1 and c3[0].dtype == torch.uint32
+    np.testing.assert_array_equal(ops.unpack_key_bytes(c3, 3).cpu().numpy(), key[:, :3])
     with pytest.raises(ValueError):
         ds.sort("key", boundaries=[1, 2])
 
@@ -486,3 +494,25 @@ def test_iter_batches_across_blocks_and_local_shuffle(cuda_device):
         next(iter(ds.iter_batches(batch_size=None, local_shuffle_buffer_size=10)))
     order = [int(b["id"][0]) for b in rd.range(90, override_num_blocks=9).randomize_block_order(seed=42).iter_batches(batch_size=None)]
     assert order == [10 * i for i in G.batcher()["randomize_block_order"]["42"]]
+
+
+def test_multi_column_sort_first_column_distinct_shortcut(cuda_device):
+    """Multi-column keys whose first column has no duplicates need only the sort by that column; one
+    duplicate anywhere must send the sort down the full chain. Both against the oracle's lexicographic order."""
+    rng = np.random.default_rng(31)
+    n = 300_000
+    a = rng.permutation(n).astype(np.int64) * 7 - 1000          # all distinct
+    b = rng.integers(0, 5, n, dtype=np.int64)
+    row = np.arange(n, dtype=np.int64)
+    for desc in (False, True):
+        got = rd.from_numpy_columns({"a": a, "b": b, "row": row}, override_num_blocks=4).sort(["a", "b"], descending=desc).to_numpy()
+        np.testing.assert_array_equal(got["row"], row[orc.stable_argsort_multi([a, b], desc)])
+        a2 = a.copy()
+        a2[123_456] = a2[17]                                      # one tie: b decides it, the sample does not see it
+        b2 = b.copy()
+        b2[123_456], b2[17] = (0, 4)
+        got = rd.from_numpy_columns({"a": a2, "b": b2, "row": row}, override_num_blocks=4).sort(["a", "b"], descending=desc).to_numpy()
+        np.testing.assert_array_equal(got["row"], row[orc.stable_argsort_multi([a2, b2], desc)])
+        f = rng.standard_normal(n)                                # float first column (codes are probed)
+        got = rd.from_numpy_columns({"f": f, "b": b, "row": row}, override_num_blocks=4).sort(["f", "b"], descending=desc).to_numpy()
+        np.testing.assert_array_equal(got["row"], row[orc.stable_argsort_multi([f, b], desc)])
