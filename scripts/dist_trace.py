@@ -10,10 +10,12 @@ from ray_project_ray_b200.sort_task_spec import SortKey
 rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
 torch.cuda.set_device(rank); dev = torch.device("cuda", rank)
 dist.init_process_group("nccl", device_id=dev)
-n = 100_000_000
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 100_000_000
+PAY = int(sys.argv[2]) if len(sys.argv) > 2 else 64   # payload bytes per row (90: gensort)
+ITERS = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 g = torch.Generator(device=dev).manual_seed(rank)
 k = torch.randint(0, 2**63 - 1, (n,), dtype=torch.int64, device=dev, generator=g)
-p = torch.empty((n, 64), dtype=torch.uint8, device=dev)
+p = torch.empty((n, PAY), dtype=torch.uint8, device=dev)
 local = DeviceBlock({"id": k, "payload": p})
 sk = SortKey("id")
 def T(label, t0):
@@ -21,7 +23,7 @@ def T(label, t0):
     t = time.perf_counter()
     if rank == 0: print(f"{label:34s} {(t - t0) * 1e3:8.2f} ms", flush=True)
     return time.perf_counter()
-for it in range(3):
+for it in range(ITERS):
     torch.cuda.synchronize(); dist.barrier(); t = time.perf_counter()
     if rank == 0: print("---- iteration", it)
     assert D.p2p_available(dev)
@@ -46,7 +48,7 @@ for it in range(3):
 # overlap experiment: received-key sort on a side stream while the payload scatter runs on the main stream
 side = D._side_stream(dev)
 from ray_project_ray_b200 import _lib
-for bps in (0, 0, 1, 2, 4):
+for bps in ((0, 0, 1, 2, 4) if len(sys.argv) <= 4 else ()):
     _lib.call("b200x_set_tuning", 1, bps)
     torch.cuda.synchronize(); dist.barrier(); t = time.perf_counter()
     ex.fence(); ex.send(["payload"]); ex.fence()
