@@ -377,6 +377,176 @@ scatter_rows_staged_kernel(const V* __restrict__ src, const uint32_t* __restrict
   }
 }
 
+
+// Realigning variant for rows whose width is not a multiple of 16 bytes (gensort's 90-byte payload, 10- or
+// 2-byte key pieces): moving such rows chunk by chunk means 2-byte (or 1-byte) loads and stores - 45 remote
+// stores per 90-byte row. Here the tile of consecutive source rows is copied into shared memory with 16-byte
+// loads (the tile starts 16-byte aligned: tile_rows is a multiple of 16), and every owner's rows - one
+// contiguous byte range at the destination - leave as ALIGNED 16-byte stores: each thread assembles one
+// destination vector from the shared-memory image (five word loads and funnel shifts when its 16 bytes lie in
+// one row, a byte loop when they span two rows). The last vector of a range is usually shared with the next
+// rows of the same owner, which lie in a later tile: the block looks ahead in `target` for that owner's next
+// row, takes the missing bytes from it and stores the whole vector, and the later tile skips its first,
+// partial vector (single-byte stores are separate NVLink packets: with them a 90-byte payload moved at half
+// the link rate). Only the first vector of a rank's whole range for an owner, and the last one when no further
+// row of that owner exists, are written byte by byte.
+constexpr int RA_THREADS = 256;
+constexpr int RA_MAX_TILE = 1024;
+constexpr int RA_DATA_BYTES = 32 * 1024;
+
+__global__ void __launch_bounds__(RA_THREADS)
+scatter_rows_realign_kernel(const unsigned char* __restrict__ src, const uint32_t* __restrict__ target, const PeerPlan p,
+                            uint64_t n, uint32_t W, uint32_t magic /* ceil(2^32 / W) */, uint32_t tile_rows) {
+  extern __shared__ __align__(16) unsigned char ra_raw[];
+  unsigned char* img = ra_raw;                                                 // [tile_rows * W] (+ 16 bytes of slack)
+  uint16_t* srow = reinterpret_cast<uint16_t*>(ra_raw + RA_DATA_BYTES + 32);   // [tile_rows] tile row at staged position
+  __shared__ uint32_t s_cnt[MAX_PEERS], s_min[MAX_PEERS], s_off[MAX_PEERS], s_vec0[MAX_PEERS + 1];
+  __shared__ unsigned long long s_dst[MAX_PEERS], s_next[MAX_PEERS];
+  __shared__ uint32_t s_missing;
+  constexpr unsigned long long NONE = ~0ull;
+  const uint64_t num_tiles = (n + tile_rows - 1) / tile_rows;
+  for (uint64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    const uint64_t r0 = tile * tile_rows;
+    const uint32_t rows = (uint32_t)min((uint64_t)tile_rows, n - r0);
+    if (threadIdx.x < MAX_PEERS) {
+      s_cnt[threadIdx.x] = 0;
+      s_min[threadIdx.x] = 0xFFFFFFFFu;
+      s_next[threadIdx.x] = NONE;
+    }
+    __syncthreads();
+    constexpr int RPT = RA_MAX_TILE / RA_THREADS;
+    uint32_t tg[RPT];
+#pragma unroll
+    for (int k = 0; k < RPT; ++k) {
+      const uint32_t lr = threadIdx.x + k * RA_THREADS;
+      tg[k] = 0;
+      if (lr < rows) {
+        tg[k] = target[r0 + lr];
+        const uint32_t d = tg[k] >> SLOT_BITS, slot = tg[k] & ((1u << SLOT_BITS) - 1u);
+        atomicAdd(&s_cnt[d], 1u);
+        atomicMin(&s_min[d], slot);
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t run = 0, vec = 0;
+      for (int d = 0; d < MAX_PEERS; ++d) {
+        s_off[d] = run;
+        s_vec0[d] = vec;
+        if (s_cnt[d]) {
+          const unsigned long long g = (unsigned long long)(p.base[d]) + (p.row_off[d] + s_min[d]) * (unsigned long long)W;
+          s_dst[d] = g;
+          // vectors are counted from the 128-byte line the range starts in, and every owner's count is padded to
+          // a multiple of 32: a warp then always stores four whole 128-byte lines (full-line NVLink packets)
+          vec += (((uint32_t)(g & 127ull) + s_cnt[d] * W + 15u) / 16u + 31u) & ~31u;
+        }
+        run += s_cnt[d];
+      }
+      s_vec0[MAX_PEERS] = vec;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < RPT; ++k) {
+      const uint32_t lr = threadIdx.x + k * RA_THREADS;
+      if (lr < rows) {
+        const uint32_t d = tg[k] >> SLOT_BITS, slot = tg[k] & ((1u << SLOT_BITS) - 1u);
+        srow[s_off[d] + (slot - s_min[d])] = (uint16_t)lr;  // the slots of one owner inside a tile are consecutive
+      }
+    }
+    // the tile as it lies in the source: sequential 16-byte loads
+    const uint32_t tbytes = rows * W;
+    const unsigned char* tsrc = src + r0 * W;
+    const uint32_t nvec = tbytes / 16;
+    for (uint32_t i = threadIdx.x; i < nvec; i += RA_THREADS)
+      reinterpret_cast<uint4*>(img)[i] = reinterpret_cast<const uint4*>(tsrc)[i];
+    for (uint32_t i = nvec * 16 + threadIdx.x; i < tbytes; i += RA_THREADS) img[i] = tsrc[i];
+    // look ahead: the next row of every owner whose range ends inside a vector
+    for (uint64_t base = r0 + rows; base < n; base += RA_THREADS) {
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        uint32_t missing = 0;
+        for (int d = 0; d < MAX_PEERS; ++d)
+          missing += (s_cnt[d] && ((s_dst[d] + (unsigned long long)s_cnt[d] * W) & 15ull) && s_next[d] == NONE) ? 1u : 0u;
+        s_missing = missing;
+      }
+      __syncthreads();
+      if (s_missing == 0) break;
+      const uint64_t i = base + threadIdx.x;
+      if (i < n) atomicMin(&s_next[target[i] >> SLOT_BITS], (unsigned long long)i);
+    }
+    __syncthreads();
+    const uint32_t total = s_vec0[MAX_PEERS];
+    const uint32_t* img32 = reinterpret_cast<const uint32_t*>(img);
+    for (uint32_t t = threadIdx.x; t < total; t += RA_THREADS) {
+      uint32_t d = 0;
+      while (t >= s_vec0[d + 1]) ++d;
+      const uint32_t k = t - s_vec0[d];
+      const unsigned long long g = s_dst[d];
+      const uint32_t a = (uint32_t)(g & 127ull), L = s_cnt[d] * W, first = s_off[d];
+      const int lo = (int)(16u * k) - (int)a;  // position of the vector's first byte inside the owner's byte range
+      if (lo + 16 <= 0 || lo >= (int)L) continue;  // before the range (line padding) or after it (warp padding)
+      unsigned char* gp = reinterpret_cast<unsigned char*>(g - a) + 16ull * k;
+      if (lo >= 0 && (uint32_t)lo + 16u <= L) {
+        const uint32_t q = __umulhi((uint32_t)lo, magic), w = (uint32_t)lo - q * W;
+        const uint32_t rowA = (uint32_t)srow[first + q] * W;
+        uint4 v;
+        if (w + 16u <= W) {
+          const uint32_t A0 = rowA + w, wi = A0 >> 2, sh = (A0 & 3u) * 8u;
+          const uint32_t x0 = img32[wi], x1 = img32[wi + 1], x2 = img32[wi + 2], x3 = img32[wi + 3], x4 = img32[wi + 4];
+          v.x = __funnelshift_r(x0, x1, sh);
+          v.y = __funnelshift_r(x1, x2, sh);
+          v.z = __funnelshift_r(x2, x3, sh);
+          v.w = __funnelshift_r(x3, x4, sh);
+        } else {
+          const uint32_t rowB = (uint32_t)srow[first + q + 1] * W;
+          uint32_t out[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+          for (uint32_t j = 0; j < 16; ++j) {
+            const uint32_t b = (w + j < W) ? img[rowA + w + j] : img[rowB + (w + j - W)];
+            out[j >> 2] |= b << ((j & 3u) * 8u);
+          }
+          v = make_uint4(out[0], out[1], out[2], out[3]);
+        }
+        *reinterpret_cast<uint4*>(gp) = v;
+      } else if (lo < 0) {
+        // first vector of the range: an earlier tile of this rank completes it unless these are the rank's first rows
+        if (s_min[d] == 0) {
+          for (int o = 0; o < lo + 16; ++o) {
+            const uint32_t q = __umulhi((uint32_t)o, magic), w = (uint32_t)o - q * W;
+            gp[o - lo] = img[(uint32_t)srow[first + q] * W + w];
+          }
+        }
+      } else {
+        // last vector: mine are the first L - lo bytes; the rest is the beginning of the owner's next row
+        const uint32_t mine = L - (uint32_t)lo;
+        const unsigned long long nxt = s_next[d];
+        if (nxt != NONE) {
+          const unsigned char* nrow = src + nxt * W;
+          uint32_t out[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+          for (uint32_t j = 0; j < 16; ++j) {
+            uint32_t b;
+            if (j < mine) {
+              const uint32_t o = (uint32_t)lo + j, q = __umulhi(o, magic), w = o - q * W;
+              b = img[(uint32_t)srow[first + q] * W + w];
+            } else {
+              b = nrow[j - mine];
+            }
+            out[j >> 2] |= b << ((j & 3u) * 8u);
+          }
+          *reinterpret_cast<uint4*>(gp) = make_uint4(out[0], out[1], out[2], out[3]);
+        } else {
+          for (uint32_t j = 0; j < mine; ++j) {
+            const uint32_t o = (uint32_t)lo + j, q = __umulhi(o, magic), w = o - q * W;
+            gp[j] = img[(uint32_t)srow[first + q] * W + w];
+          }
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
 }  // namespace b200x
 
 extern "C" int b200x_partition_targets(const void* keys, int key_type, int descending, size_t n,
@@ -455,6 +625,22 @@ extern "C" int b200x_scatter_rows_by_target(const void* src, size_t row_bytes, c
   while (v > 1 && (al & (uintptr_t)(v - 1)) != 0) v >>= 1;
   const uint32_t vpr = (uint32_t)(row_bytes / v);
   const uint64_t total = (uint64_t)n * vpr;
+  if (v < 16 && row_bytes >= 24 && row_bytes <= 1024 && ((uintptr_t)src & 15) == 0) {
+    // rows that do not split into 16-byte pieces: realign in shared memory, store aligned vectors
+    uint32_t tile_rows = (uint32_t)(RA_DATA_BYTES / row_bytes) / 16 * 16;
+    if (tile_rows > (uint32_t)RA_MAX_TILE) tile_rows = RA_MAX_TILE;
+    const size_t smem = RA_DATA_BYTES + 32 + RA_MAX_TILE * sizeof(uint16_t);
+    uint64_t gtiles = (n + tile_rows - 1) / tile_rows;
+    if (g_scatter_blocks_per_sm > 0 && gtiles > (uint64_t)sm_count() * g_scatter_blocks_per_sm)
+      gtiles = (uint64_t)sm_count() * g_scatter_blocks_per_sm;
+    const uint32_t magic = (uint32_t)((0x100000000ull + row_bytes - 1) / row_bytes);
+    prof_begin(stream, PROF_GATHER);
+    scatter_rows_realign_kernel<<<(uint32_t)gtiles, RA_THREADS, smem, stream>>>((const unsigned char*)src, target, p, n,
+                                                                                (uint32_t)row_bytes, magic, tile_rows);
+    prof_end(stream);
+    B200X_LAUNCH_CHECK("scatter_rows_realign_kernel");
+    return B200X_OK;
+  }
   if (row_bytes <= 128) {
     uint32_t tile_rows = (uint32_t)(ST_DATA_BYTES / row_bytes) / ST_THREADS * ST_THREADS;
     if (tile_rows > (uint32_t)ST_MAX_TILE) tile_rows = ST_MAX_TILE;

@@ -104,6 +104,8 @@ gather_cols8_kernel(const ColPtrs p, int ncols, const uint32_t* __restrict__ idx
   }
 }
 
+
+
 __global__ void __launch_bounds__(256) iota_kernel(uint32_t* out, uint64_t n, uint32_t start) {
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
     out[i] = start + (uint32_t)i;

@@ -191,7 +191,9 @@ def test_argsort_uint64_and_uint16(cuda_device):
 
 @pytest.mark.parametrize("shape,dtype", [((1000,), np.int64), ((1000,), np.float64), ((5000, 8), np.int64),
                                          ((3000, 64), np.uint8), ((3000, 90), np.uint8), ((3000, 100), np.uint8),
-                                         ((777, 3), np.int16), ((1000,), np.int32), ((1000,), np.uint8), ((0, 8), np.int64)])
+                                         ((777, 3), np.int16), ((1000,), np.int32), ((1000,), np.uint8), ((0, 8), np.int64),
+                                         ((100_003, 90), np.uint8), ((70_001, 25), np.uint8), ((40_000, 82), np.uint8),
+                                         ((33_333, 31), np.uint8), ((5_001, 1000), np.uint8), ((9_999, 10), np.int16)])
 def test_gather_rows(cuda_device, shape, dtype):
     rng = np.random.default_rng(7)
     src = rng.integers(0, 120, shape).astype(dtype)
@@ -327,3 +329,14 @@ def test_partition_targets_and_scatter(cuda_device, n, world, descending):
     for d in range(world):
         np.testing.assert_array_equal(bufs[d].cpu().numpy()[3:], pay[owner == d])
         np.testing.assert_array_equal(kbufs[d].cpu().numpy()[3:], keys[owner == d])
+    # row widths that are not a multiple of 16 bytes (realigned in shared memory, aligned 16-byte stores):
+    # exact contents, and nothing written before the first or after the last row of any owner
+    for w, off in ((90, 3), (82, 1), (30, 0), (100, 5), (17, 2), (25, 7)):
+        pw = rng.integers(1, 256, (n, w), dtype=np.uint8)
+        t_pw = torch.from_numpy(pw).to(cuda_device)
+        wb = [torch.zeros((int(want_counts[d]) + off + 2, w), dtype=torch.uint8, device=cuda_device) for d in range(world)]
+        ops.scatter_rows_by_target(t_pw, target, [b.data_ptr() for b in wb], [off] * world)
+        for d in range(world):
+            got = wb[d].cpu().numpy()
+            np.testing.assert_array_equal(got[off:off + int(want_counts[d])], pw[owner == d])
+            assert not got[:off].any() and not got[off + int(want_counts[d]):].any()
