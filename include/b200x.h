@@ -63,8 +63,10 @@ int b200x_profile_read(int kernel, double* total_ms, int* launches);
 /* Stable argsort of one key column. Radix sort on order-preserving 64-bit codes with 8-bit digits
  * and decoupled look-back ("onesweep" passes). The device inspects the keys and picks
  *   - LSD: one pass per varying byte (constant bytes are skipped), or
- *   - HYBRID: two passes on the top 16 varying bits, then each of the <= 65536 runs is finished
- *     in shared memory (3 trips through HBM instead of up to 8) when keys are spread out.
+ *   - HYBRID: two passes group the pairs into <= 65536 runs by a monotone function of the key - the top
+ *     16 bits of (code - smallest code), or, for skewed distributions, a sampled bucket table that
+ *     equalises the runs - then each run is finished in shared memory (3 trips through HBM instead of
+ *     up to 8). Chosen when no run exceeds 8192 pairs; duplicate-heavy columns fall back to LSD.
  *   perm_out[i] = row that lands at sorted position i
  *   codes_out   = (optional, may be NULL) the sorted order-preserving 64-bit key codes;
  *                 ascending for both sort directions (see b200x_encode_keys)
