@@ -129,3 +129,55 @@ def test_config3_groupby_200m_rows_1m_keys(cuda_device, skew):
     want_sums = torch.zeros(K, dtype=torch.int64, device=cuda_device).scatter_add_(0, k, v)
     assert torch.equal(sums, want_sums[present])                            # exact integer sums
     torch.testing.assert_close(means, sums.double() / counts.double(), rtol=1e-6, atol=0)
+
+
+def test_config4_shape_gensort_records_30m(cuda_device):
+    """configs[3] shape on one GPU: 100-byte records = 10-byte key + 90-byte payload, sorted by the byte-string
+    key. Checked by the packed key (8 big-endian bytes, then 2), row integrity (the payload's first 8 bytes are
+    the record number, from which the key can be recomputed) and the record-number checksum."""
+    from ray_project_ray_b200 import ops
+
+    n = 30_000_000
+    g = torch.Generator(device=cuda_device).manual_seed(9)
+    recno = torch.arange(n, dtype=torch.int64, device=cuda_device)
+    key = torch.empty((n, 10), dtype=torch.uint8, device=cuda_device)
+    key[:, :8] = _mix(recno).view(torch.uint8).reshape(n, 8)
+    key[:, 8:] = _mix(recno + 12345).view(torch.uint8).reshape(n, 8)[:, :2]
+    key[: n // 1000, :8] = key[0, :8]                        # 30 000 records tie on the first 8 bytes: the last 2 decide
+    payload = torch.randint(0, 256, (n, 90), dtype=torch.uint8, device=cuda_device, generator=g)
+    payload[:, :8] = recno.view(torch.uint8).reshape(n, 8)
+    out = rd.from_torch_columns({"key": key, "payload": payload}, override_num_blocks=4).sort("key")
+    assert out.columns() == ["key", "payload"] and out.count() == n and out.num_blocks() == 4
+    skey = torch.cat([b["key"] for b in out.get_internal_block_refs()])
+    spay = torch.cat([b["payload"] for b in out.get_internal_block_refs()])
+    hi = ops.pack_key_bytes(skey, 0, 8).view(torch.int64) ^ (-0x8000000000000000)   # unsigned order as signed
+    lo = ops.pack_key_bytes(skey, 8, 2).view(torch.int16).to(torch.int32) & 0xFFFF
+    assert bool(((hi[1:] > hi[:-1]) | ((hi[1:] == hi[:-1]) & (lo[1:] >= lo[:-1]))).all())
+    got_rec = spay[:, :8].contiguous().view(torch.int64).flatten()
+    assert torch.equal(skey, key[got_rec])                                           # every payload still has its key
+    assert int(got_rec.sum().item()) == n * (n - 1) // 2
+
+
+def test_config5_shape_zipf_keys_50m(cuda_device):
+    """configs[4] shape on one GPU: Zipf(1.2) int64 keys (ranks hashed over the key space): heavy duplicates send
+    the sort down its LSD path. Sortedness, stability (equal keys keep their row order) and the multiset."""
+    n, K = 50_000_000, 1 << 22
+    g = torch.Generator(device=cuda_device).manual_seed(12)
+    w = torch.arange(1, K + 1, device=cuda_device, dtype=torch.float64).pow(-1.2)
+    cdf = torch.cumsum(w, 0)
+    cdf /= cdf[-1].clone()
+    ranks = torch.searchsorted(cdf, torch.rand(n, device=cuda_device, dtype=torch.float64, generator=g)).clamp_(max=K - 1)
+    k = _mix(ranks)                                           # spread the ranks over the int64 space
+    del ranks, cdf, w
+    row = torch.arange(n, dtype=torch.int64, device=cuda_device)
+    out = rd.from_torch_columns({"k": k, "row": row}, override_num_blocks=8).sort("k")
+    sk = torch.cat([b["k"] for b in out.get_internal_block_refs()])
+    sr = torch.cat([b["row"] for b in out.get_internal_block_refs()])
+    assert bool((sk[1:] >= sk[:-1]).all())
+    assert bool(((sk[1:] > sk[:-1]) | (sr[1:] > sr[:-1])).all())                     # ties in input order
+    assert torch.equal(k[sr], sk)
+    assert int(sr.sum().item()) == n * (n - 1) // 2
+    blocks = out.get_internal_block_refs()                                           # equal keys never straddle blocks
+    for a, b in zip(blocks[:-1], blocks[1:]):
+        if a.num_rows and b.num_rows:
+            assert int(a["k"][-1]) < int(b["k"][0])
