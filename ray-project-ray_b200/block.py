@@ -457,11 +457,19 @@ class DeviceBlockAccessor(BlockAccessor):
             return None
         return perm, (codes if want_codes else None), skeys
 
-    def sort(self, sort_key: "SortKey", want_codes: bool = False):
-        """Whole block in sorted order (transform_pyarrow.sort: sort_indices + take)."""
+    def sort(self, sort_key: "SortKey", want_codes: bool = False, on_sorted_key=None):
+        """Whole block in sorted order (transform_pyarrow.sort: sort_indices + take).
+
+        `on_sorted_key(column)`, if given, is called with the sorted first key column as soon as it exists
+        and before the other columns are gathered: work that only needs the keys (cutting the result into
+        blocks, including its device -> host read) then overlaps the payload gather."""
         b = self._block
         perm, codes, skeys = self._argsort(sort_key, want_codes)
         first_key = sort_key.get_columns()[0]
+        if skeys is None and on_sorted_key is not None:  # float keys are gathered, not decoded by the sort
+            skeys = ops.gather(_contig(b.columns[first_key]), perm)
+        if on_sorted_key is not None:
+            on_sorted_key(skeys)
         names = [k for k in b.column_names if not (skeys is not None and k == first_key)]
         outs = ops.gather_columns([_contig(b.columns[k]) for k in names], perm)
         cols = dict(zip(names, outs))

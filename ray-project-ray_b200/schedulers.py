@@ -418,6 +418,33 @@ def _distributed_exchange(spec: ExchangeTaskSpec, blocks: List[DeviceBlock], out
     return _cut_sorted_evenly(out, k, False, parts)
 
 
+class _AsyncCuts:
+    """even_cuts of a sorted key column with an asynchronous device -> host read of the positions."""
+
+    _pinned: Dict[int, torch.Tensor] = {}
+
+    def __init__(self, descending: bool, parts: int):
+        self.descending, self.parts = descending, parts
+        self._event = None
+        self._host = None
+
+    def start(self, sorted_keys: torch.Tensor) -> None:
+        dev = sorted_keys.device
+        cuts = ops.even_cuts(_contig(sorted_keys), self.descending, self.parts)
+        host = self._pinned.get(self.parts)
+        if host is None or host.numel() != cuts.numel():
+            host = torch.empty(cuts.numel(), dtype=torch.int64).pin_memory()
+            self._pinned[self.parts] = host
+        host.copy_(cuts, non_blocking=True)
+        self._event = torch.cuda.Event()
+        self._event.record(torch.cuda.current_stream(dev))
+        self._host, self._keep = host, cuts
+
+    def result(self) -> List[int]:
+        self._event.synchronize()
+        return [int(c) for c in self._host.tolist()]
+
+
 def _cut(table: DeviceBlock, cuts: List[int]) -> List[DeviceBlock]:
     parts, last = [], 0
     for idx in cuts:
@@ -437,10 +464,16 @@ def fused_sort(blocks: List[DeviceBlock], boundaries: List[Any], sort_key: SortK
     if table.num_rows == 0:
         return [DeviceBlock.empty(table.device) for _ in range(R)]
     acc = DeviceBlockAccessor(table)
+    first = sort_key.get_columns()[0]
+    if isinstance(boundaries, AutoBoundaries) and R > 1:
+        # The cut positions only need the sorted keys: they are computed and read back while the payload
+        # gather is still running, so the host is already enqueuing the next operator when the gather ends.
+        cuts = _AsyncCuts(sort_key.get_descending(), R)
+        out, _ = acc.sort(sort_key, on_sorted_key=cuts.start)
+        return _cut(out, cuts.result())
     out, _ = acc.sort(sort_key)
     if R == 1:
         return [out]
-    first = sort_key.get_columns()[0]
     if isinstance(boundaries, AutoBoundaries):
         return _cut_sorted_evenly(out, first, sort_key.get_descending(), R)
     if any(b is None or (isinstance(b, tuple) and b[0] is None) for b in boundaries):
