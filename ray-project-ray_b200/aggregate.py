@@ -23,13 +23,12 @@ always true in the reference's null wrappers, _internal/null_aggregate.py:28-250
 """
 from __future__ import annotations
 
-from typing import Callable, Dict, List, Optional, Sequence, Tuple, Union
+from typing import Callable, Dict, List, Optional, Sequence
 
-import numpy as np
 import torch
 
 from . import ops
-from .block import DeviceBlock, KeyType, AggType, _contig
+from .block import DeviceBlock, _contig
 
 SEP = "::"
 

@@ -23,8 +23,6 @@ movement inside a rank is the C-ABI kernels.
 from __future__ import annotations
 
 import os
-
-import math
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import numpy as np

@@ -9,8 +9,8 @@ There is no object store here: a "block ref" is the DeviceBlock itself.
 """
 from __future__ import annotations
 
-from dataclasses import dataclass, field
-from typing import Any, Callable, Dict, Iterator, List, Optional, Tuple, Union
+from dataclasses import dataclass
+from typing import Any, Callable, Dict, List, Optional, Tuple, Union
 
 from .block import Block, BlockMetadata, DeviceBlock
 from .context import DataContext

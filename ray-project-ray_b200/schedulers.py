@@ -22,11 +22,10 @@ from typing import Any, Dict, List, Optional, Tuple
 import torch
 
 from . import ops
-from .aggregate import aggregate_sorted, resolved_names
+from .aggregate import aggregate_sorted
 from .aggregate_task_spec import SortAggregateTaskSpec
 from .block import (Block, BlockAccessor, BlockExecStats, BlockMetadata, DeviceBlock, DeviceBlockAccessor,
                     _as_device_block, _contig, find_partition_indices)
-from .context import DataContext
 from .interfaces import ExchangeTaskScheduler, ExchangeTaskSpec, RefBundle, StatsDict, TaskContext
 from .shuffle_task_spec import ShuffleTaskSpec
 from .sort_task_spec import SortKey, SortTaskSpec
