@@ -54,7 +54,8 @@ int b200x_device_count(void);
  * and CUDA-event timing of the main kernels on their launching stream: enable(1) clears the
  * record and starts recording one event pair per launch on the calling thread; read(kernel, ...)
  * synchronises and returns the summed duration and the launch count of one kernel class
- * (0 radix pass, 1 row gather, 2 run finisher, 3 joint histogram, 6 LSD histogram). Launches that
+ * (0 radix pass, 1 row gather, 2 run finisher, 3 digit histogram, 4 row permutation, 5 segmented reduce,
+ * 6 LSD histogram, 7 peer scatter). Launches that
  * return at once because the device chose the other sort path are not counted. */
 unsigned long long b200x_launch_count(void);
 int b200x_profile_enable(int on);

@@ -46,7 +46,7 @@ void count_launch();
 // Optional CUDA-event bracket around kernel launches, recorded on the launching stream while
 // b200x_profile_enable(1) is in effect (bench.py's live per-kernel timing).
 enum ProfKernel : int { PROF_PASS = 0, PROF_GATHER = 1, PROF_FINISH = 2, PROF_JOINT = 3, PROF_PERMUTE = 4, PROF_SEGRED = 5,
-                        PROF_HIST = 6, PROF_COUNT = 7 };
+                        PROF_HIST = 6, PROF_SCATTER = 7, PROF_COUNT = 8 };
 void prof_begin(cudaStream_t s, int kernel);
 void prof_end(cudaStream_t s);
 

@@ -100,7 +100,7 @@ extern "C" int b200x_scatter_rows_to_peers(const void* src, size_t row_bytes, co
   if (blocks > cap) blocks = cap;
   if (blocks == 0) blocks = 1;
   const uint32_t g = (uint32_t)blocks;
-  prof_begin(stream, PROF_GATHER);
+  prof_begin(stream, PROF_SCATTER);
   switch (v) {
     case 16: scatter_rows_to_peers_kernel<uint4><<<g, 256, 0, stream>>>((const uint4*)src, perm, p, n, vpr); break;
     case 8: scatter_rows_to_peers_kernel<uint64_t><<<g, 256, 0, stream>>>((const uint64_t*)src, perm, p, n, vpr); break;
@@ -634,7 +634,7 @@ extern "C" int b200x_scatter_rows_by_target(const void* src, size_t row_bytes, c
     if (g_scatter_blocks_per_sm > 0 && gtiles > (uint64_t)sm_count() * g_scatter_blocks_per_sm)
       gtiles = (uint64_t)sm_count() * g_scatter_blocks_per_sm;
     const uint32_t magic = (uint32_t)((0x100000000ull + row_bytes - 1) / row_bytes);
-    prof_begin(stream, PROF_GATHER);
+    prof_begin(stream, PROF_SCATTER);
     scatter_rows_realign_kernel<<<(uint32_t)gtiles, RA_THREADS, smem, stream>>>((const unsigned char*)src, target, p, n,
                                                                                 (uint32_t)row_bytes, magic, tile_rows);
     prof_end(stream);
@@ -649,7 +649,7 @@ extern "C" int b200x_scatter_rows_by_target(const void* src, size_t row_bytes, c
     if (g_scatter_blocks_per_sm > 0 && gtiles > (uint64_t)sm_count() * g_scatter_blocks_per_sm)
       gtiles = (uint64_t)sm_count() * g_scatter_blocks_per_sm;
     const uint32_t g = (uint32_t)gtiles;
-    prof_begin(stream, PROF_GATHER);
+    prof_begin(stream, PROF_SCATTER);
     switch (v) {
       case 16: scatter_rows_staged_kernel<uint4><<<g, ST_THREADS, smem, stream>>>((const uint4*)src, target, p, n, vpr, tile_rows); break;
       case 8: scatter_rows_staged_kernel<uint64_t><<<g, ST_THREADS, smem, stream>>>((const uint64_t*)src, target, p, n, vpr, tile_rows); break;
@@ -666,7 +666,7 @@ extern "C" int b200x_scatter_rows_by_target(const void* src, size_t row_bytes, c
   if (blocks > cap) blocks = cap;
   if (blocks == 0) blocks = 1;
   const uint32_t g = (uint32_t)blocks;
-  prof_begin(stream, PROF_GATHER);
+  prof_begin(stream, PROF_SCATTER);
   switch (v) {
     case 16: scatter_rows_by_target_kernel<uint4><<<g, 256, 0, stream>>>((const uint4*)src, target, p, n, vpr); break;
     case 8: scatter_rows_by_target_kernel<uint64_t><<<g, 256, 0, stream>>>((const uint64_t*)src, target, p, n, vpr); break;
