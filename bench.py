@@ -1,20 +1,27 @@
 #!/usr/bin/env python
-"""Headline benchmark: Dataset.sort throughput on B200 (BASELINE.json `metric`).
+"""Headline benchmark: Dataset.sort throughput on B200 (BASELINE.json `metric`), on the workload
+`north_star` names: synthetic gensort-shaped records.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-Workload (config.workload = "sort_100Mx72B"): per GPU 100 M rows of (int64 key `id` drawn uniformly
-from [0, 2^63) as the reference's own sort benchmark draws them,
-release/nightly_tests/dataset/sort.py:39-47, + one 64-byte fixed-width `payload` column) — the
-row shape of BASELINE.json configs[1], the largest configuration that fits one GPU — sorted by
-`Dataset.sort("id")`. A step = one full sort of the resident dataset. N > 1: every rank holds
-100 M rows (weak scaling) and the sort is global (range-partitioned all-to-all over NCCL).
+Workload (config.workload = "gensort_125Mx100B"): per GPU 125 M records of 100 bytes = a 10-byte key
+(`key`, [n, 10] uint8, random bytes) + a 90-byte payload (`payload`, [n, 90] uint8: 8-byte record number,
+8-byte tag derived from key and record number, 74 filler bytes) - BASELINE.json configs[3], the reference's
+own sort benchmark uses 100-byte rows "to approximately match Cloudsort"
+(release/nightly_tests/dataset/sort.py:96-102). The dataset is held in the device block format's record
+layout (one 128-byte record per row) and sorted by `Dataset.sort("key")`: pyarrow's lexicographic byte
+order, stable. One row in 1024 repeats its predecessor's key and one in 4096 takes its key from a pool
+shared by all ranks, so that the order of equal keys (within and across ranks) is checked on the timed
+data. A step = one full sort of the resident dataset. N > 1: every rank holds 125 M records (weak scaling,
+100 GB at N = 8) and the sort is global (range-partitioned exchange over NVLink peer memory).
 
 Printed JSON (rank 0, one line): see DESIGN.md §Measurement for every key.
   value      rows/s, inputs resident in HBM, CUDA events around K steps, max over ranks
   e2e        same metric through the public API from pinned HOST buffers (H2D + sort + D2H per step)
-  roofline   the kernel with the largest share of the step, CUDA events on its launching stream (all kernels: `kernels`)
+  roofline   N = 1: the kernel with the largest share of the step (CUDA events on its launching stream) against
+             the measured HBM peak; N > 1: the step against the slower of the HBM / NVLink rooflines of SURVEY.md 8d
+  verified   checks of the output of the last timed step, at every N (outside the timed region)
   cpu_baseline  the reference's CPU path (port calling the same pyarrow kernels) on the host cores
 """
 from __future__ import annotations
@@ -31,21 +38,22 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-ROWS_PER_GPU = 100_000_000
-PAYLOAD_BYTES = 64
-ROW_BYTES = 8 + PAYLOAD_BYTES
-CPU_SAMPLE_ROWS = 100_000_000         # the CPU arm sorts the full single-GPU workload (a few seconds on 16+ cores)
+ROWS_PER_GPU = 125_000_000
+KEY_BYTES, PAYLOAD_BYTES = 10, 90
+ROW_BYTES = KEY_BYTES + PAYLOAD_BYTES
+RECORD_PITCH = 128
+CPU_SAMPLE_ROWS = 25_000_000          # rows the CPU arm sorts per step (a bounded sample of one GPU's 125 M)
+NVLINK_GBS = 900.0                    # nominal NVLink 5 bandwidth per direction and GPU
+TAG_MULT = 0x9E3779B97F4A7C15 - (1 << 64)   # odd 64-bit constant (as int64): tag = key_hi ^ (recno * TAG_MULT)
 # Algorithmic bytes per row of one launch of each timed kernel class, and the DRAM traffic
 # per row ncu measured for it (profiles/, dram__bytes_read.sum + dram__bytes_write.sum; None = not captured).
 KERNELS = {
     0: ("onesweep_pass_kernel", 22.0, 26.0),         # HYBRID: pass A reads 8 writes 12, pass B reads 12 writes 12
-    1: ("gather_rows_kernel<uint4>", 4 + 2 * PAYLOAD_BYTES, 197.6),  # index + read row + write row (64 B rows cost 128 B of DRAM reads)
+    1: ("gather_rows_pitched_kernel (128-byte records)", 4 + 2 * ROW_BYTES, None),  # index + read record + write record
     2: ("finish_runs_kernel", 12 + 4 + 8, 23.5),      # read pair, write row index + decoded key
     3: ("digit2_hist_kernel", 8.0, 8.0),              # read key column
     6: ("hist_kernel", 8.0, None),
-    # peer exchange (N > 1): the key column (8 B rows) and the payload (64 B rows) are each read and stored once,
-    # in one launch each: (2 * 8 + 2 * 64) / 2 bytes per row and launch on average
-    7: ("scatter_rows_staged_kernel (peer exchange)", float(8 + PAYLOAD_BYTES), None),
+    7: ("scatter_rows_staged_kernel (peer exchange)", None, None),   # bytes per row depend on the column: see `nvlink`
 }
 
 
@@ -55,11 +63,11 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--rows", type=int, default=ROWS_PER_GPU, help="rows per GPU")
+    ap.add_argument("--rows", type=int, default=ROWS_PER_GPU, help="records per GPU")
     ap.add_argument("--cpu-rows", type=int, default=CPU_SAMPLE_ROWS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--no-extras", action="store_true", help="skip the random_shuffle / groupby side measurements")
+    ap.add_argument("--no-extras", action="store_true", help="skip the side measurements (72-byte sort, random_shuffle, groupby)")
     return ap.parse_args()
 
 
@@ -113,16 +121,25 @@ class ClockSampler:
                 "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def workload_config(rows_per_gpu: int, world: int, nblocks: int):
+    return {"workload": "gensort_125Mx100B", "rows_per_gpu": rows_per_gpu, "row_bytes": ROW_BYTES,
+            "key": "10 random bytes ([n, 10] uint8), lexicographic, stable", "key_bytes": KEY_BYTES,
+            "payload_bytes": PAYLOAD_BYTES, "record_pitch": RECORD_PITCH, "blocks_per_gpu": nblocks,
+            "planted_ties": "1/1024 rows repeat the previous key, 1/4096 rows draw from a 65536-key pool shared by all ranks",
+            "l2": f"inputs ({rows_per_gpu * RECORD_PITCH / 1e9:.1f} GB per GPU) exceed the 126 MB L2; no flush needed",
+            "parallelism": f"range-partitioned x{world}" if world > 1 else "single GPU"}
+
+
 def cpu_arm(rows: int, steps: int, warmup: int):
-    """The reference's CPU path (oracle port) on the host cores: seconds per sort of `rows` rows."""
+    """The reference's CPU path (oracle port) on the host cores: seconds per sort of `rows` gensort records."""
     from oracle import cpu_baseline as cb
 
     threads = cb.host_cores()
-    blocks = cb.make_blocks(rows, PAYLOAD_BYTES, max(threads, 8))
+    blocks = cb.make_gensort_blocks(rows, max(threads, 8))
     times = []
     for i in range(warmup + steps):
         t0 = time.perf_counter()
-        outs = cb.sort_blocks(blocks, "id", False, threads)
+        outs = cb.sort_blocks(blocks, ["hi", "lo"], False, threads)
         dt = time.perf_counter() - t0
         assert sum(o.num_rows for o in outs) == rows
         if i >= warmup:
@@ -137,32 +154,177 @@ def run_reference(args):
     import pyarrow
 
     rows = args.cpu_rows
-    steps, warmup = max(1, min(args.steps, 3)), min(args.warmup, 1)
-    sec, threads, nblocks = cpu_arm(rows, steps, warmup)
+    sec, threads, nblocks = cpu_arm(rows, args.steps, args.warmup)
     value = rows / sec
-    sample = (f"{rows} rows x {ROW_BYTES} B (same key/payload generator, {nblocks} blocks), pull-based map/reduce on a "
-              f"{threads}-thread pool, pyarrow {pyarrow.__version__}; rows/s is size-normalised")
+    sample = (f"{rows} gensort records x {ROW_BYTES} B per step (key as (hi uint64, lo uint16), sort(['hi','lo']), "
+              f"{nblocks} blocks), pull-based map/reduce on a {threads}-thread pool, pyarrow {pyarrow.__version__}; "
+              f"rows/s is size-normalised (the GPU arm sorts {args.rows} records per GPU and step)")
     line = {
         "impl": "reference", "metric": "Dataset.sort rows/s", "value": value, "unit": "rows/s", "n_gpus": args.gpus,
-        "steps": steps, "warmup": warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "gb_per_s": value * 2 * ROW_BYTES / 1e9,
-        "config": {"workload": "sort_100Mx72B", "rows_per_gpu": args.rows, "row_bytes": ROW_BYTES, "key": "int64 uniform [0,2^63)",
-                   "payload_bytes": PAYLOAD_BYTES, "cpu_sample_rows": rows},
+        "config": dict(workload_config(args.rows, max(args.gpus, 1), 8), cpu_sample_rows=rows),
         "cpu_baseline": {"value": value, "unit": "rows/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
 
 
+def make_records(n: int, rank: int, dev):
+    """This rank's synthetic records on the device: (key [n, 10] uint8, payload [n, 90] uint8)."""
+    import torch
+
+    from ray_project_ray_b200 import ops
+
+    g = torch.Generator(device=dev).manual_seed(77 + rank)
+    key = torch.randint(0, 256, (n, KEY_BYTES), dtype=torch.uint8, device=dev, generator=g)
+    payload = torch.randint(0, 256, (n, PAYLOAD_BYTES), dtype=torch.uint8, device=dev, generator=g)
+    pool = torch.randint(0, 256, (65536, KEY_BYTES), dtype=torch.uint8, device=dev,
+                         generator=torch.Generator(device=dev).manual_seed(4242))      # the same on every rank
+    i = torch.arange(5, n, 4096, device=dev)
+    key[i] = pool[(i * 2654435761 >> 7) % 65536]
+    i = torch.arange(1027, n, 1024, device=dev)
+    key[i] = key[i - 1]
+    del i, pool
+    recno = torch.arange(rank * n, (rank + 1) * n, dtype=torch.int64, device=dev)
+    hi = ops.pack_key_bytes(key, 0, 8).view(torch.int64)
+    payload[:, 0:8] = recno.view(torch.uint8).reshape(n, 8)
+    payload[:, 8:16] = (hi ^ (recno * TAG_MULT)).view(torch.uint8).reshape(n, 8)
+    return key, payload
+
+
+def checksums(blocks, dev):
+    """Order-independent sums over a list of blocks: rows, sum/xor of the key's first 8 bytes, sum of its last 2,
+    sum/xor of the record numbers (int64 wrap-around)."""
+    import torch
+
+    from ray_project_ray_b200 import ops
+    from ray_project_ray_b200.block import _contig
+
+    acc = torch.zeros(6, dtype=torch.int64, device=dev)
+    for b in blocks:
+        if b.num_rows == 0:
+            continue
+        hi = ops.pack_key_bytes(b.columns["key"], 0, 8).view(torch.int64)
+        lo = ops.pack_key_bytes(b.columns["key"], 8, 2).view(torch.int16).to(torch.int64) & 0xFFFF
+        rec = _contig(b.columns["payload"][:, 0:8]).view(torch.int64).reshape(-1)
+        acc[0] += b.num_rows
+        acc[1] += hi.sum()
+        acc[2] ^= _xor_reduce(hi)
+        acc[3] += lo.sum()
+        acc[4] += rec.sum()
+        acc[5] ^= _xor_reduce(rec)
+    return acc
+
+
+def _xor_reduce(x):
+    import torch
+
+    x = x.reshape(-1)
+    while x.numel() > 1:
+        if x.numel() % 2:
+            x = torch.cat([x, x.new_zeros(1)])
+        x = x[0::2] ^ x[1::2]
+    return x[0] if x.numel() else x.new_zeros(())
+
+
+def verify(out_blocks, before, world: int, rank: int, dev):
+    """Checks of a sorted result, on the device: order inside every block and across blocks / ranks (10-byte key,
+    ties by record number = input order, ranks in rank order), the payload still carries the tag of ITS key, and
+    the key / record-number checksums and the row count equal those of the input."""
+    import torch
+    import torch.distributed as dist
+
+    from ray_project_ray_b200 import ops
+    from ray_project_ray_b200.block import _contig
+
+    ok = {"sorted_within_rank": True, "tie_order": True, "payload_matches_key": True}
+    ties = 0
+    edges = []          # (hi, lo, recno) of every block's first and last row, in order
+    for b in out_blocks:
+        if b.num_rows == 0:
+            continue
+        hi_u = ops.pack_key_bytes(b.columns["key"], 0, 8).view(torch.int64)
+        hi = hi_u ^ (-0x8000000000000000)                                    # unsigned order as signed
+        lo = ops.pack_key_bytes(b.columns["key"], 8, 2).view(torch.int16).to(torch.int32) & 0xFFFF
+        head = _contig(b.columns["payload"][:, 0:16]).view(torch.int64).reshape(-1, 2)
+        rec, tag = head[:, 0], head[:, 1]
+        same = (hi[1:] == hi[:-1]) & (lo[1:] == lo[:-1])
+        in_order = (hi[1:] > hi[:-1]) | ((hi[1:] == hi[:-1]) & (lo[1:] > lo[:-1])) | same
+        ok["sorted_within_rank"] &= bool(in_order.all())
+        ok["tie_order"] &= bool((rec[1:] > rec[:-1])[same].all())
+        ties += int(same.sum())
+        ok["payload_matches_key"] &= bool((tag == (hi_u ^ (rec * TAG_MULT))).all())
+        edges.append([int(hi[0]), int(lo[0]), int(rec[0])])
+        edges.append([int(hi[-1]), int(lo[-1]), int(rec[-1])])
+    for a, c in zip(edges[1::2], edges[2::2]):                                 # last of a block vs first of the next
+        ok["sorted_within_rank"] &= tuple(c[:2]) >= tuple(a[:2])
+        if tuple(c[:2]) == tuple(a[:2]):
+            ok["tie_order"] &= c[2] > a[2]
+            ties += 1
+    after = checksums(out_blocks, dev)
+    across = True
+    if world > 1:
+        mine = torch.tensor((edges[0] + edges[-1]) if edges else [0] * 6, dtype=torch.int64, device=dev)
+        flag = torch.tensor([1 if edges else 0], dtype=torch.int64, device=dev)
+        all_e = [torch.empty_like(mine) for _ in range(world)]
+        all_f = [torch.empty_like(flag) for _ in range(world)]
+        dist.all_gather(all_e, mine)
+        dist.all_gather(all_f, flag)
+        prev = None
+        for e, f in zip(all_e, all_f):
+            if not int(f.item()):
+                continue
+            e = [int(v) for v in e.tolist()]
+            if prev is not None:
+                across &= tuple(e[:2]) >= tuple(prev[3:5])
+                if tuple(e[:2]) == tuple(prev[3:5]):
+                    ok["tie_order"] &= e[2] > prev[5]
+                    ties += 1
+            prev = e
+        # sums add up over ranks; xors are folded by gathering
+        tot = torch.stack([before, after])
+        gathered = [torch.empty_like(tot) for _ in range(world)]
+        dist.all_gather(gathered, tot)
+        g = torch.stack(gathered)                                              # [world, 2, 6]
+        before, after = g[0, 0].clone(), g[0, 1].clone()
+        for r in range(1, world):
+            for k in (0, 1, 3, 4):
+                before[k] += g[r, 0, k]
+                after[k] += g[r, 1, k]
+            for k in (2, 5):
+                before[k] ^= g[r, 0, k]
+                after[k] ^= g[r, 1, k]
+        flags = torch.tensor([int(ok[k]) for k in ("sorted_within_rank", "tie_order", "payload_matches_key")] + [ties],
+                             dtype=torch.int64, device=dev)
+        allf = [torch.empty_like(flags) for _ in range(world)]
+        dist.all_gather(allf, flags)
+        st = torch.stack(allf)
+        for j, k in enumerate(("sorted_within_rank", "tie_order", "payload_matches_key")):
+            ok[k] = bool(st[:, j].min().item())
+        ties = int(st[:, 3].sum().item())
+    b, a = before.tolist(), after.tolist()
+    ok["sorted_across_ranks"] = bool(across)
+    ok["rows"] = int(a[0])
+    ok["row_count"] = a[0] == b[0]
+    ok["key_multiset_checksum"] = a[1:4] == b[1:4]
+    ok["record_number_checksum"] = a[4:6] == b[4:6]
+    ok["equal_key_pairs_checked"] = ties
+    ok["all"] = all(v for k, v in ok.items() if isinstance(v, bool)) and ties > 0
+    return ok
+
+
 def run_ours(args):
+    import ctypes
+
     import numpy as np
     import torch
     import torch.distributed as dist
 
     import ray_project_ray_b200.data as rd
     from ray_project_ray_b200 import _lib
-    from ray_project_ray_b200.block import DeviceBlock
+    from ray_project_ray_b200.block import _contig
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -177,20 +339,19 @@ def run_ours(args):
     lib = _lib.load()
 
     n = args.rows
-    # synthetic input, generated once on the host (seeded per rank), kept in pinned memory for the e2e leg
-    rng = np.random.default_rng(1000 + rank)
-    h_keys = torch.empty(n, dtype=torch.int64).pin_memory()
-    h_pay = torch.empty((n, PAYLOAD_BYTES), dtype=torch.uint8).pin_memory()
-    chunk = 10_000_000
-    for lo in range(0, n, chunk):
-        hi = min(n, lo + chunk)
-        h_keys[lo:hi] = torch.from_numpy(rng.integers(0, np.iinfo(np.int64).max, hi - lo, dtype=np.int64))
-        h_pay[lo:hi] = torch.from_numpy(rng.integers(0, 256, (hi - lo, PAYLOAD_BYTES), dtype=np.uint8))
-    d_keys = h_keys.to(dev, non_blocking=True)
-    d_pay = h_pay.to(dev, non_blocking=True)
-    torch.cuda.synchronize()
     nblocks = 8
-    ds = rd.from_torch_columns({"id": d_keys, "payload": d_pay}, override_num_blocks=nblocks)
+    # synthetic input, generated once on the device (seeded per rank); a pinned host copy feeds the e2e leg
+    d_key, d_pay = make_records(n, rank, dev)
+    h_key = h_pay = None
+    if not args.no_e2e:
+        h_key = torch.empty((n, KEY_BYTES), dtype=torch.uint8).pin_memory()
+        h_pay = torch.empty((n, PAYLOAD_BYTES), dtype=torch.uint8).pin_memory()
+        h_key.copy_(d_key)
+        h_pay.copy_(d_pay)
+    ds = rd.from_torch_columns({"key": d_key, "payload": d_pay}, override_num_blocks=nblocks, records=True)
+    del d_key, d_pay
+    torch.cuda.synchronize()
+    before = checksums(ds.get_internal_block_refs(), dev)
 
     def barrier():
         if world > 1:
@@ -198,7 +359,7 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     def step_resident():
-        return ds.sort("id")
+        return ds.sort("key")
 
     # ---------------- device-resident: `value`
     out = None
@@ -218,26 +379,26 @@ def run_ours(args):
     barrier()
     ms_total = e0.elapsed_time(e1)
     launches = int(lib.b200x_launch_count() - launches0)
-    import ctypes
 
     kernel_times = {}
-    for kid, (kname, _, _) in KERNELS.items():
+    for kid in KERNELS:
         k_ms, k_cnt = ctypes.c_double(0), ctypes.c_int(0)
         lib.b200x_profile_read(kid, ctypes.byref(k_ms), ctypes.byref(k_cnt))
         if k_cnt.value:
             kernel_times[kid] = (k_ms.value, k_cnt.value)
     lib.b200x_profile_enable(0)
-    # correctness of what was timed: global order + multiset checksum (cheap, outside the timed region)
-    host_first = out.get_internal_block_refs()[0]["id"][:4096].cpu().numpy()
-    assert (np.diff(host_first) >= 0).all(), "output is not sorted"
-    assert out.count() > 0 if world > 1 else out.count() == n
+    # correctness of what was timed (outside the timed region): DESIGN.md §6 "verified"
+    verified = verify(out.get_internal_block_refs(), before, world, rank, dev)
+    local_out_rows = out.count()
     if world > 1:
         t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total = float(t.item())
-        cnt = torch.tensor([out.count()], dtype=torch.int64, device=dev)
-        dist.all_reduce(cnt)
-        assert int(cnt.item()) == n * world, "rows lost in the exchange"
+        rows_all = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(world)]
+        dist.all_gather(rows_all, torch.tensor([local_out_rows], dtype=torch.int64, device=dev))
+        rows_per_rank = [int(x.item()) for x in rows_all]
+    else:
+        rows_per_rank = [local_out_rows]
     ms_step = ms_total / args.steps
     total_rows = n * world
     value = total_rows / (ms_step / 1e3)
@@ -246,37 +407,43 @@ def run_ours(args):
     # ---------------- end to end through the public API from pinned host buffers: `e2e`
     e2e = None
     if not args.no_e2e:
-        o_keys = torch.empty(int(n * (1.0 if world == 1 else 1.6)), dtype=torch.int64).pin_memory()
-        o_pay = torch.empty((o_keys.numel(), PAYLOAD_BYTES), dtype=torch.uint8).pin_memory()
-
+        cap = int(n * (1.0 if world == 1 else 1.5))
+        o_key = torch.empty((cap, KEY_BYTES), dtype=torch.uint8).pin_memory()
+        o_pay = torch.empty((cap, PAYLOAD_BYTES), dtype=torch.uint8).pin_memory()
         copy_stream = torch.cuda.Stream(device=dev)
-        keep = []  # results whose D2H is still in flight
+        prev = {"objs": None, "done": None}  # the previous step's result while its D2H may still be in flight
 
         def step_e2e():
-            # H2D of this step's inputs + sort on the main stream; D2H of the result on a second stream, so
-            # that the D2H of step i overlaps the H2D of step i+1 (PCIe is full duplex). Every step still
-            # copies all of its inputs in and all of its result out.
-            k = h_keys.to(dev, non_blocking=True)
+            # H2D of this step's inputs + ingest into records + sort on the main stream; egress (records -> dense
+            # columns) + D2H of the result on a second stream, so that the D2H of step i overlaps the H2D of step
+            # i+1 (PCIe is full duplex). Every step copies all of its inputs in and all of its result out.
+            k = h_key.to(dev, non_blocking=True)
             p = h_pay.to(dev, non_blocking=True)
-            res = rd.from_torch_columns({"id": k, "payload": p}, override_num_blocks=nblocks).sort("id")
+            res = rd.from_torch_columns({"key": k, "payload": p}, override_num_blocks=nblocks, records=True).sort("key")
+            del k, p
             done = torch.cuda.Event()
             done.record()
+            if prev["done"] is not None:      # the buffers the previous D2H read from are released only once it is over
+                prev["done"].synchronize()
+            prev["objs"] = None
             copy_stream.wait_event(done)
-            lo = 0
+            lo, objs = 0, [res]
             with torch.cuda.stream(copy_stream):
                 for b in res.get_internal_block_refs():
                     m = b.num_rows
                     if m:
-                        o_keys[lo:lo + m].copy_(b["id"], non_blocking=True)
-                        o_pay[lo:lo + m].copy_(b["payload"], non_blocking=True)
+                        dk, dp = _contig(b["key"]), _contig(b["payload"])
+                        o_key[lo:lo + m].copy_(dk, non_blocking=True)
+                        o_pay[lo:lo + m].copy_(dp, non_blocking=True)
+                        objs.append((dk, dp))
                         lo += m
-            keep.append(res)
-            if len(keep) > 2:
-                keep.pop(0)
+                ev = torch.cuda.Event()
+                ev.record()
+            prev["objs"], prev["done"] = objs, ev
             return lo
 
-        e_steps = max(1, min(args.steps, 5))
-        for _ in range(min(args.warmup, 2)):
+        e_steps = max(1, min(args.steps, 4))
+        for _ in range(min(args.warmup, 1)):
             step_e2e()
         copy_stream.synchronize()
         barrier()
@@ -290,58 +457,25 @@ def run_ours(args):
         copy_stream.synchronize()
         barrier()
         e_ms = f0.elapsed_time(f1)
-        keep.clear()
-        assert (np.diff(o_keys[:min(got, 100_000)].numpy()) >= 0).all()
-        d2h = got * ROW_BYTES
+        prev["objs"] = None
+        m = min(got, 200_000)
+        hk = o_key[:m].numpy()
+        order_ok = all(bytes(hk[i]) <= bytes(hk[i + 1]) for i in range(0, m - 1, max(1, m // 2000)))
+        assert order_ok, "e2e result is not sorted"
         if world > 1:
             t = torch.tensor([e_ms], dtype=torch.float64, device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             e_ms = float(t.item())
         e2e = {"value": total_rows / (e_ms / e_steps / 1e3), "unit": "rows/s", "h2d_bytes_per_step": n * ROW_BYTES,
-               "d2h_bytes_per_step": int(d2h), "ms_per_step": e_ms / e_steps, "steps": e_steps}
-        del o_keys, o_pay
+               "d2h_bytes_per_step": int(got * ROW_BYTES), "ms_per_step": e_ms / e_steps, "steps": e_steps,
+               "note": "per rank and step: H2D of key + payload columns, ingest into 128-byte records, Dataset.sort, "
+                       "egress to dense columns, D2H of the whole sorted result"}
+        del o_key, o_pay, h_key, h_pay
 
-    # ---------------- the other two operators of the path (N = 1 only; reported under "extras", not the metric)
+    # ---------------- side measurements (N = 1 only; reported under "extras", not the metric)
     extras = None
     if world == 1 and not args.no_extras:
-        from ray_project_ray_b200.aggregate import Count, Mean, Sum
-
-        def timed(fn, steps=3, warm=2):
-            for _ in range(warm):
-                fn()
-            torch.cuda.synchronize()
-            g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            g0.record()
-            for _ in range(steps):
-                r = fn()
-            g1.record()
-            torch.cuda.synchronize()
-            return g0.elapsed_time(g1) / steps, r
-
-        peak_x = 6548.8
-        try:
-            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-                peak_x = float(json.load(f).get("hbm_gbs", peak_x))
-        except OSError:
-            pass
-        extras = {}
-        ms, r = timed(lambda: ds.random_shuffle(seed=0))
-        assert r.count() == n
-        gbs = n * 2 * ROW_BYTES / (ms / 1e3) / 1e9
-        extras["random_shuffle"] = {"workload": f"configs[1]: {n} rows x (8 B id + {PAYLOAD_BYTES} B payload), seed=0, one global bijection",
-                                    "ms_per_step": ms, "rows_per_s": n / (ms / 1e3), "gb_per_s": gbs, "frac_of_hbm_peak": gbs / peak_x}
-        del r
-        gn, groups = 2 * n, 1_000_000
-        gen = torch.Generator(device=dev).manual_seed(4)
-        gk = torch.randint(0, groups, (gn,), dtype=torch.int64, device=dev, generator=gen)
-        gv = torch.randint(-2**31, 2**31, (gn,), dtype=torch.int64, device=dev, generator=gen)
-        gds = rd.from_torch_columns({"k": gk, "v": gv}, override_num_blocks=nblocks)
-        ms, r = timed(lambda: gds.groupby("k").aggregate(Sum("v"), Mean("v"), Count()))
-        assert r.count() == groups and int(r.sum("count()")) == gn
-        gbs = (gn * 16 + groups * 32) / (ms / 1e3) / 1e9
-        extras["groupby_aggregate"] = {"workload": f"configs[2]: {gn} rows, {groups} distinct int64 keys (uniform), Sum+Mean+Count of one int64 column",
-                                       "ms_per_step": ms, "rows_per_s": gn / (ms / 1e3), "gb_per_s": gbs, "frac_of_hbm_peak": gbs / peak_x}
-        del r, gds, gk, gv
+        extras = run_extras(rd, dev, nblocks)
 
     clocks = sampler.stop() if rank == 0 else None
     if rank != 0:
@@ -357,15 +491,25 @@ def run_ours(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
-    roof, breakdown = None, {}
+    breakdown = {}
     for kid, (k_ms, k_cnt) in kernel_times.items():
         kname, alg_b, traffic_b = KERNELS[kid]
         per_launch_ms = k_ms / k_cnt
-        ach = n * alg_b / (per_launch_ms / 1e3) / 1e9
-        breakdown[kname] = {"launches": k_cnt, "ms_per_launch": per_launch_ms, "share_of_step": k_ms / ms_total,
-                            "achieved_gbs": ach, "frac": ach / peak}
-    if kernel_times:
-        kid = max(kernel_times, key=lambda k: kernel_times[k][0])   # dominant = largest share of the timed region
+        entry = {"launches": k_cnt, "ms_per_launch": per_launch_ms, "share_of_step": k_ms / ms_total}
+        if alg_b is not None:
+            rows_k = n if world == 1 else rows_per_rank[0]
+            entry["achieved_gbs"] = rows_k * alg_b / (per_launch_ms / 1e3) / 1e9
+            entry["frac"] = entry["achieved_gbs"] / peak
+        breakdown[kname] = entry
+    op_gbs = total_rows * 2 * ROW_BYTES / (ms_step / 1e3) / 1e9          # 2 x row_bytes x rows
+    t_hbm = 2 * ROW_BYTES * n / (peak * 1e9)
+    t_nvl = ROW_BYTES * n * (world - 1) / world / (NVLINK_GBS * 1e9)
+    roofline_op = {"bound": "hbm", "achieved": op_gbs / world, "peak": peak, "unit": "GB/s", "frac": op_gbs / world / peak,
+                   "algorithmic_bytes": "2 x row_bytes x rows (SURVEY.md 8d)", "peak_source": peak_src}
+    roof = None
+    if world == 1 and kernel_times:
+        cand = {k: v for k, v in kernel_times.items() if KERNELS[k][1] is not None}
+        kid = max(cand, key=lambda k: cand[k][0])   # dominant = largest share of the timed region
         kname, alg_b, traffic_b = KERNELS[kid]
         k_ms, k_cnt = kernel_times[kid]
         per_launch_ms = k_ms / k_cnt
@@ -374,41 +518,129 @@ def run_ours(args):
                 "traffic": (n * traffic_b if traffic_b else None), "peak_source": peak_src, "launches_timed": k_cnt,
                 "ms_per_launch": per_launch_ms, "share_of_step": k_ms / ms_total,
                 "algorithmic_bytes_per_launch": n * alg_b}
-        if world > 1:
-            roof["note"] = ("rank 0's kernels, timed one by one; the key sort overlaps the payload exchange, so shares "
-                            "add up to more than the step")
-            if 7 in kernel_times:
-                # the exchange is link-bound: remote bytes this GPU stores per step against NVLink
-                x_ms = kernel_times[7][0] / args.steps
-                remote = n * ROW_BYTES * (world - 1) / world
-                roof["nvlink"] = {"bytes_per_gpu_per_step": remote, "exchange_ms_per_step": x_ms,
-                                  "achieved": remote / (x_ms / 1e3) / 1e9, "peak": 900.0, "unit": "GB/s",
-                                  "frac": remote / (x_ms / 1e3) / 1e9 / 900.0,
-                                  "peak_source": "nominal NVLink 5 per direction"}
-    op_gbs = total_rows * 2 * ROW_BYTES / (ms_step / 1e3) / 1e9
+    elif world > 1:
+        # the step against the slower of the two rooflines of SURVEY.md 8d: NVLink carries row_bytes x rows x (G-1)/G
+        # per GPU and direction, HBM 2 x row_bytes x rows
+        nvl_bytes = ROW_BYTES * n * (world - 1) / world
+        bound = "nvlink" if t_nvl >= t_hbm else "hbm"
+        if bound == "nvlink":
+            ach, pk, alg = nvl_bytes / (ms_step / 1e3) / 1e9, NVLINK_GBS, nvl_bytes
+            pk_src = "nominal NVLink 5, 900 GB/s per direction and GPU"
+        else:
+            ach, pk, alg, pk_src = 2 * ROW_BYTES * n / (ms_step / 1e3) / 1e9, peak, 2 * ROW_BYTES * n, peak_src
+        # bytes this GPU really stores into its peers per step: whole 128-byte records + the two key chunk columns
+        traffic = (RECORD_PITCH + 8 + 2) * n * (world - 1) / world
+        roof = {"bound": bound, "achieved": ach, "peak": pk, "unit": "GB/s", "frac": ach / pk, "traffic": traffic,
+                "traffic_note": "bytes one GPU stores into peer memory per step (128-byte records + 8- and 2-byte key "
+                                "chunks for (G-1)/G of its rows), computed; not a link counter",
+                "peak_source": pk_src, "algorithmic_bytes_per_step": alg, "ms_per_step": ms_step,
+                "roofline_ms": max(t_hbm, t_nvl) * 1e3, "hbm_roofline_ms": t_hbm * 1e3, "nvlink_roofline_ms": t_nvl * 1e3,
+                "note": "op-level: algorithmic bytes / step time against the slower roofline (SURVEY.md 8d); rank 0's "
+                        "kernels are under `kernels` (the key sort overlaps the payload exchange)"}
+        if 7 in kernel_times:
+            x_ms = kernel_times[7][0] / args.steps
+            roof["exchange_kernels"] = {"ms_per_step": x_ms, "stored_gbs_per_direction": traffic / (x_ms / 1e3) / 1e9,
+                                        "frac_of_nvlink": traffic / (x_ms / 1e3) / 1e9 / NVLINK_GBS}
     line = {
         "metric": "Dataset.sort rows/s", "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "int64", "data": "synthetic", "gb_per_s": op_gbs,
-        "config": {"workload": "sort_100Mx72B", "rows_per_gpu": n, "row_bytes": ROW_BYTES,
-                   "key": "int64 uniform [0,2^63)", "payload_bytes": PAYLOAD_BYTES, "blocks_per_gpu": nblocks,
-                   "l2": "inputs (7.2 GB per GPU) exceed the 126 MB L2; no flush needed",
-                   "parallelism": f"range-partitioned x{world}" if world > 1 else "single GPU"},
-        "roofline": roof,
-        "roofline_op": {"bound": "hbm", "achieved": op_gbs / world, "peak": peak, "unit": "GB/s", "frac": op_gbs / world / peak,
-                        "algorithmic_bytes": "2 x row_bytes x rows (SURVEY.md 8d)", "peak_source": peak_src},
+        "dtype": "u8", "data": "synthetic", "gb_per_s": op_gbs, "gigabytes_sorted_per_step": total_rows * ROW_BYTES / 1e9,
+        "config": workload_config(n, world, nblocks),
+        "roofline": roof, "roofline_op": roofline_op, "verified": verified, "rows_per_rank_after": rows_per_rank,
+        "imbalance_max_over_mean": max(rows_per_rank) / (sum(rows_per_rank) / len(rows_per_rank)),
         "kernels": breakdown, "e2e": e2e, "extras": extras, "gpu_launches": launches, "clocks": clocks,
     }
     if not args.no_cpu_baseline and world == 1:
         import pyarrow
 
-        sec, threads, nb = cpu_arm(args.cpu_rows, 1, 0)
+        sec, threads, nb = cpu_arm(args.cpu_rows, 2, 1)
         line["cpu_baseline"] = {"value": args.cpu_rows / sec, "unit": "rows/s", "cores": threads, "kind": "port",
-                                "sample": f"{args.cpu_rows} rows x {ROW_BYTES} B, {nb} blocks, pull-based map/reduce on a "
-                                          f"{threads}-thread pool, pyarrow {pyarrow.__version__}, {sec:.2f} s"}
+                                "sample": f"{args.cpu_rows} gensort records x {ROW_BYTES} B (sort(['hi','lo'])), {nb} blocks, "
+                                          f"pull-based map/reduce on a {threads}-thread pool, pyarrow {pyarrow.__version__}, "
+                                          f"{sec:.2f} s per sort"}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_extras(rd, dev, nblocks):
+    """The other operators / shapes of the path on one GPU: round 1's 72-byte sort, random_shuffle (configs[1]) and
+    groupby-aggregate (configs[2], uniform and Zipf(1.1) keys)."""
+    import numpy as np
+    import torch
+
+    from ray_project_ray_b200.aggregate import Count, Mean, Sum
+
+    def timed(fn, steps=3, warm=2):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        for _ in range(steps):
+            r = fn()
+        g1.record()
+        torch.cuda.synchronize()
+        return g0.elapsed_time(g1) / steps, r
+
+    peak_x = 6548.8
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peak_x = float(json.load(f).get("hbm_gbs", peak_x))
+    except OSError:
+        pass
+    extras = {}
+    n = 100_000_000
+    gen = torch.Generator(device=dev).manual_seed(3)
+    ids = torch.randint(0, 2**63 - 1, (n,), dtype=torch.int64, device=dev, generator=gen)
+    pay = torch.randint(0, 256, (n, 64), dtype=torch.uint8, device=dev, generator=gen)
+    ds72 = rd.from_torch_columns({"id": ids, "payload": pay}, override_num_blocks=nblocks)
+    ms, r = timed(lambda: ds72.sort("id"))
+    assert r.count() == n
+    gbs = n * 2 * 72 / (ms / 1e3) / 1e9
+    extras["sort_100Mx72B"] = {"workload": "round 1's bench workload: 100 M rows x (int64 key uniform in [0, 2^63) + 64 B payload), dense columns",
+                               "ms_per_step": ms, "rows_per_s": n / (ms / 1e3), "gb_per_s": gbs, "frac_of_hbm_peak": gbs / peak_x}
+    del r
+    ms, r = timed(lambda: ds72.random_shuffle(seed=0))
+    assert r.count() == n
+    gbs = n * 2 * 72 / (ms / 1e3) / 1e9
+    extras["random_shuffle"] = {"workload": f"configs[1]: {n} rows x (8 B id + 64 B payload), seed=0, one global bijection, dense columns",
+                                "ms_per_step": ms, "rows_per_s": n / (ms / 1e3), "gb_per_s": gbs, "frac_of_hbm_peak": gbs / peak_x}
+    del r
+    ds72r = rd.from_torch_columns({"id": ids, "payload": pay}, override_num_blocks=nblocks, records=True)
+    del ds72, ids, pay
+    ms, r = timed(lambda: ds72r.random_shuffle(seed=0))
+    assert r.count() == n
+    gbs = n * 2 * 72 / (ms / 1e3) / 1e9
+    extras["random_shuffle_records"] = {"workload": f"the same rows as 128-byte records (id and payload move together)",
+                                        "ms_per_step": ms, "rows_per_s": n / (ms / 1e3), "gb_per_s": gbs, "frac_of_hbm_peak": gbs / peak_x}
+    del r, ds72r
+    gn, groups = 200_000_000, 1_000_000
+    gen = torch.Generator(device=dev).manual_seed(4)
+    for tag in ("uniform", "zipf1.1"):
+        if tag == "uniform":
+            gk = torch.randint(0, groups, (gn,), dtype=torch.int64, device=dev, generator=gen)
+        else:
+            # Zipf(1.1) over `groups` ranks by inverse CDF (SURVEY.md 8d C3), ranks spread over the key range by a fixed permutation
+            w = torch.arange(1, groups + 1, dtype=torch.float64, device=dev).pow(-1.1)
+            cdf = torch.cumsum(w / w.sum(), 0)
+            u = torch.rand(gn, dtype=torch.float64, device=dev, generator=gen)
+            ranks = torch.searchsorted(cdf, u).clamp_(max=groups - 1)
+            spread = torch.randperm(groups, device=dev, generator=gen)
+            gk = spread[ranks]
+            del w, cdf, u, ranks, spread
+        gv = torch.randint(-2**31, 2**31, (gn,), dtype=torch.int64, device=dev, generator=gen)
+        gds = rd.from_torch_columns({"k": gk, "v": gv}, override_num_blocks=nblocks)
+        ms, r = timed(lambda: gds.groupby("k").aggregate(Sum("v"), Mean("v"), Count()))
+        distinct = r.count()
+        assert int(r.sum("count()")) == gn and int(r.sum("sum(v)")) == int(gv.sum().item())
+        gbs = (gn * 16 + distinct * 32) / (ms / 1e3) / 1e9
+        extras[f"groupby_aggregate_{tag}"] = {
+            "workload": f"configs[2]: {gn} rows, int64 keys ({tag}, {distinct} distinct), Sum+Mean+Count of one int64 column",
+            "ms_per_step": ms, "rows_per_s": gn / (ms / 1e3), "gb_per_s": gbs, "frac_of_hbm_peak": gbs / peak_x,
+            "checked": "row count and grand total of the group sums equal the input's"}
+        del r, gds, gk, gv
+    return extras
 
 
 if __name__ == "__main__":

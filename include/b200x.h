@@ -115,6 +115,21 @@ int b200x_radix_argsort_static(const void* keys, int key_type, int descending, c
  * _internal/arrow_block.py:346-355. */
 int b200x_gather_rows(const void* src, size_t row_bytes, const uint32_t* idx, size_t n, void* dst, void* stream);
 
+/* Record layout: a block may keep several fixed-width columns of a row side by side in ONE record per row,
+ * records lying at a pitch (bytes from one row to the next) that is a multiple of 16, so that a row moves in one
+ * pass of aligned 16-byte accesses whatever its columns' widths (gensort: 10-byte key + 90-byte payload in a
+ * 128-byte record = one DRAM line). dst[i, 0:row_bytes) = src[idx[i], 0:row_bytes), rows src_pitch / dst_pitch
+ * bytes apart; bases, pitches and row_bytes are multiples of 16, row_bytes <= either pitch. Same call sites as
+ * b200x_gather_rows (Table.take moves all columns of a row: transform_pyarrow.py:24-50). */
+int b200x_gather_rows_pitched(const void* src, size_t src_pitch, const uint32_t* idx, size_t n, void* dst,
+                              size_t dst_pitch, size_t row_bytes, void* stream);
+
+/* dst[r, 0:row_bytes) = src[r, 0:row_bytes) for n rows lying src_pitch / dst_pitch bytes apart (any alignment; the
+ * widest access that divides all of them is used): columns <-> records at block ingest / egress, the step
+ * BlockAccessor.for_block / to_arrow perform when a block changes format (block.py:380-407). */
+int b200x_copy_rows_2d(const void* src, size_t src_pitch, void* dst, size_t dst_pitch, size_t row_bytes, size_t n,
+                       void* stream);
+
 /* Same gather for ncols 8-byte columns sharing one index vector; srcs_host/dsts_host are HOST
  * arrays of device pointers. */
 int b200x_gather_columns8(const void* const* srcs_host, void* const* dsts_host, int ncols, const uint32_t* idx, size_t n,
@@ -132,6 +147,17 @@ int b200x_encode_keys(const void* keys, int key_type, int descending, size_t n, 
  * codes: -0.0 == +0.0). Zero = all keys distinct: a multi-column sort (transform_pyarrow.py:17-21 with several
  * sort keys) then needs only the sort by its first column. No counterpart in the reference. */
 int b200x_count_adjacent_equal(const void* keys, int key_type, size_t n, uint64_t* count_out, void* stream);
+
+/* Multi-column sort whose first column is (almost) distinct. After a stable sort by the first key column alone
+ * (keys_sorted = that column in sorted order, or its codes with key_type U64; perm = the permutation, updated in
+ * place) every run of equal first keys is ordered by the remaining num_cols (1..3) key columns - cols_host /
+ * types_host are HOST arrays of device pointers / key types of those columns, indexed by row, compared as codes
+ * in the given direction - with a stable insertion sort of the run's permutation entries. stats_out[0] (device) =
+ * rows that lie in such runs, stats_out[1] = longest run; runs longer than 64 rows are left untouched, so a caller
+ * that reads stats_out[1] > 64 must sort by all columns instead. Gives the order of pyarrow.compute.sort_indices
+ * with several sort keys (transform_pyarrow.py:17-21) for one sort pass instead of one per column. */
+int b200x_fix_ties(const void* keys_sorted, int key_type, size_t n, uint32_t* perm, const void* const* cols_host,
+                   const int* types_host, int num_cols, int descending, unsigned long long* stats_out, void* stream);
 
 /* out[i] = bytes [offset, offset + width) of row i of a fixed-width byte-string column (row_bytes per row)
  * as a big-endian unsigned integer, left-aligned in an out_bytes-wide (2, 4 or 8) unsigned integer and
@@ -203,6 +229,8 @@ int b200x_scatter_rows_by_target(const void* src, size_t row_bytes, const uint32
  * The MT19937 stream itself is not reproduced: the contract is an exact multiset
  * permutation that is deterministic per seed. */
 int b200x_permute_rows(const void* src, size_t row_bytes, size_t n, uint64_t seed, int inverse, void* dst, void* stream);
+int b200x_permute_rows_pitched(const void* src, size_t src_pitch, size_t n, uint64_t seed, int inverse, void* dst,
+                               size_t dst_pitch, size_t row_bytes, void* stream); /* records at a pitch, see b200x_gather_rows_pitched */
 int b200x_perm_indices(size_t n, uint64_t seed, int inverse, size_t start, size_t count, uint32_t* out, void* stream);
 int b200x_perm_indices_host(size_t n, uint64_t seed, int inverse, size_t start, size_t count, uint32_t* out_host);
 

@@ -36,16 +36,21 @@ def host_cores() -> int:
         return os.cpu_count() or 1
 
 
-def _sort_table(t: pa.Table, key: str, descending: bool) -> pa.Table:
-    idx = pac.sort_indices(t, sort_keys=[(key, "descending" if descending else "ascending")])
+def _sort_table(t: pa.Table, key, descending: bool) -> pa.Table:
+    keys = [key] if isinstance(key, str) else list(key)
+    idx = pac.sort_indices(t, sort_keys=[(k, "descending" if descending else "ascending") for k in keys])
     return t.take(idx)
+
+
+def _first(key) -> str:
+    return key if isinstance(key, str) else key[0]
 
 
 def _map_task(t: pa.Table, key: str, descending: bool, boundaries: Sequence) -> List[pa.Table]:
     if t.num_rows == 0:
         return [t] * (len(boundaries) + 1)
     s = _sort_table(t, key, descending)
-    col = s[key].to_numpy()
+    col = s[_first(key)].to_numpy()   # multi-column keys are cut on their first column (equal first keys stay together)
     parts, last = [], 0
     for b in boundaries:
         if descending:
@@ -65,11 +70,12 @@ def _reduce_task(parts: Sequence[pa.Table], key: str, descending: bool) -> pa.Ta
     return _sort_table(pa.concat_tables(parts), key, descending)
 
 
-def sort_blocks(blocks: List[pa.Table], key: str, descending: bool, threads: int, seed: int = 0) -> List[pa.Table]:
+def sort_blocks(blocks: List[pa.Table], key, descending: bool, threads: int, seed: int = 0) -> List[pa.Table]:
+    """`key`: a column name or a list of them (the reference's multi-column SortKey, sort_task_spec.py:18-87)."""
     R = len(blocks)
     rng = np.random.default_rng(seed)
     n_samples = max(1, int(R * 10 / len(blocks)))
-    samples = np.concatenate([b[key].to_numpy()[rng.integers(0, b.num_rows, min(n_samples, b.num_rows))]
+    samples = np.concatenate([b[_first(key)].to_numpy()[rng.integers(0, b.num_rows, min(n_samples, b.num_rows))]
                               for b in blocks if b.num_rows])
     samples.sort()
     boundaries = list(np.quantile(samples, np.linspace(0, 1, R), method="nearest")[1:])
@@ -95,6 +101,24 @@ def make_blocks(n_rows: int, payload_bytes: int, num_blocks: int, seed: int = 0)
             pay = rng.integers(0, 256, (m, payload_bytes), dtype=np.uint8)
             cols["payload"] = pa.FixedSizeBinaryArray.from_buffers(pa.binary(payload_bytes), m, [None, pa.py_buffer(pay)])
         out.append(pa.table(cols))
+    return out
+
+
+def make_gensort_blocks(n_rows: int, num_blocks: int, seed: int = 0) -> List[pa.Table]:
+    """gensort-shaped 100-byte records on the host (BASELINE.json configs[3]): the 10-byte key as the
+    reference can sort it - (hi: uint64 = key bytes 0..7 big-endian, lo: uint16 = bytes 8..9), `sort(["hi", "lo"])`,
+    the form SURVEY.md 8c ran through the reference's own sample_boundaries / find_partition_index - plus a 90-byte
+    fixed_size_binary payload: 100 bytes per row."""
+    rng = np.random.default_rng(seed)
+    per = n_rows // num_blocks
+    out = []
+    for i in range(num_blocks):
+        m = per if i < num_blocks - 1 else n_rows - per * (num_blocks - 1)
+        hi = rng.integers(0, np.iinfo(np.uint64).max, m, dtype=np.uint64)
+        lo = rng.integers(0, 1 << 16, m, dtype=np.uint16)
+        pay = rng.integers(0, 256, (m, 90), dtype=np.uint8)
+        out.append(pa.table({"hi": pa.array(hi), "lo": pa.array(lo),
+                             "payload": pa.FixedSizeBinaryArray.from_buffers(pa.binary(90), m, [None, pa.py_buffer(pay)])}))
     return out
 
 

@@ -38,6 +38,12 @@ SIGNATURES = {
     "b200x_radix_argsort_static": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
                                            c_void_p]),
     "b200x_gather_rows": (c_int, [c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_void_p]),
+    "b200x_gather_rows_pitched": (c_int, [c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_size_t, c_size_t, c_void_p]),
+    "b200x_copy_rows_2d": (c_int, [c_void_p, c_size_t, c_void_p, c_size_t, c_size_t, c_size_t, c_void_p]),
+    "b200x_fix_ties": (c_int, [c_void_p, c_int, c_size_t, c_void_p, POINTER(c_void_p), POINTER(c_int), c_int, c_int,
+                               c_void_p, c_void_p]),
+    "b200x_permute_rows_pitched": (c_int, [c_void_p, c_size_t, c_size_t, c_uint64, c_int, c_void_p, c_size_t, c_size_t,
+                                           c_void_p]),
     "b200x_gather_columns8": (c_int, [POINTER(c_void_p), POINTER(c_void_p), c_int, c_void_p, c_size_t, c_void_p]),
     "b200x_iota_u32": (c_int, [c_void_p, c_size_t, c_uint32, c_void_p]),
     "b200x_encode_keys": (c_int, [c_void_p, c_int, c_int, c_size_t, c_void_p, c_void_p]),

@@ -11,6 +11,13 @@ Mirrors the data-plane types of the reference (python/ray/data/block.py:54, :123
                       the C ABI; nothing is computed with torch ops or on the CPU.
   BlockMetadata / BlockExecStats -> same fields.
 
+Record layout: several columns of a block may be views into ONE record buffer `[n, pitch]` (pitch a
+multiple of 16 bytes; `DeviceBlock.to_records`): column c of row r lies at `r * pitch + offset_c`. The
+columns keep their names, dtypes and shapes (they are strided torch views), but every row-moving operation
+(sort, take, random_shuffle, the multi-GPU exchange) moves the record - one pass of aligned 16-byte accesses
+per row whatever the column widths, instead of one pass per column (a gensort row = 10-byte key + 90-byte
+payload in a 128-byte record moves as one DRAM line; as two dense columns it moves in 2-byte pieces).
+
 Null values and variable-width columns are outside the device format (fixed-width
 int/float keys and payloads); ingesting an Arrow column with nulls raises.
 """
@@ -142,6 +149,109 @@ def _to_host(t: torch.Tensor) -> np.ndarray:
     return t.cpu().numpy()
 
 
+# ------------------------------------------------------------------ record layout helpers
+BYTE_KEY_SEP = "::be"   # `<column>::be<i>` = the i-th big-endian 8-byte chunk of a byte-string key column
+RECORD_ALIGN = 16
+
+
+def _inner(t: torch.Tensor) -> Tuple[int, bool]:
+    """(bytes of one row, rows are dense inside) of a column tensor."""
+    es, nbytes, expect, dense = t.element_size(), t.element_size(), 1, True
+    for size, stride in zip(reversed(t.shape[1:]), reversed(t.stride()[1:])):
+        if size != 1 and stride != expect:
+            dense = False
+        expect *= size
+        nbytes *= size
+    return nbytes, dense
+
+
+def _row_pitch(t: torch.Tensor) -> Optional[int]:
+    """Row pitch in bytes if `t` is a column whose rows are dense inside and lie further apart than their
+    width (a record member or any other row-strided view), else None."""
+    if t.dim() < 1 or t.shape[0] == 0:
+        return None
+    inner, dense = _inner(t)
+    pitch = t.stride(0) * t.element_size()
+    return pitch if dense and pitch > inner else None
+
+
+def _contiguous_strides(shape: Sequence[int]) -> Tuple[int, ...]:
+    out, run = [], 1
+    for size in reversed(shape):
+        out.append(run)
+        run *= size
+    return tuple(reversed(out))
+
+
+def member_view(rec: torch.Tensor, offset: int, dtype: torch.dtype, inner_shape: Sequence[int]) -> torch.Tensor:
+    """Column view `[m, *inner_shape]` of dtype `dtype` at byte `offset` of every record of `rec` ([m, pitch] uint8)."""
+    m, pitch = rec.shape
+    flat = rec.reshape(-1)
+    es = torch.empty(0, dtype=dtype).element_size()
+    typed = flat if dtype == torch.uint8 else flat.view(dtype)
+    inner_shape = tuple(int(x) for x in inner_shape)
+    return typed.as_strided((m,) + inner_shape, (pitch // es,) + _contiguous_strides(inner_shape),
+                            rec.storage_offset() // es + offset // es)
+
+
+@dataclass
+class RecordGroup:
+    """Columns of one block that are views into the same record buffer."""
+
+    rec: torch.Tensor                                                   # [n, pitch] uint8 view of the records
+    pitch: int
+    members: Dict[str, Tuple[int, torch.dtype, Tuple[int, ...]]]        # name -> (byte offset, dtype, inner shape)
+
+    def views(self, rec: torch.Tensor) -> Dict[str, torch.Tensor]:
+        return {k: member_view(rec, off, dt, shape) for k, (off, dt, shape) in self.members.items()}
+
+
+def record_groups(block: "DeviceBlock", names: Optional[Sequence[str]] = None) -> Tuple[List[RecordGroup], List[str]]:
+    """Split the columns `names` of a block into record groups (moved record-wise) and loose columns.
+    A group is used when its member columns fill at least half of the record (otherwise moving the dense
+    columns one by one touches fewer bytes)."""
+    names = list(block.columns) if names is None else list(names)
+    found: Dict[Tuple[int, int, int], RecordGroup] = {}
+    of: Dict[str, Tuple[int, int, int]] = {}
+    n = block.num_rows
+    for name in names:
+        t = block.columns[name]
+        pitch = _row_pitch(t) if t.is_cuda else None
+        if pitch is None or pitch % RECORD_ALIGN or pitch > (1 << 20):
+            continue
+        inner, _ = _inner(t)
+        storage = t.untyped_storage()
+        off = t.data_ptr() - storage.data_ptr()
+        col_off = off % pitch
+        rec0 = off - col_off
+        if col_off + inner > pitch or col_off % t.element_size() or (storage.data_ptr() + rec0) % RECORD_ALIGN \
+                or rec0 + n * pitch > storage.nbytes():
+            continue
+        key = (storage.data_ptr(), pitch, rec0)
+        if key not in found:
+            rec = torch.empty(0, dtype=torch.uint8, device=t.device).set_(storage, rec0, (n, pitch), (pitch, 1))
+            found[key] = RecordGroup(rec, pitch, {})
+        found[key].members[name] = (col_off, t.dtype, tuple(t.shape[1:]))
+        of[name] = key
+    groups = []
+    for key, g in found.items():
+        filled = sum(_inner(block.columns[k])[0] for k in g.members)
+        if 2 * filled >= g.pitch:
+            groups.append(g)
+        else:
+            for k in g.members:
+                del of[k]
+    return groups, [k for k in names if k not in of]
+
+
+def auto_pitch(used: int) -> int:
+    """Record pitch for `used` bytes of columns: 16 / 32 / 64, else a multiple of 128 (whole DRAM lines)."""
+    for p in (16, 32, 64):
+        if used <= p:
+            return p
+    return (used + 127) // 128 * 128
+
+
 class DeviceBlock:
     """A columnar block resident in HBM. Immutable by convention; slices are views."""
 
@@ -201,6 +311,48 @@ class DeviceBlock:
     def empty(device: Optional[torch.device] = None) -> "DeviceBlock":
         return DeviceBlock({}, num_rows=0, device=device)
 
+    def to_records(self, columns: Optional[Sequence[str]] = None, pitch: Optional[int] = None) -> "DeviceBlock":
+        """The same block with `columns` (default: all) stored side by side in one record per row (module
+        docstring, "Record layout"). Offsets follow the column order, each aligned to its element size; `pitch`
+        defaults to `auto_pitch`. Padding bytes are zero."""
+        names = list(self.columns) if columns is None else list(columns)
+        if not names or self._n == 0:
+            return self
+        layout, used = {}, 0
+        for k in names:
+            t = self.columns[k]
+            es = t.element_size()
+            used = (used + es - 1) // es * es
+            inner, _ = _inner(t)
+            layout[k] = (used, t.dtype, tuple(t.shape[1:]), inner)
+            used += inner
+        pitch = auto_pitch(used) if pitch is None else int(pitch)
+        if pitch % RECORD_ALIGN or pitch < used:
+            raise ValueError(f"record pitch {pitch} must be a multiple of {RECORD_ALIGN} and hold {used} bytes of columns")
+        rec = torch.zeros((self._n, pitch), dtype=torch.uint8, device=self.device)
+        cols = dict(self.columns)
+        for k, (off, dt, shape, inner) in layout.items():
+            t = self.columns[k]
+            src_pitch = _row_pitch(t)
+            if src_pitch is None:
+                t = t.contiguous()
+                src_pitch = inner
+            ops.copy_rows_2d(t.data_ptr(), src_pitch, rec.data_ptr() + off, pitch, inner, self._n, self.device)
+            cols[k] = member_view(rec, off, dt, shape)
+        return DeviceBlock(cols, num_rows=self._n, device=self.device)
+
+    def key_column(self, name: str) -> torch.Tensor:
+        """The dense 1-D key column `name`. `<col>::be<i>` names the i-th big-endian 8-byte chunk of the
+        byte-string column `col` (planner._expand_byte_keys): computed here when the block does not carry it."""
+        if name in self.columns:
+            return _contig(self.columns[name])
+        base, sep, idx = name.rpartition(BYTE_KEY_SEP)
+        if sep and base in self.columns and idx.isdigit():
+            col = self.columns[base]
+            off = 8 * int(idx)
+            return ops.pack_key_bytes(col if _row_pitch(col) is not None else _contig(col), off, min(8, col.shape[1] - off))
+        raise KeyError(name)
+
     # -- introspection ------------------------------------------------------------------
     @property
     def num_rows(self) -> int:
@@ -258,7 +410,7 @@ class DeviceBlock:
     # -- egress (D2H happens only here) -------------------------------------------------
     def to_numpy(self, columns: Optional[Sequence[str]] = None) -> Dict[str, np.ndarray]:
         names = list(columns) if columns is not None else list(self.columns)
-        return {k: _to_host(self.columns[k].contiguous()) for k in names}
+        return {k: _to_host(_contig(self.columns[k])) for k in names}
 
     def to_arrow(self):
         import pyarrow as pa
@@ -282,7 +434,9 @@ class DeviceBlock:
 def _join_views(parts: List[torch.Tensor]) -> torch.Tensor:
     first = parts[0]
     row = first.stride(0) * first.element_size() if first.dim() >= 1 and first.shape[0] > 0 else 0
-    contiguous = all(p.is_contiguous() and p.dtype == first.dtype and p.shape[1:] == first.shape[1:] for p in parts)
+    # dense columns, or columns at a common row pitch (record members): adjacent views re-join without a copy
+    contiguous = all(p.dtype == first.dtype and p.shape[1:] == first.shape[1:] and p.stride() == first.stride()
+                     and _inner(p)[1] for p in parts)
     if contiguous and row:
         ptr = first.data_ptr()
         same = True
@@ -389,12 +543,23 @@ class DeviceBlockAccessor(BlockAccessor):
                              input_files=input_files, exec_stats=exec_stats)
 
     # -- gathers ------------------------------------------------------------------------
+    def _take_columns(self, indices: torch.Tensor, names: Sequence[str]) -> Dict[str, torch.Tensor]:
+        """Columns `names` at rows `indices`: record groups move as whole records (one pass per group), the
+        other columns one by one (8-byte columns share a launch)."""
+        b = self._block
+        groups, loose = record_groups(b, names)
+        cols: Dict[str, torch.Tensor] = {}
+        for g in groups:
+            cols.update(g.views(ops.gather_records(g.rec, indices)))
+        outs = ops.gather_columns([_contig(b.columns[k]) for k in loose], indices)
+        cols.update(zip(loose, outs))
+        return cols
+
     def take(self, indices: torch.Tensor) -> DeviceBlock:
         """Rows at `indices` (int32 tensor holding uint32 row numbers). arrow_block.py:346-355."""
         b = self._block
-        names = b.column_names
-        outs = ops.gather_columns([_contig(b.columns[k]) for k in names], indices)
-        return DeviceBlock(dict(zip(names, outs)), num_rows=indices.numel(), device=b.device)
+        cols = self._take_columns(indices, b.column_names)
+        return DeviceBlock({k: cols[k] for k in b.column_names}, num_rows=indices.numel(), device=b.device)
 
     def random_shuffle(self, random_seed: Optional[int]) -> DeviceBlock:
         """Seeded permutation of the rows. arrow_block.py:249-255 (permutation + take, fused here)."""
@@ -402,8 +567,13 @@ class DeviceBlockAccessor(BlockAccessor):
         seed = 0 if random_seed is None else int(random_seed)
         if random_seed is None:
             seed = int.from_bytes(os.urandom(8), "little")
-        return DeviceBlock({k: ops.permute_rows(_contig(v), seed) for k, v in b.columns.items()},
-                           num_rows=b.num_rows, device=b.device)
+        groups, loose = record_groups(b)
+        cols: Dict[str, torch.Tensor] = {}
+        for g in groups:
+            cols.update(g.views(ops.permute_records(g.rec, seed)))
+        for k in loose:
+            cols[k] = ops.permute_rows(_contig(b.columns[k]), seed)
+        return DeviceBlock({k: cols[k] for k in b.column_names}, num_rows=b.num_rows, device=b.device)
 
     def sample(self, n_samples: int, sort_key: "SortKey") -> DeviceBlock:
         """`n_samples` rows of the key columns. table_block.py:252-262, arrow_block.py:365-368.
@@ -417,7 +587,7 @@ class DeviceBlockAccessor(BlockAccessor):
         n_samples = min(n_samples, b.num_rows)
         pos = ((np.arange(n_samples, dtype=np.float64) + 0.5) * (b.num_rows / max(n_samples, 1))).astype(np.int64)
         idx = torch.from_numpy(pos.astype(np.int32)).to(b.device)
-        return DeviceBlockAccessor(b.select(cols)).take(idx)
+        return DeviceBlock({c: ops.gather(b.key_column(c), idx) for c in cols}, num_rows=n_samples, device=b.device)
 
     # -- sort (arrow_block.py:449-464, :554-567) ------------------------------------------
     def _argsort(self, sort_key: "SortKey", want_codes: bool):
@@ -425,24 +595,25 @@ class DeviceBlockAccessor(BlockAccessor):
         b = self._block
         cols = sort_key.get_columns()
         desc = sort_key.get_descending()
-        if len(cols) > 1 and b.num_rows >= _DISTINCT_FIRST_MIN_ROWS:
-            first = self._argsort_if_first_column_distinct(cols[0], desc, want_codes)
+        if 1 < len(cols) <= 1 + ops.FIX_TIES_MAX_COLS and b.num_rows >= _DISTINCT_FIRST_MIN_ROWS:
+            first = self._argsort_first_column_then_ties(cols, desc, want_codes)
             if first is not None:
                 return first
         perm = codes = skeys = None
         for i, name in enumerate(reversed(cols)):
             lastcall = i == len(cols) - 1
-            perm, codes, skeys = ops.argsort(_contig(b.columns[name]), desc, perm_in=perm,
+            perm, codes, skeys = ops.argsort(b.key_column(name), desc, perm_in=perm,
                                              want_codes=want_codes and lastcall, want_keys=lastcall)
         return perm, codes, skeys
 
-    def _argsort_if_first_column_distinct(self, name: str, desc: bool, want_codes: bool):
-        """A multi-column sort whose first column has no duplicates IS the sort by that column alone (gensort's
-        10-byte key: 8 random bytes already separate the records; timestamps + id; ...). If a sample of the
-        column shows no duplicate, sort by it first and count equal neighbours: none -> done with one sort
-        instead of one chained sort per column. Otherwise None: the caller runs the LSD chain."""
+    def _argsort_first_column_then_ties(self, cols: List[str], desc: bool, want_codes: bool):
+        """A multi-column sort whose first column has (almost) no duplicates is the sort by that column alone,
+        plus a repair of the few runs of equal first keys (gensort's 10-byte key: 8 random bytes already separate
+        nearly all records; timestamp + id; ...). If a sample of the first column shows no duplicate: one sort by
+        it, then `fix_ties` orders every run of equal first keys by the remaining columns in place. A run longer
+        than the repair handles (the column was duplicate-heavy after all) -> None: the caller runs the chain."""
         b = self._block
-        col = _contig(b.columns[name])
+        col = b.key_column(cols[0])
         if col.dim() != 1 or col.element_size() < 4:
             return None
         n = b.num_rows
@@ -452,8 +623,9 @@ class DeviceBlockAccessor(BlockAccessor):
         if np.unique(sample).size < m:
             return None
         perm, codes, skeys = ops.argsort(col, desc, want_codes=want_codes or col.dtype.is_floating_point, want_keys=True)
-        probe = skeys if skeys is not None else codes
-        if int(ops.count_adjacent_equal(probe).item()) != 0:
+        probe = skeys if skeys is not None else codes.view(torch.uint64)
+        stats = ops.fix_ties(probe, perm, [b.key_column(c) for c in cols[1:]], desc)
+        if int(stats[1].item()) > ops.FIX_TIES_MAX_RUN:
             return None
         return perm, (codes if want_codes else None), skeys
 
@@ -467,13 +639,14 @@ class DeviceBlockAccessor(BlockAccessor):
         perm, codes, skeys = self._argsort(sort_key, want_codes)
         first_key = sort_key.get_columns()[0]
         if skeys is None and on_sorted_key is not None:  # float keys are gathered, not decoded by the sort
-            skeys = ops.gather(_contig(b.columns[first_key]), perm)
+            skeys = ops.gather(b.key_column(first_key), perm)
         if on_sorted_key is not None:
             on_sorted_key(skeys)
-        names = [k for k in b.column_names if not (skeys is not None and k == first_key)]
-        outs = ops.gather_columns([_contig(b.columns[k]) for k in names], perm)
-        cols = dict(zip(names, outs))
-        if skeys is not None:
+        # the sorted first key column comes out of the sort itself, unless it travels inside a record anyway
+        decoded = skeys is not None and first_key in b.columns and _row_pitch(b.columns[first_key]) is None
+        names = [k for k in b.column_names if not (decoded and k == first_key)]
+        cols = self._take_columns(perm, names)
+        if decoded:
             cols[first_key] = skeys
         out = DeviceBlock({k: cols[k] for k in b.column_names}, num_rows=b.num_rows, device=b.device)
         return out, codes
@@ -561,7 +734,15 @@ class DeviceBlockAccessor(BlockAccessor):
 
 
 def _contig(t: torch.Tensor) -> torch.Tensor:
-    return t if t.is_contiguous() else t.contiguous()
+    """Dense copy of a column unless it is dense already (record members are copied out by the 2-D copy kernel)."""
+    if t.is_contiguous():
+        return t
+    pitch = _row_pitch(t) if t.is_cuda else None
+    if pitch is None:
+        return t.contiguous()
+    out = torch.empty(t.shape, dtype=t.dtype, device=t.device)
+    ops.copy_rows_2d(t.data_ptr(), pitch, out.data_ptr(), _inner(t)[0], _inner(t)[0], t.shape[0], t.device)
+    return out
 
 
 def boundary_codes(boundaries: Sequence[Any], key_col: torch.Tensor, descending: bool) -> torch.Tensor:
@@ -602,7 +783,7 @@ def find_partitions(table: DeviceBlock, boundaries: Sequence[Any], sort_key: "So
     multi-column boundaries partition on the first key column's value only (a coarser, still
     order-respecting cut: every row of partition i sorts before every row of partition i+1)."""
     first = sort_key.get_columns()[0]
-    bounds = find_partition_indices(table.columns[first], boundaries, sort_key.get_descending())
+    bounds = find_partition_indices(table.key_column(first), boundaries, sort_key.get_descending())
     parts, last = [], 0
     for idx in bounds:
         idx = max(idx, last)

@@ -104,7 +104,76 @@ gather_cols8_kernel(const ColPtrs p, int ncols, const uint32_t* __restrict__ idx
   }
 }
 
+// Rows kept at a pitch: record r of a buffer starts at byte r * pitch (pitch a multiple of 16, base 16-byte
+// aligned) and only its first vec_per_row 16-byte vectors are moved. This is how a block keeps several
+// fixed-width columns (a gensort record = 10-byte key + 90-byte payload at a 128-byte pitch) as ONE record
+// per row: every access is an aligned 16-byte vector whatever the column widths, a 128-byte record is
+// exactly one DRAM line, and the whole row moves in one pass instead of one pass per column.
+__global__ void __launch_bounds__(256)
+gather_rows_pitched_kernel(const uint4* __restrict__ src, const uint32_t* __restrict__ idx, uint4* __restrict__ dst,
+                           uint64_t n, uint32_t vec_per_row, uint32_t src_pitch_vec, uint32_t dst_pitch_vec) {
+  constexpr int U = 4;
+  const uint64_t total = n * vec_per_row;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  const uint64_t q = stride / vec_per_row;
+  const uint32_t m = (uint32_t)(stride - q * vec_per_row);
+  uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  uint64_t r = t / vec_per_row;
+  uint32_t c = (uint32_t)(t - r * vec_per_row);
+  for (; t + (U - 1) * stride < total; t += U * stride) {
+    uint64_t s[U], d[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      s[u] = (uint64_t)idx[r] * src_pitch_vec + c;
+      d[u] = r * dst_pitch_vec + c;
+      c += m;
+      r += q;
+      if (c >= vec_per_row) {
+        c -= vec_per_row;
+        ++r;
+      }
+    }
+    uint4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) v[u] = src[s[u]];
+#pragma unroll
+    for (int u = 0; u < U; ++u) dst[d[u]] = v[u];
+  }
+  for (; t < total; t += stride) {
+    dst[r * dst_pitch_vec + c] = src[(uint64_t)idx[r] * src_pitch_vec + c];
+    c += m;
+    r += q;
+    if (c >= vec_per_row) {
+      c -= vec_per_row;
+      ++r;
+    }
+  }
+}
 
+// dst[r, 0:row_bytes) = src[r, 0:row_bytes) between two row pitches (column <-> record conversion at
+// ingest / egress). V = widest access dividing both pitches, both bases and row_bytes.
+template <typename V>
+__global__ void __launch_bounds__(256)
+copy_rows_2d_kernel(const unsigned char* __restrict__ src, uint64_t src_pitch, unsigned char* __restrict__ dst,
+                    uint64_t dst_pitch, uint32_t vec_per_row, uint64_t n) {
+  const uint64_t total = n * vec_per_row;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  const uint64_t q = stride / vec_per_row;
+  const uint32_t m = (uint32_t)(stride - q * vec_per_row);
+  uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  uint64_t r = t / vec_per_row;
+  uint32_t c = (uint32_t)(t - r * vec_per_row);
+  for (; t < total; t += stride) {
+    *reinterpret_cast<V*>(dst + r * dst_pitch + (uint64_t)c * sizeof(V)) =
+        *reinterpret_cast<const V*>(src + r * src_pitch + (uint64_t)c * sizeof(V));
+    c += m;
+    r += q;
+    if (c >= vec_per_row) {
+      c -= vec_per_row;
+      ++r;
+    }
+  }
+}
 
 __global__ void __launch_bounds__(256) iota_kernel(uint32_t* out, uint64_t n, uint32_t start) {
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
@@ -160,6 +229,63 @@ extern "C" int b200x_gather_rows(const void* src, size_t row_bytes, const uint32
   }
   prof_end(stream);
   B200X_LAUNCH_CHECK("gather_rows_kernel");
+  return B200X_OK;
+}
+
+extern "C" int b200x_gather_rows_pitched(const void* src, size_t src_pitch, const uint32_t* idx, size_t n, void* dst,
+                                         size_t dst_pitch, size_t row_bytes, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (n == 0 || row_bytes == 0) return B200X_OK;
+  if (src == nullptr || idx == nullptr || dst == nullptr) {
+    set_error("b200x_gather_rows_pitched: NULL pointer");
+    return B200X_ERR_ARG;
+  }
+  if (row_bytes > src_pitch || row_bytes > dst_pitch || row_bytes > (1u << 20)) {
+    set_error("b200x_gather_rows_pitched: row_bytes=%zu exceeds a pitch (%zu, %zu) or 1 MiB", row_bytes, src_pitch, dst_pitch);
+    return B200X_ERR_ARG;
+  }
+  if ((((uintptr_t)src | (uintptr_t)dst | src_pitch | dst_pitch | row_bytes) & 15) != 0) {
+    set_error("b200x_gather_rows_pitched: bases, pitches and row_bytes must be multiples of 16");
+    return B200X_ERR_ALIGN;
+  }
+  if (src_pitch > (1u << 24) || dst_pitch > (1u << 24)) {
+    set_error("b200x_gather_rows_pitched: pitch (%zu, %zu) above 16 MiB", src_pitch, dst_pitch);
+    return B200X_ERR_TOO_LARGE;
+  }
+  const uint32_t vpr = (uint32_t)(row_bytes / 16);
+  const uint32_t g = grid_for((uint64_t)n * vpr, 256, 16);
+  prof_begin(stream, PROF_GATHER);
+  gather_rows_pitched_kernel<<<g, 256, 0, stream>>>((const uint4*)src, idx, (uint4*)dst, n, vpr, (uint32_t)(src_pitch / 16),
+                                                    (uint32_t)(dst_pitch / 16));
+  prof_end(stream);
+  B200X_LAUNCH_CHECK("gather_rows_pitched_kernel");
+  return B200X_OK;
+}
+
+extern "C" int b200x_copy_rows_2d(const void* src, size_t src_pitch, void* dst, size_t dst_pitch, size_t row_bytes,
+                                  size_t n, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (n == 0 || row_bytes == 0) return B200X_OK;
+  if (src == nullptr || dst == nullptr || row_bytes > src_pitch || row_bytes > dst_pitch || row_bytes > (1u << 20)) {
+    set_error("b200x_copy_rows_2d: NULL pointer or row_bytes=%zu exceeds a pitch (%zu, %zu) or 1 MiB", row_bytes, src_pitch,
+              dst_pitch);
+    return B200X_ERR_ARG;
+  }
+  const uintptr_t al = (uintptr_t)src | (uintptr_t)dst | src_pitch | dst_pitch | row_bytes;
+  int v = 16;
+  while (v > 1 && (al & (uintptr_t)(v - 1)) != 0) v >>= 1;
+  const uint32_t vpr = (uint32_t)(row_bytes / v);
+  const uint32_t g = grid_for((uint64_t)n * vpr, 256, 16);
+  const unsigned char* s = (const unsigned char*)src;
+  unsigned char* d = (unsigned char*)dst;
+  switch (v) {
+    case 16: copy_rows_2d_kernel<uint4><<<g, 256, 0, stream>>>(s, src_pitch, d, dst_pitch, vpr, n); break;
+    case 8: copy_rows_2d_kernel<uint64_t><<<g, 256, 0, stream>>>(s, src_pitch, d, dst_pitch, vpr, n); break;
+    case 4: copy_rows_2d_kernel<uint32_t><<<g, 256, 0, stream>>>(s, src_pitch, d, dst_pitch, vpr, n); break;
+    case 2: copy_rows_2d_kernel<uint16_t><<<g, 256, 0, stream>>>(s, src_pitch, d, dst_pitch, vpr, n); break;
+    default: copy_rows_2d_kernel<uint8_t><<<g, 256, 0, stream>>>(s, src_pitch, d, dst_pitch, vpr, n); break;
+  }
+  B200X_LAUNCH_CHECK("copy_rows_2d_kernel");
   return B200X_OK;
 }
 

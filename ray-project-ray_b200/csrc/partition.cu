@@ -147,6 +147,83 @@ extern "C" int b200x_count_adjacent_equal(const void* keys, int key_type, size_t
   return B200X_OK;
 }
 
+// Multi-column sort, first column almost distinct: after a stable sort by the first key column alone the
+// order is already final everywhere except inside runs of equal first keys. Every such run (found by its
+// first position) is put in order by the remaining key columns with a stable insertion sort on the
+// permutation entries - the remaining columns are read through the permutation, so nothing but `perm`
+// changes. Runs longer than FIX_MAX_RUN are left alone and reported: the caller then sorts the usual way.
+constexpr int FIX_MAX_RUN = 64;
+constexpr int FIX_MAX_COLS = 3;
+struct TieCols {
+  const void* col[FIX_MAX_COLS];
+  int kt[FIX_MAX_COLS];
+  int n;
+};
+
+__device__ __forceinline__ bool tie_less(const TieCols& tc, bool desc, uint32_t a, uint32_t b) {  // row a sorts before row b
+  for (int c = 0; c < tc.n; ++c) {
+    const uint64_t ca = load_encode(tc.col[c], a, tc.kt[c], desc), cb = load_encode(tc.col[c], b, tc.kt[c], desc);
+    if (ca != cb) return ca < cb;
+  }
+  return false;
+}
+
+__global__ void __launch_bounds__(256)
+fix_ties_kernel(const void* __restrict__ keys, int kt, uint64_t n, uint32_t* __restrict__ perm, const TieCols tc, int desc,
+                unsigned long long* __restrict__ stats /* [0] rows in tie runs, [1] longest run */) {
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i + 1 < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t k = load_encode(keys, i, kt, false);
+    if (load_encode(keys, i + 1, kt, false) != k) continue;
+    if (i > 0 && load_encode(keys, i - 1, kt, false) == k) continue;  // not the first row of its run
+    uint64_t len = 2;
+    while (i + len < n && len <= FIX_MAX_RUN && load_encode(keys, i + len, kt, false) == k) ++len;
+    atomicAdd(&stats[0], (unsigned long long)len);
+    atomicMax(&stats[1], (unsigned long long)len);
+    if (len > FIX_MAX_RUN) continue;
+    uint32_t* p = perm + i;
+    for (uint32_t j = 1; j < (uint32_t)len; ++j) {
+      const uint32_t pj = p[j];
+      uint32_t q = j;
+      while (q > 0) {
+        const uint32_t pk = p[q - 1];
+        if (!tie_less(tc, desc != 0, pj, pk)) break;   // stable: equal rows keep their order
+        p[q] = pk;
+        --q;
+      }
+      p[q] = pj;
+    }
+  }
+}
+
+extern "C" int b200x_fix_ties(const void* keys_sorted, int key_type, size_t n, uint32_t* perm, const void* const* cols_host,
+                              const int* types_host, int num_cols, int descending, unsigned long long* stats_out,
+                              void* stream_) {
+  if (stats_out == nullptr || key_type < 0 || key_type >= KEY_TYPE_COUNT || num_cols < 1 || num_cols > FIX_MAX_COLS ||
+      cols_host == nullptr || types_host == nullptr || (n > 0 && (keys_sorted == nullptr || perm == nullptr))) {
+    set_error("b200x_fix_ties: bad arguments (1..%d further key columns)", FIX_MAX_COLS);
+    return B200X_ERR_ARG;
+  }
+  TieCols tc;
+  tc.n = num_cols;
+  for (int c = 0; c < FIX_MAX_COLS; ++c) {
+    tc.col[c] = c < num_cols ? cols_host[c] : nullptr;
+    tc.kt[c] = c < num_cols ? types_host[c] : 0;
+    if (c < num_cols && (tc.col[c] == nullptr || tc.kt[c] < 0 || tc.kt[c] >= KEY_TYPE_COUNT)) {
+      set_error("b200x_fix_ties: key column %d is NULL or has a bad type", c);
+      return B200X_ERR_ARG;
+    }
+  }
+  cudaStream_t st = (cudaStream_t)stream_;
+  B200X_CUDA(cudaMemsetAsync(stats_out, 0, 2 * sizeof(unsigned long long), st));
+  if (n < 2) return B200X_OK;
+  uint64_t blocks = (n + 255) / 256;
+  const uint64_t cap = (uint64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  fix_ties_kernel<<<(uint32_t)blocks, 256, 0, st>>>(keys_sorted, key_type, n, perm, tc, descending, stats_out);
+  B200X_LAUNCH_CHECK("fix_ties_kernel");
+  return B200X_OK;
+}
+
 // Fixed-width byte-string keys: bytes [offset, offset + width) of every row as one big-endian unsigned
 // integer, left-aligned in OUT (zero-padded on the right), so that comparing the integers compares
 // the byte strings lexicographically (the order pyarrow gives binary / fixed_size_binary columns).

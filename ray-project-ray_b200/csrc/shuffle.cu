@@ -102,7 +102,7 @@ perm_indices_kernel(const PermSpec s, int inverse, uint64_t start, uint64_t coun
 template <typename V>
 __global__ void __launch_bounds__(256)
 permute_rows_kernel(const V* __restrict__ src, V* __restrict__ dst, const PermSpec s, int inverse,
-                    uint32_t vec_per_row, uint32_t lanes_per_row) {
+                    uint32_t vec_per_row, uint32_t lanes_per_row, uint32_t src_pitch_vec, uint32_t dst_pitch_vec) {
   const uint64_t n = s.n;
   const unsigned lane = threadIdx.x & 31;
   const uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -117,8 +117,8 @@ permute_rows_kernel(const V* __restrict__ src, V* __restrict__ dst, const PermSp
       const uint32_t srow = __shfl_sync(0xffffffffu, sr, ri);
       const uint64_t r = r0 + ri;
       if (r < n) {
-        const V* sp = src + (uint64_t)srow * vec_per_row;
-        V* dp = dst + r * vec_per_row;
+        const V* sp = src + (uint64_t)srow * src_pitch_vec;
+        V* dp = dst + r * dst_pitch_vec;
         for (uint32_t c = c0; c < vec_per_row; c += lanes_per_row) dp[c] = sp[c];
       }
     }
@@ -193,12 +193,44 @@ extern "C" int b200x_permute_rows(const void* src, size_t row_bytes, size_t n, u
   if (blocks > cap) blocks = cap;
   const uint32_t g = (uint32_t)blocks;
   switch (v) {
-    case 16: permute_rows_kernel<uint4><<<g, 256, 0, stream>>>((const uint4*)src, (uint4*)dst, s, inverse, vpr, lpr); break;
-    case 8: permute_rows_kernel<uint64_t><<<g, 256, 0, stream>>>((const uint64_t*)src, (uint64_t*)dst, s, inverse, vpr, lpr); break;
-    case 4: permute_rows_kernel<uint32_t><<<g, 256, 0, stream>>>((const uint32_t*)src, (uint32_t*)dst, s, inverse, vpr, lpr); break;
-    case 2: permute_rows_kernel<uint16_t><<<g, 256, 0, stream>>>((const uint16_t*)src, (uint16_t*)dst, s, inverse, vpr, lpr); break;
-    default: permute_rows_kernel<uint8_t><<<g, 256, 0, stream>>>((const uint8_t*)src, (uint8_t*)dst, s, inverse, vpr, lpr); break;
+    case 16: permute_rows_kernel<uint4><<<g, 256, 0, stream>>>((const uint4*)src, (uint4*)dst, s, inverse, vpr, lpr, vpr, vpr); break;
+    case 8: permute_rows_kernel<uint64_t><<<g, 256, 0, stream>>>((const uint64_t*)src, (uint64_t*)dst, s, inverse, vpr, lpr, vpr, vpr); break;
+    case 4: permute_rows_kernel<uint32_t><<<g, 256, 0, stream>>>((const uint32_t*)src, (uint32_t*)dst, s, inverse, vpr, lpr, vpr, vpr); break;
+    case 2: permute_rows_kernel<uint16_t><<<g, 256, 0, stream>>>((const uint16_t*)src, (uint16_t*)dst, s, inverse, vpr, lpr, vpr, vpr); break;
+    default: permute_rows_kernel<uint8_t><<<g, 256, 0, stream>>>((const uint8_t*)src, (uint8_t*)dst, s, inverse, vpr, lpr, vpr, vpr); break;
   }
+  B200X_LAUNCH_CHECK("permute_rows_kernel");
+  return B200X_OK;
+}
+
+// The same permutation for rows kept at a pitch (records, see b200x_gather_rows_pitched): only the first
+// row_bytes bytes of every record move; bases, pitches and row_bytes are multiples of 16.
+extern "C" int b200x_permute_rows_pitched(const void* src, size_t src_pitch, size_t n, uint64_t seed, int inverse,
+                                          void* dst, size_t dst_pitch, size_t row_bytes, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (int rc = check_perm_n("b200x_permute_rows_pitched", n)) return rc;
+  if (n == 0 || row_bytes == 0) return B200X_OK;
+  if (src == nullptr || dst == nullptr || row_bytes > src_pitch || row_bytes > dst_pitch || row_bytes > (1u << 20) ||
+      src_pitch > (1u << 24) || dst_pitch > (1u << 24)) {
+    set_error("b200x_permute_rows_pitched: NULL pointer, or row_bytes=%zu / pitches (%zu, %zu) out of range", row_bytes,
+              src_pitch, dst_pitch);
+    return B200X_ERR_ARG;
+  }
+  if ((((uintptr_t)src | (uintptr_t)dst | src_pitch | dst_pitch | row_bytes) & 15) != 0) {
+    set_error("b200x_permute_rows_pitched: bases, pitches and row_bytes must be multiples of 16");
+    return B200X_ERR_ALIGN;
+  }
+  const PermSpec s = make_spec(n, seed);
+  const uint32_t vpr = (uint32_t)(row_bytes / 16);
+  uint32_t lpr = 1;
+  while (lpr < vpr && lpr < 32) lpr <<= 1;
+  uint64_t blocks = ((uint64_t)n * lpr + 255) / 256;
+  const uint64_t cap = (uint64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  prof_begin(stream, PROF_PERMUTE);
+  permute_rows_kernel<uint4><<<(uint32_t)blocks, 256, 0, stream>>>((const uint4*)src, (uint4*)dst, s, inverse, vpr, lpr,
+                                                                  (uint32_t)(src_pitch / 16), (uint32_t)(dst_pitch / 16));
+  prof_end(stream);
   B200X_LAUNCH_CHECK("permute_rows_kernel");
   return B200X_OK;
 }

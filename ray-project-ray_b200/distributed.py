@@ -30,7 +30,7 @@ import torch
 import torch.distributed as dist
 
 from . import ops
-from .block import DeviceBlock, DeviceBlockAccessor, _contig
+from .block import DeviceBlock, DeviceBlockAccessor, _contig, record_groups
 from .sort_task_spec import SortKey
 
 
@@ -280,6 +280,39 @@ def _gather_samples(sample_codes: torch.Tensor, samples_per_rank: int, world: in
     return np.concatenate([row[1:1 + int(row[0])].view(np.uint64) for row in host])
 
 
+def _exchange_units(local: DeviceBlock, key_cols: Sequence[str]):
+    """What travels in a sort exchange, in sending order: the key columns (dense; `<col>::be<i>` chunk names are
+    materialised here), then every record group as ONE column of whole records, then the remaining columns.
+    Returns (units: name -> dense tensor, groups, names of the non-key units)."""
+    groups, _ = record_groups(local)
+    in_group = {k for g in groups for k in g.members}
+    units: Dict[str, torch.Tensor] = {k: local.key_column(k) for k in key_cols}
+    rest = []
+    for i, g in enumerate(groups):
+        units[f"\x00rec{i}"] = g.rec
+        rest.append(f"\x00rec{i}")
+    for c in local.column_names:
+        if c not in in_group and c not in units:
+            units[c] = _contig(local.columns[c])
+            rest.append(c)
+    return units, groups, rest
+
+
+def _assemble_sorted(local: DeviceBlock, groups, recv: Dict[str, torch.Tensor], perm2: torch.Tensor, first: str, skeys2,
+                     n_recv: int, dev) -> DeviceBlock:
+    """The received rows in sorted order: records are gathered whole and re-cut into their member columns."""
+    in_group = {k for g in groups for k in g.members}
+    out_cols: Dict[str, torch.Tensor] = {}
+    for i, g in enumerate(groups):
+        out_cols.update(g.views(ops.gather_records(recv[f"\x00rec{i}"], perm2)))
+    names = [c for c in local.column_names if c not in in_group and not (skeys2 is not None and c == first)]
+    outs = ops.gather_columns([recv[c] for c in names], perm2)
+    out_cols.update(zip(names, outs))
+    if skeys2 is not None and first in local.columns and first not in in_group:
+        out_cols[first] = skeys2
+    return DeviceBlock({c: out_cols[c] for c in local.column_names}, num_rows=n_recv, device=dev)
+
+
 def _p2p_partition_sort(local: DeviceBlock, sort_key: SortKey, n: int, dev, group, samples_per_rank: int) -> DeviceBlock:
     """Partition-first distributed sort over peer memory:
       sample raw keys -> identical splitters on every rank -> per-row (owner, slot) targets (stable split,
@@ -289,7 +322,8 @@ def _p2p_partition_sort(local: DeviceBlock, sort_key: SortKey, n: int, dev, grou
     world = dist.get_world_size(group)
     key_cols = sort_key.get_columns()
     first, desc = key_cols[0], sort_key.get_descending()
-    keycol = _contig(local.columns[first])
+    units, groups, rest = _exchange_units(local, key_cols)
+    keycol = units[first]
     if n > 0:
         m = min(samples_per_rank, n)
         pos = ((np.arange(m, dtype=np.float64) + 0.5) * (n / m)).astype(np.int64).astype(np.int32)
@@ -302,9 +336,7 @@ def _p2p_partition_sort(local: DeviceBlock, sort_key: SortKey, n: int, dev, grou
     sp = torch.from_numpy(splitters.view(np.int64)).to(dev)
     target, counts = ops.partition_targets(keycol, desc, sp)
     send_counts = [int(c) for c in counts.cpu().tolist()[:world]]
-    cols = {name: (_contig(local.columns[name]), None)
-            for name in key_cols + [c for c in local.column_names if c not in key_cols]}
-    rest = [c for c in cols if c not in key_cols]
+    cols = {name: (t, None) for name, t in units.items()}
     ex = P2PExchange(cols, n, send_counts, dev, group, target=target)
     main = torch.cuda.current_stream(dev)
     ex.fence()
@@ -313,7 +345,7 @@ def _p2p_partition_sort(local: DeviceBlock, sort_key: SortKey, n: int, dev, grou
     if ex.n_recv == 0:
         ex.send(rest)
         ex.fence()
-        return DeviceBlock({k: v.clone() for k, v in ex.view(list(cols)).items()}, num_rows=0, device=dev)
+        return local.slice(0, 0)
     keys_block = DeviceBlock(ex.view(key_cols), num_rows=ex.n_recv, device=dev)
     side = _side_stream(dev)
     landed, sorted_ev = torch.cuda.Event(), torch.cuda.Event()
@@ -338,13 +370,7 @@ def _p2p_partition_sort(local: DeviceBlock, sort_key: SortKey, n: int, dev, grou
     perm2.record_stream(main)
     if skeys2 is not None:
         skeys2.record_stream(main)
-    recv = ex.view(list(cols))
-    names = [c for c in local.column_names if not (skeys2 is not None and c == first)]
-    outs = ops.gather_columns([recv[c] for c in names], perm2)
-    out_cols = dict(zip(names, outs))
-    if skeys2 is not None:
-        out_cols[first] = skeys2
-    return DeviceBlock({c: out_cols[c] for c in local.column_names}, num_rows=ex.n_recv, device=dev)
+    return _assemble_sorted(local, groups, ex.view(list(cols)), perm2, first, skeys2, ex.n_recv, dev)
 
 
 def _p2p_sort_exchange(local: DeviceBlock, sort_key: SortKey, perm, skeys, n: int, send_counts, dev, group) -> DeviceBlock:
@@ -354,7 +380,7 @@ def _p2p_sort_exchange(local: DeviceBlock, sort_key: SortKey, perm, skeys, n: in
     first = key_cols[0]
     cols = {}
     for name in key_cols + [c for c in local.column_names if c not in key_cols]:
-        col = _contig(local.columns[name])
+        col = local.key_column(name) if name in key_cols else _contig(local.columns[name])
         cols[name] = (skeys, None) if (skeys is not None and name == first) else (col, perm)
     rest = [c for c in cols if c not in key_cols]
     ex = P2PExchange(cols, n, send_counts, dev, group)

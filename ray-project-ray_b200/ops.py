@@ -116,6 +116,60 @@ def gather(col: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
     return out
 
 
+def gather_records(rec: torch.Tensor, idx: torch.Tensor, row_bytes: Optional[int] = None) -> torch.Tensor:
+    """out[i, :row_bytes] = rec[idx[i], :row_bytes] for a record buffer `rec` ([n, pitch] uint8, pitch and row_bytes
+    multiples of 16); the result has the same pitch."""
+    dev = _require_cuda(rec, idx)
+    n, pitch = idx.numel(), rec.shape[1]
+    row_bytes = pitch if row_bytes is None else row_bytes
+    out = torch.empty((n, pitch), dtype=torch.uint8, device=dev)
+    if n:
+        with torch.cuda.device(dev):
+            _lib.call("b200x_gather_rows_pitched", rec.data_ptr(), pitch, idx.data_ptr(), n, out.data_ptr(), pitch,
+                      row_bytes, _stream(dev))
+    return out
+
+
+def permute_records(rec: torch.Tensor, seed: int, inverse: bool = False, row_bytes: Optional[int] = None) -> torch.Tensor:
+    """out[j, :row_bytes] = rec[pi_seed(j), :row_bytes] for a record buffer ([n, pitch] uint8)."""
+    dev = _require_cuda(rec)
+    n, pitch = rec.shape
+    row_bytes = pitch if row_bytes is None else row_bytes
+    out = torch.empty_like(rec)
+    if n:
+        with torch.cuda.device(dev):
+            _lib.call("b200x_permute_rows_pitched", rec.data_ptr(), pitch, n, seed & 0xFFFFFFFFFFFFFFFF, int(inverse),
+                      out.data_ptr(), pitch, row_bytes, _stream(dev))
+    return out
+
+
+def copy_rows_2d(src_ptr: int, src_pitch: int, dst_ptr: int, dst_pitch: int, row_bytes: int, n: int,
+                 dev: torch.device) -> None:
+    """dst[r, :row_bytes] = src[r, :row_bytes] between two row pitches (raw device addresses: the caller keeps the
+    tensors alive)."""
+    if n and row_bytes:
+        with torch.cuda.device(dev):
+            _lib.call("b200x_copy_rows_2d", src_ptr, src_pitch, dst_ptr, dst_pitch, row_bytes, n, _stream(dev))
+
+
+def fix_ties(keys_sorted: torch.Tensor, perm: torch.Tensor, cols: Sequence[torch.Tensor], descending: bool) -> torch.Tensor:
+    """Order every run of equal keys in `keys_sorted` (the first key column after a stable sort by it alone; int64
+    codes count as uint64) by the remaining key columns `cols`, in place in `perm`. Returns int64[2] on the device:
+    rows inside tie runs, longest run (runs above 64 rows are left untouched)."""
+    dev = _require_cuda(keys_sorted, perm, *cols)
+    stats = torch.empty(2, dtype=torch.int64, device=dev)
+    ptrs = (ctypes.c_void_p * len(cols))(*[c.data_ptr() for c in cols])
+    types = (ctypes.c_int * len(cols))(*[key_type_of(c) for c in cols])
+    with torch.cuda.device(dev):
+        _lib.call("b200x_fix_ties", keys_sorted.data_ptr(), key_type_of(keys_sorted), keys_sorted.numel(), perm.data_ptr(),
+                  ptrs, types, len(cols), int(descending), stats.data_ptr(), _stream(dev))
+    return stats
+
+
+FIX_TIES_MAX_RUN = 64
+FIX_TIES_MAX_COLS = 3
+
+
 def gather_columns(cols: Sequence[torch.Tensor], idx: torch.Tensor) -> List[torch.Tensor]:
     """Gather several columns with one index vector; 8-byte 1-D columns share one launch."""
     outs: List[Optional[torch.Tensor]] = [None] * len(cols)
@@ -168,15 +222,20 @@ def _chunk_dtype(width: int) -> torch.dtype:
 
 def pack_key_bytes(col: torch.Tensor, offset: int, width: int) -> torch.Tensor:
     """Bytes [offset, offset + width) of every row of a [n, w] uint8 column as a big-endian unsigned integer
-    column (uint16 / uint32 / uint64 by width, left-aligned)."""
-    dev = _require_cuda(col)
-    if col.dim() != 2 or col.dtype != torch.uint8:
+    column (uint16 / uint32 / uint64 by width, left-aligned). The column may lie at a row pitch (a record member)."""
+    if not col.is_cuda:
+        raise RuntimeError("b200x ops need CUDA tensors: the device path has no CPU fallback")
+    if col.dim() != 2 or col.dtype != torch.uint8 or (col.shape[0] > 1 and col.stride(1) != 1):
         raise TypeError("byte-string keys are [n, width] uint8 columns")
+    dev = col.device
     n, w = col.shape
+    pitch = col.stride(0) if n > 1 else w
+    if offset + width > w:
+        raise ValueError("chunk outside the key column")
     out = torch.empty(n, dtype=_chunk_dtype(width), device=dev)
     if n:
         with torch.cuda.device(dev):
-            _lib.call("b200x_pack_key_bytes", col.data_ptr(), w, offset, width, n, out.data_ptr(), out.element_size(),
+            _lib.call("b200x_pack_key_bytes", col.data_ptr(), pitch, offset, width, n, out.data_ptr(), out.element_size(),
                       _stream(dev))
     return out
 

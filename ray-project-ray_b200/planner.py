@@ -16,7 +16,7 @@ import torch
 from . import ops
 from .aggregate import AggregateFn
 from .aggregate_task_spec import SortAggregateTaskSpec
-from .block import DeviceBlock, DeviceBlockAccessor, _contig
+from .block import BYTE_KEY_SEP, DeviceBlock, DeviceBlockAccessor, _contig, _row_pitch
 from .context import DataContext
 from .interfaces import (AllToAllTransformFn, ExchangeTaskSpec, RefBundle, StatsDict, TaskContext, _NullProgressBar)
 from .schedulers import (AutoBoundaries, GpuExchangeScheduler, PullBasedShuffleTaskScheduler,
@@ -109,7 +109,6 @@ def _unified_schema(metadata):
     return None
 
 
-BYTE_KEY_SEP = "::be"
 
 
 def _byte_key_columns(blocks: List[DeviceBlock], sort_key: SortKey) -> List[str]:
@@ -125,7 +124,21 @@ def _expand_byte_keys(refs: List[RefBundle], sort_key: SortKey, byte_cols: List[
     """A w-byte string key sorts like the tuple of its big-endian 8-byte chunks: replace the key column by
     those chunks as unsigned integer columns `<name>::be<i>` and sort by them (every scheduler, the boundary
     sampling and the multi-GPU exchange then see an ordinary multi-column integer key). The chunks hold
-    every byte of the key, so the key column itself does not travel: it is rebuilt from the sorted chunks."""
+    every byte of the key, so the key column itself does not travel: it is rebuilt from the sorted chunks.
+
+    A key column that is a record member travels inside its record anyway. Under the fused scheduler such a
+    column is left where it is and only the SortKey is rewritten: the chunk names are then resolved on demand by
+    `DeviceBlock.key_column`, and nothing is added to or rebuilt in the blocks."""
+    if DataContext.get_current().use_fused_device_exchange and all(
+            _row_pitch(b.columns[k]) is not None for ref in refs for b, _ in ref.blocks if b.num_rows for k in byte_cols):
+        new_cols = []
+        for k in sort_key.get_columns():
+            if k in byte_cols:
+                w = next(int(b.columns[k].shape[1]) for ref in refs for b, _ in ref.blocks if b.columns)
+                new_cols += [f"{k}{BYTE_KEY_SEP}{i}" for i in range((w + 7) // 8)]
+            else:
+                new_cols.append(k)
+        return refs, SortKey(new_cols, descending=[sort_key.get_descending()] * len(new_cols)), None
     out_refs, width, order = [], {}, None
     for ref in refs:
         pairs = []
@@ -155,6 +168,8 @@ def _expand_byte_keys(refs: List[RefBundle], sort_key: SortKey, byte_cols: List[
 
 def _restore_byte_keys(refs: List[RefBundle], packed) -> List[RefBundle]:
     """Undo _expand_byte_keys on the output blocks: chunks -> key column, original column order."""
+    if packed is None:   # the key columns travelled inside their records
+        return refs
     width, order = packed
     out = []
     for ref in refs:
@@ -179,17 +194,18 @@ def generate_sort_fn(sort_key: SortKey,
                      _debug_limit_shuffle_execution_to_num_blocks: Optional[int] = None) -> AllToAllTransformFn:
     """Sort blocks by the key column(s) (planner/sort.py:21-74)."""
 
-    def fn(sort_key: SortKey, refs: List[RefBundle], ctx: TaskContext) -> Tuple[List[RefBundle], StatsDict]:
+    def fn(sort_key: SortKey, refs: List[RefBundle], ctx: TaskContext, _expanded: bool = False) -> Tuple[List[RefBundle], StatsDict]:
         blocks, metadata = _blocks_and_meta(refs)
         if len(blocks) == 0:
             return (blocks, {})
-        sort_key.validate_schema(_unified_schema(metadata))
-        byte_cols = _byte_key_columns(blocks, sort_key)
+        if not _expanded:
+            sort_key.validate_schema(_unified_schema(metadata))
+        byte_cols = [] if _expanded else _byte_key_columns(blocks, sort_key)
         if byte_cols:
             if sort_key.boundaries:
                 raise ValueError("user-specified boundaries are numeric; they cannot cut a byte-string key")
             refs2, sort_key2, packed = _expand_byte_keys(refs, sort_key, byte_cols)
-            out, stats = fn(sort_key2, refs2, ctx)
+            out, stats = fn(sort_key2, refs2, ctx, True)
             return _restore_byte_keys(out, packed), stats
         num_outputs = len(blocks)  # same number of output partitions as mappers
         if not sort_key.boundaries and DataContext.get_current().use_fused_device_exchange:

@@ -382,7 +382,7 @@ def _cut_sorted_evenly(table: DeviceBlock, key: str, descending: bool, parts: in
     n = table.num_rows
     if parts <= 1 or n == 0:
         return [table] + [DeviceBlock.empty(table.device) for _ in range(parts - 1)]
-    cuts = ops.even_cuts(_contig(table.columns[key]), descending, parts).cpu().tolist()
+    cuts = ops.even_cuts(table.key_column(key), descending, parts).cpu().tolist()
     return _cut(table, [int(c) for c in cuts])
 
 
@@ -477,7 +477,7 @@ def fused_sort(blocks: List[DeviceBlock], boundaries: List[Any], sort_key: SortK
         return _cut_sorted_evenly(out, first, sort_key.get_descending(), R)
     if any(b is None or (isinstance(b, tuple) and b[0] is None) for b in boundaries):
         return [out] + [DeviceBlock.empty(table.device) for _ in range(R - 1)]
-    cuts = find_partition_indices(out.columns[first], boundaries, sort_key.get_descending())
+    cuts = find_partition_indices(out.key_column(first), boundaries, sort_key.get_descending())
     return _cut(out, cuts)
 
 

@@ -29,6 +29,7 @@ def main():
     ap.add_argument("--rows", type=int, default=125_000_000, help="records per GPU")
     ap.add_argument("--steps", type=int, default=4)
     ap.add_argument("--warmup", type=int, default=2)
+    ap.add_argument("--records", type=int, default=1, help="1 = 128-byte record layout, 0 = two dense columns")
     a = ap.parse_args()
     import ray_project_ray_b200.data as rd
     from ray_project_ray_b200 import ops
@@ -49,7 +50,8 @@ def main():
     payload[:, :8] = recno.view(torch.uint8).reshape(n, 8)
     want_sum = int(recno.sum().item())
     del recno
-    ds = rd.from_torch_columns({"key": key, "payload": payload}, override_num_blocks=4)
+    ds = rd.from_torch_columns({"key": key, "payload": payload}, override_num_blocks=4, records=bool(a.records))
+    del key, payload
 
     def barrier():
         if world > 1:
@@ -73,7 +75,7 @@ def main():
     got_sum, first, last = 0, None, None
     prev_hi = prev_lo = None
     for b in blocks:
-        k = b.columns["key"].contiguous()
+        k = b.columns["key"]
         hi = ops.pack_key_bytes(k, 0, 8).view(torch.int64) ^ (-0x8000000000000000)   # unsigned order as signed
         lo = ops.pack_key_bytes(k, 8, 2).view(torch.int16).to(torch.int32) & 0xFFFF
         ok = (hi[1:] > hi[:-1]) | ((hi[1:] == hi[:-1]) & (lo[1:] >= lo[:-1]))

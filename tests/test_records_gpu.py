@@ -1,0 +1,196 @@
+"""GPU tests of the record layout (several columns of a row side by side in one record at a 16-byte
+aligned pitch, block.py "Record layout") and of the tie repair of multi-column sorts. Everything is
+compared bit for bit with the CPU oracle on the same inputs; the kernels are called through the C ABI."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+import ray_project_ray_b200.data as rd
+from oracle import exchange_oracle as orc
+from ray_project_ray_b200 import _lib, ops
+from ray_project_ray_b200.block import (BlockAccessor, DeviceBlock, _row_pitch, auto_pitch, record_groups)
+from ray_project_ray_b200.context import DataContext
+from ray_project_ray_b200.sort_task_spec import SortKey
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(autouse=True)
+def _restore_context():
+    ctx = DataContext.get_current()
+    saved = (ctx.use_push_based_shuffle, ctx.use_fused_device_exchange)
+    yield
+    ctx.use_push_based_shuffle, ctx.use_fused_device_exchange = saved
+
+
+def _gensort(n, seed, dup_hi=0, dup_full=0):
+    rng = np.random.default_rng(seed)
+    key = rng.integers(0, 256, (n, 10)).astype(np.uint8)
+    if dup_hi:      # rows that share their first 8 key bytes with another row: the last two bytes decide
+        src = rng.integers(0, n, dup_hi)
+        dst = rng.integers(0, n, dup_hi)
+        key[dst, :8] = key[src, :8]
+    if dup_full:    # exact duplicates: input order decides
+        src = rng.integers(0, n, dup_full)
+        dst = rng.integers(0, n, dup_full)
+        key[dst] = key[src]
+    payload = rng.integers(0, 256, (n, 90)).astype(np.uint8)
+    payload[:, :8] = np.arange(n, dtype=np.int64).view(np.uint8).reshape(n, 8)
+    return key, payload
+
+
+def test_to_records_layout_and_round_trip(cuda_device):
+    key, payload = _gensort(5000, 1)
+    v = np.arange(5000, dtype=np.int64) * 3
+    b = DeviceBlock.from_numpy({"key": key, "v": v, "payload": payload}, cuda_device)
+    r = b.to_records()
+    assert auto_pitch(10 + 6 + 8 + 90) == 128
+    groups, loose = record_groups(r)
+    assert len(groups) == 1 and not loose and groups[0].pitch == 128
+    assert groups[0].members["key"][0] == 0 and groups[0].members["v"][0] == 16 and groups[0].members["payload"][0] == 24
+    assert all(_row_pitch(r.columns[k]) == 128 for k in r.columns)
+    assert r.schema() == b.schema()
+    got = r.to_numpy()
+    np.testing.assert_array_equal(got["key"], key)
+    np.testing.assert_array_equal(got["v"], v)
+    np.testing.assert_array_equal(got["payload"], payload)
+    # padding is zero, slices stay record views and re-join without a copy
+    rec = groups[0].rec.cpu().numpy()
+    assert not rec[:, 10:16].any() and not rec[:, 114:].any()
+    parts = [r.slice(0, 1234), r.slice(1234, 1234), r.slice(1234, 5000)]
+    joined = DeviceBlock.concat(parts)
+    assert joined.columns["payload"].data_ptr() == r.columns["payload"].data_ptr()
+    assert len(record_groups(joined)[0]) == 1
+    np.testing.assert_array_equal(joined.to_numpy()["payload"], payload)
+    # a chosen pitch, a subset of the columns
+    r2 = b.to_records(["key", "payload"], pitch=112)
+    g2, loose2 = record_groups(r2)
+    assert g2[0].pitch == 112 and loose2 == ["v"]
+    np.testing.assert_array_equal(r2.to_numpy()["payload"], payload)
+    with pytest.raises(ValueError):
+        b.to_records(pitch=100)
+
+
+@pytest.mark.parametrize("desc", [False, True])
+@pytest.mark.parametrize("n,dup_hi,dup_full", [(200_000, 0, 0), (200_000, 3000, 500), (70_000, 70_000, 5000), (3000, 10, 10)])
+def test_sort_gensort_records(n, dup_hi, dup_full, desc, cuda_device):
+    """Dataset.sort by the 10-byte key of gensort records kept as 128-byte records: pyarrow's order incl. ties."""
+    key, payload = _gensort(n, 7 + n, dup_hi, dup_full)
+    ds = rd.from_numpy_columns({"key": key, "payload": payload}, override_num_blocks=4, records=True)
+    assert all(_row_pitch(b.columns["payload"]) == 128 for b in ds.get_internal_block_refs())
+    out = ds.sort("key", descending=desc)
+    assert out.columns() == ["key", "payload"] and out.num_blocks() == 4
+    want = orc.stable_argsort_bytes(key, desc)
+    got = out.to_numpy()
+    np.testing.assert_array_equal(got["key"], key[want])
+    np.testing.assert_array_equal(got["payload"], payload[want])
+    # the output blocks are records again
+    assert all(len(record_groups(b)[0]) == 1 for b in out.get_internal_block_refs() if b.num_rows)
+
+
+@pytest.mark.parametrize("sched", ["pull", "push"])
+def test_sort_records_task_schedulers(sched, cuda_device):
+    ctx = DataContext.get_current()
+    ctx.use_fused_device_exchange = False
+    ctx.use_push_based_shuffle = sched == "push"
+    key, payload = _gensort(30_000, 3, 2000, 100)
+    ds = rd.from_numpy_columns({"key": key, "payload": payload}, override_num_blocks=5, records=True)
+    got = ds.sort("key").to_numpy()
+    want = orc.stable_argsort_bytes(key, False)
+    np.testing.assert_array_equal(got["key"], key[want])
+    np.testing.assert_array_equal(got["payload"], payload[want])
+
+
+def test_sort_int_key_inside_record(cuda_device):
+    rng = np.random.default_rng(5)
+    n = 150_000
+    ident = rng.integers(-1000, 1000, n, dtype=np.int64)
+    x = rng.random(n)
+    payload = rng.integers(0, 256, (n, 64)).astype(np.uint8)
+    ds = rd.from_numpy_columns({"id": ident, "x": x, "payload": payload}, override_num_blocks=3, records=True)
+    for desc in (False, True):
+        got = ds.sort("id", descending=desc).to_numpy()
+        order = orc.stable_argsort(ident, desc)
+        np.testing.assert_array_equal(got["id"], ident[order])
+        np.testing.assert_array_equal(got["x"].view(np.int64), x[order].view(np.int64))
+        np.testing.assert_array_equal(got["payload"], payload[order])
+    # shuffle and groupby see the same columns
+    sh = ds.random_shuffle(seed=11).to_numpy()
+    p = orc.feistel_permutation(n, 11)
+    np.testing.assert_array_equal(sh["id"], ident[p])
+    np.testing.assert_array_equal(sh["payload"], payload[p])
+    agg = ds.groupby("id").count().to_numpy()
+    ids, cnt = np.unique(ident, return_counts=True)
+    np.testing.assert_array_equal(agg["id"], ids)
+    np.testing.assert_array_equal(agg["count()"], cnt)
+
+
+def test_take_and_select_on_records(cuda_device):
+    key, payload = _gensort(10_000, 9)
+    b = DeviceBlock.from_numpy({"key": key, "payload": payload}, cuda_device).to_records()
+    idx = np.random.default_rng(0).integers(0, 10_000, 777).astype(np.int32)
+    t = BlockAccessor.for_block(b).take(torch.from_numpy(idx).to(cuda_device)).to_numpy()
+    np.testing.assert_array_equal(t["key"], key[idx])
+    np.testing.assert_array_equal(t["payload"], payload[idx])
+    only_key = BlockAccessor.for_block(b.select(["key"])).take(torch.from_numpy(idx).to(cuda_device))
+    assert not record_groups(only_key)[0]          # 10 of 128 bytes: moved as a dense column instead
+    np.testing.assert_array_equal(only_key.to_numpy()["key"], key[idx])
+
+
+def test_pitched_kernels_through_the_abi(cuda_device):
+    """b200x_gather_rows_pitched / b200x_permute_rows_pitched / b200x_copy_rows_2d against numpy."""
+    rng = np.random.default_rng(2)
+    n, sp, dp, w = 4097, 128, 160, 112
+    src = rng.integers(0, 256, (n, sp)).astype(np.uint8)
+    idx = rng.integers(0, n, 3001).astype(np.int32)
+    d_src = torch.from_numpy(src).to(cuda_device)
+    d_idx = torch.from_numpy(idx).to(cuda_device)
+    dst = torch.zeros((idx.size, dp), dtype=torch.uint8, device=cuda_device)
+    st = torch.cuda.current_stream().cuda_stream
+    _lib.call("b200x_gather_rows_pitched", d_src.data_ptr(), sp, d_idx.data_ptr(), idx.size, dst.data_ptr(), dp, w, st)
+    got = dst.cpu().numpy()
+    np.testing.assert_array_equal(got[:, :w], src[idx, :w])
+    assert not got[:, w:].any()
+    out = torch.zeros((n, dp), dtype=torch.uint8, device=cuda_device)
+    _lib.call("b200x_permute_rows_pitched", d_src.data_ptr(), sp, n, 99, 0, out.data_ptr(), dp, w, st)
+    p = orc.feistel_permutation(n, 99)
+    np.testing.assert_array_equal(out.cpu().numpy()[:, :w], src[p, :w])
+    for row_bytes, s_off in ((90, 10), (8, 16), (3, 1), (112, 0)):
+        dense = torch.zeros((n, row_bytes), dtype=torch.uint8, device=cuda_device)
+        _lib.call("b200x_copy_rows_2d", d_src.data_ptr() + s_off, sp, dense.data_ptr(), row_bytes, row_bytes, n, st)
+        np.testing.assert_array_equal(dense.cpu().numpy(), src[:, s_off:s_off + row_bytes])
+    lib = _lib.load()
+    assert lib.b200x_gather_rows_pitched(d_src.data_ptr(), sp, d_idx.data_ptr(), 10, dst.data_ptr(), dp, 100, st) != 0
+    assert lib.b200x_gather_rows_pitched(d_src.data_ptr(), sp, d_idx.data_ptr(), 10, dst.data_ptr(), dp, 256, st) != 0
+    assert b"16" in lib.b200x_last_error_string() or b"pitch" in lib.b200x_last_error_string()
+
+
+@pytest.mark.parametrize("desc", [False, True])
+def test_fix_ties_against_lexsort(desc, cuda_device):
+    """Sort by the first column + b200x_fix_ties == stable sort by all columns (runs up to 64 rows)."""
+    rng = np.random.default_rng(12)
+    n = 300_000
+    a = rng.integers(0, n // 3, n, dtype=np.int64)            # runs of ~3 rows
+    a[1000:1050] = 17                                          # one run of >= 50 rows
+    b = rng.integers(0, 4, n).astype(np.uint16)
+    c = rng.integers(-2, 2, n).astype(np.int32)
+    da, db, dc = (torch.from_numpy(x.view(np.int16) if x.dtype == np.uint16 else x).to(cuda_device) for x in (a, b, c))
+    db = db.view(torch.uint16)
+    perm, _, skeys = ops.argsort(da, desc, want_keys=True)
+    stats = ops.fix_ties(skeys, perm, [db, dc], desc).cpu().numpy()
+    sgn = -1 if desc else 1
+    want = np.lexsort([sgn * c.astype(np.int64), sgn * b.astype(np.int64), sgn * a])
+    np.testing.assert_array_equal(perm.cpu().numpy().view(np.uint32), want.astype(np.uint32))
+    assert stats[0] > 0 and 50 <= stats[1] <= 64
+    # a run above the limit is reported and left alone
+    a2 = a.copy()
+    a2[:100] = 5
+    perm2, _, sk2 = ops.argsort(torch.from_numpy(a2).to(cuda_device), desc, want_keys=True)
+    assert ops.fix_ties(sk2, perm2, [db], desc).cpu().numpy()[1] > ops.FIX_TIES_MAX_RUN
+    # through the accessor: the chain takes over for such columns
+    blk = DeviceBlock.from_numpy({"a": a2, "b": b.view(np.int16), "c": c}, cuda_device)
+    perm3, _, _ = BlockAccessor.for_block(blk)._argsort(SortKey(["a", "b", "c"], descending=[desc] * 3), False)
+    want3 = np.lexsort([sgn * c.astype(np.int64), sgn * b.view(np.int16).astype(np.int64), sgn * a2])
+    np.testing.assert_array_equal(perm3.cpu().numpy().view(np.uint32), want3.astype(np.uint32))
