@@ -150,14 +150,18 @@ int b200x_count_adjacent_equal(const void* keys, int key_type, size_t n, uint64_
 
 /* Multi-column sort whose first column is (almost) distinct. After a stable sort by the first key column alone
  * (keys_sorted = that column in sorted order, or its codes with key_type U64; perm = the permutation, updated in
- * place) every run of equal first keys is ordered by the remaining num_cols (1..3) key columns - cols_host /
- * types_host are HOST arrays of device pointers / key types of those columns, indexed by row, compared as codes
- * in the given direction - with a stable insertion sort of the run's permutation entries. stats_out[0] (device) =
- * rows that lie in such runs, stats_out[1] = longest run; runs longer than 64 rows are left untouched, so a caller
- * that reads stats_out[1] > 64 must sort by all columns instead. Gives the order of pyarrow.compute.sort_indices
- * with several sort keys (transform_pyarrow.py:17-21) for one sort pass instead of one per column. */
+ * place) every run of equal first keys is ordered by the remaining num_cols (1..3) key columns with a stable
+ * insertion sort of the run's permutation entries. The *_host arguments are HOST arrays over those columns:
+ * cols_host[c] = device address of row 0's value, types_host[c] = its key type, strides_host[c] = bytes from one
+ * row's value to the next (NULL or 0 = dense), be_bytes_host[c] > 0 = the value is that many big-endian bytes (the
+ * next piece of a byte-string key, read where it lies inside the row's record; types_host[c] is then ignored;
+ * NULL = none). Values are compared as codes in the given direction. stats_out[0] (device) = rows that lie in such
+ * runs, stats_out[1] = longest run; runs longer than 64 rows are left untouched, so a caller that reads
+ * stats_out[1] > 64 must sort by all columns instead. Gives the order of pyarrow.compute.sort_indices with several
+ * sort keys (transform_pyarrow.py:17-21) for one sort pass instead of one per column. */
 int b200x_fix_ties(const void* keys_sorted, int key_type, size_t n, uint32_t* perm, const void* const* cols_host,
-                   const int* types_host, int num_cols, int descending, unsigned long long* stats_out, void* stream);
+                   const int* types_host, const unsigned long long* strides_host, const int* be_bytes_host, int num_cols,
+                   int descending, unsigned long long* stats_out, void* stream);
 
 /* out[i] = bytes [offset, offset + width) of row i of a fixed-width byte-string column (row_bytes per row)
  * as a big-endian unsigned integer, left-aligned in an out_bytes-wide (2, 4 or 8) unsigned integer and
@@ -166,6 +170,14 @@ int b200x_fix_ties(const void* keys_sorted, int key_type, size_t n, uint32_t* pe
  * gives binary / fixed_size_binary keys (transform_pyarrow.py:17-21; gensort-style 10-byte keys). */
 int b200x_pack_key_bytes(const void* col, size_t row_bytes, size_t offset, int width, size_t n, void* out,
                          int out_bytes, void* stream);
+
+/* All ceil(width / 8) chunks of b200x_pack_key_bytes in one pass over a key column whose rows lie row_pitch bytes
+ * apart, row_pitch a multiple of 16 (a key held inside a record, see b200x_gather_rows_pitched): each row's key
+ * is read with the aligned 16-byte loads that cover it. outs_host / out_bytes_host are HOST arrays: chunk k goes
+ * to outs_host[k] as an unsigned integer of out_bytes_host[k] bytes (8 for full chunks; 2, 4 or 8 for the last
+ * one, at least its byte count). width <= 32. Same reference call site as b200x_pack_key_bytes. */
+int b200x_pack_key_chunks(const void* col, size_t row_pitch, int width, size_t n, void* const* outs_host,
+                          const int* out_bytes_host, void* stream);
 
 /* The inverse of b200x_pack_key_bytes: writes the first `width` big-endian bytes of chunk[i] to bytes
  * [offset, offset + width) of row i (the key column is rebuilt from its sorted chunks instead of being

@@ -40,8 +40,8 @@ SIGNATURES = {
     "b200x_gather_rows": (c_int, [c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_void_p]),
     "b200x_gather_rows_pitched": (c_int, [c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_size_t, c_size_t, c_void_p]),
     "b200x_copy_rows_2d": (c_int, [c_void_p, c_size_t, c_void_p, c_size_t, c_size_t, c_size_t, c_void_p]),
-    "b200x_fix_ties": (c_int, [c_void_p, c_int, c_size_t, c_void_p, POINTER(c_void_p), POINTER(c_int), c_int, c_int,
-                               c_void_p, c_void_p]),
+    "b200x_fix_ties": (c_int, [c_void_p, c_int, c_size_t, c_void_p, POINTER(c_void_p), POINTER(c_int),
+                               POINTER(ctypes.c_ulonglong), POINTER(c_int), c_int, c_int, c_void_p, c_void_p]),
     "b200x_permute_rows_pitched": (c_int, [c_void_p, c_size_t, c_size_t, c_uint64, c_int, c_void_p, c_size_t, c_size_t,
                                            c_void_p]),
     "b200x_gather_columns8": (c_int, [POINTER(c_void_p), POINTER(c_void_p), c_int, c_void_p, c_size_t, c_void_p]),
@@ -69,6 +69,7 @@ SIGNATURES = {
     "b200x_finalize_groups": (c_int, [c_void_p, c_int, c_void_p, c_size_t, c_int, c_int, c_void_p, c_void_p]),
     "b200x_count_adjacent_equal": (c_int, [c_void_p, c_int, c_size_t, c_void_p, c_void_p]),
     "b200x_pack_key_bytes": (c_int, [c_void_p, c_size_t, c_size_t, c_int, c_size_t, c_void_p, c_int, c_void_p]),
+    "b200x_pack_key_chunks": (c_int, [c_void_p, c_size_t, c_int, c_size_t, POINTER(c_void_p), POINTER(c_int), c_void_p]),
     "b200x_unpack_key_bytes": (c_int, [c_void_p, c_int, c_int, c_void_p, c_size_t, c_size_t, c_size_t, c_void_p]),
     "b200x_group_quantile": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_void_p, c_int, c_size_t, c_double,
                                      c_void_p, c_void_p]),

@@ -18,6 +18,13 @@ columns keep their names, dtypes and shapes (they are strided torch views), but 
 per row whatever the column widths, instead of one pass per column (a gensort row = 10-byte key + 90-byte
 payload in a 128-byte record moves as one DRAM line; as two dense columns it moves in 2-byte pieces).
 
+A byte-string key column that lives inside a record may be accompanied by its **key prefix column**: the
+key's first 8 bytes as a dense big-endian uint64 column (`DeviceBlock.aux["<col>::be0"]`), i.e. the key kept
+columnar in directly radix-sortable form next to the row records (reading a 10-byte key out of 128-byte records
+costs a pass over every record: the L2 fetches whole 128-byte lines). It is built at ingest
+(`to_records(key_prefix=[...])`), comes out of every sort for free (the sort writes the sorted keys), and is simply
+dropped by operations that do not maintain it - `key_column` packs it again on demand.
+
 Null values and variable-width columns are outside the device format (fixed-width
 int/float keys and payloads); ingesting an Arrow column with nulls raises.
 """
@@ -255,11 +262,13 @@ def auto_pitch(used: int) -> int:
 class DeviceBlock:
     """A columnar block resident in HBM. Immutable by convention; slices are views."""
 
-    __slots__ = ("columns", "_n", "device")
+    __slots__ = ("columns", "_n", "device", "aux")
 
     def __init__(self, columns: Dict[str, torch.Tensor], num_rows: Optional[int] = None,
-                 device: Optional[torch.device] = None):
+                 device: Optional[torch.device] = None, aux: Optional[Dict[str, torch.Tensor]] = None):
         self.columns: Dict[str, torch.Tensor] = dict(columns)
+        # key prefix columns (module docstring): "<col>::be0" -> dense uint64 [n]; never part of the schema
+        self.aux: Dict[str, torch.Tensor] = dict(aux) if aux else {}
         n = num_rows
         dev = device
         for name, t in self.columns.items():
@@ -311,10 +320,12 @@ class DeviceBlock:
     def empty(device: Optional[torch.device] = None) -> "DeviceBlock":
         return DeviceBlock({}, num_rows=0, device=device)
 
-    def to_records(self, columns: Optional[Sequence[str]] = None, pitch: Optional[int] = None) -> "DeviceBlock":
+    def to_records(self, columns: Optional[Sequence[str]] = None, pitch: Optional[int] = None,
+                   key_prefix: Optional[Sequence[str]] = None) -> "DeviceBlock":
         """The same block with `columns` (default: all) stored side by side in one record per row (module
         docstring, "Record layout"). Offsets follow the column order, each aligned to its element size; `pitch`
-        defaults to `auto_pitch`. Padding bytes are zero."""
+        defaults to `auto_pitch`. Padding bytes are zero. `key_prefix`: byte-string columns ([n, w] uint8) that get
+        a key prefix column (module docstring)."""
         names = list(self.columns) if columns is None else list(columns)
         if not names or self._n == 0:
             return self
@@ -339,19 +350,53 @@ class DeviceBlock:
                 src_pitch = inner
             ops.copy_rows_2d(t.data_ptr(), src_pitch, rec.data_ptr() + off, pitch, inner, self._n, self.device)
             cols[k] = member_view(rec, off, dt, shape)
-        return DeviceBlock(cols, num_rows=self._n, device=self.device)
+        aux = {}
+        for k in key_prefix or []:
+            aux[f"{k}{BYTE_KEY_SEP}0"] = ops.byte_key_chunks(cols[k])[0] if cols[k].shape[1] > 8 else \
+                ops.pack_key_bytes(cols[k], 0, cols[k].shape[1])
+        return DeviceBlock(cols, num_rows=self._n, device=self.device, aux=aux)
 
     def key_column(self, name: str) -> torch.Tensor:
         """The dense 1-D key column `name`. `<col>::be<i>` names the i-th big-endian 8-byte chunk of the
         byte-string column `col` (planner._expand_byte_keys): computed here when the block does not carry it."""
         if name in self.columns:
             return _contig(self.columns[name])
+        if name in self.aux:
+            return self.aux[name]
         base, sep, idx = name.rpartition(BYTE_KEY_SEP)
         if sep and base in self.columns and idx.isdigit():
             col = self.columns[base]
-            off = 8 * int(idx)
-            return ops.pack_key_bytes(col if _row_pitch(col) is not None else _contig(col), off, min(8, col.shape[1] - off))
+            return ops.byte_key_chunks(col if _row_pitch(col) is not None else _contig(col))[int(idx)]
         raise KeyError(name)
+
+    def key_columns(self, names: Sequence[str]) -> List[torch.Tensor]:
+        """`key_column` for several names at once: the chunks of one byte-string column are packed in a single pass."""
+        out: Dict[str, torch.Tensor] = {}
+        for name in names:
+            if name in out:
+                continue
+            if name in self.aux:
+                out[name] = self.aux[name]
+                continue
+            base, sep, idx = name.rpartition(BYTE_KEY_SEP)
+            if name not in self.columns and sep and base in self.columns and idx.isdigit():
+                col = self.columns[base]
+                chunks = ops.byte_key_chunks(col if _row_pitch(col) is not None else _contig(col))
+                for i, ch in enumerate(chunks):
+                    out[f"{base}{BYTE_KEY_SEP}{i}"] = ch
+            else:
+                out[name] = self.key_column(name)
+        return [out[name] for name in names]
+
+    def key_piece(self, name: str):
+        """A later key column as `fix_ties` takes it: a chunk of a byte-string column is read where it lies
+        (`ops.KeyPiece`), anything else is the dense column."""
+        base, sep, idx = name.rpartition(BYTE_KEY_SEP)
+        if name not in self.columns and name not in self.aux and sep and base in self.columns and idx.isdigit():
+            col = self.columns[base]
+            off = 8 * int(idx)
+            return ops.KeyPiece(col, off, min(8, col.shape[1] - off))
+        return self.key_column(name)
 
     # -- introspection ------------------------------------------------------------------
     @property
@@ -384,10 +429,11 @@ class DeviceBlock:
         start = max(0, min(start, self._n))
         end = max(start, min(end, self._n))
         return DeviceBlock({k: v[start:end] for k, v in self.columns.items()}, num_rows=end - start,
-                           device=self.device)
+                           device=self.device, aux={k: v[start:end] for k, v in self.aux.items()})
 
     def select(self, names: Sequence[str]) -> "DeviceBlock":
-        return DeviceBlock({k: self.columns[k] for k in names}, num_rows=self._n, device=self.device)
+        return DeviceBlock({k: self.columns[k] for k in names}, num_rows=self._n, device=self.device,
+                           aux={k: v for k, v in self.aux.items() if k.rpartition(BYTE_KEY_SEP)[0] in names})
 
     @staticmethod
     def concat(blocks: Sequence["DeviceBlock"]) -> "DeviceBlock":
@@ -405,7 +451,8 @@ class DeviceBlock:
         for name in names:
             parts = [b.columns[name] for b in blocks]
             out[name] = _join_views(parts)
-        return DeviceBlock(out, device=blocks[0].device)
+        aux = {k: _join_views([b.aux[k] for b in blocks]) for k in blocks[0].aux if all(k in b.aux for b in blocks)}
+        return DeviceBlock(out, device=blocks[0].device, aux=aux)
 
     # -- egress (D2H happens only here) -------------------------------------------------
     def to_numpy(self, columns: Optional[Sequence[str]] = None) -> Dict[str, np.ndarray]:
@@ -488,6 +535,22 @@ class BlockAccessor:
 # multi-column sorts try "is the first column alone enough?" from this many rows on, on a sample of this size
 _DISTINCT_FIRST_MIN_ROWS = 1 << 16
 _DISTINCT_SAMPLE = 1 << 14
+
+
+class _TieVerdict:
+    """Outcome of `ops.fix_ties`, read back without stalling the device: the two counters are copied to pinned host
+    memory behind the kernel; `ok()` waits for that copy only."""
+
+    def __init__(self, stats: torch.Tensor):
+        self._host = torch.empty(2, dtype=torch.int64).pin_memory()
+        self._host.copy_(stats, non_blocking=True)
+        self._event = torch.cuda.Event()
+        self._event.record(torch.cuda.current_stream(stats.device))
+        self._keep = stats
+
+    def ok(self) -> bool:
+        self._event.synchronize()
+        return int(self._host[1]) <= ops.FIX_TIES_MAX_RUN
 
 
 class DeviceBlockAccessor(BlockAccessor):
@@ -591,43 +654,69 @@ class DeviceBlockAccessor(BlockAccessor):
 
     # -- sort (arrow_block.py:449-464, :554-567) ------------------------------------------
     def _argsort(self, sort_key: "SortKey", want_codes: bool):
-        """Stable multi-column argsort: chain from the last key column to the first."""
+        """Stable multi-column argsort -> (perm, codes, sorted first key column)."""
+        perm, codes, skeys, verdict = self._argsort_deferred(sort_key, want_codes)
+        if verdict is not None and not verdict.ok():
+            perm, codes, skeys = self._argsort_chain(sort_key, want_codes)
+        return perm, codes, skeys
+
+    def _argsort_chain(self, sort_key: "SortKey", want_codes: bool):
+        """One stable sort per key column, from the last to the first."""
         b = self._block
-        cols = sort_key.get_columns()
-        desc = sort_key.get_descending()
+        cols, desc = sort_key.get_columns(), sort_key.get_descending()
+        perm = codes = skeys = None
+        for i, col in enumerate(reversed(b.key_columns(cols))):
+            lastcall = i == len(cols) - 1
+            perm, codes, skeys = ops.argsort(col, desc, perm_in=perm, want_codes=want_codes and lastcall, want_keys=lastcall)
+        return perm, codes, skeys
+
+    def _argsort_deferred(self, sort_key: "SortKey", want_codes: bool):
+        """(perm, codes, sorted first key column, verdict): `verdict` is None, or a `_TieVerdict` whose `ok()` must be
+        asked before the result is trusted (False -> call `_argsort_chain`). Work that only depends on `perm` can be
+        enqueued first: asking blocks the host until the sort has run, not the device."""
+        b = self._block
+        cols, desc = sort_key.get_columns(), sort_key.get_descending()
         if 1 < len(cols) <= 1 + ops.FIX_TIES_MAX_COLS and b.num_rows >= _DISTINCT_FIRST_MIN_ROWS:
             first = self._argsort_first_column_then_ties(cols, desc, want_codes)
             if first is not None:
                 return first
-        perm = codes = skeys = None
-        for i, name in enumerate(reversed(cols)):
-            lastcall = i == len(cols) - 1
-            perm, codes, skeys = ops.argsort(b.key_column(name), desc, perm_in=perm,
-                                             want_codes=want_codes and lastcall, want_keys=lastcall)
-        return perm, codes, skeys
+        return self._argsort_chain(sort_key, want_codes) + (None,)
 
     def _argsort_first_column_then_ties(self, cols: List[str], desc: bool, want_codes: bool):
         """A multi-column sort whose first column has (almost) no duplicates is the sort by that column alone,
         plus a repair of the few runs of equal first keys (gensort's 10-byte key: 8 random bytes already separate
         nearly all records; timestamp + id; ...). If a sample of the first column shows no duplicate: one sort by
-        it, then `fix_ties` orders every run of equal first keys by the remaining columns in place. A run longer
-        than the repair handles (the column was duplicate-heavy after all) -> None: the caller runs the chain."""
+        it, then `fix_ties` orders every run of equal first keys by the remaining columns in place (byte-string
+        chunks are compared where they lie in the rows). A run longer than the repair handles (the column was
+        duplicate-heavy after all) is reported through the verdict. None = not applicable: run the chain."""
         b = self._block
-        col = b.key_column(cols[0])
-        if col.dim() != 1 or col.element_size() < 4:
-            return None
-        n = b.num_rows
+        n, first = b.num_rows, cols[0]
         m = min(_DISTINCT_SAMPLE, n)
         pos = torch.from_numpy(((np.arange(m, dtype=np.float64) + 0.5) * (n / m)).astype(np.int64).astype(np.int32)).to(b.device)
-        sample = ops.encode_keys(ops.gather(col, pos), False).cpu().numpy()
+        base, sep, idx = first.rpartition(BYTE_KEY_SEP)
+        col = None
+        if first not in b.columns and first not in b.aux and sep and base in b.columns and idx.isdigit() \
+                and (_row_pitch(b.columns[base]) or 1) % RECORD_ALIGN == 0:
+            # the sample is read straight from the records, before the pass that packs the whole column
+            kcol = b.columns[base]
+            off = 8 * int(idx)
+            if kcol.shape[1] - off < 4:
+                return None
+            sample_col = ops.pack_key_bytes(ops.gather_pitched_column(kcol, pos), off, min(8, kcol.shape[1] - off))
+        else:
+            col = b.key_column(first)
+            if col.dim() != 1 or col.element_size() < 4:
+                return None
+            sample_col = ops.gather(col, pos)
+        sample = ops.encode_keys(sample_col, False).cpu().numpy()
         if np.unique(sample).size < m:
             return None
+        if col is None:
+            col = b.key_column(first)
         perm, codes, skeys = ops.argsort(col, desc, want_codes=want_codes or col.dtype.is_floating_point, want_keys=True)
         probe = skeys if skeys is not None else codes.view(torch.uint64)
-        stats = ops.fix_ties(probe, perm, [b.key_column(c) for c in cols[1:]], desc)
-        if int(stats[1].item()) > ops.FIX_TIES_MAX_RUN:
-            return None
-        return perm, (codes if want_codes else None), skeys
+        stats = ops.fix_ties(probe, perm, [b.key_piece(c) for c in cols[1:]], desc)
+        return perm, (codes if want_codes else None), skeys, _TieVerdict(stats)
 
     def sort(self, sort_key: "SortKey", want_codes: bool = False, on_sorted_key=None):
         """Whole block in sorted order (transform_pyarrow.sort: sort_indices + take).
@@ -636,19 +725,27 @@ class DeviceBlockAccessor(BlockAccessor):
         and before the other columns are gathered: work that only needs the keys (cutting the result into
         blocks, including its device -> host read) then overlaps the payload gather."""
         b = self._block
-        perm, codes, skeys = self._argsort(sort_key, want_codes)
+        perm, codes, skeys, verdict = self._argsort_deferred(sort_key, want_codes)
         first_key = sort_key.get_columns()[0]
-        if skeys is None and on_sorted_key is not None:  # float keys are gathered, not decoded by the sort
-            skeys = ops.gather(b.key_column(first_key), perm)
-        if on_sorted_key is not None:
-            on_sorted_key(skeys)
-        # the sorted first key column comes out of the sort itself, unless it travels inside a record anyway
-        decoded = skeys is not None and first_key in b.columns and _row_pitch(b.columns[first_key]) is None
-        names = [k for k in b.column_names if not (decoded and k == first_key)]
-        cols = self._take_columns(perm, names)
+        for attempt in (0, 1):
+            if skeys is None and on_sorted_key is not None:  # float keys are gathered, not decoded by the sort
+                skeys = ops.gather(b.key_column(first_key), perm)
+            if on_sorted_key is not None:
+                on_sorted_key(skeys)
+            # the sorted first key column comes out of the sort itself, unless it travels inside a record anyway
+            decoded = skeys is not None and first_key in b.columns and _row_pitch(b.columns[first_key]) is None
+            names = [k for k in b.column_names if not (decoded and k == first_key)]
+            cols = self._take_columns(perm, names)
+            if verdict is None or verdict.ok():
+                break
+            perm, codes, skeys = self._argsort_chain(sort_key, want_codes)   # rare: long runs of equal first keys
+            verdict = None
         if decoded:
             cols[first_key] = skeys
-        out = DeviceBlock({k: cols[k] for k in b.column_names}, num_rows=b.num_rows, device=b.device)
+        aux = {}
+        if skeys is not None and first_key not in b.columns and first_key.endswith(f"{BYTE_KEY_SEP}0"):
+            aux[first_key] = skeys       # the key prefix column of the sorted block, for free
+        out = DeviceBlock({k: cols[k] for k in b.column_names}, num_rows=b.num_rows, device=b.device, aux=aux)
         return out, codes
 
     def sort_and_partition(self, boundaries: List[Any], sort_key: "SortKey") -> List[DeviceBlock]:

@@ -353,22 +353,23 @@ def _default_parallelism() -> int:
     return max(torch.cuda.device_count(), 1) * 8 if torch.cuda.is_available() else 8
 
 
-def _maybe_records(whole: DeviceBlock, records) -> DeviceBlock:
+def _maybe_records(whole: DeviceBlock, records, key_prefix=None) -> DeviceBlock:
     """`records`: None/False = dense columns; True = all columns in one record per row (pitch chosen by
-    block.auto_pitch); an int = that pitch; a list of column names = those columns only."""
+    block.auto_pitch); an int = that pitch; a list of column names = those columns only. `key_prefix`: byte-string
+    columns of the record that also get a dense key prefix column (block.py module docstring)."""
     if not records:
         return whole
     if isinstance(records, (list, tuple)):
-        return whole.to_records(list(records))
-    return whole.to_records(pitch=None if records is True else int(records))
+        return whole.to_records(list(records), key_prefix=key_prefix)
+    return whole.to_records(pitch=None if records is True else int(records), key_prefix=key_prefix)
 
 
 def from_numpy_columns(cols: Dict[str, np.ndarray], *, override_num_blocks: Optional[int] = None,
-                       device: Optional[torch.device] = None, records=None) -> Dataset:
+                       device: Optional[torch.device] = None, records=None, key_prefix=None) -> Dataset:
     """One H2D copy per column; blocks are views of the resulting HBM buffers. `records`: see `_maybe_records`
     (row-wise record layout for datasets of wide or oddly sized rows, block.py "Record layout")."""
     device = device or default_device()
-    whole = _maybe_records(DeviceBlock.from_numpy(cols, device), records)
+    whole = _maybe_records(DeviceBlock.from_numpy(cols, device), records, key_prefix)
     n = whole.num_rows
     parts = _split_rows(n, override_num_blocks or _default_parallelism())
     return Dataset([whole.slice(lo, hi) for lo, hi in parts])
@@ -427,9 +428,9 @@ def from_pandas(dfs, *, override_num_blocks: Optional[int] = None) -> Dataset:
 
 
 def from_torch_columns(cols: Dict[str, torch.Tensor], *, override_num_blocks: Optional[int] = None,
-                       records=None) -> Dataset:
+                       records=None, key_prefix=None) -> Dataset:
     """Adopt CUDA tensors that are already resident in HBM (no copy, unless `records` asks for the row-wise
     record layout: see `_maybe_records`)."""
-    whole = _maybe_records(DeviceBlock(cols), records)
+    whole = _maybe_records(DeviceBlock(cols), records, key_prefix)
     parts = _split_rows(whole.num_rows, override_num_blocks or 1)
     return Dataset([whole.slice(lo, hi) for lo, hi in parts])

@@ -30,7 +30,7 @@ import torch
 import torch.distributed as dist
 
 from . import ops
-from .block import DeviceBlock, DeviceBlockAccessor, _contig, record_groups
+from .block import BYTE_KEY_SEP, DeviceBlock, DeviceBlockAccessor, _contig, record_groups
 from .sort_task_spec import SortKey
 
 
@@ -281,12 +281,12 @@ def _gather_samples(sample_codes: torch.Tensor, samples_per_rank: int, world: in
 
 
 def _exchange_units(local: DeviceBlock, key_cols: Sequence[str]):
-    """What travels in a sort exchange, in sending order: the key columns (dense; `<col>::be<i>` chunk names are
-    materialised here), then every record group as ONE column of whole records, then the remaining columns.
-    Returns (units: name -> dense tensor, groups, names of the non-key units)."""
+    """What travels in a sort exchange, in sending order: the key columns `key_cols` (dense; a `<col>::be<i>` chunk
+    name is the block's key prefix column or is packed here), then every record group as ONE column of whole
+    records, then the remaining columns. Returns (units: name -> dense tensor, groups, names of the non-key units)."""
     groups, _ = record_groups(local)
     in_group = {k for g in groups for k in g.members}
-    units: Dict[str, torch.Tensor] = {k: local.key_column(k) for k in key_cols}
+    units: Dict[str, torch.Tensor] = dict(zip(key_cols, local.key_columns(key_cols)))
     rest = []
     for i, g in enumerate(groups):
         units[f"\x00rec{i}"] = g.rec
@@ -298,6 +298,17 @@ def _exchange_units(local: DeviceBlock, key_cols: Sequence[str]):
     return units, groups, rest
 
 
+def _received_block(local: DeviceBlock, groups, recv: Dict[str, torch.Tensor], n_recv: int, dev) -> DeviceBlock:
+    """The received rows (arrival order) as a block of the sender's columns: views of the receive buffers."""
+    cols: Dict[str, torch.Tensor] = {}
+    for i, g in enumerate(groups):
+        cols.update(g.views(recv[f"\x00rec{i}"]))
+    for c in local.column_names:
+        if c not in cols and c in recv:
+            cols[c] = recv[c]
+    return DeviceBlock({c: cols[c] for c in local.column_names if c in cols}, num_rows=n_recv, device=dev)
+
+
 def _assemble_sorted(local: DeviceBlock, groups, recv: Dict[str, torch.Tensor], perm2: torch.Tensor, first: str, skeys2,
                      n_recv: int, dev) -> DeviceBlock:
     """The received rows in sorted order: records are gathered whole and re-cut into their member columns."""
@@ -305,12 +316,14 @@ def _assemble_sorted(local: DeviceBlock, groups, recv: Dict[str, torch.Tensor], 
     out_cols: Dict[str, torch.Tensor] = {}
     for i, g in enumerate(groups):
         out_cols.update(g.views(ops.gather_records(recv[f"\x00rec{i}"], perm2)))
-    names = [c for c in local.column_names if c not in in_group and not (skeys2 is not None and c == first)]
+    decoded = skeys2 is not None and first in local.columns and first not in in_group
+    names = [c for c in local.column_names if c not in in_group and not (decoded and c == first)]
     outs = ops.gather_columns([recv[c] for c in names], perm2)
     out_cols.update(zip(names, outs))
-    if skeys2 is not None and first in local.columns and first not in in_group:
+    if decoded:
         out_cols[first] = skeys2
-    return DeviceBlock({c: out_cols[c] for c in local.column_names}, num_rows=n_recv, device=dev)
+    aux = {first: skeys2} if (skeys2 is not None and first not in local.columns and first.endswith(f"{BYTE_KEY_SEP}0")) else {}
+    return DeviceBlock({c: out_cols[c] for c in local.column_names}, num_rows=n_recv, device=dev, aux=aux)
 
 
 def _p2p_partition_sort(local: DeviceBlock, sort_key: SortKey, n: int, dev, group, samples_per_rank: int) -> DeviceBlock:
@@ -318,11 +331,18 @@ def _p2p_partition_sort(local: DeviceBlock, sort_key: SortKey, n: int, dev, grou
       sample raw keys -> identical splitters on every rank -> per-row (owner, slot) targets (stable split,
       no sort) -> key columns stored into the owners' receive buffers -> while the payload columns follow
       over NVLink, the received keys are sorted on a second stream -> one gather of the received payload.
-    The payload is read once sequentially on the sender and gathered once on the receiver."""
+    The payload is read once sequentially on the sender and gathered once on the receiver.
+
+    Later key columns that are chunks of a byte-string key held inside the records (gensort: `key::be1`) do not
+    travel as columns of their own: the first column alone is exchanged and sorted early, and once the records
+    have landed the few runs of equal first keys are put in order from the key bytes in the records (`fix_ties`)."""
     world = dist.get_world_size(group)
     key_cols = sort_key.get_columns()
     first, desc = key_cols[0], sort_key.get_descending()
-    units, groups, rest = _exchange_units(local, key_cols)
+    late = 1 < len(key_cols) <= 1 + ops.FIX_TIES_MAX_COLS and all(
+        c not in local.columns and c not in local.aux and BYTE_KEY_SEP in c for c in key_cols[1:])
+    early = [first] if late else list(key_cols)
+    units, groups, rest = _exchange_units(local, early)
     keycol = units[first]
     if n > 0:
         m = min(samples_per_rank, n)
@@ -340,13 +360,13 @@ def _p2p_partition_sort(local: DeviceBlock, sort_key: SortKey, n: int, dev, grou
     ex = P2PExchange(cols, n, send_counts, dev, group, target=target)
     main = torch.cuda.current_stream(dev)
     ex.fence()
-    ex.send(key_cols)
+    ex.send(early)
     ex.fence()
     if ex.n_recv == 0:
         ex.send(rest)
         ex.fence()
         return local.slice(0, 0)
-    keys_block = DeviceBlock(ex.view(key_cols), num_rows=ex.n_recv, device=dev)
+    keys_block = DeviceBlock(ex.view(early), num_rows=ex.n_recv, device=dev)
     side = _side_stream(dev)
     landed, sorted_ev = torch.cuda.Event(), torch.cuda.Event()
     landed.record(main)
@@ -364,13 +384,28 @@ def _p2p_partition_sort(local: DeviceBlock, sort_key: SortKey, n: int, dev, grou
     ex.fence()
     with torch.cuda.stream(side):
         side.wait_event(landed)
-        perm2, _, skeys2 = DeviceBlockAccessor(keys_block)._argsort(sort_key, False)
+        if late:
+            perm2, _, skeys2 = ops.argsort(keys_block.columns[first], desc, want_keys=True)
+        else:
+            perm2, _, skeys2 = DeviceBlockAccessor(keys_block)._argsort(sort_key, False)
         sorted_ev.record(side)
     main.wait_event(sorted_ev)
     perm2.record_stream(main)
     if skeys2 is not None:
         skeys2.record_stream(main)
-    return _assemble_sorted(local, groups, ex.view(list(cols)), perm2, first, skeys2, ex.n_recv, dev)
+    recv = ex.view(list(cols))
+    verdict = None
+    if late:
+        from .block import _TieVerdict
+
+        received = _received_block(local, groups, recv, ex.n_recv, dev)
+        verdict = _TieVerdict(ops.fix_ties(skeys2, perm2, [received.key_piece(c) for c in key_cols[1:]], desc))
+    out = _assemble_sorted(local, groups, recv, perm2, first, skeys2, ex.n_recv, dev)
+    if verdict is not None and not verdict.ok():     # long runs of equal first keys: sort the received rows by all columns
+        received.aux[first] = keys_block.columns[first]
+        perm2, _, skeys2 = DeviceBlockAccessor(received)._argsort_chain(sort_key, False)
+        out = _assemble_sorted(local, groups, recv, perm2, first, skeys2, ex.n_recv, dev)
+    return out
 
 
 def _p2p_sort_exchange(local: DeviceBlock, sort_key: SortKey, perm, skeys, n: int, send_counts, dev, group) -> DeviceBlock:

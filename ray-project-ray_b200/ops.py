@@ -130,6 +130,24 @@ def gather_records(rec: torch.Tensor, idx: torch.Tensor, row_bytes: Optional[int
     return out
 
 
+def gather_pitched_column(col: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+    """Rows `idx` of a [n, w] uint8 column whose rows lie at a pitch that is a multiple of 16 (a record member), as a
+    [m, w] view of a small record buffer: only the 16-byte vectors that cover the column are read."""
+    n, w = col.shape
+    pitch = col.stride(0) if n > 1 else (w + 15) // 16 * 16
+    a = col.data_ptr() % 16
+    nb = (a + w + 15) // 16 * 16
+    if pitch % 16 or nb > pitch:
+        raise ValueError("not a record member column")
+    m = idx.numel()
+    out = torch.empty((m, nb), dtype=torch.uint8, device=col.device)
+    if m:
+        with torch.cuda.device(col.device):
+            _lib.call("b200x_gather_rows_pitched", col.data_ptr() - a, pitch, idx.data_ptr(), m, out.data_ptr(), nb, nb,
+                      _stream(col.device))
+    return out[:, a:a + w]
+
+
 def permute_records(rec: torch.Tensor, seed: int, inverse: bool = False, row_bytes: Optional[int] = None) -> torch.Tensor:
     """out[j, :row_bytes] = rec[pi_seed(j), :row_bytes] for a record buffer ([n, pitch] uint8)."""
     dev = _require_cuda(rec)
@@ -152,17 +170,40 @@ def copy_rows_2d(src_ptr: int, src_pitch: int, dst_ptr: int, dst_pitch: int, row
             _lib.call("b200x_copy_rows_2d", src_ptr, src_pitch, dst_ptr, dst_pitch, row_bytes, n, _stream(dev))
 
 
-def fix_ties(keys_sorted: torch.Tensor, perm: torch.Tensor, cols: Sequence[torch.Tensor], descending: bool) -> torch.Tensor:
+class KeyPiece:
+    """`width` big-endian bytes at byte `offset` of every row of a [n, w] uint8 column (rows dense or at a pitch): one
+    piece of a byte-string key, compared where it lies instead of being packed into a column of its own."""
+
+    __slots__ = ("col", "offset", "width")
+
+    def __init__(self, col: torch.Tensor, offset: int, width: int):
+        if col.dim() != 2 or col.dtype != torch.uint8 or not (1 <= width <= 8) or offset + width > col.shape[1]:
+            raise ValueError("a key piece is 1..8 bytes inside a [n, w] uint8 column")
+        self.col, self.offset, self.width = col, offset, width
+
+
+def fix_ties(keys_sorted: torch.Tensor, perm: torch.Tensor, cols: Sequence, descending: bool) -> torch.Tensor:
     """Order every run of equal keys in `keys_sorted` (the first key column after a stable sort by it alone; int64
-    codes count as uint64) by the remaining key columns `cols`, in place in `perm`. Returns int64[2] on the device:
-    rows inside tie runs, longest run (runs above 64 rows are left untouched)."""
-    dev = _require_cuda(keys_sorted, perm, *cols)
+    codes count as uint64) by the remaining key columns `cols` (1-D tensors, dense or strided, or `KeyPiece`s), in
+    place in `perm`. Returns int64[2] on the device: rows inside tie runs, longest run (runs above 64 rows are left
+    untouched)."""
+    dev = _require_cuda(keys_sorted, perm)
+    k = len(cols)
+    ptrs, types, strides, be = (ctypes.c_void_p * k)(), (ctypes.c_int * k)(), (ctypes.c_ulonglong * k)(), (ctypes.c_int * k)()
+    for i, c in enumerate(cols):
+        if isinstance(c, KeyPiece):
+            t = c.col
+            ptrs[i], types[i], be[i] = t.data_ptr() + c.offset, KEY_U8, c.width
+            strides[i] = t.stride(0) if t.shape[0] > 1 else t.shape[1]
+        else:
+            if c.dim() != 1 or not c.is_cuda:
+                raise ValueError("key columns are 1-D CUDA tensors")
+            ptrs[i], types[i], be[i] = c.data_ptr(), key_type_of(c), 0
+            strides[i] = (c.stride(0) if c.shape[0] > 1 else 1) * c.element_size()
     stats = torch.empty(2, dtype=torch.int64, device=dev)
-    ptrs = (ctypes.c_void_p * len(cols))(*[c.data_ptr() for c in cols])
-    types = (ctypes.c_int * len(cols))(*[key_type_of(c) for c in cols])
     with torch.cuda.device(dev):
         _lib.call("b200x_fix_ties", keys_sorted.data_ptr(), key_type_of(keys_sorted), keys_sorted.numel(), perm.data_ptr(),
-                  ptrs, types, len(cols), int(descending), stats.data_ptr(), _stream(dev))
+                  ptrs, types, strides, be, k, int(descending), stats.data_ptr(), _stream(dev))
     return stats
 
 
@@ -241,8 +282,18 @@ def pack_key_bytes(col: torch.Tensor, offset: int, width: int) -> torch.Tensor:
 
 
 def byte_key_chunks(col: torch.Tensor) -> List[torch.Tensor]:
-    """A [n, w] uint8 key column as ceil(w / 8) unsigned integer columns, most significant first."""
-    w = col.shape[1]
+    """A [n, w] uint8 key column as ceil(w / 8) unsigned integer columns, most significant first. Columns whose rows
+    lie at a multiple of 16 bytes (record members) are packed in one pass with 16-byte loads."""
+    n, w = col.shape
+    pitch = col.stride(0) if n > 1 else w
+    if col.is_cuda and n > 0 and pitch % 16 == 0 and w <= 32 and (n == 1 or col.stride(1) == 1):
+        widths = [min(8, w - off) for off in range(0, w, 8)]
+        outs = [torch.empty(n, dtype=_chunk_dtype(cw), device=col.device) for cw in widths]
+        ptrs = (ctypes.c_void_p * len(outs))(*[o.data_ptr() for o in outs])
+        nbytes = (ctypes.c_int * len(outs))(*[o.element_size() for o in outs])
+        with torch.cuda.device(col.device):
+            _lib.call("b200x_pack_key_chunks", col.data_ptr(), pitch, w, n, ptrs, nbytes, _stream(col.device))
+        return outs
     return [pack_key_bytes(col, off, min(8, w - off)) for off in range(0, w, 8)]
 
 

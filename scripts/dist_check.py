@@ -73,6 +73,29 @@ def main():
         np.testing.assert_array_equal(np.concatenate([p[1] for p in parts]), alo[order])
         np.testing.assert_array_equal(np.concatenate([p[2] for p in parts]), ap[order])
         print("gensort-shaped 2-column key sort: OK", flush=True)
+    # gensort records in the record layout (the bench workload): [n, 10] byte key + [n, 90] payload, 128-byte records,
+    # with and without the key prefix column; ties on the first 8 bytes and exact duplicates inside and across ranks
+    shared = np.random.default_rng(5).integers(0, 256, (500, 10)).astype(np.uint8)      # the same keys on every rank
+    for m, prefix in ((300_000 + 777 * rank, ["key"]), (300_000 + 777 * rank, None), (90_000, ["key"])):
+        bkey = rng.integers(0, 256, (m, 10)).astype(np.uint8)
+        dst, src = rng.integers(0, m, m // 50), rng.integers(0, m, m // 50)
+        bkey[dst, :8] = bkey[src, :8]
+        bkey[rng.integers(0, m, 3000)] = shared[rng.integers(0, 500, 3000)]
+        if m == 90_000:
+            bkey[:, :8] = bkey[rng.integers(0, 40, m), :8]      # duplicate-heavy first 8 bytes: the tie repair gives up
+        bpay = rng.integers(0, 256, (m, 90), dtype=np.uint8)
+        bpay[:, :8] = (np.arange(m, dtype=np.int64) + rank * 10_000_000).view(np.uint8).reshape(m, 8)
+        dsr = rd.from_numpy_columns({"key": bkey, "payload": bpay}, override_num_blocks=3, records=True, key_prefix=prefix)
+        for desc in (False, True):
+            got = dsr.sort("key", descending=desc).to_numpy()
+            parts = gather_np((got["key"], got["payload"]), world, rank)
+            ins = gather_np((bkey, bpay), world, rank)
+            if rank == 0:
+                ak, ap = (np.concatenate([p[i] for p in ins]) for i in range(2))
+                order = orc.stable_argsort_bytes(ak, desc)
+                np.testing.assert_array_equal(np.concatenate([p[0] for p in parts]), ak[order])
+                np.testing.assert_array_equal(np.concatenate([p[1] for p in parts]), ap[order])
+                print(f"gensort records rows={m} prefix={bool(prefix)} desc={desc}: OK, rows per rank {[len(p[0]) for p in parts]}", flush=True)
     # groupby
     gk = rng.integers(0, 3000, n, dtype=np.int64)
     gv = rng.integers(-2**31, 2**31, n, dtype=np.int64)

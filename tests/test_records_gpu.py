@@ -194,3 +194,58 @@ def test_fix_ties_against_lexsort(desc, cuda_device):
     perm3, _, _ = BlockAccessor.for_block(blk)._argsort(SortKey(["a", "b", "c"], descending=[desc] * 3), False)
     want3 = np.lexsort([sgn * c.astype(np.int64), sgn * b.view(np.int16).astype(np.int64), sgn * a2])
     np.testing.assert_array_equal(perm3.cpu().numpy().view(np.uint32), want3.astype(np.uint32))
+
+
+@pytest.mark.parametrize("width,offset,pitch", [(10, 0, 128), (10, 3, 48), (3, 13, 16), (17, 15, 64), (32, 9, 48), (8, 8, 16)])
+def test_pack_key_chunks_any_alignment(width, offset, pitch, cuda_device):
+    """b200x_pack_key_chunks (all chunks of a key held inside a record, one pass) == b200x_pack_key_bytes per chunk
+    == numpy's big-endian view."""
+    rng = np.random.default_rng(width * 100 + offset)
+    n = 10_007
+    rec = rng.integers(0, 256, (n, pitch)).astype(np.uint8)
+    d = torch.from_numpy(rec).to(cuda_device)
+    col = d[:, offset:offset + width]
+    fused = ops.byte_key_chunks(col)
+    assert len(fused) == (width + 7) // 8
+    for i, ch in enumerate(fused):
+        cw = min(8, width - 8 * i)
+        single = ops.pack_key_bytes(col, 8 * i, cw)
+        assert ch.dtype == single.dtype
+        got = ch.view({2: torch.int16, 4: torch.int32, 8: torch.int64}[ch.element_size()]).cpu().numpy()
+        np.testing.assert_array_equal(got, single.view(got.dtype if False else {2: torch.int16, 4: torch.int32, 8: torch.int64}[ch.element_size()]).cpu().numpy())
+        padded = np.zeros((n, ch.element_size()), dtype=np.uint8)
+        padded[:, :cw] = rec[:, offset + 8 * i: offset + 8 * i + cw]
+        want = padded.view({2: ">u2", 4: ">u4", 8: ">u8"}[ch.element_size()]).ravel()
+        np.testing.assert_array_equal(got.view({2: np.uint16, 4: np.uint32, 8: np.uint64}[ch.element_size()]), want.astype(want.dtype.newbyteorder("=")))
+
+
+def test_key_prefix_column(cuda_device):
+    """The key prefix column (block.py): built by to_records, used by the sort instead of a pass over the records,
+    comes out of the sort, survives slice / concat, never shows in the schema; results do not depend on it."""
+    key, payload = _gensort(120_000, 31, 1500, 300)
+    plain = rd.from_numpy_columns({"key": key, "payload": payload}, override_num_blocks=3, records=True)
+    withp = rd.from_numpy_columns({"key": key, "payload": payload}, override_num_blocks=3, records=True, key_prefix=["key"])
+    b0 = withp.get_internal_block_refs()[0]
+    assert list(b0.aux) == ["key::be0"] and b0.aux["key::be0"].dtype == torch.uint64
+    assert b0.column_names == ["key", "payload"] and withp.schema() == plain.schema()
+    want_hi = key[:b0.num_rows, :8].copy().view(">u8").astype(np.uint64).ravel()
+    np.testing.assert_array_equal(b0.aux["key::be0"].view(torch.int64).cpu().numpy().view(np.uint64), want_hi)
+    joined = DeviceBlock.concat(withp.get_internal_block_refs())
+    assert joined.aux["key::be0"].numel() == 120_000 and joined.slice(5, 50).aux["key::be0"].numel() == 45
+    for desc in (False, True):
+        a = plain.sort("key", descending=desc)
+        b = withp.sort("key", descending=desc)
+        want = orc.stable_argsort_bytes(key, desc)
+        for out in (a, b):
+            got = out.to_numpy()
+            np.testing.assert_array_equal(got["key"], key[want])
+            np.testing.assert_array_equal(got["payload"], payload[want])
+            for blk in out.get_internal_block_refs():       # the sorted blocks carry the prefix of THEIR keys
+                if blk.num_rows:
+                    hi = blk.to_numpy()["key"][:, :8].copy().view(">u8").astype(np.uint64).ravel()
+                    np.testing.assert_array_equal(blk.aux["key::be0"].view(torch.int64).cpu().numpy().view(np.uint64), hi)
+        again = b.sort("key", descending=not desc).to_numpy()    # sorting a sorted dataset uses the column it carries
+        np.testing.assert_array_equal(again["payload"], payload[orc.stable_argsort_bytes(key, not desc)])
+    sh = withp.random_shuffle(seed=4)
+    assert not sh.get_internal_block_refs()[0].aux                # not maintained by shuffle: packed again on demand
+    np.testing.assert_array_equal(sh.sort("key").to_numpy()["payload"], payload[orc.stable_argsort_bytes(key, False)])
