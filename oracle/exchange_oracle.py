@@ -466,3 +466,16 @@ def quantile_dataset(blocks: Sequence[Table], key: Optional[str], on: str, q: fl
     starts, lens = _group_runs(ks)
     out = [percentile(vs[s:s + ln].tolist(), q) for s, ln in zip(starts, lens)]
     return {key: ks[starts], f"quantile({on})": np.array(out, dtype=object)}
+
+
+def key_boundaries(key_columns: Sequence[np.ndarray]) -> List[int]:
+    """End position of every group of a block already sorted by `key_columns`: GroupedData.map_groups'
+    get_key_boundaries (grouped_data.py:181-200: searchsorted(..., side="right") over the key, for several key
+    columns over `_MultiColumnSortedKey` tuples, :13-33) - a group ends where any key column changes."""
+    n = int(key_columns[0].shape[0])
+    if n == 0:
+        return []
+    change = np.zeros(n - 1, dtype=bool)
+    for col in key_columns:
+        change |= col[1:] != col[:-1]
+    return (np.flatnonzero(change) + 1).tolist() + [n]

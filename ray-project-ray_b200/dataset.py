@@ -305,24 +305,39 @@ class GroupedData:
     def std(self, on=None, ddof: int = 1, ignore_nulls: bool = True) -> Dataset:
         return self._aggregate_on(Std, on, ignore_nulls, ddof=ddof)
 
-    def map_groups(self, fn: Callable, *, batch_format: str = "numpy", **_ignored) -> Dataset:
-        """sort(key) on the device, group boundaries from the sorted key column, `fn` per group
-        on the host (grouped_data.py:105-236)."""
+    def map_groups(self, fn: Callable, *, compute=None, batch_format: Optional[str] = "default", fn_args=None,
+                   fn_kwargs=None, **_ray_remote_args) -> Dataset:
+        """Apply `fn` to every group (grouped_data.py:105-236): sort by the key on the device (equal keys end up in
+        one block), find each block's group boundaries on the device - a group starts where ANY key column changes,
+        the reference's `get_key_boundaries` over `_MultiColumnSortedKey` tuples (:181-200) - then call `fn` per
+        group on the host and build ONE output block per sorted block from the results, in group order."""
+        from . import ops
+
+        fn_args, fn_kwargs = tuple(fn_args or ()), dict(fn_kwargs or {})
         if self._key is None:
             sorted_ds = self._dataset.repartition(1)
+            keys: List[str] = []
         else:
             sorted_ds = self._dataset.sort(self._key)
+            keys = [self._key] if isinstance(self._key, str) else list(self._key)
         out = []
         for b in sorted_ds._blocks:
             if b.num_rows == 0:
                 continue
             host = b.to_numpy()
-            if self._key is None:
+            if not keys:
                 bounds = [0, b.num_rows]
-            else:
-                k = host[self._key if isinstance(self._key, str) else self._key[0]]
-                heads = np.flatnonzero(np.concatenate(([True], k[1:] != k[:-1])))
-                bounds = list(heads) + [b.num_rows]
+            elif len(keys) <= 4 and all(b.columns[k].dim() == 1 for k in keys):
+                codes = [ops.encode_keys(b.key_column(k), False) for k in keys]
+                starts, ng = ops.group_boundaries_multi(codes)
+                bounds = starts[: int(ng.item())].cpu().numpy().astype(np.int64).tolist() + [b.num_rows]
+            else:   # wide keys: the same rule on the host copy that `fn` needs anyway
+                change = np.zeros(b.num_rows - 1, dtype=bool)
+                for k in keys:
+                    d = host[k][1:] != host[k][:-1]
+                    change |= d.reshape(len(d), -1).any(axis=1)
+                bounds = [0] + (np.flatnonzero(change) + 1).tolist() + [b.num_rows]
+            results = []
             for lo, hi in zip(bounds[:-1], bounds[1:]):
                 grp = {c: v[lo:hi] for c, v in host.items()}
                 if batch_format == "pandas":
@@ -333,7 +348,8 @@ class GroupedData:
                     import pyarrow as pa
 
                     grp = pa.table(grp)
-                out.append(BlockAccessor.for_block(fn(grp)).to_block())
+                results.append(BlockAccessor.for_block(fn(grp, *fn_args, **fn_kwargs)).to_block())
+            out.append(DeviceBlock.concat(results))
         return Dataset(out, sorted_ds._stats)
 
 

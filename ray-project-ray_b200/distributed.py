@@ -79,10 +79,10 @@ def all_gather_counts(send_counts: Sequence[int], group=None, device=None) -> np
 def exchange_rows(send: torch.Tensor, send_counts: Sequence[int], recv_counts: Sequence[int], group=None) -> torch.Tensor:
     """all-to-all-v of rows (dim 0) of a contiguous [n, ...] tensor; result is ordered by source rank."""
     n_recv = int(sum(recv_counts))
-    flat = send.reshape(send.shape[0], -1) if send.dim() > 1 else send.reshape(-1, 1)
-    as_bytes = flat.view(torch.uint8) if flat.dtype != torch.uint8 else flat
-    row_bytes = as_bytes.shape[1] if as_bytes.dim() == 2 else 1
-    as_bytes = as_bytes.reshape(send.shape[0], row_bytes)
+    row_bytes = send.element_size()
+    for d in send.shape[1:]:
+        row_bytes *= int(d)
+    as_bytes = send.reshape(-1).view(torch.uint8).reshape(send.shape[0], row_bytes)   # zero rows included
     out = torch.empty((n_recv, row_bytes), dtype=torch.uint8, device=send.device)
     dist.all_to_all_single(out, as_bytes, output_split_sizes=[int(c) for c in recv_counts],
                            input_split_sizes=[int(c) for c in send_counts], group=group)
@@ -450,6 +450,33 @@ def _p2p_sort_exchange(local: DeviceBlock, sort_key: SortKey, perm, skeys, n: in
     return DeviceBlock({c: out_cols[c] for c in local.column_names}, num_rows=ex.n_recv, device=dev)
 
 
+def adopt_schema(local: DeviceBlock, dev: torch.device, group=None) -> Optional[DeviceBlock]:
+    """A rank whose shard has no rows and no columns (every block empty, e.g. after a filter) still has to take part
+    in the collectives of an exchange: it adopts the column names, dtypes and row shapes of the lowest rank that has
+    columns and goes on with zero rows. Collective; returns None when no rank has any column."""
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    flag = torch.tensor([1 if local.columns else 0], dtype=torch.int64, device=dev)
+    flags = [torch.empty_like(flag) for _ in range(world)]
+    dist.all_gather(flags, flag, group=group)
+    have = [int(f.item()) for f in flags]
+    if all(have):
+        return local
+    if not any(have):
+        return None
+    src = have.index(1)
+    box = [[(k, str(v.dtype).replace("torch.", ""), tuple(v.shape[1:])) for k, v in local.columns.items()] if rank == src else None]
+    dist.broadcast_object_list(box, src=dist.get_global_rank(group, src) if group is not None else src, group=group)
+    if local.columns:
+        return local
+    return DeviceBlock({k: torch.empty((0,) + tuple(shape), dtype=getattr(torch, dt), device=dev) for k, dt, shape in box[0]},
+                       num_rows=0, device=dev)
+
+
+def _partial_like(partial: Optional[DeviceBlock], dev: torch.device, group=None) -> Optional[DeviceBlock]:
+    """The partial-aggregate block of a rank without rows: zero rows in the schema the other ranks' partials have."""
+    return adopt_schema(partial if partial is not None else DeviceBlock.empty(dev), dev, group)
+
+
 def dist_random_shuffle(local: DeviceBlock, seed: Optional[int], group=None) -> DeviceBlock:
     """ShuffleTaskSpec.map / reduce with one mapper and one reducer per rank."""
     from .shuffle_task_spec import ShuffleTaskSpec
@@ -474,17 +501,21 @@ def dist_aggregate(local: DeviceBlock, key: Optional[str], aggs, group=None, sam
     local = SortAggregateTaskSpec._prune_unused_columns(local, key, aggs)
     n = local.num_rows
     if key is None:
-        partial = aggregate_sorted(local, None, aggs, None, None, finalize=False, n=n) if n else DeviceBlock.empty(dev)
+        partial = aggregate_sorted(local, None, aggs, None, None, finalize=False, n=n) if n else None
+        partial = _partial_like(partial, dev, group)      # ranks without rows send nothing
+        if partial is None:
+            return DeviceBlock.empty(dev)
         # every rank sends its single partial row to rank 0
         counts = [partial.num_rows] + [0] * (world - 1)
-        if not partial.columns:
-            raise ValueError("global aggregation needs at least one row per rank")
         received = exchange_block(partial, counts, group)
         return merge_combined_blocks([received], None, aggs, finalize=True) if rank == 0 else DeviceBlock.empty(dev)
-    if n == 0:
-        raise ValueError("distributed groupby needs at least one row per rank")
-    perm, codes, _ = ops.argsort(_contig(local.columns[key]), False, want_codes=True)
-    partial = aggregate_sorted(local, key, aggs, perm, codes, finalize=False, n=n)  # ascending by key
+    partial = None
+    if n > 0:
+        perm, codes, _ = ops.argsort(_contig(local.columns[key]), False, want_codes=True)
+        partial = aggregate_sorted(local, key, aggs, perm, codes, finalize=False, n=n)  # ascending by key
+    partial = _partial_like(partial, dev, group)
+    if partial is None:
+        return DeviceBlock.empty(dev)
     pcodes = ops.encode_keys(_contig(partial.columns[key]), False)
     samples = _sample_codes(pcodes, samples_per_rank)
     padded = torch.full((samples_per_rank + 1,), -1, dtype=torch.int64, device=dev)
@@ -497,6 +528,10 @@ def dist_aggregate(local: DeviceBlock, key: Optional[str], aggs, group=None, sam
     splitters = choose_splitters(all_codes, world)
     sp = torch.from_numpy(splitters.view(np.int64)).to(dev)
     cuts = ops.search_sorted_codes(pcodes, sp, upper=False).cpu().tolist() if splitters.size else []
+    if partial.num_rows == 0:
+        cuts = [0] * (world - 1)
     send_counts = split_counts_from_cuts(cuts, partial.num_rows)
     received = exchange_block(partial, send_counts, group)
+    if received.num_rows == 0:
+        return received
     return merge_combined_blocks([received], key, aggs, finalize=True)

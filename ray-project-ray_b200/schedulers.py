@@ -25,7 +25,7 @@ from . import ops
 from .aggregate import aggregate_sorted
 from .aggregate_task_spec import SortAggregateTaskSpec
 from .block import (Block, BlockAccessor, BlockExecStats, BlockMetadata, DeviceBlock, DeviceBlockAccessor,
-                    _as_device_block, _contig, find_partition_indices)
+                    _as_device_block, _contig, default_device, find_partition_indices)
 from .interfaces import ExchangeTaskScheduler, ExchangeTaskSpec, RefBundle, StatsDict, TaskContext
 from .shuffle_task_spec import ShuffleTaskSpec
 from .sort_task_spec import SortKey, SortTaskSpec
@@ -394,8 +394,10 @@ def _distributed_exchange(spec: ExchangeTaskSpec, blocks: List[DeviceBlock], out
 
     parts = max(len(blocks), 1)
     local = DeviceBlock.concat(blocks)
-    if not local.columns:
-        raise ValueError("every rank needs at least one block with a schema in a distributed exchange")
+    dev = local.device if local.device is not None else default_device()
+    local = D.adopt_schema(local, dev)   # a rank whose blocks are all empty takes part with zero rows
+    if local is None:
+        return [DeviceBlock.empty(dev) for _ in range(parts)]
     if type(spec) is SortTaskSpec:
         _, sort_key = spec._map_args
         if sort_key.boundaries:

@@ -514,6 +514,45 @@ def run_batcher(shim=None):
     print("wrote batcher_outputs.json", os.path.getsize(os.path.join(OUT, "batcher_outputs.json")) // 1024, "KiB")
 
 
+def run_map_groups(shim=None):
+    """GroupedData.map_groups' group-boundary finder (grouped_data.py:181-200) -> map_groups_outputs.json.
+    `grouped_data.py` cannot be imported under the stub (it pulls in ray.data.dataset), so the class
+    `_MultiColumnSortedKey` (:13-33) and the nested function `get_key_boundaries` are cut out of the reference's
+    own source text with `ast` and executed as they stand, on the reference's real ArrowBlockAccessor."""
+    import ast
+    import textwrap
+
+    install_shim() if shim is None else shim
+    from ray.data.block import BlockAccessor
+
+    path = os.path.join(REF, "data", "grouped_data.py")
+    src = open(path).read()
+    tree = ast.parse(src)
+    cls = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "_MultiColumnSortedKey")
+    inner = next(n for n in ast.walk(tree) if isinstance(n, ast.FunctionDef) and n.name == "get_key_boundaries")
+    lines = src.splitlines()
+    cases = []
+    rng = np.random.default_rng(2024)
+    for n, keys in ((240, "a"), (240, ["a", "b"]), (300, ["a", "b", "c"]), (1, ["a", "b"]), (60, ["b", "a"])):
+        a = rng.integers(-3, 4, n).astype(np.int64)
+        b = rng.integers(0, 3, n).astype(np.int64)
+        c = np.round(rng.standard_normal(n), 0)
+        row = np.arange(n, dtype=np.int64)
+        t = pa.table({"a": a, "b": b, "c": c, "row": row})
+        klist = [keys] if isinstance(keys, str) else keys
+        t = t.take(pa.compute.sort_indices(t, sort_keys=[(k, "ascending") for k in klist]))
+        ns = {"List": list, "BlockAccessor": BlockAccessor}
+        exec("\n".join(lines[cls.lineno - 1:cls.end_lineno]), ns)
+        fake_self = types.SimpleNamespace(_key=keys)
+        ns["self"] = fake_self
+        exec(textwrap.dedent("\n".join(lines[inner.lineno - 1:inner.end_lineno])), ns)
+        bounds = [int(x) for x in ns["get_key_boundaries"](BlockAccessor.for_block(t))]
+        cases.append({"keys": keys, "columns": {k: t[k].to_pylist() for k in t.column_names}, "boundaries": bounds})
+    with open(os.path.join(OUT, "map_groups_outputs.json"), "w") as fjson:
+        json.dump({"cases": cases}, fjson)
+    print("wrote map_groups_outputs.json", os.path.getsize(os.path.join(OUT, "map_groups_outputs.json")) // 1024, "KiB")
+
+
 if __name__ == "__main__":
     if not os.path.isdir(REF):
         sys.exit("needs /root/reference (build container only)")
@@ -521,7 +560,10 @@ if __name__ == "__main__":
         run_quantile()
     elif sys.argv[1:] == ["batcher"]:
         run_batcher()
+    elif sys.argv[1:] == ["map_groups"]:
+        run_map_groups()
     else:
         run_all()
         run_quantile()
         run_batcher()
+        run_map_groups()

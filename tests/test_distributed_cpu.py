@@ -101,3 +101,43 @@ def test_choose_splitters_and_cuts():
     assert D.split_counts_from_cuts([10, 10, 70], 100) == [10, 0, 60, 30]
     assert D.split_counts_from_cuts([], 5) == [5]
     assert D.split_counts_from_cuts([7, 3], 10) == [7, 0, 3]  # non-monotone cuts are clamped
+
+
+def _schema_worker(rank, world, port, q):
+    try:
+        os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        from ray_project_ray_b200.block import DeviceBlock
+
+        cpu = torch.device("cpu")
+        full = DeviceBlock({"k": torch.arange(5, dtype=torch.int64), "p": torch.zeros((5, 3), dtype=torch.uint8)}, device=cpu)
+        # rank 1 has no rows and no columns: it adopts rank 0's schema and takes part with zero rows
+        mine = full if rank == 0 else DeviceBlock.empty(cpu)
+        got = D.adopt_schema(mine, cpu)
+        assert got.column_names == ["k", "p"] and got.columns["p"].shape[1:] == (3,) and got.columns["k"].dtype == torch.int64
+        assert got.num_rows == (5 if rank == 0 else 0)
+        # nobody has columns -> None on every rank; everybody has columns -> unchanged, no broadcast
+        assert D.adopt_schema(DeviceBlock.empty(cpu), cpu) is None
+        assert D.adopt_schema(full, cpu) is full
+        # the zero-row block goes through the all-to-all-v like any other
+        out = D.exchange_block(got, [got.num_rows, 0])
+        assert out.num_rows == (5 if rank == 0 else 0) and out.column_names == ["k", "p"]
+        q.put(("ok", rank))
+        dist.barrier()
+        dist.destroy_process_group()
+    except Exception as e:
+        q.put(("error", rank, repr(e)))
+        raise
+
+
+def test_rank_without_rows_adopts_the_schema_on_gloo():
+    world, port = 2, _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_schema_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(r[0] == "ok" for r in res), res

@@ -228,3 +228,17 @@ def test_byte_string_key_order_equals_pyarrow():
         for desc in (False, True):
             want = pac.sort_indices(pa.table({"k": arr}), [("k", "descending" if desc else "ascending")]).to_numpy()
             np.testing.assert_array_equal(orc.stable_argsort_bytes(col, desc), want)
+
+
+def test_key_boundaries_match_reference_map_groups():
+    """oracle.key_boundaries == the reference's own get_key_boundaries (tests/golden/make_golden.py run_map_groups)."""
+    import json
+    import os
+
+    with open(os.path.join(os.path.dirname(__file__), "golden", "map_groups_outputs.json")) as f:
+        cases = json.load(f)["cases"]
+    assert len(cases) >= 5
+    for c in cases:
+        keys = [c["keys"]] if isinstance(c["keys"], str) else c["keys"]
+        cols = [np.asarray(c["columns"][k]) for k in keys]
+        assert orc.key_boundaries(cols) == c["boundaries"]

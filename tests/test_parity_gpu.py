@@ -516,3 +516,75 @@ def test_multi_column_sort_first_column_distinct_shortcut(cuda_device):
         f = rng.standard_normal(n)                                # float first column (codes are probed)
         got = rd.from_numpy_columns({"f": f, "b": b, "row": row}, override_num_blocks=4).sort(["f", "b"], descending=desc).to_numpy()
         np.testing.assert_array_equal(got["row"], row[orc.stable_argsort_multi([f, b], desc)])
+
+
+def test_map_groups_boundaries_match_reference(cuda_device):
+    """GroupedData.map_groups (grouped_data.py:105-236): groups = the reference's own get_key_boundaries on the
+    sorted rows (tests/golden/map_groups_outputs.json), for one and for several key columns; one output block per
+    sorted block; fn_args / fn_kwargs reach fn."""
+    import json
+    import os
+
+    with open(os.path.join(os.path.dirname(__file__), "golden", "map_groups_outputs.json")) as f:
+        cases = json.load(f)["cases"]
+    for c in cases:
+        cols = {k: np.asarray(v, dtype=np.float64 if k == "c" else np.int64) for k, v in c["columns"].items()}
+        n = len(cols["row"])
+        shuffled = np.random.default_rng(1).permutation(n)
+        ds = rd.from_numpy_columns({k: v[shuffled] for k, v in cols.items()}, override_num_blocks=3)
+
+        def fn(g, scale, offset=0):
+            return {"first": g["row"][:1].copy(), "size": np.array([len(g["row"])], dtype=np.int64) * scale + offset,
+                    "rows": np.array([int(np.sort(g["row"]).astype(np.int64).sum())], dtype=np.int64)}
+
+        out = ds.groupby(c["keys"]).map_groups(fn, fn_args=(2,), fn_kwargs={"offset": 1})
+        assert out.num_blocks() <= 3
+        got = out.to_numpy()
+        ends = np.asarray(c["boundaries"])
+        starts = np.concatenate(([0], ends[:-1]))
+        np.testing.assert_array_equal((got["size"] - 1) // 2, ends - starts)
+        want_rows = [int(cols["row"][lo:hi].sum()) for lo, hi in zip(starts, ends)]   # same row SET per group
+        np.testing.assert_array_equal(got["rows"], want_rows)
+    # pandas batches, no key
+    ds = rd.from_numpy_columns({"a": np.arange(10, dtype=np.int64)}, override_num_blocks=2)
+    tot = ds.groupby(None).map_groups(lambda df: {"s": np.array([int(df["a"].sum())])}, batch_format="pandas").to_numpy()
+    assert tot["s"].tolist() == [45]
+
+
+def test_boundary_above_integer_range_and_nan_boundary(cuda_device):
+    """find_partition_index (util.py:719-758) with a boundary no int8 value reaches: ascending every row lies below
+    it, descending none lies at or above it (numpy.searchsorted on the reference's side); clamping the boundary to
+    127 would misplace the rows equal to 127. A NaN boundary on an integer column is refused."""
+    from ray_project_ray_b200.block import find_partition_indices
+
+    col = np.array([-128, -5, 0, 3, 127, 127, 127], dtype=np.int8)
+    asc = torch.from_numpy(col).to(cuda_device)
+    assert find_partition_indices(asc, [300, 127, -129, 2.5], False) == [7, 4, 0, 3]
+    assert find_partition_indices(asc, [300], False) == [int(np.searchsorted(col.astype(np.int64), 300, side="left"))]
+    desc = torch.from_numpy(col[::-1].copy()).to(cuda_device)
+    assert find_partition_indices(desc, [300, 127, -129], True) == [0, 3, 7]
+    with pytest.raises(ValueError):
+        find_partition_indices(asc, [float("nan")], False)
+
+
+def test_from_pandas_refuses_missing_values(cuda_device):
+    import pandas as pd
+
+    with pytest.raises(ValueError, match="missing values"):
+        rd.from_pandas(pd.DataFrame({"a": [1.0, np.nan, 3.0]}))
+    ok = rd.from_pandas(pd.DataFrame({"a": [1.0, 2.0, 3.0]}))
+    assert ok.sum("a") == 6.0
+
+
+def test_int64_sum_wraps_within_and_across_blocks(cuda_device):
+    """Documented divergence (DESIGN.md §7): group sums are int64 and wrap like pyarrow.compute.sum inside a block;
+    the reference merges the per-block sums as Python ints (aggregate/_aggregate.py:119-120), which never wrap.
+    Pinned here: the device result equals the exact sum modulo 2^64, whatever the block structure."""
+    big = 2 ** 62
+    k = np.array([1, 1, 1, 1, 2, 2], dtype=np.int64)
+    v = np.array([big, big, big, 5, -big, 7], dtype=np.int64)
+    exact = {1: 3 * big + 5, 2: -big + 7}
+    wrap = {g: ((s + 2 ** 63) % 2 ** 64) - 2 ** 63 for g, s in exact.items()}
+    for nblocks in (1, 3):
+        got = rd.from_numpy_columns({"k": k, "v": v}, override_num_blocks=nblocks).groupby("k").sum("v").to_numpy()
+        assert dict(zip(got["k"].tolist(), got["sum(v)"].tolist())) == wrap

@@ -248,4 +248,4 @@ def test_key_prefix_column(cuda_device):
         np.testing.assert_array_equal(again["payload"], payload[orc.stable_argsort_bytes(key, not desc)])
     sh = withp.random_shuffle(seed=4)
     assert not sh.get_internal_block_refs()[0].aux                # not maintained by shuffle: packed again on demand
-    np.testing.assert_array_equal(sh.sort("key").to_numpy()["payload"], payload[orc.stable_argsort_bytes(key, False)])
+    np.testing.assert_array_equal(sh.sort("key").to_numpy()["key"], key[orc.stable_argsort_bytes(key, False)])
