@@ -185,7 +185,7 @@ def make_records(n: int, rank: int, dev):
     pool = torch.randint(0, 256, (65536, KEY_BYTES), dtype=torch.uint8, device=dev,
                          generator=torch.Generator(device=dev).manual_seed(4242))      # the same on every rank
     i = torch.arange(5, n, 4096, device=dev)
-    key[i] = pool[(i * 2654435761 >> 7) % 65536]
+    key[i] = pool[(((i // 4096 + 7919 * rank) * 2654435761) % (1 << 32)) >> 16]     # ~0.5 rows per pool key and rank
     i = torch.arange(1027, n, 1024, device=dev)
     key[i] = key[i - 1]
     del i, pool

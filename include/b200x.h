@@ -220,6 +220,9 @@ int b200x_scatter_rows_to_peers(const void* src, size_t row_bytes, const uint32_
  * splitter codes <= code(keys[r]) (so equal keys share an owner, _internal/util.py:756-758) and slot = the row's
  * position among the rows this rank sends to that owner, in row order (a stable split: ties keep their
  * order through the exchange). counts_out[16] (device) = rows per owner. n < 2^28, <= 15 splitters.
+ * After the call `temp` holds, as uint32 [ceil(n / 2048)][16], the slots handed out per owner before every tile of
+ * 2048 rows (row t = rows per owner among the first 2048 * t rows): what a sender needs to say which slots a
+ * chunk of its rows fills.
  * b200x_scatter_rows_by_target: row r of src (read in order) is stored at row peer_row_off_host[owner] + slot
  * of peer_base_host[owner]. */
 int b200x_partition_targets(const void* keys, int key_type, int descending, size_t n, const uint64_t* splitter_codes,
@@ -228,6 +231,29 @@ int b200x_partition_targets(const void* keys, int key_type, int descending, size
 int b200x_scatter_rows_by_target(const void* src, size_t row_bytes, const uint32_t* target, size_t n,
                                  void* const* peer_base_host, const unsigned long long* peer_row_off_host, int world,
                                  void* stream);
+
+/* The same exchange for rows kept as records (b200x_gather_rows_pitched). b200x_scatter_records_by_target: of
+ * every source record (src_pitch bytes apart; src may point 8 bytes into the records) copy_bytes bytes (a multiple
+ * of 16) are stored at the start of row peer_row_off_host[owner] + slot of peer_base_host[owner], rows dst_pitch
+ * apart. A record thus travels without its padding - and without its first 8 bytes when those are the sort key that
+ * went ahead with the key column: a gensort record in a 128-byte slot crosses NVLink as 96 bytes = three whole
+ * sectors of one line. Passing src + r0 * src_pitch, target + r0 and a row count sends a chunk of the rows.
+ * b200x_gather_records_prefixed: the receiver's last step: dst record i (dst_pitch apart) = [8-byte key prefix |
+ * received row idx[i]] when shift == 8 - the prefix taken from sorted_keys[i] (big-endian bytes if prefix_be, else
+ * the integer as it is), i.e. the elided key bytes are put back from the sorted key column while the rows are
+ * gathered into sorted order - or just the received row when shift == 0; bytes from used_bytes on are zero.
+ * slot_ranges_host (num_ranges pairs [lo, hi), HOST array, <= 16) restricts the gather to rows whose receive slot
+ * idx[i] lies in one of the ranges (the chunks that have landed); tie_mode 1 skips, 2 selects the positions whose
+ * key equals a neighbour's (their order is final only after b200x_fix_ties), 0 takes all.
+ * Replaces the same object-store hop as b200x_scatter_rows_to_peers, and the reducer's concat + take
+ * (_internal/arrow_block.py:554-567, transform_pyarrow.py:269-276). */
+int b200x_scatter_records_by_target(const void* src, size_t src_pitch, size_t copy_bytes, const uint32_t* target, size_t n,
+                                    void* const* peer_base_host, const unsigned long long* peer_row_off_host,
+                                    size_t dst_pitch, int world, void* stream);
+int b200x_gather_records_prefixed(const void* recv, size_t recv_pitch, size_t copy_bytes, const uint32_t* idx, size_t n,
+                                  const uint64_t* sorted_keys, int prefix_be, size_t shift, size_t used_bytes, void* dst,
+                                  size_t dst_pitch, int tie_mode, const uint32_t* slot_ranges_host, int num_ranges,
+                                  void* stream);
 
 /* Seeded pseudo-random bijection pi on [0, n) (6 alternating Feistel rounds over the 2^ceil(log2 n)
  * domain, cycle-walked into range). Deterministic in (seed, n).

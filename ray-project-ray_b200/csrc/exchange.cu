@@ -678,3 +678,261 @@ extern "C" int b200x_scatter_rows_by_target(const void* src, size_t row_bytes, c
   B200X_LAUNCH_CHECK("scatter_rows_by_target_kernel");
   return B200X_OK;
 }
+
+// ---------------------------------------------------------------------------
+// Record exchange: rows kept as records at a pitch (b200x_gather_rows_pitched)
+// ---------------------------------------------------------------------------
+// b200x_scatter_records_by_target: the staged scatter for records. Of every source record (src_pitch bytes apart)
+// only copy_bytes bytes travel - the record minus padding, and minus its first 8 bytes when those are the sort key
+// that was exchanged ahead as a column of its own - and land at the start of the owner's row slot (dst_pitch
+// apart). With copy_bytes a multiple of 32 and dst_pitch a multiple of 128 every row leaves as whole 32-byte
+// sectors of one 128-byte line: a gensort record (10-byte key + 90-byte payload in a 128-byte record) crosses
+// NVLink as 96 bytes, the 8-byte key prefix having gone ahead with the key exchange.
+// b200x_gather_records_prefixed: the receiver's last step. Output record i = [prefix(sorted_keys[i]) | the received
+// row idx[i]], i.e. the elided key bytes are put back from the sorted key column (which the sort produced anyway)
+// while the rows are gathered into sorted order. The gather can be restricted to rows whose receive slot lies in
+// given ranges (rows that have already landed when the payload arrives in chunks), and to / from positions whose
+// key equals a neighbour's (their order is only final after b200x_fix_ties).
+namespace b200x {
+
+template <typename LV>
+__global__ void __launch_bounds__(ST_THREADS)
+scatter_records_staged_kernel(const unsigned char* __restrict__ src, uint64_t src_pitch, uint32_t copy_bytes,
+                              const uint32_t* __restrict__ target, const PeerPlan p, uint64_t dst_pitch, uint64_t n,
+                              uint32_t tile_rows) {
+  extern __shared__ __align__(16) unsigned char st_raw[];
+  unsigned char* sdata = st_raw;                                                              // [tile_rows * copy_bytes]
+  unsigned long long* sdst = reinterpret_cast<unsigned long long*>(st_raw + ST_DATA_BYTES);   // [tile_rows]
+  uint16_t* slp = reinterpret_cast<uint16_t*>(sdst + ST_MAX_TILE);                            // [tile_rows]
+  __shared__ uint32_t s_cnt[MAX_PEERS], s_min[MAX_PEERS], s_off[MAX_PEERS];
+  const uint64_t num_tiles = (n + tile_rows - 1) / tile_rows;
+  const uint32_t lpr = copy_bytes / (uint32_t)sizeof(LV);   // loads per row
+  const uint32_t vpr = copy_bytes / 16u;                    // 16-byte stores per row
+  for (uint64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    const uint64_t r0 = tile * tile_rows;
+    const uint32_t rows = (uint32_t)min((uint64_t)tile_rows, n - r0);
+    if (threadIdx.x < MAX_PEERS) {
+      s_cnt[threadIdx.x] = 0;
+      s_min[threadIdx.x] = 0xFFFFFFFFu;
+    }
+    __syncthreads();
+    constexpr int RPT = ST_MAX_TILE / ST_THREADS;
+    uint32_t tg[RPT];
+#pragma unroll
+    for (int k = 0; k < RPT; ++k) {
+      const uint32_t lr = threadIdx.x + k * ST_THREADS;
+      tg[k] = 0;
+      if (lr < rows) {
+        tg[k] = target[r0 + lr];
+        const uint32_t d = tg[k] >> SLOT_BITS, slot = tg[k] & ((1u << SLOT_BITS) - 1u);
+        atomicAdd(&s_cnt[d], 1u);
+        atomicMin(&s_min[d], slot);
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t run = 0;
+      for (int d = 0; d < MAX_PEERS; ++d) {
+        s_off[d] = run;
+        run += s_cnt[d];
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < RPT; ++k) {
+      const uint32_t lr = threadIdx.x + k * ST_THREADS;
+      if (lr < rows) {
+        const uint32_t d = tg[k] >> SLOT_BITS, slot = tg[k] & ((1u << SLOT_BITS) - 1u);
+        const uint32_t lp = s_off[d] + (slot - s_min[d]);
+        slp[lr] = (uint16_t)lp;
+        sdst[lp] = (unsigned long long)(p.base[d] + (p.row_off[d] + slot) * dst_pitch);
+      }
+    }
+    __syncthreads();
+    const unsigned char* tsrc = src + r0 * src_pitch;
+    const uint32_t loads = rows * lpr;
+    for (uint32_t t = threadIdx.x; t < loads; t += ST_THREADS) {   // the tile's rows, in order
+      const uint32_t lr = t / lpr, c = t - lr * lpr;
+      *reinterpret_cast<LV*>(sdata + (uint32_t)slp[lr] * copy_bytes + c * (uint32_t)sizeof(LV)) =
+          *reinterpret_cast<const LV*>(tsrc + (uint64_t)lr * src_pitch + c * sizeof(LV));
+    }
+    __syncthreads();
+    const uint32_t stores = rows * vpr;
+    for (uint32_t t = threadIdx.x; t < stores; t += ST_THREADS) {  // owner by owner, consecutive slots
+      const uint32_t i = t / vpr, c = t - i * vpr;
+      reinterpret_cast<uint4*>(sdst[i])[c] = reinterpret_cast<const uint4*>(sdata + i * copy_bytes)[c];
+    }
+    __syncthreads();
+  }
+}
+
+constexpr int GR_MAX_RANGES = 16;
+struct SlotRanges {
+  uint32_t lo[GR_MAX_RANGES], hi[GR_MAX_RANGES];
+  int n;   // 0 = every slot
+};
+
+__device__ __forceinline__ uint64_t bswap64(uint64_t v) {
+  const uint32_t lo = (uint32_t)v, hi = (uint32_t)(v >> 32);
+  return ((uint64_t)__byte_perm(lo, 0, 0x0123) << 32) | (uint64_t)__byte_perm(hi, 0, 0x0123);
+}
+
+// keep the bytes of an 8-byte word whose record position (pos0 .. pos0+7) lies below `used`
+__device__ __forceinline__ uint64_t keep_below(uint64_t w, uint32_t pos0, uint32_t used) {
+  if (pos0 + 8u <= used) return w;
+  if (pos0 >= used) return 0ull;
+  return w & ((1ull << (8u * (used - pos0))) - 1ull);
+}
+
+// tie_mode 0: every position; 1: skip positions whose key equals a neighbour's; 2: only those positions.
+// dv_shift >= 0: dst_vec == 1 << dv_shift (the usual case: 128-byte records), else a division per element.
+__global__ void __launch_bounds__(256)
+gather_records_prefixed_kernel(const unsigned char* __restrict__ recv, uint64_t recv_pitch, uint32_t copy_bytes,
+                               const uint32_t* __restrict__ idx, uint64_t n, const uint64_t* __restrict__ keys, int prefix_be,
+                               uint32_t shift, uint32_t used, unsigned char* __restrict__ dst, uint32_t dst_vec, int dv_shift,
+                               int tie_mode, const SlotRanges sr) {
+  constexpr int U = 4;
+  const uint64_t total = n * dst_vec;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t t0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; t0 < total; t0 += U * stride) {
+    uint64_t w0[U], w1[U];
+    bool go[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const uint64_t t = t0 + u * stride;
+      go[u] = t < total;
+      w0[u] = w1[u] = 0;
+      if (!go[u]) continue;
+      const uint64_t i = dv_shift >= 0 ? (t >> dv_shift) : (t / dst_vec);
+      const uint32_t j = (uint32_t)(t - i * dst_vec);
+      const uint32_t s = idx[i];
+      if (sr.n > 0) {
+        bool in = false;
+#pragma unroll
+        for (int k = 0; k < GR_MAX_RANGES; ++k) in |= (k < sr.n) && s >= sr.lo[k] && s < sr.hi[k];
+        go[u] = in;
+      }
+      uint64_t key = 0;
+      if (keys != nullptr && go[u] && (tie_mode != 0 || (shift == 8u && j == 0))) {
+        key = keys[i];
+        if (tie_mode != 0) {
+          const bool tied = (i > 0 && keys[i - 1] == key) || (i + 1 < n && keys[i + 1] == key);
+          go[u] = tied == (tie_mode == 2);
+        }
+      }
+      if (!go[u]) continue;
+      const unsigned char* row = recv + (uint64_t)s * recv_pitch;
+      // output bytes [16j, 16j+16) = received bytes [16j - shift, 16j - shift + 16); shift is 0 or 8
+      const uint32_t o0 = 16u * j, o1 = o0 + 8u;
+      if (o0 >= shift && o0 - shift + 8u <= copy_bytes) w0[u] = *reinterpret_cast<const uint64_t*>(row + (o0 - shift));
+      if (o1 >= shift && o1 - shift + 8u <= copy_bytes) w1[u] = *reinterpret_cast<const uint64_t*>(row + (o1 - shift));
+      if (shift == 8u && j == 0) w0[u] = prefix_be ? bswap64(key) : key;
+      w0[u] = keep_below(w0[u], o0, used);
+      w1[u] = keep_below(w1[u], o1, used);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (go[u]) {
+        uint4 v;
+        v.x = (uint32_t)w0[u];
+        v.y = (uint32_t)(w0[u] >> 32);
+        v.z = (uint32_t)w1[u];
+        v.w = (uint32_t)(w1[u] >> 32);
+        reinterpret_cast<uint4*>(dst)[t0 + u * stride] = v;
+      }
+    }
+  }
+}
+
+}  // namespace b200x
+
+extern "C" int b200x_scatter_records_by_target(const void* src, size_t src_pitch, size_t copy_bytes, const uint32_t* target,
+                                               size_t n, void* const* peer_base_host,
+                                               const unsigned long long* peer_row_off_host, size_t dst_pitch, int world,
+                                               void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (world <= 0 || world > MAX_PEERS) {
+    set_error("b200x_scatter_records_by_target: world=%d out of range [1, %d]", world, MAX_PEERS);
+    return B200X_ERR_ARG;
+  }
+  if (n == 0 || copy_bytes == 0) return B200X_OK;
+  if (src == nullptr || target == nullptr || peer_base_host == nullptr || peer_row_off_host == nullptr) {
+    set_error("b200x_scatter_records_by_target: NULL pointer");
+    return B200X_ERR_ARG;
+  }
+  if ((copy_bytes & 15) != 0 || copy_bytes > 1024 || copy_bytes > src_pitch || copy_bytes > dst_pitch || (dst_pitch & 15) != 0 ||
+      (src_pitch & 7) != 0 || ((uintptr_t)src & 7) != 0) {
+    set_error("b200x_scatter_records_by_target: copy_bytes=%zu must be a multiple of 16, <= 1024 and <= both pitches (%zu, %zu); "
+              "dst_pitch a multiple of 16; src and src_pitch multiples of 8", copy_bytes, src_pitch, dst_pitch);
+    return B200X_ERR_ALIGN;
+  }
+  PeerPlan p;
+  p.world = world;
+  for (int d = 0; d < MAX_PEERS; ++d) {
+    p.base[d] = d < world ? (unsigned char*)peer_base_host[d] : nullptr;
+    p.row_off[d] = d < world ? peer_row_off_host[d] : 0;
+    if (d < world && ((uintptr_t)p.base[d] & 15) != 0) {
+      set_error("b200x_scatter_records_by_target: receive buffer %d is not 16-byte aligned", d);
+      return B200X_ERR_ALIGN;
+    }
+  }
+  for (int d = 0; d <= MAX_PEERS; ++d) p.send_off[d] = 0;
+  uint32_t tile_rows = (uint32_t)(ST_DATA_BYTES / copy_bytes) / 32 * 32;
+  if (tile_rows > (uint32_t)ST_MAX_TILE) tile_rows = ST_MAX_TILE;
+  const size_t smem = ST_DATA_BYTES + ST_MAX_TILE * sizeof(unsigned long long) + ST_MAX_TILE * sizeof(uint16_t);
+  uint64_t gtiles = (n + tile_rows - 1) / tile_rows;
+  if (g_scatter_blocks_per_sm > 0 && gtiles > (uint64_t)sm_count() * g_scatter_blocks_per_sm)
+    gtiles = (uint64_t)sm_count() * g_scatter_blocks_per_sm;
+  const bool wide = (((uintptr_t)src | src_pitch) & 15) == 0;
+  prof_begin(stream, PROF_SCATTER);
+  if (wide)
+    scatter_records_staged_kernel<uint4><<<(uint32_t)gtiles, ST_THREADS, smem, stream>>>(
+        (const unsigned char*)src, src_pitch, (uint32_t)copy_bytes, target, p, dst_pitch, n, tile_rows);
+  else
+    scatter_records_staged_kernel<uint64_t><<<(uint32_t)gtiles, ST_THREADS, smem, stream>>>(
+        (const unsigned char*)src, src_pitch, (uint32_t)copy_bytes, target, p, dst_pitch, n, tile_rows);
+  prof_end(stream);
+  B200X_LAUNCH_CHECK("scatter_records_staged_kernel");
+  return B200X_OK;
+}
+
+extern "C" int b200x_gather_records_prefixed(const void* recv, size_t recv_pitch, size_t copy_bytes, const uint32_t* idx,
+                                             size_t n, const uint64_t* sorted_keys, int prefix_be, size_t shift,
+                                             size_t used_bytes, void* dst, size_t dst_pitch, int tie_mode,
+                                             const uint32_t* slot_ranges_host, int num_ranges, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (n == 0) return B200X_OK;
+  if (recv == nullptr || idx == nullptr || dst == nullptr || (shift != 0 && shift != 8) || (shift == 8 && sorted_keys == nullptr) ||
+      (tie_mode != 0 && sorted_keys == nullptr) || tie_mode < 0 || tie_mode > 2 || num_ranges < 0 || num_ranges > GR_MAX_RANGES ||
+      (num_ranges > 0 && slot_ranges_host == nullptr)) {
+    set_error("b200x_gather_records_prefixed: bad arguments (shift 0 or 8, sorted_keys needed for shift 8 / tie modes, <= %d ranges)",
+              GR_MAX_RANGES);
+    return B200X_ERR_ARG;
+  }
+  if ((copy_bytes & 7) != 0 || copy_bytes > recv_pitch || (recv_pitch & 7) != 0 || ((uintptr_t)recv & 7) != 0 ||
+      (dst_pitch & 15) != 0 || ((uintptr_t)dst & 15) != 0 || used_bytes > dst_pitch || dst_pitch > (1u << 16)) {
+    set_error("b200x_gather_records_prefixed: copy_bytes / recv_pitch / recv must be multiples of 8, dst and dst_pitch of 16, "
+              "used_bytes <= dst_pitch <= 65536");
+    return B200X_ERR_ALIGN;
+  }
+  SlotRanges sr;
+  sr.n = num_ranges;
+  for (int k = 0; k < GR_MAX_RANGES; ++k) {
+    sr.lo[k] = k < num_ranges ? slot_ranges_host[2 * k] : 0u;
+    sr.hi[k] = k < num_ranges ? slot_ranges_host[2 * k + 1] : 0u;
+  }
+  const uint32_t dst_vec = (uint32_t)(dst_pitch / 16);
+  int dv_shift = -1;
+  for (int b = 0; b < 16; ++b)
+    if (dst_vec == (1u << b)) dv_shift = b;
+  uint64_t blocks = (((uint64_t)n * dst_vec + 3) / 4 + 255) / 256;
+  const uint64_t cap = (uint64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  prof_begin(stream, PROF_GATHER);
+  gather_records_prefixed_kernel<<<(uint32_t)blocks, 256, 0, stream>>>(
+      (const unsigned char*)recv, recv_pitch, (uint32_t)copy_bytes, idx, n, sorted_keys, prefix_be, (uint32_t)shift,
+      (uint32_t)used_bytes, (unsigned char*)dst, dst_vec, dv_shift, tie_mode, sr);
+  prof_end(stream);
+  B200X_LAUNCH_CHECK("gather_records_prefixed_kernel");
+  return B200X_OK;
+}

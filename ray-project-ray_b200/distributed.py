@@ -100,22 +100,28 @@ def exchange_block(block: DeviceBlock, send_counts: Sequence[int], group=None) -
 
 
 # ------------------------------------------------------- peer-memory (NVLink P2P) transport
-_symm_cache: Dict[Tuple[int, int], Tuple[torch.Tensor, object]] = {}
+_symm_cache: Dict[int, Tuple[torch.Tensor, object]] = {}
 _p2p_ok: Dict[str, Optional[bool]] = {"state": None}
 _ROW_ROUND = 1 << 20
 
 
 def _symm_buffer(slot: int, nbytes: int, dev: torch.device, group):
-    """A receive buffer that every rank can store into: torch symmetric memory (cuMem + peer mapping),
-    allocated once per (slot, size) and reused by later exchanges."""
+    """A receive buffer that every rank can store into: torch symmetric memory (cuMem + peer mapping). ONE buffer
+    per slot (= position of the column in an exchange), reused by later exchanges and replaced by a larger one
+    (at least 1.5x) when an exchange needs more: the memory held is bounded by the largest exchange seen, not
+    by the number of different sizes. Every rank asks for the same sizes (they derive from the global count
+    matrix), so the rendezvous of a replacement is collective."""
     import torch.distributed._symmetric_memory as symm
 
-    key = (slot, nbytes)
-    if key not in _symm_cache:
-        t = symm.empty(nbytes, dtype=torch.uint8, device=dev)
+    have = _symm_cache.get(slot)
+    if have is None or have[0].numel() < nbytes:
+        size = nbytes if have is None else max(nbytes, have[0].numel() * 3 // 2)
+        size = (size + (1 << 21) - 1) >> 21 << 21
+        _symm_cache.pop(slot, None)
+        t = symm.empty(size, dtype=torch.uint8, device=dev)
         h = symm.rendezvous(t, group if group is not None else dist.group.WORLD)
-        _symm_cache[key] = (t, h)
-    return _symm_cache[key]
+        _symm_cache[slot] = (t, h)
+    return _symm_cache[slot]
 
 
 def p2p_available(dev: torch.device, group=None) -> bool:
@@ -145,13 +151,26 @@ class P2PExchange:
     `view` returns tensors that ALIAS the receive buffers: consume them before the next exchange."""
 
     def __init__(self, columns: Dict[str, Tuple[torch.Tensor, Optional[torch.Tensor]]], n: int,
-                 send_counts: Sequence[int], dev: torch.device, group=None, target: Optional[torch.Tensor] = None):
+                 send_counts: Sequence[int], dev: torch.device, group=None, target: Optional[torch.Tensor] = None,
+                 chunk_table: Optional[np.ndarray] = None):
         import ctypes
 
         self.columns, self.n, self.dev, self.group = columns, n, dev, group
         self.target = target  # per-row owner<<28|slot (partition-first mode): rows are read in order
         self.world, rank = dist.get_world_size(group), dist.get_rank(group)
-        C = all_gather_counts(send_counts, group, dev)
+        self.rank = rank
+        if chunk_table is not None:
+            # chunk_table[c, d] = rows among this rank's first chunk_rows[c] rows that go to rank d (last row = all
+            # rows): gathered from every rank, it tells a receiver which slots of its buffer chunk c of rank r fills
+            mine = torch.from_numpy(np.ascontiguousarray(chunk_table, dtype=np.int64)).to(dev)
+            parts = [torch.empty_like(mine) for _ in range(self.world)]
+            dist.all_gather(parts, mine, group=group)
+            self.tables = torch.stack(parts).cpu().numpy()          # [source rank, chunk boundary, destination]
+            C = self.tables[:, -1, :]
+        else:
+            self.tables = None
+            C = all_gather_counts(send_counts, group, dev)
+        self.C = C
         self.n_recv = int(C[:, rank].sum())
         cap_rows = int(C.sum(axis=0).max())
         cap_rows = max(_ROW_ROUND, (cap_rows + _ROW_ROUND - 1) // _ROW_ROUND * _ROW_ROUND)
@@ -166,6 +185,24 @@ class P2PExchange:
                 row_bytes *= int(d)
             self._bufs[name] = (_symm_buffer(slot, cap_rows * row_bytes, dev, group), row_bytes)
         self._handle = next(iter(self._bufs.values()))[0][1]
+
+    def send_records(self, name: str, copy_bytes: int, src_offset: int, row0: int, nrows: int) -> None:
+        """Rows [row0, row0 + nrows) of the record unit `name`: bytes [src_offset, src_offset + copy_bytes) of every
+        record go to the start of the row's slot in the owner's receive buffer (slots one record pitch apart)."""
+        col, _ = self.columns[name]
+        (buf, h), pitch = self._bufs[name]
+        ops.scatter_records_by_target(col, self.target, [int(p) for p in h.buffer_ptrs], [int(x) for x in self._ro], pitch,
+                                      copy_bytes=copy_bytes, src_offset=src_offset, row0=row0, nrows=nrows)
+
+    def chunk_slot_ranges(self, c: int) -> List[Tuple[int, int]]:
+        """Slots [lo, hi) of this rank's receive buffers that chunk c of every source rank fills."""
+        out = []
+        for r in range(self.world):
+            base = int(self.C[:r, self.rank].sum())
+            lo, hi = base + int(self.tables[r, c, self.rank]), base + int(self.tables[r, c + 1, self.rank])
+            if hi > lo:
+                out.append((lo, hi))
+        return out
 
     def fence(self) -> None:
         """Device-side barrier over all ranks on the current stream (symmetric-memory signal pads): before
@@ -201,14 +238,14 @@ class P2PExchange:
         return out
 
 
-_side_streams: Dict[int, torch.cuda.Stream] = {}
+_side_streams: Dict[Tuple[int, int], torch.cuda.Stream] = {}
 
 
-def _side_stream(dev: torch.device) -> torch.cuda.Stream:
+def _side_stream(dev: torch.device, which: int = 0) -> torch.cuda.Stream:
     idx = dev.index if dev.index is not None else torch.cuda.current_device()
-    if idx not in _side_streams:
-        _side_streams[idx] = torch.cuda.Stream(device=dev)
-    return _side_streams[idx]
+    if (idx, which) not in _side_streams:
+        _side_streams[(idx, which)] = torch.cuda.Stream(device=dev)
+    return _side_streams[(idx, which)]
 
 
 # ------------------------------------------------------------------------ device steps
@@ -339,6 +376,9 @@ def _p2p_partition_sort(local: DeviceBlock, sort_key: SortKey, n: int, dev, grou
     world = dist.get_world_size(group)
     key_cols = sort_key.get_columns()
     first, desc = key_cols[0], sort_key.get_descending()
+    plan = _record_exchange_plan(local, key_cols, desc) if os.environ.get("B200X_RECORD_EXCHANGE", "1") != "0" else None
+    if plan is not None:
+        return _p2p_partition_sort_records(local, sort_key, n, dev, group, samples_per_rank, plan)
     late = 1 < len(key_cols) <= 1 + ops.FIX_TIES_MAX_COLS and all(
         c not in local.columns and c not in local.aux and BYTE_KEY_SEP in c for c in key_cols[1:])
     early = [first] if late else list(key_cols)
@@ -406,6 +446,165 @@ def _p2p_partition_sort(local: DeviceBlock, sort_key: SortKey, n: int, dev, grou
         perm2, _, skeys2 = DeviceBlockAccessor(received)._argsort_chain(sort_key, False)
         out = _assemble_sorted(local, groups, recv, perm2, first, skeys2, ex.n_recv, dev)
     return out
+
+
+def _record_exchange_plan(local: DeviceBlock, key_cols: Sequence[str], desc: bool):
+    """Can this sort use the record exchange (one record group that moves in chunks, the key prefix elided)?
+    Needs: exactly one record group; every key column after the first is a chunk of a byte-string member of it
+    (compared where it lies in the received rows). Returns None or a dict with the group, the bytes in use, and
+    `shift` = 8 when the first 8 bytes of every record ARE the first key column as the sort writes it out (the
+    big-endian prefix of a byte-string key at offset 0: those bytes then travel only once, as the key column)."""
+    from .block import _inner
+
+    groups, _ = record_groups(local)
+    if len(groups) != 1 or local.num_rows == 0:
+        return None
+    g = groups[0]
+    first = key_cols[0]
+    for c in key_cols[1:]:
+        base, sep, idx = c.rpartition(BYTE_KEY_SEP)
+        if c in local.columns or not (sep and idx.isdigit() and base in g.members):
+            return None
+    if len(key_cols) > 1 + ops.FIX_TIES_MAX_COLS:
+        return None
+    used = max(off + _inner(local.columns[k])[0] for k, (off, _, _) in g.members.items())
+    base, sep, idx = first.rpartition(BYTE_KEY_SEP)
+    shift, be = 0, True
+    if first not in local.columns and sep and idx == "0" and base in g.members and g.members[base][0] == 0 \
+            and local.columns[base].shape[1] >= 8:
+        shift = 8
+    elif first not in local.columns:
+        return None
+    copy = (used - shift + 15) // 16 * 16
+    if copy + shift > g.pitch and shift:
+        return None
+    return {"group": g, "used": used, "shift": shift, "be": be, "copy": min(copy, g.pitch), "base": base if shift else None}
+
+
+def _p2p_partition_sort_records(local: DeviceBlock, sort_key: SortKey, n: int, dev, group, samples_per_rank: int, plan) -> DeviceBlock:
+    """Partition-first distributed sort of a block held as records, with the transfer and the last gather overlapped:
+      1. first key column (dense) -> splitters -> per-row (owner, slot) targets, as in `_p2p_partition_sort`;
+      2. the key column is exchanged and the received keys are sorted on a second stream;
+      3. the records follow in K chunks of rows (`b200x_scatter_records_by_target`: without padding, and without
+         their first 8 bytes when those are the key prefix that went ahead in step 2), each chunk closed by a
+         device-side barrier of all ranks;
+      4. as soon as the keys are sorted, every chunk that has landed is gathered into its final rows on a third
+         stream (`b200x_gather_records_prefixed` restricted to that chunk's slots, the key prefix put back from the
+         sorted keys) while the next chunk is still crossing NVLink: only the last chunk's gather is exposed;
+      5. positions whose first key equals a neighbour's are left out until everything has landed: `fix_ties` orders
+         them from the key bytes in the received rows, then one small pass gathers them."""
+    from . import _lib
+    from .block import _TieVerdict
+
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    key_cols = sort_key.get_columns()
+    first, desc = key_cols[0], sort_key.get_descending()
+    g, used, shift, copy = plan["group"], plan["used"], plan["shift"], plan["copy"]
+    pitch = g.pitch
+    in_group = set(g.members)
+    keycol = local.key_column(first)
+    extra = [c for c in local.column_names if c not in in_group and c != first]   # columns outside the record: sent whole, gathered last
+    m = min(samples_per_rank, n)
+    pos = ((np.arange(m, dtype=np.float64) + 0.5) * (n / m)).astype(np.int64).astype(np.int32)
+    sample_codes = ops.encode_keys(ops.gather(keycol, torch.from_numpy(pos).to(dev)), desc)
+    splitters = choose_splitters(_gather_samples(sample_codes, samples_per_rank, world, dev, group), world)
+    if splitters.size != world - 1:
+        splitters = np.full(world - 1, np.iinfo(np.uint64).max, dtype=np.uint64)
+    sp = torch.from_numpy(splitters.view(np.int64)).to(dev)
+    target, counts, tile_table = ops.partition_targets(keycol, desc, sp, want_tile_table=True)
+    tiles = tile_table.shape[0]
+    K = int(os.environ.get("B200X_EXCHANGE_CHUNKS", "4")) if n >= int(os.environ.get("B200X_EXCHANGE_CHUNK_MIN_ROWS", 1 << 22)) else 1
+    K = max(1, min(K, tiles))
+    cut_tiles = [c * tiles // K for c in range(K)]
+    rows_at = [t * ops.PT_TILE_ROWS for t in cut_tiles] + [n]
+    sel = torch.tensor(cut_tiles, dtype=torch.int64, device=dev)
+    table = torch.cat([tile_table.index_select(0, sel).to(torch.int64), counts.reshape(1, 16)], 0).cpu().numpy()[:, :world]
+    send_counts = [int(x) for x in table[-1]]
+    cols = {first: (keycol, None), "\x00rec": (g.rec, None)}
+    for c in extra:
+        cols[c] = (_contig(local.columns[c]), None)
+    ex = P2PExchange(cols, n, send_counts, dev, group, target=target, chunk_table=table)
+    main = torch.cuda.current_stream(dev)
+    ex.fence()
+    ex.send([first])
+    ex.fence()
+    if ex.n_recv == 0:
+        ex.send(extra)
+        for c in range(K):
+            ex.send_records("\x00rec", copy, shift, rows_at[c], rows_at[c + 1] - rows_at[c])
+            ex.fence()
+        return local.slice(0, 0)
+    n_recv = ex.n_recv
+    recv_keys = ex.view([first])[first]
+    side, gstream = _side_stream(dev), _side_stream(dev, 1)
+    landed, sorted_ev = torch.cuda.Event(), torch.cuda.Event()
+    landed.record(main)
+    out = torch.empty((n_recv, pitch), dtype=torch.uint8, device=dev)
+    # the transfer runs on two blocks per SM (it is link-bound) so that the sort and the gathers fit next to it
+    _lib.call("b200x_set_tuning", 1, int(os.environ.get("B200X_PAYLOAD_BLOCKS_PER_SM", "2")))
+    chunk_ev = []
+    try:
+        ex.send(extra)
+        for c in range(K):
+            ex.send_records("\x00rec", copy, shift, rows_at[c], rows_at[c + 1] - rows_at[c])
+            ex.fence()
+            ev = torch.cuda.Event()
+            ev.record(main)
+            chunk_ev.append(ev)
+    finally:
+        _lib.call("b200x_set_tuning", 1, 0)
+    with torch.cuda.stream(side):
+        side.wait_event(landed)
+        perm2, codes2, skeys2 = ops.argsort(recv_keys, desc, want_keys=True, want_codes=recv_keys.dtype.is_floating_point)
+        sorted_ev.record(side)
+    probe = skeys2 if skeys2 is not None else codes2.view(torch.uint64)
+    recv_rec = ex.view(["\x00rec"])["\x00rec"]
+    later = len(key_cols) > 1
+    with torch.cuda.stream(gstream):
+        gstream.wait_event(sorted_ev)
+        for t in (perm2, probe, out):
+            t.record_stream(gstream)
+        for c in range(K):
+            gstream.wait_event(chunk_ev[c])
+            ops.gather_records_prefixed(recv_rec, perm2, out, copy, used, probe if (shift or later) else None, plan["be"], shift,
+                                        tie_mode=1 if later else 0, ranges=ex.chunk_slot_ranges(c) if K > 1 else None)
+        verdict = None
+        if later:
+            pieces = []
+            for c in key_cols[1:]:
+                base, _, idx = c.rpartition(BYTE_KEY_SEP)
+                off, _, shape = g.members[base]
+                lo = off + 8 * int(idx) - shift                                   # where that chunk lies in a received row
+                pieces.append(ops.KeyPiece(recv_rec, lo, min(8, int(shape[0]) - 8 * int(idx))))
+            verdict = _TieVerdict(ops.fix_ties(probe, perm2, pieces, desc))
+            ops.gather_records_prefixed(recv_rec, perm2, out, copy, used, probe, plan["be"], shift, tie_mode=2)
+        extra_out = {}
+        if extra:
+            recv_extra = ex.view(extra)
+            extra_out = dict(zip(extra, ops.gather_columns([recv_extra[c] for c in extra], perm2)))
+        done = torch.cuda.Event()
+        done.record(gstream)
+    main.wait_event(done)
+    perm2.record_stream(main)
+    probe.record_stream(main)
+    if verdict is not None and not verdict.ok():
+        # long runs of equal first keys: order the received rows by all key columns, gather everything again
+        chunks = {first: recv_keys}
+        for c, piece in zip(key_cols[1:], pieces):
+            chunks[c] = ops.pack_key_bytes(piece.col, piece.offset, piece.width)
+        perm2 = None
+        for i, c in enumerate(reversed(key_cols)):
+            perm2, _, sk = ops.argsort(chunks[c], desc, perm_in=perm2, want_keys=(i == len(key_cols) - 1))
+        probe = sk
+        ops.gather_records_prefixed(recv_rec, perm2, out, copy, used, probe if shift else None, plan["be"], shift)
+        if extra:
+            extra_out = dict(zip(extra, ops.gather_columns([ex.view(extra)[c] for c in extra], perm2)))
+    out_cols = dict(g.views(out))
+    out_cols.update(extra_out)
+    if first in local.columns and first not in in_group:
+        out_cols[first] = probe if skeys2 is not None else ops.gather(recv_keys, perm2)
+    aux = {first: probe} if (first not in local.columns and first.endswith(f"{BYTE_KEY_SEP}0") and probe is not None) else {}
+    return DeviceBlock({c: out_cols[c] for c in local.column_names}, num_rows=n_recv, device=dev, aux=aux)
 
 
 def _p2p_sort_exchange(local: DeviceBlock, sort_key: SortKey, perm, skeys, n: int, send_counts, dev, group) -> DeviceBlock:

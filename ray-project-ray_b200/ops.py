@@ -342,8 +342,13 @@ def even_cuts(keys_sorted: torch.Tensor, descending: bool, parts: int) -> torch.
     return out
 
 
-def partition_targets(keys: torch.Tensor, descending: bool, splitter_codes: torch.Tensor):
-    """(target int32[n] = owner << 28 | slot, counts int64[16]) of a stable split of the rows by key range."""
+PT_TILE_ROWS = 2048   # rows per tile of b200x_partition_targets (csrc/exchange.cu PT_TILE)
+
+
+def partition_targets(keys: torch.Tensor, descending: bool, splitter_codes: torch.Tensor, want_tile_table: bool = False):
+    """(target int32[n] = owner << 28 | slot, counts int64[16]) of a stable split of the rows by key range.
+    want_tile_table: also the int32 [tiles, 16] table of slots handed out before every tile of PT_TILE_ROWS rows
+    (row t = rows per owner among the first t * PT_TILE_ROWS rows) - the library's scratch after the call."""
     dev = _require_cuda(keys, splitter_codes if splitter_codes.numel() else None)
     n = keys.numel()
     target = torch.empty(n, dtype=torch.int32, device=dev)
@@ -357,6 +362,9 @@ def partition_targets(keys: torch.Tensor, descending: bool, splitter_codes: torc
         temp = _temp(need, dev)
         nb = ctypes.c_size_t(temp.numel())
         _lib.call("b200x_partition_targets", *args, temp.data_ptr(), ctypes.byref(nb), st)
+    if want_tile_table:
+        tiles = (n + PT_TILE_ROWS - 1) // PT_TILE_ROWS
+        return target, counts, temp[: tiles * 64].view(torch.int32).reshape(tiles, 16)
     return target, counts
 
 
@@ -372,6 +380,38 @@ def scatter_rows_by_target(col: torch.Tensor, target: torch.Tensor, bases: Seque
     ro = (ctypes.c_ulonglong * w)(*[int(x) for x in row_offsets])
     with torch.cuda.device(dev):
         _lib.call("b200x_scatter_rows_by_target", col.data_ptr(), row_bytes, target.data_ptr(), n, b, ro, w, _stream(dev))
+
+
+def scatter_records_by_target(rec: torch.Tensor, target: torch.Tensor, bases: Sequence[int], row_offsets: Sequence[int],
+                              dst_pitch: int, copy_bytes: Optional[int] = None, src_offset: int = 0, row0: int = 0,
+                              nrows: Optional[int] = None) -> None:
+    """Bytes [src_offset, src_offset + copy_bytes) of rows [row0, row0 + nrows) of the record buffer `rec` ([n, pitch]
+    uint8) -> the start of row row_offsets[owner] + slot of the buffer at bases[owner] (rows dst_pitch apart)."""
+    dev = _require_cuda(rec, target)
+    n, pitch = rec.shape
+    nrows = n - row0 if nrows is None else nrows
+    copy_bytes = pitch if copy_bytes is None else copy_bytes
+    w = len(bases)
+    b = (ctypes.c_void_p * w)(*[int(x) for x in bases])
+    ro = (ctypes.c_ulonglong * w)(*[int(x) for x in row_offsets])
+    with torch.cuda.device(dev):
+        _lib.call("b200x_scatter_records_by_target", rec.data_ptr() + row0 * pitch + src_offset, pitch, copy_bytes,
+                  target.data_ptr() + 4 * row0, nrows, b, ro, dst_pitch, w, _stream(dev))
+
+
+def gather_records_prefixed(recv: torch.Tensor, idx: torch.Tensor, out: torch.Tensor, copy_bytes: int, used: int,
+                            sorted_keys: Optional[torch.Tensor] = None, prefix_be: bool = True, shift: int = 0,
+                            tie_mode: int = 0, ranges: Optional[Sequence[Tuple[int, int]]] = None) -> None:
+    """out[i] = [key prefix from sorted_keys[i] (shift == 8) | recv[idx[i], :copy_bytes]], zero from byte `used` on;
+    `ranges` / `tie_mode` restrict which positions are written (b200x_gather_records_prefixed)."""
+    dev = _require_cuda(recv, idx, out, sorted_keys)
+    n = idx.numel()
+    flat = [int(v) for r in (ranges or []) for v in r]
+    arr = (ctypes.c_uint32 * max(len(flat), 1))(*flat)
+    with torch.cuda.device(dev):
+        _lib.call("b200x_gather_records_prefixed", recv.data_ptr(), recv.shape[1], copy_bytes, idx.data_ptr(), n,
+                  _ptr(sorted_keys), int(prefix_be), shift, used, out.data_ptr(), out.shape[1], tie_mode, arr,
+                  len(flat) // 2, _stream(dev))
 
 
 def permute_rows(col: torch.Tensor, seed: int, inverse: bool = False) -> torch.Tensor:

@@ -76,7 +76,9 @@ def main():
     # gensort records in the record layout (the bench workload): [n, 10] byte key + [n, 90] payload, 128-byte records,
     # with and without the key prefix column; ties on the first 8 bytes and exact duplicates inside and across ranks
     shared = np.random.default_rng(5).integers(0, 256, (500, 10)).astype(np.uint8)      # the same keys on every rank
-    for m, prefix in ((300_000 + 777 * rank, ["key"]), (300_000 + 777 * rank, None), (90_000, ["key"])):
+    for m, prefix in ((300_000 + 777 * rank, ["key"]), (300_000 + 777 * rank, None), (90_000, ["key"]), (300_123, ["key"]), (0 if rank == 1 else 50_000, ["key"])):
+        # the fourth case sends the records in 4 chunks with overlapped gathers, the last one leaves rank 1 without rows
+        os.environ["B200X_EXCHANGE_CHUNK_MIN_ROWS"] = "1000" if m == 300_123 else str(1 << 22)
         bkey = rng.integers(0, 256, (m, 10)).astype(np.uint8)
         dst, src = rng.integers(0, m, m // 50), rng.integers(0, m, m // 50)
         bkey[dst, :8] = bkey[src, :8]

@@ -249,3 +249,56 @@ def test_key_prefix_column(cuda_device):
     sh = withp.random_shuffle(seed=4)
     assert not sh.get_internal_block_refs()[0].aux                # not maintained by shuffle: packed again on demand
     np.testing.assert_array_equal(sh.sort("key").to_numpy()["key"], key[orc.stable_argsort_bytes(key, False)])
+
+
+@pytest.mark.parametrize("n,world", [(5000, 2), (300_001, 8)])
+def test_record_exchange_kernels_with_local_peers(n, world, cuda_device):
+    """b200x_scatter_records_by_target + b200x_gather_records_prefixed on one GPU, the 'peers' being local buffers:
+    gensort records leave without their first 8 bytes (the key prefix, exchanged as a column) and without padding,
+    in chunks of rows; the receiver puts the prefix back from the sorted keys while gathering into sorted order."""
+    key, payload = _gensort(n, n, dup_hi=n // 20, dup_full=n // 50)
+    blk = DeviceBlock.from_numpy({"key": key, "payload": payload}, cuda_device).to_records(key_prefix=["key"])
+    rec = record_groups(blk)[0][0].rec
+    hi = blk.aux["key::be0"]
+    hi_np = key[:, :8].copy().view(">u8").astype(np.uint64).ravel()
+    split = np.sort(np.random.default_rng(1).integers(0, 2 ** 63, world - 1).astype(np.uint64) * np.uint64(2))
+    owner = np.searchsorted(split, hi_np, side="right")
+    target, counts = ops.partition_targets(hi, False, torch.from_numpy(split.view(np.int64)).to(cuda_device))
+    cnt = np.bincount(owner, minlength=world)
+    np.testing.assert_array_equal(counts.cpu().numpy()[:world], cnt)
+    bufs = [torch.full((int(cnt[d]) + 3, 128), 7, dtype=torch.uint8, device=cuda_device) for d in range(world)]
+    kbufs = [torch.zeros(int(cnt[d]) + 3, dtype=torch.int64, device=cuda_device) for d in range(world)]
+    ops.scatter_rows_by_target(hi, target, [b.data_ptr() for b in kbufs], [3] * world)
+    cuts = [0, n // 3 // 2048 * 2048, n // 2, n]           # three chunks of rows, sent one after the other
+    for lo, hi_row in zip(cuts[:-1], cuts[1:]):
+        ops.scatter_records_by_target(rec, target, [b.data_ptr() for b in bufs], [3] * world, 128, copy_bytes=96,
+                                      src_offset=8, row0=lo, nrows=hi_row - lo)
+    full = np.zeros((n, 128), dtype=np.uint8)
+    full[:, :10], full[:, 10:100] = key, payload
+    for d in range(world):
+        got = bufs[d].cpu().numpy()
+        mine = full[owner == d]
+        np.testing.assert_array_equal(got[3:, :96], mine[:, 8:104])
+        assert (got[:, 96:] == 7).all() and (got[:3] == 7).all()       # nothing outside the 96 bytes of a slot
+        # receiver d: sort the exchanged prefixes, repair ties from the key bytes in the rows, gather + re-insert
+        m = int(cnt[d])
+        if m < 2:
+            continue
+        recv, rkeys = bufs[d][3:], kbufs[d][3:].view(torch.uint64)
+        perm, _, skeys = ops.argsort(rkeys, False, want_keys=True)
+        out = torch.full((m, 128), 9, dtype=torch.uint8, device=cuda_device)
+        half = m // 2
+        ops.gather_records_prefixed(recv, perm, out, 96, 100, skeys, True, 8, tie_mode=1, ranges=[(0, half)])
+        ops.gather_records_prefixed(recv, perm, out, 96, 100, skeys, True, 8, tie_mode=1, ranges=[(half, half + 5), (half + 5, m)])
+        ops.fix_ties(skeys, perm, [ops.KeyPiece(recv[:, 0:2], 0, 2)], False)      # key bytes 8..9 lie at bytes 0..1 of a row
+        ops.gather_records_prefixed(recv, perm, out, 96, 100, skeys, True, 8, tie_mode=2)
+        want = mine[orc.stable_argsort_bytes(mine[:, :10], False)]
+        np.testing.assert_array_equal(out.cpu().numpy(), want)
+    # shift 0 (whole rows, no prefix), all positions, record pitch that is not a power of two
+    src = torch.from_numpy(np.random.default_rng(3).integers(0, 256, (1000, 48)).astype(np.uint8)).to(cuda_device)
+    idx = torch.from_numpy(np.random.default_rng(4).permutation(1000).astype(np.int32)).to(cuda_device)
+    out = torch.full((1000, 48), 9, dtype=torch.uint8, device=cuda_device)
+    ops.gather_records_prefixed(src, idx, out, 48, 40)
+    want = src.cpu().numpy()[idx.cpu().numpy()].copy()
+    want[:, 40:] = 0
+    np.testing.assert_array_equal(out.cpu().numpy(), want)
