@@ -304,6 +304,31 @@ int b200x_segmented_reduce(const uint32_t* group_starts, const uint32_t* num_gro
                            const double* addend, void* sum_out, void* min_out, void* max_out, void* temp,
                            size_t* temp_bytes, void* stream);
 
+/* Dense-range aggregation: grouping by an integer key column whose order-preserving codes span a small range needs
+ * no sort - the group of a row is code - min(code), and the non-empty entries of a table indexed by that number,
+ * read in index order, are the groups in ascending key order (ids, categories, dates; BASELINE configs[2]).
+ * Integer sums / counts / minima / maxima do not depend on the order of the additions, so the result equals the
+ * sorted path's bit for bit; float columns stay on the sorted path (fixed reduction order).
+ *   b200x_key_code_range: range_out[0] = smallest, range_out[1] = largest code of the column (device, 2 x uint64).
+ *   b200x_dense_group_accumulate: for every row r: g = code(keys[r]) - base_code (< range): count_tab[g] += 1,
+ *     sum_tab[g] += values[r] (int64 wrap-around), min_tab / max_tab[g] = min / max(.., values[r]); table pointers
+ *     that are NULL are skipped, values (int64) may be NULL when only counts are wanted; init != 0 first sets the
+ *     given tables to 0 / 0 / INT64_MAX / INT64_MIN. Heavy keys are combined per tile in shared memory first.
+ *   b200x_dense_group_compact: the entries with count_tab[g] != 0 in index order: keys_out[j] = the key (decoded
+ *     to key_type), count_out[j] (may be NULL), tabs_out_host[t][j] = tabs_host[t][g] for num_tabs (<= 8) int64
+ *     tables (HOST arrays of device pointers); *num_groups_out (device) = how many. Outputs need room for
+ *     min(range, n) entries. Two-phase temp query as elsewhere.
+ * Replaces the same arithmetic as b200x_segmented_reduce + b200x_group_counts + the key sort in front of them
+ * (_internal/arrow_block.py:466-548, :569-680; aggregate/_aggregate.py:90-241). */
+int b200x_key_code_range(const void* keys, int key_type, size_t n, uint64_t* range_out, void* stream);
+int b200x_dense_group_accumulate(const void* keys, int key_type, size_t n, uint64_t base_code, size_t range,
+                                 const int64_t* values, int init, int64_t* count_tab, int64_t* sum_tab, int64_t* min_tab,
+                                 int64_t* max_tab, void* stream);
+int b200x_dense_group_compact(uint64_t base_code, size_t range, int key_type, const int64_t* count_tab, int num_tabs,
+                              const int64_t* const* tabs_host, void* keys_out, int64_t* count_out,
+                              int64_t* const* tabs_out_host, uint32_t* num_groups_out, void* temp, size_t* temp_bytes,
+                              void* stream);
+
 /* counts_out[g] = rows in group g (int64), g < *num_groups; max_groups bounds the launch.
  * Replaces Count's accumulate_block (num_rows of the group slice): aggregate/_aggregate.py:90-102. */
 int b200x_group_counts(const uint32_t* group_starts, const uint32_t* num_groups, size_t max_groups, size_t n,

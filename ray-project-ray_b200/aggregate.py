@@ -23,7 +23,7 @@ always true in the reference's null wrappers, _internal/null_aggregate.py:28-250
 """
 from __future__ import annotations
 
-from typing import Callable, Dict, List, Optional, Sequence
+from typing import Callable, Dict, List, Optional, Sequence, Tuple
 
 import torch
 
@@ -409,3 +409,73 @@ def _global_reduce(col: torch.Tensor, want: str, center: Optional[float] = None)
     s, mn, mx = ops.segmented_reduce(starts, ng, 1, None, col, n, want_sum=want == "sum", want_min=want == "min",
                                      want_max=want == "max")
     return {"sum": s, "min": mn, "max": mx}[want].item()
+
+
+# ------------------------------------------------------------------ dense-range fast path
+DENSE_MAX_RANGE = 1 << 22      # table entries: count + one to three int64 tables of this length stay inside the 126 MB L2
+DENSE_MIN_ROWS = 1 << 16
+_DENSE_KINDS = ("count", "sum", "min", "max", "mean", "absmax")
+
+
+def dense_aggregate(block: DeviceBlock, key, aggs: Sequence[AggregateFn], finalize: bool) -> Optional[DeviceBlock]:
+    """groupby(key).aggregate(aggs) without a sort, or None when it does not apply: one integer key column whose
+    codes span at most DENSE_MAX_RANGE values (ids, categories, dates), and only Count / Sum / Min / Max / Mean /
+    AbsMax over int64 columns - order-independent integer arithmetic, so the rows can be added straight into
+    accumulator tables indexed by `key - min(key)` (csrc/groupby.cu, "Dense-range aggregation") and the result is
+    bit-identical to the sorted path. Costs one read of the key column to find its range (and the decision)."""
+    if not isinstance(key, str) or block.num_rows < DENSE_MIN_ROWS:
+        return None
+    kcol = block.columns[key]
+    if kcol.dim() != 1 or kcol.dtype.is_floating_point or kcol.dtype not in ops._KEY_TYPES:
+        return None
+    kinds = []
+    for agg in aggs:
+        kind = getattr(agg, "_device_kind", None)
+        if kind not in _DENSE_KINDS:
+            return None
+        if kind != "count":
+            v = block.columns.get(agg._key_fn)
+            if v is None or v.dim() != 1 or v.dtype != torch.int64:
+                return None
+        kinds.append(kind)
+    kcol = _contig(kcol)
+    lo, hi = ops.key_code_range(kcol)
+    rng = hi - lo + 1
+    if rng > DENSE_MAX_RANGE or rng > 4 * block.num_rows:
+        return None
+    dev = block.device
+    count = torch.empty(rng, dtype=torch.int64, device=dev)
+    need: Dict[str, set] = {}
+    for agg, kind in zip(aggs, kinds):
+        if kind != "count":
+            need.setdefault(agg._key_fn, set()).update({"sum": {"sum"}, "mean": {"sum"}, "min": {"min"}, "max": {"max"},
+                                                        "absmax": {"min", "max"}}[kind])
+    tabs: Dict[Tuple[str, str], torch.Tensor] = {}
+    first = True
+    for on, wants in need.items():
+        s_, mn, mx = ops.dense_group_accumulate(kcol, lo, rng, _contig(block.columns[on]), count if first else None,
+                                                "sum" in wants, "min" in wants, "max" in wants)
+        first = False
+        for what, t in (("sum", s_), ("min", mn), ("max", mx)):
+            if t is not None:
+                tabs[(on, what)] = t
+    if first:   # only counts were asked for
+        ops.dense_group_accumulate(kcol, lo, rng, None, count, False, False, False)
+    order = list(tabs)
+    keys_out, count_out, outs, G = ops.dense_group_compact(lo, rng, kcol.dtype, count, [tabs[k] for k in order],
+                                                           min(rng, block.num_rows))
+    got = dict(zip(order, outs))
+    cols: Dict[str, torch.Tensor] = {key: keys_out}
+    for agg, kind, name in zip(aggs, kinds, resolved_names(aggs)):
+        on = agg._key_fn
+        if kind == "count":
+            cols[name] = count_out
+        elif kind in ("sum", "min", "max"):
+            cols[name] = got[(on, kind)]
+        elif kind == "absmax":
+            cols[name] = ops.absmax_groups(got[(on, "min")], got[(on, "max")])
+        elif finalize:   # mean
+            cols[name] = ops.finalize_groups(got[(on, "sum")], count_out, 0)
+        else:
+            cols[name], cols[name + SEP + "count"] = got[(on, "sum")], count_out
+    return DeviceBlock(cols, num_rows=G, device=dev)

@@ -148,81 +148,30 @@ __device__ __forceinline__ unsigned match4(uint32_t d) {
   return peers;
 }
 
-// pass 1: rows per owner in each tile
-__global__ void __launch_bounds__(PT_THREADS)
-pt_count_kernel(const void* __restrict__ keys, int kt, int desc, uint64_t n, const uint64_t* __restrict__ split, int nsplit,
-                uint32_t* __restrict__ tile_counts /*[tiles][MAX_PEERS]*/) {
-  __shared__ uint64_t s_split[MAX_PEERS];
-  __shared__ uint32_t s_cnt[MAX_PEERS];
-  if (threadIdx.x < MAX_PEERS) {
-    s_split[threadIdx.x] = threadIdx.x < (unsigned)nsplit ? split[threadIdx.x] : ~0ull;
-    s_cnt[threadIdx.x] = 0;
-  }
-  __syncthreads();
-  const uint64_t base = (uint64_t)blockIdx.x * PT_TILE;
-  const unsigned lane = threadIdx.x & 31;
-  const int width = key_type_bytes(kt);
-  uint64_t raw[PT_IPT];
-#pragma unroll
-  for (int j = 0; j < PT_IPT; ++j) {  // all loads first, so that they overlap
-    const uint64_t r = base + (uint64_t)j * PT_THREADS + threadIdx.x;
-    raw[j] = r < n ? load_raw_bits(keys, r, width) : 0ull;
-  }
-#pragma unroll
-  for (int j = 0; j < PT_IPT; ++j) {
-    const uint64_t r = base + (uint64_t)j * PT_THREADS + threadIdx.x;
-    const uint32_t d = r < n ? owner_of(encode_bits(raw[j], kt, desc != 0), s_split, nsplit) : (uint32_t)(MAX_PEERS - 1);
-    const unsigned act = __ballot_sync(0xffffffffu, r < n);
-    const unsigned peers = match4(d) & act;
-    if (r < n && (int)lane == __ffs(peers) - 1) atomicAdd(&s_cnt[d], (uint32_t)__popc(peers));
-  }
-  __syncthreads();
-  if (threadIdx.x < MAX_PEERS) tile_counts[(size_t)blockIdx.x * MAX_PEERS + threadIdx.x] = s_cnt[threadIdx.x];
-}
+// One pass over the keys (decoupled look-back over tiles, as in the radix passes): every tile counts its rows per
+// owner, publishes the counts, adds up what the tiles before it published and writes its rows' targets. Tiles are
+// handed out in launch order (ticket counter), so a tile only ever waits on tiles that are already running.
+// Rows are warp-striped (item j of lane l of warp w = tile row w*256 + j*32 + l), so that slots follow row order.
+// tile_base[tile][owner] (the slots handed out before the tile) stays behind for the caller.
+constexpr uint32_t PT_FLAG_AGG = 1u << 30, PT_FLAG_INCL = 2u << 30, PT_VALUE_MASK = (1u << 30) - 1u;
 
-// pass 2 (one block per owner): exclusive scan of that owner's tile counts over tiles; total -> counts_out
-__global__ void __launch_bounds__(1024)
-pt_scan_kernel(uint32_t* __restrict__ tile_counts, uint32_t tiles, unsigned long long* __restrict__ counts_out) {
-  __shared__ uint32_t s_warp[32];
-  const int d = blockIdx.x;
-  const unsigned lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const uint32_t per = (tiles + 1023) / 1024;
-  const uint32_t lo = min(tiles, threadIdx.x * per), hi = min(tiles, lo + per);
-  uint32_t sum = 0;
-#pragma unroll 4
-  for (uint32_t t = lo; t < hi; ++t) sum += tile_counts[(size_t)t * MAX_PEERS + d];
-  uint32_t x = sum;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
-    if (lane >= (unsigned)o) x += y;
-  }
-  if (lane == 31) s_warp[w] = x;
-  __syncthreads();
-  uint32_t off = 0;
-  for (unsigned k = 0; k < w; ++k) off += s_warp[k];
-  uint32_t run = off + x - sum;
-  for (uint32_t t = lo; t < hi; ++t) {
-    const uint32_t c = tile_counts[(size_t)t * MAX_PEERS + d];
-    tile_counts[(size_t)t * MAX_PEERS + d] = run;
-    run += c;
-  }
-  if (threadIdx.x == 1023) counts_out[d] = off + x;
-}
-
-// pass 3: every row's target = owner << 28 | slot. Warp-striped rows (item j of lane l of warp w =
-// tile row w*256 + j*32 + l), so that ranks follow row order.
 __global__ void __launch_bounds__(PT_THREADS)
-pt_target_kernel(const void* __restrict__ keys, int kt, int desc, uint64_t n, const uint64_t* __restrict__ split, int nsplit,
-                 const uint32_t* __restrict__ tile_base /*[tiles][MAX_PEERS]*/, uint32_t* __restrict__ target) {
+pt_fused_kernel(const void* __restrict__ keys, int kt, int desc, uint64_t n, const uint64_t* __restrict__ split, int nsplit,
+                uint32_t* __restrict__ tile_base /*[tiles][MAX_PEERS]*/, uint32_t* __restrict__ lookback /*[tiles][MAX_PEERS]*/,
+                uint32_t* __restrict__ ticket, uint32_t tiles, uint32_t* __restrict__ target,
+                unsigned long long* __restrict__ counts_out) {
   __shared__ uint64_t s_split[MAX_PEERS];
   __shared__ uint32_t s_wcnt[PT_WARPS][MAX_PEERS];
+  __shared__ uint32_t s_tile;
+  if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
   if (threadIdx.x < MAX_PEERS) s_split[threadIdx.x] = threadIdx.x < (unsigned)nsplit ? split[threadIdx.x] : ~0ull;
   if (threadIdx.x < PT_WARPS * MAX_PEERS) (&s_wcnt[0][0])[threadIdx.x] = 0;
   __syncthreads();
+  const uint32_t tile = s_tile;
+  if (tile >= tiles) return;
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned lt = lanemask_lt();
-  const uint64_t base = (uint64_t)blockIdx.x * PT_TILE + (uint64_t)warp * 32 * PT_IPT + lane;
+  const uint64_t base = (uint64_t)tile * PT_TILE + (uint64_t)warp * 32 * PT_IPT + lane;
   uint32_t dest[PT_IPT], rank[PT_IPT];
   const int width = key_type_bytes(kt);
   uint64_t raw[PT_IPT];
@@ -249,14 +198,36 @@ pt_target_kernel(const void* __restrict__ keys, int kt, int desc, uint64_t n, co
     __syncwarp();
   }
   __syncthreads();
-  // exclusive scan over warps per owner, plus the tile's base slot
+  // one thread per owner: scan over the warps, publish the tile's count, look back, publish the inclusive count
   if (threadIdx.x < MAX_PEERS) {
-    uint32_t run = tile_base[(size_t)blockIdx.x * MAX_PEERS + threadIdx.x];
+    const unsigned d = threadIdx.x;
+    uint32_t run = 0;
     for (int w = 0; w < PT_WARPS; ++w) {
-      const uint32_t c = s_wcnt[w][threadIdx.x];
-      s_wcnt[w][threadIdx.x] = run;
+      const uint32_t c = s_wcnt[w][d];
+      s_wcnt[w][d] = run;
       run += c;
     }
+    volatile uint32_t* lb = lookback + (size_t)tile * MAX_PEERS + d;
+    *lb = (tile == 0 ? PT_FLAG_INCL : PT_FLAG_AGG) | run;
+    uint32_t excl = 0;
+    if (tile > 0) {
+      int64_t t = (int64_t)tile - 1;
+      while (true) {
+        volatile uint32_t* p = lookback + (size_t)t * MAX_PEERS + d;
+        uint32_t v = *p;
+        while ((v & ~PT_VALUE_MASK) == 0) {
+          __nanosleep(20);
+          v = *p;
+        }
+        excl += v & PT_VALUE_MASK;
+        if (v & PT_FLAG_INCL) break;
+        --t;
+      }
+      *lb = PT_FLAG_INCL | (excl + run);
+    }
+    tile_base[(size_t)tile * MAX_PEERS + d] = excl;
+    if (tile == tiles - 1) counts_out[d] = (unsigned long long)excl + run;
+    for (int w = 0; w < PT_WARPS; ++w) s_wcnt[w][d] += excl;
   }
   __syncthreads();
 #pragma unroll
@@ -566,7 +537,8 @@ extern "C" int b200x_partition_targets(const void* keys, int key_type, int desce
     return B200X_ERR_TOO_LARGE;
   }
   const uint32_t tiles = (uint32_t)((n + PT_TILE - 1) / PT_TILE);
-  const size_t need = align_up((size_t)(tiles + 1) * MAX_PEERS * sizeof(uint32_t), 256);
+  const size_t table_bytes = align_up((size_t)(tiles + 1) * MAX_PEERS * sizeof(uint32_t), 256);
+  const size_t need = 2 * table_bytes + 256;   // tile_base | look-back words | ticket
   if (temp == nullptr) {
     *temp_bytes = need;
     return B200X_OK;
@@ -587,15 +559,13 @@ extern "C" int b200x_partition_targets(const void* keys, int key_type, int desce
     set_error("b200x_partition_targets: NULL pointer");
     return B200X_ERR_ARG;
   }
-  uint32_t* tile_counts = (uint32_t*)temp;
-  pt_count_kernel<<<tiles, PT_THREADS, 0, stream>>>(keys, key_type, descending, n, splitter_codes, num_splitters,
-                                                    tile_counts);
-  B200X_LAUNCH_CHECK("pt_count_kernel");
-  pt_scan_kernel<<<MAX_PEERS, 1024, 0, stream>>>(tile_counts, tiles, counts_out);
-  B200X_LAUNCH_CHECK("pt_scan_kernel");
-  pt_target_kernel<<<tiles, PT_THREADS, 0, stream>>>(keys, key_type, descending, n, splitter_codes, num_splitters,
-                                                     tile_counts, target_out);
-  B200X_LAUNCH_CHECK("pt_target_kernel");
+  uint32_t* tile_base = (uint32_t*)temp;
+  uint32_t* lookback = (uint32_t*)((unsigned char*)temp + table_bytes);
+  uint32_t* ticket = (uint32_t*)((unsigned char*)temp + 2 * table_bytes);
+  B200X_CUDA(cudaMemsetAsync(lookback, 0, table_bytes + 256, stream));   // look-back flags and the ticket start at zero
+  pt_fused_kernel<<<tiles, PT_THREADS, 0, stream>>>(keys, key_type, descending, n, splitter_codes, num_splitters, tile_base,
+                                                    lookback, ticket, tiles, target_out, counts_out);
+  B200X_LAUNCH_CHECK("pt_fused_kernel");
   return B200X_OK;
 }
 
@@ -785,60 +755,79 @@ __device__ __forceinline__ uint64_t keep_below(uint64_t w, uint32_t pos0, uint32
 }
 
 // tie_mode 0: every position; 1: skip positions whose key equals a neighbour's; 2: only those positions.
-// dv_shift >= 0: dst_vec == 1 << dv_shift (the usual case: 128-byte records), else a division per element.
+// A warp takes 32 consecutive output rows: each lane decides for ONE of them (slot in range? tied?) - so the
+// index, the range test and the neighbour comparison cost one evaluation per row, not one per 16-byte piece -
+// then groups of lanes_per_row lanes copy the selected rows, slot and key being broadcast with shuffles.
 __global__ void __launch_bounds__(256)
 gather_records_prefixed_kernel(const unsigned char* __restrict__ recv, uint64_t recv_pitch, uint32_t copy_bytes,
                                const uint32_t* __restrict__ idx, uint64_t n, const uint64_t* __restrict__ keys, int prefix_be,
-                               uint32_t shift, uint32_t used, unsigned char* __restrict__ dst, uint32_t dst_vec, int dv_shift,
-                               int tie_mode, const SlotRanges sr) {
-  constexpr int U = 4;
-  const uint64_t total = n * dst_vec;
-  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-  for (uint64_t t0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; t0 < total; t0 += U * stride) {
-    uint64_t w0[U], w1[U];
-    bool go[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const uint64_t t = t0 + u * stride;
-      go[u] = t < total;
-      w0[u] = w1[u] = 0;
-      if (!go[u]) continue;
-      const uint64_t i = dv_shift >= 0 ? (t >> dv_shift) : (t / dst_vec);
-      const uint32_t j = (uint32_t)(t - i * dst_vec);
-      const uint32_t s = idx[i];
+                               uint32_t shift, uint32_t used, unsigned char* __restrict__ dst, uint32_t dst_vec,
+                               uint32_t lanes_per_row, int tie_mode, const SlotRanges sr) {
+  const unsigned lane = threadIdx.x & 31;
+  const uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  const uint32_t groups = 32 / lanes_per_row;        // rows copied at once by one warp
+  const uint32_t g = lane / lanes_per_row, c0 = lane % lanes_per_row;
+  const bool need_key = keys != nullptr && (tie_mode != 0 || shift == 8u);
+  for (uint64_t r0 = warp * 32; r0 < n; r0 += nwarps * 32) {
+    const uint64_t i = r0 + lane;
+    bool go = i < n;
+    uint32_t s = 0;
+    uint64_t key = 0;
+    if (go) {
+      s = idx[i];
       if (sr.n > 0) {
         bool in = false;
 #pragma unroll
         for (int k = 0; k < GR_MAX_RANGES; ++k) in |= (k < sr.n) && s >= sr.lo[k] && s < sr.hi[k];
-        go[u] = in;
+        go = in;
       }
-      uint64_t key = 0;
-      if (keys != nullptr && go[u] && (tie_mode != 0 || (shift == 8u && j == 0))) {
-        key = keys[i];
-        if (tie_mode != 0) {
-          const bool tied = (i > 0 && keys[i - 1] == key) || (i + 1 < n && keys[i + 1] == key);
-          go[u] = tied == (tie_mode == 2);
-        }
-      }
-      if (!go[u]) continue;
-      const unsigned char* row = recv + (uint64_t)s * recv_pitch;
-      // output bytes [16j, 16j+16) = received bytes [16j - shift, 16j - shift + 16); shift is 0 or 8
-      const uint32_t o0 = 16u * j, o1 = o0 + 8u;
-      if (o0 >= shift && o0 - shift + 8u <= copy_bytes) w0[u] = *reinterpret_cast<const uint64_t*>(row + (o0 - shift));
-      if (o1 >= shift && o1 - shift + 8u <= copy_bytes) w1[u] = *reinterpret_cast<const uint64_t*>(row + (o1 - shift));
-      if (shift == 8u && j == 0) w0[u] = prefix_be ? bswap64(key) : key;
-      w0[u] = keep_below(w0[u], o0, used);
-      w1[u] = keep_below(w1[u], o1, used);
     }
+    if (need_key && i < n) key = keys[i];
+    if (tie_mode != 0) {
+      uint64_t prev = __shfl_up_sync(0xffffffffu, key, 1), next = __shfl_down_sync(0xffffffffu, key, 1);
+      if (lane == 0 && i > 0 && i < n) prev = keys[i - 1];
+      if ((lane == 31 || i + 1 >= n) && i + 1 < n) next = keys[i + 1];
+      const bool tied = i < n && ((i > 0 && prev == key) || (i + 1 < n && next == key));
+      go = go && (tied == (tie_mode == 2));
+    }
+    const unsigned any = __ballot_sync(0xffffffffu, go);
+    if (any == 0) continue;
+    constexpr int U = 4;                                // rows in flight per lane group
+    for (uint32_t b = 0; b < 32; b += U * groups) {
+      for (uint32_t j = c0; j < dst_vec; j += lanes_per_row) {
+        // output bytes [16j, 16j+16) = received bytes [16j - shift, 16j - shift + 16); shift is 0 or 8
+        const uint32_t o0 = 16u * j, o1 = o0 + 8u;
+        const bool ld0 = o0 >= shift && o0 - shift + 8u <= copy_bytes, ld1 = o1 >= shift && o1 - shift + 8u <= copy_bytes;
+        uint64_t w0[U], w1[U];
+        bool act[U];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      if (go[u]) {
-        uint4 v;
-        v.x = (uint32_t)w0[u];
-        v.y = (uint32_t)(w0[u] >> 32);
-        v.z = (uint32_t)w1[u];
-        v.w = (uint32_t)(w1[u] >> 32);
-        reinterpret_cast<uint4*>(dst)[t0 + u * stride] = v;
+        for (int u = 0; u < U; ++u) {
+          const uint32_t ri = b + u * groups + g;       // row of this lane group within the warp's 32
+          const uint32_t srow = __shfl_sync(0xffffffffu, s, ri & 31u);
+          const uint64_t krow = __shfl_sync(0xffffffffu, key, ri & 31u);
+          act[u] = ri < 32u && ((any >> ri) & 1u);
+          w0[u] = w1[u] = 0;
+          if (act[u]) {
+            const unsigned char* row = recv + (uint64_t)srow * recv_pitch;
+            if (ld0) w0[u] = *reinterpret_cast<const uint64_t*>(row + (o0 - shift));
+            if (ld1) w1[u] = *reinterpret_cast<const uint64_t*>(row + (o1 - shift));
+            if (shift == 8u && j == 0) w0[u] = prefix_be ? bswap64(krow) : krow;
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          if (act[u]) {
+            const uint32_t ri = b + u * groups + g;
+            const uint64_t a0 = keep_below(w0[u], o0, used), a1 = keep_below(w1[u], o1, used);
+            uint4 v;
+            v.x = (uint32_t)a0;
+            v.y = (uint32_t)(a0 >> 32);
+            v.z = (uint32_t)a1;
+            v.w = (uint32_t)(a1 >> 32);
+            (reinterpret_cast<uint4*>(dst) + (r0 + ri) * dst_vec)[j] = v;
+          }
+        }
       }
     }
   }
@@ -922,16 +911,15 @@ extern "C" int b200x_gather_records_prefixed(const void* recv, size_t recv_pitch
     sr.hi[k] = k < num_ranges ? slot_ranges_host[2 * k + 1] : 0u;
   }
   const uint32_t dst_vec = (uint32_t)(dst_pitch / 16);
-  int dv_shift = -1;
-  for (int b = 0; b < 16; ++b)
-    if (dst_vec == (1u << b)) dv_shift = b;
-  uint64_t blocks = (((uint64_t)n * dst_vec + 3) / 4 + 255) / 256;
+  uint32_t lpr = 1;
+  while (lpr < dst_vec && lpr < 32) lpr <<= 1;
+  uint64_t blocks = ((uint64_t)n * lpr + 255) / 256;
   const uint64_t cap = (uint64_t)sm_count() * 16;
   if (blocks > cap) blocks = cap;
   prof_begin(stream, PROF_GATHER);
   gather_records_prefixed_kernel<<<(uint32_t)blocks, 256, 0, stream>>>(
       (const unsigned char*)recv, recv_pitch, (uint32_t)copy_bytes, idx, n, sorted_keys, prefix_be, (uint32_t)shift,
-      (uint32_t)used_bytes, (unsigned char*)dst, dst_vec, dv_shift, tie_mode, sr);
+      (uint32_t)used_bytes, (unsigned char*)dst, dst_vec, lpr, tie_mode, sr);
   prof_end(stream);
   B200X_LAUNCH_CHECK("gather_records_prefixed_kernel");
   return B200X_OK;

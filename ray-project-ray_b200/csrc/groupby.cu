@@ -449,6 +449,240 @@ group_quantile_kernel(const uint32_t* __restrict__ group_starts, const uint32_t*
   }
 }
 
+// ascending code -> value of the integer key column it came from
+__device__ __forceinline__ void store_decoded_key(void* out, size_t i, uint64_t code, int kt) {
+  switch (kt) {
+    case KEY_I64: ((uint64_t*)out)[i] = code ^ 0x8000000000000000ull; break;
+    case KEY_U64: ((uint64_t*)out)[i] = code; break;
+    case KEY_I32: ((uint32_t*)out)[i] = (uint32_t)code ^ 0x80000000u; break;
+    case KEY_U32: ((uint32_t*)out)[i] = (uint32_t)code; break;
+    case KEY_I16: ((uint16_t*)out)[i] = (uint16_t)((uint16_t)code ^ 0x8000u); break;
+    case KEY_U16: ((uint16_t*)out)[i] = (uint16_t)code; break;
+    case KEY_I8: ((uint8_t*)out)[i] = (uint8_t)((uint8_t)code ^ 0x80u); break;
+    default: ((uint8_t*)out)[i] = (uint8_t)code; break;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Dense-range aggregation: integer keys whose codes span a small range
+// ---------------------------------------------------------------------------
+// When max(code) - min(code) is small (ids, categories, dates: BASELINE configs[2] groups 200 M rows by 1 M
+// distinct int64 keys) the group of a row is simply code - min: no sort is needed to bring equal keys together.
+// Every row adds its value to accumulator tables indexed by that number (count, and per value column sum / min /
+// max as int64); the non-empty entries, read in index order, ARE the groups in ascending key order. Integer
+// sums, counts, minima and maxima do not depend on the order of the additions, so the result is bit-identical
+// to the sorted path; float columns keep the sorted path (a fixed reduction order is what makes them
+// reproducible). Heavy keys (Zipf) would serialise on one table entry: a block first combines the rows of one
+// tile (DG_TILE rows) in a shared-memory hash table that is emptied after every tile, so that a key costs one
+// global atomic per tile it occurs in, however often it occurs there.
+constexpr int DG_THREADS = 256;
+constexpr int DG_IPT = 4;
+constexpr int DG_TILE = DG_THREADS * DG_IPT;
+constexpr int DG_SLOTS = 2048;  // power of two, 2x the tile
+
+__global__ void __launch_bounds__(256)
+key_code_range_kernel(const void* __restrict__ keys, int kt, uint64_t n, unsigned long long* __restrict__ out) {
+  unsigned long long mn = ~0ull, mx = 0ull;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const unsigned long long c = load_encode(keys, i, kt, false);
+    mn = c < mn ? c : mn;
+    mx = c > mx ? c : mx;
+  }
+#pragma unroll
+  for (int d = 16; d >= 1; d >>= 1) {
+    const unsigned long long a = __shfl_xor_sync(0xffffffffu, mn, d), b = __shfl_xor_sync(0xffffffffu, mx, d);
+    mn = a < mn ? a : mn;
+    mx = b > mx ? b : mx;
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicMin(&out[0], mn);
+    atomicMax(&out[1], mx);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+dense_init_kernel(uint64_t range, long long* cnt, long long* sum, long long* mn, long long* mx) {
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < range; i += (uint64_t)gridDim.x * blockDim.x) {
+    if (cnt) cnt[i] = 0;
+    if (sum) sum[i] = 0;
+    if (mn) mn[i] = INT64_MAX;
+    if (mx) mx[i] = INT64_MIN;
+  }
+}
+
+__global__ void __launch_bounds__(DG_THREADS)
+dense_accumulate_kernel(const void* __restrict__ keys, int kt, uint64_t n, uint64_t base, uint32_t range,
+                        const long long* __restrict__ values, long long* __restrict__ g_cnt, long long* __restrict__ g_sum,
+                        long long* __restrict__ g_mn, long long* __restrict__ g_mx) {
+  extern __shared__ __align__(16) unsigned char dg_raw[];
+  uint32_t* s_tag = reinterpret_cast<uint32_t*>(dg_raw);                 // group number + 1, 0 = free
+  uint32_t* s_cnt = s_tag + DG_SLOTS;
+  long long* s_sum = reinterpret_cast<long long*>(s_cnt + DG_SLOTS);     // only the arrays that are used exist
+  long long* s_mn = s_sum + (g_sum ? DG_SLOTS : 0);
+  long long* s_mx = s_mn + (g_mn ? DG_SLOTS : 0);
+  for (int i = threadIdx.x; i < DG_SLOTS; i += DG_THREADS) {
+    s_tag[i] = 0;
+    s_cnt[i] = 0;
+    if (g_sum) s_sum[i] = 0;
+    if (g_mn) s_mn[i] = INT64_MAX;
+    if (g_mx) s_mx[i] = INT64_MIN;
+  }
+  __syncthreads();
+  const uint64_t tiles = (n + DG_TILE - 1) / DG_TILE;
+  for (uint64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+    const uint64_t r0 = tile * DG_TILE + threadIdx.x;
+    unsigned long long code[DG_IPT];
+    long long v[DG_IPT];
+#pragma unroll
+    for (int j = 0; j < DG_IPT; ++j) {
+      const uint64_t r = r0 + (uint64_t)j * DG_THREADS;
+      code[j] = r < n ? load_encode(keys, r, kt, false) : 0ull;
+      v[j] = (values != nullptr && r < n) ? values[r] : 0ll;
+    }
+#pragma unroll
+    for (int j = 0; j < DG_IPT; ++j) {
+      const uint64_t r = r0 + (uint64_t)j * DG_THREADS;
+      if (r >= n) continue;
+      const uint32_t gidx = (uint32_t)(code[j] - base);
+      if (gidx >= range) continue;                       // cannot happen when base / range come from the column itself
+      uint32_t slot = (gidx * 2654435761u) >> 21;        // 11 bits
+      bool placed = false;
+#pragma unroll
+      for (int probe = 0; probe < 2 && !placed; ++probe) {
+        uint32_t t = s_tag[slot];
+        if (t == 0) t = atomicCAS(&s_tag[slot], 0u, gidx + 1u);
+        if (t == 0 || t == gidx + 1u) {
+          atomicAdd(&s_cnt[slot], 1u);
+          if (g_sum) atomicAdd(reinterpret_cast<unsigned long long*>(&s_sum[slot]), (unsigned long long)v[j]);
+          if (g_mn) atomicMin(&s_mn[slot], v[j]);
+          if (g_mx) atomicMax(&s_mx[slot], v[j]);
+          placed = true;
+        }
+        slot = (slot + 1) & (DG_SLOTS - 1);
+      }
+      if (!placed) {                                     // both slots taken by other keys of this tile
+        if (g_cnt) atomicAdd(reinterpret_cast<unsigned long long*>(&g_cnt[gidx]), 1ull);
+        if (g_sum) atomicAdd(reinterpret_cast<unsigned long long*>(&g_sum[gidx]), (unsigned long long)v[j]);
+        if (g_mn) atomicMin(&g_mn[gidx], v[j]);
+        if (g_mx) atomicMax(&g_mx[gidx], v[j]);
+      }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < DG_SLOTS; i += DG_THREADS) {   // flush the tile's table and empty it
+      const uint32_t t = s_tag[i];
+      if (t != 0) {
+        const uint32_t gidx = t - 1u;
+        if (g_cnt) atomicAdd(reinterpret_cast<unsigned long long*>(&g_cnt[gidx]), (unsigned long long)s_cnt[i]);
+        if (g_sum) atomicAdd(reinterpret_cast<unsigned long long*>(&g_sum[gidx]), (unsigned long long)s_sum[i]);
+        if (g_mn) atomicMin(&g_mn[gidx], s_mn[i]);
+        if (g_mx) atomicMax(&g_mx[gidx], s_mx[i]);
+        s_tag[i] = 0;
+        s_cnt[i] = 0;
+        if (g_sum) s_sum[i] = 0;
+        if (g_mn) s_mn[i] = INT64_MAX;
+        if (g_mx) s_mx[i] = INT64_MIN;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// Compaction of the non-empty table entries, in index (= key) order: per-block counts, one-block scan, write-out.
+constexpr int DC_THREADS = 256;
+constexpr int DC_IPT = 8;
+constexpr int DC_TILE = DC_THREADS * DC_IPT;
+constexpr int DC_MAX_TABS = 8;
+struct DenseTabs {
+  const long long* in[DC_MAX_TABS];
+  long long* out[DC_MAX_TABS];
+  int n;
+};
+
+__global__ void __launch_bounds__(DC_THREADS)
+dense_count_kernel(const long long* __restrict__ cnt, uint64_t range, uint32_t* __restrict__ block_counts) {
+  __shared__ uint32_t s_sum;
+  if (threadIdx.x == 0) s_sum = 0;
+  __syncthreads();
+  uint32_t c = 0;
+  const uint64_t base = (uint64_t)blockIdx.x * DC_TILE;
+#pragma unroll
+  for (int j = 0; j < DC_IPT; ++j) {
+    const uint64_t i = base + (uint64_t)j * DC_THREADS + threadIdx.x;
+    c += (i < range && cnt[i] != 0) ? 1u : 0u;
+  }
+#pragma unroll
+  for (int d = 16; d >= 1; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(&s_sum, c);
+  __syncthreads();
+  if (threadIdx.x == 0) block_counts[blockIdx.x] = s_sum;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS)
+dense_scan_kernel(uint32_t* __restrict__ block_counts, uint32_t blocks, uint32_t* __restrict__ num_groups_out) {
+  __shared__ uint32_t s_warp[32];
+  const unsigned lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const uint32_t per = (blocks + SCAN_THREADS - 1) / SCAN_THREADS;
+  const uint32_t lo = min(blocks, threadIdx.x * per), hi = min(blocks, lo + per);
+  uint32_t sum = 0;
+  for (uint32_t t = lo; t < hi; ++t) sum += block_counts[t];
+  uint32_t x = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= (unsigned)o) x += y;
+  }
+  if (lane == 31) s_warp[w] = x;
+  __syncthreads();
+  uint32_t off = 0;
+  for (unsigned k = 0; k < w; ++k) off += s_warp[k];
+  uint32_t run = off + x - sum;
+  for (uint32_t t = lo; t < hi; ++t) {
+    const uint32_t c = block_counts[t];
+    block_counts[t] = run;
+    run += c;
+  }
+  if (threadIdx.x == SCAN_THREADS - 1) *num_groups_out = off + x;
+}
+
+__global__ void __launch_bounds__(DC_THREADS)
+dense_write_kernel(const long long* __restrict__ cnt, uint64_t range, uint64_t base_code, int kt,
+                   const uint32_t* __restrict__ block_base, void* __restrict__ keys_out, long long* __restrict__ count_out,
+                   const DenseTabs tabs) {
+  // entries of a tile in index order: thread t owns DC_IPT consecutive entries
+  __shared__ uint32_t s_warp[DC_THREADS / 32];
+  const unsigned lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const uint64_t first = (uint64_t)blockIdx.x * DC_TILE + (uint64_t)threadIdx.x * DC_IPT;
+  uint32_t mine = 0;
+  bool live[DC_IPT];
+#pragma unroll
+  for (int j = 0; j < DC_IPT; ++j) {
+    live[j] = first + j < range && cnt[first + j] != 0;
+    mine += live[j] ? 1u : 0u;
+  }
+  uint32_t x = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= (unsigned)o) x += y;
+  }
+  if (lane == 31) s_warp[w] = x;
+  __syncthreads();
+  uint32_t off = block_base[blockIdx.x];
+  for (unsigned k = 0; k < w; ++k) off += s_warp[k];
+  uint32_t g = off + x - mine;
+#pragma unroll
+  for (int j = 0; j < DC_IPT; ++j) {
+    if (!live[j]) continue;
+    const uint64_t i = first + j;
+    store_decoded_key(keys_out, g, base_code + i, kt);
+    if (count_out) count_out[g] = cnt[i];
+#pragma unroll
+    for (int t = 0; t < DC_MAX_TABS; ++t)
+      if (t < tabs.n) tabs.out[t][g] = tabs.in[t][i];
+    ++g;
+  }
+}
+
 static inline uint32_t tiles_of(size_t n) { return (uint32_t)((n + G_TILE - 1) / G_TILE); }
 
 template <typename VIn, typename T, bool CENTER>
@@ -646,5 +880,101 @@ extern "C" int b200x_group_quantile(const uint32_t* group_starts, const uint32_t
   group_quantile_kernel<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream_>>>(group_starts, num_groups, perm, values,
                                                                              value_type, n, q, out);
   B200X_LAUNCH_CHECK("group_quantile_kernel");
+  return B200X_OK;
+}
+
+extern "C" int b200x_key_code_range(const void* keys, int key_type, size_t n, uint64_t* range_out, void* stream_) {
+  cudaStream_t st = (cudaStream_t)stream_;
+  if (range_out == nullptr || key_type < 0 || key_type >= KEY_TYPE_COUNT || (n > 0 && keys == nullptr)) {
+    set_error("b200x_key_code_range: bad arguments");
+    return B200X_ERR_ARG;
+  }
+  const unsigned long long init[2] = {~0ull, 0ull};
+  B200X_CUDA(cudaMemcpyAsync(range_out, init, sizeof(init), cudaMemcpyHostToDevice, st));
+  if (n == 0) return B200X_OK;
+  uint64_t blocks = (n + 255) / 256 / 4 + 1;
+  const uint64_t cap = (uint64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  key_code_range_kernel<<<(uint32_t)blocks, 256, 0, st>>>(keys, key_type, n, (unsigned long long*)range_out);
+  B200X_LAUNCH_CHECK("key_code_range_kernel");
+  return B200X_OK;
+}
+
+extern "C" int b200x_dense_group_accumulate(const void* keys, int key_type, size_t n, uint64_t base_code, size_t range,
+                                            const int64_t* values, int init, int64_t* count_tab, int64_t* sum_tab,
+                                            int64_t* min_tab, int64_t* max_tab, void* stream_) {
+  cudaStream_t st = (cudaStream_t)stream_;
+  if (key_type < 0 || key_type >= KEY_TYPE_COUNT || key_type == KEY_F64 || key_type == KEY_F32 || range == 0 ||
+      range > ((size_t)1 << 30) || (n > 0 && keys == nullptr) ||
+      (values == nullptr && (sum_tab != nullptr || min_tab != nullptr || max_tab != nullptr)) ||
+      (count_tab == nullptr && sum_tab == nullptr && min_tab == nullptr && max_tab == nullptr)) {
+    set_error("b200x_dense_group_accumulate: bad arguments (integer key types, 1 <= range <= 2^30, values needed for sum/min/max)");
+    return B200X_ERR_ARG;
+  }
+  if (init) {
+    uint64_t blocks = (range + 255) / 256;
+    const uint64_t cap = (uint64_t)sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    dense_init_kernel<<<(uint32_t)blocks, 256, 0, st>>>(range, (long long*)count_tab, (long long*)sum_tab, (long long*)min_tab,
+                                                        (long long*)max_tab);
+    B200X_LAUNCH_CHECK("dense_init_kernel");
+  }
+  if (n == 0) return B200X_OK;
+  const size_t smem = (size_t)DG_SLOTS * (8 + 8 * ((sum_tab ? 1 : 0) + (min_tab ? 1 : 0) + (max_tab ? 1 : 0)));
+  static thread_local int attr_dev = -1;
+  int dev = 0;
+  B200X_CUDA(cudaGetDevice(&dev));
+  if (dev != attr_dev) {
+    B200X_CUDA(cudaFuncSetAttribute(dense_accumulate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DG_SLOTS * 32));
+    attr_dev = dev;
+  }
+  uint64_t tiles = (n + DG_TILE - 1) / DG_TILE;
+  const uint64_t cap = (uint64_t)sm_count() * 6;
+  if (tiles > cap) tiles = cap;
+  prof_begin(st, PROF_SEGRED);
+  dense_accumulate_kernel<<<(uint32_t)tiles, DG_THREADS, smem, st>>>(keys, key_type, n, base_code, (uint32_t)range,
+                                                                    (const long long*)values, (long long*)count_tab,
+                                                                    (long long*)sum_tab, (long long*)min_tab,
+                                                                    (long long*)max_tab);
+  prof_end(st);
+  B200X_LAUNCH_CHECK("dense_accumulate_kernel");
+  return B200X_OK;
+}
+
+extern "C" int b200x_dense_group_compact(uint64_t base_code, size_t range, int key_type, const int64_t* count_tab,
+                                         int num_tabs, const int64_t* const* tabs_host, void* keys_out, int64_t* count_out,
+                                         int64_t* const* tabs_out_host, uint32_t* num_groups_out, void* temp,
+                                         size_t* temp_bytes, void* stream_) {
+  cudaStream_t st = (cudaStream_t)stream_;
+  if (temp_bytes == nullptr) {
+    set_error("b200x_dense_group_compact: temp_bytes is NULL");
+    return B200X_ERR_ARG;
+  }
+  const uint32_t blocks = (uint32_t)((range + DC_TILE - 1) / DC_TILE);
+  const size_t need = align_up((size_t)(blocks + 1) * sizeof(uint32_t), 256);
+  if (temp == nullptr) {
+    *temp_bytes = need;
+    return B200X_OK;
+  }
+  if (*temp_bytes < need || range == 0 || range > ((size_t)1 << 30) || count_tab == nullptr || keys_out == nullptr ||
+      num_groups_out == nullptr || num_tabs < 0 || num_tabs > DC_MAX_TABS || key_type < 0 || key_type >= KEY_TYPE_COUNT ||
+      (num_tabs > 0 && (tabs_host == nullptr || tabs_out_host == nullptr))) {
+    set_error("b200x_dense_group_compact: bad arguments or temp too small (%zu < %zu)", *temp_bytes, need);
+    return B200X_ERR_ARG;
+  }
+  DenseTabs tabs;
+  tabs.n = num_tabs;
+  for (int t = 0; t < DC_MAX_TABS; ++t) {
+    tabs.in[t] = t < num_tabs ? (const long long*)tabs_host[t] : nullptr;
+    tabs.out[t] = t < num_tabs ? (long long*)tabs_out_host[t] : nullptr;
+  }
+  uint32_t* block_counts = (uint32_t*)temp;
+  dense_count_kernel<<<blocks, DC_THREADS, 0, st>>>((const long long*)count_tab, range, block_counts);
+  B200X_LAUNCH_CHECK("dense_count_kernel");
+  dense_scan_kernel<<<1, SCAN_THREADS, 0, st>>>(block_counts, blocks, num_groups_out);
+  B200X_LAUNCH_CHECK("dense_scan_kernel");
+  dense_write_kernel<<<blocks, DC_THREADS, 0, st>>>((const long long*)count_tab, range, base_code, key_type, block_counts,
+                                                    keys_out, (long long*)count_out, tabs);
+  B200X_LAUNCH_CHECK("dense_write_kernel");
   return B200X_OK;
 }

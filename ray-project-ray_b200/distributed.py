@@ -151,8 +151,8 @@ class P2PExchange:
     `view` returns tensors that ALIAS the receive buffers: consume them before the next exchange."""
 
     def __init__(self, columns: Dict[str, Tuple[torch.Tensor, Optional[torch.Tensor]]], n: int,
-                 send_counts: Sequence[int], dev: torch.device, group=None, target: Optional[torch.Tensor] = None,
-                 chunk_table: Optional[np.ndarray] = None):
+                 send_counts: Optional[Sequence[int]], dev: torch.device, group=None, target: Optional[torch.Tensor] = None,
+                 chunk_table: Optional[torch.Tensor] = None):
         import ctypes
 
         self.columns, self.n, self.dev, self.group = columns, n, dev, group
@@ -160,13 +160,14 @@ class P2PExchange:
         self.world, rank = dist.get_world_size(group), dist.get_rank(group)
         self.rank = rank
         if chunk_table is not None:
-            # chunk_table[c, d] = rows among this rank's first chunk_rows[c] rows that go to rank d (last row = all
-            # rows): gathered from every rank, it tells a receiver which slots of its buffer chunk c of rank r fills
-            mine = torch.from_numpy(np.ascontiguousarray(chunk_table, dtype=np.int64)).to(dev)
-            parts = [torch.empty_like(mine) for _ in range(self.world)]
-            dist.all_gather(parts, mine, group=group)
-            self.tables = torch.stack(parts).cpu().numpy()          # [source rank, chunk boundary, destination]
+            # chunk_table[c, d] (int64, on the device) = rows among this rank's first chunk_rows[c] rows that go to rank
+            # d (last row = all rows): gathered from every rank - the one device -> host read of the exchange - it
+            # gives the count matrix and tells a receiver which slots of its buffer chunk c of rank r fills
+            parts = [torch.empty_like(chunk_table) for _ in range(self.world)]
+            dist.all_gather(parts, chunk_table.contiguous(), group=group)
+            self.tables = torch.stack(parts).cpu().numpy()[:, :, :self.world]   # [source rank, chunk boundary, destination]
             C = self.tables[:, -1, :]
+            send_counts = [int(x) for x in C[rank]]
         else:
             self.tables = None
             C = all_gather_counts(send_counts, group, dev)
@@ -518,12 +519,11 @@ def _p2p_partition_sort_records(local: DeviceBlock, sort_key: SortKey, n: int, d
     cut_tiles = [c * tiles // K for c in range(K)]
     rows_at = [t * ops.PT_TILE_ROWS for t in cut_tiles] + [n]
     sel = torch.tensor(cut_tiles, dtype=torch.int64, device=dev)
-    table = torch.cat([tile_table.index_select(0, sel).to(torch.int64), counts.reshape(1, 16)], 0).cpu().numpy()[:, :world]
-    send_counts = [int(x) for x in table[-1]]
+    table = torch.cat([tile_table.index_select(0, sel).to(torch.int64), counts.reshape(1, 16)], 0)
     cols = {first: (keycol, None), "\x00rec": (g.rec, None)}
     for c in extra:
         cols[c] = (_contig(local.columns[c]), None)
-    ex = P2PExchange(cols, n, send_counts, dev, group, target=target, chunk_table=table)
+    ex = P2PExchange(cols, n, None, dev, group, target=target, chunk_table=table)
     main = torch.cuda.current_stream(dev)
     ex.fence()
     ex.send([first])
@@ -690,7 +690,7 @@ def dist_random_shuffle(local: DeviceBlock, seed: Optional[int], group=None) -> 
 
 def dist_aggregate(local: DeviceBlock, key: Optional[str], aggs, group=None, samples_per_rank: int = 4096) -> DeviceBlock:
     """Sort-based groupby across ranks: local partials -> range exchange of partial rows -> merge."""
-    from .aggregate import aggregate_sorted, merge_combined_blocks
+    from .aggregate import aggregate_sorted, dense_aggregate, merge_combined_blocks
     from .aggregate_task_spec import SortAggregateTaskSpec
 
     world, rank = dist.get_world_size(group), dist.get_rank(group)
@@ -710,8 +710,10 @@ def dist_aggregate(local: DeviceBlock, key: Optional[str], aggs, group=None, sam
         return merge_combined_blocks([received], None, aggs, finalize=True) if rank == 0 else DeviceBlock.empty(dev)
     partial = None
     if n > 0:
-        perm, codes, _ = ops.argsort(_contig(local.columns[key]), False, want_codes=True)
-        partial = aggregate_sorted(local, key, aggs, perm, codes, finalize=False, n=n)  # ascending by key
+        partial = dense_aggregate(local, key, aggs, finalize=False)    # small-range integer keys: no sort needed
+        if partial is None:
+            perm, codes, _ = ops.argsort(_contig(local.columns[key]), False, want_codes=True)
+            partial = aggregate_sorted(local, key, aggs, perm, codes, finalize=False, n=n)  # ascending by key
     partial = _partial_like(partial, dev, group)
     if partial is None:
         return DeviceBlock.empty(dev)

@@ -563,3 +563,49 @@ def finalize_groups(sums: torch.Tensor, counts: torch.Tensor, mode: int, ddof: i
             _lib.call("b200x_finalize_groups", sums.data_ptr(), value_type_of(sums), counts.data_ptr(), sums.numel(),
                       mode, ddof, out.data_ptr(), _stream(dev))
     return out
+
+
+def key_code_range(keys: torch.Tensor) -> Tuple[int, int]:
+    """(smallest, largest) order-preserving code of a key column, as Python ints (one device -> host read)."""
+    dev = _require_cuda(keys)
+    out = torch.empty(2, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        _lib.call("b200x_key_code_range", keys.data_ptr(), key_type_of(keys), keys.numel(), out.data_ptr(), _stream(dev))
+    lo, hi = out.cpu().tolist()
+    return lo & 0xFFFFFFFFFFFFFFFF, hi & 0xFFFFFFFFFFFFFFFF
+
+
+def dense_group_accumulate(keys: torch.Tensor, base_code: int, rng: int, values: Optional[torch.Tensor], count: Optional[torch.Tensor],
+                           want_sum: bool, want_min: bool, want_max: bool):
+    """Accumulate into int64 tables of `rng` entries indexed by code(key) - base_code. `count`: the count table to add
+    to, or None to leave counts out. Returns (sum, min, max) tables (None where not wanted); all freshly initialised."""
+    dev = _require_cuda(keys, values, count)
+    mk = lambda want: torch.empty(rng, dtype=torch.int64, device=dev) if want else None  # noqa: E731
+    s, mn, mx = mk(want_sum), mk(want_min), mk(want_max)
+    with torch.cuda.device(dev):
+        _lib.call("b200x_dense_group_accumulate", keys.data_ptr(), key_type_of(keys), keys.numel(), base_code, rng,
+                  _ptr(values), 1, _ptr(count), _ptr(s), _ptr(mn), _ptr(mx), _stream(dev))
+    return s, mn, mx
+
+
+def dense_group_compact(base_code: int, rng: int, key_dtype: torch.dtype, count: torch.Tensor, tabs: Sequence[torch.Tensor],
+                        max_groups: int):
+    """(keys, counts, compacted tables, number of groups) of the non-empty table entries in key order."""
+    dev = _require_cuda(count, *tabs)
+    kt = _KEY_TYPES[key_dtype]
+    keys_out = torch.empty(max_groups, dtype=key_dtype, device=dev)
+    count_out = torch.empty(max_groups, dtype=torch.int64, device=dev)
+    outs = [torch.empty(max_groups, dtype=torch.int64, device=dev) for _ in tabs]
+    ng = torch.zeros(1, dtype=torch.int32, device=dev)
+    tin = (ctypes.c_void_p * max(len(tabs), 1))(*[t.data_ptr() for t in tabs])
+    tout = (ctypes.c_void_p * max(len(tabs), 1))(*[t.data_ptr() for t in outs])
+    with torch.cuda.device(dev):
+        st = _stream(dev)
+        args = (base_code, rng, kt, count.data_ptr(), len(tabs), tin, keys_out.data_ptr(), count_out.data_ptr(), tout,
+                ng.data_ptr())
+        need = _lib.query_temp("b200x_dense_group_compact", *args, stream=st)
+        temp = _temp(need, dev)
+        nb = ctypes.c_size_t(temp.numel())
+        _lib.call("b200x_dense_group_compact", *args, temp.data_ptr(), ctypes.byref(nb), st)
+    g = int(ng.item())
+    return keys_out[:g], count_out[:g], [o[:g] for o in outs], g

@@ -22,7 +22,7 @@ from typing import Any, Dict, List, Optional, Tuple
 import torch
 
 from . import ops
-from .aggregate import aggregate_sorted
+from .aggregate import aggregate_sorted, dense_aggregate
 from .aggregate_task_spec import SortAggregateTaskSpec
 from .block import (Block, BlockAccessor, BlockExecStats, BlockMetadata, DeviceBlock, DeviceBlockAccessor,
                     _as_device_block, _contig, default_device, find_partition_indices)
@@ -549,8 +549,10 @@ def fused_aggregate(blocks: List[DeviceBlock], boundaries: List[Any], key, aggs)
         out = aggregate_sorted(table, k, aggs, perm, None, finalize=True, n=n)
         k = k[0]  # output blocks are cut on the first key column (rows equal in it stay together)
     else:
-        perm, codes, _ = ops.argsort(_contig(table.columns[k]), False, want_codes=True)
-        out = aggregate_sorted(table, k, aggs, perm, codes, finalize=True, n=n)
+        out = dense_aggregate(table, k, aggs, finalize=True)     # small-range integer keys: no sort needed
+        if out is None:
+            perm, codes, _ = ops.argsort(_contig(table.columns[k]), False, want_codes=True)
+            out = aggregate_sorted(table, k, aggs, perm, codes, finalize=True, n=n)
     if R == 1:
         return [out]
     if isinstance(boundaries, AutoBoundaries):

@@ -80,9 +80,10 @@ def main():
         # the fourth case sends the records in 4 chunks with overlapped gathers, the last one leaves rank 1 without rows
         os.environ["B200X_EXCHANGE_CHUNK_MIN_ROWS"] = "1000" if m == 300_123 else str(1 << 22)
         bkey = rng.integers(0, 256, (m, 10)).astype(np.uint8)
-        dst, src = rng.integers(0, m, m // 50), rng.integers(0, m, m // 50)
-        bkey[dst, :8] = bkey[src, :8]
-        bkey[rng.integers(0, m, 3000)] = shared[rng.integers(0, 500, 3000)]
+        if m:
+            dst, src = rng.integers(0, m, m // 50), rng.integers(0, m, m // 50)
+            bkey[dst, :8] = bkey[src, :8]
+            bkey[rng.integers(0, m, 3000)] = shared[rng.integers(0, 500, 3000)]
         if m == 90_000:
             bkey[:, :8] = bkey[rng.integers(0, 40, m), :8]      # duplicate-heavy first 8 bytes: the tie repair gives up
         bpay = rng.integers(0, 256, (m, 90), dtype=np.uint8)

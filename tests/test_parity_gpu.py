@@ -588,3 +588,56 @@ def test_int64_sum_wraps_within_and_across_blocks(cuda_device):
     for nblocks in (1, 3):
         got = rd.from_numpy_columns({"k": k, "v": v}, override_num_blocks=nblocks).groupby("k").sum("v").to_numpy()
         assert dict(zip(got["k"].tolist(), got["sum(v)"].tolist())) == wrap
+
+
+@pytest.mark.parametrize("dist_kind", ["uniform", "zipf", "hot", "negative_i32"])
+def test_dense_range_aggregation_equals_sorted_path(dist_kind, cuda_device):
+    """Small-range integer keys take the sort-free path (csrc/groupby.cu "Dense-range aggregation"): the same groups,
+    keys ascending, and bit-identical integer results as the sorted path and the oracle - also when one key holds a
+    large share of the rows (combined per tile in shared memory before it reaches the table)."""
+    from ray_project_ray_b200 import aggregate as A
+    from ray_project_ray_b200.aggregate import AbsMax
+
+    rng = np.random.default_rng(17)
+    n = 400_000
+    if dist_kind == "uniform":
+        k = rng.integers(0, 50_000, n, dtype=np.int64)
+    elif dist_kind == "zipf":
+        k = (rng.zipf(1.1, n) % 30_000).astype(np.int64) * 3 - 7
+    elif dist_kind == "hot":
+        k = np.where(rng.random(n) < 0.6, 12345, rng.integers(0, 100_000, n)).astype(np.int64)
+    else:
+        k = rng.integers(-2000, 2000, n).astype(np.int32)
+    v = rng.integers(-2**40, 2**40, n, dtype=np.int64)
+    w = rng.integers(-5, 5, n, dtype=np.int64)
+    ds = rd.from_numpy_columns({"k": k, "v": v, "w": w}, override_num_blocks=4)
+    aggs = [Sum("v"), Mean("v"), Count(), Min("v"), Max("w"), AbsMax("w"), Sum("w", alias_name="sw")]
+    calls = []
+    orig = A.ops.dense_group_accumulate
+    A.ops.dense_group_accumulate = lambda *a, **kw: (calls.append(1), orig(*a, **kw))[1]
+    try:
+        got = ds.groupby("k").aggregate(*aggs).to_numpy()
+    finally:
+        A.ops.dense_group_accumulate = orig
+    assert calls, "the dense path did not run"
+    saved = A.DENSE_MAX_RANGE
+    A.DENSE_MAX_RANGE = 0
+    try:
+        ref = ds.groupby("k").aggregate(*aggs).to_numpy()
+    finally:
+        A.DENSE_MAX_RANGE = saved
+    assert list(got) == list(ref)
+    for c in got:
+        assert got[c].dtype == ref[c].dtype
+        np.testing.assert_array_equal(got[c], ref[c])        # Mean = the same int64 sum / count: identical bits
+    keys, counts = np.unique(k, return_counts=True)
+    np.testing.assert_array_equal(got["k"], keys)
+    np.testing.assert_array_equal(got["count()"], counts)
+    order = np.argsort(k, kind="stable")
+    bounds = np.concatenate(([0], np.cumsum(counts)))[:-1]
+    np.testing.assert_array_equal(got["sum(v)"], np.add.reduceat(v[order], bounds))
+    np.testing.assert_array_equal(got["min(v)"], np.minimum.reduceat(v[order], bounds))
+    np.testing.assert_array_equal(got["max(w)"], np.maximum.reduceat(w[order], bounds))
+    # not applicable: float value column, wide key range -> the sorted path, same API
+    wide = rd.from_numpy_columns({"k": k.astype(np.int64) * (2**40), "v": v}, override_num_blocks=2).groupby("k").sum("v").to_numpy()
+    np.testing.assert_array_equal(wide["sum(v)"], np.add.reduceat(v[order], bounds))

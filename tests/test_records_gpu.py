@@ -263,7 +263,11 @@ def test_record_exchange_kernels_with_local_peers(n, world, cuda_device):
     hi_np = key[:, :8].copy().view(">u8").astype(np.uint64).ravel()
     split = np.sort(np.random.default_rng(1).integers(0, 2 ** 63, world - 1).astype(np.uint64) * np.uint64(2))
     owner = np.searchsorted(split, hi_np, side="right")
-    target, counts = ops.partition_targets(hi, False, torch.from_numpy(split.view(np.int64)).to(cuda_device))
+    target, counts, table = ops.partition_targets(hi, False, torch.from_numpy(split.view(np.int64)).to(cuda_device),
+                                                  want_tile_table=True)
+    tab = table.cpu().numpy()
+    for t in (0, 1, tab.shape[0] // 2, tab.shape[0] - 1):      # slots handed out before tile t = rows per owner before it
+        np.testing.assert_array_equal(tab[t][:world], np.bincount(owner[: t * ops.PT_TILE_ROWS], minlength=world))
     cnt = np.bincount(owner, minlength=world)
     np.testing.assert_array_equal(counts.cpu().numpy()[:world], cnt)
     bufs = [torch.full((int(cnt[d]) + 3, 128), 7, dtype=torch.uint8, device=cuda_device) for d in range(world)]
