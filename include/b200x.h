@@ -87,8 +87,8 @@ int b200x_radix_argsort(const void* keys, int key_type, int descending, const ui
 /* Tuning knobs (process-wide). key 0: fewest rows for which b200x_radix_argsort considers its
  * HYBRID mode (two global passes on the top 16 varying bits, then every run is finished in shared
  * memory); default 2^22. key 1: most blocks per SM the staged peer scatter launches (0 = one block per tile);
- * a small value leaves room for work running next to the transfer on another stream. Results never depend
- * on either. */
+ * a small value leaves room for work running next to the transfer on another stream. key 2: loads in flight per
+ * thread of b200x_gather_records_prefixed (2 or 4). Results never depend on any of them. */
 int b200x_set_tuning(int key, long long value);
 
 /* b200x_radix_argsort for callers that cannot allocate device memory. (No counterpart in the
@@ -242,9 +242,13 @@ int b200x_scatter_rows_by_target(const void* src, size_t row_bytes, const uint32
  * received row idx[i]] when shift == 8 - the prefix taken from sorted_keys[i] (big-endian bytes if prefix_be, else
  * the integer as it is), i.e. the elided key bytes are put back from the sorted key column while the rows are
  * gathered into sorted order - or just the received row when shift == 0; bytes from used_bytes on are zero.
- * slot_ranges_host (num_ranges pairs [lo, hi), HOST array, <= 16) restricts the gather to rows whose receive slot
- * idx[i] lies in one of the ranges (the chunks that have landed); tie_mode 1 skips, 2 selects the positions whose
- * key equals a neighbour's (their order is final only after b200x_fix_ties), 0 takes all.
+ * positions (device, num_positions entries; NULL = all n) lists the output positions to write: the rows of one
+ * chunk that has landed; tie_mode 1 skips, 2 selects the positions whose key equals a neighbour's (their order is
+ * final only after b200x_fix_ties), 0 takes all; a position list goes with tie_mode 0 only.
+ * b200x_split_positions_by_chunk builds those lists: chunk_starts_host[r * num_chunks + c] = first receive slot of
+ * chunk c of source rank r (ascending; HOST array); output position i (whose row sits in slot idx[i]) is appended
+ * to the list of its chunk, the lists lying in positions_out from list_offsets_host[c] on (sizes are known from
+ * the count tables); every list comes out in ascending order. Two-phase temp query as elsewhere.
  * Replaces the same object-store hop as b200x_scatter_rows_to_peers, and the reducer's concat + take
  * (_internal/arrow_block.py:554-567, transform_pyarrow.py:269-276). */
 int b200x_scatter_records_by_target(const void* src, size_t src_pitch, size_t copy_bytes, const uint32_t* target, size_t n,
@@ -252,8 +256,11 @@ int b200x_scatter_records_by_target(const void* src, size_t src_pitch, size_t co
                                     size_t dst_pitch, int world, void* stream);
 int b200x_gather_records_prefixed(const void* recv, size_t recv_pitch, size_t copy_bytes, const uint32_t* idx, size_t n,
                                   const uint64_t* sorted_keys, int prefix_be, size_t shift, size_t used_bytes, void* dst,
-                                  size_t dst_pitch, int tie_mode, const uint32_t* slot_ranges_host, int num_ranges,
+                                  size_t dst_pitch, int tie_mode, const uint32_t* positions, size_t num_positions,
                                   void* stream);
+int b200x_split_positions_by_chunk(const uint32_t* idx, size_t n, const uint32_t* chunk_starts_host, int num_sources,
+                                   int num_chunks, const uint32_t* list_offsets_host, uint32_t* positions_out, void* temp,
+                                   size_t* temp_bytes, void* stream);
 
 /* Seeded pseudo-random bijection pi on [0, n) (6 alternating Feistel rounds over the 2^ceil(log2 n)
  * domain, cycle-walked into range). Deterministic in (seed, n).

@@ -59,7 +59,9 @@ SIGNATURES = {
     "b200x_scatter_records_by_target": (c_int, [c_void_p, c_size_t, c_size_t, c_void_p, c_size_t, POINTER(c_void_p),
                                                 POINTER(ctypes.c_ulonglong), c_size_t, c_int, c_void_p]),
     "b200x_gather_records_prefixed": (c_int, [c_void_p, c_size_t, c_size_t, c_void_p, c_size_t, c_void_p, c_int, c_size_t,
-                                              c_size_t, c_void_p, c_size_t, c_int, POINTER(c_uint32), c_int, c_void_p]),
+                                              c_size_t, c_void_p, c_size_t, c_int, c_void_p, c_size_t, c_void_p]),
+    "b200x_split_positions_by_chunk": (c_int, [c_void_p, c_size_t, POINTER(c_uint32), c_int, c_int, POINTER(c_uint32),
+                                               c_void_p, c_void_p, _size_p, c_void_p]),
     "b200x_permute_rows": (c_int, [c_void_p, c_size_t, c_size_t, c_uint64, c_int, c_void_p, c_void_p]),
     "b200x_perm_indices": (c_int, [c_size_t, c_uint64, c_int, c_size_t, c_size_t, c_void_p, c_void_p]),
     "b200x_perm_indices_host": (c_int, [c_size_t, c_uint64, c_int, c_size_t, c_size_t, c_void_p]),

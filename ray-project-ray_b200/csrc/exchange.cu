@@ -274,6 +274,8 @@ scatter_rows_by_target_kernel(const V* __restrict__ src, const uint32_t* __restr
 // (8 GPUs, 100 M rows: key column 3.45 ms unstaged).
 // b200x_set_tuning(1, k): staged scatter launches at most k blocks per SM (0 = one block per tile)
 int g_scatter_blocks_per_sm = 0;
+// b200x_set_tuning(2, k): loads in flight per thread of the record gather (2 or 4)
+int g_gather_chains = 2;
 
 constexpr int ST_THREADS = 256;
 constexpr int ST_MAX_TILE = 1024;
@@ -736,12 +738,6 @@ scatter_records_staged_kernel(const unsigned char* __restrict__ src, uint64_t sr
   }
 }
 
-constexpr int GR_MAX_RANGES = 16;
-struct SlotRanges {
-  uint32_t lo[GR_MAX_RANGES], hi[GR_MAX_RANGES];
-  int n;   // 0 = every slot
-};
-
 __device__ __forceinline__ uint64_t bswap64(uint64_t v) {
   const uint32_t lo = (uint32_t)v, hi = (uint32_t)(v >> 32);
   return ((uint64_t)__byte_perm(lo, 0, 0x0123) << 32) | (uint64_t)__byte_perm(hi, 0, 0x0123);
@@ -754,82 +750,211 @@ __device__ __forceinline__ uint64_t keep_below(uint64_t w, uint32_t pos0, uint32
   return w & ((1ull << (8u * (used - pos0))) - 1ull);
 }
 
-// tie_mode 0: every position; 1: skip positions whose key equals a neighbour's; 2: only those positions.
-// A warp takes 32 consecutive output rows: each lane decides for ONE of them (slot in range? tied?) - so the
-// index, the range test and the neighbour comparison cost one evaluation per row, not one per 16-byte piece -
-// then groups of lanes_per_row lanes copy the selected rows, slot and key being broadcast with shuffles.
+// 16 output bytes [16j, 16j+16) of a record = received bytes [16j - shift, 16j - shift + 16) (shift 0 or 8), the
+// first 8 bytes being the key prefix when shift == 8, zero from `used` on
+__device__ __forceinline__ uint4 prefixed_vector(const unsigned char* __restrict__ row, uint32_t j, uint32_t shift,
+                                                 uint32_t copy_bytes, uint32_t used, uint64_t key, int prefix_be) {
+  const uint32_t o0 = 16u * j, o1 = o0 + 8u;
+  uint64_t w0 = 0, w1 = 0;
+  if (o0 >= shift && o0 - shift + 8u <= copy_bytes) w0 = *reinterpret_cast<const uint64_t*>(row + (o0 - shift));
+  if (o1 >= shift && o1 - shift + 8u <= copy_bytes) w1 = *reinterpret_cast<const uint64_t*>(row + (o1 - shift));
+  if (shift == 8u && j == 0) w0 = prefix_be ? bswap64(key) : key;
+  w0 = keep_below(w0, o0, used);
+  w1 = keep_below(w1, o1, used);
+  uint4 v;
+  v.x = (uint32_t)w0;
+  v.y = (uint32_t)(w0 >> 32);
+  v.z = (uint32_t)w1;
+  v.w = (uint32_t)(w1 >> 32);
+  return v;
+}
+
+// Output positions pos[0..m) (or 0..m-1 when pos is NULL): one thread per 16-byte piece, U pieces in flight.
+// A random gather is latency-bound: the kernel is kept at 32 registers so that 2048 threads are resident per SM.
+// LANES: dst_vec is a power of two <= 32 and copy_bytes a multiple of 16, so the pieces of a row sit in neighbouring
+// lanes (a thread's piece number never changes): every lane loads ONE aligned 16-byte vector of the received row
+// and, when the row is shifted by the 8-byte key prefix, takes the other half of its output vector from the lane
+// below with a shuffle.
+template <bool LANES, int U>
+__global__ void __launch_bounds__(256, LANES ? 8 : 4)
+gather_records_list_kernel(const unsigned char* __restrict__ recv, uint64_t recv_pitch, uint32_t copy_bytes,
+                           const uint32_t* __restrict__ idx, const uint32_t* __restrict__ pos, uint64_t m,
+                           const uint64_t* __restrict__ keys, int prefix_be, uint32_t shift, uint32_t used,
+                           unsigned char* __restrict__ dst, uint32_t dst_vec) {
+  const uint64_t total = m * dst_vec;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (LANES) {
+    const uint32_t c = (uint32_t)t & (dst_vec - 1u);        // stride is a multiple of 32, hence of dst_vec
+    const uint32_t sh = 31u - (uint32_t)__clz(dst_vec);
+    const bool has = 16u * c + 16u <= copy_bytes;
+    // (all lanes of a warp leave the loop together: the trip count depends on the warp's first element only)
+    for (; t - (threadIdx.x & 31) < total; t += U * stride) {
+      uint32_t orow[U], s[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const uint64_t e = t + u * stride;
+        orow[u] = e < total ? (uint32_t)(e >> sh) : 0xFFFFFFFFu;
+        if (pos != nullptr && e < total) orow[u] = pos[orow[u]];
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) s[u] = orow[u] != 0xFFFFFFFFu ? idx[orow[u]] : 0u;
+      uint4 v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        v[u] = make_uint4(0u, 0u, 0u, 0u);
+        if (has && orow[u] != 0xFFFFFFFFu) v[u] = *reinterpret_cast<const uint4*>(recv + (uint64_t)s[u] * recv_pitch + 16u * c);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        uint64_t w0 = (uint64_t)v[u].x | ((uint64_t)v[u].y << 32), w1 = (uint64_t)v[u].z | ((uint64_t)v[u].w << 32);
+        if (shift == 8u) {
+          const uint64_t below = __shfl_up_sync(0xffffffffu, w1, 1);   // upper half of the vector before mine
+          w1 = w0;
+          w0 = below;
+          if (c == 0 && orow[u] != 0xFFFFFFFFu) {
+            const uint64_t key = keys[orow[u]];
+            w0 = prefix_be ? bswap64(key) : key;
+          }
+        }
+        w0 = keep_below(w0, 16u * c, used);
+        w1 = keep_below(w1, 16u * c + 8u, used);
+        if (orow[u] != 0xFFFFFFFFu)
+          reinterpret_cast<uint4*>(dst)[(uint64_t)orow[u] * dst_vec + c] =
+              make_uint4((uint32_t)w0, (uint32_t)(w0 >> 32), (uint32_t)w1, (uint32_t)(w1 >> 32));
+      }
+    }
+  } else {
+    const uint64_t q = stride / dst_vec;
+    const uint32_t rem = (uint32_t)(stride - q * dst_vec);
+    uint64_t r = t / dst_vec;
+    uint32_t c = (uint32_t)(t - r * dst_vec);
+    for (; t < total; t += stride) {
+      const uint64_t orow = pos ? (uint64_t)pos[r] : r;
+      const uint64_t key = (shift == 8u && c == 0) ? keys[orow] : 0ull;
+      reinterpret_cast<uint4*>(dst)[orow * dst_vec + c] =
+          prefixed_vector(recv + (uint64_t)idx[orow] * recv_pitch, c, shift, copy_bytes, used, key, prefix_be);
+      c += rem;
+      r += q;
+      if (c >= dst_vec) {
+        c -= dst_vec;
+        ++r;
+      }
+    }
+  }
+}
+
+// Only (tie_mode 2) or all but (tie_mode 1) the positions whose key equals a neighbour's. A warp takes 32
+// consecutive output rows, each lane decides for one of them, then groups of lanes copy the selected rows.
 __global__ void __launch_bounds__(256)
-gather_records_prefixed_kernel(const unsigned char* __restrict__ recv, uint64_t recv_pitch, uint32_t copy_bytes,
-                               const uint32_t* __restrict__ idx, uint64_t n, const uint64_t* __restrict__ keys, int prefix_be,
-                               uint32_t shift, uint32_t used, unsigned char* __restrict__ dst, uint32_t dst_vec,
-                               uint32_t lanes_per_row, int tie_mode, const SlotRanges sr) {
+gather_records_ties_kernel(const unsigned char* __restrict__ recv, uint64_t recv_pitch, uint32_t copy_bytes,
+                           const uint32_t* __restrict__ idx, uint64_t n, const uint64_t* __restrict__ keys, int prefix_be,
+                           uint32_t shift, uint32_t used, unsigned char* __restrict__ dst, uint32_t dst_vec,
+                           uint32_t lanes_per_row, int tie_mode) {
   const unsigned lane = threadIdx.x & 31;
   const uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
   const uint32_t groups = 32 / lanes_per_row;        // rows copied at once by one warp
   const uint32_t g = lane / lanes_per_row, c0 = lane % lanes_per_row;
-  const bool need_key = keys != nullptr && (tie_mode != 0 || shift == 8u);
   for (uint64_t r0 = warp * 32; r0 < n; r0 += nwarps * 32) {
     const uint64_t i = r0 + lane;
-    bool go = i < n;
-    uint32_t s = 0;
-    uint64_t key = 0;
-    if (go) {
-      s = idx[i];
-      if (sr.n > 0) {
-        bool in = false;
-#pragma unroll
-        for (int k = 0; k < GR_MAX_RANGES; ++k) in |= (k < sr.n) && s >= sr.lo[k] && s < sr.hi[k];
-        go = in;
-      }
-    }
-    if (need_key && i < n) key = keys[i];
-    if (tie_mode != 0) {
-      uint64_t prev = __shfl_up_sync(0xffffffffu, key, 1), next = __shfl_down_sync(0xffffffffu, key, 1);
-      if (lane == 0 && i > 0 && i < n) prev = keys[i - 1];
-      if ((lane == 31 || i + 1 >= n) && i + 1 < n) next = keys[i + 1];
-      const bool tied = i < n && ((i > 0 && prev == key) || (i + 1 < n && next == key));
-      go = go && (tied == (tie_mode == 2));
-    }
+    const uint64_t key = i < n ? keys[i] : 0ull;
+    uint64_t prev = __shfl_up_sync(0xffffffffu, key, 1), next = __shfl_down_sync(0xffffffffu, key, 1);
+    if (lane == 0 && i > 0 && i < n) prev = keys[i - 1];
+    if (lane == 31 && i + 1 < n) next = keys[i + 1];
+    const bool tied = i < n && ((i > 0 && prev == key) || (i + 1 < n && next == key));
+    const bool go = i < n && (tied == (tie_mode == 2));
     const unsigned any = __ballot_sync(0xffffffffu, go);
     if (any == 0) continue;
-    constexpr int U = 4;                                // rows in flight per lane group
-    for (uint32_t b = 0; b < 32; b += U * groups) {
-      for (uint32_t j = c0; j < dst_vec; j += lanes_per_row) {
-        // output bytes [16j, 16j+16) = received bytes [16j - shift, 16j - shift + 16); shift is 0 or 8
-        const uint32_t o0 = 16u * j, o1 = o0 + 8u;
-        const bool ld0 = o0 >= shift && o0 - shift + 8u <= copy_bytes, ld1 = o1 >= shift && o1 - shift + 8u <= copy_bytes;
-        uint64_t w0[U], w1[U];
-        bool act[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const uint32_t ri = b + u * groups + g;       // row of this lane group within the warp's 32
-          const uint32_t srow = __shfl_sync(0xffffffffu, s, ri & 31u);
-          const uint64_t krow = __shfl_sync(0xffffffffu, key, ri & 31u);
-          act[u] = ri < 32u && ((any >> ri) & 1u);
-          w0[u] = w1[u] = 0;
-          if (act[u]) {
-            const unsigned char* row = recv + (uint64_t)srow * recv_pitch;
-            if (ld0) w0[u] = *reinterpret_cast<const uint64_t*>(row + (o0 - shift));
-            if (ld1) w1[u] = *reinterpret_cast<const uint64_t*>(row + (o1 - shift));
-            if (shift == 8u && j == 0) w0[u] = prefix_be ? bswap64(krow) : krow;
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          if (act[u]) {
-            const uint32_t ri = b + u * groups + g;
-            const uint64_t a0 = keep_below(w0[u], o0, used), a1 = keep_below(w1[u], o1, used);
-            uint4 v;
-            v.x = (uint32_t)a0;
-            v.y = (uint32_t)(a0 >> 32);
-            v.z = (uint32_t)a1;
-            v.w = (uint32_t)(a1 >> 32);
-            (reinterpret_cast<uint4*>(dst) + (r0 + ri) * dst_vec)[j] = v;
-          }
-        }
-      }
+    const uint32_t s = go ? idx[i] : 0u;
+    for (uint32_t b = 0; b < 32; b += groups) {
+      const uint32_t ri = b + g;                        // row of this lane group within the warp's 32
+      const uint32_t srow = __shfl_sync(0xffffffffu, s, ri);
+      const uint64_t krow = __shfl_sync(0xffffffffu, key, ri);
+      if (!((any >> ri) & 1u)) continue;
+      const unsigned char* row = recv + (uint64_t)srow * recv_pitch;
+      uint4* drow = reinterpret_cast<uint4*>(dst) + (r0 + ri) * dst_vec;
+      for (uint32_t j = c0; j < dst_vec; j += lanes_per_row) drow[j] = prefixed_vector(row, j, shift, copy_bytes, used, krow, prefix_be);
     }
+  }
+}
+
+// Output positions grouped by the chunk their row arrived in. starts[r * chunks + c] = first receive slot of chunk
+// c of source r (ascending over the whole array). The order inside a chunk's list does not matter.
+constexpr int SP_MAX_STARTS = 128;
+struct ChunkStarts {
+  uint32_t start[SP_MAX_STARTS];
+  uint32_t list_off[MAX_PEERS];   // where every chunk's list begins in positions_out
+  int total, chunks;
+};
+
+// Every warp owns a contiguous range of output positions; pass 1 counts its positions per chunk, a scan turns the
+// counts into list offsets, pass 2 writes the positions - so every list comes out in ascending order, which keeps
+// the later reads of idx[] and sorted_keys[] through a list close to sequential. No global atomics.
+__device__ __forceinline__ int chunk_of_slot(const uint32_t* s_start, int total, int chunks, uint32_t s) {
+  int lo = 0, hi = total;                     // number of starts <= s, by bisection
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (s_start[mid] <= s) lo = mid + 1; else hi = mid;
+  }
+  return lo > 0 ? (lo - 1) % chunks : 0;
+}
+
+template <bool WRITE>
+__global__ void __launch_bounds__(256)
+split_positions_kernel(const uint32_t* __restrict__ idx, uint64_t n, uint64_t rows_per_warp, const ChunkStarts cs,
+                       uint32_t* __restrict__ warp_counts /*[warps][MAX_PEERS]: counts (pass 1) / exclusive offsets (pass 2)*/,
+                       uint32_t* __restrict__ positions_out) {
+  __shared__ uint32_t s_start[SP_MAX_STARTS];
+  for (int i = threadIdx.x; i < SP_MAX_STARTS; i += blockDim.x) s_start[i] = i < cs.total ? cs.start[i] : 0xFFFFFFFFu;
+  __syncthreads();
+  const unsigned lane = threadIdx.x & 31, lt = lanemask_lt();
+  const uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint64_t lo = warp * rows_per_warp, hi = min(n, lo + rows_per_warp);
+  // lane c keeps chunk c's running count (pass 1) or next list position (pass 2)
+  uint32_t mine = 0;
+  if (WRITE && lane < (unsigned)cs.chunks) mine = cs.list_off[lane] + warp_counts[warp * MAX_PEERS + lane];
+  for (uint64_t r0 = lo; r0 < hi; r0 += 32) {
+    const uint64_t i = r0 + lane;
+    const int chunk = i < hi ? chunk_of_slot(s_start, cs.total, cs.chunks, idx[i]) : -1;
+    for (int c = 0; c < cs.chunks; ++c) {
+      const unsigned m = __ballot_sync(0xffffffffu, chunk == c);
+      if (m == 0) continue;
+      if (WRITE) {
+        const uint32_t base = __shfl_sync(0xffffffffu, mine, c);
+        if (chunk == c) positions_out[base + __popc(m & lt)] = (uint32_t)i;
+      }
+      if ((int)lane == c) mine += (uint32_t)__popc(m);
+    }
+  }
+  if (!WRITE && lane < (unsigned)MAX_PEERS) warp_counts[warp * MAX_PEERS + lane] = lane < (unsigned)cs.chunks ? mine : 0u;
+}
+
+// exclusive scan over the warps of every chunk's counts (one block per chunk)
+__global__ void __launch_bounds__(1024)
+split_scan_kernel(uint32_t* __restrict__ warp_counts, uint32_t warps) {
+  __shared__ uint32_t s_warp[32];
+  const int c = blockIdx.x;
+  const unsigned lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const uint32_t per = (warps + 1023) / 1024;
+  const uint32_t lo = min(warps, threadIdx.x * per), hi = min(warps, lo + per);
+  uint32_t sum = 0;
+  for (uint32_t t = lo; t < hi; ++t) sum += warp_counts[(size_t)t * MAX_PEERS + c];
+  uint32_t x = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= (unsigned)o) x += y;
+  }
+  if (lane == 31) s_warp[w] = x;
+  __syncthreads();
+  uint32_t off = 0;
+  for (unsigned k = 0; k < w; ++k) off += s_warp[k];
+  uint32_t run = off + x - sum;
+  for (uint32_t t = lo; t < hi; ++t) {
+    const uint32_t v = warp_counts[(size_t)t * MAX_PEERS + c];
+    warp_counts[(size_t)t * MAX_PEERS + c] = run;
+    run += v;
   }
 }
 
@@ -888,14 +1013,14 @@ extern "C" int b200x_scatter_records_by_target(const void* src, size_t src_pitch
 extern "C" int b200x_gather_records_prefixed(const void* recv, size_t recv_pitch, size_t copy_bytes, const uint32_t* idx,
                                              size_t n, const uint64_t* sorted_keys, int prefix_be, size_t shift,
                                              size_t used_bytes, void* dst, size_t dst_pitch, int tie_mode,
-                                             const uint32_t* slot_ranges_host, int num_ranges, void* stream_) {
+                                             const uint32_t* positions, size_t num_positions, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
-  if (n == 0) return B200X_OK;
+  if (n == 0 || (positions != nullptr && num_positions == 0)) return B200X_OK;
   if (recv == nullptr || idx == nullptr || dst == nullptr || (shift != 0 && shift != 8) || (shift == 8 && sorted_keys == nullptr) ||
-      (tie_mode != 0 && sorted_keys == nullptr) || tie_mode < 0 || tie_mode > 2 || num_ranges < 0 || num_ranges > GR_MAX_RANGES ||
-      (num_ranges > 0 && slot_ranges_host == nullptr)) {
-    set_error("b200x_gather_records_prefixed: bad arguments (shift 0 or 8, sorted_keys needed for shift 8 / tie modes, <= %d ranges)",
-              GR_MAX_RANGES);
+      (tie_mode != 0 && sorted_keys == nullptr) || tie_mode < 0 || tie_mode > 2 || (positions != nullptr && tie_mode != 0) ||
+      num_positions > n) {
+    set_error("b200x_gather_records_prefixed: bad arguments (shift 0 or 8; sorted_keys needed for shift 8 and the tie modes; "
+              "a position list excludes the tie modes)");
     return B200X_ERR_ARG;
   }
   if ((copy_bytes & 7) != 0 || copy_bytes > recv_pitch || (recv_pitch & 7) != 0 || ((uintptr_t)recv & 7) != 0 ||
@@ -904,23 +1029,86 @@ extern "C" int b200x_gather_records_prefixed(const void* recv, size_t recv_pitch
               "used_bytes <= dst_pitch <= 65536");
     return B200X_ERR_ALIGN;
   }
-  SlotRanges sr;
-  sr.n = num_ranges;
-  for (int k = 0; k < GR_MAX_RANGES; ++k) {
-    sr.lo[k] = k < num_ranges ? slot_ranges_host[2 * k] : 0u;
-    sr.hi[k] = k < num_ranges ? slot_ranges_host[2 * k + 1] : 0u;
-  }
   const uint32_t dst_vec = (uint32_t)(dst_pitch / 16);
-  uint32_t lpr = 1;
-  while (lpr < dst_vec && lpr < 32) lpr <<= 1;
-  uint64_t blocks = ((uint64_t)n * lpr + 255) / 256;
   const uint64_t cap = (uint64_t)sm_count() * 16;
-  if (blocks > cap) blocks = cap;
   prof_begin(stream, PROF_GATHER);
-  gather_records_prefixed_kernel<<<(uint32_t)blocks, 256, 0, stream>>>(
-      (const unsigned char*)recv, recv_pitch, (uint32_t)copy_bytes, idx, n, sorted_keys, prefix_be, (uint32_t)shift,
-      (uint32_t)used_bytes, (unsigned char*)dst, dst_vec, lpr, tie_mode, sr);
+  if (tie_mode == 0) {
+    const uint64_t m = positions != nullptr ? num_positions : n;
+    uint64_t blocks = (m * dst_vec + 255) / 256;
+    if (blocks > cap) blocks = cap;
+    const bool lanes = dst_vec <= 32 && (dst_vec & (dst_vec - 1)) == 0 && (copy_bytes & 15) == 0 && ((uintptr_t)recv & 15) == 0 &&
+                       (recv_pitch & 15) == 0;
+    if (lanes && g_gather_chains == 4)
+      gather_records_list_kernel<true, 4><<<(uint32_t)blocks, 256, 0, stream>>>(
+          (const unsigned char*)recv, recv_pitch, (uint32_t)copy_bytes, idx, positions, m, sorted_keys, prefix_be, (uint32_t)shift,
+          (uint32_t)used_bytes, (unsigned char*)dst, dst_vec);
+    else if (lanes)
+      gather_records_list_kernel<true, 2><<<(uint32_t)blocks, 256, 0, stream>>>(
+          (const unsigned char*)recv, recv_pitch, (uint32_t)copy_bytes, idx, positions, m, sorted_keys, prefix_be, (uint32_t)shift,
+          (uint32_t)used_bytes, (unsigned char*)dst, dst_vec);
+    else
+      gather_records_list_kernel<false, 1><<<(uint32_t)blocks, 256, 0, stream>>>(
+          (const unsigned char*)recv, recv_pitch, (uint32_t)copy_bytes, idx, positions, m, sorted_keys, prefix_be, (uint32_t)shift,
+          (uint32_t)used_bytes, (unsigned char*)dst, dst_vec);
+  } else {
+    uint32_t lpr = 1;
+    while (lpr < dst_vec && lpr < 32) lpr <<= 1;
+    uint64_t blocks = ((uint64_t)n + 255) / 256;
+    if (blocks > cap) blocks = cap;
+    gather_records_ties_kernel<<<(uint32_t)blocks, 256, 0, stream>>>(
+        (const unsigned char*)recv, recv_pitch, (uint32_t)copy_bytes, idx, n, sorted_keys, prefix_be, (uint32_t)shift,
+        (uint32_t)used_bytes, (unsigned char*)dst, dst_vec, lpr, tie_mode);
+  }
   prof_end(stream);
-  B200X_LAUNCH_CHECK("gather_records_prefixed_kernel");
+  B200X_LAUNCH_CHECK("gather_records_prefixed");
+  return B200X_OK;
+}
+
+extern "C" int b200x_split_positions_by_chunk(const uint32_t* idx, size_t n, const uint32_t* chunk_starts_host, int num_sources,
+                                              int num_chunks, const uint32_t* list_offsets_host, uint32_t* positions_out,
+                                              void* temp, size_t* temp_bytes, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (temp_bytes == nullptr) {
+    set_error("b200x_split_positions_by_chunk: temp_bytes is NULL");
+    return B200X_ERR_ARG;
+  }
+  // every warp takes a contiguous range of positions (a multiple of 32 rows)
+  uint64_t warps = (uint64_t)sm_count() * 8 * 8;
+  uint64_t rows_per_warp = ((n + warps - 1) / warps + 31) / 32 * 32;
+  if (rows_per_warp == 0) rows_per_warp = 32;
+  warps = (n + rows_per_warp - 1) / rows_per_warp;
+  if (warps == 0) warps = 1;
+  warps = (warps + 7) / 8 * 8;   // whole blocks of 8 warps
+  const size_t need = align_up(warps * MAX_PEERS * sizeof(uint32_t), 256);
+  if (temp == nullptr) {
+    *temp_bytes = need;
+    return B200X_OK;
+  }
+  if (*temp_bytes < need || num_sources < 1 || num_chunks < 1 || num_chunks > MAX_PEERS ||
+      num_sources * num_chunks > SP_MAX_STARTS || chunk_starts_host == nullptr || list_offsets_host == nullptr ||
+      (n > 0 && (idx == nullptr || positions_out == nullptr))) {
+    set_error("b200x_split_positions_by_chunk: bad arguments (sources x chunks <= %d, chunks <= %d) or temp too small",
+              SP_MAX_STARTS, MAX_PEERS);
+    return B200X_ERR_ARG;
+  }
+  ChunkStarts cs;
+  cs.total = num_sources * num_chunks;
+  cs.chunks = num_chunks;
+  for (int i = 0; i < SP_MAX_STARTS; ++i) cs.start[i] = i < cs.total ? chunk_starts_host[i] : 0xFFFFFFFFu;
+  for (int i = 1; i < cs.total; ++i)
+    if (cs.start[i] < cs.start[i - 1]) {
+      set_error("b200x_split_positions_by_chunk: chunk starts must ascend");
+      return B200X_ERR_ARG;
+    }
+  for (int c = 0; c < MAX_PEERS; ++c) cs.list_off[c] = c < num_chunks ? list_offsets_host[c] : 0u;
+  if (n == 0) return B200X_OK;
+  uint32_t* warp_counts = (uint32_t*)temp;
+  const uint32_t blocks = (uint32_t)(warps / 8);
+  split_positions_kernel<false><<<blocks, 256, 0, stream>>>(idx, n, rows_per_warp, cs, warp_counts, positions_out);
+  B200X_LAUNCH_CHECK("split_positions_kernel<count>");
+  split_scan_kernel<<<num_chunks, 1024, 0, stream>>>(warp_counts, (uint32_t)warps);
+  B200X_LAUNCH_CHECK("split_scan_kernel");
+  split_positions_kernel<true><<<blocks, 256, 0, stream>>>(idx, n, rows_per_warp, cs, warp_counts, positions_out);
+  B200X_LAUNCH_CHECK("split_positions_kernel<write>");
   return B200X_OK;
 }

@@ -195,48 +195,17 @@ class P2PExchange:
         ops.scatter_records_by_target(col, self.target, [int(p) for p in h.buffer_ptrs], [int(x) for x in self._ro], pitch,
                                       copy_bytes=copy_bytes, src_offset=src_offset, row0=row0, nrows=nrows)
 
-    def chunk_slot_ranges(self, c: int) -> List[Tuple[int, int]]:
-        """Slots [lo, hi) of this rank's receive buffers that chunk c of every source rank fills."""
-        out = []
+    def chunk_layout(self) -> Tuple[List[int], List[int]]:
+        """(starts, sizes): starts[r * K + c] = first slot of this rank's receive buffers that chunk c of source rank r
+        fills (ascending); sizes[c] = rows of chunk c over all sources."""
+        K = self.tables.shape[1] - 1
+        starts, sizes = [], [0] * K
         for r in range(self.world):
             base = int(self.C[:r, self.rank].sum())
-            lo, hi = base + int(self.tables[r, c, self.rank]), base + int(self.tables[r, c + 1, self.rank])
-            if hi > lo:
-                out.append((lo, hi))
-        return out
-
-    def fence(self) -> None:
-        """Device-side barrier over all ranks on the current stream (symmetric-memory signal pads): before
-        the first send = everyone is done reading the previous contents; after a send = all stores landed."""
-        self._handle.barrier(channel=0)
-
-    def send(self, names: Sequence[str]) -> None:
-        import ctypes
-
-        from . import _lib
-
-        with torch.cuda.device(self.dev):
-            st = torch.cuda.current_stream(self.dev).cuda_stream
-            for name in names:
-                col, order = self.columns[name]
-                (buf, h), row_bytes = self._bufs[name]
-                bases = (ctypes.c_void_p * self.world)(*[int(p) for p in h.buffer_ptrs])
-                if self.target is not None:
-                    _lib.call("b200x_scatter_rows_by_target", _contig(col).data_ptr(), row_bytes, self.target.data_ptr(),
-                              self.n, bases, self._ro, self.world, st)
-                    continue
-                _lib.call("b200x_scatter_rows_to_peers", _contig(col).data_ptr(), row_bytes,
-                          None if order is None else order.data_ptr(), self.n, self._so, bases, self._ro, self.world, st)
-
-    def view(self, names: Sequence[str]) -> Dict[str, torch.Tensor]:
-        out = {}
-        for name in names:
-            col, _ = self.columns[name]
-            (buf, _), row_bytes = self._bufs[name]
-            flat = buf[: self.n_recv * row_bytes]
-            shape = (self.n_recv,) + tuple(col.shape[1:])
-            out[name] = flat.view(col.dtype).reshape(shape) if col.dtype != torch.uint8 else flat.reshape(shape)
-        return out
+            for c in range(K):
+                starts.append(base + int(self.tables[r, c, self.rank]))
+                sizes[c] += int(self.tables[r, c + 1, self.rank] - self.tables[r, c, self.rank])
+        return starts, sizes
 
 
 _side_streams: Dict[Tuple[int, int], torch.cuda.Stream] = {}
@@ -564,10 +533,14 @@ def _p2p_partition_sort_records(local: DeviceBlock, sort_key: SortKey, n: int, d
         gstream.wait_event(sorted_ev)
         for t in (perm2, probe, out):
             t.record_stream(gstream)
+        lists = [None]
+        if K > 1:       # output positions grouped by the chunk their row arrives in (known as soon as the keys are sorted)
+            starts, sizes = ex.chunk_layout()
+            lists = ops.split_positions_by_chunk(perm2, starts, world, K, sizes)
         for c in range(K):
             gstream.wait_event(chunk_ev[c])
-            ops.gather_records_prefixed(recv_rec, perm2, out, copy, used, probe if (shift or later) else None, plan["be"], shift,
-                                        tie_mode=1 if later else 0, ranges=ex.chunk_slot_ranges(c) if K > 1 else None)
+            ops.gather_records_prefixed(recv_rec, perm2, out, copy, used, probe if shift else None, plan["be"], shift,
+                                        positions=lists[c])
         verdict = None
         if later:
             pieces = []

@@ -401,17 +401,39 @@ def scatter_records_by_target(rec: torch.Tensor, target: torch.Tensor, bases: Se
 
 def gather_records_prefixed(recv: torch.Tensor, idx: torch.Tensor, out: torch.Tensor, copy_bytes: int, used: int,
                             sorted_keys: Optional[torch.Tensor] = None, prefix_be: bool = True, shift: int = 0,
-                            tie_mode: int = 0, ranges: Optional[Sequence[Tuple[int, int]]] = None) -> None:
-    """out[i] = [key prefix from sorted_keys[i] (shift == 8) | recv[idx[i], :copy_bytes]], zero from byte `used` on;
-    `ranges` / `tie_mode` restrict which positions are written (b200x_gather_records_prefixed)."""
-    dev = _require_cuda(recv, idx, out, sorted_keys)
-    n = idx.numel()
-    flat = [int(v) for r in (ranges or []) for v in r]
-    arr = (ctypes.c_uint32 * max(len(flat), 1))(*flat)
+                            tie_mode: int = 0, positions: Optional[torch.Tensor] = None) -> None:
+    """out[i] = [key prefix from sorted_keys[i] (shift == 8) | recv[idx[i], :copy_bytes]], zero from byte `used` on, for
+    the output positions in `positions` (all if None) / selected by `tie_mode` (b200x_gather_records_prefixed)."""
+    dev = _require_cuda(recv, idx, out, sorted_keys, positions)
     with torch.cuda.device(dev):
-        _lib.call("b200x_gather_records_prefixed", recv.data_ptr(), recv.shape[1], copy_bytes, idx.data_ptr(), n,
-                  _ptr(sorted_keys), int(prefix_be), shift, used, out.data_ptr(), out.shape[1], tie_mode, arr,
-                  len(flat) // 2, _stream(dev))
+        _lib.call("b200x_gather_records_prefixed", recv.data_ptr(), recv.shape[1], copy_bytes, idx.data_ptr(), idx.numel(),
+                  _ptr(sorted_keys), int(prefix_be), shift, used, out.data_ptr(), out.shape[1], tie_mode, _ptr(positions),
+                  0 if positions is None else positions.numel(), _stream(dev))
+
+
+def split_positions_by_chunk(idx: torch.Tensor, chunk_starts: Sequence[int], num_sources: int, num_chunks: int,
+                             chunk_sizes: Sequence[int]) -> List[torch.Tensor]:
+    """Output positions 0..n-1 grouped by the chunk their row (receive slot idx[i]) arrived in: one int32 tensor per
+    chunk (views of one buffer; chunk_sizes are known from the count tables)."""
+    dev = _require_cuda(idx)
+    n = idx.numel()
+    offs, run = [], 0
+    for sz in chunk_sizes:
+        offs.append(run)
+        run += int(sz)
+    if run != n:
+        raise ValueError("chunk sizes must add up to the number of rows")
+    positions = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+    starts = (ctypes.c_uint32 * len(chunk_starts))(*[int(x) for x in chunk_starts])
+    offsets = (ctypes.c_uint32 * num_chunks)(*offs)
+    with torch.cuda.device(dev):
+        st = _stream(dev)
+        args = (idx.data_ptr(), n, starts, num_sources, num_chunks, offsets, positions.data_ptr())
+        need = _lib.query_temp("b200x_split_positions_by_chunk", *args, stream=st)
+        temp = _temp(need, dev)
+        nb = ctypes.c_size_t(temp.numel())
+        _lib.call("b200x_split_positions_by_chunk", *args, temp.data_ptr(), ctypes.byref(nb), st)
+    return [positions[o:o + int(sz)] for o, sz in zip(offs, chunk_sizes)]
 
 
 def permute_rows(col: torch.Tensor, seed: int, inverse: bool = False) -> torch.Tensor:

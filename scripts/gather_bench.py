@@ -32,14 +32,22 @@ def timed(fn, reps=3):
 print("gather_rows_pitched 128 B            ", round(timed(lambda: ops.gather_records(recv, perm)), 3), "ms")
 print("prefixed, shift 0, one pass          ", round(timed(lambda: ops.gather_records_prefixed(recv, perm, out, 128, 128)), 3), "ms")
 print("prefixed, shift 8 copy 96, one pass  ", round(timed(lambda: ops.gather_records_prefixed(recv, perm, out, 96, 100, keys, True, 8)), 3), "ms")
+from ray_project_ray_b200 import _lib
+_lib.call("b200x_set_tuning", 2, 4)
+print("  the same with 4 loads in flight     ", round(timed(lambda: ops.gather_records_prefixed(recv, perm, out, 96, 100, keys, True, 8)), 3), "ms")
+_lib.call("b200x_set_tuning", 2, 2)
 print("  + tie_mode 1                       ", round(timed(lambda: ops.gather_records_prefixed(recv, perm, out, 96, 100, keys, True, 8, tie_mode=1)), 3), "ms")
 print("  tie_mode 2 only                    ", round(timed(lambda: ops.gather_records_prefixed(recv, perm, out, 96, 100, keys, True, 8, tie_mode=2)), 3), "ms")
 for K in (2, 4, 8):
     W = 8
+    per = n // W
+    starts = [r * per + c * per // K for r in range(W) for c in range(K)]
+    sizes = [sum((r * per + (c + 1) * per // K if c + 1 < K else (r + 1) * per if r + 1 < W else n) - starts[r * K + c]
+                 for r in range(W)) for c in range(K)]
+    print(f"  split positions into {K} chunk lists   ", round(timed(lambda: ops.split_positions_by_chunk(perm, starts, W, K, sizes)), 3), "ms")
+    lists = ops.split_positions_by_chunk(perm, starts, W, K, sizes)
+
     def passes():
         for c in range(K):
-            # chunk c of each of W sources: a slice of every source's slot range
-            per = n // W
-            rng = [(r * per + c * per // K, r * per + (c + 1) * per // K) for r in range(W)]
-            ops.gather_records_prefixed(recv, perm, out, 96, 100, keys, True, 8, tie_mode=1, ranges=rng)
-    print(f"  {K} passes over slot ranges (8 sources)", round(timed(passes), 3), "ms")
+            ops.gather_records_prefixed(recv, perm, out, 96, 100, keys, True, 8, positions=lists[c])
+    print(f"  {K} list passes                        ", round(timed(passes), 3), "ms")

@@ -291,11 +291,28 @@ def test_record_exchange_kernels_with_local_peers(n, world, cuda_device):
         recv, rkeys = bufs[d][3:], kbufs[d][3:].view(torch.uint64)
         perm, _, skeys = ops.argsort(rkeys, False, want_keys=True)
         out = torch.full((m, 128), 9, dtype=torch.uint8, device=cuda_device)
-        half = m // 2
-        ops.gather_records_prefixed(recv, perm, out, 96, 100, skeys, True, 8, tie_mode=1, ranges=[(0, half)])
-        ops.gather_records_prefixed(recv, perm, out, 96, 100, skeys, True, 8, tie_mode=1, ranges=[(half, half + 5), (half + 5, m)])
+        # the rows "arrive" in 3 chunks from 2 sources: positions are grouped by chunk, gathered chunk by chunk
+        a, b = m // 3, m // 2
+        starts = [0, a // 2, a, b, b + (m - b) // 4, b + (m - b) // 2]           # source 0: slots [0, b), source 1: [b, m)
+        sizes = [(a // 2 - 0) + (starts[4] - b), (a - a // 2) + (starts[5] - starts[4]), (b - a) + (m - starts[5])]
+        lists = ops.split_positions_by_chunk(perm, starts, 2, 3, sizes)
+        seen = np.sort(np.concatenate([x.cpu().numpy() for x in lists]))
+        np.testing.assert_array_equal(seen, np.arange(m))                        # every position in exactly one list
+        pn = perm.cpu().numpy().view(np.uint32)
+        for c, lst in enumerate(lists):
+            assert (np.diff(lst.cpu().numpy().astype(np.int64)) > 0).all()       # every list in ascending order
+            slots = pn[lst.cpu().numpy()]
+            in_c = ((slots >= starts[c]) & (slots < (starts[c + 1] if c < 2 else b))) | \
+                   ((slots >= starts[3 + c]) & (slots < (starts[4 + c] if c < 2 else m)))
+            assert in_c.all()
+            ops.gather_records_prefixed(recv, perm, out, 96, 100, skeys, True, 8, positions=lst)
         ops.fix_ties(skeys, perm, [ops.KeyPiece(recv[:, 0:2], 0, 2)], False)      # key bytes 8..9 lie at bytes 0..1 of a row
         ops.gather_records_prefixed(recv, perm, out, 96, 100, skeys, True, 8, tie_mode=2)
+        # the same in one pass, ties left out first (tie_mode 1) and put in afterwards
+        out2 = torch.full((m, 128), 9, dtype=torch.uint8, device=cuda_device)
+        ops.gather_records_prefixed(recv, perm, out2, 96, 100, skeys, True, 8, tie_mode=1)
+        ops.gather_records_prefixed(recv, perm, out2, 96, 100, skeys, True, 8, tie_mode=2)
+        np.testing.assert_array_equal(out2.cpu().numpy(), out.cpu().numpy())
         want = mine[orc.stable_argsort_bytes(mine[:, :10], False)]
         np.testing.assert_array_equal(out.cpu().numpy(), want)
     # shift 0 (whole rows, no prefix), all positions, record pitch that is not a power of two
