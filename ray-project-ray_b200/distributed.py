@@ -208,6 +208,40 @@ class P2PExchange:
         return starts, sizes
 
 
+    def fence(self) -> None:
+        """Device-side barrier over all ranks on the current stream (symmetric-memory signal pads): before
+        the first send = everyone is done reading the previous contents; after a send = all stores landed."""
+        self._handle.barrier(channel=0)
+
+    def send(self, names: Sequence[str]) -> None:
+        import ctypes
+
+        from . import _lib
+
+        with torch.cuda.device(self.dev):
+            st = torch.cuda.current_stream(self.dev).cuda_stream
+            for name in names:
+                col, order = self.columns[name]
+                (buf, h), row_bytes = self._bufs[name]
+                bases = (ctypes.c_void_p * self.world)(*[int(p) for p in h.buffer_ptrs])
+                if self.target is not None:
+                    _lib.call("b200x_scatter_rows_by_target", _contig(col).data_ptr(), row_bytes, self.target.data_ptr(),
+                              self.n, bases, self._ro, self.world, st)
+                    continue
+                _lib.call("b200x_scatter_rows_to_peers", _contig(col).data_ptr(), row_bytes,
+                          None if order is None else order.data_ptr(), self.n, self._so, bases, self._ro, self.world, st)
+
+    def view(self, names: Sequence[str]) -> Dict[str, torch.Tensor]:
+        out = {}
+        for name in names:
+            col, _ = self.columns[name]
+            (buf, _), row_bytes = self._bufs[name]
+            flat = buf[: self.n_recv * row_bytes]
+            shape = (self.n_recv,) + tuple(col.shape[1:])
+            out[name] = flat.view(col.dtype).reshape(shape) if col.dtype != torch.uint8 else flat.reshape(shape)
+        return out
+
+
 _side_streams: Dict[Tuple[int, int], torch.cuda.Stream] = {}
 
 
