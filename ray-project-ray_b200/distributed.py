@@ -310,15 +310,27 @@ def dist_sort(local: DeviceBlock, sort_key: SortKey, group=None, samples_per_ran
     return out
 
 
-def _gather_samples(sample_codes: torch.Tensor, samples_per_rank: int, world: int, dev, group) -> np.ndarray:
-    """all_gather every rank's (possibly fewer than samples_per_rank) sample codes -> one uint64 host array."""
-    padded = torch.full((samples_per_rank + 1,), -1, dtype=torch.int64, device=dev)
-    padded[0] = sample_codes.numel()
-    padded[1:1 + sample_codes.numel()] = sample_codes
+_HEADER = 8
+
+
+def _gather_samples(sample_codes: torch.Tensor, samples_per_rank: int, world: int, dev, group, header: Sequence[int] = ()):
+    """all_gather every rank's (possibly fewer than samples_per_rank) sample codes -> one uint64 host array, plus the
+    ranks' `header` values (up to 8 int64 per rank, gathered in the same collective) as an int64 [world, 8] array."""
+    padded = torch.full((_HEADER + samples_per_rank + 1,), -1, dtype=torch.int64, device=dev)
+    hdr = list(header) + [0] * (_HEADER - len(header))
+    padded[:_HEADER] = torch.tensor(hdr, dtype=torch.int64)
+    padded[_HEADER] = sample_codes.numel()
+    padded[_HEADER + 1:_HEADER + 1 + sample_codes.numel()] = sample_codes
     gathered = [torch.empty_like(padded) for _ in range(world)]
     dist.all_gather(gathered, padded, group=group)
     host = torch.stack(gathered).cpu().numpy()
-    return np.concatenate([row[1:1 + int(row[0])].view(np.uint64) for row in host])
+    codes = np.concatenate([row[_HEADER + 1:_HEADER + 1 + int(row[_HEADER])].view(np.uint64) for row in host])
+    return codes, host[:, :_HEADER]
+
+
+def _densify(block: DeviceBlock) -> DeviceBlock:
+    """The same block with every column dense (records dissolved, no key prefix columns)."""
+    return DeviceBlock({k: _contig(v) for k, v in block.columns.items()}, num_rows=block.num_rows, device=block.device)
 
 
 def _exchange_units(local: DeviceBlock, key_cols: Sequence[str]):
@@ -381,22 +393,33 @@ def _p2p_partition_sort(local: DeviceBlock, sort_key: SortKey, n: int, dev, grou
     key_cols = sort_key.get_columns()
     first, desc = key_cols[0], sort_key.get_descending()
     plan = _record_exchange_plan(local, key_cols, desc) if os.environ.get("B200X_RECORD_EXCHANGE", "1") != "0" else None
-    if plan is not None:
-        return _p2p_partition_sort_records(local, sort_key, n, dev, group, samples_per_rank, plan)
-    late = 1 < len(key_cols) <= 1 + ops.FIX_TIES_MAX_COLS and all(
-        c not in local.columns and c not in local.aux and BYTE_KEY_SEP in c for c in key_cols[1:])
-    early = [first] if late else list(key_cols)
-    units, groups, rest = _exchange_units(local, early)
-    keycol = units[first]
+    has_groups = bool(record_groups(local)[0])
+    keycol = local.key_column(first)
     if n > 0:
         m = min(samples_per_rank, n)
         pos = ((np.arange(m, dtype=np.float64) + 0.5) * (n / m)).astype(np.int64).astype(np.int32)
         sample_codes = ops.encode_keys(ops.gather(keycol, torch.from_numpy(pos).to(dev)), desc)
     else:
         sample_codes = torch.empty(0, dtype=torch.int64, device=dev)
-    splitters = choose_splitters(_gather_samples(sample_codes, samples_per_rank, world, dev, group), world)
+    # every rank must walk through the same protocol: the layout-dependent choices are agreed on in the collective
+    # that gathers the samples. A rank without rows cannot tell how the others lay out their records; if there is
+    # one, or the layouts differ, all ranks exchange plain dense columns.
+    header = [int(n > 0), int(plan is not None)] + ([plan["group"].pitch, plan["used"], plan["shift"], plan["copy"]] if plan else [0] * 4) \
+        + [int(has_groups)]
+    all_codes, hdrs = _gather_samples(sample_codes, samples_per_rank, world, dev, group, header)
+    splitters = choose_splitters(all_codes, world)
     if splitters.size != world - 1:   # no rank has any row
         splitters = np.full(world - 1, np.iinfo(np.uint64).max, dtype=np.uint64)
+    everyone_has_rows = bool(hdrs[:, 0].all())
+    if everyone_has_rows and bool(hdrs[:, 1].all()) and (hdrs[:, 2:6] == hdrs[0, 2:6]).all():
+        return _p2p_partition_sort_records(local, sort_key, n, dev, group, keycol, splitters, plan)
+    if hdrs[:, 6].any() and not (everyone_has_rows and hdrs[:, 6].all()):
+        local = _densify(local)
+    late = 1 < len(key_cols) <= 1 + ops.FIX_TIES_MAX_COLS and all(
+        c not in local.columns and c not in local.aux and BYTE_KEY_SEP in c for c in key_cols[1:])
+    early = [first] if late else list(key_cols)
+    units, groups, rest = _exchange_units(local, early)
+    keycol = units[first]
     sp = torch.from_numpy(splitters.view(np.int64)).to(dev)
     target, counts = ops.partition_targets(keycol, desc, sp)
     send_counts = [int(c) for c in counts.cpu().tolist()[:world]]
@@ -485,7 +508,8 @@ def _record_exchange_plan(local: DeviceBlock, key_cols: Sequence[str], desc: boo
     return {"group": g, "used": used, "shift": shift, "be": be, "copy": min(copy, g.pitch), "base": base if shift else None}
 
 
-def _p2p_partition_sort_records(local: DeviceBlock, sort_key: SortKey, n: int, dev, group, samples_per_rank: int, plan) -> DeviceBlock:
+def _p2p_partition_sort_records(local: DeviceBlock, sort_key: SortKey, n: int, dev, group, keycol: torch.Tensor, splitters: np.ndarray,
+                                plan) -> DeviceBlock:
     """Partition-first distributed sort of a block held as records, with the transfer and the last gather overlapped:
       1. first key column (dense) -> splitters -> per-row (owner, slot) targets, as in `_p2p_partition_sort`;
       2. the key column is exchanged and the received keys are sorted on a second stream;
@@ -506,14 +530,7 @@ def _p2p_partition_sort_records(local: DeviceBlock, sort_key: SortKey, n: int, d
     g, used, shift, copy = plan["group"], plan["used"], plan["shift"], plan["copy"]
     pitch = g.pitch
     in_group = set(g.members)
-    keycol = local.key_column(first)
     extra = [c for c in local.column_names if c not in in_group and c != first]   # columns outside the record: sent whole, gathered last
-    m = min(samples_per_rank, n)
-    pos = ((np.arange(m, dtype=np.float64) + 0.5) * (n / m)).astype(np.int64).astype(np.int32)
-    sample_codes = ops.encode_keys(ops.gather(keycol, torch.from_numpy(pos).to(dev)), desc)
-    splitters = choose_splitters(_gather_samples(sample_codes, samples_per_rank, world, dev, group), world)
-    if splitters.size != world - 1:
-        splitters = np.full(world - 1, np.iinfo(np.uint64).max, dtype=np.uint64)
     sp = torch.from_numpy(splitters.view(np.int64)).to(dev)
     target, counts, tile_table = ops.partition_targets(keycol, desc, sp, want_tile_table=True)
     tiles = tile_table.shape[0]
