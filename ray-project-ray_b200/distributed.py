@@ -152,7 +152,7 @@ class P2PExchange:
 
     def __init__(self, columns: Dict[str, Tuple[torch.Tensor, Optional[torch.Tensor]]], n: int,
                  send_counts: Optional[Sequence[int]], dev: torch.device, group=None, target: Optional[torch.Tensor] = None,
-                 chunk_table: Optional[torch.Tensor] = None):
+                 chunk_table: Optional[torch.Tensor] = None, recv_row_bytes: Optional[Dict[str, int]] = None):
         import ctypes
 
         self.columns, self.n, self.dev, self.group = columns, n, dev, group
@@ -184,12 +184,16 @@ class P2PExchange:
             row_bytes = col.element_size()
             for d in col.shape[1:]:
                 row_bytes *= int(d)
+            row_bytes = (recv_row_bytes or {}).get(name, row_bytes)   # records arrive without padding / key prefix
             self._bufs[name] = (_symm_buffer(slot, cap_rows * row_bytes, dev, group), row_bytes)
         self._handle = next(iter(self._bufs.values()))[0][1]
 
     def send_records(self, name: str, copy_bytes: int, src_offset: int, row0: int, nrows: int) -> None:
         """Rows [row0, row0 + nrows) of the record unit `name`: bytes [src_offset, src_offset + copy_bytes) of every
-        record go to the start of the row's slot in the owner's receive buffer (slots one record pitch apart)."""
+        record go to the row's slot in the owner's receive buffer. Slots lie copy_bytes apart (dense): the rows an
+        owner receives from one sender are consecutive slots, so they leave as whole 128-byte lines - NVLink moved a
+        line per store however few of its bytes were written (5.3 G lines/s measured at 8 GPUs, whether 96 or 128 bytes
+        of each 128-byte slot were sent), so the padding must not exist at the destination either."""
         col, _ = self.columns[name]
         (buf, h), pitch = self._bufs[name]
         ops.scatter_records_by_target(col, self.target, [int(p) for p in h.buffer_ptrs], [int(x) for x in self._ro], pitch,
@@ -237,6 +241,9 @@ class P2PExchange:
             col, _ = self.columns[name]
             (buf, _), row_bytes = self._bufs[name]
             flat = buf[: self.n_recv * row_bytes]
+            if col.dim() == 2 and col.dtype == torch.uint8 and row_bytes != col.shape[1]:   # records received dense
+                out[name] = flat.reshape(self.n_recv, row_bytes)
+                continue
             shape = (self.n_recv,) + tuple(col.shape[1:])
             out[name] = flat.view(col.dtype).reshape(shape) if col.dtype != torch.uint8 else flat.reshape(shape)
         return out
@@ -543,7 +550,7 @@ def _p2p_partition_sort_records(local: DeviceBlock, sort_key: SortKey, n: int, d
     cols = {first: (keycol, None), "\x00rec": (g.rec, None)}
     for c in extra:
         cols[c] = (_contig(local.columns[c]), None)
-    ex = P2PExchange(cols, n, None, dev, group, target=target, chunk_table=table)
+    ex = P2PExchange(cols, n, None, dev, group, target=target, chunk_table=table, recv_row_bytes={"\x00rec": copy})
     main = torch.cuda.current_stream(dev)
     ex.fence()
     ex.send([first])
