@@ -49,11 +49,11 @@ TAG_MULT = 0x9E3779B97F4A7C15 - (1 << 64)   # odd 64-bit constant (as int64): ta
 # per row ncu measured for it (profiles/, dram__bytes_read.sum + dram__bytes_write.sum; None = not captured).
 KERNELS = {
     0: ("onesweep_pass_kernel", 22.0, 26.0),         # HYBRID: pass A reads 8 writes 12, pass B reads 12 writes 12
-    1: ("gather_rows_pitched_kernel (128-byte records)", 4 + 2 * ROW_BYTES, None),  # index + read record + write record
+    1: ("record gather (gather_rows_pitched_kernel / gather_records_list_kernel, 128-byte records)", 4 + 2 * ROW_BYTES, None),  # index + read record + write record
     2: ("finish_runs_kernel", 12 + 4 + 8, 23.5),      # read pair, write row index + decoded key
     3: ("digit2_hist_kernel", 8.0, 8.0),              # read key column
     6: ("hist_kernel", 8.0, None),
-    7: ("scatter_rows_staged_kernel (peer exchange)", None, None),   # bytes per row depend on the column: see `nvlink`
+    7: ("peer scatter (scatter_rows_staged_kernel for the keys, scatter_records_staged_kernel for the records)", None, None),
 }
 
 
@@ -535,11 +535,12 @@ def run_ours(args):
             pk_src = "nominal NVLink 5, 900 GB/s per direction and GPU"
         else:
             ach, pk, alg, pk_src = 2 * ROW_BYTES * n / (ms_step / 1e3) / 1e9, peak, 2 * ROW_BYTES * n, peak_src
-        # bytes this GPU really stores into its peers per step: whole 128-byte records + the two key chunk columns
-        traffic = (RECORD_PITCH + 8 + 2) * n * (world - 1) / world
+        # bytes this GPU really stores into its peers per step: 96 bytes of every record (the record without its
+        # padding and without the 8-byte key prefix) + the 8-byte key prefix column, for (G-1)/G of its rows
+        traffic = (96 + 8) * n * (world - 1) / world
         roof = {"bound": bound, "achieved": ach, "peak": pk, "unit": "GB/s", "frac": ach / pk, "traffic": traffic,
-                "traffic_note": "bytes one GPU stores into peer memory per step (128-byte records + 8- and 2-byte key "
-                                "chunks for (G-1)/G of its rows), computed; not a link counter",
+                "traffic_note": "bytes one GPU stores into peer memory per step (96 of every record's 128 bytes + the 8-byte "
+                                "key prefix, for (G-1)/G of its rows), computed; not a link counter",
                 "peak_source": pk_src, "algorithmic_bytes_per_step": alg, "ms_per_step": ms_step,
                 "roofline_ms": max(t_hbm, t_nvl) * 1e3, "hbm_roofline_ms": t_hbm * 1e3, "nvlink_roofline_ms": t_nvl * 1e3,
                 "note": "op-level: algorithmic bytes / step time against the slower roofline (SURVEY.md 8d); rank 0's "

@@ -276,6 +276,8 @@ scatter_rows_by_target_kernel(const V* __restrict__ src, const uint32_t* __restr
 int g_scatter_blocks_per_sm = 0;
 // b200x_set_tuning(2, k): loads in flight per thread of the record gather (2 or 4)
 int g_gather_chains = 2;
+// b200x_set_tuning(3, k): most blocks per SM the record gather launches (it shares the SMs with the transfer)
+int g_gather_blocks_per_sm = 16;
 
 constexpr int ST_THREADS = 256;
 constexpr int ST_MAX_TILE = 1024;
@@ -1030,7 +1032,7 @@ extern "C" int b200x_gather_records_prefixed(const void* recv, size_t recv_pitch
     return B200X_ERR_ALIGN;
   }
   const uint32_t dst_vec = (uint32_t)(dst_pitch / 16);
-  const uint64_t cap = (uint64_t)sm_count() * 16;
+  const uint64_t cap = (uint64_t)sm_count() * g_gather_blocks_per_sm;
   prof_begin(stream, PROF_GATHER);
   if (tie_mode == 0) {
     const uint64_t m = positions != nullptr ? num_positions : n;

@@ -541,7 +541,9 @@ def _p2p_partition_sort_records(local: DeviceBlock, sort_key: SortKey, n: int, d
     sp = torch.from_numpy(splitters.view(np.int64)).to(dev)
     target, counts, tile_table = ops.partition_targets(keycol, desc, sp, want_tile_table=True)
     tiles = tile_table.shape[0]
-    K = int(os.environ.get("B200X_EXCHANGE_CHUNKS", "4")) if n >= int(os.environ.get("B200X_EXCHANGE_CHUNK_MIN_ROWS", 1 << 22)) else 1
+    # chunks: measured at 8 GPUs x 125 M gensort records: 1 -> 30.6 ms, 2 -> 30.4, 4 -> 31.8, 8 -> 33.6 per sort (the
+    # gathers that run next to the transfer slow it by about what they hide; every chunk ends in a barrier of all ranks)
+    K = int(os.environ.get("B200X_EXCHANGE_CHUNKS", "2")) if n >= int(os.environ.get("B200X_EXCHANGE_CHUNK_MIN_ROWS", 1 << 22)) else 1
     K = max(1, min(K, tiles))
     cut_tiles = [c * tiles // K for c in range(K)]
     rows_at = [t * ops.PT_TILE_ROWS for t in cut_tiles] + [n]
@@ -595,10 +597,16 @@ def _p2p_partition_sort_records(local: DeviceBlock, sort_key: SortKey, n: int, d
         if K > 1:       # output positions grouped by the chunk their row arrives in (known as soon as the keys are sorted)
             starts, sizes = ex.chunk_layout()
             lists = ops.split_positions_by_chunk(perm2, starts, world, K, sizes)
+        # while chunks are still crossing NVLink the gathers leave block slots to the transfer kernel
+        gather_bps = int(os.environ.get("B200X_GATHER_BLOCKS_PER_SM", "6"))
         for c in range(K):
             gstream.wait_event(chunk_ev[c])
-            ops.gather_records_prefixed(recv_rec, perm2, out, copy, used, probe if shift else None, plan["be"], shift,
-                                        positions=lists[c])
+            _lib.call("b200x_set_tuning", 3, gather_bps if c + 1 < K else 16)
+            try:
+                ops.gather_records_prefixed(recv_rec, perm2, out, copy, used, probe if shift else None, plan["be"], shift,
+                                            positions=lists[c])
+            finally:
+                _lib.call("b200x_set_tuning", 3, 16)
         verdict = None
         if later:
             pieces = []
