@@ -89,7 +89,8 @@ int b200x_radix_argsort(const void* keys, int key_type, int descending, const ui
  * memory); default 2^22. key 1: most blocks per SM the staged peer scatter launches (0 = one block per tile);
  * a small value leaves room for work running next to the transfer on another stream. key 2: loads in flight per
  * thread of b200x_gather_records_prefixed (2 or 4); key 3: most blocks per SM it launches (default 16; fewer leave
- * room for a transfer running next to it). Results never depend on any of them. */
+ * room for a transfer running next to it); key 4: b200x_scatter_records_by_target writes an owner's rows of a tile
+ * with one bulk copy from shared memory (1, default) or with 16-byte stores (0). Results never depend on any of them. */
 int b200x_set_tuning(int key, long long value);
 
 /* b200x_radix_argsort for callers that cannot allocate device memory. (No counterpart in the

@@ -278,6 +278,8 @@ int g_scatter_blocks_per_sm = 0;
 int g_gather_chains = 2;
 // b200x_set_tuning(3, k): most blocks per SM the record gather launches (it shares the SMs with the transfer)
 int g_gather_blocks_per_sm = 16;
+// b200x_set_tuning(4, 0 | 1): the record scatter writes an owner's rows with one bulk copy (1, default) or with 16-byte stores (0)
+int g_scatter_bulk = 1;
 
 constexpr int ST_THREADS = 256;
 constexpr int ST_MAX_TILE = 1024;
@@ -669,7 +671,17 @@ extern "C" int b200x_scatter_rows_by_target(const void* src, size_t row_bytes, c
 // key equals a neighbour's (their order is only final after b200x_fix_ties).
 namespace b200x {
 
-template <typename LV>
+// BULK (dst_pitch == copy_bytes: an owner's rows of a tile are one contiguous byte range at the destination): the
+// write-out is ONE bulk copy per owner, shared memory -> the peer's buffer, issued by one thread and carried out by
+// the SM's copy unit (cp.async.bulk, SASS UBLKCP) instead of a loop of 16-byte stores through the registers of all
+// threads: the block's warps are free again as soon as the copies are queued, and the stores leave in large bursts.
+__device__ __forceinline__ void bulk_store_to_global(void* gdst, const void* ssrc, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst),
+               "r"((uint32_t)__cvta_generic_to_shared(ssrc)), "r"(bytes)
+               : "memory");
+}
+
+template <typename LV, bool BULK>
 __global__ void __launch_bounds__(ST_THREADS)
 scatter_records_staged_kernel(const unsigned char* __restrict__ src, uint64_t src_pitch, uint32_t copy_bytes,
                               const uint32_t* __restrict__ target, const PeerPlan p, uint64_t dst_pitch, uint64_t n,
@@ -730,13 +742,30 @@ scatter_records_staged_kernel(const unsigned char* __restrict__ src, uint64_t sr
       *reinterpret_cast<LV*>(sdata + (uint32_t)slp[lr] * copy_bytes + c * (uint32_t)sizeof(LV)) =
           *reinterpret_cast<const LV*>(tsrc + (uint64_t)lr * src_pitch + c * sizeof(LV));
     }
-    __syncthreads();
-    const uint32_t stores = rows * vpr;
-    for (uint32_t t = threadIdx.x; t < stores; t += ST_THREADS) {  // owner by owner, consecutive slots
-      const uint32_t i = t / vpr, c = t - i * vpr;
-      reinterpret_cast<uint4*>(sdst[i])[c] = reinterpret_cast<const uint4*>(sdata + i * copy_bytes)[c];
+    if (BULK) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the staged rows become visible to the copy unit
+      __syncthreads();
+      if (threadIdx.x < MAX_PEERS && s_cnt[threadIdx.x] != 0) {
+        const uint32_t d = threadIdx.x;
+        bulk_store_to_global(p.base[d] + (p.row_off[d] + s_min[d]) * dst_pitch, sdata + s_off[d] * copy_bytes,
+                             s_cnt[d] * copy_bytes);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // shared memory may be rewritten
+      }
+      __syncthreads();
+    } else {
+      __syncthreads();
+      const uint32_t stores = rows * vpr;
+      for (uint32_t t = threadIdx.x; t < stores; t += ST_THREADS) {  // owner by owner, consecutive slots
+        const uint32_t i = t / vpr, c = t - i * vpr;
+        reinterpret_cast<uint4*>(sdst[i])[c] = reinterpret_cast<const uint4*>(sdata + i * copy_bytes)[c];
+      }
+      __syncthreads();
     }
-    __syncthreads();
+  }
+  if (BULK) {
+    if (threadIdx.x < MAX_PEERS) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // all copies have been performed
+    __threadfence_system();
   }
 }
 
@@ -1000,13 +1029,18 @@ extern "C" int b200x_scatter_records_by_target(const void* src, size_t src_pitch
   if (g_scatter_blocks_per_sm > 0 && gtiles > (uint64_t)sm_count() * g_scatter_blocks_per_sm)
     gtiles = (uint64_t)sm_count() * g_scatter_blocks_per_sm;
   const bool wide = (((uintptr_t)src | src_pitch) & 15) == 0;
+  const bool bulk = dst_pitch == copy_bytes && g_scatter_bulk != 0;
+  const unsigned char* s8 = (const unsigned char*)src;
+  const uint32_t cb = (uint32_t)copy_bytes, g = (uint32_t)gtiles;
   prof_begin(stream, PROF_SCATTER);
-  if (wide)
-    scatter_records_staged_kernel<uint4><<<(uint32_t)gtiles, ST_THREADS, smem, stream>>>(
-        (const unsigned char*)src, src_pitch, (uint32_t)copy_bytes, target, p, dst_pitch, n, tile_rows);
+  if (wide && bulk)
+    scatter_records_staged_kernel<uint4, true><<<g, ST_THREADS, smem, stream>>>(s8, src_pitch, cb, target, p, dst_pitch, n, tile_rows);
+  else if (wide)
+    scatter_records_staged_kernel<uint4, false><<<g, ST_THREADS, smem, stream>>>(s8, src_pitch, cb, target, p, dst_pitch, n, tile_rows);
+  else if (bulk)
+    scatter_records_staged_kernel<uint64_t, true><<<g, ST_THREADS, smem, stream>>>(s8, src_pitch, cb, target, p, dst_pitch, n, tile_rows);
   else
-    scatter_records_staged_kernel<uint64_t><<<(uint32_t)gtiles, ST_THREADS, smem, stream>>>(
-        (const unsigned char*)src, src_pitch, (uint32_t)copy_bytes, target, p, dst_pitch, n, tile_rows);
+    scatter_records_staged_kernel<uint64_t, false><<<g, ST_THREADS, smem, stream>>>(s8, src_pitch, cb, target, p, dst_pitch, n, tile_rows);
   prof_end(stream);
   B200X_LAUNCH_CHECK("scatter_records_staged_kernel");
   return B200X_OK;

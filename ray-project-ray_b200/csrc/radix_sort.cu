@@ -1365,7 +1365,7 @@ static TempLayout temp_layout(size_t n, int npass) {
 
 using namespace b200x;
 
-namespace b200x { extern int g_scatter_blocks_per_sm; extern int g_gather_chains; extern int g_gather_blocks_per_sm; }
+namespace b200x { extern int g_scatter_blocks_per_sm; extern int g_gather_chains; extern int g_gather_blocks_per_sm; extern int g_scatter_bulk; }
 
 extern "C" int b200x_set_tuning(int key, long long value) {
   if (key == 0 && value >= 0) {
@@ -1374,6 +1374,10 @@ extern "C" int b200x_set_tuning(int key, long long value) {
   }
   if (key == 1 && value >= 0 && value <= 32) {
     b200x::g_scatter_blocks_per_sm = (int)value;
+    return B200X_OK;
+  }
+  if (key == 4 && (value == 0 || value == 1)) {
+    b200x::g_scatter_bulk = (int)value;
     return B200X_OK;
   }
   if (key == 3 && value >= 1 && value <= 32) {

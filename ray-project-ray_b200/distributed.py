@@ -571,6 +571,7 @@ def _p2p_partition_sort_records(local: DeviceBlock, sort_key: SortKey, n: int, d
     out = torch.empty((n_recv, pitch), dtype=torch.uint8, device=dev)
     # the transfer runs on two blocks per SM (it is link-bound) so that the sort and the gathers fit next to it
     _lib.call("b200x_set_tuning", 1, int(os.environ.get("B200X_PAYLOAD_BLOCKS_PER_SM", "2")))
+    _lib.call("b200x_set_tuning", 4, int(os.environ.get("B200X_SCATTER_BULK", "1")))
     chunk_ev = []
     try:
         ex.send(extra)

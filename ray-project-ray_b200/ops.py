@@ -118,15 +118,21 @@ def gather(col: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
 
 def gather_records(rec: torch.Tensor, idx: torch.Tensor, row_bytes: Optional[int] = None) -> torch.Tensor:
     """out[i, :row_bytes] = rec[idx[i], :row_bytes] for a record buffer `rec` ([n, pitch] uint8, pitch and row_bytes
-    multiples of 16); the result has the same pitch."""
+    multiples of 16); the result has the same pitch. Pitches of 16 .. 512 bytes that are powers of two take the
+    lane-cooperative record gather (b200x_gather_records_prefixed without a prefix: 5.9 against 6.2 ms per 125 M
+    128-byte records), the others b200x_gather_rows_pitched."""
     dev = _require_cuda(rec, idx)
     n, pitch = idx.numel(), rec.shape[1]
     row_bytes = pitch if row_bytes is None else row_bytes
     out = torch.empty((n, pitch), dtype=torch.uint8, device=dev)
     if n:
         with torch.cuda.device(dev):
-            _lib.call("b200x_gather_rows_pitched", rec.data_ptr(), pitch, idx.data_ptr(), n, out.data_ptr(), pitch,
-                      row_bytes, _stream(dev))
+            if row_bytes == pitch and 16 <= pitch <= 512 and pitch & (pitch - 1) == 0:
+                _lib.call("b200x_gather_records_prefixed", rec.data_ptr(), pitch, pitch, idx.data_ptr(), n, None, 0, 0, pitch,
+                          out.data_ptr(), pitch, 0, None, 0, _stream(dev))
+            else:
+                _lib.call("b200x_gather_rows_pitched", rec.data_ptr(), pitch, idx.data_ptr(), n, out.data_ptr(), pitch,
+                          row_bytes, _stream(dev))
     return out
 
 

@@ -279,6 +279,19 @@ def test_record_exchange_kernels_with_local_peers(n, world, cuda_device):
                                       src_offset=8, row0=lo, nrows=hi_row - lo)
     full = np.zeros((n, 128), dtype=np.uint8)
     full[:, :10], full[:, 10:100] = key, payload
+    # dense slots (96 bytes apart, as the exchange receives them): written by one bulk copy per owner and tile, or by
+    # 16-byte stores - the same bytes either way, nothing before the first or after the last slot
+    for bulk in (1, 0):
+        _lib.call("b200x_set_tuning", 4, bulk)
+        dense = [torch.full((int(cnt[d]) + 5, 96), 7, dtype=torch.uint8, device=cuda_device) for d in range(world)]
+        try:
+            ops.scatter_records_by_target(rec, target, [b.data_ptr() for b in dense], [2] * world, 96, copy_bytes=96, src_offset=8)
+        finally:
+            _lib.call("b200x_set_tuning", 4, 1)
+        for d in range(world):
+            got = dense[d].cpu().numpy()
+            np.testing.assert_array_equal(got[2:2 + int(cnt[d])], full[owner == d][:, 8:104])
+            assert (got[:2] == 7).all() and (got[2 + int(cnt[d]):] == 7).all()
     for d in range(world):
         got = bufs[d].cpu().numpy()
         mine = full[owner == d]
