@@ -13,7 +13,10 @@
  *     required size in *temp_bytes, then again with a 256-byte aligned buffer.
  *   - `stream` is a cudaStream_t (NULL = legacy default stream). Calls are
  *     asynchronous: they enqueue work and return without synchronising.
- *   - The CUDA device must be current on the calling thread (cudaSetDevice).
+ *   - Every entry point that launches work makes the GPU that owns its first device buffer current for the
+ *     duration of the call and restores the caller's current device before it returns, so it may be called from
+ *     any thread (the reference's executor runs the bulk function on helper threads). `stream` must be a stream of
+ *     that GPU (or NULL).
  *   - Return value: 0 = OK; > 0 = argument error (B200X_ERR_*);
  *     < 0 = -(cudaError_t). b200x_last_error_string() gives the message of the
  *     last failure on the calling thread. Nothing throws across the ABI.

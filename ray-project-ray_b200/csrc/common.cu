@@ -26,6 +26,22 @@ int cuda_fail(cudaError_t e, const char* what) {
   return -(int)e;
 }
 
+DeviceGuard::DeviceGuard(const void* ptr) {
+  if (ptr == nullptr) return;
+  cudaPointerAttributes attr;
+  if (cudaPointerGetAttributes(&attr, ptr) != cudaSuccess) {
+    cudaGetLastError();   // not a CUDA pointer: nothing to do, and no sticky error for the caller
+    return;
+  }
+  if (attr.type != cudaMemoryTypeDevice && attr.type != cudaMemoryTypeManaged) return;
+  if (cudaGetDevice(&prev) != cudaSuccess) return;
+  if (attr.device != prev && cudaSetDevice(attr.device) == cudaSuccess) switched = true;
+}
+
+DeviceGuard::~DeviceGuard() {
+  if (switched) cudaSetDevice(prev);
+}
+
 int sm_count() {
   static thread_local int cached_dev = -1;
   static thread_local int cached_sms = 148;

@@ -40,6 +40,19 @@ static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; 
 // Number of SMs of the current device (cached per device).
 int sm_count();
 
+// Every entry point runs on the GPU that owns its (first local) buffer, whatever device is current on the calling
+// thread - the reference's executor calls the bulk function from helper threads, which start out on device 0 - and
+// leaves the caller's current device as it found it. A NULL or host pointer leaves everything alone.
+struct DeviceGuard {
+  int prev = -1;
+  bool switched = false;
+  explicit DeviceGuard(const void* ptr);
+  ~DeviceGuard();
+  DeviceGuard(const DeviceGuard&) = delete;
+  DeviceGuard& operator=(const DeviceGuard&) = delete;
+};
+#define B200X_ON_DEVICE_OF(ptr) ::b200x::DeviceGuard _b200x_device_guard((const void*)(ptr))
+
 // Every kernel launch of the library is counted (b200x_launch_count).
 void count_launch();
 

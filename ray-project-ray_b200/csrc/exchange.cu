@@ -66,6 +66,7 @@ using namespace b200x;
 extern "C" int b200x_scatter_rows_to_peers(const void* src, size_t row_bytes, const uint32_t* perm, size_t n,
                                            const unsigned long long* send_off_host, void* const* peer_base_host,
                                            const unsigned long long* peer_row_off_host, int world, void* stream_) {
+  B200X_ON_DEVICE_OF(src);
   cudaStream_t stream = (cudaStream_t)stream_;
   if (world <= 0 || world > MAX_PEERS) {
     set_error("b200x_scatter_rows_to_peers: world=%d out of range [1, %d]", world, MAX_PEERS);
@@ -529,6 +530,7 @@ scatter_rows_realign_kernel(const unsigned char* __restrict__ src, const uint32_
 extern "C" int b200x_partition_targets(const void* keys, int key_type, int descending, size_t n,
                                        const uint64_t* splitter_codes, int num_splitters, uint32_t* target_out,
                                        unsigned long long* counts_out, void* temp, size_t* temp_bytes, void* stream_) {
+  B200X_ON_DEVICE_OF(counts_out);
   cudaStream_t stream = (cudaStream_t)stream_;
   if (temp_bytes == nullptr) {
     set_error("b200x_partition_targets: temp_bytes is NULL");
@@ -578,6 +580,7 @@ extern "C" int b200x_partition_targets(const void* keys, int key_type, int desce
 extern "C" int b200x_scatter_rows_by_target(const void* src, size_t row_bytes, const uint32_t* target, size_t n,
                                             void* const* peer_base_host, const unsigned long long* peer_row_off_host,
                                             int world, void* stream_) {
+  B200X_ON_DEVICE_OF(src);
   cudaStream_t stream = (cudaStream_t)stream_;
   if (world <= 0 || world > MAX_PEERS) {
     set_error("b200x_scatter_rows_by_target: world=%d out of range [1, %d]", world, MAX_PEERS);
@@ -995,6 +998,7 @@ extern "C" int b200x_scatter_records_by_target(const void* src, size_t src_pitch
                                                size_t n, void* const* peer_base_host,
                                                const unsigned long long* peer_row_off_host, size_t dst_pitch, int world,
                                                void* stream_) {
+  B200X_ON_DEVICE_OF(src);
   cudaStream_t stream = (cudaStream_t)stream_;
   if (world <= 0 || world > MAX_PEERS) {
     set_error("b200x_scatter_records_by_target: world=%d out of range [1, %d]", world, MAX_PEERS);
@@ -1050,6 +1054,7 @@ extern "C" int b200x_gather_records_prefixed(const void* recv, size_t recv_pitch
                                              size_t n, const uint64_t* sorted_keys, int prefix_be, size_t shift,
                                              size_t used_bytes, void* dst, size_t dst_pitch, int tie_mode,
                                              const uint32_t* positions, size_t num_positions, void* stream_) {
+  B200X_ON_DEVICE_OF(idx);
   cudaStream_t stream = (cudaStream_t)stream_;
   if (n == 0 || (positions != nullptr && num_positions == 0)) return B200X_OK;
   if (recv == nullptr || idx == nullptr || dst == nullptr || (shift != 0 && shift != 8) || (shift == 8 && sorted_keys == nullptr) ||
@@ -1103,6 +1108,7 @@ extern "C" int b200x_gather_records_prefixed(const void* recv, size_t recv_pitch
 extern "C" int b200x_split_positions_by_chunk(const uint32_t* idx, size_t n, const uint32_t* chunk_starts_host, int num_sources,
                                               int num_chunks, const uint32_t* list_offsets_host, uint32_t* positions_out,
                                               void* temp, size_t* temp_bytes, void* stream_) {
+  B200X_ON_DEVICE_OF(positions_out);
   cudaStream_t stream = (cudaStream_t)stream_;
   if (temp_bytes == nullptr) {
     set_error("b200x_split_positions_by_chunk: temp_bytes is NULL");

@@ -194,6 +194,7 @@ using namespace b200x;
 
 extern "C" int b200x_gather_rows(const void* src, size_t row_bytes, const uint32_t* idx, size_t n, void* dst,
                                  void* stream_) {
+  B200X_ON_DEVICE_OF(src);
   cudaStream_t stream = (cudaStream_t)stream_;
   if (n == 0 || row_bytes == 0) return B200X_OK;
   if (src == nullptr || idx == nullptr || dst == nullptr) {
@@ -234,6 +235,7 @@ extern "C" int b200x_gather_rows(const void* src, size_t row_bytes, const uint32
 
 extern "C" int b200x_gather_rows_pitched(const void* src, size_t src_pitch, const uint32_t* idx, size_t n, void* dst,
                                          size_t dst_pitch, size_t row_bytes, void* stream_) {
+  B200X_ON_DEVICE_OF(src);
   cudaStream_t stream = (cudaStream_t)stream_;
   if (n == 0 || row_bytes == 0) return B200X_OK;
   if (src == nullptr || idx == nullptr || dst == nullptr) {
@@ -264,6 +266,7 @@ extern "C" int b200x_gather_rows_pitched(const void* src, size_t src_pitch, cons
 
 extern "C" int b200x_copy_rows_2d(const void* src, size_t src_pitch, void* dst, size_t dst_pitch, size_t row_bytes,
                                   size_t n, void* stream_) {
+  B200X_ON_DEVICE_OF(src);
   cudaStream_t stream = (cudaStream_t)stream_;
   if (n == 0 || row_bytes == 0) return B200X_OK;
   if (src == nullptr || dst == nullptr || row_bytes > src_pitch || row_bytes > dst_pitch || row_bytes > (1u << 20)) {
@@ -291,6 +294,7 @@ extern "C" int b200x_copy_rows_2d(const void* src, size_t src_pitch, void* dst, 
 
 extern "C" int b200x_gather_columns8(const void* const* srcs, void* const* dsts, int ncols, const uint32_t* idx,
                                      size_t n, void* stream_) {
+  B200X_ON_DEVICE_OF(idx);
   cudaStream_t stream = (cudaStream_t)stream_;
   if (n == 0 || ncols == 0) return B200X_OK;
   if (srcs == nullptr || dsts == nullptr || idx == nullptr || ncols < 0) {
@@ -315,6 +319,7 @@ extern "C" int b200x_gather_columns8(const void* const* srcs, void* const* dsts,
 }
 
 extern "C" int b200x_iota_u32(uint32_t* out, size_t n, uint32_t start, void* stream_) {
+  B200X_ON_DEVICE_OF(out);
   if (n == 0) return B200X_OK;
   if (out == nullptr) {
     set_error("b200x_iota_u32: NULL pointer");

@@ -711,6 +711,7 @@ extern "C" int b200x_group_boundaries_multi(const uint64_t* const* codes_host, i
 
 extern "C" int b200x_group_boundaries(const uint64_t* codes, size_t n, uint32_t* group_starts, uint32_t* num_groups_out,
                                       void* temp, size_t* temp_bytes, void* stream_) {
+  B200X_ON_DEVICE_OF(group_starts);
   const uint64_t* one[1] = {codes};
   return b200x_group_boundaries_multi(one, 1, n, group_starts, num_groups_out, temp, temp_bytes, stream_);
 }
@@ -718,6 +719,7 @@ extern "C" int b200x_group_boundaries(const uint64_t* codes, size_t n, uint32_t*
 extern "C" int b200x_group_boundaries_multi(const uint64_t* const* codes_host, int num_cols, size_t n,
                                             uint32_t* group_starts, uint32_t* num_groups_out, void* temp,
                                             size_t* temp_bytes, void* stream_) {
+  B200X_ON_DEVICE_OF(group_starts);
   if (codes_host == nullptr || num_cols < 1 || num_cols > MAX_GROUP_COLS) {
     set_error("b200x_group_boundaries_multi: 1..%d key columns", MAX_GROUP_COLS);
     return B200X_ERR_ARG;
@@ -773,6 +775,7 @@ extern "C" int b200x_segmented_reduce(const uint32_t* group_starts, const uint32
                                       const void* values, int value_type, size_t n, const double* center,
                                       const int64_t* weights, const double* addend, void* sum_out, void* min_out,
                                       void* max_out, void* temp, size_t* temp_bytes, void* stream_) {
+  B200X_ON_DEVICE_OF(values);
   cudaStream_t stream = (cudaStream_t)stream_;
   if (temp_bytes == nullptr) {
     set_error("b200x_segmented_reduce: temp_bytes is NULL");
@@ -812,6 +815,7 @@ extern "C" int b200x_segmented_reduce(const uint32_t* group_starts, const uint32
 
 extern "C" int b200x_group_counts(const uint32_t* group_starts, const uint32_t* num_groups, size_t max_groups, size_t n,
                                   int64_t* counts_out, void* stream_) {
+  B200X_ON_DEVICE_OF(counts_out);
   if (max_groups == 0) return B200X_OK;
   if (group_starts == nullptr || num_groups == nullptr || counts_out == nullptr) {
     set_error("b200x_group_counts: NULL pointer");
@@ -827,6 +831,7 @@ extern "C" int b200x_group_counts(const uint32_t* group_starts, const uint32_t* 
 
 extern "C" int b200x_finalize_groups(const void* sum, int value_type, const int64_t* counts, size_t num_groups, int mode,
                                      int ddof, double* out, void* stream_) {
+  B200X_ON_DEVICE_OF(out);
   if (num_groups == 0) return B200X_OK;
   if (sum == nullptr || counts == nullptr || out == nullptr || (mode != 0 && mode != 1) ||
       (value_type != B200X_VAL_I64 && value_type != B200X_VAL_F64)) {
@@ -843,6 +848,7 @@ extern "C" int b200x_finalize_groups(const void* sum, int value_type, const int6
 
 extern "C" int b200x_absmax_groups(const void* min_in, const void* max_in, int value_type, size_t num_groups, void* out,
                                    void* stream_) {
+  B200X_ON_DEVICE_OF(out);
   if (num_groups == 0) return B200X_OK;
   if (min_in == nullptr || max_in == nullptr || out == nullptr ||
       (value_type != B200X_VAL_I64 && value_type != B200X_VAL_F64)) {
@@ -860,6 +866,7 @@ extern "C" int b200x_absmax_groups(const void* min_in, const void* max_in, int v
 extern "C" int b200x_group_quantile(const uint32_t* group_starts, const uint32_t* num_groups, size_t max_groups,
                                     const uint32_t* perm, const void* values, int value_type, size_t n, double q,
                                     double* out, void* stream_) {
+  B200X_ON_DEVICE_OF(out);
   if (max_groups == 0 || n == 0) return B200X_OK;
   if (group_starts == nullptr || num_groups == nullptr || values == nullptr || out == nullptr ||
       (value_type != B200X_VAL_I64 && value_type != B200X_VAL_F64)) {
@@ -884,6 +891,7 @@ extern "C" int b200x_group_quantile(const uint32_t* group_starts, const uint32_t
 }
 
 extern "C" int b200x_key_code_range(const void* keys, int key_type, size_t n, uint64_t* range_out, void* stream_) {
+  B200X_ON_DEVICE_OF(range_out);
   cudaStream_t st = (cudaStream_t)stream_;
   if (range_out == nullptr || key_type < 0 || key_type >= KEY_TYPE_COUNT || (n > 0 && keys == nullptr)) {
     set_error("b200x_key_code_range: bad arguments");
@@ -903,6 +911,7 @@ extern "C" int b200x_key_code_range(const void* keys, int key_type, size_t n, ui
 extern "C" int b200x_dense_group_accumulate(const void* keys, int key_type, size_t n, uint64_t base_code, size_t range,
                                             const int64_t* values, int init, int64_t* count_tab, int64_t* sum_tab,
                                             int64_t* min_tab, int64_t* max_tab, void* stream_) {
+  B200X_ON_DEVICE_OF((keys ? (const void*)keys : (const void*)count_tab));
   cudaStream_t st = (cudaStream_t)stream_;
   if (key_type < 0 || key_type >= KEY_TYPE_COUNT || key_type == KEY_F64 || key_type == KEY_F32 || range == 0 ||
       range > ((size_t)1 << 30) || (n > 0 && keys == nullptr) ||
@@ -945,6 +954,7 @@ extern "C" int b200x_dense_group_compact(uint64_t base_code, size_t range, int k
                                          int num_tabs, const int64_t* const* tabs_host, void* keys_out, int64_t* count_out,
                                          int64_t* const* tabs_out_host, uint32_t* num_groups_out, void* temp,
                                          size_t* temp_bytes, void* stream_) {
+  B200X_ON_DEVICE_OF(count_tab);
   cudaStream_t st = (cudaStream_t)stream_;
   if (temp_bytes == nullptr) {
     set_error("b200x_dense_group_compact: temp_bytes is NULL");

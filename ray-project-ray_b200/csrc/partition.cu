@@ -78,6 +78,7 @@ using namespace b200x;
 
 extern "C" int b200x_even_cuts(const void* keys_sorted, int key_type, int descending, size_t n, int parts,
                                uint64_t* out_index, void* stream_) {
+  B200X_ON_DEVICE_OF(out_index);
   if (parts <= 1) return B200X_OK;
   if (n == 0 || keys_sorted == nullptr || out_index == nullptr || key_type < 0 || key_type >= KEY_TYPE_COUNT) {
     set_error("b200x_even_cuts: bad arguments");
@@ -92,6 +93,7 @@ extern "C" int b200x_even_cuts(const void* keys_sorted, int key_type, int descen
 extern "C" int b200x_search_sorted_keys(const void* keys_sorted, int key_type, int descending, size_t n,
                                         const uint64_t* bound_codes, int num_bounds, int upper, uint64_t* out_index,
                                         void* stream_) {
+  B200X_ON_DEVICE_OF(bound_codes);
   if (num_bounds == 0) return B200X_OK;
   if (bound_codes == nullptr || out_index == nullptr || num_bounds < 0 || (n > 0 && keys_sorted == nullptr) ||
       key_type < 0 || key_type >= KEY_TYPE_COUNT) {
@@ -106,6 +108,7 @@ extern "C" int b200x_search_sorted_keys(const void* keys_sorted, int key_type, i
 
 extern "C" int b200x_encode_keys(const void* keys, int key_type, int descending, size_t n, uint64_t* codes_out,
                                  void* stream_) {
+  B200X_ON_DEVICE_OF(keys);
   if (n == 0) return B200X_OK;
   if (keys == nullptr || codes_out == nullptr || key_type < 0 || key_type >= KEY_TYPE_COUNT) {
     set_error("b200x_encode_keys: bad arguments");
@@ -132,6 +135,7 @@ count_adjacent_equal_kernel(const void* __restrict__ keys, int kt, uint64_t n, u
 }
 
 extern "C" int b200x_count_adjacent_equal(const void* keys, int key_type, size_t n, uint64_t* count_out, void* stream_) {
+  B200X_ON_DEVICE_OF(keys);
   if (count_out == nullptr || key_type < 0 || key_type >= KEY_TYPE_COUNT || (n > 0 && keys == nullptr)) {
     set_error("b200x_count_adjacent_equal: bad arguments");
     return B200X_ERR_ARG;
@@ -210,6 +214,7 @@ fix_ties_kernel(const void* __restrict__ keys, int kt, uint64_t n, uint32_t* __r
 extern "C" int b200x_fix_ties(const void* keys_sorted, int key_type, size_t n, uint32_t* perm, const void* const* cols_host,
                               const int* types_host, const unsigned long long* strides_host, const int* be_bytes_host,
                               int num_cols, int descending, unsigned long long* stats_out, void* stream_) {
+  B200X_ON_DEVICE_OF(keys_sorted);
   if (stats_out == nullptr || key_type < 0 || key_type >= KEY_TYPE_COUNT || num_cols < 1 || num_cols > FIX_MAX_COLS ||
       cols_host == nullptr || types_host == nullptr || (n > 0 && (keys_sorted == nullptr || perm == nullptr))) {
     set_error("b200x_fix_ties: bad arguments (1..%d further key columns)", FIX_MAX_COLS);
@@ -323,6 +328,7 @@ pack_key_chunks_kernel(const uint4* __restrict__ rec /* 16-byte aligned: key add
 
 extern "C" int b200x_pack_key_chunks(const void* col, size_t row_pitch, int width, size_t n, void* const* outs_host,
                                      const int* out_bytes_host, void* stream_) {
+  B200X_ON_DEVICE_OF(col);
   if (n == 0) return B200X_OK;
   const int nchunks = (width + 7) / 8;
   if (col == nullptr || outs_host == nullptr || out_bytes_host == nullptr || width < 1 || nchunks > PK_MAX_CHUNKS ||
@@ -368,6 +374,7 @@ static bool chunk_args_ok(size_t row_bytes, size_t offset, int width, int chunk_
 
 extern "C" int b200x_pack_key_bytes(const void* col, size_t row_bytes, size_t offset, int width, size_t n, void* out,
                                     int out_bytes, void* stream_) {
+  B200X_ON_DEVICE_OF(col);
   if (n == 0) return B200X_OK;
   if (col == nullptr || out == nullptr || !chunk_args_ok(row_bytes, offset, width, out_bytes)) {
     set_error("b200x_pack_key_bytes: bad arguments (row_bytes=%zu offset=%zu width=%d out_bytes=%d)", row_bytes, offset,
@@ -389,6 +396,7 @@ extern "C" int b200x_pack_key_bytes(const void* col, size_t row_bytes, size_t of
 
 extern "C" int b200x_unpack_key_bytes(const void* chunk, int chunk_bytes, int width, void* col, size_t row_bytes,
                                       size_t offset, size_t n, void* stream_) {
+  B200X_ON_DEVICE_OF(chunk);
   if (n == 0) return B200X_OK;
   if (col == nullptr || chunk == nullptr || !chunk_args_ok(row_bytes, offset, width, chunk_bytes)) {
     set_error("b200x_unpack_key_bytes: bad arguments (row_bytes=%zu offset=%zu width=%d chunk_bytes=%d)", row_bytes,
@@ -410,6 +418,7 @@ extern "C" int b200x_unpack_key_bytes(const void* chunk, int chunk_bytes, int wi
 
 extern "C" int b200x_search_sorted_codes(const uint64_t* codes, size_t n, const uint64_t* bound_codes, int num_bounds,
                                          int upper, uint64_t* out_index, void* stream_) {
+  B200X_ON_DEVICE_OF(bound_codes);
   if (num_bounds == 0) return B200X_OK;
   if (bound_codes == nullptr || out_index == nullptr || num_bounds < 0 || (n > 0 && codes == nullptr)) {
     set_error("b200x_search_sorted_codes: bad arguments");

@@ -1395,6 +1395,7 @@ extern "C" int b200x_set_tuning(int key, long long value) {
 extern "C" int b200x_radix_argsort(const void* keys, int key_type, int descending, const uint32_t* perm_in,
                                    uint32_t* perm_out, uint64_t* codes_out, void* keys_out, size_t n, int begin_bit,
                                    int end_bit, void* temp, size_t* temp_bytes, void* stream_) {
+  B200X_ON_DEVICE_OF(keys);
   cudaStream_t stream = (cudaStream_t)stream_;
   if (temp_bytes == nullptr) {
     set_error("b200x_radix_argsort: temp_bytes is NULL");

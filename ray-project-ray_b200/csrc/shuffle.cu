@@ -139,6 +139,7 @@ static int check_perm_n(const char* fn, size_t n) {
 
 extern "C" int b200x_perm_indices(size_t n, uint64_t seed, int inverse, size_t start, size_t count, uint32_t* out,
                                   void* stream_) {
+  B200X_ON_DEVICE_OF(out);
   if (int rc = check_perm_n("b200x_perm_indices", n)) return rc;
   if (count == 0) return B200X_OK;
   if (out == nullptr || start + count > n) {
@@ -169,6 +170,7 @@ extern "C" int b200x_perm_indices_host(size_t n, uint64_t seed, int inverse, siz
 
 extern "C" int b200x_permute_rows(const void* src, size_t row_bytes, size_t n, uint64_t seed, int inverse, void* dst,
                                   void* stream_) {
+  B200X_ON_DEVICE_OF(src);
   cudaStream_t stream = (cudaStream_t)stream_;
   if (int rc = check_perm_n("b200x_permute_rows", n)) return rc;
   if (n == 0 || row_bytes == 0) return B200X_OK;
@@ -207,6 +209,7 @@ extern "C" int b200x_permute_rows(const void* src, size_t row_bytes, size_t n, u
 // row_bytes bytes of every record move; bases, pitches and row_bytes are multiples of 16.
 extern "C" int b200x_permute_rows_pitched(const void* src, size_t src_pitch, size_t n, uint64_t seed, int inverse,
                                           void* dst, size_t dst_pitch, size_t row_bytes, void* stream_) {
+  B200X_ON_DEVICE_OF(src);
   cudaStream_t stream = (cudaStream_t)stream_;
   if (int rc = check_perm_n("b200x_permute_rows_pitched", n)) return rc;
   if (n == 0 || row_bytes == 0) return B200X_OK;

@@ -29,6 +29,20 @@ def main():
     from ray_project_ray_b200.context import DataContext
     from ray_project_ray_b200 import distributed as D
 
+    if torch.cuda.device_count() >= 2:
+        # entry points run on the GPU that owns their buffers whatever device is current on the calling thread
+        from ray_project_ray_b200 import _lib
+
+        other = (local + 1) % torch.cuda.device_count()
+        t = torch.zeros(1000, dtype=torch.int32, device=f"cuda:{local}")
+        torch.cuda.synchronize()
+        torch.cuda.set_device(other)
+        _lib.call("b200x_iota_u32", t.data_ptr(), 1000, 5, None)
+        assert torch.cuda.current_device() == other
+        torch.cuda.set_device(local)
+        torch.cuda.synchronize()
+        assert t.cpu().tolist() == list(range(5, 1005))
+        print(f"rank {rank}: call with another device current: OK", flush=True)
     n = 200_000 + 1000 * rank
     rng = np.random.default_rng(100 + rank)
     for transport, kind in (("nccl", "i64_ties"), ("nccl", "f64"), ("auto", "i64_ties"), ("auto", "f64"), ("p2p_sort_first", "i64_ties"), ("p2p_sort_first", "f64"), ("auto", "i64_ties")):
