@@ -478,10 +478,13 @@ def run_ours(args):
                        "egress to dense columns, D2H of the whole sorted result"}
         del o_key, o_pay, h_key, h_pay
 
-    # ---------------- side measurements (N = 1 only; reported under "extras", not the metric)
+    # ---------------- side measurements (reported under "extras", not the metric)
     extras = None
     if world == 1 and not args.no_extras:
         extras = run_extras(rd, dev, nblocks, ds_noprefix, n)
+    elif world > 1 and not args.no_extras:
+        del ds
+        extras = run_extras_distributed(rd, dev, world, rank, nblocks)
     del ds_noprefix
 
     clocks = sampler.stop() if rank == 0 else None
@@ -658,6 +661,100 @@ def run_extras(rd, dev, nblocks, ds_noprefix, n_main):
             "checked": "row count and grand total of the group sums equal the input's"}
         del r, gds, gk, gv
     return extras
+
+
+def run_extras_distributed(rd, dev, world, rank, nblocks):
+    """The other two operators of the path across the ranks, each checked on the device (all ranks take part, rank 0
+    reports): random_shuffle of 50 M rows x 72 B per GPU, groupby-aggregate of 100 M rows per GPU over 1 M keys."""
+    import torch
+    import torch.distributed as dist
+
+    from ray_project_ray_b200.aggregate import Count, Mean, Sum
+
+    def timed(fn, steps=2, warm=1):
+        for _ in range(warm):
+            r = fn()
+        dist.barrier()
+        torch.cuda.synchronize()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        for _ in range(steps):
+            r = fn()
+        g1.record()
+        dist.barrier()
+        torch.cuda.synchronize()
+        t = torch.tensor([g0.elapsed_time(g1) / steps], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()), r
+
+    def total(x):
+        t = torch.as_tensor(x, dtype=torch.int64, device=dev).reshape(1).clone()
+        dist.all_reduce(t)
+        return int(t.item())
+
+    extras = {}
+    n = 50_000_000
+    ids = torch.arange(rank * n, (rank + 1) * n, dtype=torch.int64, device=dev)
+    pay = torch.randint(0, 256, (n, 64), dtype=torch.uint8, device=dev, generator=torch.Generator(device=dev).manual_seed(5 + rank))
+    pay[:, :8] = (ids * TAG_MULT).view(torch.uint8).reshape(n, 8)
+    ds = rd.from_torch_columns({"id": ids, "payload": pay}, override_num_blocks=nblocks)
+    ms, r = timed(lambda: ds.random_shuffle(seed=0))
+    blocks = [b for b in r.get_internal_block_refs() if b.num_rows]
+    oid = torch.cat([b["id"] for b in blocks])
+    opay = torch.cat([b["payload"][:, :8].contiguous().view(torch.int64).reshape(-1) for b in blocks])
+    again = torch.cat([b["id"] for b in ds.random_shuffle(seed=0).get_internal_block_refs() if b.num_rows])
+    other = torch.cat([b["id"] for b in ds.random_shuffle(seed=1).get_internal_block_refs() if b.num_rows])
+    home = (oid // n == rank).sum()
+    ok = {"rows": total(oid.numel()) == n * world,
+          "id_multiset_checksum": total(oid.sum()) == total(ids.sum()) and _all_equal_xor(_xor_reduce(oid), _xor_reduce(ids), dev),
+          "payload_travels_with_id": bool((opay == oid * TAG_MULT).all()),
+          "same_seed_same_order": oid.numel() == again.numel() and bool((oid == again).all()),
+          "other_seed_other_order": oid.numel() != other.numel() or float((oid != other).double().mean()) > 0.9,
+          "rows_mix_across_ranks": abs(total(home) / (n * world) - 1.0 / world) < 0.01}
+    ok = {k: bool(total(int(v)) == world) for k, v in ok.items()}
+    gbs = n * world * 2 * 72 / (ms / 1e3) / 1e9
+    extras["random_shuffle"] = {"workload": f"{n} rows x (8 B id + 64 B payload) per GPU, seed=0, across {world} GPUs",
+                                "ms_per_step": ms, "rows_per_s": n * world / (ms / 1e3), "gb_per_s": gbs, "verified": ok}
+    del ds, ids, pay, r, blocks, oid, opay, again, other
+    gn, groups = 100_000_000, 1_000_000
+    gen = torch.Generator(device=dev).manual_seed(40 + rank)
+    gk = torch.randint(0, groups, (gn,), dtype=torch.int64, device=dev, generator=gen)
+    gv = torch.randint(-2**31, 2**31, (gn,), dtype=torch.int64, device=dev, generator=gen)
+    gds = rd.from_torch_columns({"k": gk, "v": gv}, override_num_blocks=nblocks)
+    ms, r = timed(lambda: gds.groupby("k").aggregate(Sum("v"), Mean("v"), Count()))
+    blocks = [b for b in r.get_internal_block_refs() if b.num_rows]
+    k = torch.cat([b["k"] for b in blocks]) if blocks else gk[:0]
+    cnt = torch.cat([b["count()"] for b in blocks]) if blocks else gk[:0]
+    sm = torch.cat([b["sum(v)"] for b in blocks]) if blocks else gk[:0]
+    mean = torch.cat([b["mean(v)"] for b in blocks]) if blocks else gk[:0].double()
+    edge = torch.tensor([int(k[0]), int(k[-1])] if k.numel() else [2**62, -1], dtype=torch.int64, device=dev)
+    edges = [torch.empty_like(edge) for _ in range(world)]
+    dist.all_gather(edges, edge)
+    e = [x.tolist() for x in edges if x[1] >= 0]
+    ok = {"keys_ascending_and_distinct": bool((k[1:] > k[:-1]).all()) and all(b[0] > a[1] for a, b in zip(e[:-1], e[1:])),
+          "row_count": total(cnt.sum()) == gn * world, "grand_total": total(sm.sum()) == total(gv.sum()),
+          "groups": total(k.numel()) == groups,
+          "mean_is_sum_over_count": bool(torch.allclose(mean, sm.double() / cnt.double(), rtol=1e-12, atol=0))}
+    ok = {kk: bool(total(int(v)) == world) for kk, v in ok.items()}
+    extras["groupby_aggregate"] = {"workload": f"{gn} rows per GPU, {groups} distinct int64 keys (uniform), Sum+Mean+Count, across {world} GPUs",
+                                   "ms_per_step": ms, "rows_per_s": gn * world / (ms / 1e3), "verified": ok}
+    return extras
+
+
+def _all_equal_xor(mine, theirs, dev):
+    """XOR of a value over all ranks == XOR of another value over all ranks."""
+    import torch
+    import torch.distributed as dist
+
+    world = dist.get_world_size()
+    pair = torch.stack([mine.reshape(()), theirs.reshape(())]).to(dev)
+    parts = [torch.empty_like(pair) for _ in range(world)]
+    dist.all_gather(parts, pair)
+    a = b = 0
+    for p in parts:
+        a ^= int(p[0])
+        b ^= int(p[1])
+    return a == b
 
 
 if __name__ == "__main__":

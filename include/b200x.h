@@ -282,6 +282,18 @@ int b200x_permute_rows(const void* src, size_t row_bytes, size_t n, uint64_t see
 int b200x_permute_rows_pitched(const void* src, size_t src_pitch, size_t n, uint64_t seed, int inverse, void* dst,
                                size_t dst_pitch, size_t row_bytes, void* stream); /* records at a pitch, see b200x_gather_rows_pitched */
 int b200x_perm_indices(size_t n, uint64_t seed, int inverse, size_t start, size_t count, uint32_t* out, void* stream);
+
+/* random_shuffle across the GPUs of one box as ONE scatter over peer memory: this rank holds rows [first_global,
+ * first_global + n_local) of a dataset of total_rows rows (rows src_pitch bytes apart, row_bytes bytes each); row G is
+ * stored at position q = pi^-1(G) of the shuffled dataset, which lies on rank q / rows_per_rank at row
+ * q % rows_per_rank of peer_base_host[rank] (rows dst_pitch apart; HOST array of peer-mapped device addresses). The
+ * concatenation of the ranks' buffers equals b200x_permute_rows of the concatenated dataset with the same seed. No
+ * counts are exchanged (every rank gets rows_per_rank rows, the last one the rest), no send buffer, no second local
+ * shuffle. Replaces ShuffleTaskSpec.map + the object-store hop + ShuffleTaskSpec.reduce
+ * (_internal/planner/exchange/shuffle_task_spec.py:81-132). */
+int b200x_permute_scatter_to_peers(const void* src, size_t src_pitch, size_t row_bytes, size_t n_local, size_t first_global,
+                                   size_t total_rows, uint64_t seed, size_t rows_per_rank, void* const* peer_base_host,
+                                   size_t dst_pitch, int world, void* stream);
 int b200x_perm_indices_host(size_t n, uint64_t seed, int inverse, size_t start, size_t count, uint32_t* out_host);
 
 /* Group boundaries of an ascending code array: group_starts[g] = first position of group g,

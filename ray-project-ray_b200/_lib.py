@@ -63,6 +63,8 @@ SIGNATURES = {
     "b200x_split_positions_by_chunk": (c_int, [c_void_p, c_size_t, POINTER(c_uint32), c_int, c_int, POINTER(c_uint32),
                                                c_void_p, c_void_p, _size_p, c_void_p]),
     "b200x_permute_rows": (c_int, [c_void_p, c_size_t, c_size_t, c_uint64, c_int, c_void_p, c_void_p]),
+    "b200x_permute_scatter_to_peers": (c_int, [c_void_p, c_size_t, c_size_t, c_size_t, c_size_t, c_size_t, c_uint64, c_size_t,
+                                               POINTER(c_void_p), c_size_t, c_int, c_void_p]),
     "b200x_perm_indices": (c_int, [c_size_t, c_uint64, c_int, c_size_t, c_size_t, c_void_p, c_void_p]),
     "b200x_perm_indices_host": (c_int, [c_size_t, c_uint64, c_int, c_size_t, c_size_t, c_void_p]),
     "b200x_group_boundaries": (c_int, [c_void_p, c_size_t, c_void_p, c_void_p, c_void_p, _size_p, c_void_p]),

@@ -237,3 +237,90 @@ extern "C" int b200x_permute_rows_pitched(const void* src, size_t src_pitch, siz
   B200X_LAUNCH_CHECK("permute_rows_kernel");
   return B200X_OK;
 }
+
+// Shuffle across GPUs as ONE scatter: local row i is row first_global + i of the whole dataset (total rows over all
+// ranks); its place in the shuffled dataset is pi(first_global + i), which lies on rank pi / rows_per_rank at row
+// pi % rows_per_rank - the row is stored straight there through the peer mapping. Every rank evaluates the same
+// bijection, so no counts, send buffers or second local shuffle are needed: the receive buffer IS the result.
+namespace b200x {
+constexpr int PS_MAX_PEERS = 16;
+struct PeerBases {
+  unsigned char* base[PS_MAX_PEERS];
+};
+
+template <typename V>
+__global__ void __launch_bounds__(256)
+permute_scatter_kernel(const V* __restrict__ src, uint32_t src_pitch_vec, uint32_t vec_per_row, uint32_t lanes_per_row,
+                       uint64_t n_local, uint64_t first_global, const PermSpec s, uint64_t rows_per_rank, const PeerBases pb,
+                       uint64_t dst_pitch_vec) {
+  const unsigned lane = threadIdx.x & 31;
+  const uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  const uint32_t groups = 32 / lanes_per_row;
+  const uint32_t g = lane / lanes_per_row, c0 = lane % lanes_per_row;
+  for (uint64_t r0 = warp * 32; r0 < n_local; r0 += nwarps * 32) {
+    const uint64_t mine = r0 + lane;
+    const uint64_t p = mine < n_local ? perm_eval(s, first_global + mine, true) : 0ull;   // where my row goes
+    for (uint32_t i = 0; i < 32; i += groups) {
+      const uint32_t ri = i + g;
+      const uint64_t pr = __shfl_sync(0xffffffffu, p, ri);
+      const uint64_t r = r0 + ri;
+      if (r < n_local) {
+        const uint64_t d = pr / rows_per_rank, slot = pr - d * rows_per_rank;
+        const V* sp = src + r * src_pitch_vec;
+        V* dp = reinterpret_cast<V*>(pb.base[d]) + slot * dst_pitch_vec;
+        for (uint32_t c = c0; c < vec_per_row; c += lanes_per_row) dp[c] = sp[c];
+      }
+    }
+  }
+}
+}  // namespace b200x
+
+extern "C" int b200x_permute_scatter_to_peers(const void* src, size_t src_pitch, size_t row_bytes, size_t n_local,
+                                              size_t first_global, size_t total_rows, uint64_t seed, size_t rows_per_rank,
+                                              void* const* peer_base_host, size_t dst_pitch, int world, void* stream_) {
+  B200X_ON_DEVICE_OF(src);
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (int rc = check_perm_n("b200x_permute_scatter_to_peers", total_rows)) return rc;
+  if (n_local == 0 || row_bytes == 0) return B200X_OK;
+  if (src == nullptr || peer_base_host == nullptr || world < 1 || world > PS_MAX_PEERS || rows_per_rank == 0 ||
+      first_global + n_local > total_rows || rows_per_rank * (size_t)world < total_rows || row_bytes > src_pitch ||
+      row_bytes > dst_pitch || row_bytes > (1u << 20)) {
+    set_error("b200x_permute_scatter_to_peers: bad arguments (rows [%zu, %zu) of %zu, %zu rows per rank x %d ranks, row_bytes %zu)",
+              first_global, first_global + n_local, total_rows, rows_per_rank, world, row_bytes);
+    return B200X_ERR_ARG;
+  }
+  PeerBases pb;
+  uintptr_t al = (uintptr_t)src | src_pitch | dst_pitch | row_bytes;
+  for (int d = 0; d < PS_MAX_PEERS; ++d) {
+    pb.base[d] = d < world ? (unsigned char*)peer_base_host[d] : nullptr;
+    if (d < world) al |= (uintptr_t)pb.base[d];
+    if (d < world && pb.base[d] == nullptr) {
+      set_error("b200x_permute_scatter_to_peers: receive buffer %d is NULL", d);
+      return B200X_ERR_ARG;
+    }
+  }
+  // scatter form of out[q] = in[pi(q)] (b200x_permute_rows): row G goes to the position q with pi(q) = G, q = pi^-1(G)
+  const PermSpec s = make_spec(total_rows, seed);
+  int v = 16;
+  while (v > 1 && (al & (uintptr_t)(v - 1)) != 0) v >>= 1;
+  const uint32_t vpr = (uint32_t)(row_bytes / v);
+  uint32_t lpr = 1;
+  while (lpr < vpr && lpr < 32) lpr <<= 1;
+  uint64_t blocks = ((uint64_t)n_local * lpr + 255) / 256;
+  const uint64_t cap = (uint64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  const uint32_t g = (uint32_t)blocks, spv = (uint32_t)(src_pitch / v);
+  const uint64_t dpv = dst_pitch / v;
+  prof_begin(stream, PROF_PERMUTE);
+  switch (v) {
+    case 16: permute_scatter_kernel<uint4><<<g, 256, 0, stream>>>((const uint4*)src, spv, vpr, lpr, n_local, first_global, s, rows_per_rank, pb, dpv); break;
+    case 8: permute_scatter_kernel<uint64_t><<<g, 256, 0, stream>>>((const uint64_t*)src, spv, vpr, lpr, n_local, first_global, s, rows_per_rank, pb, dpv); break;
+    case 4: permute_scatter_kernel<uint32_t><<<g, 256, 0, stream>>>((const uint32_t*)src, spv, vpr, lpr, n_local, first_global, s, rows_per_rank, pb, dpv); break;
+    case 2: permute_scatter_kernel<uint16_t><<<g, 256, 0, stream>>>((const uint16_t*)src, spv, vpr, lpr, n_local, first_global, s, rows_per_rank, pb, dpv); break;
+    default: permute_scatter_kernel<uint8_t><<<g, 256, 0, stream>>>((const uint8_t*)src, spv, vpr, lpr, n_local, first_global, s, rows_per_rank, pb, dpv); break;
+  }
+  prof_end(stream);
+  B200X_LAUNCH_CHECK("permute_scatter_kernel");
+  return B200X_OK;
+}

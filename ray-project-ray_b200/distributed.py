@@ -717,15 +717,65 @@ def _partial_like(partial: Optional[DeviceBlock], dev: torch.device, group=None)
 
 
 def dist_random_shuffle(local: DeviceBlock, seed: Optional[int], group=None) -> DeviceBlock:
-    """ShuffleTaskSpec.map / reduce with one mapper and one reducer per rank."""
+    """random_shuffle across the ranks. Over peer memory: ONE global seeded bijection, every row stored straight at its
+    place in the shuffled dataset (`b200x_permute_scatter_to_peers`) - the concatenation of the ranks' results equals
+    the single-GPU shuffle of the concatenated input with the same seed. Without peer memory: ShuffleTaskSpec.map /
+    reduce with one mapper and one reducer per rank over NCCL all-to-all-v."""
     from .shuffle_task_spec import ShuffleTaskSpec
 
     world, rank = dist.get_world_size(group), dist.get_rank(group)
+    dev = local.device
+    if dev is not None and dev.type == "cuda" and _transport() != "nccl" and p2p_available(dev, group):
+        return _p2p_random_shuffle(local, seed, dev, group)
     parts = ShuffleTaskSpec.map(rank, local, world, 0, None, True, seed)[:-1]
     send = DeviceBlock.concat(parts) if any(p.num_rows for p in parts) else local.slice(0, 0)
     received = exchange_block(send if send.columns else local.slice(0, 0), [p.num_rows for p in parts], group)
     out, _ = ShuffleTaskSpec.reduce(True, seed, received)
     return out
+
+
+def _p2p_random_shuffle(local: DeviceBlock, seed: Optional[int], dev, group) -> DeviceBlock:
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    n = local.num_rows
+    has_groups = bool(record_groups(local)[0])
+    draw = int.from_bytes(os.urandom(7), "little") if seed is None else int(seed) & ((1 << 62) - 1)
+    mine = torch.tensor([n, draw, int(has_groups)], dtype=torch.int64, device=dev)
+    parts = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(parts, mine, group=group)
+    info = torch.stack(parts).cpu().numpy()
+    counts = [int(x) for x in info[:, 0]]
+    total, first = sum(counts), sum(counts[:rank])
+    use_seed = int(info[0, 1])                      # seed=None: rank 0's draw, the same on every rank
+    if total == 0:
+        return local.slice(0, 0)
+    if total > 0xFFFFFFFF:
+        raise ValueError(f"random_shuffle handles at most 2^32-1 rows in all, got {total}")
+    # a rank without rows cannot know how the others lay out their records: then everybody moves dense columns
+    if info[:, 2].any() and not (all(counts) and info[:, 2].all()):
+        local = _densify(local)
+    per = (total + world - 1) // world
+    got = max(0, min(total, (rank + 1) * per) - rank * per)
+    groups, loose = record_groups(local)
+    units = [(f"\x00rec{i}", g.rec) for i, g in enumerate(groups)] + [(c, _contig(local.columns[c])) for c in loose]
+    bufs = []
+    for slot, (name, t) in enumerate(units):
+        row_bytes = t.element_size()
+        for d in t.shape[1:]:
+            row_bytes *= int(d)
+        bufs.append((_symm_buffer(slot, per * row_bytes, dev, group), row_bytes))
+    handle = bufs[0][0][1]
+    handle.barrier(channel=0)                       # everyone is done with the buffers' previous contents
+    for (name, t), ((buf, h), row_bytes) in zip(units, bufs):
+        ops.permute_scatter_to_peers(t, first, total, use_seed, per, [int(p) for p in h.buffer_ptrs], row_bytes)
+    handle.barrier(channel=0)                       # every row has landed
+    cols: Dict[str, torch.Tensor] = {}
+    for (name, t), ((buf, _), row_bytes) in zip(units, bufs):
+        flat = buf[: got * row_bytes].clone()       # the receive buffer belongs to the next exchange
+        if name.startswith("\x00rec"):
+            cols.update(groups[int(name[4:])].views(flat.reshape(got, row_bytes)))
+        else:
+            cols[name] = (flat.view(t.dtype) if t.dtype != torch.uint8 else flat).reshape((got,) + tuple(t.shape[1:]))
+    return DeviceBlock({c: cols[c] for c in local.column_names}, num_rows=got, device=dev)
 
 
 def dist_aggregate(local: DeviceBlock, key: Optional[str], aggs, group=None, samples_per_rank: int = 4096) -> DeviceBlock:

@@ -637,3 +637,19 @@ def dense_group_compact(base_code: int, rng: int, key_dtype: torch.dtype, count:
         _lib.call("b200x_dense_group_compact", *args, temp.data_ptr(), ctypes.byref(nb), st)
     g = int(ng.item())
     return keys_out[:g], count_out[:g], [o[:g] for o in outs], g
+
+
+def permute_scatter_to_peers(col: torch.Tensor, first_global: int, total_rows: int, seed: int, rows_per_rank: int,
+                             bases: Sequence[int], dst_pitch: int) -> None:
+    """Rows of `col` ([n, ...] dense, or a [n, pitch] record buffer) = rows [first_global, first_global + n) of a dataset of
+    total_rows rows: each is stored at its place in the shuffled dataset, on whichever rank that is."""
+    dev = _require_cuda(col)
+    n = col.shape[0]
+    row_bytes = col.element_size()
+    for d in col.shape[1:]:
+        row_bytes *= int(d)
+    w = len(bases)
+    b = (ctypes.c_void_p * w)(*[int(x) for x in bases])
+    with torch.cuda.device(dev):
+        _lib.call("b200x_permute_scatter_to_peers", col.data_ptr(), row_bytes, row_bytes, n, first_global, total_rows,
+                  seed & 0xFFFFFFFFFFFFFFFF, rows_per_rank, b, dst_pitch, w, _stream(dev))

@@ -151,6 +151,22 @@ def main():
         for x in pa:
             assert len(set(x // 10_000_000)) == world  # every rank's output draws from every rank
         print("random_shuffle: OK (deterministic per seed, exact multiset), rows per rank", [len(x) for x in pa], flush=True)
+        if D._p2p_ok["state"]:     # over peer memory: exactly the single-GPU shuffle of the concatenated input
+            allrows = np.concatenate(ins)
+            np.testing.assert_array_equal(A, allrows[orc.feistel_permutation(len(allrows), 0)])
+            print("random_shuffle: equals the one-GPU permutation of the concatenated input", flush=True)
+    # the same with a payload, as records, with unequal shard sizes; and a rank without rows
+    for m, recs in ((123_457 + 1000 * rank, True), (123_457 + 1000 * rank, False), (0 if rank == 1 else 77_000, True)):
+        rid = np.arange(m, dtype=np.int64) + rank * 10_000_000
+        pay = np.random.default_rng(rank).integers(0, 256, (m, 40), dtype=np.uint8)
+        got = rd.from_numpy_columns({"row": rid, "pay": pay}, override_num_blocks=3, records=recs).random_shuffle(seed=9).to_numpy()
+        outs, ins2 = gather_np((got["row"], got["pay"]), world, rank), gather_np((rid, pay), world, rank)
+        if rank == 0:
+            ar, ap = np.concatenate([x[0] for x in ins2]), np.concatenate([x[1] for x in ins2])
+            p = orc.feistel_permutation(len(ar), 9)
+            np.testing.assert_array_equal(np.concatenate([x[0] for x in outs]), ar[p])
+            np.testing.assert_array_equal(np.concatenate([x[1] for x in outs]), ap[p])
+            print(f"random_shuffle rows={m} records={recs}: OK, rows per rank {[len(x[0]) for x in outs]}", flush=True)
     dist.barrier()
     dist.destroy_process_group()
 
