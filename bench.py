@@ -49,7 +49,7 @@ TAG_MULT = 0x9E3779B97F4A7C15 - (1 << 64)   # odd 64-bit constant (as int64): ta
 # per row ncu measured for it (profiles/, dram__bytes_read.sum + dram__bytes_write.sum; None = not captured).
 KERNELS = {
     0: ("onesweep_pass_kernel", 22.0, 26.0),         # HYBRID: pass A reads 8 writes 12, pass B reads 12 writes 12
-    1: ("record gather (gather_rows_pitched_kernel / gather_records_list_kernel, 128-byte records)", 4 + 2 * ROW_BYTES, None),  # index + read record + write record
+    1: ("record gather (gather_rows_pitched_kernel / gather_records_list_kernel, 128-byte records)", 4 + 2 * ROW_BYTES, 259.7),  # index + read record + write record; ncu: 16.5 GB read + 16.0 GB written per 125 M records (2 x the 128-byte record)
     2: ("finish_runs_kernel", 12 + 4 + 8, 23.5),      # read pair, write row index + decoded key
     3: ("digit2_hist_kernel", 8.0, 8.0),              # read key column
     6: ("hist_kernel", 8.0, None),
