@@ -411,10 +411,21 @@ def run_ours(args):
 
     # ---------------- end to end through the public API from pinned host buffers: `e2e`
     e2e = None
+    pinned_ok = not args.no_e2e
     if not args.no_e2e:
-        cap = int(n * (1.0 if world == 1 else 1.5))
-        o_key = torch.empty((cap, KEY_BYTES), dtype=torch.uint8).pin_memory()
-        o_pay = torch.empty((cap, PAYLOAD_BYTES), dtype=torch.uint8).pin_memory()
+        cap = int(n * (1.0 if world == 1 else 1.25))
+        try:
+            o_key = torch.empty((cap, KEY_BYTES), dtype=torch.uint8).pin_memory()
+            o_pay = torch.empty((cap, PAYLOAD_BYTES), dtype=torch.uint8).pin_memory()
+        except RuntimeError as err:      # the host cannot pin another 14 GB per rank: no end-to-end leg (every rank agrees)
+            pinned_ok, e2e = False, {"unavailable": f"pinned host allocation failed: {err}"[:200]}
+        if world > 1:
+            flag = torch.tensor([int(pinned_ok)], dtype=torch.int64, device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            if pinned_ok and not int(flag.item()):
+                e2e = {"unavailable": "pinned host allocation failed on another rank"}
+            pinned_ok = bool(flag.item())
+    if pinned_ok:
         copy_stream = torch.cuda.Stream(device=dev)
         prev = {"objs": None, "done": None}  # the previous step's result while its D2H may still be in flight
 
@@ -436,8 +447,10 @@ def run_ours(args):
             lo, objs = 0, [res]
             with torch.cuda.stream(copy_stream):
                 for b in res.get_internal_block_refs():
-                    m = b.num_rows
-                    if m:
+                    m = min(b.num_rows, cap - lo)      # (a rank never receives 25 % more than its share; guarded anyway)
+                    if m > 0:
+                        if m < b.num_rows:
+                            b = b.slice(0, m)
                         dk, dp = _contig(b["key"]), _contig(b["payload"])
                         o_key[lo:lo + m].copy_(dk, non_blocking=True)
                         o_pay[lo:lo + m].copy_(dp, non_blocking=True)

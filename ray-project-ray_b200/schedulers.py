@@ -322,7 +322,15 @@ class GpuExchangeScheduler(ExchangeTaskScheduler):
                 reduce_ray_remote_args: Optional[Dict[str, Any]] = None, merge_factor: float = 2,
                 _debug_limit_execution_to_num_blocks: Optional[int] = None) -> Tuple[List[RefBundle], StatsDict]:
         spec = self._exchange_spec
-        if _debug_limit_execution_to_num_blocks is not None or type(spec) not in (
+        # One fused pass handles what one sort call and one GPU's memory hold: more rows than `fused_max_rows`
+        # (default: the argsort's limit) go through the task-structured scheduler, which works block by block.
+        from . import distributed as D
+        from .context import DataContext
+
+        total_rows = sum(m.num_rows or 0 for rb in refs for _, m in rb.blocks)
+        too_large = total_rows > int(DataContext.get_current().get_config("fused_max_rows", ops.MAX_SORT_ROWS)) \
+            and not D.is_distributed() and type(spec) in (SortTaskSpec, SortAggregateTaskSpec)
+        if too_large or _debug_limit_execution_to_num_blocks is not None or type(spec) not in (
                 SortTaskSpec, ShuffleTaskSpec, SortAggregateTaskSpec):
             if type(spec) in (SortTaskSpec, SortAggregateTaskSpec) and isinstance(spec._map_args[0], AutoBoundaries):
                 # the task-structured path needs real splitters: sample them now
@@ -339,8 +347,6 @@ class GpuExchangeScheduler(ExchangeTaskScheduler):
         input_owned = all(b.owns_blocks for b in refs)
         in_meta = [m for rb in refs for _, m in rb.blocks]
         stats = BlockExecStats.builder()
-        from . import distributed as D
-
         if D.is_distributed():
             outs = _distributed_exchange(spec, blocks, output_num_blocks)
             st = stats.build()

@@ -641,3 +641,25 @@ def test_dense_range_aggregation_equals_sorted_path(dist_kind, cuda_device):
     # not applicable: float value column, wide key range -> the sorted path, same API
     wide = rd.from_numpy_columns({"k": k.astype(np.int64) * (2**40), "v": v}, override_num_blocks=2).groupby("k").sum("v").to_numpy()
     np.testing.assert_array_equal(wide["sum(v)"], np.add.reduceat(v[order], bounds))
+
+
+def test_fused_scheduler_hands_over_when_the_dataset_is_too_large(cuda_device):
+    """More rows than one fused pass takes (`fused_max_rows`, by default the argsort's 2^30-1): the default scheduler
+    runs the task-structured one with sampled boundaries instead of failing; same global result."""
+    ctx = DataContext.get_current()
+    rng = np.random.default_rng(8)
+    k = rng.integers(0, 1000, 50_000, dtype=np.int64)
+    v = rng.integers(-9, 9, 50_000, dtype=np.int64)
+    ds = rd.from_numpy_columns({"k": k, "v": v}, override_num_blocks=5)
+    ctx.set_config("fused_max_rows", 10_000)
+    try:
+        got = ds.sort("k", descending=True).to_numpy()
+        agg = ds.groupby("k").sum("v").to_numpy()
+    finally:
+        ctx.set_config("fused_max_rows", (1 << 30) - 1)
+    order = orc.stable_argsort(k, True)
+    np.testing.assert_array_equal(got["k"], k[order])
+    np.testing.assert_array_equal(got["v"], v[order])
+    keys = np.unique(k)
+    np.testing.assert_array_equal(agg["k"], keys)
+    np.testing.assert_array_equal(agg["sum(v)"], [v[k == x].sum() for x in keys])
