@@ -575,7 +575,12 @@ def _p2p_partition_sort_records(local: DeviceBlock, sort_key: SortKey, n: int, d
     chunk_ev = []
     try:
         ex.send(extra)
+        # (wider later chunks, once the received-key sort is over, made the step SLOWER at 8 GPUs: 32.6 ms with 8
+        # blocks per SM, 34.3 with one block per tile, against 29.0 with two blocks per SM throughout)
+        late_bps = int(os.environ.get("B200X_PAYLOAD_BLOCKS_PER_SM_LATE", os.environ.get("B200X_PAYLOAD_BLOCKS_PER_SM", "2")))
         for c in range(K):
+            if c > 0:
+                _lib.call("b200x_set_tuning", 1, late_bps)
             ex.send_records("\x00rec", copy, shift, rows_at[c], rows_at[c + 1] - rows_at[c])
             ex.fence()
             ev = torch.cuda.Event()
