@@ -358,6 +358,20 @@ int b200x_dense_group_compact(uint64_t base_code, size_t range, int key_type, co
 int b200x_group_counts(const uint32_t* group_starts, const uint32_t* num_groups, size_t max_groups, size_t n,
                        int64_t* counts_out, void* stream);
 
+/* Nulls in value columns (the reference's null policy, _internal/null_aggregate.py:11-17, applied by the wrappers of
+ * :28-250 and by pyarrow's skip_nulls in _internal/arrow_block.py:387-425). A nullable column is its values plus one
+ * validity byte per row (non-zero = present).
+ * b200x_mask_values: out_values[i] = valid[i] ? values[i] : the identity of the reduction the column enters next
+ *   (fill_mode 0: 0 for sums; 1: the largest int64 / +inf for minima; 2: the smallest / -inf for maxima), and
+ *   out_valid64[i] = valid[i] ? 1 : 0 as int64 (reduced per group like any other column: the number of non-null rows,
+ *   which is also Mean's and Std's denominator). Either output may be NULL.
+ * b200x_group_validity: out[g] = 1 if group g's result exists: ignore_nulls != 0: nvalid[g] > 0 (nulls are skipped, an
+ *   all-null group has no result); ignore_nulls == 0: nvalid[g] == rows[g] > 0 (one null makes the result null). */
+int b200x_mask_values(const void* values, int value_type, const uint8_t* valid, size_t n, int fill_mode, void* out_values,
+                      int64_t* out_valid64, void* stream);
+int b200x_group_validity(const int64_t* nvalid, const int64_t* rows, size_t num_groups, int ignore_nulls, uint8_t* out,
+                         void* stream);
+
 /* mode 0: out[g] = sum[g] / counts[g]                         (Mean.finalize, aggregate/_aggregate.py:238)
  * mode 1: out[g] = counts[g] < 2 ? 0 : sqrt(sum[g] / (counts[g] - ddof))   (Std.finalize, :296-302) */
 int b200x_finalize_groups(const void* sum, int value_type, const int64_t* counts, size_t num_groups, int mode, int ddof,

@@ -479,3 +479,37 @@ def key_boundaries(key_columns: Sequence[np.ndarray]) -> List[int]:
     for col in key_columns:
         change |= col[1:] != col[:-1]
     return (np.flatnonzero(change) + 1).tolist() + [n]
+
+
+def null_group_aggregate(keys: Optional[np.ndarray], values: np.ndarray, is_null: np.ndarray, kind: str, ignore_nulls: bool,
+                         ddof: int = 1) -> List[Optional[float]]:
+    """One aggregation of a nullable value column per group (ascending keys; `keys=None`: one global group) under the
+    reference's null policy (_internal/null_aggregate.py:11-17): ignore_nulls -> aggregate the non-null values, None
+    if there are none; otherwise one null makes the group's result None. Mean / Std count non-null values only
+    (arrow_block.py:384-386 + aggregate/_aggregate.py:205-302)."""
+    groups = [None] if keys is None else np.unique(keys).tolist()
+    out: List[Optional[float]] = []
+    for g in groups:
+        sel = np.ones(len(values), dtype=bool) if g is None else (keys == g)
+        v, nul = values[sel], is_null[sel]
+        if nul.all() or (nul.any() and not ignore_nulls) or len(v) == 0:
+            out.append(None)
+            continue
+        v = v[~nul]
+        if kind == "sum":
+            out.append(v.sum().item())
+        elif kind == "min":
+            out.append(v.min().item())
+        elif kind == "max":
+            out.append(v.max().item())
+        elif kind == "abs_max":
+            out.append(np.abs(v).max().item())
+        elif kind == "mean":
+            out.append(float(v.sum()) / len(v))
+        elif kind == "std":
+            m = float(v.astype(np.float64).sum()) / len(v)
+            m2 = float(((v.astype(np.float64) - m) ** 2).sum())
+            out.append(0.0 if len(v) - ddof <= 0 else math.sqrt(m2 / (len(v) - ddof)))
+        else:
+            raise ValueError(kind)
+    return out

@@ -78,6 +78,8 @@ SIGNATURES = {
                                              c_void_p, c_void_p, c_void_p, c_void_p]),
     "b200x_dense_group_compact": (c_int, [c_uint64, c_size_t, c_int, c_void_p, c_int, POINTER(c_void_p), c_void_p, c_void_p,
                                           POINTER(c_void_p), c_void_p, c_void_p, _size_p, c_void_p]),
+    "b200x_mask_values": (c_int, [c_void_p, c_int, c_void_p, c_size_t, c_int, c_void_p, c_void_p, c_void_p]),
+    "b200x_group_validity": (c_int, [c_void_p, c_void_p, c_size_t, c_int, c_void_p, c_void_p]),
     "b200x_group_counts": (c_int, [c_void_p, c_void_p, c_size_t, c_size_t, c_void_p, c_void_p]),
     "b200x_finalize_groups": (c_int, [c_void_p, c_int, c_void_p, c_size_t, c_int, c_int, c_void_p, c_void_p]),
     "b200x_count_adjacent_equal": (c_int, [c_void_p, c_int, c_size_t, c_void_p, c_void_p]),

@@ -18,8 +18,14 @@ selects outputs of the segmented-reduce kernel, and a partially combined block (
                  (sorted by key) and every aggregation is evaluated at the final merge
 
 User-defined AggregateFn callables cannot run on the device and raise NotImplementedError.
-Nulls do not exist in the device block format, so `ignore_nulls` has no effect (has_data is
-always true in the reference's null wrappers, _internal/null_aggregate.py:28-250).
+
+Nulls (the reference's policy, _internal/null_aggregate.py:11-17, wrappers :28-250): a nullable value column carries
+a hidden validity column (block.py). Per group, with ignore_nulls=True the aggregation covers the non-null values and
+is null when there are none; with ignore_nulls=False one null makes it null. Count() counts rows, nulls included;
+Mean's and Std's denominators count non-null values (pyarrow's count, arrow_block.py:384-386). On the device a null row
+enters a reduction as that reduction's identity (`b200x_mask_values`); the partial accumulators of a nullable column
+gain `name::nvalid` (non-null values) and `name::rows` (rows), which are summed at the merge, and the finished column
+gets its own hidden validity column (`b200x_group_validity`). Quantile over a nullable column is not implemented.
 """
 from __future__ import annotations
 
@@ -28,7 +34,7 @@ from typing import Callable, Dict, List, Optional, Sequence, Tuple
 import torch
 
 from . import ops
-from .block import DeviceBlock, _contig
+from .block import DeviceBlock, VALID_SEP, _contig, valid_name
 
 SEP = "::"
 
@@ -183,38 +189,77 @@ def _reduce_partials(kind: str, agg: AggregateFn, name: str, src: DeviceBlock, s
                 cache["count"] = ops.group_counts(starts, ng, G, n)
             return cache["count"]
 
+        def validity(on):
+            m = src.columns.get(valid_name(on))
+            return None if m is None else _contig(m)
+
+        def nvalid(on):
+            """Non-null values per group (= rows per group for a column without nulls)."""
+            m = validity(on)
+            if m is None:
+                return counts()
+            if ("nvalid", on) not in cache:
+                cache[("valid64", on)] = ops.valid_as_int64(m)
+                cache[("nvalid", on)] = ops.segmented_reduce(starts, ng, G, perm, cache[("valid64", on)], n)[0]
+            return cache[("nvalid", on)]
+
         def smm(on):
             if ("smm", on) not in cache:
-                cache[("smm", on)] = ops.segmented_reduce(starts, ng, G, perm, _value_column(src, on), n, True, True, True)
+                v, m = _value_column(src, on), validity(on)
+                if m is None:
+                    cache[("smm", on)] = ops.segmented_reduce(starts, ng, G, perm, v, n, True, True, True)
+                else:   # a null row enters every reduction as that reduction's identity
+                    s_ = ops.segmented_reduce(starts, ng, G, perm, ops.mask_values(v, m, 0), n)[0]
+                    mn = ops.segmented_reduce(starts, ng, G, perm, ops.mask_values(v, m, 1), n, False, True, False)[1]
+                    mx = ops.segmented_reduce(starts, ng, G, perm, ops.mask_values(v, m, 2), n, False, False, True)[2]
+                    cache[("smm", on)] = (s_, mn, mx)
             return cache[("smm", on)]
+
+        def with_null_counts(acc, on):
+            """Accumulators of a nullable column also say how many of the group's rows were non-null / there at all."""
+            if validity(on) is not None:
+                acc[name + SEP + "nvalid"], acc[name + SEP + "rows"] = nvalid(on), counts()
+            return acc
 
         if kind == "count":
             return {name: counts()}
         if kind == "quantile":
             on = agg._key_fn
+            if validity(on) is not None:
+                raise NotImplementedError(f"Quantile over the nullable column {on!r} is not implemented on device blocks")
             if ("qperm", on) not in cache:  # rows ordered by (keys, value): same group positions as `starts`
                 cache[("qperm", on)] = _argsort_keys(src, list(cache.get("keys", [])) + [on], want_codes=False)[0]
             return {name: ops.group_quantile(starts, ng, G, cache[("qperm", on)], _value_column(src, on), n, agg._q)}
+        on = agg._key_fn
         if kind in ("sum", "min", "max"):
-            return {name: smm(agg._key_fn)[("sum", "min", "max").index(kind)]}
+            return with_null_counts({name: smm(on)[("sum", "min", "max").index(kind)]}, on)
         if kind == "absmax":
-            t = smm(agg._key_fn)
-            return {name: ops.absmax_groups(t[1], t[2])}
-        if kind == "mean":
-            return {name: smm(agg._key_fn)[0], name + SEP + "count": counts()}
+            t = smm(on)
+            return with_null_counts({name: ops.absmax_groups(t[1], t[2])}, on)
+        if kind == "mean":      # the denominator counts the non-null values
+            return with_null_counts({name: smm(on)[0], name + SEP + "count": nvalid(on)}, on)
         if kind == "std":
-            s_, cnt = smm(agg._key_fn)[0], counts()
-            if ("mean", agg._key_fn) not in cache:
-                cache[("mean", agg._key_fn)] = ops.finalize_groups(s_, cnt, 0)
-            m2 = ops.segmented_reduce(starts, ng, G, perm, _value_column(src, agg._key_fn), n,
-                                      center=cache[("mean", agg._key_fn)])[0]
-            return {name: m2, name + SEP + "sum": s_, name + SEP + "count": cnt}
+            s_, cnt = smm(on)[0], nvalid(on)
+            if ("mean", on) not in cache:
+                cache[("mean", on)] = ops.finalize_groups(s_, cnt, 0)
+            if validity(on) is None:
+                m2 = ops.segmented_reduce(starts, ng, G, perm, _value_column(src, on), n, center=cache[("mean", on)])[0]
+            else:               # null rows get weight 0 in the sum of squared differences
+                nvalid(on)
+                m2 = ops.segmented_reduce(starts, ng, G, perm, ops.mask_values(_value_column(src, on), validity(on), 0), n,
+                                          center=cache[("mean", on)], weights=cache[("valid64", on)])[0]
+            return with_null_counts({name: m2, name + SEP + "sum": s_, name + SEP + "count": cnt}, on)
     if kind == "count":
         if raw:
             out[name] = ops.group_counts(starts, ng, G, n)
         else:
             out[name] = ops.segmented_reduce(starts, ng, G, perm, _contig(src.columns[name]), n)[0]
         return out
+    if not raw and name + SEP + "nvalid" in src.columns:    # partials of a nullable column: both counts add up
+        for extra in ("nvalid", "rows"):
+            out[name + SEP + extra] = ops.segmented_reduce(starts, ng, G, perm, _contig(src.columns[name + SEP + extra]), n)[0]
+    if raw and src.columns.get(valid_name(agg._key_fn)) is not None:
+        raise NotImplementedError("nullable value columns are reduced through the shared-pass path (cache) only")
     col = _value_column(src, agg._key_fn) if raw else _contig(src.columns[name])
     if kind == "sum":
         out[name] = ops.segmented_reduce(starts, ng, G, perm, col, n)[0]
@@ -264,6 +309,13 @@ def _finalize(kind: str, agg: AggregateFn, name: str, acc: Dict[str, torch.Tenso
     raise ValueError(kind)
 
 
+def _finalize_validity(agg: AggregateFn, name: str, acc: Dict[str, torch.Tensor], hidden: Dict[str, torch.Tensor]) -> None:
+    """The finished column of a nullable input is nullable itself: null_aggregate.py:11-17 decides per group."""
+    if name + SEP + "nvalid" in acc:
+        hidden[valid_name(name)] = ops.group_validity(acc[name + SEP + "nvalid"], acc[name + SEP + "rows"],
+                                                      bool(getattr(agg, "_ignore_nulls", True)))
+
+
 def _check_key(key):
     """None (global aggregation), one column name, or a list of >= 2 column names (at most 4)."""
     if isinstance(key, list):
@@ -301,11 +353,18 @@ def _argsort_keys(block: DeviceBlock, keys: List[str], want_codes: bool):
     return perm, codes
 
 
+def _refuse_nullable_keys(block: DeviceBlock, keys: Sequence[str]) -> None:
+    for k in keys:
+        if valid_name(k) in block.columns:
+            raise NotImplementedError(f"groupby key column {k!r} is nullable: null keys are not supported on device blocks")
+
+
 def aggregate_sorted(block: DeviceBlock, key, aggs: Sequence[AggregateFn], perm, codes, finalize: bool, n: int) -> DeviceBlock:
     """One-shot groupby over rows visited in sorted order `perm`. `codes`: the ascending codes of the
     (single) key column in that order, or None to derive them from the block."""
     key = _check_key(key)
     keys = _key_list(key)
+    _refuse_nullable_keys(block, keys)
     dev = block.device
     names = resolved_names(aggs)
     if not finalize and _holistic(aggs):
@@ -334,13 +393,16 @@ def aggregate_sorted(block: DeviceBlock, key, aggs: Sequence[AggregateFn], perm,
         for k in keys:
             cols[k] = ops.gather(_contig(block.columns[k]), first_rows)
     cache: dict = {"keys": keys}
+    hidden: Dict[str, torch.Tensor] = {}
     for agg, name in zip(aggs, names):
         kind = _device_kind(agg)
         acc = _reduce_partials(kind, agg, name, block, starts, ng, G, perm, n, raw=True, cache=cache)
         if finalize:
             cols[name] = _finalize(kind, agg, name, acc)
+            _finalize_validity(agg, name, acc, hidden)
         else:
             cols.update(acc)
+    cols.update(hidden)
     return DeviceBlock(cols, num_rows=G, device=dev)
 
 
@@ -385,13 +447,16 @@ def merge_combined_blocks(blocks: Sequence[DeviceBlock], key, aggs: Sequence[Agg
         first_rows = ops.gather(perm, starts[:G].contiguous())
         for k in keys:
             cols[k] = ops.gather(_contig(allp.columns[k]), first_rows)
+    hidden: Dict[str, torch.Tensor] = {}
     for agg, name in zip(aggs, names):
         kind = _device_kind(agg)
         acc = _reduce_partials(kind, agg, name, allp, starts, ng, G, perm, n, raw=False)
         if finalize:
             cols[name] = _finalize(kind, agg, name, acc)
+            _finalize_validity(agg, name, acc, hidden)
         else:
             cols.update(acc)
+    cols.update(hidden)
     return DeviceBlock(cols, num_rows=G, device=dev)
 
 
@@ -423,7 +488,7 @@ def dense_aggregate(block: DeviceBlock, key, aggs: Sequence[AggregateFn], finali
     AbsMax over int64 columns - order-independent integer arithmetic, so the rows can be added straight into
     accumulator tables indexed by `key - min(key)` (csrc/groupby.cu, "Dense-range aggregation") and the result is
     bit-identical to the sorted path. Costs one read of the key column to find its range (and the decision)."""
-    if not isinstance(key, str) or block.num_rows < DENSE_MIN_ROWS:
+    if not isinstance(key, str) or block.num_rows < DENSE_MIN_ROWS or valid_name(key) in block.columns:
         return None
     kcol = block.columns[key]
     if kcol.dim() != 1 or kcol.dtype.is_floating_point or kcol.dtype not in ops._KEY_TYPES:
@@ -435,7 +500,7 @@ def dense_aggregate(block: DeviceBlock, key, aggs: Sequence[AggregateFn], finali
             return None
         if kind != "count":
             v = block.columns.get(agg._key_fn)
-            if v is None or v.dim() != 1 or v.dtype != torch.int64:
+            if v is None or v.dim() != 1 or v.dtype != torch.int64 or valid_name(agg._key_fn) in block.columns:
                 return None
         kinds.append(kind)
     kcol = _contig(kcol)

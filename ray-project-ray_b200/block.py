@@ -25,8 +25,11 @@ costs a pass over every record: the L2 fetches whole 128-byte lines). It is buil
 (`to_records(key_prefix=[...])`), comes out of every sort for free (the sort writes the sorted keys), and is simply
 dropped by operations that do not maintain it - `key_column` packs it again on demand.
 
-Null values and variable-width columns are outside the device format (fixed-width
-int/float keys and payloads); ingesting an Arrow column with nulls raises.
+Null values: a nullable VALUE column is its values (0 where null) plus a hidden validity column `<col>::valid`
+(uint8, 1 = present) that travels through every operation like any other column and never shows in the schema;
+aggregations apply the reference's null policy to it (aggregate.py), egress turns it back into Arrow nulls / NaN.
+Nulls in sort or groupby KEY columns and variable-width columns are outside the device format (SURVEY.md §8:
+fixed-width int/float keys and payloads).
 """
 from __future__ import annotations
 
@@ -158,6 +161,15 @@ def _to_host(t: torch.Tensor) -> np.ndarray:
 
 # ------------------------------------------------------------------ record layout helpers
 BYTE_KEY_SEP = "::be"   # `<column>::be<i>` = the i-th big-endian 8-byte chunk of a byte-string key column
+VALID_SEP = "::valid"   # `<column>::valid` = hidden validity column (uint8, 1 = present) of a nullable value column
+
+
+def valid_name(col: str) -> str:
+    return f"{col}{VALID_SEP}"
+
+
+def is_hidden(name: str) -> bool:
+    return name.endswith(VALID_SEP)
 RECORD_ALIGN = 16
 
 
@@ -295,12 +307,18 @@ class DeviceBlock:
 
         device = device or default_device()
         cols: Dict[str, torch.Tensor] = {}
+        hidden: Dict[str, torch.Tensor] = {}
         for name in table.column_names:
             col = table[name]
-            if col.null_count:
-                raise ValueError(f"column {name!r} has nulls; the device block format holds non-null fixed-width data")
             if isinstance(col, pa.ChunkedArray):
                 col = col.combine_chunks()
+            if col.null_count:
+                if not (pa.types.is_integer(col.type) or pa.types.is_floating(col.type)):
+                    raise ValueError(f"column {name!r} ({col.type}) has nulls; only numeric columns may be nullable in a device block")
+                import pyarrow.compute as pac
+
+                hidden[valid_name(name)] = _to_device(pac.is_valid(col).to_numpy(zero_copy_only=False).astype(np.uint8), device)
+                col = pac.fill_null(col, 0)
             if pa.types.is_fixed_size_binary(col.type):
                 w = col.type.byte_width
                 buf = np.frombuffer(col.buffers()[1], dtype=np.uint8, count=len(col) * w, offset=col.offset * w)
@@ -310,19 +328,29 @@ class DeviceBlock:
             else:
                 arr = col.to_numpy(zero_copy_only=False)
             cols[name] = _to_device(arr, device)
+        cols.update(hidden)
         return DeviceBlock(cols, num_rows=table.num_rows, device=device)
 
     @staticmethod
     def from_pandas(df, device: Optional[torch.device] = None) -> "DeviceBlock":
-        """pandas marks missing values with NaN / None / NaT and the reference turns them into Arrow nulls on the
-        way in (pa.Table.from_pandas). The device block format holds no nulls, so such a frame is refused - passing
-        the NaNs through would silently change Count / Mean / Min / Max (null_aggregate.py:11-17). NaN as a VALUE is
-        what `from_numpy` ingests."""
+        """pandas marks missing values with NaN / None and the reference turns them into Arrow nulls on the way in
+        (pa.Table.from_pandas): numeric columns with missing values become nullable columns here too (NaN as a VALUE
+        is what `from_numpy` ingests). Missing values in non-numeric columns are refused."""
+        cols: Dict[str, np.ndarray] = {}
+        hidden: Dict[str, np.ndarray] = {}
         for c in df.columns:
-            if df[c].isna().any():
-                raise ValueError(f"column {c!r} has missing values (NaN / None), which are nulls in ray.data; the device "
-                                 f"block format holds non-null fixed-width data")
-        return DeviceBlock.from_numpy({str(c): df[c].to_numpy() for c in df.columns}, device)
+            ser = df[c]
+            if ser.isna().any():
+                if not (np.issubdtype(ser.dtype, np.number) or str(ser.dtype) in ("Int64", "Int32", "Float64")):
+                    raise ValueError(f"column {c!r} ({ser.dtype}) has missing values; only numeric columns may be nullable "
+                                     f"in a device block")
+                hidden[valid_name(str(c))] = (~ser.isna()).to_numpy().astype(np.uint8)
+                ser = ser.fillna(0)
+                if str(ser.dtype) in ("Int64", "Int32"):
+                    ser = ser.astype(str(ser.dtype).lower())
+            cols[str(c)] = ser.to_numpy()
+        cols.update(hidden)
+        return DeviceBlock.from_numpy(cols, device)
 
     @staticmethod
     def empty(device: Optional[torch.device] = None) -> "DeviceBlock":
@@ -424,10 +452,19 @@ class DeviceBlock:
     def __repr__(self):
         return f"DeviceBlock(rows={self._n}, {self.schema()})"
 
+    def visible_names(self) -> List[str]:
+        """The columns a user sees: everything but the hidden validity columns."""
+        return [k for k in self.columns if not is_hidden(k)]
+
+    def validity(self, col: str) -> Optional[torch.Tensor]:
+        """uint8 [n] (1 = present) if `col` is nullable, else None."""
+        return self.columns.get(valid_name(col))
+
     def schema(self) -> Optional[Schema]:
         if not self.columns:
             return None
-        return Schema(list(self.columns), [(t.dtype, tuple(t.shape[1:])) for t in self.columns.values()])
+        names = self.visible_names()
+        return Schema(names, [(self.columns[k].dtype, tuple(self.columns[k].shape[1:])) for k in names])
 
     def size_bytes(self) -> int:
         return int(sum(t.numel() * t.element_size() for t in self.columns.values()))
@@ -440,6 +477,7 @@ class DeviceBlock:
                            device=self.device, aux={k: v[start:end] for k, v in self.aux.items()})
 
     def select(self, names: Sequence[str]) -> "DeviceBlock":
+        names = list(names) + [valid_name(k) for k in names if valid_name(k) in self.columns and valid_name(k) not in names]
         return DeviceBlock({k: self.columns[k] for k in names}, num_rows=self._n, device=self.device,
                            aux={k: v for k, v in self.aux.items() if k.rpartition(BYTE_KEY_SEP)[0] in names})
 
@@ -455,26 +493,45 @@ class DeviceBlock:
         if len(blocks) == 1:
             return blocks[0]
         names = blocks[0].column_names
+        for b in blocks[1:]:    # a column may be nullable in some blocks only: the others are all-present
+            names += [k for k in b.column_names if is_hidden(k) and k not in names]
         out: Dict[str, torch.Tensor] = {}
         for name in names:
-            parts = [b.columns[name] for b in blocks]
+            parts = [b.columns[name] if name in b.columns else torch.ones(b.num_rows, dtype=torch.uint8, device=b.device)
+                     for b in blocks]
             out[name] = _join_views(parts)
         aux = {k: _join_views([b.aux[k] for b in blocks]) for k in blocks[0].aux if all(k in b.aux for b in blocks)}
         return DeviceBlock(out, device=blocks[0].device, aux=aux)
 
     # -- egress (D2H happens only here) -------------------------------------------------
     def to_numpy(self, columns: Optional[Sequence[str]] = None) -> Dict[str, np.ndarray]:
-        names = list(columns) if columns is not None else list(self.columns)
-        return {k: _to_host(_contig(self.columns[k])) for k in names}
+        """Host copies of the (visible) columns. Null entries of a nullable column come back as NaN - the column as
+        float64 if it holds integers, which is what pyarrow's to_numpy gives a nullable integer column."""
+        names = list(columns) if columns is not None else self.visible_names()
+        out = {}
+        for k in names:
+            v = _to_host(_contig(self.columns[k]))
+            m = self.columns.get(valid_name(k))
+            if m is not None and v.ndim == 1:
+                ok = _to_host(_contig(m)).astype(bool)
+                if not ok.all():
+                    v = v.astype(np.float64) if not np.issubdtype(v.dtype, np.floating) else v.copy()
+                    v[~ok] = np.nan
+            out[k] = v
+        return out
 
     def to_arrow(self):
         import pyarrow as pa
 
         arrays, names = [], []
-        for k, v in self.to_numpy().items():
+        for k in self.visible_names():
+            v = _to_host(_contig(self.columns[k]))
+            m = self.columns.get(valid_name(k))
             if v.ndim == 2:
                 arrays.append(pa.FixedSizeBinaryArray.from_buffers(pa.binary(v.shape[1] * v.dtype.itemsize), len(v),
                                                                    [None, pa.py_buffer(np.ascontiguousarray(v))]))
+            elif m is not None:
+                arrays.append(pa.array(v, mask=~_to_host(_contig(m)).astype(bool)))
             else:
                 arrays.append(pa.array(v))
             names.append(k)
@@ -576,7 +633,7 @@ class DeviceBlockAccessor(BlockAccessor):
         return self._block.schema()
 
     def column_names(self) -> List[str]:
-        return self._block.column_names
+        return self._block.visible_names()
 
     def to_block(self) -> DeviceBlock:
         return self._block
@@ -594,8 +651,16 @@ class DeviceBlockAccessor(BlockAccessor):
 
     def iter_rows(self, public_row_format: bool = True) -> Iterator[Dict[str, Any]]:
         host = self._block.to_numpy()
+        nullable = {k for k in host if self._block.validity(k) is not None}
+
+        def item(k, v, i):
+            if v.ndim != 1:
+                return v[i]
+            x = v[i].item()
+            return None if (k in nullable and x != x) else x      # a null comes back from to_numpy as NaN
+
         for i in range(self._block.num_rows):
-            yield {k: (v[i].item() if v.ndim == 1 else v[i]) for k, v in host.items()}
+            yield {k: item(k, v, i) for k, v in host.items()}
 
     def slice(self, start: int, end: int, copy: bool = False) -> DeviceBlock:
         out = self._block.slice(start, end)
@@ -684,6 +749,10 @@ class DeviceBlockAccessor(BlockAccessor):
         enqueued first: asking blocks the host until the sort has run, not the device."""
         b = self._block
         cols, desc = sort_key.get_columns(), sort_key.get_descending()
+        for c in cols:
+            if valid_name(c.rpartition(BYTE_KEY_SEP)[0] or c) in b.columns or valid_name(c) in b.columns:
+                raise NotImplementedError(f"sort key column {c!r} is nullable: null keys (sorted last by the reference) are not "
+                                          f"supported on device blocks")
         if 1 < len(cols) <= 1 + ops.FIX_TIES_MAX_COLS and b.num_rows >= _DISTINCT_FIRST_MIN_ROWS:
             first = self._argsort_first_column_then_ties(cols, desc, want_codes)
             if first is not None:

@@ -398,7 +398,7 @@ finalize_kernel(const void* __restrict__ sum, int vt, const int64_t* __restrict_
   for (uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; g < G; g += (uint64_t)gridDim.x * blockDim.x) {
     const double s = (vt == B200X_VAL_I64) ? (double)((const int64_t*)sum)[g] : ((const double*)sum)[g];
     const double c = (double)counts[g];
-    if (mode == 0) out[g] = s / c;
+    if (mode == 0) out[g] = c == 0 ? 0.0 : s / c;   // (no non-null value: the column's validity says so; keeps merges NaN-free)
     else out[g] = (counts[g] < 2) ? 0.0 : sqrt(s / (c - (double)ddof));
   }
 }
@@ -681,6 +681,31 @@ dense_write_kernel(const long long* __restrict__ cnt, uint64_t range, uint64_t b
       if (t < tabs.n) tabs.out[t][g] = tabs.in[t][i];
     ++g;
   }
+}
+
+// ---------------------------------------------------------------------------
+// Nulls in value columns: the reference's null policy (null_aggregate.py:11-17)
+// ---------------------------------------------------------------------------
+// A nullable column is its values plus a validity byte per row. The reductions above have no notion of validity, so a
+// null row is given the identity of the reduction it enters - 0 for sums, the type's largest / smallest value for
+// min / max - and the number of valid rows per group is reduced like any other int64 column (out_valid64).
+template <typename T>
+__global__ void __launch_bounds__(256)
+mask_values_kernel(const T* __restrict__ values, const unsigned char* __restrict__ valid, uint64_t n, T fill,
+                   T* __restrict__ out_values, long long* __restrict__ out_valid64) {
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const bool ok = valid[i] != 0;
+    if (out_values) out_values[i] = ok ? values[i] : fill;
+    if (out_valid64) out_valid64[i] = ok ? 1ll : 0ll;
+  }
+}
+
+// validity of a group's result: ignore_nulls: at least one valid row; else: no null row at all (and at least one row)
+__global__ void __launch_bounds__(256)
+group_validity_kernel(const long long* __restrict__ nvalid, const long long* __restrict__ rows, uint64_t g, int ignore_nulls,
+                      unsigned char* __restrict__ out) {
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < g; i += (uint64_t)gridDim.x * blockDim.x)
+    out[i] = (nvalid[i] > 0 && (ignore_nulls || nvalid[i] == rows[i])) ? 1 : 0;
 }
 
 static inline uint32_t tiles_of(size_t n) { return (uint32_t)((n + G_TILE - 1) / G_TILE); }
@@ -986,5 +1011,48 @@ extern "C" int b200x_dense_group_compact(uint64_t base_code, size_t range, int k
   dense_write_kernel<<<blocks, DC_THREADS, 0, st>>>((const long long*)count_tab, range, base_code, key_type, block_counts,
                                                     keys_out, (long long*)count_out, tabs);
   B200X_LAUNCH_CHECK("dense_write_kernel");
+  return B200X_OK;
+}
+
+extern "C" int b200x_mask_values(const void* values, int value_type, const uint8_t* valid, size_t n, int fill_mode,
+                                 void* out_values, int64_t* out_valid64, void* stream_) {
+  B200X_ON_DEVICE_OF(valid);
+  cudaStream_t st = (cudaStream_t)stream_;
+  if (n == 0) return B200X_OK;
+  if (valid == nullptr || (out_values == nullptr && out_valid64 == nullptr) || (out_values != nullptr && values == nullptr) ||
+      (value_type != 0 && value_type != 1) || fill_mode < 0 || fill_mode > 2) {
+    set_error("b200x_mask_values: bad arguments (int64 / float64 values, fill_mode 0 zero, 1 largest, 2 smallest)");
+    return B200X_ERR_ARG;
+  }
+  uint64_t blocks = (n + 255) / 256;
+  const uint64_t cap = (uint64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  if (value_type == 0) {   // B200X_VAL_I64
+    const int64_t fill = fill_mode == 0 ? 0 : (fill_mode == 1 ? INT64_MAX : INT64_MIN);
+    mask_values_kernel<int64_t><<<(uint32_t)blocks, 256, 0, st>>>((const int64_t*)values, valid, n, fill, (int64_t*)out_values,
+                                                                  (long long*)out_valid64);
+  } else {
+    const double fill = fill_mode == 0 ? 0.0 : (fill_mode == 1 ? (double)INFINITY : -(double)INFINITY);
+    mask_values_kernel<double><<<(uint32_t)blocks, 256, 0, st>>>((const double*)values, valid, n, fill, (double*)out_values,
+                                                                 (long long*)out_valid64);
+  }
+  B200X_LAUNCH_CHECK("mask_values_kernel");
+  return B200X_OK;
+}
+
+extern "C" int b200x_group_validity(const int64_t* nvalid, const int64_t* rows, size_t num_groups, int ignore_nulls,
+                                    uint8_t* out, void* stream_) {
+  B200X_ON_DEVICE_OF(out);
+  if (num_groups == 0) return B200X_OK;
+  if (nvalid == nullptr || rows == nullptr || out == nullptr) {
+    set_error("b200x_group_validity: NULL pointer");
+    return B200X_ERR_ARG;
+  }
+  uint64_t blocks = (num_groups + 255) / 256;
+  const uint64_t cap = (uint64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  group_validity_kernel<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream_>>>((const long long*)nvalid, (const long long*)rows,
+                                                                           num_groups, ignore_nulls, out);
+  B200X_LAUNCH_CHECK("group_validity_kernel");
   return B200X_OK;
 }

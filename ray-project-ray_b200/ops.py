@@ -653,3 +653,32 @@ def permute_scatter_to_peers(col: torch.Tensor, first_global: int, total_rows: i
     with torch.cuda.device(dev):
         _lib.call("b200x_permute_scatter_to_peers", col.data_ptr(), row_bytes, row_bytes, n, first_global, total_rows,
                   seed & 0xFFFFFFFFFFFFFFFF, rows_per_rank, b, dst_pitch, w, _stream(dev))
+
+
+def mask_values(values: torch.Tensor, valid: torch.Tensor, fill_mode: int) -> torch.Tensor:
+    """values with null rows (valid == 0) replaced by the identity of a sum (0), min (1) or max (2) reduction."""
+    dev = _require_cuda(values, valid)
+    out = torch.empty_like(values)
+    with torch.cuda.device(dev):
+        _lib.call("b200x_mask_values", values.data_ptr(), value_type_of(values), valid.data_ptr(), values.numel(), fill_mode,
+                  out.data_ptr(), None, _stream(dev))
+    return out
+
+
+def valid_as_int64(valid: torch.Tensor) -> torch.Tensor:
+    """The validity bytes of a column as an int64 0 / 1 column (summed per group = number of non-null rows)."""
+    dev = _require_cuda(valid)
+    out = torch.empty(valid.numel(), dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        _lib.call("b200x_mask_values", None, VAL_I64, valid.data_ptr(), valid.numel(), 0, None, out.data_ptr(), _stream(dev))
+    return out
+
+
+def group_validity(nvalid: torch.Tensor, rows: torch.Tensor, ignore_nulls: bool) -> torch.Tensor:
+    """uint8 per group: does the aggregation have a result under the reference's null policy?"""
+    dev = _require_cuda(nvalid, rows)
+    out = torch.empty(nvalid.numel(), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        _lib.call("b200x_group_validity", nvalid.data_ptr(), rows.data_ptr(), nvalid.numel(), int(ignore_nulls), out.data_ptr(),
+                  _stream(dev))
+    return out

@@ -452,6 +452,71 @@ def run_quantile(shim=None):
     print("wrote quantile_outputs.json", os.path.getsize(os.path.join(OUT, "quantile_outputs.json")) // 1024, "KiB")
 
 
+def run_nulls(shim=None):
+    """Aggregations over nullable value columns (null policy of _internal/null_aggregate.py:11-17) -> null_outputs.json
+    (inputs included): the reference's own generate_aggregate_fn, pull and push, ignore_nulls True and False, grouped
+    and global; groups with no null, some nulls, only nulls."""
+    ray, rb, tc, PB = shim or install_shim()
+    from ray.data.block import BlockAccessor
+    from ray.data.context import DataContext
+    from ray.data.aggregate import AbsMax, Count, Max, Mean, Min, Std, Sum
+    agg_mod = importlib.import_module("ray.data._internal.planner.aggregate")
+
+    def bundles(tables):
+        return [rb.RefBundle([(Ref(t), BlockAccessor.for_block(t).get_metadata(None, None))], owns_blocks=True)
+                for t in tables]
+
+    def ctx():
+        return tc.TaskContext(task_idx=0, target_max_block_size=1 << 30,
+                              sub_progress_bar_dict={"Sort Sample": PB(), "Shuffle Map": PB(), "Shuffle Reduce": PB()})
+
+    def run(tables, key, aggs, push):
+        DataContext.get_current().use_push_based_shuffle = push
+        random.seed(777)
+        out, _ = agg_mod.generate_aggregate_fn(key, aggs)(bundles(tables), ctx())
+        cols = {}
+        for b in out:
+            t = ray.get(b.blocks[0][0])
+            if t.num_rows:
+                for c in t.column_names:
+                    cols.setdefault(c, []).extend(t[c].to_pylist())
+        return cols
+
+    rng = np.random.default_rng(20240711)
+    N, B, G = 1200, 4, 23
+    k = rng.integers(0, G, N, dtype=np.int64)
+    vi = rng.integers(-1000, 1000, N, dtype=np.int64)
+    vf = np.round(rng.standard_normal(N) * 10, 3)
+    null_i = rng.random(N) < 0.2
+    null_f = rng.random(N) < 0.3
+    null_i[k == 3] = True           # a group with only nulls
+    null_f[k == 3] = True
+    null_i[k == 5] = False          # a group without nulls
+    null_f[k == 5] = False
+    n = N // B
+    tables = [pa.table({"k": k[i * n:(i + 1) * n],
+                        "vi": pa.array(vi[i * n:(i + 1) * n], mask=null_i[i * n:(i + 1) * n]),
+                        "vf": pa.array(vf[i * n:(i + 1) * n], mask=null_f[i * n:(i + 1) * n]),
+                        "w": vi[i * n:(i + 1) * n]}) for i in range(B)]
+    gold = {"pyarrow": pa.__version__, "k": k.tolist(), "vi": vi.tolist(), "vf": vf.tolist(), "null_i": null_i.tolist(),
+            "null_f": null_f.tolist(), "blocks": B, "grouped": {}, "global": {}}
+
+    def aggs(ignore):
+        return [Count(), Sum("vi", ignore_nulls=ignore), Min("vi", ignore_nulls=ignore), Max("vi", ignore_nulls=ignore),
+                Mean("vi", ignore_nulls=ignore), Std("vi", ignore_nulls=ignore), AbsMax("vi", ignore_nulls=ignore),
+                Sum("vf", ignore_nulls=ignore), Min("vf", ignore_nulls=ignore), Max("vf", ignore_nulls=ignore),
+                Mean("vf", ignore_nulls=ignore), Std("vf", ignore_nulls=ignore), Sum("w", ignore_nulls=ignore), Mean("w")]
+
+    for push in (False, True):
+        for ignore in (True, False):
+            gold["grouped"][f"{'push' if push else 'pull'}_ignore{int(ignore)}"] = run(tables, "k", aggs(ignore), push)
+    for ignore in (True, False):
+        gold["global"][f"ignore{int(ignore)}"] = run(tables, None, aggs(ignore), False)
+    with open(os.path.join(OUT, "null_outputs.json"), "w") as fjson:
+        json.dump(gold, fjson, default=lambda o: o.item() if hasattr(o, "item") else str(o))
+    print("wrote null_outputs.json", os.path.getsize(os.path.join(OUT, "null_outputs.json")) // 1024, "KiB")
+
+
 def run_batcher(shim=None):
     """Batcher / ShufflingBatcher goldens (_internal/batcher.py) -> batcher_outputs.json. The classes are
     the reference's own; the driver loop is block_batching/util.py:116-139 restated (that module needs
@@ -562,8 +627,11 @@ if __name__ == "__main__":
         run_batcher()
     elif sys.argv[1:] == ["map_groups"]:
         run_map_groups()
+    elif sys.argv[1:] == ["nulls"]:
+        run_nulls()
     else:
         run_all()
         run_quantile()
         run_batcher()
         run_map_groups()
+        run_nulls()

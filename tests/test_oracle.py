@@ -242,3 +242,37 @@ def test_key_boundaries_match_reference_map_groups():
         keys = [c["keys"]] if isinstance(c["keys"], str) else c["keys"]
         cols = [np.asarray(c["columns"][k]) for k in keys]
         assert orc.key_boundaries(cols) == c["boundaries"]
+
+
+def _null_golden():
+    import json
+    import os
+
+    with open(os.path.join(os.path.dirname(__file__), "golden", "null_outputs.json")) as f:
+        return json.load(f)
+
+
+def test_null_policy_oracle_matches_reference_outputs():
+    """oracle.null_group_aggregate == the reference's own generate_aggregate_fn on nullable columns (pull and push,
+    ignore_nulls True / False, grouped and global): tests/golden/make_golden.py run_nulls."""
+    g = _null_golden()
+    k = np.asarray(g["k"])
+    cols = {"vi": (np.asarray(g["vi"], dtype=np.int64), np.asarray(g["null_i"])),
+            "vf": (np.asarray(g["vf"], dtype=np.float64), np.asarray(g["null_f"])),
+            "w": (np.asarray(g["vi"], dtype=np.int64), np.zeros(len(k), dtype=bool))}
+    checked = 0
+    for tag, out in list(g["grouped"].items()) + [("global_" + t, o) for t, o in g["global"].items()]:
+        ignore = tag.endswith("1")
+        keys = None if tag.startswith("global") else k
+        assert out["count()"] == ([len(k)] if keys is None else np.unique(k, return_counts=True)[1].tolist())
+        for name, got in out.items():
+            if "(" not in name or name == "count()":
+                continue
+            kind, col = name[:-1].split("(")
+            want = orc.null_group_aggregate(keys, cols[col][0], cols[col][1], kind, ignore or name == "mean(w)")
+            assert [x is None for x in got] == [x is None for x in want], (tag, name)
+            a = np.array([x for x in got if x is not None], dtype=np.float64)
+            b = np.array([x for x in want if x is not None], dtype=np.float64)
+            np.testing.assert_allclose(a, b, rtol=1e-12, atol=1e-9, err_msg=f"{tag} {name}")
+            checked += 1
+    assert checked >= 6 * 13

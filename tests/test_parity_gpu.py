@@ -567,13 +567,98 @@ def test_boundary_above_integer_range_and_nan_boundary(cuda_device):
         find_partition_indices(asc, [float("nan")], False)
 
 
-def test_from_pandas_refuses_missing_values(cuda_device):
+@pytest.mark.parametrize("sched", ["fused", "pull", "push"])
+@pytest.mark.parametrize("ignore", [True, False])
+def test_null_policy_matches_reference_outputs(sched, ignore, cuda_device):
+    """Aggregations over nullable value columns equal the outputs of the reference's own generate_aggregate_fn
+    (tests/golden/null_outputs.json): nulls skipped or poisoning per `ignore_nulls`, all-null groups null, Count counts
+    rows, Mean / Std divide by the non-null count - grouped under every scheduler, and global."""
+    import json
+    import os
+
+    from ray_project_ray_b200.aggregate import AbsMax
+
+    with open(os.path.join(os.path.dirname(__file__), "golden", "null_outputs.json")) as f:
+        g = json.load(f)
+    _set_scheduler(sched)
+    N, B = len(g["k"]), g["blocks"]
+    n = N // B
+    tables = []
+    for i in range(B):
+        sl = slice(i * n, (i + 1) * n)
+        tables.append(pa.table({"k": np.asarray(g["k"][sl], dtype=np.int64),
+                                "vi": pa.array(np.asarray(g["vi"][sl], dtype=np.int64), mask=np.asarray(g["null_i"][sl])),
+                                "vf": pa.array(np.asarray(g["vf"][sl], dtype=np.float64), mask=np.asarray(g["null_f"][sl])),
+                                "w": np.asarray(g["vi"][sl], dtype=np.int64)}))
+    ds = rd.from_arrow(tables)
+    assert ds.columns() == ["k", "vi", "vf", "w"]                    # validity columns are hidden
+    back = ds.to_numpy()
+    assert np.isnan(back["vi"][np.asarray(g["null_i"])]).all() and not np.isnan(back["vi"][~np.asarray(g["null_i"])]).any()
+    aggs = [Count(), Sum("vi", ignore_nulls=ignore), Min("vi", ignore_nulls=ignore), Max("vi", ignore_nulls=ignore),
+            Mean("vi", ignore_nulls=ignore), Std("vi", ignore_nulls=ignore), AbsMax("vi", ignore_nulls=ignore),
+            Sum("vf", ignore_nulls=ignore), Min("vf", ignore_nulls=ignore), Max("vf", ignore_nulls=ignore),
+            Mean("vf", ignore_nulls=ignore), Std("vf", ignore_nulls=ignore), Sum("w", ignore_nulls=ignore), Mean("w")]
+    out = ds.groupby("k").aggregate(*aggs)
+    want = g["grouped"][f"{'push' if sched == 'push' else 'pull'}_ignore{int(ignore)}"]
+    assert out.columns() == list(want)
+    rows = out.take_all()
+    assert [r["k"] for r in rows] == want["k"] and [r["count()"] for r in rows] == want["count()"]
+    for c in want:
+        got = [r[c] for r in rows]
+        assert [x is None for x in got] == [x is None for x in want[c]], c
+        a = np.array([x for x in got if x is not None], dtype=np.float64)
+        b = np.array([x for x in want[c] if x is not None], dtype=np.float64)
+        if c.startswith(("sum(vi", "min(vi", "max(vi", "abs_max(vi", "sum(w")):
+            np.testing.assert_array_equal(a, b, err_msg=c)             # integer results are exact
+        else:
+            np.testing.assert_allclose(a, b, rtol=FLOAT_RTOL, atol=0, err_msg=c)
+    glob = ds.aggregate(*aggs)
+    gw = g["global"][f"ignore{int(ignore)}"]
+    for c, v in gw.items():
+        if v[0] is None:
+            assert glob[c] is None, c
+        else:
+            assert glob[c] is not None and abs(glob[c] - v[0]) <= FLOAT_RTOL * abs(v[0]), c
+    # through Arrow and back: nulls where they were
+    t = out.get_internal_block_refs()[0].to_arrow() if out.num_blocks() else None
+    if t is not None and t.num_rows:
+        assert t["sum(vi)"].null_count == sum(x is None for x in [r["sum(vi)"] for r in out.get_internal_block_refs()[0:1] for r in
+                                                                  BlockAccessor.for_block(r).iter_rows()])
+    # nullable keys are refused, not silently grouped under 0
+    bad = rd.from_arrow(pa.table({"k": pa.array([1, None, 2]), "v": [1, 2, 3]}))
+    with pytest.raises(NotImplementedError):
+        bad.groupby("k").sum("v").take_all()
+    with pytest.raises(NotImplementedError):
+        bad.sort("k").take_all()
+
+
+def test_from_pandas_missing_values_are_nulls(cuda_device):
+    """pandas NaN / None in a numeric column = nulls in ray.data (pa.Table.from_pandas): ingested as a nullable column,
+    so Count / Mean / Min see them as the reference does; non-numeric columns with missing values are refused."""
     import pandas as pd
 
-    with pytest.raises(ValueError, match="missing values"):
-        rd.from_pandas(pd.DataFrame({"a": [1.0, np.nan, 3.0]}))
+    ds = rd.from_pandas(pd.DataFrame({"a": [1.0, np.nan, 3.0], "b": [1, 2, 3]}))
+    assert ds.columns() == ["a", "b"]
+    assert ds.sum("a") == 4.0 and ds.mean("a") == 2.0 and ds.min("a") == 1.0
+    assert ds.sum("a", ignore_nulls=False) is None
+    assert ds.aggregate(Count()) == {"count()": 3}
     ok = rd.from_pandas(pd.DataFrame({"a": [1.0, 2.0, 3.0]}))
     assert ok.sum("a") == 6.0
+    with pytest.raises(ValueError, match="missing values"):
+        rd.from_pandas(pd.DataFrame({"s": ["x", None, "z"]}))
+    # nulls ride along through sort and shuffle as payload
+    rng = np.random.default_rng(2)
+    k = rng.permutation(5000).astype(np.int64)
+    v = rng.random(5000)
+    mask = rng.random(5000) < 0.3
+    t = pa.table({"k": k, "v": pa.array(v, mask=mask)})
+    s = rd.from_arrow(t).sort("k").to_numpy()
+    order = np.argsort(k)
+    np.testing.assert_array_equal(np.isnan(s["v"]), mask[order])
+    np.testing.assert_array_equal(s["v"][~mask[order]], v[order][~mask[order]])
+    sh = rd.from_arrow(t).random_shuffle(seed=1).to_numpy()
+    p = orc.feistel_permutation(5000, 1)
+    np.testing.assert_array_equal(np.isnan(sh["v"]), mask[p])
 
 
 def test_int64_sum_wraps_within_and_across_blocks(cuda_device):
