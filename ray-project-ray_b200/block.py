@@ -341,12 +341,14 @@ class DeviceBlock:
         for c in df.columns:
             ser = df[c]
             if ser.isna().any():
-                if not (np.issubdtype(ser.dtype, np.number) or str(ser.dtype) in ("Int64", "Int32", "Float64")):
+                import pandas as pd
+
+                if not pd.api.types.is_numeric_dtype(ser.dtype):
                     raise ValueError(f"column {c!r} ({ser.dtype}) has missing values; only numeric columns may be nullable "
                                      f"in a device block")
                 hidden[valid_name(str(c))] = (~ser.isna()).to_numpy().astype(np.uint8)
                 ser = ser.fillna(0)
-                if str(ser.dtype) in ("Int64", "Int32"):
+                if str(ser.dtype) in ("Int64", "Int32", "Int16", "Int8", "Float64", "Float32"):   # pandas' nullable dtypes
                     ser = ser.astype(str(ser.dtype).lower())
             cols[str(c)] = ser.to_numpy()
         cols.update(hidden)
