@@ -751,10 +751,16 @@ class DeviceBlockAccessor(BlockAccessor):
         enqueued first: asking blocks the host until the sort has run, not the device."""
         b = self._block
         cols, desc = sort_key.get_columns(), sort_key.get_descending()
-        for c in cols:
-            if valid_name(c.rpartition(BYTE_KEY_SEP)[0] or c) in b.columns or valid_name(c) in b.columns:
-                raise NotImplementedError(f"sort key column {c!r} is nullable: null keys (sorted last by the reference) are not "
-                                          f"supported on device blocks")
+        nullable = [c for c in cols if valid_name(c) in b.columns]
+        if nullable:
+            if len(cols) > 1:
+                raise NotImplementedError(f"multi-column sort keys with a nullable column ({nullable[0]!r}) are not supported "
+                                          f"on device blocks")
+            # Arrow puts nulls last in BOTH directions, after NaN, in input order (transform_pyarrow.py:17-21):
+            # a stable sort by the values, then a stable sort by "is present" descending on top of it
+            perm, _, _ = ops.argsort(b.key_column(cols[0]), desc)
+            perm, _, _ = ops.argsort(_contig(b.columns[valid_name(cols[0])]), True, perm_in=perm)
+            return perm, None, None, None
         if 1 < len(cols) <= 1 + ops.FIX_TIES_MAX_COLS and b.num_rows >= _DISTINCT_FIRST_MIN_ROWS:
             first = self._argsort_first_column_then_ties(cols, desc, want_codes)
             if first is not None:
@@ -834,6 +840,9 @@ class DeviceBlockAccessor(BlockAccessor):
         table, _ = self.sort(sort_key)
         if len(boundaries) == 0:
             return [table]
+        if any(b.validity(c) is not None for c in sort_key.get_columns()):
+            raise NotImplementedError("range partitioning by a nullable sort key is not supported on device blocks "
+                                      "(the default fused scheduler sorts such a dataset in one pass)")
         return find_partitions(table, boundaries, sort_key)
 
     @staticmethod

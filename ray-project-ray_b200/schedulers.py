@@ -408,6 +408,8 @@ def _distributed_exchange(spec: ExchangeTaskSpec, blocks: List[DeviceBlock], out
         _, sort_key = spec._map_args
         if sort_key.boundaries:
             raise NotImplementedError("user-specified boundaries are not supported across ranks")
+        if any(local.validity(c) is not None for c in sort_key.get_columns()):
+            raise NotImplementedError("nullable sort keys are not supported across ranks")
         out = D.dist_sort(local, sort_key)
         return _cut_sorted_evenly(out, sort_key.get_columns()[0], sort_key.get_descending(), parts)
     if type(spec) is ShuffleTaskSpec:
@@ -472,6 +474,13 @@ def fused_sort(blocks: List[DeviceBlock], boundaries: List[Any], sort_key: SortK
         return [DeviceBlock.empty(table.device) for _ in range(R)]
     acc = DeviceBlockAccessor(table)
     first = sort_key.get_columns()[0]
+    if table.validity(first) is not None:
+        # nulls sort last whatever the direction, so the sorted key column is not monotone: no key-based cuts
+        if not isinstance(boundaries, AutoBoundaries) and R > 1:
+            raise NotImplementedError("user boundaries on a nullable sort key are not supported on device blocks")
+        out, _ = acc.sort(sort_key)
+        n = out.num_rows
+        return _cut(out, [(i * n) // R for i in range(1, R)])
     if isinstance(boundaries, AutoBoundaries) and R > 1:
         # The cut positions only need the sorted keys: they are computed and read back while the payload
         # gather is still running, so the host is already enqueuing the next operator when the gather ends.

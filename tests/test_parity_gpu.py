@@ -628,8 +628,16 @@ def test_null_policy_matches_reference_outputs(sched, ignore, cuda_device):
     bad = rd.from_arrow(pa.table({"k": pa.array([1, None, 2]), "v": [1, 2, 3]}))
     with pytest.raises(NotImplementedError):
         bad.groupby("k").sum("v").take_all()
-    with pytest.raises(NotImplementedError):
-        bad.sort("k").take_all()
+    # a nullable SORT key: nulls last in both directions, after NaN, in input order (pyarrow's sort_indices)
+    rng = np.random.default_rng(3)
+    kv = np.round(rng.standard_normal(4000), 1)
+    kv[::97] = np.nan
+    kmask = rng.random(4000) < 0.15
+    t = pa.table({"k": pa.array(kv, mask=kmask), "row": np.arange(4000, dtype=np.int64)})
+    for desc in (False, True):
+        got = rd.from_arrow(t, override_num_blocks=None).sort("k", descending=desc).to_numpy()["row"]
+        want = pac.sort_indices(t, sort_keys=[("k", "descending" if desc else "ascending")], null_placement="at_end").to_numpy()
+        np.testing.assert_array_equal(got, want)
 
 
 def test_from_pandas_missing_values_are_nulls(cuda_device):
