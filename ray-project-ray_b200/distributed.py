@@ -269,8 +269,32 @@ def _sample_codes(codes_sorted: torch.Tensor, num_samples: int) -> torch.Tensor:
     return ops.gather(codes_sorted, torch.from_numpy(pos).to(codes_sorted.device))
 
 
-def dist_sort(local: DeviceBlock, sort_key: SortKey, group=None, samples_per_rank: int = 4096) -> DeviceBlock:
-    """Globally sort the rows held by all ranks; rank r ends up with the r-th key range."""
+def rank_splitters_from_boundaries(boundary_codes: np.ndarray, world: int, descending: bool) -> Tuple[np.ndarray, List[int]]:
+    """User boundaries across ranks (planner/sort.py:47-54: the R = len(boundaries) + 1 output partitions are fixed by
+    the user): rank r owns the partitions [edges[r], edges[r+1]), edges[j] = j * R // W, so the splitter between rank r
+    and r + 1 is the boundary that separates partition edges[r+1] - 1 from edges[r+1]. `boundary_codes`: the
+    boundaries' codes in partition order (ascending as codes for both directions). A row whose key equals a boundary
+    belongs to the partition on its right when ascending (`x < b` goes left, util.py:745-758) and to the one on its left
+    when descending (`x >= b` goes left): there the splitter is the boundary's code + 1. Returns (W-1 splitter codes,
+    edges)."""
+    R = len(boundary_codes) + 1
+    edges = [(j * R) // world for j in range(world + 1)]
+    out = np.zeros(world - 1, dtype=np.uint64)
+    top = np.uint64(0xFFFFFFFFFFFFFFFF)
+    for r in range(world - 1):
+        i = edges[r + 1] - 1
+        if i < 0:
+            out[r] = 0                      # this rank and the ones before it own no partition: everything goes right
+        else:
+            c = np.uint64(boundary_codes[i])
+            out[r] = (c + np.uint64(1) if c != top else top) if descending else c
+    return out, edges
+
+
+def dist_sort(local: DeviceBlock, sort_key: SortKey, group=None, samples_per_rank: int = 4096,
+              splitter_codes: Optional[np.ndarray] = None) -> DeviceBlock:
+    """Globally sort the rows held by all ranks; rank r ends up with the r-th key range. `splitter_codes` (W-1 ascending
+    uint64 codes, the same on every rank) fixes the ranges instead of sampling them."""
     world = dist.get_world_size(group)
     dev = local.device
     acc = DeviceBlockAccessor(local)
@@ -279,7 +303,7 @@ def dist_sort(local: DeviceBlock, sort_key: SortKey, group=None, samples_per_ran
     desc = sort_key.get_descending()
     use_p2p = dev.type == "cuda" and _transport() != "nccl" and p2p_available(dev, group)
     if use_p2p and _transport() != "p2p_sort_first":
-        return _p2p_partition_sort(local, sort_key, n, dev, group, samples_per_rank)
+        return _p2p_partition_sort(local, sort_key, n, dev, group, samples_per_rank, splitter_codes)
     perm = skeys = None
     if n > 0 and use_p2p:
         perm, codes, skeys = acc._argsort(sort_key, want_codes=True)   # no local gather: rows leave in sort order
@@ -301,7 +325,7 @@ def dist_sort(local: DeviceBlock, sort_key: SortKey, group=None, samples_per_ran
     dist.all_gather(gathered, padded, group=group)
     host = torch.stack(gathered).cpu().numpy()
     all_codes = np.concatenate([row[1:1 + int(row[0])].view(np.uint64) for row in host])
-    splitters = choose_splitters(all_codes, world)
+    splitters = choose_splitters(all_codes, world) if splitter_codes is None else np.asarray(splitter_codes, dtype=np.uint64)
     if n > 0 and splitters.size:
         sp = torch.from_numpy(splitters.view(np.int64)).to(dev)
         cuts = ops.search_sorted_codes(codes, sp, upper=False).cpu().tolist()
@@ -386,7 +410,8 @@ def _assemble_sorted(local: DeviceBlock, groups, recv: Dict[str, torch.Tensor], 
     return DeviceBlock({c: out_cols[c] for c in local.column_names}, num_rows=n_recv, device=dev, aux=aux)
 
 
-def _p2p_partition_sort(local: DeviceBlock, sort_key: SortKey, n: int, dev, group, samples_per_rank: int) -> DeviceBlock:
+def _p2p_partition_sort(local: DeviceBlock, sort_key: SortKey, n: int, dev, group, samples_per_rank: int,
+                        splitter_codes: Optional[np.ndarray] = None) -> DeviceBlock:
     """Partition-first distributed sort over peer memory:
       sample raw keys -> identical splitters on every rank -> per-row (owner, slot) targets (stable split,
       no sort) -> key columns stored into the owners' receive buffers -> while the payload columns follow
@@ -414,7 +439,7 @@ def _p2p_partition_sort(local: DeviceBlock, sort_key: SortKey, n: int, dev, grou
     header = [int(n > 0), int(plan is not None)] + ([plan["group"].pitch, plan["used"], plan["shift"], plan["copy"]] if plan else [0] * 4) \
         + [int(has_groups)]
     all_codes, hdrs = _gather_samples(sample_codes, samples_per_rank, world, dev, group, header)
-    splitters = choose_splitters(all_codes, world)
+    splitters = choose_splitters(all_codes, world) if splitter_codes is None else np.asarray(splitter_codes, dtype=np.uint64)
     if splitters.size != world - 1:   # no rank has any row
         splitters = np.full(world - 1, np.iinfo(np.uint64).max, dtype=np.uint64)
     everyone_has_rows = bool(hdrs[:, 0].all())
@@ -783,6 +808,34 @@ def _p2p_random_shuffle(local: DeviceBlock, seed: Optional[int], dev, group) -> 
     return DeviceBlock({c: cols[c] for c in local.column_names}, num_rows=got, device=dev)
 
 
+def _dist_aggregate_multi(local: DeviceBlock, keys: List[str], aggs, group, samples_per_rank: int) -> DeviceBlock:
+    """groupby over several key columns across ranks: local partials (sorted by all key columns), exchanged by the range
+    of the FIRST key column - equal first keys share an owner, so equal key tuples do - then merged by all columns."""
+    from .aggregate import _argsort_keys, aggregate_sorted, merge_combined_blocks
+
+    world = dist.get_world_size(group)
+    dev = local.device
+    n = local.num_rows
+    partial = None
+    if n > 0:
+        perm, _ = _argsort_keys(local, keys, want_codes=False)
+        partial = aggregate_sorted(local, keys, aggs, perm, None, finalize=False, n=n)
+    partial = _partial_like(partial, dev, group)
+    if partial is None:
+        return DeviceBlock.empty(dev)
+    pcodes = ops.encode_keys(_contig(partial.columns[keys[0]]), False)
+    all_codes, _ = _gather_samples(_sample_codes(pcodes, samples_per_rank), samples_per_rank, world, dev, group)
+    splitters = choose_splitters(all_codes, world)
+    if partial.num_rows and splitters.size:
+        cuts = ops.search_sorted_codes(pcodes, torch.from_numpy(splitters.view(np.int64)).to(dev), upper=False).cpu().tolist()
+    else:
+        cuts = [0] * (world - 1)
+    received = exchange_block(partial, split_counts_from_cuts(cuts, partial.num_rows), group)
+    if received.num_rows == 0:
+        return received
+    return merge_combined_blocks([received], keys, aggs, finalize=True)
+
+
 def dist_aggregate(local: DeviceBlock, key: Optional[str], aggs, group=None, samples_per_rank: int = 4096) -> DeviceBlock:
     """Sort-based groupby across ranks: local partials -> range exchange of partial rows -> merge."""
     from .aggregate import aggregate_sorted, dense_aggregate, merge_combined_blocks
@@ -790,9 +843,9 @@ def dist_aggregate(local: DeviceBlock, key: Optional[str], aggs, group=None, sam
 
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     dev = local.device
-    if isinstance(key, list):
-        raise NotImplementedError("multi-column groupby keys are not supported across ranks yet")
     local = SortAggregateTaskSpec._prune_unused_columns(local, key, aggs)
+    if isinstance(key, list):
+        return _dist_aggregate_multi(local, key, aggs, group, samples_per_rank)
     n = local.num_rows
     if key is None:
         partial = aggregate_sorted(local, None, aggs, None, None, finalize=False, n=n) if n else None

@@ -19,13 +19,14 @@ from __future__ import annotations
 import math
 from typing import Any, Dict, List, Optional, Tuple
 
+import numpy as np
 import torch
 
 from . import ops
 from .aggregate import aggregate_sorted, dense_aggregate
 from .aggregate_task_spec import SortAggregateTaskSpec
 from .block import (Block, BlockAccessor, BlockExecStats, BlockMetadata, DeviceBlock, DeviceBlockAccessor,
-                    _as_device_block, _contig, default_device, find_partition_indices)
+                    _as_device_block, _contig, boundary_codes, default_device, find_partition_indices)
 from .interfaces import ExchangeTaskScheduler, ExchangeTaskSpec, RefBundle, StatsDict, TaskContext
 from .shuffle_task_spec import ShuffleTaskSpec
 from .sort_task_spec import SortKey, SortTaskSpec
@@ -406,10 +407,25 @@ def _distributed_exchange(spec: ExchangeTaskSpec, blocks: List[DeviceBlock], out
         return [DeviceBlock.empty(dev) for _ in range(parts)]
     if type(spec) is SortTaskSpec:
         _, sort_key = spec._map_args
-        if sort_key.boundaries:
-            raise NotImplementedError("user-specified boundaries are not supported across ranks")
         if any(local.validity(c) is not None for c in sort_key.get_columns()):
             raise NotImplementedError("nullable sort keys are not supported across ranks")
+        boundaries = spec._map_args[0]
+        if not isinstance(boundaries, AutoBoundaries) and len(boundaries) > 0:
+            # user boundaries (already in partition order): the partitions are dealt to the ranks in order, every rank
+            # sorts its key range and cuts it at the boundaries that fall inside it
+            import torch.distributed as dist
+
+            first, desc = sort_key.get_columns()[0], sort_key.get_descending()
+            codes = boundary_codes(boundaries, local.key_column(first), desc).cpu().numpy().view(np.uint64)
+            splitters, edges = D.rank_splitters_from_boundaries(codes, dist.get_world_size(), desc)
+            out = D.dist_sort(local, sort_key, splitter_codes=splitters)
+            rank = dist.get_rank()
+            mine = list(boundaries[edges[rank]:edges[rank + 1] - 1]) if edges[rank + 1] > edges[rank] else []
+            if edges[rank + 1] == edges[rank]:
+                return []
+            if not mine or out.num_rows == 0:
+                return [out] + [DeviceBlock.empty(dev) for _ in range(len(mine))]
+            return _cut(out, find_partition_indices(out.key_column(first), mine, desc))
         out = D.dist_sort(local, sort_key)
         return _cut_sorted_evenly(out, sort_key.get_columns()[0], sort_key.get_descending(), parts)
     if type(spec) is ShuffleTaskSpec:

@@ -113,6 +113,40 @@ def main():
                 np.testing.assert_array_equal(np.concatenate([p[0] for p in parts]), ak[order])
                 np.testing.assert_array_equal(np.concatenate([p[1] for p in parts]), ap[order])
                 print(f"gensort records rows={m} prefix={bool(prefix)} desc={desc}: OK, rows per rank {[len(p[0]) for p in parts]}", flush=True)
+    # user boundaries across ranks (planner/sort.py:47-54): the partitions are dealt to the ranks in order; the blocks of
+    # all ranks, in rank order, are the reference's partitions (rows equal to a boundary included on the right side)
+    bk = rng.integers(0, 1000, 50_000 + 100 * rank, dtype=np.int64)
+    brow = np.arange(len(bk), dtype=np.int64) + rank * 10_000_000
+    for bounds in ([100, 250, 251, 600, 999, 5000], [500], [10, 20, 30, 40, 50, 60, 70, 80, 90]):
+        for desc in (False, True):
+            res = rd.from_numpy_columns({"k": bk, "row": brow}, override_num_blocks=3).sort("k", descending=desc, boundaries=bounds)
+            sizes = [b.num_rows for b in res.get_internal_block_refs()]
+            got = res.to_numpy()["row"]
+            parts, ins = gather_np((sizes, got), world, rank), gather_np((bk, brow), world, rank)
+            if rank == 0:
+                ak, ar = np.concatenate([x[0] for x in ins]), np.concatenate([x[1] for x in ins])
+                order = orc.stable_argsort(ak, desc)
+                np.testing.assert_array_equal(np.concatenate([p[1] for p in parts]), ar[order])
+                sk = ak[order]
+                bs = sorted(bounds, reverse=desc)
+                cuts = [int((sk >= b).sum()) if desc else int((sk < b).sum()) for b in bs]
+                want_sizes = np.diff([0] + cuts + [len(sk)]).tolist()
+                assert [x for p in parts for x in p[0]] == want_sizes, (bounds, desc, [p[0] for p in parts], want_sizes)
+                print(f"sort with user boundaries {bounds} desc={desc}: OK, blocks per rank {[len(p[0]) for p in parts]}", flush=True)
+    # groupby by two key columns across ranks
+    g1, g2 = rng.integers(0, 40, n, dtype=np.int64), rng.integers(0, 25, n, dtype=np.int64)
+    gvv = rng.integers(-100, 100, n, dtype=np.int64)
+    got = rd.from_numpy_columns({"a": g1, "b": g2, "v": gvv}, override_num_blocks=4).groupby(["a", "b"]).aggregate(Sum("v"), Count()).to_numpy()
+    parts, ins = gather_np(got, world, rank), gather_np((g1, g2, gvv), world, rank)
+    if rank == 0:
+        A1, A2, AV = (np.concatenate([p[i] for p in ins]) for i in range(3))
+        cat = {c: np.concatenate([p[c] for p in parts]) for c in parts[0]}
+        combo = A1 * 1000 + A2
+        keys, inv = np.unique(combo, return_inverse=True)
+        np.testing.assert_array_equal(cat["a"] * 1000 + cat["b"], keys)
+        np.testing.assert_array_equal(cat["sum(v)"], np.bincount(inv, weights=AV).astype(np.int64))
+        np.testing.assert_array_equal(cat["count()"], np.bincount(inv))
+        print("groupby by two key columns: OK, groups per rank", [len(p["a"]) for p in parts], flush=True)
     # groupby
     gk = rng.integers(0, 3000, n, dtype=np.int64)
     gv = rng.integers(-2**31, 2**31, n, dtype=np.int64)

@@ -141,3 +141,22 @@ def test_rank_without_rows_adopts_the_schema_on_gloo():
     for p in procs:
         p.join(timeout=60)
     assert all(r[0] == "ok" for r in res), res
+
+
+def test_rank_splitters_from_user_boundaries():
+    """Which boundary separates which ranks (planner/sort.py:47-54 across ranks): R partitions dealt to W ranks in
+    order; equal-to-boundary rows go right when ascending, left when descending (util.py:745-758)."""
+    codes = np.array([10, 20, 30, 40, 50], dtype=np.uint64)            # 6 partitions
+    sp, edges = D.rank_splitters_from_boundaries(codes, 3, False)
+    assert edges == [0, 2, 4, 6] and sp.tolist() == [20, 40]
+    sp, edges = D.rank_splitters_from_boundaries(codes, 3, True)       # descending: boundary + 1 (codes are complemented)
+    assert sp.tolist() == [21, 41]
+    sp, edges = D.rank_splitters_from_boundaries(np.array([7], dtype=np.uint64), 4, False)   # 2 partitions, 4 ranks
+    assert edges == [0, 0, 1, 1, 2] and sp.tolist() == [0, 7, 7]
+    top = np.uint64(0xFFFFFFFFFFFFFFFF)
+    sp, _ = D.rank_splitters_from_boundaries(np.array([top], dtype=np.uint64), 2, True)
+    assert sp.tolist() == [int(top)]
+    # ownership under the device rule: owner = number of splitters <= code
+    sp, edges = D.rank_splitters_from_boundaries(codes, 3, False)
+    owner = lambda c: int((sp <= np.uint64(c)).sum())                   # noqa: E731
+    assert [owner(c) for c in (0, 19, 20, 39, 40, 99)] == [0, 0, 1, 1, 2, 2]
