@@ -438,9 +438,10 @@ def _distributed_exchange(spec: ExchangeTaskSpec, blocks: List[DeviceBlock], out
     _, key, aggs = spec._map_args
     k = key[0] if isinstance(key, list) and len(key) == 1 else key
     out = D.dist_aggregate(local, k, aggs)
-    if k is None:
+    if k is None or (isinstance(k, list) and not k) or not out.columns:
         return [out]
-    return _cut_sorted_evenly(out, k, False, parts)
+    # output blocks are cut on the first key column (rows equal in it stay together)
+    return _cut_sorted_evenly(out, k[0] if isinstance(k, list) else k, False, parts)
 
 
 class _AsyncCuts:
