@@ -561,6 +561,9 @@ def run_ours(args):
                 "roofline_ms": max(t_hbm, t_nvl) * 1e3, "hbm_roofline_ms": t_hbm * 1e3, "nvlink_roofline_ms": t_nvl * 1e3,
                 "note": "op-level: algorithmic bytes / step time against the slower roofline (SURVEY.md 8d); rank 0's "
                         "kernels are under `kernels` (the key sort overlaps the payload exchange)"}
+        roofline_op = {"bound": bound, "achieved": ach, "peak": pk, "unit": "GB/s", "frac": ach / pk,
+                       "algorithmic_bytes": "row_bytes x rows x (G-1)/G per GPU and direction (SURVEY.md 8d)" if bound == "nvlink"
+                       else "2 x row_bytes x rows (SURVEY.md 8d)", "peak_source": pk_src}
         if 7 in kernel_times:
             x_ms = kernel_times[7][0] / args.steps
             roof["exchange_kernels"] = {"ms_per_step": x_ms, "stored_gbs_per_direction": traffic / (x_ms / 1e3) / 1e9,
