@@ -344,12 +344,11 @@ def run_ours(args):
     nblocks = 8
     # synthetic input, generated once on the device (seeded per rank); a pinned host copy feeds the e2e leg
     d_key, d_pay = make_records(n, rank, dev)
-    h_key = h_pay = None
-    if not args.no_e2e:
-        h_key = torch.empty((n, KEY_BYTES), dtype=torch.uint8).pin_memory()
-        h_pay = torch.empty((n, PAYLOAD_BYTES), dtype=torch.uint8).pin_memory()
-        h_key.copy_(d_key)
-        h_pay.copy_(d_pay)
+    h_rec = None
+    if not args.no_e2e:      # the e2e leg's input on the host: row-oriented 100-byte records, as a gensort file holds them
+        h_rec = torch.empty((n, ROW_BYTES), dtype=torch.uint8).pin_memory()
+        h_rec[:, :KEY_BYTES].copy_(d_key)
+        h_rec[:, KEY_BYTES:].copy_(d_pay)
     ds = rd.from_torch_columns({"key": d_key, "payload": d_pay}, override_num_blocks=nblocks, records=True, key_prefix=["key"])
     ds_noprefix = None
     if world == 1 and not args.no_extras:   # the same records without the key prefix column (extras)
@@ -415,8 +414,7 @@ def run_ours(args):
     if not args.no_e2e:
         cap = int(n * (1.0 if world == 1 else 1.25))
         try:
-            o_key = torch.empty((cap, KEY_BYTES), dtype=torch.uint8).pin_memory()
-            o_pay = torch.empty((cap, PAYLOAD_BYTES), dtype=torch.uint8).pin_memory()
+            o_rec = torch.empty((cap, ROW_BYTES), dtype=torch.uint8).pin_memory()
         except RuntimeError as err:      # the host cannot pin another 14 GB per rank: no end-to-end leg (every rank agrees)
             pinned_ok, e2e = False, {"unavailable": f"pinned host allocation failed: {err}"[:200]}
         if world > 1:
@@ -433,11 +431,10 @@ def run_ours(args):
             # H2D of this step's inputs + ingest into records + sort on the main stream; egress (records -> dense
             # columns) + D2H of the result on a second stream, so that the D2H of step i overlaps the H2D of step
             # i+1 (PCIe is full duplex). Every step copies all of its inputs in and all of its result out.
-            k = h_key.to(dev, non_blocking=True)
-            p = h_pay.to(dev, non_blocking=True)
-            res = rd.from_torch_columns({"key": k, "payload": p}, override_num_blocks=nblocks, records=True,
-                                        key_prefix=["key"]).sort("key")
-            del k, p
+            d = h_rec.to(dev, non_blocking=True)
+            res = rd.from_torch_columns({"key": d[:, :KEY_BYTES], "payload": d[:, KEY_BYTES:]}, override_num_blocks=nblocks,
+                                        records=True, key_prefix=["key"]).sort("key")
+            del d
             done = torch.cuda.Event()
             done.record()
             if prev["done"] is not None:      # the buffers the previous D2H read from are released only once it is over
@@ -451,10 +448,9 @@ def run_ours(args):
                     if m > 0:
                         if m < b.num_rows:
                             b = b.slice(0, m)
-                        dk, dp = _contig(b["key"]), _contig(b["payload"])
-                        o_key[lo:lo + m].copy_(dk, non_blocking=True)
-                        o_pay[lo:lo + m].copy_(dp, non_blocking=True)
-                        objs.append((dk, dp))
+                        dense = b.rows_as_bytes(["key", "payload"])       # records -> dense 100-byte rows
+                        o_rec[lo:lo + m].copy_(dense, non_blocking=True)
+                        objs.append(dense)
                         lo += m
                 ev = torch.cuda.Event()
                 ev.record()
@@ -478,7 +474,7 @@ def run_ours(args):
         e_ms = f0.elapsed_time(f1)
         prev["objs"] = None
         m = min(got, 200_000)
-        hk = o_key[:m].numpy()
+        hk = o_rec[:m, :KEY_BYTES].numpy()
         order_ok = all(bytes(hk[i]) <= bytes(hk[i + 1]) for i in range(0, m - 1, max(1, m // 2000)))
         assert order_ok, "e2e result is not sorted"
         if world > 1:
@@ -487,9 +483,10 @@ def run_ours(args):
             e_ms = float(t.item())
         e2e = {"value": total_rows / (e_ms / e_steps / 1e3), "unit": "rows/s", "h2d_bytes_per_step": n * ROW_BYTES,
                "d2h_bytes_per_step": int(got * ROW_BYTES), "ms_per_step": e_ms / e_steps, "steps": e_steps,
-               "note": "per rank and step: H2D of key + payload columns, ingest into 128-byte records, Dataset.sort, "
-                       "egress to dense columns, D2H of the whole sorted result"}
-        del o_key, o_pay, h_key, h_pay
+               "note": "per rank and step: H2D of the 100-byte records (row-oriented, as a gensort file holds them), ingest "
+                       "into 128-byte records + key prefix, Dataset.sort, egress to dense 100-byte rows, D2H of the whole "
+                       "sorted result"}
+        del o_rec, h_rec
 
     # ---------------- side measurements (reported under "extras", not the metric)
     extras = None

@@ -336,3 +336,21 @@ def test_record_exchange_kernels_with_local_peers(n, world, cuda_device):
     want = src.cpu().numpy()[idx.cpu().numpy()].copy()
     want[:, 40:] = 0
     np.testing.assert_array_equal(out.cpu().numpy(), want)
+
+
+def test_row_oriented_ingest_and_egress(cuda_device):
+    """Records that arrive row-oriented (one [n, 100] buffer, the gensort file format) become a record block with ONE
+    copy per row run, and leave the same way (`rows_as_bytes`)."""
+    key, payload = _gensort(20_000, 44, 300, 50)
+    rows = np.concatenate([key, payload], axis=1)
+    d = torch.from_numpy(rows).to(cuda_device)
+    ds = rd.from_torch_columns({"key": d[:, :10], "payload": d[:, 10:]}, override_num_blocks=3, records=True, key_prefix=["key"])
+    blk = DeviceBlock.concat(ds.get_internal_block_refs())
+    np.testing.assert_array_equal(blk.rows_as_bytes().cpu().numpy(), rows)
+    np.testing.assert_array_equal(blk.rows_as_bytes(["payload"]).cpu().numpy(), payload)
+    out = DeviceBlock.concat(ds.sort("key").get_internal_block_refs())
+    want = rows[orc.stable_argsort_bytes(key, False)]
+    np.testing.assert_array_equal(out.rows_as_bytes().cpu().numpy(), want)
+    # dense columns go through the same call
+    dense = DeviceBlock.from_numpy({"key": key, "payload": payload}, cuda_device)
+    np.testing.assert_array_equal(dense.rows_as_bytes().cpu().numpy(), rows)
