@@ -166,7 +166,7 @@ def run_reference(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "gb_per_s": value * 2 * ROW_BYTES / 1e9,
-        "config": dict(workload_config(args.rows, max(args.gpus, 1), 8), cpu_sample_rows=rows),
+        "config": workload_config(args.rows, max(args.gpus, 1), 8),      # the GPU arm's config, key for key
         "cpu_baseline": {"value": value, "unit": "rows/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
