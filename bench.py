@@ -320,7 +320,6 @@ def verify(out_blocks, before, world: int, rank: int, dev):
 def run_ours(args):
     import ctypes
 
-    import numpy as np
     import torch
     import torch.distributed as dist
 
@@ -590,7 +589,6 @@ def run_ours(args):
 def run_extras(rd, dev, nblocks, ds_noprefix, n_main):
     """The other operators / shapes of the path on one GPU: round 1's 72-byte sort, random_shuffle (configs[1]) and
     groupby-aggregate (configs[2], uniform and Zipf(1.1) keys)."""
-    import numpy as np
     import torch
 
     from ray_project_ray_b200.aggregate import Count, Mean, Sum

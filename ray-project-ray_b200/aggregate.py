@@ -34,7 +34,7 @@ from typing import Callable, Dict, List, Optional, Sequence, Tuple
 import torch
 
 from . import ops
-from .block import DeviceBlock, VALID_SEP, _contig, valid_name
+from .block import DeviceBlock, _contig, valid_name
 
 SEP = "::"
 

@@ -1,7 +1,6 @@
 """GPU tests of the record layout (several columns of a row side by side in one record at a 16-byte
 aligned pitch, block.py "Record layout") and of the tie repair of multi-column sorts. Everything is
 compared bit for bit with the CPU oracle on the same inputs; the kernels are called through the C ABI."""
-import ctypes
 
 import numpy as np
 import pytest
