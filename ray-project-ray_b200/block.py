@@ -139,16 +139,27 @@ _NP_UNSIGNED_VIEW = {np.dtype(np.uint64): (np.int64, "uint64"), np.dtype(np.uint
                      np.dtype(np.uint16): (np.int16, "uint16")}
 
 
+def _from_numpy(col: np.ndarray) -> torch.Tensor:
+    """torch view of a host array that is only read (Arrow buffers are read-only: no copy just to silence torch)."""
+    if col.flags.writeable:
+        return torch.from_numpy(col)
+    import warnings
+
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore", UserWarning)
+        return torch.from_numpy(col)
+
+
 def _to_device(col: np.ndarray, device: torch.device) -> torch.Tensor:
     col = np.ascontiguousarray(col)
     if col.dtype in _NP_UNSIGNED_VIEW:
         signed, name = _NP_UNSIGNED_VIEW[col.dtype]
-        return torch.from_numpy(col.view(signed)).to(device, non_blocking=True).view(getattr(torch, name))
+        return _from_numpy(col.view(signed)).to(device, non_blocking=True).view(getattr(torch, name))
     if col.dtype == np.bool_:
         col = col.view(np.uint8)
     if col.dtype not in _NP_TO_TORCH:
         raise TypeError(f"column dtype {col.dtype} is not a fixed-width type the device block format holds")
-    return torch.from_numpy(col).to(device, non_blocking=True)
+    return _from_numpy(col).to(device, non_blocking=True)
 
 
 def _to_host(t: torch.Tensor) -> np.ndarray:

@@ -189,3 +189,59 @@ def test_randomize_block_order_equals_reference_order():
         assert [int(r.blocks[0][0].columns["row"][0]) for r in out] == want
         assert list(stats) == ["RandomizeBlockOrder"] and len(stats["RandomizeBlockOrder"]) == 9
     assert generate_randomize_blocks_fn(RandomizeBlocks(None, seed=1))([], None) == ([], {"RandomizeBlockOrder": []})
+
+
+def test_record_layout_helpers_on_host_tensors():
+    """Pitch detection, member views and the copy-free re-join of record slices are plain stride arithmetic."""
+    import torch
+
+    from ray_project_ray_b200.block import _inner, _join_views, _row_pitch, auto_pitch, member_view
+
+    assert [auto_pitch(x) for x in (1, 16, 17, 33, 64, 65, 100, 128, 129, 300)] == [16, 16, 32, 64, 64, 128, 128, 128, 256, 384]
+    rec = torch.arange(10 * 128, dtype=torch.int64).to(torch.uint8).reshape(10, 128)
+    key = member_view(rec, 0, torch.uint8, (10,))
+    pay = member_view(rec, 10, torch.uint8, (90,))
+    val = member_view(rec, 104, torch.int64, ())
+    assert key.shape == (10, 10) and pay.shape == (10, 90) and val.shape == (10,)
+    assert _row_pitch(key) == 128 and _row_pitch(pay) == 128 and _row_pitch(val) == 128 and _row_pitch(rec) is None
+    assert _inner(pay) == (90, True) and _inner(val) == (8, True)
+    assert torch.equal(pay, rec[:, 10:100]) and torch.equal(val, rec[:, 104:112].contiguous().view(torch.int64).reshape(-1))
+    parts = [pay[0:3], pay[3:4], pay[4:10]]
+    joined = _join_views(parts)
+    assert joined.data_ptr() == pay.data_ptr() and joined.shape == (10, 90) and torch.equal(joined, pay)
+    other = pay.clone()                                        # a separate allocation is copied, not aliased
+    cat = _join_views([pay[0:3], other[3:10]])
+    assert cat.data_ptr() != pay.data_ptr() and torch.equal(cat, pay)
+    transposed = torch.zeros(4, 6).t()                         # not dense inside a row: neither a record member nor joined
+    assert _row_pitch(transposed) is None
+
+
+def test_hidden_validity_columns_on_host_blocks():
+    """Nullable columns at the edges of the path (no kernel involved): Arrow nulls in, hidden `::valid` column, schema
+    and column names without it, `select` and `concat` keep it, Arrow nulls / NaN / None out."""
+    import pyarrow as pa
+    import torch
+
+    from ray_project_ray_b200.block import DeviceBlock, DeviceBlockAccessor, is_hidden, valid_name
+
+    cpu = torch.device("cpu")
+    t = pa.table({"k": [1, 2, 3, 4], "v": pa.array([1.5, None, 3.5, None]), "i": pa.array([7, 8, None, 9])})
+    b = DeviceBlock.from_arrow(t, cpu)
+    assert b.visible_names() == ["k", "v", "i"] and b.schema().names == ["k", "v", "i"]
+    assert [c for c in b.column_names if is_hidden(c)] == [valid_name("v"), valid_name("i")]
+    assert b.validity("k") is None and b.validity("v").tolist() == [1, 0, 1, 0]
+    host = b.to_numpy()
+    assert np.isnan(host["v"][[1, 3]]).all() and host["v"][0] == 1.5
+    assert host["i"].dtype == np.float64 and np.isnan(host["i"][2]) and host["i"][3] == 9      # as pyarrow's to_numpy
+    back = b.to_arrow()
+    assert back["v"].to_pylist() == [1.5, None, 3.5, None] and back["i"].to_pylist() == [7, 8, None, 9]
+    rows = list(DeviceBlockAccessor(b).iter_rows())
+    assert rows[1] == {"k": 2, "v": None, "i": 8.0} and rows[2]["i"] is None
+    sel = b.select(["v"])
+    assert sel.column_names == ["v", valid_name("v")] and sel.schema().names == ["v"]
+    plain = DeviceBlock.from_arrow(pa.table({"k": [5], "v": [9.0], "i": [1]}), cpu)            # no nulls: no hidden columns
+    assert not any(is_hidden(c) for c in plain.column_names)
+    both = DeviceBlock.concat([b, plain])
+    assert both.num_rows == 5 and both.validity("v").tolist() == [1, 0, 1, 0, 1] and both.validity("i").tolist() == [1, 1, 0, 1, 1]
+    with pytest.raises(ValueError):
+        DeviceBlock.from_arrow(pa.table({"s": pa.array([b"ab", None], type=pa.binary(2))}), cpu)
