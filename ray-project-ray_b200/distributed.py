@@ -142,6 +142,23 @@ def p2p_available(dev: torch.device, group=None) -> bool:
     return bool(_p2p_ok["state"])
 
 
+def chunk_layout_from_tables(tables: np.ndarray, rank: int) -> Tuple[List[int], List[int]]:
+    """Where the chunks of a chunked exchange land in rank `rank`'s receive buffers. `tables[r, c, d]` = rows among
+    source rank r's first c chunks that go to rank d (`tables[r, K, d]` = all of r's rows for d). Buffers are filled
+    in source-rank order, every source's rows in row order, so chunk c of source r fills the slots
+    [base_r + tables[r, c, rank], base_r + tables[r, c + 1, rank]) with base_r = rows of the lower source ranks.
+    Returns (starts, sizes): starts[r * K + c] = first slot of chunk c of source r (ascending); sizes[c] = rows of
+    chunk c over all sources."""
+    world, K = tables.shape[0], tables.shape[1] - 1
+    starts, sizes = [], [0] * K
+    for r in range(world):
+        base = int(tables[:r, K, rank].sum())
+        for c in range(K):
+            starts.append(base + int(tables[r, c, rank]))
+            sizes[c] += int(tables[r, c + 1, rank] - tables[r, c, rank])
+    return starts, sizes
+
+
 class P2PExchange:
     """Fused gather + exchange over peer memory. `columns` maps name -> (source column, row order or
     None). Row i of the send order (row order[i] of the source) goes to the rank that owns it, written
@@ -200,17 +217,8 @@ class P2PExchange:
                                       copy_bytes=copy_bytes, src_offset=src_offset, row0=row0, nrows=nrows)
 
     def chunk_layout(self) -> Tuple[List[int], List[int]]:
-        """(starts, sizes): starts[r * K + c] = first slot of this rank's receive buffers that chunk c of source rank r
-        fills (ascending); sizes[c] = rows of chunk c over all sources."""
-        K = self.tables.shape[1] - 1
-        starts, sizes = [], [0] * K
-        for r in range(self.world):
-            base = int(self.C[:r, self.rank].sum())
-            for c in range(K):
-                starts.append(base + int(self.tables[r, c, self.rank]))
-                sizes[c] += int(self.tables[r, c + 1, self.rank] - self.tables[r, c, self.rank])
-        return starts, sizes
-
+        """(starts, sizes) of the chunks in this rank's receive buffers: see `chunk_layout_from_tables`."""
+        return chunk_layout_from_tables(self.tables, self.rank)
 
     def fence(self) -> None:
         """Device-side barrier over all ranks on the current stream (symmetric-memory signal pads): before

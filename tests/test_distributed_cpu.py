@@ -160,3 +160,32 @@ def test_rank_splitters_from_user_boundaries():
     sp, edges = D.rank_splitters_from_boundaries(codes, 3, False)
     owner = lambda c: int((sp <= np.uint64(c)).sum())                   # noqa: E731
     assert [owner(c) for c in (0, 19, 20, 39, 40, 99)] == [0, 0, 1, 1, 2, 2]
+
+
+def test_chunk_layout_of_a_chunked_exchange():
+    """Bookkeeping of the chunked record exchange: which receive slots every (source rank, chunk) fills. Checked
+    against a brute-force simulation of the stable split."""
+    rng = np.random.default_rng(5)
+    world, K = 3, 4
+    n = [1000, 0, 777]
+    owners = [rng.integers(0, world, m) for m in n]
+    cuts = [[(c * m) // K for c in range(K)] + [m] for m in n]                      # chunk c = rows [cuts[c], cuts[c+1])
+    tables = np.zeros((world, K + 1, world), dtype=np.int64)
+    for r in range(world):
+        for c in range(K + 1):
+            tables[r, c] = np.bincount(owners[r][:cuts[r][c]], minlength=world)
+    for me in range(world):
+        starts, sizes = D.chunk_layout_from_tables(tables, me)
+        assert starts == sorted(starts) and sum(sizes) == sum(int((o == me).sum()) for o in owners)
+        # simulate: the receive buffer is filled source by source, rows in row order; label every slot with its chunk
+        label = []
+        for r in range(world):
+            for i in np.flatnonzero(owners[r] == me):
+                label.append((r, int(np.searchsorted(cuts[r], i, side="right")) - 1))
+        for r in range(world):
+            for c in range(K):
+                lo = starts[r * K + c]
+                hi = starts[r * K + c + 1] if r * K + c + 1 < len(starts) else len(label)
+                got = [x for x in label[lo:hi] if x[0] == r]                          # (empty chunks share their start)
+                assert all(x == (r, c) for x in got) and len(got) == int(tables[r, c + 1, me] - tables[r, c, me])
+        assert sizes == [sum(1 for x in label if x[1] == c) for c in range(K)]
